@@ -1,0 +1,181 @@
+/*
+ * fdlp_b200.h -- C ABI of libfdlp_b200.so: the B200 (sm_100a) FDLP-spectrogram / mel-spectrogram
+ * feature-extraction hot path of sadhusamik/speech_recognition_tools, behind plain C entry points.
+ *
+ * The reference has no FFI: its hot path is the Python function `getFeats(args)`
+ * (src/featgen/computeFDLPSpectrogram.py:29-237) calling numpy/scipy.  The entry points below are what a
+ * ctypes binding in that file would call instead of the inner loops (INTEGRATION.md shows the stub):
+ *
+ *   fdlp_plan_create    <- one-time setup of getFeats: filterbank (computeFDLPSpectrogram.py:49-63,
+ *                          features.py:172-219), mask/lifter/gamma weights (:94-118) and the derived
+ *                          integer geometry (:104,173,201-204,220-221; features.py:134-135)
+ *   fdlp_forward        <- the per-utterance body (:159-227): noise mix (features.py:24-31), getFrames
+ *                          (features.py:118-154), DCT (:178), the (segment, band) hot loop (:188-218:
+ *                          computeLpcFast features.py:222-230, computeModSpecFromLpc features.py:233-246,
+ *                          envelope :201-205), overlap-add (:207-225), log (:227) -- for a packed batch
+ *   mel_plan_create / mel_forward <- compute_mel_spectrum (src/featgen/computeMelSpectrum.py:40-157)
+ *   cmvn partial sums   <- Kaldi `compute-cmvn-stats` (e2e/wsj/run_fdlp_e1.sh:280), accumulated in the
+ *                          last kernel; the cross-GPU sum is an NCCL all-reduce done by the host.
+ *
+ * Conventions
+ *   - every function returns an int status: 0 = ok, <0 = error (FDLP_E_*); no C++ exception crosses the ABI;
+ *   - "dev" pointers are device pointers owned by the caller (e.g. torch tensors' data_ptr()); the library
+ *     only borrows them for the duration of the stream-ordered work it enqueues;
+ *   - "host" pointers are read during the call only;
+ *   - the plan owns its tables (filterbank, twiddles, windows, cosine basis) and its scratch buffers;
+ *     one plan per (device, configuration); a plan is not re-entrant, distinct plans are independent;
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); nothing synchronises the device
+ *     except plan creation/destruction and scratch growth.
+ */
+#ifndef FDLP_B200_H
+#define FDLP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FDLP_OK 0
+#define FDLP_E_ARG (-1)         /* invalid argument / unsupported configuration            */
+#define FDLP_E_CUDA (-2)        /* a CUDA runtime call failed (see fdlp_last_error)         */
+#define FDLP_E_UNSUPPORTED (-3) /* segment length not factorable into radices 2,3,4,5 etc. */
+#define FDLP_E_NOMEM (-4)
+
+/* per-utterance status bits written by fdlp_forward (0 = clean) */
+#define FDLP_ST_SINGULAR 1 /* a Levinson step hit a zero/non-finite prediction error (reference: LinAlgError) */
+#define FDLP_ST_NONFINITE 2 /* gain <= 0 or non-finite: the band is NaN in the reference as well              */
+
+#define FDLP_FBANK_MEL 0      /* createFbank(nfilters, 2N, srate, warp)                 features.py:172-190 */
+#define FDLP_FBANK_COCHLEAR 1 /* createFbankCochlear(nfilters, 2N, srate, om_w, alp, fixed, bet, warp) :197-219 */
+#define FDLP_FBANK_CUSTOM 2   /* caller-supplied [nfilters, N+1] float64 rows (host pointer)                 */
+
+#define FDLP_WAV_INT16 0
+#define FDLP_WAV_FLOAT32 1
+
+#define FDLP_NOISE_NONE 0
+#define FDLP_NOISE_INT16_WRAP 1 /* energies squared and averaged with int16 wrap-around, features.py:27-28 on int16 input */
+#define FDLP_NOISE_FLOAT 2      /* energies in floating point (float32 signal: float32 squares; float64 mean)  */
+
+typedef struct fdlp_plan fdlp_plan;
+typedef struct mel_plan mel_plan;
+
+/* Arguments of the reference's argparse surface that shape the computation
+ * (computeFDLPSpectrogram.py:241-262).  String options are pre-parsed by the Python host. */
+typedef struct {
+  int32_t srate;            /* 16000 */
+  int32_t nfilters;         /* --nfilters */
+  int32_t order;            /* --order */
+  int32_t coeff_num;        /* --coeff_num */
+  int32_t frate;            /* --frate */
+  double fduration;         /* --fduration */
+  double overlap_fraction;  /* --overlap_fraction as given by the user (the reference flips it to 1-x) */
+  int32_t fbank_kind;       /* FDLP_FBANK_* */
+  double fbank_args[5];     /* mel: {warp}; cochlear: {om_w, alp, fixed, bet, warp} (--fbank_type) */
+  const double* weights;    /* host, [coeff_num]: mask * lifter * gamma (and odd_mod_zero) folded, :94-118,194-200 */
+  const double* custom_fbank; /* host, [nfilters, N+1] when fbank_kind == FDLP_FBANK_CUSTOM, else NULL */
+  int32_t dct_fp32;         /* 0: float64 shared-memory FFT when it fits (default); 1: force float32 */
+} fdlp_params;
+
+/* Integer geometry derived exactly as the reference does (np.round = half-to-even). */
+typedef struct {
+  int32_t N;     /* segment length int(srate*fduration) */
+  int32_t S;     /* segment shift int(srate / (1/((1-of)*fduration))) */
+  int32_t M;     /* envelope FFT length 2*int(fduration*frate) */
+  int32_t kk;    /* round(fduration*frate) */
+  int32_t kkb2;  /* round(fduration*frate/2) */
+  int32_t kks;   /* round(fduration*frate*(1-of)) */
+  int32_t L;     /* min(coeff_num, M): cepstral coefficients that reach the envelope */
+  int32_t nlags; /* order + 2 */
+  int32_t dct_is_fp64;
+} fdlp_geometry;
+
+/* One packed batch.  All pointers are DEVICE pointers unless noted. */
+typedef struct {
+  const void* wav;              /* packed samples of all utterances, int16 or float32 */
+  int32_t wav_dtype;            /* FDLP_WAV_* */
+  int32_t n_utt;
+  int32_t n_seg;                /* total segments in the batch = sum_u ceil((T_u-1)/S) */
+  int64_t n_frames;             /* total output frames = sum_u ceil(T_u*frate/srate) */
+  int32_t max_utt_frames;       /* longest utterance of the batch, in frames */
+  const int64_t* utt_wav_off;   /* [n_utt+1] sample offsets into wav */
+  const int32_t* utt_seg_off;   /* [n_utt+1] first segment of each utterance */
+  const int64_t* utt_frame_off; /* [n_utt+1] first output frame of each utterance */
+  const int32_t* seg_utt;       /* [n_seg] owning utterance */
+  const int32_t* seg_ptr;       /* [n_seg] overlap-add frame pointer of the segment (jitter included,
+                                   computeFDLPSpectrogram.py:220-225), computed by the host */
+  /* optional noise mixing (features.py:24-31); noise_mode == FDLP_NOISE_NONE disables it */
+  int32_t noise_mode;
+  const void* noise;            /* noise samples, same dtype rules as the reference: int16 */
+  const int64_t* utt_noise_off; /* [n_utt] start offset into noise for each utterance (rand_num) */
+  const double* utt_snr_db;     /* [n_utt] SNR in dB */
+  /* outputs */
+  float* feats;                 /* [n_frames, nfilters] row-major log features */
+  double* cmvn_acc;             /* [2, nfilters+1] running sums (ADDED to; caller zeroes), or NULL */
+  int32_t* status;              /* [n_utt] FDLP_ST_* bits (OR-ed into; caller zeroes) */
+} fdlp_batch;
+
+const char* fdlp_last_error(void);
+int fdlp_version(void);
+
+int fdlp_plan_create(const fdlp_params* params, fdlp_plan** out_plan);
+int fdlp_plan_destroy(fdlp_plan* plan);
+int fdlp_plan_get_geometry(const fdlp_plan* plan, fdlp_geometry* out);
+/* copy the plan's filterbank ([nfilters, N], last column already dropped) to a host buffer */
+int fdlp_plan_get_fbank(const fdlp_plan* plan, double* host_out);
+/* bytes of scratch the plan will hold for a batch of n_seg segments */
+int64_t fdlp_plan_scratch_bytes(const fdlp_plan* plan, int32_t n_seg);
+
+/* the whole hot path for one packed batch, stream-ordered */
+int fdlp_forward(fdlp_plan* plan, const fdlp_batch* batch, void* stream);
+
+/* stage-level entry points (used by the parity tests to check each kernel against the oracle;
+ * they run the same kernels fdlp_forward launches, on the plan's scratch) */
+int fdlp_stage_dct(fdlp_plan* plan, const fdlp_batch* batch, double* dct_out /*[n_seg,N]*/, void* stream);
+int fdlp_stage_autocorr(fdlp_plan* plan, const double* dct /*[n_seg,N]*/, int32_t n_seg,
+                        double* r_out /*[n_seg,nfilters,nlags]*/, void* stream);
+int fdlp_stage_lpc_envelope(fdlp_plan* plan, const double* r /*[n_seg,nfilters,nlags]*/, int32_t n_seg,
+                            double* lpc_out /*[n_seg,nfilters,order+1] or NULL*/, double* gain_out /*[n_seg,nfilters] or NULL*/,
+                            double* cep_out /*[n_seg,nfilters,L] or NULL*/, double* env_out /*[n_seg,nfilters,kk]*/,
+                            int32_t* seg_status /*[n_seg] or NULL*/, void* stream);
+
+/* ---- mel-spectrogram baseline (computeMelSpectrum.py) ---- */
+typedef struct {
+  int32_t srate;
+  int32_t nfilters;
+  int32_t nfft;          /* --nfft (power of two) */
+  int32_t frate;
+  double fduration;      /* --fduration (0.02) */
+  int32_t fbank_kind;
+  double fbank_args[5];
+  const double* custom_fbank; /* host [nfilters, nfft/2+1] */
+  int32_t power;         /* 0: log10 (spectrum_type=log), 1: squared (spectrum_type=power) */
+} mel_params;
+
+typedef struct {
+  const void* wav;
+  int32_t wav_dtype;
+  int32_t n_utt;
+  int64_t n_frames;             /* sum_u ceil((T_u-1)/shift) */
+  const int64_t* utt_wav_off;   /* [n_utt+1] */
+  const int64_t* utt_frame_off; /* [n_utt+1] */
+  float* feats;                 /* [n_frames, nfilters] */
+  double* cmvn_acc;             /* [2, nfilters+1] or NULL */
+} mel_batch;
+
+int mel_plan_create(const mel_params* params, mel_plan** out_plan);
+int mel_plan_destroy(mel_plan* plan);
+int mel_plan_get_fbank(const mel_plan* plan, double* host_out /*[nfilters, nfft/2+1]*/);
+int mel_forward(mel_plan* plan, const mel_batch* batch, void* stream);
+
+/* ---- CMVN apply (ESPnet dump.sh / Kaldi apply-cmvn, e2e/wsj/run_fdlp_e1.sh:293-303) ---- */
+int cmvn_apply(float* feats /*dev [n_frames, dim], in place*/, int64_t n_frames, int32_t dim,
+               const double* stats /*dev [2, dim+1]*/, int32_t norm_vars, void* stream);
+
+/* FP64 pipe probe: runs a register-resident DFMA / DMMA loop and returns TFLOP/s (roofline denominator) */
+int fdlp_measure_fp64_peak(double* dfma_tflops, double* dmma_tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FDLP_B200_H */

@@ -1,0 +1,113 @@
+"""ctypes binding of libfdlp_b200.so (C ABI declared in include/fdlp_b200.h).
+
+The library is the product: there is no CPU fallback.  Importing this module without the built
+shared object raises ImportError with the build command (`make` / `__graft_entry__.build()`)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfdlp_b200.so")
+
+FDLP_OK = 0
+FDLP_E_ARG, FDLP_E_CUDA, FDLP_E_UNSUPPORTED, FDLP_E_NOMEM = -1, -2, -3, -4
+FDLP_ST_SINGULAR, FDLP_ST_NONFINITE = 1, 2
+FDLP_FBANK_MEL, FDLP_FBANK_COCHLEAR, FDLP_FBANK_CUSTOM = 0, 1, 2
+FDLP_WAV_INT16, FDLP_WAV_FLOAT32 = 0, 1
+FDLP_NOISE_NONE, FDLP_NOISE_INT16_WRAP, FDLP_NOISE_FLOAT = 0, 1, 2
+
+
+class FdlpParams(C.Structure):
+    _fields_ = [
+        ("srate", C.c_int32), ("nfilters", C.c_int32), ("order", C.c_int32), ("coeff_num", C.c_int32),
+        ("frate", C.c_int32), ("fduration", C.c_double), ("overlap_fraction", C.c_double),
+        ("fbank_kind", C.c_int32), ("fbank_args", C.c_double * 5),
+        ("weights", C.POINTER(C.c_double)), ("custom_fbank", C.POINTER(C.c_double)),
+        ("dct_fp32", C.c_int32),
+    ]
+
+
+class FdlpGeometry(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("N", "S", "M", "kk", "kkb2", "kks", "L", "nlags", "dct_is_fp64")]
+
+
+class FdlpBatch(C.Structure):
+    _fields_ = [
+        ("wav", C.c_void_p), ("wav_dtype", C.c_int32), ("n_utt", C.c_int32), ("n_seg", C.c_int32),
+        ("n_frames", C.c_int64), ("max_utt_frames", C.c_int32),
+        ("utt_wav_off", C.c_void_p), ("utt_seg_off", C.c_void_p), ("utt_frame_off", C.c_void_p),
+        ("seg_utt", C.c_void_p), ("seg_ptr", C.c_void_p),
+        ("noise_mode", C.c_int32), ("noise", C.c_void_p), ("utt_noise_off", C.c_void_p), ("utt_snr_db", C.c_void_p),
+        ("feats", C.c_void_p), ("cmvn_acc", C.c_void_p), ("status", C.c_void_p),
+    ]
+
+
+class MelParams(C.Structure):
+    _fields_ = [
+        ("srate", C.c_int32), ("nfilters", C.c_int32), ("nfft", C.c_int32), ("frate", C.c_int32),
+        ("fduration", C.c_double), ("fbank_kind", C.c_int32), ("fbank_args", C.c_double * 5),
+        ("custom_fbank", C.POINTER(C.c_double)), ("power", C.c_int32),
+    ]
+
+
+class MelBatch(C.Structure):
+    _fields_ = [
+        ("wav", C.c_void_p), ("wav_dtype", C.c_int32), ("n_utt", C.c_int32), ("n_frames", C.c_int64),
+        ("utt_wav_off", C.c_void_p), ("utt_frame_off", C.c_void_p), ("feats", C.c_void_p), ("cmvn_acc", C.c_void_p),
+    ]
+
+
+# every symbol include/fdlp_b200.h declares: (name, restype, argtypes)
+SYMBOLS = [
+    ("fdlp_last_error", C.c_char_p, []),
+    ("fdlp_version", C.c_int, []),
+    ("fdlp_plan_create", C.c_int, [C.POINTER(FdlpParams), C.POINTER(C.c_void_p)]),
+    ("fdlp_plan_destroy", C.c_int, [C.c_void_p]),
+    ("fdlp_plan_get_geometry", C.c_int, [C.c_void_p, C.POINTER(FdlpGeometry)]),
+    ("fdlp_plan_get_fbank", C.c_int, [C.c_void_p, C.c_void_p]),
+    ("fdlp_plan_scratch_bytes", C.c_int64, [C.c_void_p, C.c_int32]),
+    ("fdlp_forward", C.c_int, [C.c_void_p, C.POINTER(FdlpBatch), C.c_void_p]),
+    ("fdlp_stage_dct", C.c_int, [C.c_void_p, C.POINTER(FdlpBatch), C.c_void_p, C.c_void_p]),
+    ("fdlp_stage_autocorr", C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
+    ("fdlp_stage_lpc_envelope", C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p, C.c_void_p]),
+    ("mel_plan_create", C.c_int, [C.POINTER(MelParams), C.POINTER(C.c_void_p)]),
+    ("mel_plan_destroy", C.c_int, [C.c_void_p]),
+    ("mel_plan_get_fbank", C.c_int, [C.c_void_p, C.c_void_p]),
+    ("mel_forward", C.c_int, [C.c_void_p, C.POINTER(MelBatch), C.c_void_p]),
+    ("cmvn_apply", C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]),
+    ("fdlp_measure_fp64_peak", C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+]
+
+_lib = None
+
+
+def load():
+    """Load the shared library once; raise loudly if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "libfdlp_b200.so is not built (%s). Run `make` or `python -c 'import __graft_entry__ as g; g.build()'` "
+            "at the repository root. There is no CPU fallback." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, restype, argtypes in SYMBOLS:
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = restype
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+class FdlpError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("libfdlp_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+def check(rc):
+    if rc != FDLP_OK:
+        msg = load().fdlp_last_error()
+        raise FdlpError(rc, msg.decode("utf-8", "replace") if msg else "")

@@ -1,0 +1,129 @@
+// K3: sub-band windowing fused with the circular autocorrelation of the windowed DCT coefficients.
+//
+// Reference: band_dct = fbank[j, 0:-1] * cos_trans[i, :]   (src/featgen/computeFDLPSpectrogram.py:190-191)
+//            y = real(ifft(fft(x) * conj(fft(x))))          (src/featgen/features.py:223-225, computeLpcFast)
+//            of which only lags 0..order+1 are consumed     (features.py:226-228).
+//
+// r[k] = sum_n x[n] x[(n+k) mod N] is evaluated in direct form on the FP64 tensor path (DMMA.8x8x4):
+// view x as a matrix X[m][c] = x[8m + c] (N/8 rows of 8).  Then
+//     C_a[c][c'] = sum_m X[m][c] * X[(m+a) mod rows][c']        (an 8 x 8 x (N/8) GEMM per block a)
+// holds every product with lag 8a + (c' - c), so r[8a+d] is the sum of the d-th super-diagonal of C_a and
+// the (d-8)-th sub-diagonal of C_{a+1}.  Both DMMA operands are the SAME fragment pattern
+//     frag(r)[lane] = x[8 * (r + lane%4) + lane/4],
+// a contiguous 256-byte read per warp, so the windowed coefficients x = F_j * c are formed on the fly from
+// two coalesced global loads (no shared-memory staging) and kept in a register ring: a step of 4 rows
+// issues NA DMMAs (one per lag block) and fetches only 4 new fragments.  One warp owns one
+// (segment, band, lag-group); FP64 products and accumulation are mandatory.
+#pragma once
+#include "common.cuh"
+
+namespace fdlp {
+
+struct AcArgs {
+  const double* dct;     // [n_seg, N]
+  const double* fbank;   // [J, N]
+  const int32_t* row_lo; // [J] first 8-sample row (multiple of 4) with a non-zero tap
+  const int32_t* row_hi; // [J] one past the last such row (multiple of 4)
+  double* r;             // [n_seg, J, nlags]
+  int N, J, nlags, rows, n_seg;
+  int a_groups;          // lag groups per band (each NA blocks of 8 lags)
+  int na_total;          // a_groups * NA
+};
+
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
+constexpr int kAcWarps = 4;
+
+template <int NA>
+__global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_dmma_kernel(const AcArgs a) {
+  constexpr int RS = NA + 4;  // register ring of B fragments
+  constexpr int U = RS / 4;   // steps per unrolled group (ring indices become compile-time)
+  extern __shared__ __align__(16) double cs[];  // [bands_per_cta][na_total][8][8]
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int bands_per_cta = kAcWarps / a.a_groups;
+  const int nbg = (a.J + bands_per_cta - 1) / bands_per_cta;
+  const int seg = blockIdx.x / nbg;
+  const int bl = warp / a.a_groups;  // band slot in this CTA
+  const int band = (blockIdx.x % nbg) * bands_per_cta + bl;
+  const int a_base = (warp % a.a_groups) * NA;
+  const int lr = lane & 3, lc = lane >> 2;
+  const int rows = a.rows;
+
+  double acc[NA][2];
+#pragma unroll
+  for (int i = 0; i < NA; ++i) acc[i][0] = acc[i][1] = 0.0;
+
+  if (band < a.J) {
+    const double* __restrict__ c = a.dct + (size_t)seg * a.N;
+    const double* __restrict__ f = a.fbank + (size_t)band * a.N;
+    const int m_lo = a.row_lo[band], m_hi = a.row_hi[band];
+    const int nsteps = (m_hi - m_lo) >> 2;
+
+    auto frag = [&](int r) -> double {
+      const int idx = (((r + lr) % rows) << 3) + lc;
+      return __ldg(f + idx) * __ldg(c + idx);
+    };
+
+    double ring[RS];
+#pragma unroll
+    for (int i = 0; i < NA; ++i) ring[i] = frag(m_lo + a_base + i);
+#pragma unroll
+    for (int i = NA; i < RS; ++i) ring[i] = 0.0;
+    double a_next = (a_base == 0) ? 0.0 : frag(m_lo);
+
+    for (int s0 = 0; s0 < nsteps; s0 += U) {
+#pragma unroll
+      for (int s = 0; s < U; ++s) {
+        if (s0 + s < nsteps) {
+          const int m0 = m_lo + ((s0 + s) << 2);
+          // prefetch the 4 fragments the next step adds (they replace the 4 oldest ring slots)
+#pragma unroll
+          for (int t = 0; t < 4; ++t) ring[(4 * s + NA + t) % RS] = frag(m0 + a_base + NA + t);
+          double afrag;
+          if (a_base == 0) {
+            afrag = ring[(4 * s) % RS];
+          } else {
+            afrag = a_next;
+            a_next = frag(m0 + 4);
+          }
+#pragma unroll
+          for (int i = 0; i < NA; ++i) dmma884(acc[i][0], acc[i][1], afrag, ring[(4 * s + i) % RS]);
+        }
+      }
+    }
+  }
+
+  // ---- C fragments -> shared, then diagonal sums -> lags ----
+  {
+    double* my = cs + ((size_t)bl * a.na_total + a_base) * 64;
+#pragma unroll
+    for (int i = 0; i < NA; ++i) {
+      // lane holds C[row = lane/4][col = 2*(lane%4) + {0,1}]
+      *reinterpret_cast<double2*>(my + i * 64 + lc * 8 + 2 * lr) = make_double2(acc[i][0], acc[i][1]);
+    }
+  }
+  __syncthreads();
+  if (band < a.J) {
+    const double* mine = cs + (size_t)bl * a.na_total * 64;
+    double* rout = a.r + ((size_t)seg * a.J + band) * a.nlags;
+    const int sub = warp % a.a_groups;  // the a_groups warps of a band split the lags
+    for (int k = sub * 32 + lane; k < a.nlags; k += 32 * a.a_groups) {
+      const int ab = k >> 3, d = k & 7;
+      double s = 0.0;
+      const double* c0 = mine + ab * 64;
+      for (int row = 0; row + d < 8; ++row) s += c0[row * 8 + row + d];
+      if (d > 0) {
+        const double* c1 = c0 + 64;
+        for (int row = 8 - d; row < 8; ++row) s += c1[row * 8 + row + d - 8];
+      }
+      rout[k] = s;
+    }
+  }
+}
+
+}  // namespace fdlp

@@ -1,0 +1,209 @@
+// K1+K2: segment framing (reflect padding, Hamming) fused with the long DCT-II.
+//
+// Reference: getFrames (src/featgen/features.py:118-154) and
+//            scipy.fftpack.dct(time_frames) / sqrt(2N) (src/featgen/computeFDLPSpectrogram.py:174-178).
+//
+// One CTA per segment.  The DCT-II of length N is computed with Makhoul's reordering as a real FFT of
+// length N, itself done as an N/2-point complex FFT held entirely in shared memory (float64: 8N bytes,
+// 187.5 KB at N = 24000; float32 when 8N does not fit).  The FFT is an in-place decimation-in-frequency
+// mixed-radix (4/2/3/5) transform; its digit-reversed output order is absorbed by the unpack step through
+// a precomputed permutation.  Samples are fetched with 16-byte vector loads aligned on the global
+// address (8 int16 or 4 float32 per load); only segments touching an utterance edge take the scalar
+// reflect path.
+#pragma once
+#include "common.cuh"
+
+namespace fdlp {
+
+constexpr int kMaxRadixPasses = 16;
+
+struct DctArgs {
+  const void* wav;
+  const int64_t* utt_wav_off;
+  const int32_t* utt_seg_off;
+  const int32_t* seg_utt;
+  // optional noise mixing (features.py:24-31): sample = sig + alpha[u] * noise[noise_off[u] + q]
+  const int16_t* noise;
+  const int64_t* utt_noise_off;
+  const double* utt_alpha;
+  int N, S, n;  // n = N/2
+  int npass;
+  int radix[kMaxRadixPasses];
+  const double* ham;       // [N] np.hamming(N)
+  const double2* tw;       // [n] exp(-2 pi i k / n)
+  const int32_t* perm;     // [n] position of X[k] after the DIF passes
+  const double2* unpackA;  // [n+1] exp(-2 pi i k / N)
+  const double2* postB;    // [N]  exp(-i pi k / (2N)) * 2 / sqrt(2N)
+  double* out;             // [n_seg, N]
+  int vec_ok;              // wav base pointer is 16-byte aligned
+};
+
+template <typename T>
+__device__ __forceinline__ cplx<T> load_tw(const double2* tw, int idx) {
+  double2 w = __ldg(tw + idx);
+  return {(T)w.x, (T)w.y};
+}
+
+template <typename T, int R>
+__device__ __forceinline__ void dft_small(cplx<T>* a) {
+  if constexpr (R == 2) {
+    cplx<T> t = a[0];
+    a[0] = cadd(t, a[1]);
+    a[1] = csub(t, a[1]);
+  } else if constexpr (R == 4) {
+    cplx<T> t0 = cadd(a[0], a[2]), t1 = csub(a[0], a[2]);
+    cplx<T> t2 = cadd(a[1], a[3]), t3 = mulmj(csub(a[1], a[3]));
+    a[0] = cadd(t0, t2);
+    a[2] = csub(t0, t2);
+    a[1] = cadd(t1, t3);
+    a[3] = csub(t1, t3);
+  } else if constexpr (R == 3) {
+    const T s = (T)0.86602540378443864676;
+    cplx<T> t1 = cadd(a[1], a[2]);
+    cplx<T> t2 = {a[0].x - (T)0.5 * t1.x, a[0].y - (T)0.5 * t1.y};
+    cplx<T> t3 = mulmj(cscale(csub(a[1], a[2]), s));
+    a[0] = cadd(a[0], t1);
+    a[1] = cadd(t2, t3);
+    a[2] = csub(t2, t3);
+  } else if constexpr (R == 5) {
+    const T c1 = (T)0.30901699437494742410, c2 = (T)-0.80901699437494742410;
+    const T s1 = (T)0.95105651629515357212, s2 = (T)0.58778525229247312917;
+    cplx<T> t1 = cadd(a[1], a[4]), t2 = cadd(a[2], a[3]);
+    cplx<T> t3 = csub(a[1], a[4]), t4 = csub(a[2], a[3]);
+    cplx<T> m1 = {a[0].x + c1 * t1.x + c2 * t2.x, a[0].y + c1 * t1.y + c2 * t2.y};
+    cplx<T> m2 = {a[0].x + c2 * t1.x + c1 * t2.x, a[0].y + c2 * t1.y + c1 * t2.y};
+    cplx<T> n1 = mulmj(cplx<T>{s1 * t3.x + s2 * t4.x, s1 * t3.y + s2 * t4.y});
+    cplx<T> n2 = mulmj(cplx<T>{s2 * t3.x - s1 * t4.x, s2 * t3.y - s1 * t4.y});
+    a[0] = cadd(a[0], cadd(t1, t2));
+    a[1] = cadd(m1, n1);
+    a[4] = csub(m1, n1);
+    a[2] = cadd(m2, n2);
+    a[3] = csub(m2, n2);
+  }
+}
+
+// One decimation-in-frequency pass of radix R over sub-transforms of length L (in place).
+template <typename T, int R>
+__device__ __forceinline__ void fft_pass(cplx<T>* z, int n, int L, const double2* tw) {
+  const int sub = L / R;
+  const int nb = n / R;
+  const int twstep = n / L;
+  for (int b = threadIdx.x; b < nb; b += blockDim.x) {
+    const int blk = b / sub, j = b - blk * sub;
+    cplx<T>* p = z + blk * L + j;
+    cplx<T> a[R];
+#pragma unroll
+    for (int t = 0; t < R; ++t) a[t] = p[t * sub];
+    dft_small<T, R>(a);
+    p[0] = a[0];
+#pragma unroll
+    for (int u = 1; u < R; ++u) {
+      cplx<T> w = load_tw<T>(tw, j * u * twstep);
+      p[u * sub] = cmul(a[u], w);
+    }
+  }
+  __syncthreads();
+}
+
+template <typename S>
+__device__ __forceinline__ double sample_to_double(S v) { return (double)v; }
+
+// Scalar sample fetch with reflect padding and optional noise mixing.
+template <typename S>
+__device__ __forceinline__ double fetch_sample(const DctArgs& a, const S* sig, int64_t q, int64_t T, int u,
+                                               double alpha, const int16_t* nz) {
+  q = reflect_index(q, T);
+  double v = (double)sig[q];
+  if (nz) v += alpha * (double)nz[q];
+  return v;
+}
+
+template <typename T, typename S>
+__global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* sv = reinterpret_cast<T*>(smem_raw);  // v[] (real view) == z[] (complex view)
+  cplx<T>* z = reinterpret_cast<cplx<T>*>(smem_raw);
+
+  const int seg = blockIdx.x;
+  const int u = a.seg_utt[seg];
+  const int k = seg - a.utt_seg_off[u];
+  const int64_t woff = a.utt_wav_off[u];
+  const int64_t T_utt = a.utt_wav_off[u + 1] - woff;
+  const S* sig = reinterpret_cast<const S*>(a.wav) + woff;
+  const int N = a.N;
+  const int ext = (N % 2 == 0) ? N / 2 - 1 : (N - 1) / 2;
+  const int64_t q_base = (int64_t)k * a.S - ext;  // utterance-relative index of window sample 0
+  const int16_t* nz = a.noise ? a.noise + a.utt_noise_off[u] : nullptr;
+  const double alpha = a.noise ? a.utt_alpha[u] : 0.0;
+
+  // ---- load: coalesced / vectorised read of the windowed segment, scattered into Makhoul order ----
+  constexpr int VEC = 16 / (int)sizeof(S);
+  const int64_t g0 = woff + q_base;                 // global sample index of window sample 0 (may be < 0)
+  const int sh = (int)(((g0 % VEC) + VEC) % VEC);   // window sample i sits at global index g0+i; chunks start where that is 0 mod VEC
+  const int nchunk = (N + sh + VEC - 1) / VEC;
+  for (int c = threadIdx.x; c < nchunk; c += blockDim.x) {
+    const int i0 = c * VEC - sh;
+    const int64_t q0 = q_base + i0;
+    double v[VEC];
+    const bool interior = a.vec_ok && !nz && i0 >= 0 && i0 + VEC <= N && q0 >= 0 && q0 + VEC <= T_utt;
+    if (interior) {
+      const int4 raw = __ldg(reinterpret_cast<const int4*>(sig + q0));
+      const S* rs = reinterpret_cast<const S*>(&raw);
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) v[e] = (double)rs[e];
+    } else {
+#pragma unroll
+      for (int e = 0; e < VEC; ++e) {
+        const int i = i0 + e;
+        v[e] = (i >= 0 && i < N) ? fetch_sample<S>(a, sig, q0 + e, T_utt, u, alpha, nz) : 0.0;
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+      const int i = i0 + e;
+      if (i >= 0 && i < N) {
+        const double xw = v[e] * __ldg(a.ham + i);
+        const int vi = (i & 1) ? (N - 1 - (i >> 1)) : (i >> 1);
+        sv[vi] = (T)xw;
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- N/2-point complex FFT, in place, decimation in frequency ----
+  int L = a.n;
+  for (int p = 0; p < a.npass; ++p) {
+    const int R = a.radix[p];
+    if (R == 4) fft_pass<T, 4>(z, a.n, L, a.tw);
+    else if (R == 2) fft_pass<T, 2>(z, a.n, L, a.tw);
+    else if (R == 3) fft_pass<T, 3>(z, a.n, L, a.tw);
+    else fft_pass<T, 5>(z, a.n, L, a.tw);
+    L /= R;
+  }
+
+  // ---- unpack to the length-N real FFT, Makhoul post-twiddle, scale, store ----
+  double* out = a.out + (size_t)seg * N;
+  const int n = a.n;
+  for (int kq = threadIdx.x; kq <= n; kq += blockDim.x) {
+    const int k1 = (kq == n) ? 0 : kq;
+    const int k2 = (kq == 0) ? 0 : n - kq;
+    const cplx<T> zk = z[a.perm[k1]];
+    cplx<T> zc = z[a.perm[k2]];
+    zc.y = -zc.y;
+    const cplx<double> Zk = {(double)zk.x, (double)zk.y}, Zc = {(double)zc.x, (double)zc.y};
+    const cplx<double> E = {0.5 * (Zk.x + Zc.x), 0.5 * (Zk.y + Zc.y)};
+    const cplx<double> D = {0.5 * (Zk.x - Zc.x), 0.5 * (Zk.y - Zc.y)};
+    const double2 A = __ldg(a.unpackA + kq);
+    // V = E - j * A * D
+    const cplx<double> AD = cmul(cplx<double>{A.x, A.y}, D);
+    const cplx<double> V = {E.x + AD.y, E.y - AD.x};
+    const double2 B = __ldg(a.postB + kq);
+    out[kq] = B.x * V.x - B.y * V.y;  // Re(B * V), B carries 2/sqrt(2N)
+    if (kq > 0 && kq < n) {
+      const double2 B2 = __ldg(a.postB + (N - kq));
+      out[N - kq] = B2.x * V.x + B2.y * V.y;  // Re(B2 * conj(V))
+    }
+  }
+}
+
+}  // namespace fdlp

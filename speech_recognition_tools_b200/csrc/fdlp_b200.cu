@@ -1,0 +1,672 @@
+// libfdlp_b200.so -- C ABI (include/fdlp_b200.h) over the sm_100a kernels of the FDLP-spectrogram hot path.
+// Host side: plan construction (filterbanks, windows, twiddles, cosine basis -- the one-time setup of the
+// reference's getFeats, src/featgen/computeFDLPSpectrogram.py:43-118) and the stream-ordered launch sequence.
+#include <math.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "autocorr.cuh"
+#include "common.cuh"
+#include "dct.cuh"
+#include "lpc_env.cuh"
+#include "mel.cuh"
+#include "noise.cuh"
+#include "ola.cuh"
+
+namespace fdlp {
+thread_local char g_err[512] = "";
+
+// ---------------------------------------------------------------- numpy-compatible host helpers
+static double np_round_half_even(double x) { return nearbyint(x); }  // default rounding mode = to nearest even
+
+static std::vector<double> np_linspace(double start, double stop, int num) {
+  std::vector<double> v(num);
+  if (num == 1) { v[0] = start; return v; }
+  const double step = (stop - start) / (num - 1);
+  for (int i = 0; i < num; ++i) v[i] = start + i * step;
+  v[num - 1] = stop;
+  return v;
+}
+
+static std::vector<double> np_hamming(int M) {
+  std::vector<double> w(M);
+  if (M == 1) { w[0] = 1.0; return w; }
+  for (int i = 0; i < M; ++i) { const double n = (1 - M) + 2.0 * i; w[i] = 0.54 + 0.46 * cos(M_PI * n / (M - 1)); }
+  return w;
+}
+static std::vector<double> np_hanning(int M) {
+  std::vector<double> w(M);
+  if (M == 1) { w[0] = 1.0; return w; }
+  for (int i = 0; i < M; ++i) { const double n = (1 - M) + 2.0 * i; w[i] = 0.5 + 0.5 * cos(M_PI * n / (M - 1)); }
+  return w;
+}
+
+// createFbank, src/featgen/features.py:172-190
+static std::vector<double> make_mel_fbank(int nfilters, int nfft, int srate, double warp) {
+  const double mel_max = 2595 * log10(1 + (srate / warp) / 1400);
+  std::vector<double> fw = np_linspace(0, mel_max, nfilters + 2);
+  const int nbins = (int)floor(nfft / 2.0 + 1);
+  std::vector<double> f((size_t)nfilters * nbins, 0.0);
+  std::vector<double> bin(nfilters + 2);
+  for (int i = 0; i < nfilters + 2; ++i) {
+    const double hz = warp * (700 * (pow(10.0, fw[i] / 2595) - 1));
+    bin[i] = floor((nfft + 1) * hz / srate);
+  }
+  for (int m = 1; m <= nfilters; ++m) {
+    const int lo = (int)bin[m - 1], ce = (int)bin[m], hi = (int)bin[m + 1];
+    for (int k = lo; k < ce && k < nbins; ++k) f[(size_t)(m - 1) * nbins + k] = (k - bin[m - 1]) / (bin[m] - bin[m - 1]);
+    for (int k = ce; k < hi && k < nbins; ++k) f[(size_t)(m - 1) * nbins + k] = (bin[m + 1] - k) / (bin[m + 1] - bin[m]);
+  }
+  return f;
+}
+
+// createFbankCochlear + warp_func_bark, src/featgen/features.py:193-219
+static std::vector<double> make_cochlear_fbank(int nfilters, int nfft, int srate, double om_w, double alp, int fixed,
+                                               double bet, double warp) {
+  const double f_max = srate / 2.0;
+  auto bark = [&](double x) { return 6 * asinh((x / warp) / 600); };
+  std::vector<double> cf = np_linspace(0, bark(f_max), nfilters);
+  const int nbins = (int)floor(nfft / 2.0 + 1);
+  std::vector<double> fl = np_linspace(0, f_max, nbins);
+  std::vector<double> f((size_t)nfilters * nbins);
+  for (int i = 0; i < nfilters; ++i) {
+    const double fc = cf[i];
+    const double a = (fixed == 1) ? alp : alp * exp(-0.1 * fc);
+    for (int j = 0; j < nbins; ++j) {
+      const double d = bark(fl[j]) - fc;
+      double v;
+      if (d <= -om_w / 2) v = pow(10.0, a * (d + om_w / 2));
+      else if (d > -om_w / 2 && d < om_w / 2) v = 1.0;
+      else v = pow(10.0, -bet * (d - om_w / 2));
+      f[(size_t)i * nbins + j] = v;
+    }
+  }
+  return f;
+}
+
+static int factor_radices(int n, int* radix, int* npass) {
+  int e2 = 0, e3 = 0, e5 = 0;
+  while (n % 2 == 0) { n /= 2; ++e2; }
+  while (n % 3 == 0) { n /= 3; ++e3; }
+  while (n % 5 == 0) { n /= 5; ++e5; }
+  if (n != 1) return -1;
+  int c = 0;
+  for (int i = 0; i < e2 / 2; ++i) radix[c++] = 4;
+  if (e2 % 2) radix[c++] = 2;
+  for (int i = 0; i < e3; ++i) radix[c++] = 3;
+  for (int i = 0; i < e5; ++i) radix[c++] = 5;
+  if (c > kMaxRadixPasses) return -1;
+  *npass = c;
+  return 0;
+}
+
+struct FftTables {
+  int n = 0, npass = 0;
+  int radix[kMaxRadixPasses];
+  double2* d_tw = nullptr;
+  int32_t* d_perm = nullptr;
+  double2* d_unpackA = nullptr;  // [n+1] exp(-2 pi i k / (2n))
+};
+
+template <typename T>
+static int upload(T** dptr, const std::vector<T>& h) {
+  FDLP_CUDA(cudaMalloc((void**)dptr, h.size() * sizeof(T)));
+  FDLP_CUDA(cudaMemcpy(*dptr, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+static int build_fft_tables(int n, FftTables* t) {
+  t->n = n;
+  if (factor_radices(n, t->radix, &t->npass) != 0)
+    return set_err(FDLP_E_UNSUPPORTED, "FFT length %s%ld has a prime factor other than 2, 3, 5", "", n);
+  std::vector<double2> tw(n), A(n + 1);
+  for (int k = 0; k < n; ++k) {
+    const long double ang = -2.0L * M_PIl * k / n;
+    tw[k] = make_double2((double)cosl(ang), (double)sinl(ang));
+  }
+  for (int k = 0; k <= n; ++k) {
+    const long double ang = -2.0L * M_PIl * k / (2.0L * n);
+    A[k] = make_double2((double)cosl(ang), (double)sinl(ang));
+  }
+  std::vector<int32_t> perm(n);
+  for (int k = 0; k < n; ++k) {
+    int kk = k, pos = 0, L = n;
+    for (int q = 0; q < t->npass; ++q) { const int r = t->radix[q]; L /= r; pos += (kk % r) * L; kk /= r; }
+    perm[k] = pos;
+  }
+  int rc;
+  if ((rc = upload(&t->d_tw, tw))) return rc;
+  if ((rc = upload(&t->d_perm, perm))) return rc;
+  if ((rc = upload(&t->d_unpackA, A))) return rc;
+  return 0;
+}
+static void free_fft_tables(FftTables* t) {
+  cudaFree(t->d_tw); cudaFree(t->d_perm); cudaFree(t->d_unpackA);
+  t->d_tw = nullptr; t->d_perm = nullptr; t->d_unpackA = nullptr;
+}
+
+}  // namespace fdlp
+
+using namespace fdlp;
+
+// ================================================================ FDLP plan
+struct fdlp_plan {
+  fdlp_params prm;
+  fdlp_geometry g;
+  int device = 0;
+  int na = 0, a_groups = 1;  // autocorrelation lag blocking
+  bool dct_fp64 = true;
+  size_t dct_smem = 0, ac_smem = 0, lpc_smem = 0, ola_smem = 0;
+  std::vector<double> h_fbank;  // [J, N]
+  FftTables fft;
+  double* d_ham = nullptr;
+  double2* d_postB = nullptr;
+  double* d_fbank = nullptr;
+  int32_t *d_row_lo = nullptr, *d_row_hi = nullptr;
+  double *d_weights = nullptr, *d_cosM = nullptr, *d_wratio = nullptr;
+  // scratch (grow-only)
+  int cap_seg = 0, cap_utt = 0;
+  double *d_dct = nullptr, *d_r = nullptr, *d_env = nullptr, *d_alpha = nullptr;
+};
+
+static void plan_free(fdlp_plan* p) {
+  if (!p) return;
+  free_fft_tables(&p->fft);
+  cudaFree(p->d_ham); cudaFree(p->d_postB); cudaFree(p->d_fbank); cudaFree(p->d_row_lo); cudaFree(p->d_row_hi);
+  cudaFree(p->d_weights); cudaFree(p->d_cosM); cudaFree(p->d_wratio);
+  cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_alpha);
+  delete p;
+}
+
+template <int NA>
+static int ac_set_attr(size_t smem) {
+  FDLP_CUDA(cudaFuncSetAttribute(autocorr_dmma_kernel<NA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  return 0;
+}
+
+static int ensure_scratch(fdlp_plan* p, int n_seg, int n_utt) {
+  if (n_seg > p->cap_seg) {
+    cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env);
+    p->d_dct = p->d_r = p->d_env = nullptr; p->cap_seg = 0;
+    const size_t J = p->prm.nfilters;
+    FDLP_CUDA(cudaMalloc((void**)&p->d_dct, (size_t)n_seg * p->g.N * sizeof(double)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_r, (size_t)n_seg * J * p->g.nlags * sizeof(double)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_env, (size_t)n_seg * J * p->g.kk * sizeof(double)));
+    p->cap_seg = n_seg;
+  }
+  if (n_utt > p->cap_utt) {
+    cudaFree(p->d_alpha); p->d_alpha = nullptr; p->cap_utt = 0;
+    FDLP_CUDA(cudaMalloc((void**)&p->d_alpha, (size_t)n_utt * sizeof(double)));
+    p->cap_utt = n_utt;
+  }
+  return 0;
+}
+
+extern "C" const char* fdlp_last_error(void) { return g_err; }
+extern "C" int fdlp_version(void) { return 100; }
+
+extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
+  if (!prm || !out) return set_err(FDLP_E_ARG, "null argument%s", "");
+  *out = nullptr;
+  if (prm->nfilters < 1 || prm->order < 1 || prm->coeff_num < 2 || prm->frate < 1 || prm->srate < 1 ||
+      !(prm->fduration > 0) || !(prm->overlap_fraction >= 0 && prm->overlap_fraction < 1) || !prm->weights)
+    return set_err(FDLP_E_ARG, "invalid fdlp_params%s", "");
+  fdlp_plan* p = new (std::nothrow) fdlp_plan();
+  if (!p) return set_err(FDLP_E_NOMEM, "out of host memory%s", "");
+  p->prm = *prm;
+  cudaGetDevice(&p->device);
+
+  // ---- geometry, with the reference's exact float expressions ----
+  const double of = 1 - prm->overlap_fraction;               // computeFDLPSpectrogram.py:104
+  const double lfr = 1 / (of * prm->fduration);              // :173
+  fdlp_geometry& g = p->g;
+  g.N = (int)(prm->srate * prm->fduration);                  // features.py:134
+  g.S = (int)(prm->srate / lfr);                             // features.py:135
+  g.M = 2 * (int)(prm->fduration * prm->frate);              // :201
+  g.kk = (int)np_round_half_even(prm->fduration * prm->frate);       // :203
+  g.kkb2 = (int)np_round_half_even(prm->fduration * prm->frate / 2); // :204
+  g.kks = (int)np_round_half_even(prm->fduration * prm->frate * of); // :220
+  g.L = std::min(prm->coeff_num, g.M);
+  g.nlags = prm->order + 2;
+  const int N = g.N, J = prm->nfilters;
+  if (N < 64 || N % 32 != 0 || g.S < 1 || g.M < 2 || g.kk < 1 || g.kk > g.M) {
+    plan_free(p);
+    return set_err(FDLP_E_UNSUPPORTED, "segment length %s%ld must be a multiple of 32 (and kk <= M)", "", N);
+  }
+  // lag blocking for the DMMA autocorrelation: blocks of 8 lags, NA blocks per warp
+  const int kmax = g.nlags - 1;
+  const int na_total = (kmax + 7) / 8 + 1;
+  int groups = 1;
+  while ((na_total + groups - 1) / groups > 20) groups *= 2;
+  if (groups > 4 || na_total + 8 > N / 8) {
+    plan_free(p);
+    return set_err(FDLP_E_UNSUPPORTED, "LPC order %s%ld too large for this segment length", "", prm->order);
+  }
+  p->a_groups = groups;
+  p->na = (((na_total + groups - 1) / groups) + 3) & ~3;
+
+  int rc = build_fft_tables(N / 2, &p->fft);
+  if (rc) { plan_free(p); return rc; }
+
+  // ---- tables ----
+  {
+    std::vector<double> ham = np_hamming(N);
+    std::vector<double2> B(N);
+    const long double sc = 2.0L / sqrtl(2.0L * N);
+    for (int k = 0; k < N; ++k) {
+      const long double ang = -M_PIl * k / (2.0L * N);
+      B[k] = make_double2((double)(cosl(ang) * sc), (double)(sinl(ang) * sc));
+    }
+    if ((rc = upload(&p->d_ham, ham)) || (rc = upload(&p->d_postB, B))) { plan_free(p); return rc; }
+  }
+  {
+    std::vector<double> full;
+    if (prm->fbank_kind == FDLP_FBANK_MEL) full = make_mel_fbank(J, 2 * N, prm->srate, prm->fbank_args[0]);
+    else if (prm->fbank_kind == FDLP_FBANK_COCHLEAR)
+      full = make_cochlear_fbank(J, 2 * N, prm->srate, prm->fbank_args[0], prm->fbank_args[1], (int)prm->fbank_args[2],
+                                 prm->fbank_args[3], prm->fbank_args[4]);
+    else if (prm->fbank_kind == FDLP_FBANK_CUSTOM && prm->custom_fbank)
+      full.assign(prm->custom_fbank, prm->custom_fbank + (size_t)J * (N + 1));
+    else { plan_free(p); return set_err(FDLP_E_ARG, "invalid filter bank kind%s", ""); }
+    // fbank[j, 0:-1]  (computeFDLPSpectrogram.py:190)
+    p->h_fbank.resize((size_t)J * N);
+    std::vector<int32_t> lo(J), hi(J);
+    const int rows = N / 8;
+    for (int j = 0; j < J; ++j) {
+      int first = N, last = -1;
+      for (int k = 0; k < N; ++k) {
+        const double v = full[(size_t)j * (N + 1) + k];
+        p->h_fbank[(size_t)j * N + k] = v;
+        if (v != 0.0) { if (k < first) first = k; last = k; }
+      }
+      if (last < 0) { lo[j] = 0; hi[j] = 0; }
+      else {
+        lo[j] = (first / 8) & ~3;
+        hi[j] = std::min(rows, ((last / 8 + 1) + 3) & ~3);
+      }
+    }
+    if ((rc = upload(&p->d_fbank, p->h_fbank)) || (rc = upload(&p->d_row_lo, lo)) || (rc = upload(&p->d_row_hi, hi))) {
+      plan_free(p); return rc;
+    }
+  }
+  {
+    std::vector<double> w(prm->weights, prm->weights + g.L);
+    std::vector<double> cosM(g.M), wr(g.kk);
+    for (int q = 0; q < g.M; ++q) cosM[q] = (double)cosl(2.0L * M_PIl * q / g.M);
+    std::vector<double> hn = np_hanning(g.kk), hm = np_hamming(g.kk);
+    for (int t = 0; t < g.kk; ++t) wr[t] = hn[t] / hm[t];
+    if ((rc = upload(&p->d_weights, w)) || (rc = upload(&p->d_cosM, cosM)) || (rc = upload(&p->d_wratio, wr))) {
+      plan_free(p); return rc;
+    }
+  }
+
+  // ---- kernel attributes ----
+  int max_smem = 0;
+  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device);
+  if (max_smem <= 0) max_smem = 227 * 1024;  // building / probing without a device
+  p->dct_fp64 = !prm->dct_fp32 && (size_t)N * 8 <= (size_t)max_smem;
+  p->dct_smem = (size_t)N * (p->dct_fp64 ? 8 : 4);
+  g.dct_is_fp64 = p->dct_fp64 ? 1 : 0;
+  if (p->dct_smem > (size_t)max_smem) {
+    plan_free(p);
+    return set_err(FDLP_E_UNSUPPORTED, "segment length %s%ld does not fit in shared memory", "", N);
+  }
+  p->ac_smem = (size_t)(kAcWarps / p->a_groups) * (p->na * p->a_groups) * 64 * sizeof(double);
+  p->lpc_smem = ((size_t)g.M + kLpcWarps * lpc_smem_doubles_per_warp(prm->order, g.nlags, g.L)) * sizeof(double);
+  p->ola_smem = (size_t)J * (kOlaFT + 1) * sizeof(double);
+  if (p->lpc_smem > (size_t)max_smem || p->ola_smem > (size_t)max_smem || p->ac_smem > (size_t)max_smem) {
+    plan_free(p);
+    return set_err(FDLP_E_UNSUPPORTED, "configuration needs more shared memory than available%s", "");
+  }
+#define SET_SMEM(kern, bytes)                                                                              \
+  do {                                                                                                     \
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)); \
+    if (e != cudaSuccess) { plan_free(p); return set_err(FDLP_E_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e)); } \
+  } while (0)
+  if (p->dct_fp64) {
+    SET_SMEM((dct_segments_kernel<double, int16_t>), p->dct_smem);
+    SET_SMEM((dct_segments_kernel<double, float>), p->dct_smem);
+  } else {
+    SET_SMEM((dct_segments_kernel<float, int16_t>), p->dct_smem);
+    SET_SMEM((dct_segments_kernel<float, float>), p->dct_smem);
+  }
+  SET_SMEM(lpc_envelope_kernel, p->lpc_smem);
+  SET_SMEM(ola_log_kernel, p->ola_smem);
+  switch (p->na) {
+    case 4: SET_SMEM(autocorr_dmma_kernel<4>, p->ac_smem); break;
+    case 8: SET_SMEM(autocorr_dmma_kernel<8>, p->ac_smem); break;
+    case 12: SET_SMEM(autocorr_dmma_kernel<12>, p->ac_smem); break;
+    case 16: SET_SMEM(autocorr_dmma_kernel<16>, p->ac_smem); break;
+    case 20: SET_SMEM(autocorr_dmma_kernel<20>, p->ac_smem); break;
+    default: plan_free(p); return set_err(FDLP_E_UNSUPPORTED, "unsupported lag blocking%s", "");
+  }
+#undef SET_SMEM
+  *out = p;
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_plan_destroy(fdlp_plan* p) {
+  plan_free(p);
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_plan_get_geometry(const fdlp_plan* p, fdlp_geometry* out) {
+  if (!p || !out) return set_err(FDLP_E_ARG, "null argument%s", "");
+  *out = p->g;
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_plan_get_fbank(const fdlp_plan* p, double* host_out) {
+  if (!p || !host_out) return set_err(FDLP_E_ARG, "null argument%s", "");
+  memcpy(host_out, p->h_fbank.data(), p->h_fbank.size() * sizeof(double));
+  return FDLP_OK;
+}
+
+extern "C" int64_t fdlp_plan_scratch_bytes(const fdlp_plan* p, int32_t n_seg) {
+  if (!p) return -1;
+  const int64_t J = p->prm.nfilters;
+  return (int64_t)n_seg * 8 * ((int64_t)p->g.N + J * p->g.nlags + J * p->g.kk);
+}
+
+// ---------------------------------------------------------------- launches
+static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, cudaStream_t st) {
+  DctArgs a;
+  memset(&a, 0, sizeof(a));
+  a.wav = b->wav; a.utt_wav_off = b->utt_wav_off; a.utt_seg_off = b->utt_seg_off; a.seg_utt = b->seg_utt;
+  if (b->noise_mode != FDLP_NOISE_NONE) {
+    a.noise = (const int16_t*)b->noise; a.utt_noise_off = b->utt_noise_off; a.utt_alpha = p->d_alpha;
+  }
+  a.N = p->g.N; a.S = p->g.S; a.n = p->g.N / 2; a.npass = p->fft.npass;
+  for (int i = 0; i < p->fft.npass; ++i) a.radix[i] = p->fft.radix[i];
+  a.ham = p->d_ham; a.tw = p->fft.d_tw; a.perm = p->fft.d_perm; a.unpackA = p->fft.d_unpackA; a.postB = p->d_postB;
+  a.out = out;
+  a.vec_ok = (((uintptr_t)b->wav) % 16 == 0) ? 1 : 0;
+  const dim3 grid(b->n_seg), block(512);
+  if (b->wav_dtype == FDLP_WAV_INT16) {
+    if (p->dct_fp64) dct_segments_kernel<double, int16_t><<<grid, block, p->dct_smem, st>>>(a);
+    else dct_segments_kernel<float, int16_t><<<grid, block, p->dct_smem, st>>>(a);
+  } else {
+    if (p->dct_fp64) dct_segments_kernel<double, float><<<grid, block, p->dct_smem, st>>>(a);
+    else dct_segments_kernel<float, float><<<grid, block, p->dct_smem, st>>>(a);
+  }
+  FDLP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int launch_autocorr(fdlp_plan* p, const double* dct, int n_seg, double* r, cudaStream_t st) {
+  AcArgs a;
+  a.dct = dct; a.fbank = p->d_fbank; a.row_lo = p->d_row_lo; a.row_hi = p->d_row_hi; a.r = r;
+  a.N = p->g.N; a.J = p->prm.nfilters; a.nlags = p->g.nlags; a.rows = p->g.N / 8; a.n_seg = n_seg;
+  a.a_groups = p->a_groups; a.na_total = p->na * p->a_groups;
+  const int bpc = kAcWarps / p->a_groups;
+  const int nbg = (a.J + bpc - 1) / bpc;
+  const dim3 grid((unsigned)((size_t)n_seg * nbg)), block(kAcWarps * 32);
+  switch (p->na) {
+    case 4: autocorr_dmma_kernel<4><<<grid, block, p->ac_smem, st>>>(a); break;
+    case 8: autocorr_dmma_kernel<8><<<grid, block, p->ac_smem, st>>>(a); break;
+    case 12: autocorr_dmma_kernel<12><<<grid, block, p->ac_smem, st>>>(a); break;
+    case 16: autocorr_dmma_kernel<16><<<grid, block, p->ac_smem, st>>>(a); break;
+    default: autocorr_dmma_kernel<20><<<grid, block, p->ac_smem, st>>>(a); break;
+  }
+  FDLP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out, double* gain_out, double* cep_out,
+                      double* env, int32_t* status, const int32_t* seg_utt, cudaStream_t st) {
+  LpcArgs a;
+  a.r = r; a.n_tasks = n_seg * p->prm.nfilters; a.J = p->prm.nfilters;
+  a.order = p->prm.order; a.nlags = p->g.nlags; a.L = p->g.L; a.M = p->g.M; a.kk = p->g.kk;
+  a.weights = p->d_weights; a.cosM = p->d_cosM; a.wratio = p->d_wratio;
+  a.lpc_out = lpc_out; a.gain_out = gain_out; a.cep_out = cep_out; a.env = env;
+  a.status = status; a.seg_utt = seg_utt;
+  const dim3 grid((a.n_tasks + kLpcWarps - 1) / kLpcWarps), block(kLpcWarps * 32);
+  lpc_envelope_kernel<<<grid, block, p->lpc_smem, st>>>(a);
+  FDLP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int check_batch(const fdlp_plan* p, const fdlp_batch* b) {
+  if (!p || !b) return set_err(FDLP_E_ARG, "null argument%s", "");
+  if (b->n_utt < 0 || b->n_seg < 0 || b->n_frames < 0) return set_err(FDLP_E_ARG, "negative batch sizes%s", "");
+  if (b->n_seg > 0 && (!b->wav || !b->utt_wav_off || !b->utt_seg_off || !b->seg_utt))
+    return set_err(FDLP_E_ARG, "null batch pointer%s", "");
+  if (b->wav_dtype != FDLP_WAV_INT16 && b->wav_dtype != FDLP_WAV_FLOAT32) return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
+  if (b->noise_mode != FDLP_NOISE_NONE && (!b->noise || !b->utt_noise_off || !b->utt_snr_db))
+    return set_err(FDLP_E_ARG, "noise mixing requested without noise arrays%s", "");
+  return 0;
+}
+
+static int launch_noise(fdlp_plan* p, const fdlp_batch* b, cudaStream_t st) {
+  if (b->noise_mode == FDLP_NOISE_NONE) return 0;
+  NoiseArgs a;
+  a.wav = b->wav; a.wav_dtype = b->wav_dtype; a.utt_wav_off = b->utt_wav_off; a.noise = (const int16_t*)b->noise;
+  a.utt_noise_off = b->utt_noise_off; a.utt_snr_db = b->utt_snr_db; a.utt_alpha = p->d_alpha; a.mode = b->noise_mode;
+  noise_alpha_kernel<<<b->n_utt, 256, 0, st>>>(a);
+  FDLP_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
+  int rc = check_batch(p, b);
+  if (rc) return rc;
+  if (b->n_seg == 0 || b->n_utt == 0) return FDLP_OK;
+  if (!b->feats || !b->utt_frame_off || !b->seg_ptr) return set_err(FDLP_E_ARG, "null output / frame pointers%s", "");
+  cudaStream_t st = (cudaStream_t)stream;
+  if ((rc = ensure_scratch(p, b->n_seg, b->n_utt))) return rc;
+  if ((rc = launch_noise(p, b, st))) return rc;
+  if ((rc = launch_dct(p, b, p->d_dct, st))) return rc;
+  if ((rc = launch_autocorr(p, p->d_dct, b->n_seg, p->d_r, st))) return rc;
+  if ((rc = launch_lpc(p, p->d_r, b->n_seg, nullptr, nullptr, nullptr, p->d_env, b->status, b->seg_utt, st))) return rc;
+  OlaArgs o;
+  o.env = p->d_env; o.utt_seg_off = b->utt_seg_off; o.utt_frame_off = b->utt_frame_off; o.seg_ptr = b->seg_ptr;
+  o.feats = b->feats; o.cmvn = b->cmvn_acc; o.J = p->prm.nfilters; o.kk = p->g.kk; o.kkb2 = p->g.kkb2;
+  // grid.y covers the longest utterance; the host passes it through n_frames / n_utt bounds
+  int64_t max_tiles = (b->max_utt_frames + kOlaFT - 1) / kOlaFT;
+  if (max_tiles < 1) max_tiles = 1;
+  if (max_tiles > 65535) return set_err(FDLP_E_ARG, "utterance too long%s", "");
+  const dim3 grid(b->n_utt, (unsigned)max_tiles), block(256);
+  ola_log_kernel<<<grid, block, p->ola_smem, st>>>(o);
+  FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_stage_dct(fdlp_plan* p, const fdlp_batch* b, double* dct_out, void* stream) {
+  int rc = check_batch(p, b);
+  if (rc) return rc;
+  if (!dct_out) return set_err(FDLP_E_ARG, "null output%s", "");
+  if (b->n_seg == 0) return FDLP_OK;
+  if ((rc = ensure_scratch(p, 1, b->n_utt))) return rc;
+  if ((rc = launch_noise(p, b, (cudaStream_t)stream))) return rc;
+  return launch_dct(p, b, dct_out, (cudaStream_t)stream);
+}
+
+extern "C" int fdlp_stage_autocorr(fdlp_plan* p, const double* dct, int32_t n_seg, double* r_out, void* stream) {
+  if (!p || !dct || !r_out || n_seg < 0) return set_err(FDLP_E_ARG, "bad argument%s", "");
+  if (n_seg == 0) return FDLP_OK;
+  return launch_autocorr(p, dct, n_seg, r_out, (cudaStream_t)stream);
+}
+
+extern "C" int fdlp_stage_lpc_envelope(fdlp_plan* p, const double* r, int32_t n_seg, double* lpc_out, double* gain_out,
+                                       double* cep_out, double* env_out, int32_t* seg_status, void* stream) {
+  if (!p || !r || !env_out || n_seg < 0) return set_err(FDLP_E_ARG, "bad argument%s", "");
+  if (n_seg == 0) return FDLP_OK;
+  return launch_lpc(p, r, n_seg, lpc_out, gain_out, cep_out, env_out, seg_status, nullptr, (cudaStream_t)stream);
+}
+
+// ================================================================ mel plan
+struct mel_plan {
+  mel_params prm;
+  int flen = 0, shift = 0, n = 0;
+  FftTables fft;
+  std::vector<double> h_fbank;  // [J, n+1]
+  double* d_ham = nullptr;
+  float* d_fbank = nullptr;
+  int32_t *d_lo = nullptr, *d_hi = nullptr;
+  int32_t* d_frame_utt = nullptr;
+  int64_t cap_frames = 0;
+  size_t smem = 0;
+};
+
+static void mel_free(mel_plan* p) {
+  if (!p) return;
+  free_fft_tables(&p->fft);
+  cudaFree(p->d_ham); cudaFree(p->d_fbank); cudaFree(p->d_lo); cudaFree(p->d_hi); cudaFree(p->d_frame_utt);
+  delete p;
+}
+
+extern "C" int mel_plan_create(const mel_params* prm, mel_plan** out) {
+  if (!prm || !out) return set_err(FDLP_E_ARG, "null argument%s", "");
+  *out = nullptr;
+  if (prm->nfilters < 1 || prm->nfft < 8 || (prm->nfft & 1) || prm->frate < 1 || !(prm->fduration > 0))
+    return set_err(FDLP_E_ARG, "invalid mel_params%s", "");
+  mel_plan* p = new (std::nothrow) mel_plan();
+  if (!p) return set_err(FDLP_E_NOMEM, "out of host memory%s", "");
+  p->prm = *prm;
+  p->flen = (int)(prm->srate * prm->fduration);   // features.py:134
+  p->shift = (int)(prm->srate / (double)prm->frate);  // features.py:135
+  p->n = prm->nfft / 2;
+  if (p->flen < 1 || p->shift < 1) { mel_free(p); return set_err(FDLP_E_ARG, "empty frames%s", ""); }
+  int rc = build_fft_tables(p->n, &p->fft);
+  if (rc) { mel_free(p); return rc; }
+  const int J = prm->nfilters, nb = p->n + 1;
+  if (prm->fbank_kind == FDLP_FBANK_MEL) p->h_fbank = make_mel_fbank(J, prm->nfft, prm->srate, prm->fbank_args[0]);
+  else if (prm->fbank_kind == FDLP_FBANK_COCHLEAR)
+    p->h_fbank = make_cochlear_fbank(J, prm->nfft, prm->srate, prm->fbank_args[0], prm->fbank_args[1],
+                                     (int)prm->fbank_args[2], prm->fbank_args[3], prm->fbank_args[4]);
+  else if (prm->fbank_kind == FDLP_FBANK_CUSTOM && prm->custom_fbank)
+    p->h_fbank.assign(prm->custom_fbank, prm->custom_fbank + (size_t)J * nb);
+  else { mel_free(p); return set_err(FDLP_E_ARG, "invalid filter bank kind%s", ""); }
+  std::vector<float> f32(p->h_fbank.size());
+  std::vector<int32_t> lo(J), hi(J);
+  for (int j = 0; j < J; ++j) {
+    int first = nb, last = -1;
+    for (int k = 0; k < nb; ++k) {
+      const double v = p->h_fbank[(size_t)j * nb + k];
+      f32[(size_t)j * nb + k] = (float)v;
+      if (v != 0.0) { if (k < first) first = k; last = k; }
+    }
+    lo[j] = last < 0 ? 0 : first;
+    hi[j] = last < 0 ? 0 : last + 1;
+  }
+  std::vector<double> ham = np_hamming(p->flen);
+  if ((rc = upload(&p->d_ham, ham)) || (rc = upload(&p->d_fbank, f32)) || (rc = upload(&p->d_lo, lo)) ||
+      (rc = upload(&p->d_hi, hi))) { mel_free(p); return rc; }
+  p->smem = (size_t)prm->nfft * sizeof(float) + (size_t)(p->n + 1) * sizeof(float);
+  cudaError_t e = cudaFuncSetAttribute(mel_frames_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(mel_frames_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem);
+  if (e != cudaSuccess) { mel_free(p); return set_err(FDLP_E_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
+  *out = p;
+  return FDLP_OK;
+}
+
+extern "C" int mel_plan_destroy(mel_plan* p) { mel_free(p); return FDLP_OK; }
+
+extern "C" int mel_plan_get_fbank(const mel_plan* p, double* host_out) {
+  if (!p || !host_out) return set_err(FDLP_E_ARG, "null argument%s", "");
+  memcpy(host_out, p->h_fbank.data(), p->h_fbank.size() * sizeof(double));
+  return FDLP_OK;
+}
+
+extern "C" int mel_forward(mel_plan* p, const mel_batch* b, void* stream) {
+  if (!p || !b) return set_err(FDLP_E_ARG, "null argument%s", "");
+  if (b->n_utt <= 0 || b->n_frames <= 0) return FDLP_OK;
+  if (!b->wav || !b->utt_wav_off || !b->utt_frame_off || !b->feats) return set_err(FDLP_E_ARG, "null batch pointer%s", "");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (b->n_frames > p->cap_frames) {
+    cudaFree(p->d_frame_utt); p->d_frame_utt = nullptr; p->cap_frames = 0;
+    FDLP_CUDA(cudaMalloc((void**)&p->d_frame_utt, (size_t)b->n_frames * sizeof(int32_t)));
+    p->cap_frames = b->n_frames;
+  }
+  mel_frame_map_kernel<<<b->n_utt, 128, 0, st>>>(b->utt_frame_off, b->n_utt, p->d_frame_utt);
+  FDLP_CUDA(cudaGetLastError());
+  MelArgs a;
+  memset(&a, 0, sizeof(a));
+  a.wav = b->wav; a.utt_wav_off = b->utt_wav_off; a.utt_frame_off = b->utt_frame_off; a.frame_utt = p->d_frame_utt;
+  a.flen = p->flen; a.shift = p->shift; a.nfft = p->prm.nfft; a.n = p->n; a.npass = p->fft.npass;
+  for (int i = 0; i < p->fft.npass; ++i) a.radix[i] = p->fft.radix[i];
+  a.ham = p->d_ham; a.tw = p->fft.d_tw; a.perm = p->fft.d_perm; a.unpackA = p->fft.d_unpackA;
+  a.fbank = p->d_fbank; a.band_lo = p->d_lo; a.band_hi = p->d_hi; a.feats = b->feats; a.cmvn = b->cmvn_acc;
+  a.J = p->prm.nfilters; a.power = p->prm.power;
+  if (b->n_frames > 2147483647LL) return set_err(FDLP_E_ARG, "too many frames in one batch%s", "");
+  const dim3 grid((unsigned)b->n_frames), block(128);
+  if (b->wav_dtype == FDLP_WAV_INT16) mel_frames_kernel<int16_t><<<grid, block, p->smem, st>>>(a);
+  else if (b->wav_dtype == FDLP_WAV_FLOAT32) mel_frames_kernel<float><<<grid, block, p->smem, st>>>(a);
+  else return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
+  FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
+// ================================================================ CMVN apply
+extern "C" int cmvn_apply(float* feats, int64_t n_frames, int32_t dim, const double* stats, int32_t norm_vars, void* stream) {
+  if (!feats || !stats || n_frames < 0 || dim < 1) return set_err(FDLP_E_ARG, "bad argument%s", "");
+  if (n_frames == 0) return FDLP_OK;
+  const int64_t total = n_frames * dim;
+  const int64_t blocks = (total + 255) / 256;
+  if (blocks > 2147483647LL) return set_err(FDLP_E_ARG, "too many elements%s", "");
+  cmvn_apply_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(feats, n_frames, dim, stats, norm_vars);
+  FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
+// ================================================================ FP64 peak probe
+namespace fdlp {
+__global__ void __launch_bounds__(256) peak_dfma_kernel(double* out, double a, double b, int iters) {
+  double acc[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) acc[i] = threadIdx.x + i;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc[i] = fma(acc[i], a, b);
+  }
+  double s = 0;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) s += acc[i];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+__global__ void __launch_bounds__(256) peak_dmma_kernel(double* out, double a, double b, int iters) {
+  double c[16][2];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { c[i][0] = threadIdx.x; c[i][1] = i; }
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) dmma884(c[i][0], c[i][1], a, b);
+  }
+  double s = 0;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) s += c[i][0] + c[i][1];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+}  // namespace fdlp
+
+extern "C" int fdlp_measure_fp64_peak(double* dfma_tflops, double* dmma_tflops) {
+  int dev = 0, sms = 0;
+  FDLP_CUDA(cudaGetDevice(&dev));
+  FDLP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int blocks = sms * 8, threads = 256, iters = 4096;
+  double* out = nullptr;
+  FDLP_CUDA(cudaMalloc((void**)&out, sizeof(double) * blocks * threads));
+  cudaEvent_t e0, e1;
+  FDLP_CUDA(cudaEventCreate(&e0));
+  FDLP_CUDA(cudaEventCreate(&e1));
+  double best[2] = {1e30, 1e30};
+  for (int which = 0; which < 2; ++which) {
+    for (int rep = 0; rep < 6; ++rep) {
+      FDLP_CUDA(cudaEventRecord(e0));
+      if (which == 0) peak_dfma_kernel<<<blocks, threads>>>(out, 1.0000001, 1e-9, iters);
+      else peak_dmma_kernel<<<blocks, threads>>>(out, 1.0000001, 1e-9, iters);
+      FDLP_CUDA(cudaEventRecord(e1));
+      FDLP_CUDA(cudaEventSynchronize(e1));
+      float ms = 0;
+      FDLP_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+      if (rep >= 2 && ms < best[which]) best[which] = ms;
+    }
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out);
+  const double threads_total = (double)blocks * threads;
+  if (dfma_tflops) *dfma_tflops = threads_total * iters * 16 * 2 / (best[0] * 1e-3) / 1e12;
+  if (dmma_tflops) *dmma_tflops = (threads_total / 32) * iters * 16 * 512.0 / (best[1] * 1e-3) / 1e12;
+  return FDLP_OK;
+}

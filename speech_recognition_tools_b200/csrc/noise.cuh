@@ -1,0 +1,79 @@
+// K0: SNR-scaled noise mixing coefficient per utterance.
+//
+// Reference: add_noise_to_wav  src/featgen/features.py:24-31
+//     ns    = noise[rand_num : rand_num + len(sig)]
+//     E_s   = mean(sig ** 2);  E_n = mean(ns ** 2)        <- computed IN THE INPUT DTYPE
+//     alp   = sqrt(E_s / (E_n * 10 ** (snr / 10)))
+//     out   = sig + alp * ns                               (float64)
+// WAVs are read as int16 and never normalised (computeFDLPSpectrogram.py:156-157), so `sig ** 2` wraps
+// modulo 2^16 in the reference.  FDLP_NOISE_INT16_WRAP reproduces that exactly with integer sums (the mean
+// of the wrapped squares is an exact integer / T); FDLP_NOISE_FLOAT uses the true float64 energies.
+// The mix itself (sig + alp * ns) is applied by the framing kernel while it loads samples (dct.cuh), so the
+// mixed waveform is never written to memory.
+#pragma once
+#include "common.cuh"
+
+namespace fdlp {
+
+struct NoiseArgs {
+  const void* wav;
+  int wav_dtype;
+  const int64_t* utt_wav_off;
+  const int16_t* noise;
+  const int64_t* utt_noise_off;
+  const double* utt_snr_db;
+  double* utt_alpha;  // out [n_utt]
+  int mode;
+};
+
+__device__ __forceinline__ long long wrap_sq16(int v) {
+  return (long long)(short)(v * v);  // int16 * int16 -> int16 with wrap-around, as numpy does
+}
+
+__global__ void __launch_bounds__(256) noise_alpha_kernel(const NoiseArgs a) {
+  const int u = blockIdx.x;
+  const int64_t woff = a.utt_wav_off[u];
+  const int64_t T = a.utt_wav_off[u + 1] - woff;
+  const int16_t* nz = a.noise + a.utt_noise_off[u];
+  long long is = 0, in = 0;
+  double fs = 0.0, fn = 0.0;
+  const bool wrap = (a.mode == FDLP_NOISE_INT16_WRAP);
+  if (a.wav_dtype == FDLP_WAV_INT16) {
+    const int16_t* s = reinterpret_cast<const int16_t*>(a.wav) + woff;
+    for (int64_t i = threadIdx.x; i < T; i += blockDim.x) {
+      const int sv = s[i], nv = nz[i];
+      if (wrap) { is += wrap_sq16(sv); in += wrap_sq16(nv); }
+      else { fs += (double)sv * sv; fn += (double)nv * nv; }
+    }
+  } else {
+    const float* s = reinterpret_cast<const float*>(a.wav) + woff;
+    for (int64_t i = threadIdx.x; i < T; i += blockDim.x) {
+      const float sv = s[i];
+      const int nv = nz[i];
+      // float32 signal: numpy squares in float32 (rounded), the noise is still int16
+      if (wrap) { fs += (double)__fmul_rn(sv, sv); in += wrap_sq16(nv); }
+      else { fs += (double)sv * sv; fn += (double)nv * nv; }
+    }
+  }
+  __shared__ long long sh_i[2][8];
+  __shared__ double sh_f[2][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int o = 16; o > 0; o >>= 1) {
+    is += __shfl_xor_sync(0xffffffffu, is, o);
+    in += __shfl_xor_sync(0xffffffffu, in, o);
+    fs += __shfl_xor_sync(0xffffffffu, fs, o);
+    fn += __shfl_xor_sync(0xffffffffu, fn, o);
+  }
+  if (lane == 0) { sh_i[0][warp] = is; sh_i[1][warp] = in; sh_f[0][warp] = fs; sh_f[1][warp] = fn; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long tis = 0, tin = 0;
+    double tfs = 0, tfn = 0;
+    for (int w = 0; w < 8; ++w) { tis += sh_i[0][w]; tin += sh_i[1][w]; tfs += sh_f[0][w]; tfn += sh_f[1][w]; }
+    const double Es = ((double)tis + tfs) / (double)T;
+    const double En = ((double)tin + tfn) / (double)T;
+    a.utt_alpha[u] = sqrt(Es / (En * pow(10.0, a.utt_snr_db[u] / 10.0)));
+  }
+}
+
+}  // namespace fdlp

@@ -1,0 +1,106 @@
+// K6: overlap-add of the per-segment envelopes into 100 Hz frames, floor + natural log, FP32 store,
+// and the per-dimension CMVN partial sums.
+//
+// Reference: OLA        src/featgen/computeFDLPSpectrogram.py:182,207-225
+//            log / clip src/featgen/computeFDLPSpectrogram.py:227  (np.log(np.clip(feats.T, a_min=1e-14)))
+//            CMVN stats Kaldi compute-cmvn-stats, e2e/wsj/run_fdlp_e1.sh:280 (un-vendored: layout restated)
+//
+// Gather form: every output frame pulls its contributors in ascending segment order (the order the
+// reference adds them), so the result is deterministic and needs no atomics.  The segment pointers
+// (with the randrange(2) jitter of line 225) are computed by the host and passed in.
+// A block owns one (utterance, tile of FT frames): phase 1 reads envelopes with the frame index fastest
+// (coalesced along t), phase 2 writes [frame, band] rows with the band index fastest (coalesced).
+#pragma once
+#include "common.cuh"
+
+namespace fdlp {
+
+struct OlaArgs {
+  const double* env;             // [n_seg, J, kk]
+  const int32_t* utt_seg_off;    // [n_utt+1]
+  const int64_t* utt_frame_off;  // [n_utt+1]
+  const int32_t* seg_ptr;        // [n_seg]
+  float* feats;                  // [n_frames, J]
+  double* cmvn;                  // [2, J+1] or null
+  int J, kk, kkb2;
+};
+
+constexpr int kOlaFT = 64;  // frames per block
+
+__global__ void __launch_bounds__(256) ola_log_kernel(const OlaArgs a) {
+  extern __shared__ __align__(16) double tile[];  // [J][FT+1]
+  const int u = blockIdx.x;
+  const int64_t foff = a.utt_frame_off[u];
+  const int Fr = (int)(a.utt_frame_off[u + 1] - foff);
+  const int f0 = blockIdx.y * kOlaFT;
+  if (f0 >= Fr) return;
+  const int nf = min(kOlaFT, Fr - f0);
+  const int s0 = a.utt_seg_off[u], nseg = a.utt_seg_off[u + 1] - s0;
+  const int J = a.J, kk = a.kk, kkb2 = a.kkb2;
+  constexpr int LD = kOlaFT + 1;
+
+  for (int e = threadIdx.x; e < J * kOlaFT; e += blockDim.x) {
+    const int j = e / kOlaFT, fl = e % kOlaFT;
+    const int f = f0 + fl;
+    double acc = 0.0;
+    if (fl < nf) {
+      for (int i = 0; i < nseg; ++i) {
+        int t;
+        if (i == 0) {
+          // feats[:, 0:kkb2] += E[kkb2:]  (or feats[:, :] += E[kkb2:kkb2+Fr] when Fr < kkb2)
+          const int d1 = Fr < kkb2 ? Fr : kkb2;
+          t = (f < d1) ? kkb2 + f : -1;
+        } else {
+          const int ptr = a.seg_ptr[s0 + i];
+          t = f - ptr;
+          if (t < 0 || t >= kk) t = -1;
+        }
+        if (t >= 0 && t < kk) acc += a.env[((size_t)(s0 + i) * J + j) * kk + t];
+      }
+    }
+    tile[j * LD + fl] = acc;
+  }
+  __syncthreads();
+
+  for (int e = threadIdx.x; e < nf * J; e += blockDim.x) {
+    const int fl = e / J, j = e % J;
+    const double v = tile[j * LD + fl];
+    // np.clip propagates NaN; fmax would not
+    const double lg = isnan(v) ? v : log(v < 1e-14 ? 1e-14 : v);
+    const float o = (float)lg;
+    a.feats[(size_t)(foff + f0 + fl) * J + j] = o;
+    tile[j * LD + fl] = (double)o;  // keep the rounded value for the CMVN sums
+  }
+  if (a.cmvn) {
+    __syncthreads();
+    for (int j = threadIdx.x; j < J; j += blockDim.x) {
+      double s1 = 0.0, s2 = 0.0;
+      for (int fl = 0; fl < nf; ++fl) {
+        const double v = tile[j * LD + fl];
+        s1 += v;
+        s2 = fma(v, v, s2);
+      }
+      atomicAdd(a.cmvn + j, s1);
+      atomicAdd(a.cmvn + (J + 1) + j, s2);
+    }
+    if (threadIdx.x == 0) atomicAdd(a.cmvn + J, (double)nf);
+  }
+}
+
+// Kaldi apply-cmvn (--norm-vars) with global stats: x <- (x - mean) / sqrt(var)
+__global__ void cmvn_apply_kernel(float* feats, int64_t n, int dim, const double* stats, int norm_vars) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * dim) return;
+  const int d = (int)(i % dim);
+  const double cnt = stats[dim];
+  const double mean = stats[d] / cnt;
+  double v = (double)feats[i] - mean;
+  if (norm_vars) {
+    double var = stats[(dim + 1) + d] / cnt - mean * mean;
+    if (var < 1e-20) var = 1e-20;
+    v *= rsqrt(var);
+  }
+  feats[i] = (float)v;
+}
+
+}  // namespace fdlp

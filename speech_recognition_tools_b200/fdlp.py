@@ -1,0 +1,432 @@
+"""Host side of the B200 FDLP-spectrogram extractor.
+
+Mirrors the reference's `getFeats` (src/featgen/computeFDLPSpectrogram.py:29-237): same options, same
+frame/segment geometry, same output layout (frames x sub-bands, natural log).  The host does only what
+the reference does once per job or per utterance outside the hot loop -- option parsing, the integer
+segment/frame bookkeeping and the overlap-add pointer trace with its `randrange(2)` jitter
+(:220-225) -- and hands packed device buffers to libfdlp_b200.so through the C ABI
+(include/fdlp_b200.h).  All arithmetic on samples and features happens in the CUDA kernels; there is no
+CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import random as _random
+from dataclasses import dataclass, field
+from typing import List, Optional, Sequence, Union
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+LOG_FLOOR = math.log(1e-14)
+
+
+# --------------------------------------------------------------------------- configuration
+@dataclass
+class FdlpConfig:
+    """The reference's argparse surface (computeFDLPSpectrogram.py:241-262) minus I/O options."""
+    nfilters: int = 20
+    coeff_num: int = 50
+    coeff_range: str = "1,20"
+    order: int = 50
+    fduration: float = 0.5
+    frate: int = 100
+    overlap_fraction: float = 0.25
+    fbank_type: str = "mel,1"
+    odd_mod_zero: bool = False
+    gamma_weight: str = "None"
+    lifter: Optional[Sequence[float]] = None  # contents of --lifter_config (first line, comma separated)
+    srate: int = 16000
+    dct_fp32: bool = False
+
+    @classmethod
+    def from_args(cls, args) -> "FdlpConfig":
+        lifter = None
+        if getattr(args, "lifter_config", None):
+            with open(args.lifter_config, "r") as fid:  # computeFDLPSpectrogram.py:43-46
+                lifter = [float(x) for x in fid.readline().strip().split(",")]
+        gw = args.gamma_weight
+        if not isinstance(gw, str):
+            gw = ",".join(gw)
+        return cls(nfilters=args.nfilters, coeff_num=args.coeff_num, coeff_range=args.coeff_range, order=args.order,
+                   fduration=args.fduration, frate=args.frate, overlap_fraction=args.overlap_fraction,
+                   fbank_type=args.fbank_type, odd_mod_zero=bool(args.odd_mod_zero), gamma_weight=gw, lifter=lifter)
+
+
+def parse_fbank_type(fbank_type: str):
+    """computeFDLPSpectrogram.py:49-63: 'mel,warp' or 'cochlear,om_w,alp,fixed,bet,warp'."""
+    tok = fbank_type.strip().split(",")
+    if tok[0] == "mel":
+        if len(tok) < 2:
+            raise ValueError("Mel filter bank not configured properly....")
+        return L.FDLP_FBANK_MEL, [float(tok[1]), 0, 0, 0, 0]
+    if tok[0] == "cochlear":
+        if len(tok) < 6:
+            raise ValueError("Cochlear filter bank not configured properly....")
+        return L.FDLP_FBANK_COCHLEAR, [float(tok[1]), float(tok[2]), float(int(tok[3])), float(tok[4]), float(tok[5])]
+    raise ValueError("Invalid type of filter bank, use mel or cochlear with proper configuration")
+
+
+def build_weights(cfg: FdlpConfig) -> np.ndarray:
+    """Mask (computeFDLPSpectrogram.py:94-103) * lifter (:195-196) * gamma weights (:107-118,197-198), with
+    `ms[1::2] = 0` (:199-200) folded in: one float64 vector of length coeff_num."""
+    lo, hi = (int(v) for v in cfg.coeff_range.split(","))
+    w = np.array([1.0 if (lo <= i <= hi) else 0.0 for i in range(cfg.coeff_num)])
+    if cfg.lifter is not None:
+        lifter = np.asarray(cfg.lifter, dtype=np.float64)
+        if lifter.shape[0] != cfg.coeff_num:
+            raise ValueError("operands could not be broadcast together with shapes (%d,) (%d,)"
+                             % (cfg.coeff_num, lifter.shape[0]))
+        w = w * lifter
+    g = cfg.gamma_weight.strip().split(",")
+    if g[0] != "None":
+        import scipy.stats
+        if cfg.order != cfg.coeff_num:
+            raise ValueError("operands could not be broadcast together with shapes (%d,) (%d,)"
+                             % (cfg.coeff_num, cfg.order))
+        x = np.linspace(0, cfg.order - 1, cfg.order)
+        scale, shape, pk_required = float(g[0]), float(g[1]), float(g[2])
+        pk_required = pk_required * (2 * cfg.fduration)
+        pk = (shape - 1) * scale
+        loc = -pk + pk_required
+        w = w * (scipy.stats.gamma.pdf(x, a=shape, loc=loc, scale=scale) * 3 * scale)
+    if cfg.odd_mod_zero:
+        w = w.copy()
+        w[1::2] = 0.0
+    return np.ascontiguousarray(w, dtype=np.float64)
+
+
+def segment_count(T: int, N: int, S: int) -> int:
+    """Number of frames getFrames yields (features.py:134-154): idx = sp_b + k*S while idx + sp_f < T + 2*extend."""
+    if N % 2 == 0:
+        lim = T - 1   # k*S < T - 1
+    else:
+        lim = T
+    return max(0, -(-lim // S))
+
+
+def frame_count(T: int, frate: int, srate: int) -> int:
+    """computeFDLPSpectrogram.py:182: int(np.ceil(tframes * frate / srate))."""
+    return int(np.ceil(T * frate / srate))
+
+
+def ola_pointers(nseg: int, Fr: int, kk: int, kkb2: int, kks: int, rng) -> List[int]:
+    """Overlap-add pointer trace, computeFDLPSpectrogram.py:207-225, raising where numpy would.
+
+    One `rng.randrange(2)` draw per segment i >= 1 (including the last), exactly as line 225."""
+    ptrs = []
+    ptr = 0
+    for i in range(nseg):
+        ptrs.append(ptr)
+        if i == 0:
+            if Fr >= kkb2 and (kk - kkb2) != kkb2:
+                raise ValueError("operands could not be broadcast together with shapes (%d,) (%d,) "
+                                 "(odd fduration*frate is not supported by the reference either)" % (kkb2, kk - kkb2))
+        elif i >= nseg - 2:
+            n = Fr - ptr
+            if n < 0 and (kk + n) > 1:
+                raise ValueError("operands could not be broadcast together with shapes (0,) (%d,): "
+                                 "overlap-add pointer ran past the utterance (reference raises too)" % (kk + n))
+        else:
+            if ptr + kk > Fr:
+                raise ValueError("operands could not be broadcast together with shapes (%d,) (%d,): "
+                                 "overlap-add pointer ran past the utterance (reference raises too)"
+                                 % (max(0, Fr - ptr), kk))
+        if i == 0:
+            ptr = int(ptr + kks - kkb2)
+        else:
+            ptr = int(ptr + kks + rng.randrange(2))
+    return ptrs
+
+
+# --------------------------------------------------------------------------- batch bookkeeping
+@dataclass
+class BatchLayout:
+    """Host-side index tables of one packed batch (what fdlp_batch points at)."""
+    lengths: np.ndarray
+    utt_wav_off: np.ndarray
+    utt_seg_off: np.ndarray
+    utt_frame_off: np.ndarray
+    seg_utt: np.ndarray
+    seg_ptr: np.ndarray
+    n_utt: int = 0
+    n_seg: int = 0
+    n_frames: int = 0
+    max_utt_frames: int = 0
+    dev: dict = field(default_factory=dict)
+
+    def to(self, device):
+        if self.dev.get("device") == device:
+            return self
+        # one pinned staging buffer, one H2D copy, then typed views
+        parts = [self.utt_wav_off.astype(np.int64), self.utt_frame_off.astype(np.int64),
+                 self.utt_seg_off.astype(np.int32), self.seg_utt.astype(np.int32), self.seg_ptr.astype(np.int32)]
+        sizes = [p.nbytes for p in parts]
+        padded = [(s + 15) // 16 * 16 for s in sizes]
+        host = torch.empty(sum(padded), dtype=torch.uint8, pin_memory=torch.cuda.is_available())
+        hv = host.numpy()
+        off = 0
+        offs = []
+        for p, s, ps in zip(parts, sizes, padded):
+            hv[off:off + s] = p.view(np.uint8).reshape(-1)
+            offs.append(off)
+            off += ps
+        d = host.to(device, non_blocking=True)
+        names = ["utt_wav_off", "utt_frame_off", "utt_seg_off", "seg_utt", "seg_ptr"]
+        dtypes = [torch.int64, torch.int64, torch.int32, torch.int32, torch.int32]
+        self.dev = {"device": device, "_buf": d, "_host": host}
+        for name, o, s, dt in zip(names, offs, sizes, dtypes):
+            self.dev[name] = d[o:o + s].view(dt)
+        return self
+
+
+def _as_rngs(jitter, n_utt):
+    """`jitter`: a random.Random consumed sequentially over the utterances (what the reference does within
+    one process), an int seed for such a generator, or a sequence of per-utterance seeds."""
+    if jitter is None:
+        jitter = 0
+    if isinstance(jitter, _random.Random):
+        return [jitter] * n_utt
+    if isinstance(jitter, (int, np.integer)):
+        r = _random.Random(int(jitter))
+        return [r] * n_utt
+    seeds = list(jitter)
+    if len(seeds) != n_utt:
+        raise ValueError("need one jitter seed per utterance")
+    return [s if isinstance(s, _random.Random) else _random.Random(int(s)) for s in seeds]
+
+
+# --------------------------------------------------------------------------- noise
+@dataclass
+class NoiseSpec:
+    """--add_noise 'type,snr' (features.py:24-44): `samples` is the int16 noise recording, `snr_db` a scalar or
+    per-utterance array, `rand` the per-utterance uniform draws standing for `np.random.rand()` (or a
+    np.random.RandomState consumed sequentially, or an int seed)."""
+    samples: Union[np.ndarray, torch.Tensor]
+    snr_db: Union[float, Sequence[float]]
+    rand: Union[None, int, np.random.RandomState, Sequence[float]] = None
+    mode: str = "int16_wrap"  # 'int16_wrap' = the reference's numpy dtype semantics; 'float' = true energies
+
+
+# --------------------------------------------------------------------------- extractor
+class FdlpExtractor:
+    """One plan (filterbank, twiddles, scratch) on one device; call it with a list of waveforms."""
+
+    def __init__(self, cfg: Optional[FdlpConfig] = None, device=None, **kwargs):
+        self.cfg = cfg if cfg is not None else FdlpConfig(**kwargs)
+        if not torch.cuda.is_available():
+            raise RuntimeError("FdlpExtractor needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
+        self._lib = L.load()
+        kind, fargs = parse_fbank_type(self.cfg.fbank_type)
+        self._weights = build_weights(self.cfg)
+        prm = L.FdlpParams()
+        prm.srate, prm.nfilters, prm.order = self.cfg.srate, self.cfg.nfilters, self.cfg.order
+        prm.coeff_num, prm.frate = self.cfg.coeff_num, self.cfg.frate
+        prm.fduration, prm.overlap_fraction = float(self.cfg.fduration), float(self.cfg.overlap_fraction)
+        prm.fbank_kind = kind
+        prm.fbank_args = (C.c_double * 5)(*fargs)
+        prm.weights = self._weights.ctypes.data_as(C.POINTER(C.c_double))
+        prm.custom_fbank = None
+        prm.dct_fp32 = 1 if self.cfg.dct_fp32 else 0
+        self._plan = C.c_void_p()
+        with torch.cuda.device(self.device):
+            L.check(self._lib.fdlp_plan_create(C.byref(prm), C.byref(self._plan)))
+        g = L.FdlpGeometry()
+        L.check(self._lib.fdlp_plan_get_geometry(self._plan, C.byref(g)))
+        self.geom = {n: getattr(g, n) for n, _ in L.FdlpGeometry._fields_}
+
+    def close(self):
+        if getattr(self, "_plan", None) and self._plan.value:
+            with torch.cuda.device(self.device):
+                self._lib.fdlp_plan_destroy(self._plan)
+            self._plan = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- introspection
+    @property
+    def nfilters(self):
+        return self.cfg.nfilters
+
+    def filterbank(self) -> np.ndarray:
+        out = np.empty((self.cfg.nfilters, self.geom["N"]), dtype=np.float64)
+        L.check(self._lib.fdlp_plan_get_fbank(self._plan, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def scratch_bytes(self, n_seg: int) -> int:
+        return int(self._lib.fdlp_plan_scratch_bytes(self._plan, int(n_seg)))
+
+    # ---- bookkeeping
+    def layout(self, lengths: Sequence[int], jitter=None) -> BatchLayout:
+        g = self.geom
+        lengths = np.asarray(lengths, dtype=np.int64)
+        n_utt = len(lengths)
+        if n_utt and lengths.min() < 2:
+            raise ValueError("utterances need at least 2 samples")
+        rngs = _as_rngs(jitter, n_utt)
+        nsegs = np.array([segment_count(int(T), g["N"], g["S"]) for T in lengths], dtype=np.int64)
+        frs = np.array([frame_count(int(T), self.cfg.frate, self.cfg.srate) for T in lengths], dtype=np.int64)
+        seg_ptr = []
+        for u in range(n_utt):
+            seg_ptr.extend(ola_pointers(int(nsegs[u]), int(frs[u]), g["kk"], g["kkb2"], g["kks"], rngs[u]))
+        lay = BatchLayout(
+            lengths=lengths,
+            utt_wav_off=np.concatenate([[0], np.cumsum(lengths)]).astype(np.int64),
+            utt_seg_off=np.concatenate([[0], np.cumsum(nsegs)]).astype(np.int32),
+            utt_frame_off=np.concatenate([[0], np.cumsum(frs)]).astype(np.int64),
+            seg_utt=np.repeat(np.arange(n_utt, dtype=np.int32), nsegs).astype(np.int32),
+            seg_ptr=np.asarray(seg_ptr, dtype=np.int32),
+            n_utt=n_utt, n_seg=int(nsegs.sum()), n_frames=int(frs.sum()),
+            max_utt_frames=int(frs.max()) if n_utt else 0)
+        return lay
+
+    @staticmethod
+    def pack(wavs: Sequence[Union[np.ndarray, torch.Tensor]]):
+        """Concatenate 1-D waveforms (all int16 or all float32) into one pinned host tensor."""
+        ts = [w if isinstance(w, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(w)) for w in wavs]
+        for t in ts:
+            if t.dim() != 1:
+                raise ValueError("waveforms must be mono 1-D arrays (the reference pads every axis otherwise)")
+        dt = ts[0].dtype
+        if dt not in (torch.int16, torch.float32) or any(t.dtype != dt for t in ts):
+            raise TypeError("waveforms must all be int16 or all float32 (what scipy.io.wavfile.read returns)")
+        total = sum(int(t.numel()) for t in ts)
+        host = torch.empty(total, dtype=dt, pin_memory=torch.cuda.is_available())
+        torch.cat(ts, out=host)
+        return host, [int(t.numel()) for t in ts]
+
+    def _batch_struct(self, wav_dev, lay, feats, cmvn, status, noise_dev):
+        b = L.FdlpBatch()
+        d = lay.dev
+        b.wav = wav_dev.data_ptr()
+        b.wav_dtype = L.FDLP_WAV_INT16 if wav_dev.dtype == torch.int16 else L.FDLP_WAV_FLOAT32
+        b.n_utt, b.n_seg, b.n_frames, b.max_utt_frames = lay.n_utt, lay.n_seg, lay.n_frames, lay.max_utt_frames
+        b.utt_wav_off = d["utt_wav_off"].data_ptr()
+        b.utt_seg_off = d["utt_seg_off"].data_ptr()
+        b.utt_frame_off = d["utt_frame_off"].data_ptr()
+        b.seg_utt = d["seg_utt"].data_ptr()
+        b.seg_ptr = d["seg_ptr"].data_ptr()
+        if noise_dev is None:
+            b.noise_mode = L.FDLP_NOISE_NONE
+        else:
+            b.noise_mode = noise_dev["mode"]
+            b.noise = noise_dev["samples"].data_ptr()
+            b.utt_noise_off = noise_dev["off"].data_ptr()
+            b.utt_snr_db = noise_dev["snr"].data_ptr()
+        b.feats = feats.data_ptr() if feats is not None else None
+        b.cmvn_acc = cmvn.data_ptr() if cmvn is not None else None
+        b.status = status.data_ptr() if status is not None else None
+        return b
+
+    def _noise_to_device(self, noise: Optional[NoiseSpec], lay: BatchLayout):
+        if noise is None:
+            return None
+        ns = noise.samples
+        if not isinstance(ns, torch.Tensor):
+            ns = torch.from_numpy(np.ascontiguousarray(ns))
+        if ns.dtype != torch.int16:
+            raise TypeError("noise recording must be int16 (scipy.io.wavfile.read of noises/<type>.wav)")
+        n_utt = lay.n_utt
+        rand = noise.rand
+        if rand is None or isinstance(rand, (int, np.integer)):
+            rand = np.random.RandomState(0 if rand is None else int(rand))
+        if isinstance(rand, np.random.RandomState):
+            draws = np.array([rand.rand() for _ in range(n_utt)])
+        else:
+            draws = np.asarray(list(rand), dtype=np.float64)
+        Tn = int(ns.numel())
+        if n_utt and Tn <= int(lay.lengths.max()):
+            raise ValueError("noise recording must be longer than every utterance (features.py:25-26)")
+        off = np.floor(draws * (Tn - lay.lengths)).astype(np.int64)  # features.py:25
+        snr = np.broadcast_to(np.asarray(noise.snr_db, dtype=np.float64), (n_utt,)).copy()
+        mode = {"int16_wrap": L.FDLP_NOISE_INT16_WRAP, "float": L.FDLP_NOISE_FLOAT}[noise.mode]
+        return dict(mode=mode, samples=ns.to(self.device, non_blocking=True),
+                    off=torch.from_numpy(off).to(self.device), snr=torch.from_numpy(snr).to(self.device))
+
+    # ---- the hot path
+    def forward_packed(self, wav_dev: torch.Tensor, lay: BatchLayout, feats: Optional[torch.Tensor] = None,
+                       cmvn: Optional[torch.Tensor] = None, status: Optional[torch.Tensor] = None,
+                       noise_dev=None):
+        """Run the whole path on an already-resident packed batch.  Returns (feats [n_frames, J] fp32, status)."""
+        lay.to(self.device)
+        if feats is None:
+            feats = torch.empty((lay.n_frames, self.cfg.nfilters), dtype=torch.float32, device=self.device)
+        if status is None:
+            status = torch.zeros(max(lay.n_utt, 1), dtype=torch.int32, device=self.device)
+        b = self._batch_struct(wav_dev, lay, feats, cmvn, status, noise_dev)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        with torch.cuda.device(self.device):
+            L.check(self._lib.fdlp_forward(self._plan, C.byref(b), C.c_void_p(stream)))
+        return feats, status
+
+    def __call__(self, wavs: Sequence[Union[np.ndarray, torch.Tensor]], jitter=None,
+                 noise: Optional[NoiseSpec] = None, cmvn: Optional[torch.Tensor] = None,
+                 return_status: bool = False):
+        """Extract FDLP spectrograms for a list of mono waveforms.  Returns a list of [Fr_u, nfilters]
+        float32 device tensors (views into one buffer), in input order."""
+        host, lengths = self.pack(wavs)
+        lay = self.layout(lengths, jitter)
+        wav_dev = host.to(self.device, non_blocking=True)
+        noise_dev = self._noise_to_device(noise, lay)
+        feats, status = self.forward_packed(wav_dev, lay, cmvn=cmvn, noise_dev=noise_dev)
+        outs = [feats[int(lay.utt_frame_off[u]):int(lay.utt_frame_off[u + 1])] for u in range(lay.n_utt)]
+        if return_status:
+            return outs, status
+        return outs
+
+    # ---- stage-level access for the parity tests (same kernels, intermediate buffers exposed)
+    def stage_dct(self, wavs, noise: Optional[NoiseSpec] = None):
+        host, lengths = self.pack(wavs)
+        lay = self.layout(lengths, 0).to(self.device)
+        wav_dev = host.to(self.device)
+        noise_dev = self._noise_to_device(noise, lay)
+        out = torch.empty((lay.n_seg, self.geom["N"]), dtype=torch.float64, device=self.device)
+        b = self._batch_struct(wav_dev, lay, None, None, None, noise_dev)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        with torch.cuda.device(self.device):
+            L.check(self._lib.fdlp_stage_dct(self._plan, C.byref(b), C.c_void_p(out.data_ptr()), C.c_void_p(stream)))
+        return out, lay
+
+    def stage_autocorr(self, dct: torch.Tensor):
+        dct = dct.contiguous()
+        n_seg = dct.shape[0]
+        r = torch.empty((n_seg, self.cfg.nfilters, self.geom["nlags"]), dtype=torch.float64, device=self.device)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        with torch.cuda.device(self.device):
+            L.check(self._lib.fdlp_stage_autocorr(self._plan, C.c_void_p(dct.data_ptr()), n_seg,
+                                                  C.c_void_p(r.data_ptr()), C.c_void_p(stream)))
+        return r
+
+    def stage_lpc_envelope(self, r: torch.Tensor):
+        r = r.contiguous()
+        n_seg, J = r.shape[0], self.cfg.nfilters
+        kw = dict(dtype=torch.float64, device=self.device)
+        lpc = torch.empty((n_seg, J, self.cfg.order + 1), **kw)
+        gain = torch.empty((n_seg, J), **kw)
+        cep = torch.empty((n_seg, J, self.geom["L"]), **kw)
+        env = torch.empty((n_seg, J, self.geom["kk"]), **kw)
+        st = torch.zeros(n_seg, dtype=torch.int32, device=self.device)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        with torch.cuda.device(self.device):
+            L.check(self._lib.fdlp_stage_lpc_envelope(
+                self._plan, C.c_void_p(r.data_ptr()), n_seg, C.c_void_p(lpc.data_ptr()), C.c_void_p(gain.data_ptr()),
+                C.c_void_p(cep.data_ptr()), C.c_void_p(env.data_ptr()), C.c_void_p(st.data_ptr()), C.c_void_p(stream)))
+        return dict(lpc=lpc, gain=gain, cep=cep, env=env, status=st)
+
+
+def fdlp_spectrogram(wavs, *, jitter=None, noise: Optional[NoiseSpec] = None, device=None, **cfg_kwargs):
+    """Functional form: `fdlp_spectrogram([wav0, wav1, ...], nfilters=80, order=150, ...)` ->
+    list of [Fr, nfilters] float32 tensors on the device."""
+    ex = FdlpExtractor(FdlpConfig(**cfg_kwargs), device=device)
+    try:
+        return ex(wavs, jitter=jitter, noise=noise)
+    finally:
+        ex.close()
