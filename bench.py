@@ -1,0 +1,377 @@
+#!/usr/bin/env python
+"""bench.py -- FDLP-spectrogram extraction throughput (audio-seconds per second, xRT).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1], SURVEY.md 8d cfg #2): 1000 synthetic utterances per GPU, 2-15 s,
+16 kHz int16, half white / half speech-like, extracted with the WSJ recipe parameters
+(/root/reference/e2e/wsj/run_fdlp_e1.sh:56-75).  One step = one pass of the hot path over that batch.
+Multi-GPU: utterances are sharded, one batch per rank (weak scaling); the only collective is the
+global-CMVN all-reduce of 2 x (J+1) float64 sums at the end of every step.
+
+Prints ONE JSON line (rank 0).  `--impl reference` times the CPU oracle port (oracle/fdlp.py, the numpy
+restatement of the reference; the reference itself is Python and is not present on the GPU box) on a
+bounded sample of the same workload with all host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+from concurrent.futures import ProcessPoolExecutor
+import multiprocessing as mp
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from speech_recognition_tools_b200 import synth  # noqa: E402
+
+WSJ = dict(nfilters=80, order=150, fduration=1.5, frate=100, overlap_fraction=0.25, coeff_num=100,
+           coeff_range="0,100", fbank_type="cochlear,1,1,1,2.5,1")
+MEL_RECIPE = dict(nfilters=80, nfft=2048, fduration=0.02, frate=100, fbank_type="mel,1")
+N_UTT = 1000
+METRIC = "audio-sec/sec (xRT) FDLP extraction"
+UNIT = "audio-seconds/second"
+WORKLOAD = ("configs[1]: WSJ-shaped batch, %d synthetic 16 kHz int16 utterances of 2-15 s per GPU (half white, "
+            "half speech-like), FDLP-spectrogram with WSJ recipe params (80 cochlear bands, LPC order 150, "
+            "1.5 s segments, 100 cepstral coeffs)" % N_UTT)
+
+
+# --------------------------------------------------------------------------- workload
+def _gen(args):
+    kind, seed, utt, T = args
+    return synth.make_utterance(kind, seed, utt, int(T), 30.0)
+
+
+def build_workload(rank: int, n_utt: int = N_UTT, workers: int = 0):
+    lengths = synth.wsj_shaped_lengths(n_utt, seed=1234 + rank)
+    jobs = [("white" if u % 2 == 0 else "speechlike", 100 + rank, u, int(lengths[u])) for u in range(n_utt)]
+    workers = workers or min(16, os.cpu_count() or 1)
+    if workers > 1:
+        with ProcessPoolExecutor(max_workers=workers, mp_context=mp.get_context('spawn')) as ex:
+            wavs = list(ex.map(_gen, jobs, chunksize=8))
+    else:
+        wavs = [_gen(j) for j in jobs]
+    return wavs, lengths
+
+
+# --------------------------------------------------------------------------- CPU oracle port (baseline)
+_ORACLE_FB = {}
+
+
+def _oracle_one(args):
+    os.environ.setdefault("OMP_NUM_THREADS", "1")  # e2e/wsj/path.sh:22
+    x, seed = args
+    import random
+
+    from oracle import fdlp as ofdlp
+    key = "wsj"
+    if key not in _ORACLE_FB:
+        _ORACLE_FB[key] = ofdlp.make_fbank(WSJ["fbank_type"], WSJ["nfilters"], int(2 * WSJ["fduration"] * 16000), 16000)
+    out = ofdlp.fdlp_spectrogram(x, fbank=_ORACLE_FB[key], rng=random.Random(seed), **WSJ)
+    return out.shape[0]
+
+
+def cpu_oracle_throughput(wavs, cores: int, pool=None):
+    """Audio-seconds per wall-second of the oracle port on `wavs`, one process per core (mirrors the recipes'
+    --nj job arrays with OMP_NUM_THREADS=1)."""
+    audio = sum(len(w) for w in wavs) / 16000.0
+    jobs = [(w, i) for i, w in enumerate(wavs)]
+    own = pool is None
+    if own:
+        pool = ProcessPoolExecutor(max_workers=cores, mp_context=mp.get_context('spawn'))
+        list(pool.map(_oracle_one, [(wavs[0][:40000], 0)] * cores))  # start workers, build the filterbank once each
+    t0 = time.perf_counter()
+    list(pool.map(_oracle_one, jobs, chunksize=1))
+    dt = time.perf_counter() - t0
+    if own:
+        pool.shutdown()
+    return audio / dt, audio, dt
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Samples SM clock and throttle reasons with NVML while the timed region runs."""
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+        except Exception:  # noqa: BLE001
+            self._nv = None
+
+    def _run(self):
+        nv = self._nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksThrottleReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+                for bit, nm in names.items():
+                    if mask & bit:
+                        self.reasons.add(nm)
+            except Exception:  # noqa: BLE001
+                pass
+            self._stop.wait(0.02)
+
+    def start(self):
+        if self._nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join()
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# --------------------------------------------------------------------------- our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from speech_recognition_tools_b200 import _lib
+    from speech_recognition_tools_b200.fdlp import FdlpConfig, FdlpExtractor
+    from speech_recognition_tools_b200.mel import MelConfig, MelExtractor
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node %d for --gpus %d" % (args.gpus, args.gpus))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    wavs, lengths = build_workload(rank)
+    audio_s = float(lengths.sum()) / 16000.0
+
+    ex = FdlpExtractor(FdlpConfig(**WSJ), device=dev)
+    J = WSJ["nfilters"]
+    host_wav, lens = ex.pack(wavs)
+    lay = ex.layout(lens, jitter=rank).to(dev)
+    wav_dev = host_wav.to(dev)
+    feats = torch.empty((lay.n_frames, J), dtype=torch.float32, device=dev)
+    status = torch.zeros(lay.n_utt, dtype=torch.int32, device=dev)
+    cmvn = torch.zeros((2, J + 1), dtype=torch.float64, device=dev)
+    feats_host = torch.empty((lay.n_frames, J), dtype=torch.float32, pin_memory=True)
+
+    def step_resident():
+        cmvn.zero_()
+        ex.forward_packed(wav_dev, lay, feats=feats, cmvn=cmvn, status=status)
+        if world > 1:
+            dist.all_reduce(cmvn)  # global CMVN: the path's one collective (e2e/wsj/run_fdlp_e1.sh:280)
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    def timed(fn, steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sync_all()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        sync_all()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    # ---- device-resident throughput (`value`) ----
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    total_ms = timed(step_resident, args.steps)
+    clocks = sampler.stop()
+    ms_per_step = total_ms / args.steps
+    total_audio = torch.tensor([audio_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(total_audio)
+    total_audio = float(total_audio.item())
+    value = total_audio / (ms_per_step * 1e-3)
+    bad_status = int((status != 0).sum().item())
+
+    # ---- end to end through the public API path: pinned host wav -> device, features -> pinned host ----
+    idx_bytes = sum(int(v.numel() * v.element_size()) for k, v in lay.dev.items() if k == "_buf")
+
+    def step_e2e():
+        lay.dev = {}
+        lay.to(dev)                                   # index tables: pinned -> device
+        w = host_wav.to(dev, non_blocking=True)       # samples: pinned -> device
+        cmvn.zero_()
+        ex.forward_packed(w, lay, feats=feats, cmvn=cmvn, status=status)
+        if world > 1:
+            dist.all_reduce(cmvn)
+        feats_host.copy_(feats, non_blocking=True)    # result: device -> pinned host
+        torch.cuda.current_stream(dev).synchronize()
+
+    for _ in range(2):
+        step_e2e()
+    e2e_steps = max(3, min(args.steps, 10))
+    e2e_ms = timed(step_e2e, e2e_steps) / e2e_steps
+    e2e_value = total_audio / (e2e_ms * 1e-3)
+    h2d = int(host_wav.numel() * host_wav.element_size()) + idx_bytes
+    d2h = int(feats_host.numel() * 4)
+
+    # ---- per-stage device times of the dominant kernel (CUDA events inside fdlp_forward, same stream) ----
+    ex.set_profiling(True)
+    stage = {"dct": 0.0, "autocorr": 0.0, "lpc_env": 0.0, "ola": 0.0}
+    nprof = 5
+    for _ in range(nprof):
+        step_resident()
+        s = ex.stage_ms()
+        for k in stage:
+            stage[k] += s[k] / nprof
+    ex.set_profiling(False)
+
+    out = None
+    if rank == 0:
+        lib = _lib.load()
+        import ctypes as C
+        dfma, dmma = C.c_double(), C.c_double()
+        _lib.check(lib.fdlp_measure_fp64_peak(C.byref(dfma), C.byref(dmma)))
+        peak = max(dfma.value, dmma.value)
+        g = ex.geom
+        # ALGORITHMIC flops of the autocorrelation: 2 * (p+2) * sum_j len(supp_j) per segment;
+        # the cochlear filters have full support (N taps)
+        ac_flops = 2.0 * g["nlags"] * J * g["N"] * lay.n_seg
+        achieved = ac_flops / (stage["autocorr"] * 1e-3) / 1e12
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "autocorr_traffic.json")
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+            except Exception:  # noqa: BLE001
+                traffic = None
+        roofline = {"bound": "tensor", "pipe": "fp64 (DMMA.8x8x4 / DFMA)", "kernel": "autocorr_dmma_kernel",
+                    "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                    "traffic": traffic, "peak_source": "fdlp_measure_fp64_peak, measured live on this GPU "
+                    "(MEASURED_PEAKS.json has no FP64 entry); dfma=%.2f dmma=%.2f" % (dfma.value, dmma.value),
+                    "algorithmic_flops_per_launch": ac_flops, "kernel_ms": stage["autocorr"],
+                    "stage_ms": stage, "share_of_step": stage["autocorr"] / sum(stage.values())}
+
+        # ---- mel-spectrogram baseline path on the same batch (BASELINE.json configs[1]) ----
+        mel = MelExtractor(MelConfig(**MEL_RECIPE), device=dev)
+        mlay = mel.layout(lens).to(dev)
+        mfeats = torch.empty((mlay.n_frames, MEL_RECIPE["nfilters"]), dtype=torch.float32, device=dev)
+        for _ in range(3):
+            mel.forward_packed(wav_dev, mlay, feats=mfeats)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(dev)
+        e0.record()
+        for _ in range(5):
+            mel.forward_packed(wav_dev, mlay, feats=mfeats)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        mel_ms = e0.elapsed_time(e1) / 5
+        mel_bytes = host_wav.numel() * 2 + mfeats.numel() * 4
+        mel_info = {"value": audio_s / (mel_ms * 1e-3), "unit": UNIT, "ms_per_step": mel_ms,
+                    "hbm_gbs_algorithmic": mel_bytes / (mel_ms * 1e-3) / 1e9}
+
+        # ---- CPU baseline: the oracle port on a bounded sample of the same workload ----
+        cores = os.cpu_count() or 1
+        n_sample = min(len(wavs), max(cores * 3, 32))
+        cpu_val, cpu_audio, cpu_dt = cpu_oracle_throughput(wavs[:n_sample], cores)
+        cpu_baseline = {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port",
+                        "sample": "first %d utterances of the workload (%.0f audio-s) in %.1f s wall, one process "
+                                  "per core, OMP_NUM_THREADS=1" % (n_sample, cpu_audio, cpu_dt)}
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "params": WSJ, "utterances_per_gpu": N_UTT,
+                       "audio_seconds_total": total_audio, "segments_per_gpu": lay.n_seg, "frames_per_gpu": lay.n_frames,
+                       "l2": "no flush needed: per-step inputs+scratch (%.1f GB) exceed the 126 MB L2"
+                             % ((ex.scratch_bytes(lay.n_seg) + h2d) / 1e9),
+                       "sharding": "utterances sharded across ranks, no data-path collective; CMVN all-reduce per step",
+                       "utterances_with_status": bad_status},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
+                    "ms_per_step": e2e_ms},
+            "gpu_launches": 4 * args.steps * world,
+            "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "mel_baseline": mel_info,
+        }
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if out is not None:
+        print(json.dumps(out))
+        sys.stdout.flush()
+
+
+# --------------------------------------------------------------------------- reference arm
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    n_sample = max(cores * 2, 16)
+    wavs, lengths = build_workload(0, n_utt=n_sample, workers=min(cores, 16))
+    pool = ProcessPoolExecutor(max_workers=cores, mp_context=mp.get_context('spawn'))
+    list(pool.map(_oracle_one, [(wavs[0][:40000], 0)] * cores))
+    warm = max(args.warmup, 1)
+    for _ in range(min(warm, 1)):
+        cpu_oracle_throughput(wavs, cores, pool)
+    t_audio, t_wall = 0.0, 0.0
+    for _ in range(args.steps):
+        _, a, dt = cpu_oracle_throughput(wavs, cores, pool)
+        t_audio += a
+        t_wall += dt
+    pool.shutdown()
+    value = t_audio / t_wall
+    sample = ("each step = first %d utterances of the rank-0 workload (%.0f audio-s), oracle/fdlp.py (numpy/scipy "
+              "restatement of the reference, float64), one process per core, OMP_NUM_THREADS=1" % (n_sample, t_audio / args.steps))
+    out = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": warm, "ms_per_step": 1e3 * t_wall / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "params": WSJ, "note": "CPU reference arm runs on rank 0 only, on a bounded sample"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out))
+    sys.stdout.flush()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -129,6 +129,12 @@ int64_t fdlp_plan_scratch_bytes(const fdlp_plan* plan, int32_t n_seg);
 /* the whole hot path for one packed batch, stream-ordered */
 int fdlp_forward(fdlp_plan* plan, const fdlp_batch* batch, void* stream);
 
+/* optional per-stage timing of fdlp_forward with CUDA events recorded on the launching stream:
+ * out4 = {framing+DCT (incl. noise coefficient), autocorrelation, LPC+cepstrum+envelope, OLA+log} in ms
+ * for the most recent fdlp_forward (get_stage_ms waits for that call to finish) */
+int fdlp_plan_set_profiling(fdlp_plan* plan, int32_t enable);
+int fdlp_plan_get_stage_ms(fdlp_plan* plan, float* out4);
+
 /* stage-level entry points (used by the parity tests to check each kernel against the oracle;
  * they run the same kernels fdlp_forward launches, on the plan's scratch) */
 int fdlp_stage_dct(fdlp_plan* plan, const fdlp_batch* batch, double* dct_out /*[n_seg,N]*/, void* stream);

@@ -169,6 +169,9 @@ struct fdlp_plan {
   // scratch (grow-only)
   int cap_seg = 0, cap_utt = 0;
   double *d_dct = nullptr, *d_r = nullptr, *d_env = nullptr, *d_alpha = nullptr;
+  // optional per-stage timing (CUDA events on the launching stream)
+  bool profiling = false;
+  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
 static void plan_free(fdlp_plan* p) {
@@ -177,6 +180,7 @@ static void plan_free(fdlp_plan* p) {
   cudaFree(p->d_ham); cudaFree(p->d_postB); cudaFree(p->d_fbank); cudaFree(p->d_row_lo); cudaFree(p->d_row_hi);
   cudaFree(p->d_weights); cudaFree(p->d_cosM); cudaFree(p->d_wratio);
   cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_alpha);
+  for (int i = 0; i < 5; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
   delete p;
 }
 
@@ -456,10 +460,15 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
   if (!b->feats || !b->utt_frame_off || !b->seg_ptr) return set_err(FDLP_E_ARG, "null output / frame pointers%s", "");
   cudaStream_t st = (cudaStream_t)stream;
   if ((rc = ensure_scratch(p, b->n_seg, b->n_utt))) return rc;
+  const bool prof = p->profiling;
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[0], st));
   if ((rc = launch_noise(p, b, st))) return rc;
   if ((rc = launch_dct(p, b, p->d_dct, st))) return rc;
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[1], st));
   if ((rc = launch_autocorr(p, p->d_dct, b->n_seg, p->d_r, st))) return rc;
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[2], st));
   if ((rc = launch_lpc(p, p->d_r, b->n_seg, nullptr, nullptr, nullptr, p->d_env, b->status, b->seg_utt, st))) return rc;
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[3], st));
   OlaArgs o;
   o.env = p->d_env; o.utt_seg_off = b->utt_seg_off; o.utt_frame_off = b->utt_frame_off; o.seg_ptr = b->seg_ptr;
   o.feats = b->feats; o.cmvn = b->cmvn_acc; o.J = p->prm.nfilters; o.kk = p->g.kk; o.kkb2 = p->g.kkb2;
@@ -470,6 +479,22 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
   const dim3 grid(b->n_utt, (unsigned)max_tiles), block(256);
   ola_log_kernel<<<grid, block, p->ola_smem, st>>>(o);
   FDLP_CUDA(cudaGetLastError());
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[4], st));
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_plan_set_profiling(fdlp_plan* p, int32_t enable) {
+  if (!p) return set_err(FDLP_E_ARG, "null argument%s", "");
+  if (enable && !p->ev[0])
+    for (int i = 0; i < 5; ++i) FDLP_CUDA(cudaEventCreate(&p->ev[i]));
+  p->profiling = enable != 0;
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_plan_get_stage_ms(fdlp_plan* p, float* out4) {
+  if (!p || !out4 || !p->ev[0]) return set_err(FDLP_E_ARG, "profiling was not enabled%s", "");
+  FDLP_CUDA(cudaEventSynchronize(p->ev[4]));
+  for (int i = 0; i < 4; ++i) FDLP_CUDA(cudaEventElapsedTime(&out4[i], p->ev[i], p->ev[i + 1]));
   return FDLP_OK;
 }
 

@@ -264,6 +264,15 @@ class FdlpExtractor:
     def scratch_bytes(self, n_seg: int) -> int:
         return int(self._lib.fdlp_plan_scratch_bytes(self._plan, int(n_seg)))
 
+    def set_profiling(self, enable: bool = True):
+        L.check(self._lib.fdlp_plan_set_profiling(self._plan, 1 if enable else 0))
+
+    def stage_ms(self):
+        """Per-stage CUDA-event durations of the most recent forward (needs set_profiling(True))"""
+        out = (C.c_float * 4)()
+        L.check(self._lib.fdlp_plan_get_stage_ms(self._plan, out))
+        return dict(dct=out[0], autocorr=out[1], lpc_env=out[2], ola=out[3])
+
     # ---- bookkeeping
     def layout(self, lengths: Sequence[int], jitter=None) -> BatchLayout:
         g = self.geom

@@ -1,0 +1,150 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Everything goes through the C ABI
+(libfdlp_b200.so via ctypes); the oracle and the golden fixtures are only the checker.
+
+Tolerances: the product target is max-abs <= 1e-3 and rel <= 1e-4 on the natural-log features
+(BASELINE.json north_star).  The CUDA path computes in float64 and stores float32, so the tests hold it
+to 5e-6 absolute + 2e-7 relative (float32 rounding of values up to ~20), far inside the target."""
+import random
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import cmvn as ocmvn
+from oracle import fdlp as ofdlp
+from tests.golden_util import FDLP_DEFAULTS, golden_cases, load_case, split_params
+from speech_recognition_tools_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+FLOOR = float(np.log(1e-14))
+ATOL, RTOL = 5e-6, 2e-7
+WSJ = dict(nfilters=80, order=150, fduration=1.5, frate=100, overlap_fraction=0.25, coeff_num=100,
+           coeff_range="0,100", fbank_type="cochlear,1,1,1,2.5,1")
+
+_cache = {}
+
+
+def extractor(lifter=None, **kw):
+    from speech_recognition_tools_b200.fdlp import FdlpConfig, FdlpExtractor
+    key = repr(sorted(kw.items())) + repr(lifter)
+    if key not in _cache:
+        _cache[key] = FdlpExtractor(FdlpConfig(lifter=lifter, **kw), device="cuda:0")
+    return _cache[key]
+
+
+def assert_feats_close(got, ref):
+    got = np.asarray(got, dtype=np.float64)
+    assert got.shape == ref.shape
+    fl_ref = ref <= FLOOR + 1e-9
+    assert np.array_equal(fl_ref, got <= FLOOR + 1e-4), "floor (never-written) frames differ"
+    np.testing.assert_allclose(got[fl_ref], np.float32(FLOOR), rtol=0, atol=0)
+    np.testing.assert_allclose(got[~fl_ref], ref[~fl_ref], rtol=RTOL, atol=ATOL)
+
+
+@pytest.mark.parametrize("name", [n for n in golden_cases("fdlp") if n != "fdlp_opt_diff"])
+def test_fdlp_matches_reference_golden(name):
+    from speech_recognition_tools_b200.fdlp import NoiseSpec
+    c = load_case(name)
+    meta = c["meta"]
+    p, add_noise, lifter = split_params(meta)
+    ex = extractor(lifter=lifter, **dict(FDLP_DEFAULTS, **p))
+    noise = None
+    if add_noise and add_noise != "clean":
+        nm, snr = add_noise.split(",")
+        noise = NoiseSpec(samples=c["noise"]["data"], snr_db=float(snr), rand=meta["seed"])
+    outs, st = ex([c["x"]], jitter=[meta["seed"]], noise=noise, return_status=True)
+    assert int(st.cpu()[0]) == 0
+    assert_feats_close(outs[0].cpu().numpy(), c["feats"])
+
+
+def test_stage_by_stage_against_oracle():
+    """frames+DCT, autocorrelation lags, LPC, gain, cepstrum and envelope, each against the oracle."""
+    x = synth.make_utterance("speechlike", 3, 5, 30000, 30.0)
+    ex = extractor(**FDLP_DEFAULTS)
+    fb = ofdlp.create_fbank(20, 16000, 16000, 1.0)
+    st = ofdlp.fdlp_stages(x, nfilters=20, order=50, fduration=0.5, overlap_fraction=0.25, coeff_num=50, fbank=fb)
+    np.testing.assert_allclose(ex.filterbank(), fb[:, :-1], rtol=1e-13, atol=0)
+    dct, lay = ex.stage_dct([x])
+    assert dct.shape == st["dct"].shape
+    scale = np.abs(st["dct"]).max()
+    np.testing.assert_allclose(dct.cpu().numpy(), st["dct"], rtol=0, atol=1e-12 * scale)
+    r = ex.stage_autocorr(dct)
+    r0 = np.abs(st["r"][:, :, :1])
+    assert np.max(np.abs(r.cpu().numpy() - st["r"]) / r0) < 1e-12
+    out = ex.stage_lpc_envelope(torch.from_numpy(st["r"]).cuda())
+    assert int(out["status"].abs().sum()) == 0
+    np.testing.assert_allclose(out["gain"].cpu().numpy(), st["gg"], rtol=1e-6)
+    np.testing.assert_allclose(out["cep"].cpu().numpy(), st["cep"], rtol=0, atol=1e-6)
+    np.testing.assert_allclose(out["lpc"].cpu().numpy(), st["lpc"], rtol=0, atol=1e-5 * np.abs(st["lpc"]).max())
+
+
+def test_batch_equals_single_utterance_bit_for_bit():
+    """Ragged batch (nseg 1..many, mixed families) == each utterance on its own, exactly."""
+    ex = extractor(**WSJ)
+    Ts = [17000, 32000, 52001, 100000, 240000, 18001, 36000]
+    wavs = [synth.make_utterance("white" if i % 2 else "speechlike", 9, i, T, 30.0) for i, T in enumerate(Ts)]
+    seeds = list(range(40, 40 + len(Ts)))
+    batch = ex(wavs, jitter=seeds)
+    for w, s, b in zip(wavs, seeds, batch):
+        single = ex([w], jitter=[s])[0]
+        assert torch.equal(single, b)
+
+
+def test_wsj_batch_against_oracle_and_cmvn():
+    ex = extractor(**WSJ)
+    Ts = [40000, 70000, 33000]
+    wavs = [synth.make_utterance("speechlike" if i % 2 == 0 else "white", 21, i, T, 300.0) for i, T in enumerate(Ts)]
+    cm = torch.zeros((2, 81), dtype=torch.float64, device="cuda:0")
+    outs = ex(wavs, jitter=[5, 6, 7], cmvn=cm)
+    fb = ofdlp.make_fbank(WSJ["fbank_type"], 80, 48000, 16000)
+    for w, s, o in zip(wavs, (5, 6, 7), outs):
+        ref = ofdlp.fdlp_spectrogram(w, fbank=fb, rng=random.Random(s), **WSJ)
+        assert_feats_close(o.cpu().numpy(), ref)
+    # CMVN sums: float64 sums over the float32 features (Kaldi compute-cmvn-stats layout)
+    ref_stats = ocmvn.cmvn_stats([o.cpu().numpy() for o in outs])
+    np.testing.assert_allclose(cm.cpu().numpy(), ref_stats, rtol=1e-12, atol=1e-9)
+
+
+def test_float_noise_mode_and_status_flags():
+    from speech_recognition_tools_b200.fdlp import NoiseSpec
+    ex = extractor(**FDLP_DEFAULTS)
+    x = synth.make_utterance("white", 2, 2, 24000)
+    nz = synth.noise_int16("pink", 60000)
+    out = ex([x], jitter=[1], noise=NoiseSpec(samples=nz, snr_db=10.0, rand=[0.25], mode="float"))[0].cpu().numpy()
+    off = int(np.floor(0.25 * (len(nz) - len(x))))
+    ns = nz[off:off + len(x)].astype(np.float64)
+    xs = x.astype(np.float64)
+    alp = np.sqrt(np.mean(xs ** 2) / (np.mean(ns ** 2) * 10 ** (10.0 / 10)))
+    ref = ofdlp.fdlp_spectrogram(xs + alp * ns, rng=random.Random(1), **FDLP_DEFAULTS)
+    assert_feats_close(out, ref)
+    # an all-zero utterance makes every Toeplitz system singular: the reference raises LinAlgError,
+    # the library reports it per utterance instead of silently dropping it
+    outs, st = ex([np.zeros(20000, dtype=np.int16), x], jitter=[1, 1], return_status=True)
+    st = st.cpu().numpy()
+    assert st[0] != 0 and st[1] == 0
+
+
+def test_full_size_properties():
+    """BASELINE-sized segments (N = 24000, 80 bands, order 150): properties that need no oracle --
+    frame counts, floor-frame layout implied by the pointer trace, and linearity of the log features in the
+    input gain (scaling the waveform by g adds exactly log(g) to every non-floor frame)."""
+    ex = extractor(**WSJ)
+    lengths = synth.wsj_shaped_lengths(24, seed=77)
+    wavs = [synth.make_utterance("white", 31, i, int(T)) // 4 for i, T in enumerate(lengths)]
+    seeds = list(range(24))
+    a = ex(wavs, jitter=seeds)
+    b = ex([w * 2 for w in wavs], jitter=seeds)
+    lay = ex.layout([len(w) for w in wavs], jitter=seeds)
+    for u, (fa, fb_) in enumerate(zip(a, b)):
+        assert fa.shape == (int(np.ceil(len(wavs[u]) * 100 / 16000)), 80)
+        fa, fb_ = fa.cpu().numpy().astype(np.float64), fb_.cpu().numpy().astype(np.float64)
+        floor = fa <= FLOOR + 1e-4
+        np.testing.assert_allclose((fb_ - fa)[~floor], np.log(2.0), rtol=0, atol=2e-5)
+        s0, s1 = lay.utt_seg_off[u], lay.utt_seg_off[u + 1]
+        covered = np.zeros(fa.shape[0], dtype=bool)
+        covered[:min(ex.geom["kkb2"], fa.shape[0])] = True
+        for p in lay.seg_ptr[s0 + 1:s1]:
+            covered[p:p + ex.geom["kk"]] = True
+        # hanning(kk) is zero at both ends, so first/last frame of a lone segment may be floor as well
+        assert np.all(floor[~covered])

@@ -1,0 +1,112 @@
+"""CPU tests of the host-side logic and of the C-ABI library (no GPU needed): the library loads and exports
+every symbol include/fdlp_b200.h declares; the Python bookkeeping (segment / frame counts, overlap-add
+pointer trace with jitter, folded weights) agrees with the oracle."""
+import os
+import random
+import re
+
+import numpy as np
+import pytest
+
+from oracle import fdlp as ofdlp
+from speech_recognition_tools_b200 import _lib, synth
+from speech_recognition_tools_b200.fdlp import (FdlpConfig, build_weights, frame_count, ola_pointers,
+                                                parse_fbank_type, segment_count)
+from speech_recognition_tools_b200.mel import mel_frame_count
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    lib = _lib.load()
+    header = open(os.path.join(ROOT, "include", "fdlp_b200.h")).read()
+    declared = set(re.findall(r"\b((?:fdlp|mel|cmvn)_[a-z0-9_]+)\s*\(", header))
+    declared -= {"fdlp_plan", "mel_plan"}
+    assert declared, "no declarations parsed"
+    bound = {name for name, _, _ in _lib.SYMBOLS}
+    assert declared == bound, (declared ^ bound)
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.fdlp_version() >= 100
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "speech_recognition_tools_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(".py"):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
+
+
+@pytest.mark.parametrize("fdur", [0.5, 1.5])
+def test_segment_and_frame_counts_match_oracle(fdur):
+    g = ofdlp.derived_sizes(fdur, 100, 0.25)
+    rng = np.random.default_rng(3)
+    Ts = [2, 3, 100, g["S"], g["S"] + 1, g["S"] + 2, 2 * g["S"] + 1] + list(rng.integers(2, 300000, 40))
+    for T in Ts:
+        fr = ofdlp.get_frames(np.ones(int(T)), 16000, g["lfr"], fdur)
+        assert segment_count(int(T), g["N"], g["S"]) == fr.shape[0]
+        assert frame_count(int(T), 100, 16000) == int(np.ceil(T * 100 / 16000))
+
+
+def test_mel_frame_count_matches_oracle():
+    for T in (2, 161, 162, 320, 321, 8000, 8001, 40001):
+        fr = ofdlp.get_frames(np.ones(T), 16000, 100, 0.02)
+        assert mel_frame_count(T, 320, 160) == fr.shape[0]
+
+
+@pytest.mark.parametrize("fdur,T", [(0.5, 40001), (0.5, 100), (0.5, 3000), (1.5, 100000), (1.5, 17000), (1.5, 160000)])
+def test_ola_pointer_trace_matches_oracle(fdur, T):
+    g = ofdlp.derived_sizes(fdur, 100, 0.25)
+    x = synth.white_int16(0, 0, T)
+    params = dict(nfilters=4, order=8, fduration=fdur, coeff_num=10, coeff_range="0,9")
+    for seed in (0, 1, 7):
+        _, tr = ofdlp.fdlp_spectrogram(x, rng=random.Random(seed), return_trace=True, **params)
+        ptrs = ola_pointers(tr["nseg"], tr["Fr"], g["kk"], g["kkb2"], g["kks"], random.Random(seed))
+        assert ptrs == tr["ptrs"]
+
+
+def test_ola_pointer_overflow_raises_like_the_reference():
+    # default params drift +1 frame per segment and overflow for long utterances
+    g = ofdlp.derived_sizes(0.5, 100, 0.25)
+    T = 35 * 16000
+    nseg, Fr = segment_count(T, g["N"], g["S"]), frame_count(T, 100, 16000)
+    with pytest.raises(ValueError):
+        ola_pointers(nseg, Fr, g["kk"], g["kkb2"], g["kks"], random.Random(0))
+
+
+def test_weights_match_oracle():
+    lifter = list(1.0 + 0.1 * np.arange(50))
+    for kw in (dict(), dict(coeff_range="0,49", gamma_weight="2,3,4"), dict(lifter=lifter, coeff_range="1,40"),
+               dict(odd_mod_zero=True, coeff_range="0,49"), dict(coeff_num=450, coeff_range="1,450", order=150)):
+        cfg = FdlpConfig(**kw)
+        w = build_weights(cfg)
+        ref = ofdlp.build_weights(cfg.coeff_num, cfg.coeff_range, cfg.order, cfg.fduration, cfg.gamma_weight, cfg.lifter)
+        if cfg.odd_mod_zero:
+            ref = ref.copy()
+            ref[1::2] = 0
+        np.testing.assert_array_equal(w, ref)
+    with pytest.raises(ValueError):
+        build_weights(FdlpConfig(gamma_weight="2,3,4", order=50, coeff_num=40))
+
+
+def test_fbank_type_parsing_errors():
+    with pytest.raises(ValueError):
+        parse_fbank_type("mel")
+    with pytest.raises(ValueError):
+        parse_fbank_type("cochlear,1,1")
+    with pytest.raises(ValueError):
+        parse_fbank_type("gammatone,1")
+    assert parse_fbank_type("cochlear,1,1,1,2.5,1")[1] == [1.0, 1.0, 1.0, 2.5, 1.0]
+
+
+def test_synth_is_deterministic_and_never_silent():
+    a = synth.white_int16(3, 5, 5000)
+    b = synth.white_int16(3, 5, 5000)
+    assert np.array_equal(a, b) and a.dtype == np.int16
+    assert 2500 < a.astype(np.float64).std() < 3500
+    s = synth.speechlike_int16(3, 5, 48000, 30.0)
+    assert s.dtype == np.int16 and np.abs(s).max() > 1000
+    for k in range(0, 48000 - 8000, 6000):
+        assert np.any(s[k:k + 8000] != 0)

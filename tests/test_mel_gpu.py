@@ -1,0 +1,36 @@
+"""GPU parity tests of the mel-spectrogram baseline path against the reference's golden outputs.
+Tolerance: 1e-4 in log10; the kernel is float32."""
+import numpy as np
+import pytest
+
+from tests.golden_util import MEL_DEFAULTS, golden_cases, load_case, split_params
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", golden_cases("mel"))
+def test_mel_matches_reference_golden(name):
+    from speech_recognition_tools_b200.mel import MelConfig, MelExtractor
+    c = load_case(name)
+    p, _, _ = split_params(c["meta"])
+    kw = dict(MEL_DEFAULTS, **p)
+    ex = MelExtractor(MelConfig(**kw), device="cuda:0")
+    got = ex([c["x"]])[0].cpu().numpy().astype(np.float64)
+    ref = c["feats"]
+    assert got.shape == ref.shape
+    if kw["spectrum_type"] == "power":
+        np.testing.assert_allclose(got, ref, rtol=2e-5)
+    else:
+        np.testing.assert_allclose(got, ref, rtol=0, atol=1e-4)
+    ex.close()
+
+
+def test_mel_batch_equals_single():
+    import torch
+    from speech_recognition_tools_b200 import synth
+    from speech_recognition_tools_b200.mel import MelConfig, MelExtractor
+    ex = MelExtractor(MelConfig(nfilters=80, nfft=2048), device="cuda:0")
+    wavs = [synth.make_utterance("white", 4, i, T) for i, T in enumerate((161, 8000, 40001, 322))]
+    outs = ex(wavs)
+    for w, o in zip(wavs, outs):
+        assert torch.equal(ex([w])[0], o)
