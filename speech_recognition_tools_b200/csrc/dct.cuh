@@ -34,7 +34,9 @@ struct DctArgs {
   const int32_t* perm;     // [n] position of X[k] after the DIF passes
   const double2* unpackA;  // [n+1] exp(-2 pi i k / N)
   const double2* postB;    // [N]  exp(-i pi k / (2N)) * 2 / sqrt(2N)
-  double* out;             // [n_seg, N]
+  double* out;             // [n_seg, out_ld]
+  int out_ld;              // row stride of out (>= N)
+  int out_pad;             // coefficients 0..out_pad-1 are repeated at N..N+out_pad-1 (circular extension)
   int vec_ok;              // wav base pointer is 16-byte aligned
 };
 
@@ -182,7 +184,7 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
   }
 
   // ---- unpack to the length-N real FFT, Makhoul post-twiddle, scale, store ----
-  double* out = a.out + (size_t)seg * N;
+  double* out = a.out + (size_t)seg * a.out_ld;
   const int n = a.n;
   for (int kq = threadIdx.x; kq <= n; kq += blockDim.x) {
     const int k1 = (kq == n) ? 0 : kq;
@@ -198,7 +200,9 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
     const cplx<double> AD = cmul(cplx<double>{A.x, A.y}, D);
     const cplx<double> V = {E.x + AD.y, E.y - AD.x};
     const double2 B = __ldg(a.postB + kq);
-    out[kq] = B.x * V.x - B.y * V.y;  // Re(B * V), B carries 2/sqrt(2N)
+    const double yk = B.x * V.x - B.y * V.y;  // Re(B * V), B carries 2/sqrt(2N)
+    out[kq] = yk;
+    if (kq < a.out_pad) out[N + kq] = yk;
     if (kq > 0 && kq < n) {
       const double2 B2 = __ldg(a.postB + (N - kq));
       out[N - kq] = B2.x * V.x + B2.y * V.y;  // Re(B2 * conj(V))

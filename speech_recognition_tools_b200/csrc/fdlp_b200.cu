@@ -157,6 +157,7 @@ struct fdlp_plan {
   fdlp_geometry g;
   int device = 0;
   int na = 0, a_groups = 1;  // autocorrelation lag blocking
+  int pad = 0, ld = 0;       // circular extension (doubles) and row stride of the DCT / filterbank buffers
   bool dct_fp64 = true;
   size_t dct_smem = 0, ac_smem = 0, lpc_smem = 0, ola_smem = 0;
   std::vector<double> h_fbank;  // [J, N]
@@ -184,18 +185,12 @@ static void plan_free(fdlp_plan* p) {
   delete p;
 }
 
-template <int NA>
-static int ac_set_attr(size_t smem) {
-  FDLP_CUDA(cudaFuncSetAttribute(autocorr_dmma_kernel<NA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  return 0;
-}
-
 static int ensure_scratch(fdlp_plan* p, int n_seg, int n_utt) {
   if (n_seg > p->cap_seg) {
     cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env);
     p->d_dct = p->d_r = p->d_env = nullptr; p->cap_seg = 0;
     const size_t J = p->prm.nfilters;
-    FDLP_CUDA(cudaMalloc((void**)&p->d_dct, (size_t)n_seg * p->g.N * sizeof(double)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_dct, (size_t)n_seg * p->ld * sizeof(double)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_r, (size_t)n_seg * J * p->g.nlags * sizeof(double)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_env, (size_t)n_seg * J * p->g.kk * sizeof(double)));
     p->cap_seg = n_seg;
@@ -250,6 +245,12 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   }
   p->a_groups = groups;
   p->na = (((na_total + groups - 1) / groups) + 3) & ~3;
+  p->pad = 8 * (p->na * groups + 12);
+  p->ld = N + p->pad;
+  if (p->pad > N / 2) {
+    plan_free(p);
+    return set_err(FDLP_E_UNSUPPORTED, "LPC order %s%ld too large for this segment length", "", prm->order);
+  }
 
   int rc = build_fft_tables(N / 2, &p->fft);
   if (rc) { plan_free(p); return rc; }
@@ -291,7 +292,10 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
         hi[j] = std::min(rows, ((last / 8 + 1) + 3) & ~3);
       }
     }
-    if ((rc = upload(&p->d_fbank, p->h_fbank)) || (rc = upload(&p->d_row_lo, lo)) || (rc = upload(&p->d_row_hi, hi))) {
+    std::vector<double> fpad((size_t)J * p->ld);
+    for (int j = 0; j < J; ++j)
+      for (int k = 0; k < p->ld; ++k) fpad[(size_t)j * p->ld + k] = p->h_fbank[(size_t)j * N + (k % N)];
+    if ((rc = upload(&p->d_fbank, fpad)) || (rc = upload(&p->d_row_lo, lo)) || (rc = upload(&p->d_row_hi, hi))) {
       plan_free(p); return rc;
     }
   }
@@ -338,14 +342,16 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   }
   SET_SMEM(lpc_envelope_kernel, p->lpc_smem);
   SET_SMEM(ola_log_kernel, p->ola_smem);
+#define SET_AC(NA_)                                                                     \
+  case NA_:                                                                             \
+    if (p->a_groups > 1) SET_SMEM((autocorr_dmma_kernel<NA_, true>), p->ac_smem);       \
+    else SET_SMEM((autocorr_dmma_kernel<NA_, false>), p->ac_smem);                      \
+    break;
   switch (p->na) {
-    case 4: SET_SMEM(autocorr_dmma_kernel<4>, p->ac_smem); break;
-    case 8: SET_SMEM(autocorr_dmma_kernel<8>, p->ac_smem); break;
-    case 12: SET_SMEM(autocorr_dmma_kernel<12>, p->ac_smem); break;
-    case 16: SET_SMEM(autocorr_dmma_kernel<16>, p->ac_smem); break;
-    case 20: SET_SMEM(autocorr_dmma_kernel<20>, p->ac_smem); break;
+    SET_AC(4) SET_AC(8) SET_AC(12) SET_AC(16) SET_AC(20)
     default: plan_free(p); return set_err(FDLP_E_UNSUPPORTED, "unsupported lag blocking%s", "");
   }
+#undef SET_AC
 #undef SET_SMEM
   *out = p;
   return FDLP_OK;
@@ -371,11 +377,11 @@ extern "C" int fdlp_plan_get_fbank(const fdlp_plan* p, double* host_out) {
 extern "C" int64_t fdlp_plan_scratch_bytes(const fdlp_plan* p, int32_t n_seg) {
   if (!p) return -1;
   const int64_t J = p->prm.nfilters;
-  return (int64_t)n_seg * 8 * ((int64_t)p->g.N + J * p->g.nlags + J * p->g.kk);
+  return (int64_t)n_seg * 8 * ((int64_t)p->ld + J * p->g.nlags + J * p->g.kk);
 }
 
 // ---------------------------------------------------------------- launches
-static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, cudaStream_t st) {
+static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld, int out_pad, cudaStream_t st) {
   DctArgs a;
   memset(&a, 0, sizeof(a));
   a.wav = b->wav; a.utt_wav_off = b->utt_wav_off; a.utt_seg_off = b->utt_seg_off; a.seg_utt = b->seg_utt;
@@ -385,7 +391,7 @@ static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, cudaStream
   a.N = p->g.N; a.S = p->g.S; a.n = p->g.N / 2; a.npass = p->fft.npass;
   for (int i = 0; i < p->fft.npass; ++i) a.radix[i] = p->fft.radix[i];
   a.ham = p->d_ham; a.tw = p->fft.d_tw; a.perm = p->fft.d_perm; a.unpackA = p->fft.d_unpackA; a.postB = p->d_postB;
-  a.out = out;
+  a.out = out; a.out_ld = out_ld; a.out_pad = out_pad;
   a.vec_ok = (((uintptr_t)b->wav) % 16 == 0) ? 1 : 0;
   const dim3 grid(b->n_seg), block(512);
   if (b->wav_dtype == FDLP_WAV_INT16) {
@@ -402,18 +408,21 @@ static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, cudaStream
 static int launch_autocorr(fdlp_plan* p, const double* dct, int n_seg, double* r, cudaStream_t st) {
   AcArgs a;
   a.dct = dct; a.fbank = p->d_fbank; a.row_lo = p->d_row_lo; a.row_hi = p->d_row_hi; a.r = r;
-  a.N = p->g.N; a.J = p->prm.nfilters; a.nlags = p->g.nlags; a.rows = p->g.N / 8; a.n_seg = n_seg;
+  a.N = p->g.N; a.J = p->prm.nfilters; a.nlags = p->g.nlags; a.rows = p->g.N / 8; a.n_seg = n_seg; a.ld = p->ld;
   a.a_groups = p->a_groups; a.na_total = p->na * p->a_groups;
   const int bpc = kAcWarps / p->a_groups;
   const int nbg = (a.J + bpc - 1) / bpc;
   const dim3 grid((unsigned)((size_t)n_seg * nbg)), block(kAcWarps * 32);
+#define RUN_AC(NA_)                                                                                   \
+  case NA_:                                                                                           \
+    if (p->a_groups > 1) autocorr_dmma_kernel<NA_, true><<<grid, block, p->ac_smem, st>>>(a);         \
+    else autocorr_dmma_kernel<NA_, false><<<grid, block, p->ac_smem, st>>>(a);                        \
+    break;
   switch (p->na) {
-    case 4: autocorr_dmma_kernel<4><<<grid, block, p->ac_smem, st>>>(a); break;
-    case 8: autocorr_dmma_kernel<8><<<grid, block, p->ac_smem, st>>>(a); break;
-    case 12: autocorr_dmma_kernel<12><<<grid, block, p->ac_smem, st>>>(a); break;
-    case 16: autocorr_dmma_kernel<16><<<grid, block, p->ac_smem, st>>>(a); break;
-    default: autocorr_dmma_kernel<20><<<grid, block, p->ac_smem, st>>>(a); break;
+    RUN_AC(4) RUN_AC(8) RUN_AC(12) RUN_AC(16) RUN_AC(20)
+    default: return set_err(FDLP_E_UNSUPPORTED, "unsupported lag blocking%s", "");
   }
+#undef RUN_AC
   FDLP_CUDA(cudaGetLastError());
   return 0;
 }
@@ -463,7 +472,7 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
   const bool prof = p->profiling;
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[0], st));
   if ((rc = launch_noise(p, b, st))) return rc;
-  if ((rc = launch_dct(p, b, p->d_dct, st))) return rc;
+  if ((rc = launch_dct(p, b, p->d_dct, p->ld, p->pad, st))) return rc;
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[1], st));
   if ((rc = launch_autocorr(p, p->d_dct, b->n_seg, p->d_r, st))) return rc;
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[2], st));
@@ -505,13 +514,20 @@ extern "C" int fdlp_stage_dct(fdlp_plan* p, const fdlp_batch* b, double* dct_out
   if (b->n_seg == 0) return FDLP_OK;
   if ((rc = ensure_scratch(p, 1, b->n_utt))) return rc;
   if ((rc = launch_noise(p, b, (cudaStream_t)stream))) return rc;
-  return launch_dct(p, b, dct_out, (cudaStream_t)stream);
+  return launch_dct(p, b, dct_out, p->g.N, 0, (cudaStream_t)stream);
 }
 
 extern "C" int fdlp_stage_autocorr(fdlp_plan* p, const double* dct, int32_t n_seg, double* r_out, void* stream) {
   if (!p || !dct || !r_out || n_seg < 0) return set_err(FDLP_E_ARG, "bad argument%s", "");
   if (n_seg == 0) return FDLP_OK;
-  return launch_autocorr(p, dct, n_seg, r_out, (cudaStream_t)stream);
+  int rc = ensure_scratch(p, n_seg, 1);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t N8 = (size_t)p->g.N * sizeof(double), ld8 = (size_t)p->ld * sizeof(double);
+  FDLP_CUDA(cudaMemcpy2DAsync(p->d_dct, ld8, dct, N8, N8, n_seg, cudaMemcpyDeviceToDevice, st));
+  FDLP_CUDA(cudaMemcpy2DAsync(p->d_dct + p->g.N, ld8, dct, N8, (size_t)p->pad * sizeof(double), n_seg,
+                              cudaMemcpyDeviceToDevice, st));
+  return launch_autocorr(p, p->d_dct, n_seg, r_out, st);
 }
 
 extern "C" int fdlp_stage_lpc_envelope(fdlp_plan* p, const double* r, int32_t n_seg, double* lpc_out, double* gain_out,
