@@ -166,10 +166,11 @@ struct fdlp_plan {
   double2* d_postB = nullptr;
   double* d_fbank = nullptr;
   int32_t *d_row_lo = nullptr, *d_row_hi = nullptr;
-  double *d_weights = nullptr, *d_cosM = nullptr, *d_wratio = nullptr;
+  double *d_weights = nullptr, *d_inv_n = nullptr, *d_basis = nullptr, *d_wratio = nullptr;
+  int Lp = 0, ldb = 0, env_ny = 1, lpc_threads = 256;
   // scratch (grow-only)
   int cap_seg = 0, cap_utt = 0;
-  double *d_dct = nullptr, *d_r = nullptr, *d_env = nullptr, *d_alpha = nullptr;
+  double *d_dct = nullptr, *d_r = nullptr, *d_env = nullptr, *d_alpha = nullptr, *d_ms = nullptr;
   // optional per-stage timing (CUDA events on the launching stream)
   bool profiling = false;
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -179,20 +180,21 @@ static void plan_free(fdlp_plan* p) {
   if (!p) return;
   free_fft_tables(&p->fft);
   cudaFree(p->d_ham); cudaFree(p->d_postB); cudaFree(p->d_fbank); cudaFree(p->d_row_lo); cudaFree(p->d_row_hi);
-  cudaFree(p->d_weights); cudaFree(p->d_cosM); cudaFree(p->d_wratio);
-  cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_alpha);
+  cudaFree(p->d_weights); cudaFree(p->d_inv_n); cudaFree(p->d_basis); cudaFree(p->d_wratio);
+  cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_alpha); cudaFree(p->d_ms);
   for (int i = 0; i < 5; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
   delete p;
 }
 
 static int ensure_scratch(fdlp_plan* p, int n_seg, int n_utt) {
   if (n_seg > p->cap_seg) {
-    cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env);
-    p->d_dct = p->d_r = p->d_env = nullptr; p->cap_seg = 0;
+    cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_ms);
+    p->d_dct = p->d_r = p->d_env = p->d_ms = nullptr; p->cap_seg = 0;
     const size_t J = p->prm.nfilters;
     FDLP_CUDA(cudaMalloc((void**)&p->d_dct, (size_t)n_seg * p->ld * sizeof(double)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_r, (size_t)n_seg * J * p->g.nlags * sizeof(double)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_env, (size_t)n_seg * J * p->g.kk * sizeof(double)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_ms, ((size_t)n_seg * J + 8) * p->Lp * sizeof(double)));
     p->cap_seg = n_seg;
   }
   if (n_utt > p->cap_utt) {
@@ -301,11 +303,19 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   }
   {
     std::vector<double> w(prm->weights, prm->weights + g.L);
-    std::vector<double> cosM(g.M), wr(g.kk);
-    for (int q = 0; q < g.M; ++q) cosM[q] = (double)cosl(2.0L * M_PIl * q / g.M);
+    p->Lp = (g.L + 3) & ~3;
+    p->env_ny = (g.kk + 79) / 80;          // envelope kernel: 10 blocks of 8 frames per warp pass
+    p->ldb = p->env_ny * 80;
+    std::vector<double> inv_n(g.L, 0.0), wr(g.kk), basis((size_t)p->Lp * p->ldb, 0.0);
+    for (int n = 1; n < g.L; ++n) inv_n[n] = 1.0 / n;
+    // cosine basis of fft(ms, M): cos(2 pi n t / M), argument reduced exactly in integers
+    for (int n = 0; n < g.L; ++n)
+      for (int t = 0; t < g.kk; ++t)
+        basis[(size_t)n * p->ldb + t] = (double)cosl(2.0L * M_PIl * (long double)(((long long)n * t) % g.M) / g.M);
     std::vector<double> hn = np_hanning(g.kk), hm = np_hamming(g.kk);
     for (int t = 0; t < g.kk; ++t) wr[t] = hn[t] / hm[t];
-    if ((rc = upload(&p->d_weights, w)) || (rc = upload(&p->d_cosM, cosM)) || (rc = upload(&p->d_wratio, wr))) {
+    if ((rc = upload(&p->d_weights, w)) || (rc = upload(&p->d_inv_n, inv_n)) || (rc = upload(&p->d_basis, basis)) ||
+        (rc = upload(&p->d_wratio, wr))) {
       plan_free(p); return rc;
     }
   }
@@ -322,7 +332,10 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
     return set_err(FDLP_E_UNSUPPORTED, "segment length %s%ld does not fit in shared memory", "", N);
   }
   p->ac_smem = (size_t)(kAcWarps / p->a_groups) * (p->na * p->a_groups) * 64 * sizeof(double);
-  p->lpc_smem = ((size_t)g.M + kLpcWarps * lpc_smem_doubles_per_warp(prm->order, g.nlags, g.L)) * sizeof(double);
+  p->lpc_threads = kLpcMaxThreads;
+  while (p->lpc_threads > 32 && (size_t)(p->lpc_threads / kLpcGroup) * lpc_task_stride(prm->order, g.nlags, g.L) * sizeof(double) > (size_t)max_smem / 2)
+    p->lpc_threads /= 2;
+  p->lpc_smem = (size_t)(p->lpc_threads / kLpcGroup) * lpc_task_stride(prm->order, g.nlags, g.L) * sizeof(double);
   p->ola_smem = (size_t)J * (kOlaFT + 1) * sizeof(double);
   if (p->lpc_smem > (size_t)max_smem || p->ola_smem > (size_t)max_smem || p->ac_smem > (size_t)max_smem) {
     plan_free(p);
@@ -340,7 +353,7 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
     SET_SMEM((dct_segments_kernel<float, int16_t>), p->dct_smem);
     SET_SMEM((dct_segments_kernel<float, float>), p->dct_smem);
   }
-  SET_SMEM(lpc_envelope_kernel, p->lpc_smem);
+  SET_SMEM(lpc_cepstrum_kernel, p->lpc_smem);
   SET_SMEM(ola_log_kernel, p->ola_smem);
 #define SET_AC(NA_)                                                                     \
   case NA_:                                                                             \
@@ -377,7 +390,7 @@ extern "C" int fdlp_plan_get_fbank(const fdlp_plan* p, double* host_out) {
 extern "C" int64_t fdlp_plan_scratch_bytes(const fdlp_plan* p, int32_t n_seg) {
   if (!p) return -1;
   const int64_t J = p->prm.nfilters;
-  return (int64_t)n_seg * 8 * ((int64_t)p->ld + J * p->g.nlags + J * p->g.kk);
+  return (int64_t)n_seg * 8 * ((int64_t)p->ld + J * p->g.nlags + J * p->g.kk + J * p->Lp);
 }
 
 // ---------------------------------------------------------------- launches
@@ -431,12 +444,18 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
                       double* env, int32_t* status, const int32_t* seg_utt, cudaStream_t st) {
   LpcArgs a;
   a.r = r; a.n_tasks = n_seg * p->prm.nfilters; a.J = p->prm.nfilters;
-  a.order = p->prm.order; a.nlags = p->g.nlags; a.L = p->g.L; a.M = p->g.M; a.kk = p->g.kk;
-  a.weights = p->d_weights; a.cosM = p->d_cosM; a.wratio = p->d_wratio;
-  a.lpc_out = lpc_out; a.gain_out = gain_out; a.cep_out = cep_out; a.env = env;
+  a.order = p->prm.order; a.nlags = p->g.nlags; a.L = p->g.L; a.Lp = p->Lp;
+  a.weights = p->d_weights; a.inv_n = p->d_inv_n;
+  a.lpc_out = lpc_out; a.gain_out = gain_out; a.cep_out = cep_out; a.ms = p->d_ms;
   a.status = status; a.seg_utt = seg_utt;
-  const dim3 grid((a.n_tasks + kLpcWarps - 1) / kLpcWarps), block(kLpcWarps * 32);
-  lpc_envelope_kernel<<<grid, block, p->lpc_smem, st>>>(a);
+  const int tpc = p->lpc_threads / kLpcGroup;
+  lpc_cepstrum_kernel<<<(a.n_tasks + tpc - 1) / tpc, p->lpc_threads, p->lpc_smem, st>>>(a);
+  FDLP_CUDA(cudaGetLastError());
+  EnvArgs e;
+  e.ms = p->d_ms; e.basis = p->d_basis; e.wratio = p->d_wratio; e.env = env;
+  e.n_tasks = a.n_tasks; e.Lp = p->Lp; e.ldb = p->ldb; e.kk = p->g.kk;
+  const dim3 grid((a.n_tasks + 8 * kEnvWarps - 1) / (8 * kEnvWarps), p->env_ny);
+  envelope_dmma_kernel<10><<<grid, kEnvWarps * 32, 0, st>>>(e);
   FDLP_CUDA(cudaGetLastError());
   return 0;
 }
@@ -534,6 +553,8 @@ extern "C" int fdlp_stage_lpc_envelope(fdlp_plan* p, const double* r, int32_t n_
                                        double* cep_out, double* env_out, int32_t* seg_status, void* stream) {
   if (!p || !r || !env_out || n_seg < 0) return set_err(FDLP_E_ARG, "bad argument%s", "");
   if (n_seg == 0) return FDLP_OK;
+  int rc = ensure_scratch(p, n_seg, 1);
+  if (rc) return rc;
   return launch_lpc(p, r, n_seg, lpc_out, gain_out, cep_out, env_out, seg_status, nullptr, (cudaStream_t)stream);
 }
 

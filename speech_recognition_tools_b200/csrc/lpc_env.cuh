@@ -1,5 +1,5 @@
-// K4 + K5: per-(segment, band) Levinson-Durbin LPC, LPC gain, LPC->cepstrum recursion, cepstral weighting
-// and the Hilbert-envelope evaluation -- one warp per (segment, band), float64 throughout.
+// K4 + K5: per-(segment, band) Levinson-Durbin LPC, LPC gain, LPC->cepstrum recursion and cepstral
+// weighting (K4), then the Hilbert-envelope evaluation as a dense FP64 tensor-core contraction (K5).
 //
 // Reference: computeLpcFast        src/featgen/features.py:226-228  (solve_toeplitz + the gain quirk
 //                                  gg = y[0] + sum_{k=0..p} xlpc[k] * y[k+1])
@@ -9,7 +9,16 @@
 //              abs(exp(fft(ms, M)))[t] == exp(sum_n ms[n] cos(2 pi n t / M)) because ms is real, so the
 //              envelope is a real contraction of the weighted cepstrum against a cosine basis, then exp,
 //              then the hanning(kk)/hamming(kk) window ratio.
+//
+// K4 is a chain of order-long serial recursions, so it is instruction-issue bound, not flop bound.  Each
+// (segment, band) is owned by a GROUP of 8 lanes (4 solves per warp): the length-m dot products and
+// updates keep most lanes busy for m up to 150..300, the tree reduction is 3 shuffle stages instead of 5,
+// and the reciprocal of the prediction error is computed once for 4 solves.  All state lives in shared
+// memory; the Levinson update is done in place on the symmetric pairs (i, m-i).
+// K5 is a GEMM [tasks x L] x [L x kk] on DMMA.8x8x4: float64 holds the tolerance by construction (the
+// TF32 / BF16x3 alternatives named in the north star are evaluated numerically in tests/test_envelope_precision.py).
 #pragma once
+#include "autocorr.cuh"
 #include "common.cuh"
 
 namespace fdlp {
@@ -17,114 +26,170 @@ namespace fdlp {
 struct LpcArgs {
   const double* r;        // [n_tasks, nlags]
   int n_tasks, J;
-  int order, nlags, L, M, kk;
+  int order, nlags, L, Lp;  // Lp = L rounded up to a multiple of 4 (row stride of ms)
   const double* weights;  // [L]
-  const double* cosM;     // [M] cos(2 pi q / M)
-  const double* wratio;   // [kk] np.hanning(kk) / np.hamming(kk)
+  const double* inv_n;    // [L] 1/n (inv_n[0] unused)
   double* lpc_out;        // [n_tasks, order+1] or null
   double* gain_out;       // [n_tasks] or null
   double* cep_out;        // [n_tasks, L] or null (before weighting)
-  double* env;            // [n_tasks, kk]
+  double* ms;             // [n_tasks_padded, Lp] weighted cepstrum (zero padded), input of K5
   int32_t* status;        // status words to OR FDLP_ST_* bits into, or null
   const int32_t* seg_utt; // [n_seg] segment -> status index (utterance); null: index by segment
 };
 
-constexpr int kLpcWarps = 8;
+constexpr int kLpcMaxThreads = 256;
+constexpr int kLpcGroup = 8;  // lanes per (segment, band); a CTA of T threads owns T/8 solves
 
-__host__ __device__ inline size_t lpc_smem_doubles_per_warp(int order, int nlags, int L) {
-  return (size_t)nlags + 2 * (size_t)(order + 1) + 2 * (size_t)L;
+// per-task shared memory (doubles): r | a (length max(p+1, L)) | cep/mc ; stride == 8 (mod 16) so that the
+// two groups of a half-warp fall in disjoint banks
+__host__ __device__ inline int lpc_task_stride(int order, int nlags, int L) {
+  const int alen = (order + 1 > L) ? order + 1 : L;
+  int s = nlags + alen + L;
+  s += (8 - (s % 16) + 16) % 16;
+  return s;
 }
 
-__global__ void __launch_bounds__(kLpcWarps * 32) lpc_envelope_kernel(const LpcArgs a) {
+__device__ __forceinline__ double group_sum8(double v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  return v;
+}
+
+__global__ void __launch_bounds__(kLpcMaxThreads) lpc_cepstrum_kernel(const LpcArgs a) {
   extern __shared__ __align__(16) double sm[];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int p = a.order, L = a.L, M = a.M;
+  const int g = threadIdx.x & (kLpcGroup - 1);
+  const int slot = threadIdx.x / kLpcGroup;
+  const int p = a.order, L = a.L;
+  const int alen = (p + 1 > L) ? p + 1 : L;
+  double* s_r = sm + (size_t)slot * lpc_task_stride(p, a.nlags, L);
+  double* s_a = s_r + a.nlags;
+  double* s_mc = s_a + alen;
 
-  double* s_cos = sm;  // [M]
-  double* base = sm + M + (size_t)warp * lpc_smem_doubles_per_warp(p, a.nlags, L);
-  double* s_r = base;                 // [nlags]
-  double* s_a0 = s_r + a.nlags;       // [p+1]
-  double* s_a1 = s_a0 + (p + 1);      // [p+1]
-  double* s_cep = s_a1 + (p + 1);     // [L]
-  double* s_mc = s_cep + L;           // [L]  m * cep[m]
-
-  for (int q = threadIdx.x; q < M; q += blockDim.x) s_cos[q] = a.cosM[q];
-  __syncthreads();
-
-  const int task = blockIdx.x * kLpcWarps + warp;
-  if (task >= a.n_tasks) return;
+  int task = blockIdx.x * (blockDim.x / kLpcGroup) + slot;
+  const bool live = task < a.n_tasks;
+  if (!live) task = a.n_tasks - 1;  // idle groups shadow the last task (keeps warp-level shuffles uniform)
 
   const double* rg = a.r + (size_t)task * a.nlags;
-  for (int i = lane; i < a.nlags; i += 32) s_r[i] = rg[i];
-  for (int i = lane; i <= p; i += 32) { s_a0[i] = (i == 0) ? 1.0 : 0.0; s_a1[i] = (i == 0) ? 1.0 : 0.0; }
+  for (int i = g; i < a.nlags; i += kLpcGroup) s_r[i] = rg[i];
+  for (int i = g; i < alen; i += kLpcGroup) s_a[i] = (i == 0) ? 1.0 : 0.0;
   __syncwarp();
 
-  // ---- Levinson-Durbin: T a = -r[1..p] ----
-  double* cur = s_a0;
-  double* nxt = s_a1;
+  // ---- Levinson-Durbin: T a = -r[1..p], in place ----
   double E = s_r[0];
   int bad = 0;
   for (int m = 1; m <= p; ++m) {
     double part = 0.0;
-    for (int i = 1 + lane; i < m; i += 32) part = fma(cur[i], s_r[m - i], part);
-    const double acc = warp_sum(part) + s_r[m];
+    for (int i = 1 + g; i < m; i += kLpcGroup) part = fma(s_a[i], s_r[m - i], part);
+    const double acc = group_sum8(part) + s_r[m];
     if (E == 0.0 || !isfinite(E)) bad = FDLP_ST_SINGULAR;
     const double k = -acc / E;
-    for (int i = 1 + lane; i < m; i += 32) nxt[i] = fma(k, cur[m - i], cur[i]);
-    if (lane == 0) nxt[m] = k;
+    for (int i = 1 + g; 2 * i < m; i += kLpcGroup) {
+      const double ai = s_a[i], aj = s_a[m - i];
+      s_a[i] = fma(k, aj, ai);
+      s_a[m - i] = fma(k, ai, aj);
+    }
+    if (g == 0) {
+      if ((m & 1) == 0) { const double ah = s_a[m >> 1]; s_a[m >> 1] = fma(k, ah, ah); }
+      s_a[m] = k;
+    }
     E *= (1.0 - k * k);
     __syncwarp();
-    double* t = cur; cur = nxt; nxt = t;
   }
-  // cur[0..p] = xlpc (cur[0] == 1)
 
   // ---- gain: gg = r[0] + sum_{k=0..p} xlpc[k] * r[k+1]  (features.py:228) ----
   double gpart = 0.0;
-  for (int i = lane; i <= p; i += 32) gpart = fma(cur[i], s_r[i + 1], gpart);
-  const double gg = s_r[0] + warp_sum(gpart);
+  for (int i = g; i <= p; i += kLpcGroup) gpart = fma(s_a[i], s_r[i + 1], gpart);
+  const double gg = s_r[0] + group_sum8(gpart);
   if (!(gg > 0.0) || !isfinite(gg)) bad |= FDLP_ST_NONFINITE;
 
-  if (a.lpc_out) for (int i = lane; i <= p; i += 32) a.lpc_out[(size_t)task * (p + 1) + i] = cur[i];
-  if (a.gain_out && lane == 0) a.gain_out[task] = gg;
+  if (live) {
+    if (a.lpc_out) for (int i = g; i <= p; i += kLpcGroup) a.lpc_out[(size_t)task * (p + 1) + i] = s_a[i];
+    if (a.gain_out && g == 0) a.gain_out[task] = gg;
+  }
+  __syncwarp();
 
-  // ---- LPC -> cepstrum (features.py:233-246); x[0] = 1, x[i] = -a[i], zero beyond the order ----
-  auto xval = [&](int i) -> double { return (i <= p) ? -cur[i] : 0.0; };
-  if (lane == 0) {
-    s_cep[0] = log(sqrt(gg));
+  // ---- LPC -> cepstrum (features.py:233-246): x[0] = 1, x[i] = -a[i] (zero beyond the order) ----
+  for (int i = 1 + g; i <= p; i += kLpcGroup) s_a[i] = -s_a[i];
+  // the recursion only needs m*cep[m] (kept in s_mc); the plain values go straight to global memory
+  double* msg = a.ms + (size_t)task * a.Lp;
+  __syncwarp();
+  const double c0 = log(sqrt(gg));
+  const double c1 = (L > 1) ? s_a[1] : 0.0;
+  if (g == 0) {
     s_mc[0] = 0.0;
-    if (L > 1) { s_cep[1] = xval(1); s_mc[1] = s_cep[1]; }
+    if (L > 1) s_mc[1] = c1;
+    if (live) {
+      msg[0] = c0 * a.weights[0];
+      if (L > 1) msg[1] = c1 * a.weights[1];
+      if (a.cep_out) { a.cep_out[(size_t)task * L] = c0; if (L > 1) a.cep_out[(size_t)task * L + 1] = c1; }
+    }
   }
   __syncwarp();
   for (int n = 2; n < L; ++n) {
     double part = 0.0;
-    for (int m = 1 + lane; m < n; m += 32) part = fma(xval(n - m), s_mc[m], part);
-    const double v = warp_sum(part) / (double)n + xval(n);
-    if (lane == 0) { s_cep[n] = v; s_mc[n] = v * (double)n; }
+    for (int m = 1 + g; m < n; m += kLpcGroup) part = fma(s_a[n - m], s_mc[m], part);
+    const double v = fma(group_sum8(part), a.inv_n[n], s_a[n]);
+    if (g == 0) {
+      s_mc[n] = v * (double)n;
+      if (live) {
+        msg[n] = v * a.weights[n];
+        if (a.cep_out) a.cep_out[(size_t)task * L + n] = v;
+      }
+    }
     __syncwarp();
   }
-  if (a.cep_out) for (int i = lane; i < L; i += 32) a.cep_out[(size_t)task * L + i] = s_cep[i];
-  __syncwarp();
+  if (live && g == 0) for (int n = L; n < a.Lp; ++n) msg[n] = 0.0;
 
-  // ---- weighting (mask * lifter * gamma, odd-zero folded in) ----
-  for (int i = lane; i < L; i += 32) s_mc[i] = s_cep[i] * a.weights[i];
-  __syncwarp();
-
-  // ---- envelope: exp(sum_n ms[n] cos(2 pi n t / M)) * hanning/hamming ----
-  double* eout = a.env + (size_t)task * a.kk;
-  for (int t = lane; t < a.kk; t += 32) {
-    double s = 0.0;
-    int idx = 0;
-    const int step = t % M;
-    for (int n = 0; n < L; ++n) {
-      s = fma(s_mc[n], s_cos[idx], s);
-      idx += step;
-      if (idx >= M) idx -= M;
-    }
-    eout[t] = exp(s) * a.wratio[t];
-  }
-  if (bad && a.status && lane == 0) {
+  if (bad && live && a.status && g == 0) {
     const int seg = task / a.J;
     atomicOr(a.status + (a.seg_utt ? a.seg_utt[seg] : seg), bad);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K5: env[task, t] = exp( sum_n ms[task, n] * cos(2 pi n t / M) ) * wratio[t],  t < kk
+// One warp owns 8 tasks (the DMMA M dimension) and NT blocks of 8 output frames; the cosine basis
+// B[n][t] is a plan table ([Lp, ldb], zero rows beyond L) read through L1/L2.
+struct EnvArgs {
+  const double* ms;      // [n_tasks_padded, Lp]
+  const double* basis;   // [Lp, ldb]
+  const double* wratio;  // [kk]
+  double* env;           // [n_tasks, kk]
+  int n_tasks, Lp, ldb, kk;
+};
+
+constexpr int kEnvWarps = 4;
+
+template <int NT>
+__global__ void __launch_bounds__(kEnvWarps * 32) envelope_dmma_kernel(const EnvArgs a) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lr = lane & 3, lc = lane >> 2;
+  const int task0 = (blockIdx.x * kEnvWarps + warp) * 8;
+  if (task0 >= a.n_tasks) return;
+  const int t_base = blockIdx.y * NT * 8;
+  double acc[NT][2];
+#pragma unroll
+  for (int i = 0; i < NT; ++i) acc[i][0] = acc[i][1] = 0.0;
+  // A[row = lane/4][col = lane%4] = ms[task0 + lane/4][k0 + lane%4]   (rows beyond n_tasks are padding)
+  const double* pa = a.ms + (size_t)(task0 + lc) * a.Lp + lr;
+  // B[row = lane%4][col = lane/4] = basis[k0 + lane%4][t0 + lane/4]
+  const double* pb = a.basis + (size_t)lr * a.ldb + t_base + lc;
+  for (int k0 = 0; k0 < a.Lp; k0 += 4) {
+    const double af = __ldg(pa + k0);
+    const double* pbk = pb + (size_t)k0 * a.ldb;
+#pragma unroll
+    for (int i = 0; i < NT; ++i) dmma884(acc[i][0], acc[i][1], af, __ldg(pbk + 8 * i));
+  }
+  // C[row = lane/4][col = 2*(lane%4) + {0,1}]
+  const int task = task0 + lc;
+  if (task < a.n_tasks) {
+#pragma unroll
+    for (int i = 0; i < NT; ++i) {
+      const int t = t_base + 8 * i + 2 * lr;
+      if (t < a.kk) a.env[(size_t)task * a.kk + t] = exp(acc[i][0]) * __ldg(a.wratio + t);
+      if (t + 1 < a.kk) a.env[(size_t)task * a.kk + t + 1] = exp(acc[i][1]) * __ldg(a.wratio + t + 1);
+    }
   }
 }
 
