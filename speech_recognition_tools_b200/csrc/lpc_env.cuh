@@ -16,7 +16,8 @@
 // and the reciprocal of the prediction error is computed once for 4 solves.  All state lives in shared
 // memory; the Levinson update is done in place on the symmetric pairs (i, m-i).
 // K5 is a GEMM [tasks x L] x [L x kk] on DMMA.8x8x4: float64 holds the tolerance by construction (the
-// TF32 / BF16x3 alternatives named in the north star are evaluated numerically in tests/test_envelope_precision.py).
+// TF32 / BF16x3 alternatives named in the north star are evaluated numerically in
+// tests/test_envelope_precision.py: TF32 5.4e-3 fails, BF16x3 1.6e-5 holds but buys nothing at 0.4 % of the flops).
 #pragma once
 #include "autocorr.cuh"
 #include "common.cuh"

@@ -188,7 +188,7 @@ def _as_rngs(jitter, n_utt):
     one process), an int seed for such a generator, or a sequence of per-utterance seeds."""
     if jitter is None:
         jitter = 0
-    if isinstance(jitter, _random.Random):
+    if isinstance(jitter, _random.Random) or hasattr(jitter, "randrange"):
         return [jitter] * n_utt
     if isinstance(jitter, (int, np.integer)):
         r = _random.Random(int(jitter))
