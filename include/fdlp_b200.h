@@ -75,6 +75,7 @@ typedef struct {
   const double* weights;    /* host, [coeff_num]: mask * lifter * gamma (and odd_mod_zero) folded, :94-118,194-200 */
   const double* custom_fbank; /* host, [nfilters, N+1] when fbank_kind == FDLP_FBANK_CUSTOM, else NULL */
   int32_t dct_fp32;         /* 0: float64 shared-memory FFT when it fits (default); 1: force float32 */
+  double tail_eps;          /* autocorrelation skips filter taps below tail_eps * max|F_j| (0: only exact zeros) */
 } fdlp_params;
 
 /* Integer geometry derived exactly as the reference does (np.round = half-to-even). */
@@ -88,6 +89,7 @@ typedef struct {
   int32_t L;     /* min(coeff_num, M): cepstral coefficients that reach the envelope */
   int32_t nlags; /* order + 2 */
   int32_t dct_is_fp64;
+  int64_t support_taps; /* sum over bands of the taps the autocorrelation visits (<= nfilters * N) */
 } fdlp_geometry;
 
 /* One packed batch.  All pointers are DEVICE pointers unless noted. */

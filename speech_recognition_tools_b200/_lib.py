@@ -24,12 +24,13 @@ class FdlpParams(C.Structure):
         ("frate", C.c_int32), ("fduration", C.c_double), ("overlap_fraction", C.c_double),
         ("fbank_kind", C.c_int32), ("fbank_args", C.c_double * 5),
         ("weights", C.POINTER(C.c_double)), ("custom_fbank", C.POINTER(C.c_double)),
-        ("dct_fp32", C.c_int32),
+        ("dct_fp32", C.c_int32), ("tail_eps", C.c_double),
     ]
 
 
 class FdlpGeometry(C.Structure):
-    _fields_ = [(n, C.c_int32) for n in ("N", "S", "M", "kk", "kkb2", "kks", "L", "nlags", "dct_is_fp64")]
+    _fields_ = [(n, C.c_int32) for n in ("N", "S", "M", "kk", "kkb2", "kks", "L", "nlags", "dct_is_fp64")] + \
+               [("support_taps", C.c_int64)]
 
 
 class FdlpBatch(C.Structure):

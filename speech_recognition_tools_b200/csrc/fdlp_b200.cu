@@ -281,19 +281,33 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
     p->h_fbank.resize((size_t)J * N);
     std::vector<int32_t> lo(J), hi(J);
     const int rows = N / 8;
+    // Row range of the autocorrelation per band: taps that are exactly zero (mel triangles) are skipped, and
+    // so are tails below tail_eps * max|F_j| (cochlear skirts decay as 10^(-2.5 bark)).  A dropped tap changes
+    // r[k] by at most tail_eps^2 * |c|^2; with the default 1e-12 that is below the float64 rounding of r[0]
+    // for any input whose full-band / in-band energy ratio is under 1e8.
+    const double eps = prm->tail_eps > 0 ? prm->tail_eps : 0.0;
+    int64_t support = 0;
     for (int j = 0; j < J; ++j) {
-      int first = N, last = -1;
+      double vmax = 0.0;
       for (int k = 0; k < N; ++k) {
         const double v = full[(size_t)j * (N + 1) + k];
         p->h_fbank[(size_t)j * N + k] = v;
-        if (v != 0.0) { if (k < first) first = k; last = k; }
+        vmax = std::max(vmax, fabs(v));
+      }
+      const double thr = eps * vmax;
+      int first = N, last = -1;
+      for (int k = 0; k < N; ++k) {
+        const double v = fabs(p->h_fbank[(size_t)j * N + k]);
+        if (v != 0.0 && v >= thr) { if (k < first) first = k; last = k; }
       }
       if (last < 0) { lo[j] = 0; hi[j] = 0; }
       else {
         lo[j] = (first / 8) & ~3;
         hi[j] = std::min(rows, ((last / 8 + 1) + 3) & ~3);
       }
+      support += (int64_t)(hi[j] - lo[j]) * 8;
     }
+    g.support_taps = support;
     std::vector<double> fpad((size_t)J * p->ld);
     for (int j = 0; j < J; ++j)
       for (int k = 0; k < p->ld; ++k) fpad[(size_t)j * p->ld + k] = p->h_fbank[(size_t)j * N + (k % N)];

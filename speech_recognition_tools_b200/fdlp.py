@@ -41,6 +41,8 @@ class FdlpConfig:
     lifter: Optional[Sequence[float]] = None  # contents of --lifter_config (first line, comma separated)
     srate: int = 16000
     dct_fp32: bool = False
+    # the autocorrelation skips filter taps below tail_eps * max|F_j| (0.0: only exactly-zero taps); see DESIGN.md
+    tail_eps: float = 1e-12
 
     @classmethod
     def from_args(cls, args) -> "FdlpConfig":
@@ -232,6 +234,7 @@ class FdlpExtractor:
         prm.weights = self._weights.ctypes.data_as(C.POINTER(C.c_double))
         prm.custom_fbank = None
         prm.dct_fp32 = 1 if self.cfg.dct_fp32 else 0
+        prm.tail_eps = float(self.cfg.tail_eps)
         self._plan = C.c_void_p()
         with torch.cuda.device(self.device):
             L.check(self._lib.fdlp_plan_create(C.byref(prm), C.byref(self._plan)))

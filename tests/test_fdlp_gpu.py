@@ -167,3 +167,19 @@ def test_long_segment_high_order_against_oracle():
     ex15 = extractor(**kw15)
     assert ex15.geom["dct_is_fp64"] == 1
     assert_feats_close(ex15([x], jitter=[3])[0].cpu().numpy(), ofdlp.fdlp_spectrogram(x, rng=random.Random(3), **kw15))
+
+
+def test_tail_pruning_is_below_output_resolution():
+    """The autocorrelation skips cochlear filter skirts below 1e-12 of the band maximum (48 % of the taps at the
+    WSJ setting).  Against the exact-support plan (tail_eps = 0) on an input with an 80 dB hum far from
+    most bands, the float32 features must be unchanged to within one rounding step."""
+    x = synth.make_utterance("speechlike", 5, 1, 60000, 3.0).astype(np.float64)
+    x = np.clip(x + 20000 * np.sin(2 * np.pi * 100 * np.arange(len(x)) / 16000), -32768, 32767).astype(np.int16)
+    pruned, exact = extractor(**WSJ), extractor(tail_eps=0.0, **WSJ)
+    assert exact.geom["support_taps"] == 80 * 24000
+    assert 0.45 < pruned.geom["support_taps"] / (80 * 24000) < 0.6
+    a = pruned([x], jitter=[1])[0].cpu().numpy().astype(np.float64)
+    b = exact([x], jitter=[1])[0].cpu().numpy().astype(np.float64)
+    np.testing.assert_allclose(a, b, rtol=2e-7, atol=2e-6)
+    ref = ofdlp.fdlp_spectrogram(x, fbank=ofdlp.make_fbank(WSJ["fbank_type"], 80, 48000, 16000), rng=random.Random(1), **WSJ)
+    assert_feats_close(a, ref)

@@ -37,12 +37,12 @@ def main():
             for k, v in s.items():
                 acc[k] = acc.get(k, 0) + v / 4
     g = ex.geom
-    flops = 2.0 * g["nlags"] * cfg["nfilters"] * g["N"] * lay.n_seg
+    flops = 2.0 * g["nlags"] * g["support_taps"] * lay.n_seg
     audio = lengths.sum() / 16000.0
     tot = sum(acc.values())
-    print("n_seg=%d audio=%.0fs stage_ms=%s total=%.2fms xRT=%.0f autocorr=%.2f TFLOP/s (algorithmic)" %
+    print("n_seg=%d audio=%.0fs stage_ms=%s total=%.2fms xRT=%.0f autocorr=%.2f TFLOP/s (visited taps, support %.3f)" %
           (lay.n_seg, audio, {k: round(v, 3) for k, v in acc.items()}, tot, audio / tot * 1e3,
-           flops / acc["autocorr"] / 1e9))
+           flops / acc["autocorr"] / 1e9, g["support_taps"] / (cfg["nfilters"] * g["N"])))
 
 
 if __name__ == "__main__":
