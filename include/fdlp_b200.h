@@ -135,6 +135,10 @@ int fdlp_forward(fdlp_plan* plan, const fdlp_batch* batch, void* stream);
  * out4 = {framing+DCT (incl. noise coefficient), autocorrelation, LPC+cepstrum+envelope, OLA+log} in ms
  * for the most recent fdlp_forward (get_stage_ms waits for that call to finish) */
 int fdlp_plan_set_profiling(fdlp_plan* plan, int32_t enable);
+/* fdlp_forward pipelines chunks of segments over two streams (the latency-bound LPC recursions of one chunk
+ * overlap the FP64-bound autocorrelation of the next).  Off by default: on B200 the two kernels do not become
+ * co-resident (measured), so it brings nothing yet; results are identical either way. */
+int fdlp_plan_set_overlap(fdlp_plan* plan, int32_t enable);
 int fdlp_plan_get_stage_ms(fdlp_plan* plan, float* out4);
 
 /* stage-level entry points (used by the parity tests to check each kernel against the oracle;

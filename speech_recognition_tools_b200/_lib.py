@@ -70,6 +70,7 @@ SYMBOLS = [
     ("fdlp_plan_scratch_bytes", C.c_int64, [C.c_void_p, C.c_int32]),
     ("fdlp_forward", C.c_int, [C.c_void_p, C.POINTER(FdlpBatch), C.c_void_p]),
     ("fdlp_plan_set_profiling", C.c_int, [C.c_void_p, C.c_int32]),
+    ("fdlp_plan_set_overlap", C.c_int, [C.c_void_p, C.c_int32]),
     ("fdlp_plan_get_stage_ms", C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     ("fdlp_stage_dct", C.c_int, [C.c_void_p, C.POINTER(FdlpBatch), C.c_void_p, C.c_void_p]),
     ("fdlp_stage_autocorr", C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),

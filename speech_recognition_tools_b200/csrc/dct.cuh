@@ -38,6 +38,7 @@ struct DctArgs {
   int out_ld;              // row stride of out (>= N)
   int out_pad;             // coefficients 0..out_pad-1 are repeated at N..N+out_pad-1 (circular extension)
   int vec_ok;              // wav base pointer is 16-byte aligned
+  int seg0;                // first segment of this launch (chunked launches); out is indexed by blockIdx.x
 };
 
 template <typename T>
@@ -126,7 +127,7 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
   T* sv = reinterpret_cast<T*>(smem_raw);  // v[] (real view) == z[] (complex view)
   cplx<T>* z = reinterpret_cast<cplx<T>*>(smem_raw);
 
-  const int seg = blockIdx.x;
+  const int seg = a.seg0 + blockIdx.x;
   const int u = a.seg_utt[seg];
   const int k = seg - a.utt_seg_off[u];
   const int64_t woff = a.utt_wav_off[u];
@@ -184,7 +185,7 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
   }
 
   // ---- unpack to the length-N real FFT, Makhoul post-twiddle, scale, store ----
-  double* out = a.out + (size_t)seg * a.out_ld;
+  double* out = a.out + (size_t)blockIdx.x * a.out_ld;
   const int n = a.n;
   for (int kq = threadIdx.x; kq <= n; kq += blockDim.x) {
     const int k1 = (kq == n) ? 0 : kq;

@@ -2,6 +2,7 @@
 // Host side: plan construction (filterbanks, windows, twiddles, cosine basis -- the one-time setup of the
 // reference's getFeats, src/featgen/computeFDLPSpectrogram.py:43-118) and the stream-ordered launch sequence.
 #include <math.h>
+#include <stdlib.h>
 
 #include <algorithm>
 #include <new>
@@ -152,6 +153,8 @@ static void free_fft_tables(FftTables* t) {
 using namespace fdlp;
 
 // ================================================================ FDLP plan
+constexpr int kMaxChunks = 8;
+
 struct fdlp_plan {
   fdlp_params prm;
   fdlp_geometry g;
@@ -173,6 +176,12 @@ struct fdlp_plan {
   double *d_dct = nullptr, *d_r = nullptr, *d_env = nullptr, *d_alpha = nullptr, *d_ms = nullptr;
   // optional per-stage timing (CUDA events on the launching stream)
   bool profiling = false;
+  // two-stream pipeline: K4/K5 of chunk c run on `side` while K2/K3 of chunk c+1 run on the caller's stream
+  // (measured on B200: K3 and K4 CTAs do not become co-resident -- 19.6 + 3.8 ms alone, 23.1 ms together -- so
+  // the pipeline brings nothing yet and is off by default; fdlp_plan_set_overlap turns it on)
+  bool overlap = false;
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_start = nullptr, ev_side = nullptr, ev_chunk[kMaxChunks] = {};
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
@@ -183,6 +192,10 @@ static void plan_free(fdlp_plan* p) {
   cudaFree(p->d_weights); cudaFree(p->d_inv_n); cudaFree(p->d_basis); cudaFree(p->d_wratio);
   cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_alpha); cudaFree(p->d_ms);
   for (int i = 0; i < 5; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
+  for (int i = 0; i < kMaxChunks; ++i) if (p->ev_chunk[i]) cudaEventDestroy(p->ev_chunk[i]);
+  if (p->ev_start) cudaEventDestroy(p->ev_start);
+  if (p->ev_side) cudaEventDestroy(p->ev_side);
+  if (p->side) cudaStreamDestroy(p->side);
   delete p;
 }
 
@@ -194,7 +207,7 @@ static int ensure_scratch(fdlp_plan* p, int n_seg, int n_utt) {
     FDLP_CUDA(cudaMalloc((void**)&p->d_dct, (size_t)n_seg * p->ld * sizeof(double)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_r, (size_t)n_seg * J * p->g.nlags * sizeof(double)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_env, (size_t)n_seg * J * p->g.kk * sizeof(double)));
-    FDLP_CUDA(cudaMalloc((void**)&p->d_ms, ((size_t)n_seg * J + 8) * p->Lp * sizeof(double)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_ms, ((size_t)n_seg * J + 16) * p->Lp * sizeof(double)));
     p->cap_seg = n_seg;
   }
   if (n_utt > p->cap_utt) {
@@ -218,6 +231,7 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   if (!p) return set_err(FDLP_E_NOMEM, "out of host memory%s", "");
   p->prm = *prm;
   cudaGetDevice(&p->device);
+
 
   // ---- geometry, with the reference's exact float expressions ----
   const double of = 1 - prm->overlap_fraction;               // computeFDLPSpectrogram.py:104
@@ -380,6 +394,15 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   }
 #undef SET_AC
 #undef SET_SMEM
+  {
+    int lo_prio = 0, hi_prio = 0;
+    cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio);
+    cudaError_t e = cudaStreamCreateWithPriority(&p->side, cudaStreamNonBlocking, hi_prio);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_start, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_side, cudaEventDisableTiming);
+    for (int i = 0; i < kMaxChunks && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&p->ev_chunk[i], cudaEventDisableTiming);
+    if (e != cudaSuccess) { plan_free(p); return set_err(FDLP_E_CUDA, "stream/event creation: %s", cudaGetErrorString(e)); }
+  }
   *out = p;
   return FDLP_OK;
 }
@@ -408,7 +431,9 @@ extern "C" int64_t fdlp_plan_scratch_bytes(const fdlp_plan* p, int32_t n_seg) {
 }
 
 // ---------------------------------------------------------------- launches
-static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld, int out_pad, cudaStream_t st) {
+static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld, int out_pad, cudaStream_t st,
+                      int seg0 = 0, int nseg = -1) {
+  if (nseg < 0) nseg = b->n_seg;
   DctArgs a;
   memset(&a, 0, sizeof(a));
   a.wav = b->wav; a.utt_wav_off = b->utt_wav_off; a.utt_seg_off = b->utt_seg_off; a.seg_utt = b->seg_utt;
@@ -418,9 +443,9 @@ static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld
   a.N = p->g.N; a.S = p->g.S; a.n = p->g.N / 2; a.npass = p->fft.npass;
   for (int i = 0; i < p->fft.npass; ++i) a.radix[i] = p->fft.radix[i];
   a.ham = p->d_ham; a.tw = p->fft.d_tw; a.perm = p->fft.d_perm; a.unpackA = p->fft.d_unpackA; a.postB = p->d_postB;
-  a.out = out; a.out_ld = out_ld; a.out_pad = out_pad;
+  a.out = out; a.out_ld = out_ld; a.out_pad = out_pad; a.seg0 = seg0;
   a.vec_ok = (((uintptr_t)b->wav) % 16 == 0) ? 1 : 0;
-  const dim3 grid(b->n_seg), block(512);
+  const dim3 grid(nseg), block(512);
   if (b->wav_dtype == FDLP_WAV_INT16) {
     if (p->dct_fp64) dct_segments_kernel<double, int16_t><<<grid, block, p->dct_smem, st>>>(a);
     else dct_segments_kernel<float, int16_t><<<grid, block, p->dct_smem, st>>>(a);
@@ -455,18 +480,20 @@ static int launch_autocorr(fdlp_plan* p, const double* dct, int n_seg, double* r
 }
 
 static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out, double* gain_out, double* cep_out,
-                      double* env, int32_t* status, const int32_t* seg_utt, cudaStream_t st) {
+                      double* env, int32_t* status, const int32_t* seg_utt, cudaStream_t st, size_t task0 = 0) {
   LpcArgs a;
   a.r = r; a.n_tasks = n_seg * p->prm.nfilters; a.J = p->prm.nfilters;
   a.order = p->prm.order; a.nlags = p->g.nlags; a.L = p->g.L; a.Lp = p->Lp;
   a.weights = p->d_weights; a.inv_n = p->d_inv_n;
-  a.lpc_out = lpc_out; a.gain_out = gain_out; a.cep_out = cep_out; a.ms = p->d_ms;
+  a.lpc_out = lpc_out; a.gain_out = gain_out; a.cep_out = cep_out;
+  // every chunk starts on a multiple of 8 tasks (chunk boundaries are whole segments, J tasks each, padded below)
+  a.ms = p->d_ms + (task0 + 7) / 8 * 8 * p->Lp;
   a.status = status; a.seg_utt = seg_utt;
   const int tpc = p->lpc_threads / kLpcGroup;
   lpc_cepstrum_kernel<<<(a.n_tasks + tpc - 1) / tpc, p->lpc_threads, p->lpc_smem, st>>>(a);
   FDLP_CUDA(cudaGetLastError());
   EnvArgs e;
-  e.ms = p->d_ms; e.basis = p->d_basis; e.wratio = p->d_wratio; e.env = env;
+  e.ms = a.ms; e.basis = p->d_basis; e.wratio = p->d_wratio; e.env = env;
   e.n_tasks = a.n_tasks; e.Lp = p->Lp; e.ldb = p->ldb; e.kk = p->g.kk;
   const dim3 grid((a.n_tasks + 8 * kEnvWarps - 1) / (8 * kEnvWarps), p->env_ny);
   envelope_dmma_kernel<10><<<grid, kEnvWarps * 32, 0, st>>>(e);
@@ -503,14 +530,38 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   if ((rc = ensure_scratch(p, b->n_seg, b->n_utt))) return rc;
   const bool prof = p->profiling;
+  const int J = p->prm.nfilters;
+  int nchunk = 1;
+  if (p->overlap && !prof && p->side) nchunk = std::min(kMaxChunks, b->n_seg / 16);
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[0], st));
   if ((rc = launch_noise(p, b, st))) return rc;
-  if ((rc = launch_dct(p, b, p->d_dct, p->ld, p->pad, st))) return rc;
-  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[1], st));
-  if ((rc = launch_autocorr(p, p->d_dct, b->n_seg, p->d_r, st))) return rc;
-  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[2], st));
-  if ((rc = launch_lpc(p, p->d_r, b->n_seg, nullptr, nullptr, nullptr, p->d_env, b->status, b->seg_utt, st))) return rc;
-  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[3], st));
+  if (nchunk <= 1) {
+    if ((rc = launch_dct(p, b, p->d_dct, p->ld, p->pad, st))) return rc;
+    if (prof) FDLP_CUDA(cudaEventRecord(p->ev[1], st));
+    if ((rc = launch_autocorr(p, p->d_dct, b->n_seg, p->d_r, st))) return rc;
+    if (prof) FDLP_CUDA(cudaEventRecord(p->ev[2], st));
+    if ((rc = launch_lpc(p, p->d_r, b->n_seg, nullptr, nullptr, nullptr, p->d_env, b->status, b->seg_utt, st))) return rc;
+    if (prof) FDLP_CUDA(cudaEventRecord(p->ev[3], st));
+  } else {
+    // The serial recursions of K4 are latency bound and leave the FP64 pipe idle; K3 saturates it.  Chunks of
+    // segments flow through two streams so that K4/K5 of chunk c share the SMs with K2/K3 of chunk c+1.
+    FDLP_CUDA(cudaEventRecord(p->ev_start, st));
+    FDLP_CUDA(cudaStreamWaitEvent(p->side, p->ev_start, 0));
+    for (int c = 0; c < nchunk; ++c) {
+      const int s0 = (int)((int64_t)b->n_seg * c / nchunk), s1 = (int)((int64_t)b->n_seg * (c + 1) / nchunk);
+      const int ns = s1 - s0;
+      double* dct_c = p->d_dct + (size_t)s0 * p->ld;
+      double* r_c = p->d_r + (size_t)s0 * J * p->g.nlags;
+      if ((rc = launch_dct(p, b, dct_c, p->ld, p->pad, st, s0, ns))) return rc;
+      if ((rc = launch_autocorr(p, dct_c, ns, r_c, st))) return rc;
+      FDLP_CUDA(cudaEventRecord(p->ev_chunk[c], st));
+      FDLP_CUDA(cudaStreamWaitEvent(p->side, p->ev_chunk[c], 0));
+      if ((rc = launch_lpc(p, r_c, ns, nullptr, nullptr, nullptr, p->d_env + (size_t)s0 * J * p->g.kk, b->status,
+                           b->seg_utt + s0, p->side, (size_t)s0 * J))) return rc;
+    }
+    FDLP_CUDA(cudaEventRecord(p->ev_side, p->side));
+    FDLP_CUDA(cudaStreamWaitEvent(st, p->ev_side, 0));
+  }
   OlaArgs o;
   o.env = p->d_env; o.utt_seg_off = b->utt_seg_off; o.utt_frame_off = b->utt_frame_off; o.seg_ptr = b->seg_ptr;
   o.feats = b->feats; o.cmvn = b->cmvn_acc; o.J = p->prm.nfilters; o.kk = p->g.kk; o.kkb2 = p->g.kkb2;
@@ -522,6 +573,12 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
   ola_log_kernel<<<grid, block, p->ola_smem, st>>>(o);
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[4], st));
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_plan_set_overlap(fdlp_plan* p, int32_t enable) {
+  if (!p) return set_err(FDLP_E_ARG, "null argument%s", "");
+  p->overlap = enable != 0;
   return FDLP_OK;
 }
 

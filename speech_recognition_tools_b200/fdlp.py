@@ -270,6 +270,9 @@ class FdlpExtractor:
     def set_profiling(self, enable: bool = True):
         L.check(self._lib.fdlp_plan_set_profiling(self._plan, 1 if enable else 0))
 
+    def set_overlap(self, enable: bool = True):
+        L.check(self._lib.fdlp_plan_set_overlap(self._plan, 1 if enable else 0))
+
     def stage_ms(self):
         """Per-stage CUDA-event durations of the most recent forward (needs set_profiling(True))"""
         out = (C.c_float * 4)()

@@ -183,3 +183,17 @@ def test_tail_pruning_is_below_output_resolution():
     np.testing.assert_allclose(a, b, rtol=2e-7, atol=2e-6)
     ref = ofdlp.fdlp_spectrogram(x, fbank=ofdlp.make_fbank(WSJ["fbank_type"], 80, 48000, 16000), rng=random.Random(1), **WSJ)
     assert_feats_close(a, ref)
+
+
+def test_two_stream_chunk_pipeline_gives_identical_results():
+    ex = extractor(**WSJ)
+    lengths = synth.wsj_shaped_lengths(40, seed=5)
+    wavs = [synth.make_utterance("white", 8, i, int(T)) for i, T in enumerate(lengths)]
+    a = ex(wavs, jitter=3)
+    ex.set_overlap(True)
+    try:
+        b = ex(wavs, jitter=3)
+    finally:
+        ex.set_overlap(False)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)

@@ -36,6 +36,19 @@ def main():
         if it >= 2:
             for k, v in s.items():
                 acc[k] = acc.get(k, 0) + v / 4
+    ex.set_profiling(False)
+    for ov in (0, 1):
+        ex.set_overlap(bool(ov))
+        for _ in range(2):
+            ex.forward_packed(wav, lay, feats=feats)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(5):
+            ex.forward_packed(wav, lay, feats=feats)
+        e1.record()
+        torch.cuda.synchronize()
+        print("overlap=%d  %.2f ms/step" % (ov, e0.elapsed_time(e1) / 5))
     g = ex.geom
     flops = 2.0 * g["nlags"] * g["support_taps"] * lay.n_seg
     audio = lengths.sum() / 16000.0
