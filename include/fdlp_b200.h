@@ -89,7 +89,12 @@ typedef struct {
   int32_t L;     /* min(coeff_num, M): cepstral coefficients that reach the envelope */
   int32_t nlags; /* order + 2 */
   int32_t dct_is_fp64;
-  int64_t support_taps; /* sum over bands of the taps the autocorrelation visits (<= nfilters * N) */
+  int64_t support_taps; /* sum over bands of the taps inside the filters' support (<= nfilters * N) */
+  /* family decomposition of the autocorrelation (0 when the plan uses the direct per-band kernel only) */
+  int64_t family_taps;  /* taps per segment of the band-independent block sums (nfam * N) */
+  int64_t direct_taps;  /* sum over bands of the taps that still go through the direct per-band kernel */
+  int32_t nfam;         /* number of templates (pass band + skirts) */
+  int32_t block_len;    /* samples per block */
 } fdlp_geometry;
 
 /* One packed batch.  All pointers are DEVICE pointers unless noted. */
@@ -140,6 +145,13 @@ int fdlp_plan_set_profiling(fdlp_plan* plan, int32_t enable);
  * co-resident (measured), so it brings nothing yet; results are identical either way. */
 int fdlp_plan_set_overlap(fdlp_plan* plan, int32_t enable);
 int fdlp_plan_get_stage_ms(fdlp_plan* plan, float* out4);
+/* autocorrelation algorithm: 0 (default) = family decomposition when the filterbank allows it (cochlear filters:
+ * block sums shared by all bands + a direct remainder), 1 = always the direct per-band kernel.  Both evaluate
+ * computeLpcFast's circular autocorrelation (features.py:223-225) with float64 products and sums. */
+int fdlp_plan_set_autocorr_mode(fdlp_plan* plan, int32_t mode);
+/* out3 = {family block sums, per-band combination, direct per-band kernel} in ms for the most recent
+ * profiled fdlp_forward */
+int fdlp_plan_get_autocorr_ms(fdlp_plan* plan, float* out3);
 
 /* stage-level entry points (used by the parity tests to check each kernel against the oracle;
  * they run the same kernels fdlp_forward launches, on the plan's scratch) */

@@ -30,7 +30,8 @@ class FdlpParams(C.Structure):
 
 class FdlpGeometry(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("N", "S", "M", "kk", "kkb2", "kks", "L", "nlags", "dct_is_fp64")] + \
-               [("support_taps", C.c_int64)]
+               [("support_taps", C.c_int64), ("family_taps", C.c_int64), ("direct_taps", C.c_int64),
+                ("nfam", C.c_int32), ("block_len", C.c_int32)]
 
 
 class FdlpBatch(C.Structure):
@@ -72,6 +73,8 @@ SYMBOLS = [
     ("fdlp_plan_set_profiling", C.c_int, [C.c_void_p, C.c_int32]),
     ("fdlp_plan_set_overlap", C.c_int, [C.c_void_p, C.c_int32]),
     ("fdlp_plan_get_stage_ms", C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    ("fdlp_plan_set_autocorr_mode", C.c_int, [C.c_void_p, C.c_int32]),
+    ("fdlp_plan_get_autocorr_ms", C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     ("fdlp_stage_dct", C.c_int, [C.c_void_p, C.POINTER(FdlpBatch), C.c_void_p, C.c_void_p]),
     ("fdlp_stage_autocorr", C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     ("fdlp_stage_lpc_envelope", C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -139,4 +139,265 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_dmma_kernel(const A
   }
 }
 
+// ============================================================================================
+// Family decomposition (used when the plan finds band-independent templates, e.g. cochlear filters).
+//
+// A cochlear filter is piecewise F_j[n] = w_j,g * T_g[n] with T_0 = 1 (pass band),
+// T_1[n] = 10^(-bet * bark(n)) (upper skirt), T_2[n] = 10^(alp * bark(n)) (lower skirt) -- features.py:197-219.
+// For a block of samples that lies, together with its p+1 look-ahead samples, inside ONE region of band j,
+//     sum_{n in block} x_j[n] x_j[n+k] = w_j,g^2 * P_g[block][k],   P_g[block][k] = sum_{n in block} (T_g c)[n] (T_g c)[n+k]
+// and P_g is shared by every band: it is computed once per segment (family_block_autocorr_kernel, the same
+// DMMA scheme as above with accumulators flushed per block), combined per band (family_combine_kernel), and
+// only the few blocks per band that straddle a region boundary (or wrap around N) go through the direct
+// per-band kernel (autocorr_ranges_kernel).  The result is the exact autocorrelation of the sequence
+// (w T_g c), a relative 1e-12 perturbation of F_j c, evaluated with the same FP64 products and sums.
+
+struct FamArgs {
+  const double* dct;   // [n_seg, ld]
+  const double* tmpl;  // [nfam, ld] templates, circular extension like fbank
+  double* p;           // [n_seg, nfam, nblk, nlags]
+  int n_seg, ld, nfam, nblk, nlags;
+  int nsteps_total;    // N / 32
+  int q;               // a block is q * U steps of 32 samples (U = (NA + 4) / 4)
+  int bpc, nchunk;     // blocks per warp task, tasks per (segment, family)
+};
+
+constexpr int kFoldStride = 72;  // doubles between C tiles in shared memory (bank-conflict-free diagonal reads)
+
+template <int NA>
+__global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel(const FamArgs a) {
+  constexpr int RS = NA + 4;
+  constexpr int U = RS / 4;
+  extern __shared__ __align__(16) double cs[];  // [kAcWarps][NA][kFoldStride]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long long task = (long long)blockIdx.x * kAcWarps + warp;
+  const int per_seg = a.nfam * a.nchunk;
+  if (task >= (long long)a.n_seg * per_seg) return;  // warps are independent: no block-wide barrier below
+  const int seg = (int)(task / per_seg);
+  const int rem = (int)(task % per_seg);
+  const int chunk = rem / a.nfam, fam = rem % a.nfam;  // neighbouring warps share the rows of c
+  const int blk0 = chunk * a.bpc;
+  const int blk1 = min(a.nblk, blk0 + a.bpc);
+  const int spb = U * a.q;
+  const int lr = lane & 3, lc = lane >> 2;
+  const int lane_off = (lr << 3) + lc;
+  const int m_lo = blk0 * spb * 4;
+
+  const double* __restrict__ pc = a.dct + (size_t)seg * a.ld + (size_t)m_lo * 8 + lane_off;
+  const double* __restrict__ pf = a.tmpl + (size_t)fam * a.ld + (size_t)m_lo * 8 + lane_off;
+  double ring[RS];
+#pragma unroll
+  for (int i = 0; i < NA; ++i) ring[i] = __ldg(pf + 8 * i) * __ldg(pc + 8 * i);
+  pc += 8 * NA;
+  pf += 8 * NA;
+  double qf[4], qc[4];
+#pragma unroll
+  for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
+#pragma unroll
+  for (int i = NA; i < RS; ++i) ring[i] = 0.0;
+
+  double* my = cs + (size_t)warp * NA * kFoldStride;
+  int step = blk0 * spb;
+  for (int blk = blk0; blk < blk1; ++blk) {
+    double acc[NA][2];
+#pragma unroll
+    for (int i = 0; i < NA; ++i) acc[i][0] = acc[i][1] = 0.0;
+    for (int g = 0; g < a.q; ++g) {
+#pragma unroll
+      for (int s = 0; s < U; ++s) {
+        if (step + s < a.nsteps_total) {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) ring[(4 * s + NA + t) % RS] = qf[t] * qc[t];
+          const double afrag = ring[(4 * s) % RS];
+          pc += 32;
+          pf += 32;
+#pragma unroll
+          for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
+#pragma unroll
+          for (int i = 0; i < NA; ++i) dmma884(acc[i][0], acc[i][1], afrag, ring[(4 * s + i) % RS]);
+        }
+      }
+      step += U;
+    }
+    // flush: C tiles -> shared (warp-private), diagonal sums -> P[seg][fam][blk][0..nlags)
+#pragma unroll
+    for (int i = 0; i < NA; ++i)
+      *reinterpret_cast<double2*>(my + i * kFoldStride + lc * 8 + 2 * lr) = make_double2(acc[i][0], acc[i][1]);
+    __syncwarp();
+    double* pout = a.p + (((size_t)seg * a.nfam + fam) * a.nblk + blk) * a.nlags;
+    for (int k = lane; k < a.nlags; k += 32) {
+      const int ab = k >> 3, d = k & 7;
+      const double* c0 = my + ab * kFoldStride;
+      double sum = 0.0;
+      for (int row = 0; row + d < 8; ++row) sum += c0[row * 8 + row + d];
+      if (d > 0) {
+        const double* c1 = c0 + kFoldStride;
+        for (int row = 8 - d; row < 8; ++row) sum += c1[row * 8 + row + d - 8];
+      }
+      pout[k] = sum;
+    }
+    __syncwarp();
+  }
+}
+
+// ---- per-band combination of the family block sums ----
+struct CombArgs {
+  const double* p;      // [n_seg, nfam, nblk, nlags]
+  double* r;            // [n_seg, J, nlags]  (written)
+  const int8_t* cls;    // [J, nblk] family of the block for this band, -1 = direct, -2 = outside the support
+  const double* wsq;    // [J, nfam] squared template weights
+  const int32_t* blo;   // [J] first block with cls >= 0
+  const int32_t* bhi;   // [J] one past the last block with cls >= 0
+  int n_seg, J, nfam, nblk, nlags;
+  int JB;               // bands per band group (kCombBG groups)
+  int LW;               // warps per band group = ceil(nlags / 32)
+};
+
+constexpr int kCombTB = 16;  // blocks per shared-memory tile
+constexpr int kCombBG = 4;   // band groups per CTA
+constexpr int kCombMaxFam = 3;
+
+// One CTA per segment.  Thread = (lag k, band group); it keeps JBT band accumulators in registers and walks
+// the block tiles staged in shared memory.  Summation order is fixed (blocks ascending), so results do not
+// depend on the batch composition.
+template <int JBT>
+__global__ void __launch_bounds__(kCombBG * 5 * 32) family_combine_kernel(const CombArgs a) {
+  extern __shared__ __align__(16) double ps[];  // [nfam][kCombTB][nlags]
+  const int seg = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int bg = warp / a.LW;
+  const int k = (warp % a.LW) * 32 + lane;
+  const bool active = (bg < kCombBG) && (k < a.nlags);
+  const int j0 = bg * a.JB;
+  double acc[JBT];
+#pragma unroll
+  for (int i = 0; i < JBT; ++i) acc[i] = 0.0;
+  const int tile_elems = a.nfam * kCombTB * a.nlags;
+  const double* pseg = a.p + (size_t)seg * a.nfam * a.nblk * a.nlags;
+  for (int m0 = 0; m0 < a.nblk; m0 += kCombTB) {
+    for (int idx = threadIdx.x; idx < tile_elems; idx += blockDim.x) {
+      const int g = idx / (kCombTB * a.nlags);
+      const int rem = idx - g * (kCombTB * a.nlags);
+      const int mm = rem / a.nlags, kk = rem - mm * a.nlags;
+      const int m = m0 + mm;
+      ps[idx] = (m < a.nblk) ? __ldg(pseg + ((size_t)g * a.nblk + m) * a.nlags + kk) : 0.0;
+    }
+    __syncthreads();
+    if (active) {
+      const int mend = min(kCombTB, a.nblk - m0);
+#pragma unroll
+      for (int jj = 0; jj < JBT; ++jj) {
+        const int j = j0 + jj;
+        if (jj < a.JB && j < a.J) {
+          const int lo = __ldg(a.blo + j), hi = __ldg(a.bhi + j);
+          if (m0 < hi && m0 + kCombTB > lo) {
+            double w[kCombMaxFam];
+#pragma unroll
+            for (int g = 0; g < kCombMaxFam; ++g) w[g] = (g < a.nfam) ? __ldg(a.wsq + (size_t)j * a.nfam + g) : 0.0;
+            const int8_t* cj = a.cls + (size_t)j * a.nblk + m0;
+            for (int mm = 0; mm < mend; ++mm) {
+              const int c = cj[mm];
+              if (c >= 0) {
+                const double wv = (c == 0) ? w[0] : ((c == 1) ? w[1] : w[2]);
+                acc[jj] = fma(wv, ps[(c * kCombTB + mm) * a.nlags + k], acc[jj]);
+              }
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (active) {
+#pragma unroll
+    for (int jj = 0; jj < JBT; ++jj) {
+      const int j = j0 + jj;
+      if (jj < a.JB && j < a.J) a.r[((size_t)seg * a.J + j) * a.nlags + k] = acc[jj];
+    }
+  }
+}
+
+// ---- direct per-band kernel restricted to row ranges (blocks that straddle a region boundary) ----
+constexpr int kMaxRanges = 8;
+
+struct AcRangeArgs {
+  const double* dct;     // [n_seg, ld]
+  const double* fbank;   // [J, ld]
+  const int32_t* nrng;   // [J] number of row ranges of the band
+  const int32_t* rng;    // [J, kMaxRanges, 2] (row_lo, row_hi), multiples of 4 rows
+  double* r;             // [n_seg, J, nlags]  (ADDED to)
+  int J, nlags, n_seg, ld;
+};
+
+template <int NA>
+__global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const AcRangeArgs a) {
+  constexpr int RS = NA + 4;
+  constexpr int U = RS / 4;
+  extern __shared__ __align__(16) double cs[];  // [kAcWarps][NA][kFoldStride]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nbg = (a.J + kAcWarps - 1) / kAcWarps;
+  const int seg = blockIdx.x / nbg;
+  const int band = (blockIdx.x % nbg) * kAcWarps + warp;
+  if (band >= a.J) return;
+  const int nr = a.nrng[band];
+  if (nr == 0) return;
+  const int lr = lane & 3, lc = lane >> 2;
+  const int lane_off = (lr << 3) + lc;
+
+  double acc[NA][2];
+#pragma unroll
+  for (int i = 0; i < NA; ++i) acc[i][0] = acc[i][1] = 0.0;
+
+  for (int q = 0; q < nr; ++q) {
+    const int m_lo = a.rng[(band * kMaxRanges + q) * 2], m_hi = a.rng[(band * kMaxRanges + q) * 2 + 1];
+    const int nsteps = (m_hi - m_lo) >> 2;
+    const double* __restrict__ pc = a.dct + (size_t)seg * a.ld + (size_t)m_lo * 8 + lane_off;
+    const double* __restrict__ pf = a.fbank + (size_t)band * a.ld + (size_t)m_lo * 8 + lane_off;
+    double ring[RS];
+#pragma unroll
+    for (int i = 0; i < NA; ++i) ring[i] = __ldg(pf + 8 * i) * __ldg(pc + 8 * i);
+    pc += 8 * NA;
+    pf += 8 * NA;
+    double qf[4], qc[4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
+#pragma unroll
+    for (int i = NA; i < RS; ++i) ring[i] = 0.0;
+    for (int s0 = 0; s0 < nsteps; s0 += U) {
+#pragma unroll
+      for (int s = 0; s < U; ++s) {
+        if (s0 + s < nsteps) {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) ring[(4 * s + NA + t) % RS] = qf[t] * qc[t];
+          const double afrag = ring[(4 * s) % RS];
+          pc += 32;
+          pf += 32;
+#pragma unroll
+          for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
+#pragma unroll
+          for (int i = 0; i < NA; ++i) dmma884(acc[i][0], acc[i][1], afrag, ring[(4 * s + i) % RS]);
+        }
+      }
+    }
+  }
+
+  double* my = cs + (size_t)warp * NA * kFoldStride;
+#pragma unroll
+  for (int i = 0; i < NA; ++i)
+    *reinterpret_cast<double2*>(my + i * kFoldStride + lc * 8 + 2 * lr) = make_double2(acc[i][0], acc[i][1]);
+  __syncwarp();
+  double* rout = a.r + ((size_t)seg * a.J + band) * a.nlags;
+  for (int k = lane; k < a.nlags; k += 32) {
+    const int ab = k >> 3, d = k & 7;
+    const double* c0 = my + ab * kFoldStride;
+    double sum = 0.0;
+    for (int row = 0; row + d < 8; ++row) sum += c0[row * 8 + row + d];
+    if (d > 0) {
+      const double* c1 = c0 + kFoldStride;
+      for (int row = 8 - d; row < 8; ++row) sum += c1[row * 8 + row + d - 8];
+    }
+    rout[k] += sum;
+  }
+}
+
 }  // namespace fdlp

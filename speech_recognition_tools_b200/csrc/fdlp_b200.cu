@@ -171,6 +171,17 @@ struct fdlp_plan {
   int32_t *d_row_lo = nullptr, *d_row_hi = nullptr;
   double *d_weights = nullptr, *d_inv_n = nullptr, *d_basis = nullptr, *d_wratio = nullptr;
   int Lp = 0, ldb = 0, env_ny = 1, lpc_threads = 256;
+  // family decomposition of the autocorrelation (autocorr.cuh): templates, per-band block classes, direct ranges
+  bool fam_ok = false;       // the plan found templates and may use the family path
+  int ac_mode = 0;           // 0: family path when available, 1: always the direct per-band kernel
+  int nfam = 0, nblk = 0, fam_q = 1, fam_bpc = 1, fam_nchunk = 1, blk_len = 0;
+  int comb_JB = 0, comb_LW = 0, comb_jbt = 0;
+  size_t fam_smem = 0, comb_smem = 0;
+  double *d_tmpl = nullptr, *d_wsq = nullptr, *d_p = nullptr;
+  int8_t* d_cls = nullptr;
+  int32_t *d_blo = nullptr, *d_bhi = nullptr, *d_nrng = nullptr, *d_rng = nullptr;
+  int cap_seg_p = 0;
+  cudaEvent_t ev_ac[4] = {nullptr, nullptr, nullptr, nullptr};
   // scratch (grow-only)
   int cap_seg = 0, cap_utt = 0;
   double *d_dct = nullptr, *d_r = nullptr, *d_env = nullptr, *d_alpha = nullptr, *d_ms = nullptr;
@@ -191,6 +202,9 @@ static void plan_free(fdlp_plan* p) {
   cudaFree(p->d_ham); cudaFree(p->d_postB); cudaFree(p->d_fbank); cudaFree(p->d_row_lo); cudaFree(p->d_row_hi);
   cudaFree(p->d_weights); cudaFree(p->d_inv_n); cudaFree(p->d_basis); cudaFree(p->d_wratio);
   cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_alpha); cudaFree(p->d_ms);
+  cudaFree(p->d_tmpl); cudaFree(p->d_wsq); cudaFree(p->d_p); cudaFree(p->d_cls);
+  cudaFree(p->d_blo); cudaFree(p->d_bhi); cudaFree(p->d_nrng); cudaFree(p->d_rng);
+  for (int i = 0; i < 4; ++i) if (p->ev_ac[i]) cudaEventDestroy(p->ev_ac[i]);
   for (int i = 0; i < 5; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
   for (int i = 0; i < kMaxChunks; ++i) if (p->ev_chunk[i]) cudaEventDestroy(p->ev_chunk[i]);
   if (p->ev_start) cudaEventDestroy(p->ev_start);
@@ -215,6 +229,115 @@ static int ensure_scratch(fdlp_plan* p, int n_seg, int n_utt) {
     FDLP_CUDA(cudaMalloc((void**)&p->d_alpha, (size_t)n_utt * sizeof(double)));
     p->cap_utt = n_utt;
   }
+  return 0;
+}
+
+
+// ---------------------------------------------------------------- family decomposition (host analysis)
+// Finds, for every (band, block of blk_len samples), whether the filter restricted to the block and its
+// look-ahead of 8*na samples is a constant multiple of one band-independent template.  The decision is made
+// numerically on the filterbank the plan actually uses (built the reference's way), so a block that does not
+// match simply stays on the direct path; the analytic form of createFbankCochlear (features.py:197-219) only
+// supplies the candidate templates.
+static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, const std::vector<int32_t>& row_hi) {
+  const fdlp_params& prm = p->prm;
+  const int N = p->g.N, J = prm.nfilters;
+  p->fam_ok = false;
+  if (prm.fbank_kind != FDLP_FBANK_COCHLEAR || p->a_groups != 1 || J > kCombBG * 32) return 0;
+  const double alp = prm.fbank_args[1], bet = prm.fbank_args[3], warp = prm.fbank_args[4];
+  const int fixed = (int)prm.fbank_args[2];
+  const int nfam = (fixed == 1) ? 3 : 2;
+  const int U = (p->na + 4) / 4;
+  int q = 1;
+  if (const char* e = getenv("FDLP_FAM_Q")) q = std::max(1, atoi(e));
+  const int blk_len = 32 * U * q;
+  const int nblk = (N + blk_len - 1) / blk_len;
+  if (nblk < 4) return 0;
+  const int look = 8 * p->na;  // lags the DMMA tiles evaluate
+  const double tol = 1e-12;
+
+  // templates (same expressions as make_cochlear_fbank)
+  const double f_max = prm.srate / 2.0;
+  std::vector<double> fl = np_linspace(0, f_max, N + 1);
+  std::vector<double> tm((size_t)nfam * N);
+  for (int n = 0; n < N; ++n) {
+    const double b = 6 * asinh((fl[n] / warp) / 600);
+    tm[n] = 1.0;
+    tm[(size_t)N + n] = pow(10.0, -bet * b);
+    if (nfam > 2) tm[(size_t)2 * N + n] = pow(10.0, alp * b);
+  }
+  std::vector<int8_t> cls((size_t)J * nblk, (int8_t)-2);
+  std::vector<double> wsq((size_t)J * nfam, 0.0);
+  std::vector<int32_t> blo(J, 0), bhi(J, 0), nrng(J, 0), rng((size_t)J * kMaxRanges * 2, 0);
+  int64_t direct_taps = 0;
+  for (int j = 0; j < J; ++j) {
+    const double* F = &p->h_fbank[(size_t)j * N];
+    std::vector<double> wref(nfam, 0.0);
+    const int s_lo = row_lo[j] * 8, s_hi = row_hi[j] * 8;
+    int first = nblk, last = -1;
+    for (int m = 0; m < nblk; ++m) {
+      const int s = m * blk_len, e = std::min(N, s + blk_len);
+      if (e <= s_lo || s >= s_hi) continue;  // outside the support: -2
+      int c = -1;
+      if (e + look <= N) {
+        for (int g = 0; g < nfam && c < 0; ++g) {
+          const double* T = &tm[(size_t)g * N];
+          double w = wref[g] > 0 ? wref[g] : F[s] / T[s];
+          if (!(w > 0) || !std::isfinite(w)) continue;
+          bool ok = true;
+          for (int n = s; n < e + look && ok; ++n) ok = fabs(F[n] - w * T[n]) <= tol * w * T[n];
+          if (ok) { c = g; wref[g] = w; }
+        }
+      }
+      cls[(size_t)j * nblk + m] = (int8_t)c;
+      if (c >= 0) { first = std::min(first, m); last = m; }
+    }
+    for (int g = 0; g < nfam; ++g) wsq[(size_t)j * nfam + g] = wref[g] * wref[g];
+    blo[j] = (last >= 0) ? first : 0;
+    bhi[j] = (last >= 0) ? last + 1 : 0;
+    // merge runs of direct blocks into row ranges
+    int nr = 0;
+    for (int m = 0; m < nblk;) {
+      if (cls[(size_t)j * nblk + m] != -1) { ++m; continue; }
+      int m2 = m;
+      while (m2 < nblk && cls[(size_t)j * nblk + m2] == -1) ++m2;
+      if (nr >= kMaxRanges) return 0;  // too fragmented: keep the direct path for the whole plan
+      const int s = m * blk_len, e = std::min(N, m2 * blk_len);
+      rng[((size_t)j * kMaxRanges + nr) * 2] = s / 8;
+      rng[((size_t)j * kMaxRanges + nr) * 2 + 1] = e / 8;
+      direct_taps += e - s;
+      ++nr;
+      m = m2;
+    }
+    nrng[j] = nr;
+  }
+  // worthwhile only if the shared work plus the direct remainder is well below the per-band total
+  const int64_t fam_taps = (int64_t)nfam * N;
+  if ((fam_taps + direct_taps) * 2 > p->g.support_taps) return 0;
+
+  std::vector<double> tpad((size_t)nfam * p->ld);
+  for (int g = 0; g < nfam; ++g)
+    for (int k = 0; k < p->ld; ++k) tpad[(size_t)g * p->ld + k] = tm[(size_t)g * N + (k % N)];
+  int rc;
+  if ((rc = upload(&p->d_tmpl, tpad)) || (rc = upload(&p->d_cls, cls)) || (rc = upload(&p->d_wsq, wsq)) ||
+      (rc = upload(&p->d_blo, blo)) || (rc = upload(&p->d_bhi, bhi)) || (rc = upload(&p->d_nrng, nrng)) ||
+      (rc = upload(&p->d_rng, rng)))
+    return rc;
+  p->nfam = nfam; p->nblk = nblk; p->fam_q = q; p->blk_len = blk_len;
+  int bpc = 25;
+  if (const char* e = getenv("FDLP_FAM_BPC")) bpc = std::max(1, atoi(e));
+  p->fam_bpc = std::min(bpc, nblk);
+  p->fam_nchunk = (nblk + p->fam_bpc - 1) / p->fam_bpc;
+  p->comb_JB = (J + kCombBG - 1) / kCombBG;
+  p->comb_LW = (p->g.nlags + 31) / 32;
+  p->comb_jbt = p->comb_JB <= 8 ? 8 : (p->comb_JB <= 16 ? 16 : (p->comb_JB <= 24 ? 24 : 32));
+  p->fam_smem = (size_t)kAcWarps * p->na * kFoldStride * sizeof(double);
+  p->comb_smem = (size_t)nfam * kCombTB * p->g.nlags * sizeof(double);
+  p->g.family_taps = fam_taps;
+  p->g.direct_taps = direct_taps;
+  p->g.nfam = nfam;
+  p->g.block_len = blk_len;
+  p->fam_ok = p->comb_LW <= 5;
   return 0;
 }
 
@@ -328,6 +451,7 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
     if ((rc = upload(&p->d_fbank, fpad)) || (rc = upload(&p->d_row_lo, lo)) || (rc = upload(&p->d_row_hi, hi))) {
       plan_free(p); return rc;
     }
+    if ((rc = build_families(p, lo, hi))) { plan_free(p); return rc; }
   }
   {
     std::vector<double> w(prm->weights, prm->weights + g.L);
@@ -393,6 +517,24 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
     default: plan_free(p); return set_err(FDLP_E_UNSUPPORTED, "unsupported lag blocking%s", "");
   }
 #undef SET_AC
+  if (p->fam_ok) {
+#define SET_FAM(NA_)                                                        \
+  case NA_:                                                                 \
+    SET_SMEM((family_block_autocorr_kernel<NA_>), p->fam_smem);             \
+    SET_SMEM((autocorr_ranges_kernel<NA_>), p->fam_smem);                   \
+    break;
+    switch (p->na) {
+      SET_FAM(4) SET_FAM(8) SET_FAM(12) SET_FAM(16) SET_FAM(20)
+      default: p->fam_ok = false;
+    }
+#undef SET_FAM
+    switch (p->comb_jbt) {
+      case 8: SET_SMEM((family_combine_kernel<8>), p->comb_smem); break;
+      case 16: SET_SMEM((family_combine_kernel<16>), p->comb_smem); break;
+      case 24: SET_SMEM((family_combine_kernel<24>), p->comb_smem); break;
+      default: SET_SMEM((family_combine_kernel<32>), p->comb_smem); break;
+    }
+  }
 #undef SET_SMEM
   {
     int lo_prio = 0, hi_prio = 0;
@@ -427,7 +569,8 @@ extern "C" int fdlp_plan_get_fbank(const fdlp_plan* p, double* host_out) {
 extern "C" int64_t fdlp_plan_scratch_bytes(const fdlp_plan* p, int32_t n_seg) {
   if (!p) return -1;
   const int64_t J = p->prm.nfilters;
-  return (int64_t)n_seg * 8 * ((int64_t)p->ld + J * p->g.nlags + J * p->g.kk + J * p->Lp);
+  const int64_t fam = (p->fam_ok && p->ac_mode == 0) ? (int64_t)p->nfam * p->nblk * p->g.nlags : 0;
+  return (int64_t)n_seg * 8 * ((int64_t)p->ld + J * p->g.nlags + J * p->g.kk + J * p->Lp + fam);
 }
 
 // ---------------------------------------------------------------- launches
@@ -457,7 +600,7 @@ static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld
   return 0;
 }
 
-static int launch_autocorr(fdlp_plan* p, const double* dct, int n_seg, double* r, cudaStream_t st) {
+static int launch_autocorr_direct(fdlp_plan* p, const double* dct, int n_seg, double* r, cudaStream_t st) {
   AcArgs a;
   a.dct = dct; a.fbank = p->d_fbank; a.row_lo = p->d_row_lo; a.row_hi = p->d_row_hi; a.r = r;
   a.N = p->g.N; a.J = p->prm.nfilters; a.nlags = p->g.nlags; a.rows = p->g.N / 8; a.n_seg = n_seg; a.ld = p->ld;
@@ -477,6 +620,67 @@ static int launch_autocorr(fdlp_plan* p, const double* dct, int n_seg, double* r
 #undef RUN_AC
   FDLP_CUDA(cudaGetLastError());
   return 0;
+}
+
+static int ensure_family_scratch(fdlp_plan* p, int n_seg) {
+  if (n_seg > p->cap_seg_p) {
+    cudaFree(p->d_p); p->d_p = nullptr; p->cap_seg_p = 0;
+    FDLP_CUDA(cudaMalloc((void**)&p->d_p, (size_t)n_seg * p->nfam * p->nblk * p->g.nlags * sizeof(double)));
+    p->cap_seg_p = n_seg;
+  }
+  return 0;
+}
+
+// family path: shared block sums -> per-band combination -> direct remainder (autocorr.cuh)
+static int launch_autocorr_family(fdlp_plan* p, const double* dct, int n_seg, double* r, cudaStream_t st, bool prof) {
+  int rc = ensure_family_scratch(p, n_seg);
+  if (rc) return rc;
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev_ac[0], st));
+  FamArgs f;
+  f.dct = dct; f.tmpl = p->d_tmpl; f.p = p->d_p; f.n_seg = n_seg; f.ld = p->ld; f.nfam = p->nfam; f.nblk = p->nblk;
+  f.nlags = p->g.nlags; f.nsteps_total = p->g.N / 32; f.q = p->fam_q; f.bpc = p->fam_bpc; f.nchunk = p->fam_nchunk;
+  const long long tasks = (long long)n_seg * p->nfam * p->fam_nchunk;
+  const dim3 gridA((unsigned)((tasks + kAcWarps - 1) / kAcWarps)), block(kAcWarps * 32);
+  AcRangeArgs d;
+  d.dct = dct; d.fbank = p->d_fbank; d.nrng = p->d_nrng; d.rng = p->d_rng; d.r = r;
+  d.J = p->prm.nfilters; d.nlags = p->g.nlags; d.n_seg = n_seg; d.ld = p->ld;
+  const int nbg = (d.J + kAcWarps - 1) / kAcWarps;
+  const dim3 gridD((unsigned)((size_t)n_seg * nbg));
+  CombArgs c;
+  c.p = p->d_p; c.r = r; c.cls = p->d_cls; c.wsq = p->d_wsq; c.blo = p->d_blo; c.bhi = p->d_bhi;
+  c.n_seg = n_seg; c.J = p->prm.nfilters; c.nfam = p->nfam; c.nblk = p->nblk; c.nlags = p->g.nlags;
+  c.JB = p->comb_JB; c.LW = p->comb_LW;
+  const dim3 gridC(n_seg), blockC(kCombBG * p->comb_LW * 32);
+#define RUN_FAM_A(NA_) case NA_: family_block_autocorr_kernel<NA_><<<gridA, block, p->fam_smem, st>>>(f); break;
+#define RUN_FAM_D(NA_) case NA_: autocorr_ranges_kernel<NA_><<<gridD, block, p->fam_smem, st>>>(d); break;
+  switch (p->na) {
+    RUN_FAM_A(4) RUN_FAM_A(8) RUN_FAM_A(12) RUN_FAM_A(16) RUN_FAM_A(20)
+    default: return set_err(FDLP_E_UNSUPPORTED, "unsupported lag blocking%s", "");
+  }
+  FDLP_CUDA(cudaGetLastError());
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev_ac[1], st));
+  switch (p->comb_jbt) {
+    case 8: family_combine_kernel<8><<<gridC, blockC, p->comb_smem, st>>>(c); break;
+    case 16: family_combine_kernel<16><<<gridC, blockC, p->comb_smem, st>>>(c); break;
+    case 24: family_combine_kernel<24><<<gridC, blockC, p->comb_smem, st>>>(c); break;
+    default: family_combine_kernel<32><<<gridC, blockC, p->comb_smem, st>>>(c); break;
+  }
+  FDLP_CUDA(cudaGetLastError());
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev_ac[2], st));
+  switch (p->na) {
+    RUN_FAM_D(4) RUN_FAM_D(8) RUN_FAM_D(12) RUN_FAM_D(16) RUN_FAM_D(20)
+    default: return set_err(FDLP_E_UNSUPPORTED, "unsupported lag blocking%s", "");
+  }
+#undef RUN_FAM_A
+#undef RUN_FAM_D
+  FDLP_CUDA(cudaGetLastError());
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev_ac[3], st));
+  return 0;
+}
+
+static int launch_autocorr(fdlp_plan* p, const double* dct, int n_seg, double* r, cudaStream_t st, bool prof = false) {
+  if (p->fam_ok && p->ac_mode == 0) return launch_autocorr_family(p, dct, n_seg, r, st, prof);
+  return launch_autocorr_direct(p, dct, n_seg, r, st);
 }
 
 static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out, double* gain_out, double* cep_out,
@@ -538,7 +742,7 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
   if (nchunk <= 1) {
     if ((rc = launch_dct(p, b, p->d_dct, p->ld, p->pad, st))) return rc;
     if (prof) FDLP_CUDA(cudaEventRecord(p->ev[1], st));
-    if ((rc = launch_autocorr(p, p->d_dct, b->n_seg, p->d_r, st))) return rc;
+    if ((rc = launch_autocorr(p, p->d_dct, b->n_seg, p->d_r, st, prof))) return rc;
     if (prof) FDLP_CUDA(cudaEventRecord(p->ev[2], st));
     if ((rc = launch_lpc(p, p->d_r, b->n_seg, nullptr, nullptr, nullptr, p->d_env, b->status, b->seg_utt, st))) return rc;
     if (prof) FDLP_CUDA(cudaEventRecord(p->ev[3], st));
@@ -584,8 +788,10 @@ extern "C" int fdlp_plan_set_overlap(fdlp_plan* p, int32_t enable) {
 
 extern "C" int fdlp_plan_set_profiling(fdlp_plan* p, int32_t enable) {
   if (!p) return set_err(FDLP_E_ARG, "null argument%s", "");
-  if (enable && !p->ev[0])
+  if (enable && !p->ev[0]) {
     for (int i = 0; i < 5; ++i) FDLP_CUDA(cudaEventCreate(&p->ev[i]));
+    for (int i = 0; i < 4; ++i) FDLP_CUDA(cudaEventCreate(&p->ev_ac[i]));
+  }
   p->profiling = enable != 0;
   return FDLP_OK;
 }
@@ -594,6 +800,24 @@ extern "C" int fdlp_plan_get_stage_ms(fdlp_plan* p, float* out4) {
   if (!p || !out4 || !p->ev[0]) return set_err(FDLP_E_ARG, "profiling was not enabled%s", "");
   FDLP_CUDA(cudaEventSynchronize(p->ev[4]));
   for (int i = 0; i < 4; ++i) FDLP_CUDA(cudaEventElapsedTime(&out4[i], p->ev[i], p->ev[i + 1]));
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_plan_set_autocorr_mode(fdlp_plan* p, int32_t mode) {
+  if (!p || mode < 0 || mode > 1) return set_err(FDLP_E_ARG, "bad argument%s", "");
+  p->ac_mode = mode;
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_plan_get_autocorr_ms(fdlp_plan* p, float* out3) {
+  if (!p || !out3 || !p->ev[0]) return set_err(FDLP_E_ARG, "profiling was not enabled%s", "");
+  out3[0] = out3[1] = out3[2] = 0.f;
+  FDLP_CUDA(cudaEventSynchronize(p->ev[4]));
+  if (p->fam_ok && p->ac_mode == 0) {
+    for (int i = 0; i < 3; ++i) FDLP_CUDA(cudaEventElapsedTime(&out3[i], p->ev_ac[i], p->ev_ac[i + 1]));
+  } else {
+    FDLP_CUDA(cudaEventElapsedTime(&out3[2], p->ev[1], p->ev[2]));
+  }
   return FDLP_OK;
 }
 

@@ -273,6 +273,16 @@ class FdlpExtractor:
     def set_overlap(self, enable: bool = True):
         L.check(self._lib.fdlp_plan_set_overlap(self._plan, 1 if enable else 0))
 
+    def set_autocorr_mode(self, mode: str = "auto"):
+        """'auto': family decomposition when the filterbank allows it (cochlear); 'direct': per-band kernel only."""
+        L.check(self._lib.fdlp_plan_set_autocorr_mode(self._plan, {"auto": 0, "direct": 1}[mode]))
+
+    def autocorr_ms(self):
+        """CUDA-event durations of the three autocorrelation kernels of the most recent profiled forward."""
+        out = (C.c_float * 3)()
+        L.check(self._lib.fdlp_plan_get_autocorr_ms(self._plan, out))
+        return dict(family_blocks=out[0], combine=out[1], direct=out[2])
+
     def stage_ms(self):
         """Per-stage CUDA-event durations of the most recent forward (needs set_profiling(True))"""
         out = (C.c_float * 4)()

@@ -197,3 +197,30 @@ def test_two_stream_chunk_pipeline_gives_identical_results():
         ex.set_overlap(False)
     for x, y in zip(a, b):
         assert torch.equal(x, y)
+
+
+def test_family_autocorrelation_matches_direct_kernel_and_oracle():
+    """Cochlear filters: the autocorrelation is assembled from band-independent block sums plus a direct
+    remainder (autocorr.cuh).  Lags must agree with the direct per-band kernel and with the oracle's
+    FFT-based circular autocorrelation to float64 rounding (relative to r[0]), and so must the features."""
+    x = synth.make_utterance("speechlike", 3, 7, 70000, 3.0)
+    ex = extractor(**WSJ)
+    g = ex.geom
+    assert g["nfam"] == 3 and g["block_len"] % 32 == 0
+    assert (g["family_taps"] + g["direct_taps"]) * 4 < g["support_taps"]
+    dct, _ = ex.stage_dct([x])
+    r_fam = ex.stage_autocorr(dct).cpu().numpy()
+    feats_fam = ex([x], jitter=[2])[0].cpu().numpy()
+    ex.set_autocorr_mode("direct")
+    try:
+        r_dir = ex.stage_autocorr(dct).cpu().numpy()
+        feats_dir = ex([x], jitter=[2])[0].cpu().numpy()
+    finally:
+        ex.set_autocorr_mode("auto")
+    fb = ofdlp.make_fbank(WSJ["fbank_type"], 80, 48000, 16000)[:, :-1]
+    d = dct.cpu().numpy()
+    r_ref = np.stack([ofdlp.autocorr_circular(fb * d[i])[:, :152] for i in range(d.shape[0])])
+    r0 = r_ref[:, :, :1]
+    assert np.max(np.abs(r_dir - r_ref) / r0) < 1e-12
+    assert np.max(np.abs(r_fam - r_ref) / r0) < 1e-12
+    np.testing.assert_allclose(feats_fam, feats_dir, rtol=2e-7, atol=5e-6)

@@ -32,7 +32,8 @@ def main():
     acc = {}
     for it in range(6):
         ex.forward_packed(wav, lay, feats=feats)
-        s = ex.stage_ms()
+        s = dict(ex.stage_ms())
+        s.update({"ac_" + k: v for k, v in ex.autocorr_ms().items()})
         if it >= 2:
             for k, v in s.items():
                 acc[k] = acc.get(k, 0) + v / 4
@@ -52,7 +53,8 @@ def main():
     g = ex.geom
     flops = 2.0 * g["nlags"] * g["support_taps"] * lay.n_seg
     audio = lengths.sum() / 16000.0
-    tot = sum(acc.values())
+    tot = sum(v for k, v in acc.items() if not k.startswith("ac_"))
+    print("geom", {k: g[k] for k in ("support_taps", "family_taps", "direct_taps", "nfam", "block_len")})
     print("n_seg=%d audio=%.0fs stage_ms=%s total=%.2fms xRT=%.0f autocorr=%.2f TFLOP/s (visited taps, support %.3f)" %
           (lay.n_seg, audio, {k: round(v, 3) for k, v in acc.items()}, tot, audio / tot * 1e3,
            flops / acc["autocorr"] / 1e9, g["support_taps"] / (cfg["nfilters"] * g["N"])))
