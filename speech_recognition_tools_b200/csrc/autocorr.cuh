@@ -241,80 +241,89 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel
 }
 
 // ---- per-band combination of the family block sums ----
-struct CombArgs {
-  const double* p;      // [n_seg, nfam, nblk, nlags]
-  double* r;            // [n_seg, J, nlags]  (written)
-  const int8_t* cls;    // [J, nblk] family of the block for this band, -1 = direct, -2 = outside the support
-  const double* wsq;    // [J, nfam] squared template weights
-  const int32_t* blo;   // [J] first block with cls >= 0
-  const int32_t* bhi;   // [J] one past the last block with cls >= 0
-  int n_seg, J, nfam, nblk, nlags;
-  int JB;               // bands per band group (kCombBG groups)
-  int LW;               // warps per band group = ceil(nlags / 32)
-};
-
-constexpr int kCombTB = 16;  // blocks per shared-memory tile
-constexpr int kCombBG = 4;   // band groups per CTA
+// Band j takes, from family g, the blocks [a, b) that lie inside one region of its filter.  For the lower
+// skirt a = 0 for every band and for the upper skirt b is the common last block, so the sums are running
+// (prefix / suffix) sums over the blocks, accumulated from the far, small end of the skirt towards the pass
+// band -- pure additions in a fixed order, no differences of partial sums.  The pass band is a short range.
+constexpr int kCombRange = 0, kCombPrefix = 1, kCombSuffix = 2;
 constexpr int kCombMaxFam = 3;
 
-// One CTA per segment.  Thread = (lag k, band group); it keeps JBT band accumulators in registers and walks
-// the block tiles staged in shared memory.  Summation order is fixed (blocks ascending), so results do not
-// depend on the batch composition.
-template <int JBT>
-__global__ void __launch_bounds__(kCombBG * 5 * 32) family_combine_kernel(const CombArgs a) {
-  extern __shared__ __align__(16) double ps[];  // [nfam][kCombTB][nlags]
+struct CombArgs {
+  const double* p;        // [n_seg, nfam, nblk, nlags]
+  double* r;              // [n_seg, J, nlags]  (written)
+  const int32_t* order;   // [nfam, J] bands with a non-empty range, in emission order
+  const int32_t* ra;      // [nfam, J] first block of the band's range
+  const int32_t* rb;      // [nfam, J] one past the last block
+  const double* wsq;      // [J, nfam] squared template weights
+  int32_t mode[kCombMaxFam];   // kComb*
+  int32_t nband[kCombMaxFam];  // entries of order[g]
+  int32_t end[kCombMaxFam];    // suffix mode: common end block
+  int n_seg, J, nfam, nblk, nlags;
+};
+
+// One CTA per segment, one thread per lag; the thread owns column k of the [J, nlags] result staged in
+// shared memory, so no barrier is needed.
+__global__ void __launch_bounds__(160) family_combine_kernel(const CombArgs a) {
+  extern __shared__ __align__(16) double rs[];  // [J][nlags]
   const int seg = blockIdx.x;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int bg = warp / a.LW;
-  const int k = (warp % a.LW) * 32 + lane;
-  const bool active = (bg < kCombBG) && (k < a.nlags);
-  const int j0 = bg * a.JB;
-  double acc[JBT];
+  const int k = threadIdx.x;
+  if (k >= a.nlags) return;
+  for (int j = 0; j < a.J; ++j) rs[j * a.nlags + k] = 0.0;
 #pragma unroll
-  for (int i = 0; i < JBT; ++i) acc[i] = 0.0;
-  const int tile_elems = a.nfam * kCombTB * a.nlags;
-  const double* pseg = a.p + (size_t)seg * a.nfam * a.nblk * a.nlags;
-  for (int m0 = 0; m0 < a.nblk; m0 += kCombTB) {
-    for (int idx = threadIdx.x; idx < tile_elems; idx += blockDim.x) {
-      const int g = idx / (kCombTB * a.nlags);
-      const int rem = idx - g * (kCombTB * a.nlags);
-      const int mm = rem / a.nlags, kk = rem - mm * a.nlags;
-      const int m = m0 + mm;
-      ps[idx] = (m < a.nblk) ? __ldg(pseg + ((size_t)g * a.nblk + m) * a.nlags + kk) : 0.0;
-    }
-    __syncthreads();
-    if (active) {
-      const int mend = min(kCombTB, a.nblk - m0);
+  for (int g = 0; g < kCombMaxFam; ++g) {
+    if (g >= a.nfam) break;
+    const double* pg = a.p + (((size_t)seg * a.nfam + g) * a.nblk) * a.nlags + k;
+    const int32_t* ord = a.order + g * a.J;
+    const int32_t* ra = a.ra + g * a.J;
+    const int32_t* rb = a.rb + g * a.J;
+    const int nb = a.nband[g];
+    if (a.mode[g] == kCombPrefix) {
+      double run = 0.0;
+      int idx = 0;
+      for (int m0 = 0; m0 <= a.nblk; m0 += 8) {
+        double v[8];
 #pragma unroll
-      for (int jj = 0; jj < JBT; ++jj) {
-        const int j = j0 + jj;
-        if (jj < a.JB && j < a.J) {
-          const int lo = __ldg(a.blo + j), hi = __ldg(a.bhi + j);
-          if (m0 < hi && m0 + kCombTB > lo) {
-            double w[kCombMaxFam];
+        for (int u = 0; u < 8; ++u) v[u] = (m0 + u < a.nblk) ? __ldg(pg + (size_t)(m0 + u) * a.nlags) : 0.0;
 #pragma unroll
-            for (int g = 0; g < kCombMaxFam; ++g) w[g] = (g < a.nfam) ? __ldg(a.wsq + (size_t)j * a.nfam + g) : 0.0;
-            const int8_t* cj = a.cls + (size_t)j * a.nblk + m0;
-            for (int mm = 0; mm < mend; ++mm) {
-              const int c = cj[mm];
-              if (c >= 0) {
-                const double wv = (c == 0) ? w[0] : ((c == 1) ? w[1] : w[2]);
-                acc[jj] = fma(wv, ps[(c * kCombTB + mm) * a.nlags + k], acc[jj]);
-              }
-            }
+        for (int u = 0; u < 8; ++u) {
+          const int m = m0 + u;
+          while (idx < nb && rb[ord[idx]] == m) {
+            const int j = ord[idx];
+            rs[j * a.nlags + k] = fma(__ldg(a.wsq + (size_t)j * a.nfam + g), run, rs[j * a.nlags + k]);
+            ++idx;
+          }
+          run += v[u];
+        }
+      }
+    } else if (a.mode[g] == kCombSuffix) {
+      double run = 0.0;
+      int idx = 0;
+      for (int m0 = a.end[g] - 1; m0 >= 0; m0 -= 8) {
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = (m0 - u >= 0) ? __ldg(pg + (size_t)(m0 - u) * a.nlags) : 0.0;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int m = m0 - u;
+          run += v[u];
+          while (idx < nb && ra[ord[idx]] == m) {
+            const int j = ord[idx];
+            rs[j * a.nlags + k] = fma(__ldg(a.wsq + (size_t)j * a.nfam + g), run, rs[j * a.nlags + k]);
+            ++idx;
           }
         }
       }
+    } else {
+      for (int idx = 0; idx < nb; ++idx) {
+        const int j = ord[idx];
+        double sum = 0.0;
+        for (int m = ra[j]; m < rb[j]; ++m) sum += __ldg(pg + (size_t)m * a.nlags);
+        rs[j * a.nlags + k] = fma(__ldg(a.wsq + (size_t)j * a.nfam + g), sum, rs[j * a.nlags + k]);
+      }
     }
-    __syncthreads();
   }
-  if (active) {
-#pragma unroll
-    for (int jj = 0; jj < JBT; ++jj) {
-      const int j = j0 + jj;
-      if (jj < a.JB && j < a.J) a.r[((size_t)seg * a.J + j) * a.nlags + k] = acc[jj];
-    }
-  }
+  double* rout = a.r + (size_t)seg * a.J * a.nlags + k;
+  for (int j = 0; j < a.J; ++j) rout[(size_t)j * a.nlags] = rs[j * a.nlags + k];
 }
 
 // ---- direct per-band kernel restricted to row ranges (blocks that straddle a region boundary) ----

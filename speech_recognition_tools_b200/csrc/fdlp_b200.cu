@@ -175,11 +175,10 @@ struct fdlp_plan {
   bool fam_ok = false;       // the plan found templates and may use the family path
   int ac_mode = 0;           // 0: family path when available, 1: always the direct per-band kernel
   int nfam = 0, nblk = 0, fam_q = 1, fam_bpc = 1, fam_nchunk = 1, blk_len = 0;
-  int comb_JB = 0, comb_LW = 0, comb_jbt = 0;
+  int32_t comb_mode[3] = {0, 0, 0}, comb_nband[3] = {0, 0, 0}, comb_end[3] = {0, 0, 0};
   size_t fam_smem = 0, comb_smem = 0;
   double *d_tmpl = nullptr, *d_wsq = nullptr, *d_p = nullptr;
-  int8_t* d_cls = nullptr;
-  int32_t *d_blo = nullptr, *d_bhi = nullptr, *d_nrng = nullptr, *d_rng = nullptr;
+  int32_t *d_order = nullptr, *d_ra = nullptr, *d_rb = nullptr, *d_nrng = nullptr, *d_rng = nullptr;
   int cap_seg_p = 0;
   cudaEvent_t ev_ac[4] = {nullptr, nullptr, nullptr, nullptr};
   // scratch (grow-only)
@@ -202,8 +201,8 @@ static void plan_free(fdlp_plan* p) {
   cudaFree(p->d_ham); cudaFree(p->d_postB); cudaFree(p->d_fbank); cudaFree(p->d_row_lo); cudaFree(p->d_row_hi);
   cudaFree(p->d_weights); cudaFree(p->d_inv_n); cudaFree(p->d_basis); cudaFree(p->d_wratio);
   cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_alpha); cudaFree(p->d_ms);
-  cudaFree(p->d_tmpl); cudaFree(p->d_wsq); cudaFree(p->d_p); cudaFree(p->d_cls);
-  cudaFree(p->d_blo); cudaFree(p->d_bhi); cudaFree(p->d_nrng); cudaFree(p->d_rng);
+  cudaFree(p->d_tmpl); cudaFree(p->d_wsq); cudaFree(p->d_p);
+  cudaFree(p->d_order); cudaFree(p->d_ra); cudaFree(p->d_rb); cudaFree(p->d_nrng); cudaFree(p->d_rng);
   for (int i = 0; i < 4; ++i) if (p->ev_ac[i]) cudaEventDestroy(p->ev_ac[i]);
   for (int i = 0; i < 5; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
   for (int i = 0; i < kMaxChunks; ++i) if (p->ev_chunk[i]) cudaEventDestroy(p->ev_chunk[i]);
@@ -243,7 +242,7 @@ static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, cons
   const fdlp_params& prm = p->prm;
   const int N = p->g.N, J = prm.nfilters;
   p->fam_ok = false;
-  if (prm.fbank_kind != FDLP_FBANK_COCHLEAR || p->a_groups != 1 || J > kCombBG * 32) return 0;
+  if (prm.fbank_kind != FDLP_FBANK_COCHLEAR || p->a_groups != 1) return 0;
   const double alp = prm.fbank_args[1], bet = prm.fbank_args[3], warp = prm.fbank_args[4];
   const int fixed = (int)prm.fbank_args[2];
   const int nfam = (fixed == 1) ? 3 : 2;
@@ -266,51 +265,85 @@ static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, cons
     tm[(size_t)N + n] = pow(10.0, -bet * b);
     if (nfam > 2) tm[(size_t)2 * N + n] = pow(10.0, alp * b);
   }
-  std::vector<int8_t> cls((size_t)J * nblk, (int8_t)-2);
+  // cls[j][m]: family of block m for band j (regardless of the tail_eps support: a skirt continues as the same
+  // template outside it, and the running sums below include those blocks for free), -1 = no template fits
+  std::vector<int8_t> cls((size_t)J * nblk, (int8_t)-1);
   std::vector<double> wsq((size_t)J * nfam, 0.0);
-  std::vector<int32_t> blo(J, 0), bhi(J, 0), nrng(J, 0), rng((size_t)J * kMaxRanges * 2, 0);
+  std::vector<int32_t> ra((size_t)nfam * J, 0), rb((size_t)nfam * J, 0), order((size_t)nfam * J, 0);
+  std::vector<int32_t> nrng(J, 0), rng((size_t)J * kMaxRanges * 2, 0);
   int64_t direct_taps = 0;
   for (int j = 0; j < J; ++j) {
     const double* F = &p->h_fbank[(size_t)j * N];
     std::vector<double> wref(nfam, 0.0);
-    const int s_lo = row_lo[j] * 8, s_hi = row_hi[j] * 8;
-    int first = nblk, last = -1;
     for (int m = 0; m < nblk; ++m) {
       const int s = m * blk_len, e = std::min(N, s + blk_len);
-      if (e <= s_lo || s >= s_hi) continue;  // outside the support: -2
-      int c = -1;
-      if (e + look <= N) {
-        for (int g = 0; g < nfam && c < 0; ++g) {
-          const double* T = &tm[(size_t)g * N];
-          double w = wref[g] > 0 ? wref[g] : F[s] / T[s];
-          if (!(w > 0) || !std::isfinite(w)) continue;
-          bool ok = true;
-          for (int n = s; n < e + look && ok; ++n) ok = fabs(F[n] - w * T[n]) <= tol * w * T[n];
-          if (ok) { c = g; wref[g] = w; }
-        }
+      if (e + look > N) continue;  // the look-ahead wraps around N: not a single region
+      for (int g = 0; g < nfam; ++g) {
+        const double* T = &tm[(size_t)g * N];
+        const double w = wref[g] > 0 ? wref[g] : F[s] / T[s];
+        if (!(w > 0) || !std::isfinite(w)) continue;
+        bool ok = true;
+        for (int n = s; n < e + look && ok; ++n) ok = fabs(F[n] - w * T[n]) <= tol * w * T[n];
+        if (ok) { cls[(size_t)j * nblk + m] = (int8_t)g; wref[g] = w; break; }
       }
-      cls[(size_t)j * nblk + m] = (int8_t)c;
-      if (c >= 0) { first = std::min(first, m); last = m; }
     }
-    for (int g = 0; g < nfam; ++g) wsq[(size_t)j * nfam + g] = wref[g] * wref[g];
-    blo[j] = (last >= 0) ? first : 0;
-    bhi[j] = (last >= 0) ? last + 1 : 0;
-    // merge runs of direct blocks into row ranges
+    for (int g = 0; g < nfam; ++g) {
+      wsq[(size_t)j * nfam + g] = wref[g] * wref[g];
+      // the blocks of one family must be one contiguous run
+      int first = -1, last = -1, count = 0;
+      for (int m = 0; m < nblk; ++m)
+        if (cls[(size_t)j * nblk + m] == g) { if (first < 0) first = m; last = m; ++count; }
+      if (count > 0 && count != last - first + 1) return 0;
+      ra[(size_t)g * J + j] = count ? first : 0;
+      rb[(size_t)g * J + j] = count ? last + 1 : 0;
+    }
+    // blocks inside the support that no template fits: merged into row ranges for the direct kernel
+    const int s_lo = row_lo[j] * 8, s_hi = row_hi[j] * 8;
     int nr = 0;
     for (int m = 0; m < nblk;) {
-      if (cls[(size_t)j * nblk + m] != -1) { ++m; continue; }
+      const int s = m * blk_len, e = std::min(N, s + blk_len);
+      const bool direct = cls[(size_t)j * nblk + m] < 0 && e > s_lo && s < s_hi;
+      if (!direct) { ++m; continue; }
       int m2 = m;
-      while (m2 < nblk && cls[(size_t)j * nblk + m2] == -1) ++m2;
+      while (m2 < nblk && cls[(size_t)j * nblk + m2] < 0 && std::min(N, (m2 + 1) * blk_len) > s_lo && m2 * blk_len < s_hi) ++m2;
       if (nr >= kMaxRanges) return 0;  // too fragmented: keep the direct path for the whole plan
-      const int s = m * blk_len, e = std::min(N, m2 * blk_len);
+      const int e2 = std::min(N, m2 * blk_len);
       rng[((size_t)j * kMaxRanges + nr) * 2] = s / 8;
-      rng[((size_t)j * kMaxRanges + nr) * 2 + 1] = e / 8;
-      direct_taps += e - s;
+      rng[((size_t)j * kMaxRanges + nr) * 2 + 1] = e2 / 8;
+      direct_taps += e2 - s;
       ++nr;
       m = m2;
     }
     nrng[j] = nr;
   }
+  // combination mode per family: prefix sums when every range starts at block 0, suffix sums when every range
+  // ends at the same block, plain short range sums otherwise
+  int32_t mode[kCombMaxFam] = {0, 0, 0}, nband[kCombMaxFam] = {0, 0, 0}, endb[kCombMaxFam] = {0, 0, 0};
+  for (int g = 0; g < nfam; ++g) {
+    std::vector<int> bands;
+    bool all_a0 = true, all_b_same = true;
+    int bend = -1;
+    for (int j = 0; j < J; ++j) {
+      const int a0 = ra[(size_t)g * J + j], b0 = rb[(size_t)g * J + j];
+      if (b0 <= a0) continue;
+      bands.push_back(j);
+      if (a0 != 0) all_a0 = false;
+      if (bend < 0) bend = b0; else if (b0 != bend) all_b_same = false;
+    }
+    nband[g] = (int)bands.size();
+    if (all_a0 && !bands.empty()) {
+      mode[g] = kCombPrefix;
+      std::stable_sort(bands.begin(), bands.end(), [&](int x, int y) { return rb[(size_t)g * J + x] < rb[(size_t)g * J + y]; });
+    } else if (all_b_same && !bands.empty()) {
+      mode[g] = kCombSuffix;
+      endb[g] = bend;
+      std::stable_sort(bands.begin(), bands.end(), [&](int x, int y) { return ra[(size_t)g * J + x] > ra[(size_t)g * J + y]; });
+    } else {
+      mode[g] = kCombRange;
+    }
+    for (size_t i = 0; i < bands.size(); ++i) order[(size_t)g * J + i] = bands[i];
+  }
+  for (int g = 0; g < kCombMaxFam; ++g) { p->comb_mode[g] = mode[g]; p->comb_nband[g] = nband[g]; p->comb_end[g] = endb[g]; }
   // worthwhile only if the shared work plus the direct remainder is well below the per-band total
   const int64_t fam_taps = (int64_t)nfam * N;
   if ((fam_taps + direct_taps) * 2 > p->g.support_taps) return 0;
@@ -319,8 +352,8 @@ static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, cons
   for (int g = 0; g < nfam; ++g)
     for (int k = 0; k < p->ld; ++k) tpad[(size_t)g * p->ld + k] = tm[(size_t)g * N + (k % N)];
   int rc;
-  if ((rc = upload(&p->d_tmpl, tpad)) || (rc = upload(&p->d_cls, cls)) || (rc = upload(&p->d_wsq, wsq)) ||
-      (rc = upload(&p->d_blo, blo)) || (rc = upload(&p->d_bhi, bhi)) || (rc = upload(&p->d_nrng, nrng)) ||
+  if ((rc = upload(&p->d_tmpl, tpad)) || (rc = upload(&p->d_wsq, wsq)) || (rc = upload(&p->d_order, order)) ||
+      (rc = upload(&p->d_ra, ra)) || (rc = upload(&p->d_rb, rb)) || (rc = upload(&p->d_nrng, nrng)) ||
       (rc = upload(&p->d_rng, rng)))
     return rc;
   p->nfam = nfam; p->nblk = nblk; p->fam_q = q; p->blk_len = blk_len;
@@ -328,16 +361,13 @@ static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, cons
   if (const char* e = getenv("FDLP_FAM_BPC")) bpc = std::max(1, atoi(e));
   p->fam_bpc = std::min(bpc, nblk);
   p->fam_nchunk = (nblk + p->fam_bpc - 1) / p->fam_bpc;
-  p->comb_JB = (J + kCombBG - 1) / kCombBG;
-  p->comb_LW = (p->g.nlags + 31) / 32;
-  p->comb_jbt = p->comb_JB <= 8 ? 8 : (p->comb_JB <= 16 ? 16 : (p->comb_JB <= 24 ? 24 : 32));
   p->fam_smem = (size_t)kAcWarps * p->na * kFoldStride * sizeof(double);
-  p->comb_smem = (size_t)nfam * kCombTB * p->g.nlags * sizeof(double);
+  p->comb_smem = (size_t)J * p->g.nlags * sizeof(double);
   p->g.family_taps = fam_taps;
   p->g.direct_taps = direct_taps;
   p->g.nfam = nfam;
   p->g.block_len = blk_len;
-  p->fam_ok = p->comb_LW <= 5;
+  p->fam_ok = p->g.nlags <= 160 && p->comb_smem <= 200 * 1024;
   return 0;
 }
 
@@ -528,12 +558,7 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
       default: p->fam_ok = false;
     }
 #undef SET_FAM
-    switch (p->comb_jbt) {
-      case 8: SET_SMEM((family_combine_kernel<8>), p->comb_smem); break;
-      case 16: SET_SMEM((family_combine_kernel<16>), p->comb_smem); break;
-      case 24: SET_SMEM((family_combine_kernel<24>), p->comb_smem); break;
-      default: SET_SMEM((family_combine_kernel<32>), p->comb_smem); break;
-    }
+    SET_SMEM(family_combine_kernel, p->comb_smem);
   }
 #undef SET_SMEM
   {
@@ -647,10 +672,10 @@ static int launch_autocorr_family(fdlp_plan* p, const double* dct, int n_seg, do
   const int nbg = (d.J + kAcWarps - 1) / kAcWarps;
   const dim3 gridD((unsigned)((size_t)n_seg * nbg));
   CombArgs c;
-  c.p = p->d_p; c.r = r; c.cls = p->d_cls; c.wsq = p->d_wsq; c.blo = p->d_blo; c.bhi = p->d_bhi;
+  c.p = p->d_p; c.r = r; c.order = p->d_order; c.ra = p->d_ra; c.rb = p->d_rb; c.wsq = p->d_wsq;
+  for (int g = 0; g < kCombMaxFam; ++g) { c.mode[g] = p->comb_mode[g]; c.nband[g] = p->comb_nband[g]; c.end[g] = p->comb_end[g]; }
   c.n_seg = n_seg; c.J = p->prm.nfilters; c.nfam = p->nfam; c.nblk = p->nblk; c.nlags = p->g.nlags;
-  c.JB = p->comb_JB; c.LW = p->comb_LW;
-  const dim3 gridC(n_seg), blockC(kCombBG * p->comb_LW * 32);
+  const dim3 gridC(n_seg), blockC(160);
 #define RUN_FAM_A(NA_) case NA_: family_block_autocorr_kernel<NA_><<<gridA, block, p->fam_smem, st>>>(f); break;
 #define RUN_FAM_D(NA_) case NA_: autocorr_ranges_kernel<NA_><<<gridD, block, p->fam_smem, st>>>(d); break;
   switch (p->na) {
@@ -659,12 +684,7 @@ static int launch_autocorr_family(fdlp_plan* p, const double* dct, int n_seg, do
   }
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev_ac[1], st));
-  switch (p->comb_jbt) {
-    case 8: family_combine_kernel<8><<<gridC, blockC, p->comb_smem, st>>>(c); break;
-    case 16: family_combine_kernel<16><<<gridC, blockC, p->comb_smem, st>>>(c); break;
-    case 24: family_combine_kernel<24><<<gridC, blockC, p->comb_smem, st>>>(c); break;
-    default: family_combine_kernel<32><<<gridC, blockC, p->comb_smem, st>>>(c); break;
-  }
+  family_combine_kernel<<<gridC, blockC, p->comb_smem, st>>>(c);
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev_ac[2], st));
   switch (p->na) {
