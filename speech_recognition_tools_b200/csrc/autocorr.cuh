@@ -152,6 +152,34 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_dmma_kernel(const A
 // per-band kernel (autocorr_ranges_kernel).  The result is the exact autocorrelation of the sequence
 // (w T_g c), a relative 1e-12 perturbation of F_j c, evaluated with the same FP64 products and sums.
 
+// Diagonal fold of a warp's NA accumulator tiles into lags, through warp-private shared memory.
+// C_i[row][col] (lane holds row = lane/4, cols 2*(lane%4)+{0,1}) carries lag 8i + col - row.  Elements are stored
+// skewed, slot (i + (col >= row)) / diagonal ((col - row) & 7) / row, so the 8 terms of lag 8*ab + d are the 8
+// contiguous doubles at slot ab+1, diagonal d: four 16-byte loads and a 3-level add tree per lag.
+constexpr int kFoldStride = 72;  // doubles per slot (64 + 8: consecutive slots start 8 banks apart)
+__host__ __device__ constexpr int fold_smem_doubles(int na) { return (na + 1) * kFoldStride; }
+
+__device__ __forceinline__ void prefetch_l1(const void* ptr) { asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr)); }
+
+template <int NA>
+__device__ __forceinline__ void fold_store_tiles(const double (&acc)[NA][2], double* my, int lane) {
+  const int lr = lane & 3, lc = lane >> 2;
+  const int c0 = 2 * lr, c1 = 2 * lr + 1;
+  const int o0 = ((c0 >= lc) ? kFoldStride : 0) + (((c0 - lc) & 7) << 3) + lc;
+  const int o1 = ((c1 >= lc) ? kFoldStride : 0) + (((c1 - lc) & 7) << 3) + lc;
+#pragma unroll
+  for (int i = 0; i < NA; ++i) {
+    my[i * kFoldStride + o0] = acc[i][0];
+    my[i * kFoldStride + o1] = acc[i][1];
+  }
+}
+
+__device__ __forceinline__ double fold_lag(const double* my, int k) {
+  const double2* q = reinterpret_cast<const double2*>(my + ((k >> 3) + 1) * kFoldStride + ((k & 7) << 3));
+  const double2 v0 = q[0], v1 = q[1], v2 = q[2], v3 = q[3];
+  return ((v0.x + v0.y) + (v1.x + v1.y)) + ((v2.x + v2.y) + (v3.x + v3.y));
+}
+
 struct FamArgs {
   const double* dct;   // [n_seg, ld]
   const double* tmpl;  // [nfam, ld] templates, circular extension like fbank
@@ -161,8 +189,6 @@ struct FamArgs {
   int q;               // a block is q * U steps of 32 samples (U = (NA + 4) / 4)
   int bpc, nchunk;     // blocks per warp task, tasks per (segment, family)
 };
-
-constexpr int kFoldStride = 72;  // doubles between C tiles in shared memory (bank-conflict-free diagonal reads)
 
 template <int NA>
 __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel(const FamArgs a) {
@@ -196,13 +222,18 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel
 #pragma unroll
   for (int i = NA; i < RS; ++i) ring[i] = 0.0;
 
-  double* my = cs + (size_t)warp * NA * kFoldStride;
+  double* my = cs + (size_t)warp * fold_smem_doubles(NA);
   int step = blk0 * spb;
+  // the rows of c come from HBM (the templates stay in L1/L2): pull them into L1 two groups of U steps ahead
+  const double* cpf = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + NA + 4 + 8 * U) * 8 + lane * 16;
+  const int pf_lanes = (U * 32 * 8 + 127) / 128;
   for (int blk = blk0; blk < blk1; ++blk) {
     double acc[NA][2];
 #pragma unroll
     for (int i = 0; i < NA; ++i) acc[i][0] = acc[i][1] = 0.0;
     for (int g = 0; g < a.q; ++g) {
+      if (lane < pf_lanes) prefetch_l1(cpf);
+      cpf += U * 32;
 #pragma unroll
       for (int s = 0; s < U; ++s) {
         if (step + s < a.nsteps_total) {
@@ -220,22 +251,10 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel
       step += U;
     }
     // flush: C tiles -> shared (warp-private), diagonal sums -> P[seg][fam][blk][0..nlags)
-#pragma unroll
-    for (int i = 0; i < NA; ++i)
-      *reinterpret_cast<double2*>(my + i * kFoldStride + lc * 8 + 2 * lr) = make_double2(acc[i][0], acc[i][1]);
+    fold_store_tiles<NA>(acc, my, lane);
     __syncwarp();
     double* pout = a.p + (((size_t)seg * a.nfam + fam) * a.nblk + blk) * a.nlags;
-    for (int k = lane; k < a.nlags; k += 32) {
-      const int ab = k >> 3, d = k & 7;
-      const double* c0 = my + ab * kFoldStride;
-      double sum = 0.0;
-      for (int row = 0; row + d < 8; ++row) sum += c0[row * 8 + row + d];
-      if (d > 0) {
-        const double* c1 = c0 + kFoldStride;
-        for (int row = 8 - d; row < 8; ++row) sum += c1[row * 8 + row + d - 8];
-      }
-      pout[k] = sum;
-    }
+    for (int k = lane; k < a.nlags; k += 32) pout[k] = fold_lag(my, k);
     __syncwarp();
   }
 }
@@ -362,6 +381,11 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
     const int nsteps = (m_hi - m_lo) >> 2;
     const double* __restrict__ pc = a.dct + (size_t)seg * a.ld + (size_t)m_lo * 8 + lane_off;
     const double* __restrict__ pf = a.fbank + (size_t)band * a.ld + (size_t)m_lo * 8 + lane_off;
+    if (q + 1 < nr) {  // the first rows of the next range: into L1 while this range computes
+      const size_t nxt = (size_t)a.rng[(band * kMaxRanges + q + 1) * 2] * 8 + (lane & 15) * 16;
+      if ((lane & 15) * 16 < (NA + 8) * 8)
+        prefetch_l1((lane < 16) ? (a.dct + (size_t)seg * a.ld + nxt) : (a.fbank + (size_t)band * a.ld + nxt));
+    }
     double ring[RS];
 #pragma unroll
     for (int i = 0; i < NA; ++i) ring[i] = __ldg(pf + 8 * i) * __ldg(pc + 8 * i);
@@ -390,23 +414,11 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
     }
   }
 
-  double* my = cs + (size_t)warp * NA * kFoldStride;
-#pragma unroll
-  for (int i = 0; i < NA; ++i)
-    *reinterpret_cast<double2*>(my + i * kFoldStride + lc * 8 + 2 * lr) = make_double2(acc[i][0], acc[i][1]);
+  double* my = cs + (size_t)warp * fold_smem_doubles(NA);
+  fold_store_tiles<NA>(acc, my, lane);
   __syncwarp();
   double* rout = a.r + ((size_t)seg * a.J + band) * a.nlags;
-  for (int k = lane; k < a.nlags; k += 32) {
-    const int ab = k >> 3, d = k & 7;
-    const double* c0 = my + ab * kFoldStride;
-    double sum = 0.0;
-    for (int row = 0; row + d < 8; ++row) sum += c0[row * 8 + row + d];
-    if (d > 0) {
-      const double* c1 = c0 + kFoldStride;
-      for (int row = 8 - d; row < 8; ++row) sum += c1[row * 8 + row + d - 8];
-    }
-    rout[k] += sum;
-  }
+  for (int k = lane; k < a.nlags; k += 32) rout[k] += fold_lag(my, k);
 }
 
 }  // namespace fdlp

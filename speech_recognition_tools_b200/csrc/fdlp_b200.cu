@@ -361,7 +361,7 @@ static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, cons
   if (const char* e = getenv("FDLP_FAM_BPC")) bpc = std::max(1, atoi(e));
   p->fam_bpc = std::min(bpc, nblk);
   p->fam_nchunk = (nblk + p->fam_bpc - 1) / p->fam_bpc;
-  p->fam_smem = (size_t)kAcWarps * p->na * kFoldStride * sizeof(double);
+  p->fam_smem = (size_t)kAcWarps * fold_smem_doubles(p->na) * sizeof(double);
   p->comb_smem = (size_t)J * p->g.nlags * sizeof(double);
   p->g.family_taps = fam_taps;
   p->g.direct_taps = direct_taps;

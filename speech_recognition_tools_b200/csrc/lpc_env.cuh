@@ -77,23 +77,39 @@ __global__ void __launch_bounds__(kLpcMaxThreads) lpc_cepstrum_kernel(const LpcA
   __syncwarp();
 
   // ---- Levinson-Durbin: T a = -r[1..p], in place ----
+  // One pass per order m: the symmetric pairs (i, m-i) are updated in place and, with the new values still in
+  // registers, multiplied into the NEXT order's inner product acc_{m+1} = r[m+1] + sum_i a'[i] r[m+1-i], so every
+  // coefficient is read and written once per order.  k = -acc * (1/E) with the reciprocal from __drcp_rn.
   double E = s_r[0];
   int bad = 0;
+  double acc = s_r[1];
   for (int m = 1; m <= p; ++m) {
-    double part = 0.0;
-    for (int i = 1 + g; i < m; i += kLpcGroup) part = fma(s_a[i], s_r[m - i], part);
-    const double acc = group_sum8(part) + s_r[m];
     if (E == 0.0 || !isfinite(E)) bad = FDLP_ST_SINGULAR;
-    const double k = -acc / E;
+    const double k = -acc * __drcp_rn(E);
+    const double* rn = s_r + 1;  // rn[i] = r[i+1]
+    double part = 0.0;
+#pragma unroll 2
     for (int i = 1 + g; 2 * i < m; i += kLpcGroup) {
-      const double ai = s_a[i], aj = s_a[m - i];
-      s_a[i] = fma(k, aj, ai);
-      s_a[m - i] = fma(k, ai, aj);
+      const int jx = m - i;
+      const double ai = s_a[i], aj = s_a[jx];
+      const double ni = fma(k, aj, ai), nj = fma(k, ai, aj);
+      s_a[i] = ni;
+      s_a[jx] = nj;
+      part = fma(ni, rn[jx], part);
+      part = fma(nj, rn[i], part);
     }
     if (g == 0) {
-      if ((m & 1) == 0) { const double ah = s_a[m >> 1]; s_a[m >> 1] = fma(k, ah, ah); }
+      if ((m & 1) == 0) {
+        const int h = m >> 1;
+        const double ah = s_a[h];
+        const double nh = fma(k, ah, ah);
+        s_a[h] = nh;
+        part = fma(nh, rn[h], part);
+      }
       s_a[m] = k;
+      part = fma(k, s_r[1], part);
     }
+    acc = group_sum8(part) + s_r[m + 1];  // nlags = p + 2, so r[p+1] exists (the value is unused after m = p)
     E *= (1.0 - k * k);
     __syncwarp();
   }
