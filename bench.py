@@ -243,12 +243,16 @@ def run_ours(args):
     # ---- per-stage device times of the dominant kernel (CUDA events inside fdlp_forward, same stream) ----
     ex.set_profiling(True)
     stage = {"dct": 0.0, "autocorr": 0.0, "lpc_env": 0.0, "ola": 0.0}
+    ac_ms = {"family_blocks": 0.0, "combine": 0.0, "direct": 0.0}
     nprof = 5
     for _ in range(nprof):
         step_resident()
         s = ex.stage_ms()
         for k in stage:
             stage[k] += s[k] / nprof
+        s = ex.autocorr_ms()
+        for k in ac_ms:
+            ac_ms[k] += s[k] / nprof
     ex.set_profiling(False)
 
     out = None
@@ -259,28 +263,45 @@ def run_ours(args):
         _lib.check(lib.fdlp_measure_fp64_peak(C.byref(dfma), C.byref(dmma)))
         peak = max(dfma.value, dmma.value)
         g = ex.geom
-        # ALGORITHMIC flops of the autocorrelation: 2 * (p+2) * sum_j len(supp_j) per segment, with
-        # supp_j = the taps of band j the kernel visits: cochlear skirts below 1e-12 * max|F_j| are skipped
-        # (DESIGN.md section 4), which leaves 52 % of the 80 x 24000 taps; the dense count is reported beside it
-        ac_flops = 2.0 * g["nlags"] * g["support_taps"] * lay.n_seg
-        ac_flops_dense = 2.0 * g["nlags"] * J * g["N"] * lay.n_seg
-        achieved = ac_flops / (stage["autocorr"] * 1e-3) / 1e12
+        p_, L_, kk_ = WSJ["order"], g["L"], g["kk"]
+        # ALGORITHMIC flops per launch of each FP64 kernel.  Autocorrelation, family path:
+        #   block sums   2 (p+2) * nfam * N          per segment  (band-independent, shared by the J bands)
+        #   direct part  2 (p+2) * sum_j direct_j    per segment  (blocks that straddle a filter-region boundary)
+        # direct path (mel / custom filterbanks): 2 (p+2) * sum_j len(supp_j) per segment.
+        # LPC + cepstrum + envelope: (2 p^2 + 1.5 L^2 + 2 L kk) per (segment, band).
+        nseg = lay.n_seg
+        kern = {}
+        if g["nfam"] > 0:
+            kern["family_block_autocorr_kernel"] = (ac_ms["family_blocks"], 2.0 * g["nlags"] * g["family_taps"] * nseg)
+            kern["autocorr_ranges_kernel"] = (ac_ms["direct"], 2.0 * g["nlags"] * g["direct_taps"] * nseg)
+        else:
+            kern["autocorr_dmma_kernel"] = (stage["autocorr"], 2.0 * g["nlags"] * g["support_taps"] * nseg)
+        kern["lpc_cepstrum_kernel+envelope_dmma_kernel"] = (stage["lpc_env"], (2.0 * p_ * p_ + 1.5 * L_ * L_ + 2.0 * L_ * kk_) * J * nseg)
+        top = max(kern, key=lambda k: kern[k][0])
+        top_ms, top_flops = kern[top]
+        achieved = top_flops / (top_ms * 1e-3) / 1e12
+        ac_flops_support = 2.0 * g["nlags"] * g["support_taps"] * nseg
         traffic = None
-        tp = os.path.join(ROOT, "profiles", "autocorr_traffic.json")
+        tp = os.path.join(ROOT, "profiles", "top_kernel_traffic.json")
         if os.path.exists(tp):
             try:
-                traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+                traffic = json.load(open(tp)).get(top)
             except Exception:  # noqa: BLE001
                 traffic = None
-        roofline = {"bound": "tensor", "pipe": "fp64 (DMMA.8x8x4 / DFMA)", "kernel": "autocorr_dmma_kernel",
+        roofline = {"bound": "tensor", "pipe": "fp64 (DMMA.8x8x4 / DFMA)", "kernel": top,
                     "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                     "traffic": traffic, "peak_source": "fdlp_measure_fp64_peak, measured live on this GPU "
                     "(MEASURED_PEAKS.json has no FP64 entry); dfma=%.2f dmma=%.2f" % (dfma.value, dmma.value),
-                    "algorithmic_flops_per_launch": ac_flops, "dense_support_flops_per_launch": ac_flops_dense,
-                    "support_fraction": g["support_taps"] / float(J * g["N"]),
-                    "dense_equivalent_tflops": ac_flops_dense / (stage["autocorr"] * 1e-3) / 1e12,
-                    "kernel_ms": stage["autocorr"],
-                    "stage_ms": stage, "share_of_step": stage["autocorr"] / sum(stage.values())}
+                    "algorithmic_flops_per_launch": top_flops, "kernel_ms": top_ms,
+                    "kernels": {k: {"ms": v[0], "algorithmic_tflops": v[1] / (v[0] * 1e-3) / 1e12 if v[0] > 0 else None,
+                                    "frac": (v[1] / (v[0] * 1e-3) / 1e12 / peak) if v[0] > 0 else None}
+                                for k, v in kern.items()},
+                    "autocorr": {"ms": stage["autocorr"], "family_combine_ms": ac_ms["combine"],
+                                 "per_band_support_flops": ac_flops_support,
+                                 "per_band_equivalent_tflops": ac_flops_support / (stage["autocorr"] * 1e-3) / 1e12,
+                                 "note": "per-band-equivalent = flops a per-band direct evaluation over the filters' "
+                                         "support would execute; the family decomposition shares most of them"},
+                    "stage_ms": stage, "share_of_step": top_ms / sum(stage.values())}
 
         # ---- mel-spectrogram baseline path on the same batch (BASELINE.json configs[1]) ----
         mel = MelExtractor(MelConfig(**MEL_RECIPE), device=dev)
@@ -319,7 +340,7 @@ def run_ours(args):
                        "utterances_with_status": bad_status},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
                     "ms_per_step": e2e_ms},
-            "gpu_launches": 5 * args.steps * world,
+            "gpu_launches": (7 if ex.geom["nfam"] > 0 else 5) * args.steps * world,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "mel_baseline": mel_info,
         }
     if world > 1:
