@@ -185,6 +185,36 @@ class BatchLayout:
         return self
 
 
+def split_layout(lay: "BatchLayout", n_chunks: int):
+    """Cut a packed batch into up to `n_chunks` runs of whole utterances with about equal segment counts.
+    Returns [(u0, u1, sub_layout)]; the sub-layout's offsets are relative to the chunk's first sample / segment /
+    frame, so each chunk is a self-contained fdlp_batch over a slice of the packed buffers."""
+    n_chunks = max(1, min(int(n_chunks), lay.n_utt))
+    bounds = [0]
+    for c in range(1, n_chunks):
+        target = lay.n_seg * c / n_chunks
+        u = int(np.searchsorted(lay.utt_seg_off, target, side="left"))
+        u = min(max(u, bounds[-1] + 1), lay.n_utt - (n_chunks - c))
+        bounds.append(u)
+    bounds.append(lay.n_utt)
+    out = []
+    for u0, u1 in zip(bounds[:-1], bounds[1:]):
+        s0, s1 = int(lay.utt_seg_off[u0]), int(lay.utt_seg_off[u1])
+        f0, f1 = int(lay.utt_frame_off[u0]), int(lay.utt_frame_off[u1])
+        frs = np.diff(lay.utt_frame_off[u0:u1 + 1])
+        sub = BatchLayout(
+            lengths=lay.lengths[u0:u1],
+            utt_wav_off=(lay.utt_wav_off[u0:u1 + 1] - lay.utt_wav_off[u0]).astype(np.int64),
+            utt_seg_off=(lay.utt_seg_off[u0:u1 + 1] - s0).astype(np.int32),
+            utt_frame_off=(lay.utt_frame_off[u0:u1 + 1] - f0).astype(np.int64),
+            seg_utt=(lay.seg_utt[s0:s1] - u0).astype(np.int32),
+            seg_ptr=lay.seg_ptr[s0:s1].astype(np.int32),
+            n_utt=u1 - u0, n_seg=s1 - s0, n_frames=f1 - f0,
+            max_utt_frames=int(frs.max()) if u1 > u0 else 0)
+        out.append((u0, u1, sub))
+    return out
+
+
 def _as_rngs(jitter, n_utt):
     """`jitter`: a random.Random consumed sequentially over the utterances (what the reference does within
     one process), an int seed for such a generator, or a sequence of per-utterance seeds."""
@@ -391,6 +421,60 @@ class FdlpExtractor:
         with torch.cuda.device(self.device):
             L.check(self._lib.fdlp_forward(self._plan, C.byref(b), C.c_void_p(stream)))
         return feats, status
+
+    def extract_host(self, host_wav: torch.Tensor, lay: BatchLayout, feats_host: Optional[torch.Tensor] = None,
+                     n_chunks: int = 4, cmvn: Optional[torch.Tensor] = None, status: Optional[torch.Tensor] = None,
+                     wav_dev: Optional[torch.Tensor] = None, feats: Optional[torch.Tensor] = None):
+        """End-to-end call for a packed batch that lives in (pinned) HOST memory: samples go host -> device,
+        features device -> host, and both copies overlap the kernels.  The batch is cut into `n_chunks` runs of
+        whole utterances; chunk c+1 is uploaded on a copy stream while chunk c computes on the current stream
+        and the features of chunk c-1 are downloaded on a third stream.  Results are identical to one
+        forward_packed over the whole batch (utterances are independent).  Returns (feats_dev, feats_host, status);
+        the current stream waits for the last download."""
+        dev = self.device
+        J = self.cfg.nfilters
+        if wav_dev is None:
+            wav_dev = torch.empty(host_wav.numel(), dtype=host_wav.dtype, device=dev)
+        if feats is None:
+            feats = torch.empty((lay.n_frames, J), dtype=torch.float32, device=dev)
+        if feats_host is None:
+            feats_host = torch.empty((lay.n_frames, J), dtype=torch.float32, pin_memory=True)
+        if status is None:
+            status = torch.zeros(max(lay.n_utt, 1), dtype=torch.int32, device=dev)
+        if not hasattr(self, "_s_in"):
+            self._s_in, self._s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        cur = torch.cuda.current_stream(dev)
+        chunks = split_layout(lay, n_chunks)
+        ev0 = torch.cuda.Event()
+        ev0.record(cur)
+        self._s_in.wait_event(ev0)
+        self._s_out.wait_event(ev0)
+        ev_in = []
+        with torch.cuda.stream(self._s_in):
+            for u0, u1, sub in chunks:
+                w0, w1 = int(lay.utt_wav_off[u0]), int(lay.utt_wav_off[u1])
+                wav_dev[w0:w1].copy_(host_wav[w0:w1], non_blocking=True)
+                # the framing kernel uses 16-byte loads when the batch base pointer is 16-byte aligned:
+                # hand it the slice from the aligned sample below w0 and shift the offsets instead
+                sub.utt_wav_off = sub.utt_wav_off + (w0 % 8)
+                sub.to(dev)
+                e = torch.cuda.Event()
+                e.record(self._s_in)
+                ev_in.append(e)
+        for (u0, u1, sub), e in zip(chunks, ev_in):
+            w0, w1 = int(lay.utt_wav_off[u0]), int(lay.utt_wav_off[u1])
+            f0, f1 = int(lay.utt_frame_off[u0]), int(lay.utt_frame_off[u1])
+            cur.wait_event(e)
+            self.forward_packed(wav_dev[w0 - (w0 % 8):w1], sub, feats=feats[f0:f1], cmvn=cmvn, status=status[u0:u1])
+            done = torch.cuda.Event()
+            done.record(cur)
+            self._s_out.wait_event(done)
+            with torch.cuda.stream(self._s_out):
+                feats_host[f0:f1].copy_(feats[f0:f1], non_blocking=True)
+        fin = torch.cuda.Event()
+        fin.record(self._s_out)
+        cur.wait_event(fin)
+        return feats, feats_host, status
 
     def __call__(self, wavs: Sequence[Union[np.ndarray, torch.Tensor]], jitter=None,
                  noise: Optional[NoiseSpec] = None, cmvn: Optional[torch.Tensor] = None,

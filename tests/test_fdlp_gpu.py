@@ -224,3 +224,21 @@ def test_family_autocorrelation_matches_direct_kernel_and_oracle():
     assert np.max(np.abs(r_dir - r_ref) / r0) < 1e-12
     assert np.max(np.abs(r_fam - r_ref) / r0) < 1e-12
     np.testing.assert_allclose(feats_fam, feats_dir, rtol=2e-7, atol=5e-6)
+
+
+def test_extract_host_pipeline_equals_single_batch():
+    """The chunked host->device->host pipeline (copies overlapping the kernels) must give bit-identical
+    features and CMVN-independent results to one forward_packed over the whole batch."""
+    ex = extractor(**WSJ)
+    lengths = synth.wsj_shaped_lengths(23, seed=9)
+    wavs = [synth.make_utterance("white" if i % 2 else "speechlike", 4, i, int(T), 30.0) for i, T in enumerate(lengths)]
+    host, lens = ex.pack(wavs)
+    lay = ex.layout(lens, jitter=5)
+    ref, st = ex.forward_packed(host.to(ex.device), lay)
+    lay2 = ex.layout(lens, jitter=5)
+    for n_chunks in (1, 3, 7):
+        feats, feats_host, st2 = ex.extract_host(host, lay2, n_chunks=n_chunks)
+        torch.cuda.synchronize()
+        assert torch.equal(feats, ref)
+        assert torch.equal(feats_host, ref.cpu())
+        assert torch.equal(st, st2)
