@@ -154,9 +154,11 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_dmma_kernel(const A
 
 // Diagonal fold of a warp's NA accumulator tiles into lags, through warp-private shared memory.
 // C_i[row][col] (lane holds row = lane/4, cols 2*(lane%4)+{0,1}) carries lag 8i + col - row.  Elements are stored
-// skewed, slot (i + (col >= row)) / diagonal ((col - row) & 7) / row, so the 8 terms of lag 8*ab + d are the 8
-// contiguous doubles at slot ab+1, diagonal d: four 16-byte loads and a 3-level add tree per lag.
-constexpr int kFoldStride = 72;  // doubles per slot (64 + 8: consecutive slots start 8 banks apart)
+// skewed: slot (i + (col >= row)), diagonal d = (col - row) & 7, position row ^ (d >> 1), so the 8 terms of lag
+// 8*ab + d are the 8 doubles of slot ab+1, diagonal d (in some order).  The XOR on the store side and the
+// per-lane rotation on the load side make both 2 wavefronts per instruction, the minimum for 32 x 8 bytes
+// (searched exhaustively over swizzles; the plain layout costs 4 per store and 16 per load).
+constexpr int kFoldStride = 64;  // doubles per slot
 __host__ __device__ constexpr int fold_smem_doubles(int na) { return (na + 1) * kFoldStride; }
 
 __device__ __forceinline__ void prefetch_l1(const void* ptr) { asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr)); }
@@ -165,8 +167,9 @@ template <int NA>
 __device__ __forceinline__ void fold_store_tiles(const double (&acc)[NA][2], double* my, int lane) {
   const int lr = lane & 3, lc = lane >> 2;
   const int c0 = 2 * lr, c1 = 2 * lr + 1;
-  const int o0 = ((c0 >= lc) ? kFoldStride : 0) + (((c0 - lc) & 7) << 3) + lc;
-  const int o1 = ((c1 >= lc) ? kFoldStride : 0) + (((c1 - lc) & 7) << 3) + lc;
+  const int d0 = (c0 - lc) & 7, d1 = (c1 - lc) & 7;
+  const int o0 = ((c0 >= lc) ? kFoldStride : 0) + (d0 << 3) + (lc ^ (d0 >> 1));
+  const int o1 = ((c1 >= lc) ? kFoldStride : 0) + (d1 << 3) + (lc ^ (d1 >> 1));
 #pragma unroll
   for (int i = 0; i < NA; ++i) {
     my[i * kFoldStride + o0] = acc[i][0];
@@ -174,10 +177,13 @@ __device__ __forceinline__ void fold_store_tiles(const double (&acc)[NA][2], dou
   }
 }
 
-__device__ __forceinline__ double fold_lag(const double* my, int k) {
-  const double2* q = reinterpret_cast<const double2*>(my + ((k >> 3) + 1) * kFoldStride + ((k & 7) << 3));
-  const double2 v0 = q[0], v1 = q[1], v2 = q[2], v3 = q[3];
-  return ((v0.x + v0.y) + (v1.x + v1.y)) + ((v2.x + v2.y) + (v3.x + v3.y));
+__device__ __forceinline__ double fold_lag(const double* my, int k, int lane) {
+  const double* q = my + ((k >> 3) + 1) * kFoldStride + ((k & 7) << 3);
+  const int rot = lane >> 2;
+  double v[8];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) v[r] = q[(r + rot) & 7];
+  return ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
 }
 
 struct FamArgs {
@@ -254,7 +260,7 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel
     fold_store_tiles<NA>(acc, my, lane);
     __syncwarp();
     double* pout = a.p + (((size_t)seg * a.nfam + fam) * a.nblk + blk) * a.nlags;
-    for (int k = lane; k < a.nlags; k += 32) pout[k] = fold_lag(my, k);
+    for (int k = lane; k < a.nlags; k += 32) pout[k] = fold_lag(my, k, lane);
     __syncwarp();
   }
 }
@@ -418,7 +424,7 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
   fold_store_tiles<NA>(acc, my, lane);
   __syncwarp();
   double* rout = a.r + ((size_t)seg * a.J + band) * a.nlags;
-  for (int k = lane; k < a.nlags; k += 32) rout[k] += fold_lag(my, k);
+  for (int k = lane; k < a.nlags; k += 32) rout[k] += fold_lag(my, k, lane);
 }
 
 }  // namespace fdlp
