@@ -162,6 +162,7 @@ constexpr int kFoldStride = 64;  // doubles per slot
 __host__ __device__ constexpr int fold_smem_doubles(int na) { return (na + 1) * kFoldStride; }
 
 __device__ __forceinline__ void prefetch_l1(const void* ptr) { asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr)); }
+__device__ __forceinline__ void prefetch_l2(const void* ptr) { asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr)); }
 
 template <int NA>
 __device__ __forceinline__ void fold_store_tiles(const double (&acc)[NA][2], double* my, int lane) {
@@ -267,88 +268,61 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel
 
 // ---- per-band combination of the family block sums ----
 // Band j takes, from family g, the blocks [a, b) that lie inside one region of its filter.  For the lower
-// skirt a = 0 for every band and for the upper skirt b is the common last block, so the sums are running
+// skirt a = 0 for every band and for the upper skirt b is the common last block, so those sums are running
 // (prefix / suffix) sums over the blocks, accumulated from the far, small end of the skirt towards the pass
-// band -- pure additions in a fixed order, no differences of partial sums.  The pass band is a short range.
+// band -- pure additions in a fixed order, no differences of partial sums.  family_scan_kernel turns P into
+// these running sums in place; the pass band is a short range of per-block values.  The per-band gather
+// (one running-sum vector per skirt + the pass-band blocks) happens in the epilogue of autocorr_ranges_kernel.
 constexpr int kCombRange = 0, kCombPrefix = 1, kCombSuffix = 2;
 constexpr int kCombMaxFam = 3;
 
-struct CombArgs {
-  const double* p;        // [n_seg, nfam, nblk, nlags]
-  double* r;              // [n_seg, J, nlags]  (written)
-  const int32_t* order;   // [nfam, J] bands with a non-empty range, in emission order
-  const int32_t* ra;      // [nfam, J] first block of the band's range
-  const int32_t* rb;      // [nfam, J] one past the last block
-  const double* wsq;      // [J, nfam] squared template weights
+struct ScanArgs {
+  double* p;                   // [n_seg, nfam, nblk, nlags], scanned in place for prefix / suffix families
   int32_t mode[kCombMaxFam];   // kComb*
-  int32_t nband[kCombMaxFam];  // entries of order[g]
   int32_t end[kCombMaxFam];    // suffix mode: common end block
-  int n_seg, J, nfam, nblk, nlags;
+  int32_t scan_fam[kCombMaxFam];  // families that need a scan
+  int n_scan, n_seg, nfam, nblk, nlags;
 };
 
-// One CTA per segment, one thread per lag; the thread owns column k of the [J, nlags] result staged in
-// shared memory, so no barrier is needed.
-__global__ void __launch_bounds__(160) family_combine_kernel(const CombArgs a) {
-  extern __shared__ __align__(16) double rs[];  // [J][nlags]
-  const int seg = blockIdx.x;
+// grid (n_seg * n_scan), one thread per lag
+__global__ void __launch_bounds__(160) family_scan_kernel(const ScanArgs a) {
   const int k = threadIdx.x;
   if (k >= a.nlags) return;
-  for (int j = 0; j < a.J; ++j) rs[j * a.nlags + k] = 0.0;
+  const int seg = blockIdx.x / a.n_scan;
+  const int which = blockIdx.x % a.n_scan;
+  int g = a.scan_fam[0], mode = a.mode[0], end = a.end[0];
 #pragma unroll
-  for (int g = 0; g < kCombMaxFam; ++g) {
-    if (g >= a.nfam) break;
-    const double* pg = a.p + (((size_t)seg * a.nfam + g) * a.nblk) * a.nlags + k;
-    const int32_t* ord = a.order + g * a.J;
-    const int32_t* ra = a.ra + g * a.J;
-    const int32_t* rb = a.rb + g * a.J;
-    const int nb = a.nband[g];
-    if (a.mode[g] == kCombPrefix) {
-      double run = 0.0;
-      int idx = 0;
-      for (int m0 = 0; m0 <= a.nblk; m0 += 8) {
-        double v[8];
+  for (int i = 1; i < kCombMaxFam; ++i)
+    if (which == i) { g = a.scan_fam[i]; }
 #pragma unroll
-        for (int u = 0; u < 8; ++u) v[u] = (m0 + u < a.nblk) ? __ldg(pg + (size_t)(m0 + u) * a.nlags) : 0.0;
+  for (int i = 0; i < kCombMaxFam; ++i)
+    if (g == i) { mode = a.mode[i]; end = a.end[i]; }
+  double* pg = a.p + (((size_t)seg * a.nfam + g) * a.nblk) * a.nlags + k;
+  const size_t st = a.nlags;
+  double run = 0.0;
+  if (mode == kCombPrefix) {
+    for (int m0 = 0; m0 < a.nblk; m0 += 8) {
+      double v[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int m = m0 + u;
-          while (idx < nb && rb[ord[idx]] == m) {
-            const int j = ord[idx];
-            rs[j * a.nlags + k] = fma(__ldg(a.wsq + (size_t)j * a.nfam + g), run, rs[j * a.nlags + k]);
-            ++idx;
-          }
-          run += v[u];
-        }
+      for (int u = 0; u < 8; ++u) v[u] = (m0 + u < a.nblk) ? pg[(size_t)(m0 + u) * st] : 0.0;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        run += v[u];
+        if (m0 + u < a.nblk) pg[(size_t)(m0 + u) * st] = run;
       }
-    } else if (a.mode[g] == kCombSuffix) {
-      double run = 0.0;
-      int idx = 0;
-      for (int m0 = a.end[g] - 1; m0 >= 0; m0 -= 8) {
-        double v[8];
+    }
+  } else {
+    for (int m0 = end - 1; m0 >= 0; m0 -= 8) {
+      double v[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) v[u] = (m0 - u >= 0) ? __ldg(pg + (size_t)(m0 - u) * a.nlags) : 0.0;
+      for (int u = 0; u < 8; ++u) v[u] = (m0 - u >= 0) ? pg[(size_t)(m0 - u) * st] : 0.0;
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int m = m0 - u;
-          run += v[u];
-          while (idx < nb && ra[ord[idx]] == m) {
-            const int j = ord[idx];
-            rs[j * a.nlags + k] = fma(__ldg(a.wsq + (size_t)j * a.nfam + g), run, rs[j * a.nlags + k]);
-            ++idx;
-          }
-        }
-      }
-    } else {
-      for (int idx = 0; idx < nb; ++idx) {
-        const int j = ord[idx];
-        double sum = 0.0;
-        for (int m = ra[j]; m < rb[j]; ++m) sum += __ldg(pg + (size_t)m * a.nlags);
-        rs[j * a.nlags + k] = fma(__ldg(a.wsq + (size_t)j * a.nfam + g), sum, rs[j * a.nlags + k]);
+      for (int u = 0; u < 8; ++u) {
+        run += v[u];
+        if (m0 - u >= 0) pg[(size_t)(m0 - u) * st] = run;
       }
     }
   }
-  double* rout = a.r + (size_t)seg * a.J * a.nlags + k;
-  for (int j = 0; j < a.J; ++j) rout[(size_t)j * a.nlags] = rs[j * a.nlags + k];
 }
 
 // ---- direct per-band kernel restricted to row ranges (blocks that straddle a region boundary) ----
@@ -359,8 +333,15 @@ struct AcRangeArgs {
   const double* fbank;   // [J, ld]
   const int32_t* nrng;   // [J] number of row ranges of the band
   const int32_t* rng;    // [J, kMaxRanges, 2] (row_lo, row_hi), multiples of 4 rows
-  double* r;             // [n_seg, J, nlags]  (ADDED to)
+  double* r;             // [n_seg, J, nlags]  (written: direct remainder + family terms)
   int J, nlags, n_seg, ld;
+  // family terms gathered in the epilogue
+  const double* p;       // [n_seg, nfam, nblk, nlags] block sums (prefix / suffix families already scanned)
+  const int32_t* ra;     // [nfam, J] first block of the band's range
+  const int32_t* rb;     // [nfam, J] one past the last block
+  const double* wsq;     // [J, nfam] squared template weights
+  int32_t mode[kCombMaxFam];
+  int nfam, nblk;
 };
 
 template <int NA>
@@ -374,7 +355,23 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
   const int band = (blockIdx.x % nbg) * kAcWarps + warp;
   if (band >= a.J) return;
   const int nr = a.nrng[band];
-  if (nr == 0) return;
+  // the family terms gathered in the epilogue live in HBM: start pulling their lines into L2 now
+  {
+    const int lines = (a.nlags * 8 + 127) / 128;
+#pragma unroll
+    for (int g = 0; g < kCombMaxFam; ++g) {
+      if (g < a.nfam) {
+        const int b0 = a.ra[g * a.J + band], b1 = a.rb[g * a.J + band];
+        if (b1 > b0) {
+          const double* pg = a.p + (((size_t)seg * a.nfam + g) * a.nblk) * a.nlags;
+          const int r0 = (a.mode[g] == kCombPrefix) ? b1 - 1 : b0;
+          const int nrow = (a.mode[g] == kCombRange) ? b1 - b0 : 1;
+          for (int idx = lane; idx < nrow * lines; idx += 32)
+            prefetch_l2(pg + (size_t)(r0 + idx / lines) * a.nlags + (idx % lines) * 16);
+        }
+      }
+    }
+  }
   const int lr = lane & 3, lc = lane >> 2;
   const int lane_off = (lr << 3) + lc;
 
@@ -424,7 +421,32 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
   fold_store_tiles<NA>(acc, my, lane);
   __syncwarp();
   double* rout = a.r + ((size_t)seg * a.J + band) * a.nlags;
-  for (int k = lane; k < a.nlags; k += 32) rout[k] += fold_lag(my, k, lane);
+  for (int k = lane; k < a.nlags; k += 32) {
+    double val = fold_lag(my, k, lane);
+#pragma unroll
+    for (int g = 0; g < kCombMaxFam; ++g) {
+      if (g < a.nfam) {
+        const int b0 = a.ra[g * a.J + band], b1 = a.rb[g * a.J + band];
+        if (b1 > b0) {
+          const double* pg = a.p + (((size_t)seg * a.nfam + g) * a.nblk) * a.nlags + k;
+          double t;
+          if (a.mode[g] == kCombPrefix) t = pg[(size_t)(b1 - 1) * a.nlags];
+          else if (a.mode[g] == kCombSuffix) t = pg[(size_t)b0 * a.nlags];
+          else {
+            t = 0.0;
+            for (int m = b0; m < b1; m += 8) {
+              double v[8];
+#pragma unroll
+              for (int u = 0; u < 8; ++u) v[u] = (m + u < b1) ? pg[(size_t)(m + u) * a.nlags] : 0.0;
+              t += ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+            }
+          }
+          val = fma(a.wsq[(size_t)band * a.nfam + g], t, val);
+        }
+      }
+    }
+    rout[k] = val;
+  }
 }
 
 }  // namespace fdlp

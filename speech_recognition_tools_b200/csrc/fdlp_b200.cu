@@ -367,7 +367,7 @@ static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, cons
   p->g.direct_taps = direct_taps;
   p->g.nfam = nfam;
   p->g.block_len = blk_len;
-  p->fam_ok = p->g.nlags <= 160 && p->comb_smem <= 200 * 1024;
+  p->fam_ok = p->g.nlags <= 160;
   return 0;
 }
 
@@ -558,7 +558,6 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
       default: p->fam_ok = false;
     }
 #undef SET_FAM
-    SET_SMEM(family_combine_kernel, p->comb_smem);
   }
 #undef SET_SMEM
   {
@@ -671,11 +670,15 @@ static int launch_autocorr_family(fdlp_plan* p, const double* dct, int n_seg, do
   d.J = p->prm.nfilters; d.nlags = p->g.nlags; d.n_seg = n_seg; d.ld = p->ld;
   const int nbg = (d.J + kAcWarps - 1) / kAcWarps;
   const dim3 gridD((unsigned)((size_t)n_seg * nbg));
-  CombArgs c;
-  c.p = p->d_p; c.r = r; c.order = p->d_order; c.ra = p->d_ra; c.rb = p->d_rb; c.wsq = p->d_wsq;
-  for (int g = 0; g < kCombMaxFam; ++g) { c.mode[g] = p->comb_mode[g]; c.nband[g] = p->comb_nband[g]; c.end[g] = p->comb_end[g]; }
-  c.n_seg = n_seg; c.J = p->prm.nfilters; c.nfam = p->nfam; c.nblk = p->nblk; c.nlags = p->g.nlags;
-  const dim3 gridC(n_seg), blockC(160);
+  d.p = p->d_p; d.ra = p->d_ra; d.rb = p->d_rb; d.wsq = p->d_wsq; d.nfam = p->nfam; d.nblk = p->nblk;
+  ScanArgs c;
+  c.p = p->d_p; c.n_scan = 0; c.n_seg = n_seg; c.nfam = p->nfam; c.nblk = p->nblk; c.nlags = p->g.nlags;
+  for (int g = 0; g < kCombMaxFam; ++g) {
+    c.mode[g] = p->comb_mode[g]; c.end[g] = p->comb_end[g]; c.scan_fam[g] = 0; d.mode[g] = p->comb_mode[g];
+  }
+  for (int g = 0; g < p->nfam; ++g)
+    if (p->comb_mode[g] != kCombRange && p->comb_nband[g] > 0) c.scan_fam[c.n_scan++] = g;
+  const dim3 gridC((unsigned)((size_t)n_seg * std::max(c.n_scan, 1))), blockC(160);
 #define RUN_FAM_A(NA_) case NA_: family_block_autocorr_kernel<NA_><<<gridA, block, p->fam_smem, st>>>(f); break;
 #define RUN_FAM_D(NA_) case NA_: autocorr_ranges_kernel<NA_><<<gridD, block, p->fam_smem, st>>>(d); break;
   switch (p->na) {
@@ -684,7 +687,7 @@ static int launch_autocorr_family(fdlp_plan* p, const double* dct, int n_seg, do
   }
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev_ac[1], st));
-  family_combine_kernel<<<gridC, blockC, p->comb_smem, st>>>(c);
+  if (c.n_scan > 0) family_scan_kernel<<<gridC, blockC, 0, st>>>(c);
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev_ac[2], st));
   switch (p->na) {
