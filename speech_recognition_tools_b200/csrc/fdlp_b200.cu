@@ -716,8 +716,17 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
   // every chunk starts on a multiple of 8 tasks (chunk boundaries are whole segments, J tasks each, padded below)
   a.ms = p->d_ms + (task0 + 7) / 8 * 8 * p->Lp;
   a.status = status; a.seg_utt = seg_utt;
-  const int tpc = p->lpc_threads / kLpcGroup;
-  lpc_cepstrum_kernel<<<(a.n_tasks + tpc - 1) / tpc, p->lpc_threads, p->lpc_smem, st>>>(a);
+  // register-resident kernel when the order and the cepstrum length fit 8 lanes x NS slots, else shared memory
+  const int need = std::max(p->prm.order + 1, p->g.L);
+  static const bool force_smem = getenv("FDLP_LPC_SMEM") != nullptr;
+  if (need <= 64 && !force_smem) {
+    lpc_cepstrum_reg_kernel<8><<<(a.n_tasks + 15) / 16, 128, 0, st>>>(a);
+  } else if (need <= 160 && !force_smem) {
+    lpc_cepstrum_reg_kernel<20><<<(a.n_tasks + 15) / 16, 128, 0, st>>>(a);
+  } else {
+    const int tpc = p->lpc_threads / kLpcGroup;
+    lpc_cepstrum_kernel<<<(a.n_tasks + tpc - 1) / tpc, p->lpc_threads, p->lpc_smem, st>>>(a);
+  }
   FDLP_CUDA(cudaGetLastError());
   EnvArgs e;
   e.ms = a.ms; e.basis = p->d_basis; e.wratio = p->d_wratio; e.env = env;

@@ -165,6 +165,129 @@ __global__ void __launch_bounds__(kLpcMaxThreads) lpc_cepstrum_kernel(const LpcA
 }
 
 // ---------------------------------------------------------------------------------------------------
+// K4, register-resident variant (orders up to 8*NS - 2, L <= 8*NS): the shared-memory kernel above is bound by
+// shared-memory bandwidth (every order reads and writes the whole coefficient vector and reads r).  Here the
+// 8 lanes of a group hold everything in registers, element i in lane i%8, slot i/8, and the Levinson step is
+// written with the forward vector f_i = a_i and the backward vector b_i = a_{m-i}:
+//     sb = shift(b) (sb_i = b_{i-1});  f' = f + k sb;  b' = sb + k f;  acc_{m+1} = sum_j b'_j r[j+1]
+// so nothing is ever reversed: the shift is one lane rotation per slot (lane 0 takes the previous slot) and
+// r[j+1] sits at a FIXED element index, i.e. in registers too.  The LPC->cepstrum recursion uses the same
+// rotation on y_m = x[n-m].  The slot loops are unrolled per phase (orders 8S..8S+7 touch slots 0..S).
+template <int NS>
+__global__ void __launch_bounds__(128) lpc_cepstrum_reg_kernel(const LpcArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int g = lane & 7;
+  const int gbase = lane & ~7;
+  const int src_prev = gbase | ((g + 7) & 7);  // lane holding element i-1
+  const int p = a.order, L = a.L;
+  int task = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+  const bool live = task < a.n_tasks;
+  if (!live) task = a.n_tasks - 1;  // idle groups shadow the last task (keeps the shuffles uniform)
+
+  const double* rg = a.r + (size_t)task * a.nlags;
+  double f[NS], b[NS], rr[NS];
+#pragma unroll
+  for (int s = 0; s < NS; ++s) {
+    const int i = 8 * s + g;
+    rr[s] = (i + 1 < a.nlags) ? __ldg(rg + i + 1) : 0.0;
+    f[s] = 0.0;
+    b[s] = 0.0;
+  }
+  const double r0 = __ldg(rg);
+  if (g == 0) { f[0] = 1.0; b[0] = 1.0; }
+
+  // ---- Levinson-Durbin ----
+  double E = r0;
+  int bad = 0;
+  double acc = __shfl_sync(0xffffffffu, rr[0], gbase);  // r[1]
+#pragma unroll
+  for (int S = 0; S < NS; ++S) {
+    const int m_lo = (8 * S > 1) ? 8 * S : 1;
+    const int m_hi = (8 * S + 7 < p) ? 8 * S + 7 : p;
+    for (int m = m_lo; m <= m_hi; ++m) {
+      if (E == 0.0 || !isfinite(E)) bad = FDLP_ST_SINGULAR;
+      const double k = -acc * __drcp_rn(E);
+      double part = 0.0;
+      double t_hi = __shfl_sync(0xffffffffu, b[S], src_prev);
+#pragma unroll
+      for (int s = S; s >= 0; --s) {
+        const double t_lo = (s > 0) ? __shfl_sync(0xffffffffu, b[s - 1], src_prev) : 0.0;
+        const double sb = (g == 0) ? t_lo : t_hi;
+        const double fo = f[s];
+        f[s] = fma(k, sb, fo);
+        const double nb = fma(k, fo, sb);
+        b[s] = nb;
+        part = fma(nb, rr[s], part);
+        t_hi = t_lo;
+      }
+      acc = group_sum8(part);
+      E *= (1.0 - k * k);
+    }
+  }
+
+  // ---- gain: gg = r[0] + sum_{i=0..p} a[i] * r[i+1]  (features.py:228) ----
+  double gpart = 0.0;
+#pragma unroll
+  for (int s = 0; s < NS; ++s) gpart = fma(f[s], rr[s], gpart);
+  const double gg = r0 + group_sum8(gpart);
+  if (!(gg > 0.0) || !isfinite(gg)) bad |= FDLP_ST_NONFINITE;
+  if (live) {
+    if (a.lpc_out) {
+#pragma unroll
+      for (int s = 0; s < NS; ++s)
+        if (8 * s + g <= p) a.lpc_out[(size_t)task * (p + 1) + 8 * s + g] = f[s];
+    }
+    if (a.gain_out && g == 0) a.gain_out[task] = gg;
+  }
+
+  // ---- LPC -> cepstrum (features.py:233-246): x[i] = -a[i] (i >= 1), zero beyond the order ----
+  // mc[s]: m * cep[m] at element m (element 0 stays 0);  y[s]: y_m = x[n - m], rotated by one element per n
+  double* msg = a.ms + (size_t)task * a.Lp;
+#pragma unroll
+  for (int s = 0; s < NS; ++s) { f[s] = -f[s]; b[s] = 0.0; rr[s] = 0.0; }  // f := x, b := y, rr := mc
+  const double c0 = log(sqrt(gg));
+  const double c1 = (L > 1) ? __shfl_sync(0xffffffffu, f[0], gbase | 1) : 0.0;  // x[1]
+  if (g == 1) rr[0] = c1;  // 1 * cep[1]
+  if (g == 0) b[0] = c1;   // y^(1): element 0 = x[1]
+  if (g == 0 && live) {
+    msg[0] = c0 * a.weights[0];
+    if (L > 1) msg[1] = c1 * a.weights[1];
+    if (a.cep_out) { a.cep_out[(size_t)task * L] = c0; if (L > 1) a.cep_out[(size_t)task * L + 1] = c1; }
+  }
+#pragma unroll
+  for (int S = 0; S < NS; ++S) {
+    const int n_lo = (8 * S > 2) ? 8 * S : 2;
+    const int n_hi = (8 * S + 7 < L - 1) ? 8 * S + 7 : L - 1;
+    for (int n = n_lo; n <= n_hi; ++n) {
+      const double xn = (n <= p) ? __shfl_sync(0xffffffffu, f[S], gbase | (n & 7)) : 0.0;
+      double part = 0.0;
+      double t_hi = __shfl_sync(0xffffffffu, b[S], src_prev);
+#pragma unroll
+      for (int s = S; s >= 0; --s) {
+        const double t_lo = (s > 0) ? __shfl_sync(0xffffffffu, b[s - 1], src_prev) : 0.0;
+        double y = (g == 0) ? t_lo : t_hi;
+        if (s == 0 && g == 0) y = xn;  // element 0 of y^(n) is x[n]
+        b[s] = y;
+        part = fma(rr[s], y, part);
+        t_hi = t_lo;
+      }
+      const double v = fma(group_sum8(part), __ldg(a.inv_n + n), xn);
+      if (g == (n & 7)) rr[S] = v * (double)n;
+      if (g == 0 && live) {
+        msg[n] = v * __ldg(a.weights + n);
+        if (a.cep_out) a.cep_out[(size_t)task * L + n] = v;
+      }
+    }
+  }
+  if (live && g == 0) for (int n = L; n < a.Lp; ++n) msg[n] = 0.0;
+
+  if (bad && live && a.status && g == 0) {
+    const int seg = task / a.J;
+    atomicOr(a.status + (a.seg_utt ? a.seg_utt[seg] : seg), bad);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
 // K5: env[task, t] = exp( sum_n ms[task, n] * cos(2 pi n t / M) ) * wratio[t],  t < kk
 // One warp owns 8 tasks (the DMMA M dimension) and NT blocks of 8 output frames; the cosine basis
 // B[n][t] is a plan table ([Lp, ldb], zero rows beyond L) read through L1/L2.
