@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(kLpcMaxThreads) lpc_cepstrum_kernel(const LpcA
 // r[j+1] sits at a FIXED element index, i.e. in registers too.  The LPC->cepstrum recursion uses the same
 // rotation on y_m = x[n-m].  The slot loops are unrolled per phase (orders 8S..8S+7 touch slots 0..S).
 template <int NS>
-__global__ void __launch_bounds__(128) lpc_cepstrum_reg_kernel(const LpcArgs a) {
+__global__ void __launch_bounds__(128, (NS > 8) ? 3 : 5) lpc_cepstrum_reg_kernel(const LpcArgs a) {
   const int lane = threadIdx.x & 31;
   const int g = lane & 7;
   const int gbase = lane & ~7;
@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(128) lpc_cepstrum_reg_kernel(const LpcArgs a) 
     for (int m = m_lo; m <= m_hi; ++m) {
       if (E == 0.0 || !isfinite(E)) bad = FDLP_ST_SINGULAR;
       const double k = -acc * __drcp_rn(E);
-      double part = 0.0;
+      double part = 0.0, part1 = 0.0;
       double t_hi = __shfl_sync(0xffffffffu, b[S], src_prev);
 #pragma unroll
       for (int s = S; s >= 0; --s) {
@@ -217,10 +217,11 @@ __global__ void __launch_bounds__(128) lpc_cepstrum_reg_kernel(const LpcArgs a) 
         f[s] = fma(k, sb, fo);
         const double nb = fma(k, fo, sb);
         b[s] = nb;
-        part = fma(nb, rr[s], part);
+        if (s & 1) part1 = fma(nb, rr[s], part1);
+        else part = fma(nb, rr[s], part);
         t_hi = t_lo;
       }
-      acc = group_sum8(part);
+      acc = group_sum8(part + part1);
       E *= (1.0 - k * k);
     }
   }
@@ -260,7 +261,7 @@ __global__ void __launch_bounds__(128) lpc_cepstrum_reg_kernel(const LpcArgs a) 
     const int n_hi = (8 * S + 7 < L - 1) ? 8 * S + 7 : L - 1;
     for (int n = n_lo; n <= n_hi; ++n) {
       const double xn = (n <= p) ? __shfl_sync(0xffffffffu, f[S], gbase | (n & 7)) : 0.0;
-      double part = 0.0;
+      double part = 0.0, part1 = 0.0;
       double t_hi = __shfl_sync(0xffffffffu, b[S], src_prev);
 #pragma unroll
       for (int s = S; s >= 0; --s) {
@@ -268,10 +269,11 @@ __global__ void __launch_bounds__(128) lpc_cepstrum_reg_kernel(const LpcArgs a) 
         double y = (g == 0) ? t_lo : t_hi;
         if (s == 0 && g == 0) y = xn;  // element 0 of y^(n) is x[n]
         b[s] = y;
-        part = fma(rr[s], y, part);
+        if (s & 1) part1 = fma(rr[s], y, part1);
+        else part = fma(rr[s], y, part);
         t_hi = t_lo;
       }
-      const double v = fma(group_sum8(part), __ldg(a.inv_n + n), xn);
+      const double v = fma(group_sum8(part + part1), __ldg(a.inv_n + n), xn);
       if (g == (n & 7)) rr[S] = v * (double)n;
       if (g == 0 && live) {
         msg[n] = v * __ldg(a.weights + n);
