@@ -245,6 +245,7 @@ def run_ours(args):
     ex.set_profiling(True)
     stage = {"dct": 0.0, "autocorr": 0.0, "lpc_env": 0.0, "ola": 0.0}
     ac_ms = {"family_blocks": 0.0, "combine": 0.0, "direct": 0.0}
+    kms = {}
     nprof = 5
     for _ in range(nprof):
         step_resident()
@@ -254,6 +255,8 @@ def run_ours(args):
         s = ex.autocorr_ms()
         for k in ac_ms:
             ac_ms[k] += s[k] / nprof
+        for k, v in ex.kernel_ms().items():
+            kms[k] = kms.get(k, 0.0) + v / nprof
     ex.set_profiling(False)
 
     out = None
@@ -273,11 +276,12 @@ def run_ours(args):
         nseg = lay.n_seg
         kern = {}
         if g["nfam"] > 0:
-            kern["family_block_autocorr_kernel"] = (ac_ms["family_blocks"], 2.0 * g["nlags"] * g["family_taps"] * nseg)
-            kern["autocorr_ranges_kernel"] = (ac_ms["direct"], 2.0 * g["nlags"] * g["direct_taps"] * nseg)
+            kern["family_block_autocorr_kernel"] = (kms["family_block_autocorr_kernel"], 2.0 * g["nlags"] * g["family_taps"] * nseg)
+            kern["autocorr_ranges_kernel"] = (kms["autocorr_direct"], 2.0 * g["nlags"] * g["direct_taps"] * nseg)
         else:
-            kern["autocorr_dmma_kernel"] = (stage["autocorr"], 2.0 * g["nlags"] * g["support_taps"] * nseg)
-        kern["lpc_cepstrum_kernel+envelope_dmma_kernel"] = (stage["lpc_env"], (2.0 * p_ * p_ + 1.5 * L_ * L_ + 2.0 * L_ * kk_) * J * nseg)
+            kern["autocorr_dmma_kernel"] = (kms["autocorr_direct"], 2.0 * g["nlags"] * g["support_taps"] * nseg)
+        kern["lpc_cepstrum_reg_kernel"] = (kms["lpc_cepstrum"], (2.0 * p_ * p_ + 1.5 * L_ * L_) * J * nseg)
+        kern["envelope_dmma_kernel"] = (kms["envelope_dmma_kernel"], 2.0 * L_ * kk_ * J * nseg)
         top = max(kern, key=lambda k: kern[k][0])
         top_ms, top_flops = kern[top]
         achieved = top_flops / (top_ms * 1e-3) / 1e12
@@ -293,7 +297,7 @@ def run_ours(args):
                     "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                     "traffic": traffic, "peak_source": "fdlp_measure_fp64_peak, measured live on this GPU "
                     "(MEASURED_PEAKS.json has no FP64 entry); dfma=%.2f dmma=%.2f" % (dfma.value, dmma.value),
-                    "algorithmic_flops_per_launch": top_flops, "kernel_ms": top_ms,
+                    "algorithmic_flops_per_launch": top_flops, "top_kernel_ms": top_ms,
                     "kernels": {k: {"ms": v[0], "algorithmic_tflops": v[1] / (v[0] * 1e-3) / 1e12 if v[0] > 0 else None,
                                     "frac": (v[1] / (v[0] * 1e-3) / 1e12 / peak) if v[0] > 0 else None}
                                 for k, v in kern.items()},
@@ -302,7 +306,7 @@ def run_ours(args):
                                  "per_band_equivalent_tflops": ac_flops_support / (stage["autocorr"] * 1e-3) / 1e12,
                                  "note": "per-band-equivalent = flops a per-band direct evaluation over the filters' "
                                          "support would execute; the family decomposition shares most of them"},
-                    "stage_ms": stage, "share_of_step": top_ms / sum(stage.values())}
+                    "stage_ms": stage, "kernel_ms": kms, "share_of_step": top_ms / sum(stage.values())}
 
         # ---- mel-spectrogram baseline path on the same batch (BASELINE.json configs[1]) ----
         mel = MelExtractor(MelConfig(**MEL_RECIPE), device=dev)

@@ -152,6 +152,9 @@ int fdlp_plan_set_autocorr_mode(fdlp_plan* plan, int32_t mode);
 /* out3 = {family block sums, per-band combination, direct per-band kernel} in ms for the most recent
  * profiled fdlp_forward */
 int fdlp_plan_get_autocorr_ms(fdlp_plan* plan, float* out3);
+/* out7 = per-kernel ms of the most recent profiled fdlp_forward: {framing+DCT, family block sums, family scan,
+ * direct per-band autocorrelation (+ family gather), LPC+cepstrum, envelope, overlap-add+log} */
+int fdlp_plan_get_kernel_ms(fdlp_plan* plan, float* out7);
 
 /* stage-level entry points (used by the parity tests to check each kernel against the oracle;
  * they run the same kernels fdlp_forward launches, on the plan's scratch) */

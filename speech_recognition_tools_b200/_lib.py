@@ -75,6 +75,7 @@ SYMBOLS = [
     ("fdlp_plan_get_stage_ms", C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     ("fdlp_plan_set_autocorr_mode", C.c_int, [C.c_void_p, C.c_int32]),
     ("fdlp_plan_get_autocorr_ms", C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    ("fdlp_plan_get_kernel_ms", C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     ("fdlp_stage_dct", C.c_int, [C.c_void_p, C.POINTER(FdlpBatch), C.c_void_p, C.c_void_p]),
     ("fdlp_stage_autocorr", C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     ("fdlp_stage_lpc_envelope", C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -181,6 +181,7 @@ struct fdlp_plan {
   int32_t *d_order = nullptr, *d_ra = nullptr, *d_rb = nullptr, *d_nrng = nullptr, *d_rng = nullptr;
   int cap_seg_p = 0;
   cudaEvent_t ev_ac[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_lpc = nullptr;  // between the LPC/cepstrum kernel and the envelope kernel
   // scratch (grow-only)
   int cap_seg = 0, cap_utt = 0;
   double *d_dct = nullptr, *d_r = nullptr, *d_env = nullptr, *d_alpha = nullptr, *d_ms = nullptr;
@@ -204,6 +205,7 @@ static void plan_free(fdlp_plan* p) {
   cudaFree(p->d_tmpl); cudaFree(p->d_wsq); cudaFree(p->d_p);
   cudaFree(p->d_order); cudaFree(p->d_ra); cudaFree(p->d_rb); cudaFree(p->d_nrng); cudaFree(p->d_rng);
   for (int i = 0; i < 4; ++i) if (p->ev_ac[i]) cudaEventDestroy(p->ev_ac[i]);
+  if (p->ev_lpc) cudaEventDestroy(p->ev_lpc);
   for (int i = 0; i < 5; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
   for (int i = 0; i < kMaxChunks; ++i) if (p->ev_chunk[i]) cudaEventDestroy(p->ev_chunk[i]);
   if (p->ev_start) cudaEventDestroy(p->ev_start);
@@ -728,6 +730,7 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
     lpc_cepstrum_kernel<<<(a.n_tasks + tpc - 1) / tpc, p->lpc_threads, p->lpc_smem, st>>>(a);
   }
   FDLP_CUDA(cudaGetLastError());
+  if (p->profiling && p->ev_lpc) FDLP_CUDA(cudaEventRecord(p->ev_lpc, st));
   EnvArgs e;
   e.ms = a.ms; e.basis = p->d_basis; e.wratio = p->d_wratio; e.env = env;
   e.n_tasks = a.n_tasks; e.Lp = p->Lp; e.ldb = p->ldb; e.kk = p->g.kk;
@@ -823,6 +826,7 @@ extern "C" int fdlp_plan_set_profiling(fdlp_plan* p, int32_t enable) {
   if (enable && !p->ev[0]) {
     for (int i = 0; i < 5; ++i) FDLP_CUDA(cudaEventCreate(&p->ev[i]));
     for (int i = 0; i < 4; ++i) FDLP_CUDA(cudaEventCreate(&p->ev_ac[i]));
+    FDLP_CUDA(cudaEventCreate(&p->ev_lpc));
   }
   p->profiling = enable != 0;
   return FDLP_OK;
@@ -850,6 +854,22 @@ extern "C" int fdlp_plan_get_autocorr_ms(fdlp_plan* p, float* out3) {
   } else {
     FDLP_CUDA(cudaEventElapsedTime(&out3[2], p->ev[1], p->ev[2]));
   }
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_plan_get_kernel_ms(fdlp_plan* p, float* out7) {
+  if (!p || !out7 || !p->ev[0]) return set_err(FDLP_E_ARG, "profiling was not enabled%s", "");
+  for (int i = 0; i < 7; ++i) out7[i] = 0.f;
+  FDLP_CUDA(cudaEventSynchronize(p->ev[4]));
+  FDLP_CUDA(cudaEventElapsedTime(&out7[0], p->ev[0], p->ev[1]));
+  if (p->fam_ok && p->ac_mode == 0) {
+    for (int i = 0; i < 3; ++i) FDLP_CUDA(cudaEventElapsedTime(&out7[1 + i], p->ev_ac[i], p->ev_ac[i + 1]));
+  } else {
+    FDLP_CUDA(cudaEventElapsedTime(&out7[3], p->ev[1], p->ev[2]));
+  }
+  FDLP_CUDA(cudaEventElapsedTime(&out7[4], p->ev[2], p->ev_lpc));
+  FDLP_CUDA(cudaEventElapsedTime(&out7[5], p->ev_lpc, p->ev[3]));
+  FDLP_CUDA(cudaEventElapsedTime(&out7[6], p->ev[3], p->ev[4]));
   return FDLP_OK;
 }
 

@@ -313,6 +313,15 @@ class FdlpExtractor:
         L.check(self._lib.fdlp_plan_get_autocorr_ms(self._plan, out))
         return dict(family_blocks=out[0], combine=out[1], direct=out[2])
 
+    KERNELS = ("dct_segments_kernel", "family_block_autocorr_kernel", "family_scan_kernel", "autocorr_direct",
+               "lpc_cepstrum", "envelope_dmma_kernel", "ola_log_kernel")
+
+    def kernel_ms(self):
+        """Per-kernel CUDA-event durations of the most recent profiled forward, keyed by KERNELS."""
+        out = (C.c_float * 7)()
+        L.check(self._lib.fdlp_plan_get_kernel_ms(self._plan, out))
+        return dict(zip(self.KERNELS, [float(v) for v in out]))
+
     def stage_ms(self):
         """Per-stage CUDA-event durations of the most recent forward (needs set_profiling(True))"""
         out = (C.c_float * 4)()
