@@ -164,27 +164,42 @@ __host__ __device__ constexpr int fold_smem_doubles(int na) { return (na + 1) * 
 __device__ __forceinline__ void prefetch_l1(const void* ptr) { asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr)); }
 __device__ __forceinline__ void prefetch_l2(const void* ptr) { asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr)); }
 
-template <int NA>
-__device__ __forceinline__ void fold_store_tiles(const double (&acc)[NA][2], double* my, int lane) {
+// Lane-constant shared-memory addresses of the fold, computed once per kernel so that every store and load of
+// a flush is [register + immediate].  Loads are 16-byte pairs; the pair order is rotated per lane
+// ((u + (lane >> 1)) & 3), which spreads the 32 rows of an instruction over all banks (4 wavefronts for 512 B).
+struct FoldCtx {
+  double* s0;          // store address of acc[.][0] in slot 0
+  double* s1;          // store address of acc[.][1] in slot 0
+  const double2* q[4]; // load addresses of the 4 pairs of lag `lane`
+};
+
+__device__ __forceinline__ FoldCtx fold_ctx(double* my, int lane) {
   const int lr = lane & 3, lc = lane >> 2;
   const int c0 = 2 * lr, c1 = 2 * lr + 1;
   const int d0 = (c0 - lc) & 7, d1 = (c1 - lc) & 7;
-  const int o0 = ((c0 >= lc) ? kFoldStride : 0) + (d0 << 3) + (lc ^ (d0 >> 1));
-  const int o1 = ((c1 >= lc) ? kFoldStride : 0) + (d1 << 3) + (lc ^ (d1 >> 1));
+  FoldCtx f;
+  f.s0 = my + ((c0 >= lc) ? kFoldStride : 0) + (d0 << 3) + (lc ^ (d0 >> 1));
+  f.s1 = my + ((c1 >= lc) ? kFoldStride : 0) + (d1 << 3) + (lc ^ (d1 >> 1));
+  const double2* row = reinterpret_cast<const double2*>(my + kFoldStride + 8 * lane);  // lag k = lane: 8 (k + 8)
+  const int rot = (lane >> 1) & 3;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) f.q[u] = row + ((u + rot) & 3);
+  return f;
+}
+
+template <int NA>
+__device__ __forceinline__ void fold_store_tiles(const double (&acc)[NA][2], const FoldCtx& f) {
 #pragma unroll
   for (int i = 0; i < NA; ++i) {
-    my[i * kFoldStride + o0] = acc[i][0];
-    my[i * kFoldStride + o1] = acc[i][1];
+    f.s0[i * kFoldStride] = acc[i][0];
+    f.s1[i * kFoldStride] = acc[i][1];
   }
 }
 
-__device__ __forceinline__ double fold_lag(const double* my, int k, int lane) {
-  const double* q = my + ((k >> 3) + 1) * kFoldStride + ((k & 7) << 3);
-  const int rot = lane >> 2;
-  double v[8];
-#pragma unroll
-  for (int r = 0; r < 8; ++r) v[r] = q[(r + rot) & 7];
-  return ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+// lag k = lane + 32 t
+__device__ __forceinline__ double fold_lag(const FoldCtx& f, int t) {
+  const double2 v0 = f.q[0][t * 128], v1 = f.q[1][t * 128], v2 = f.q[2][t * 128], v3 = f.q[3][t * 128];
+  return ((v0.x + v0.y) + (v1.x + v1.y)) + ((v2.x + v2.y) + (v3.x + v3.y));
 }
 
 struct FamArgs {
@@ -229,7 +244,7 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel
 #pragma unroll
   for (int i = NA; i < RS; ++i) ring[i] = 0.0;
 
-  double* my = cs + (size_t)warp * fold_smem_doubles(NA);
+  const FoldCtx fc = fold_ctx(cs + (size_t)warp * fold_smem_doubles(NA), lane);
   int step = blk0 * spb;
   // the rows of c come from HBM (the templates stay in L1/L2): pull them into L1 two groups of U steps ahead
   const double* cpf = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + NA + 4 + 8 * U) * 8 + lane * 16;
@@ -258,10 +273,12 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel
       step += U;
     }
     // flush: C tiles -> shared (warp-private), diagonal sums -> P[seg][fam][blk][0..nlags)
-    fold_store_tiles<NA>(acc, my, lane);
+    fold_store_tiles<NA>(acc, fc);
     __syncwarp();
-    double* pout = a.p + (((size_t)seg * a.nfam + fam) * a.nblk + blk) * a.nlags;
-    for (int k = lane; k < a.nlags; k += 32) pout[k] = fold_lag(my, k, lane);
+    double* pout = a.p + (((size_t)seg * a.nfam + fam) * a.nblk + blk) * a.nlags + lane;
+#pragma unroll
+    for (int t = 0; t < NA / 4; ++t)
+      if (lane + 32 * t < a.nlags) pout[32 * t] = fold_lag(fc, t);
     __syncwarp();
   }
 }
@@ -417,12 +434,15 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
     }
   }
 
-  double* my = cs + (size_t)warp * fold_smem_doubles(NA);
-  fold_store_tiles<NA>(acc, my, lane);
+  const FoldCtx fc = fold_ctx(cs + (size_t)warp * fold_smem_doubles(NA), lane);
+  fold_store_tiles<NA>(acc, fc);
   __syncwarp();
   double* rout = a.r + ((size_t)seg * a.J + band) * a.nlags;
-  for (int k = lane; k < a.nlags; k += 32) {
-    double val = fold_lag(my, k, lane);
+#pragma unroll 1
+  for (int t = 0; t < NA / 4; ++t) {
+    const int k = lane + 32 * t;
+    if (k >= a.nlags) break;
+    double val = fold_lag(fc, t);
 #pragma unroll
     for (int g = 0; g < kCombMaxFam; ++g) {
       if (g < a.nfam) {
