@@ -438,35 +438,51 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
   fold_store_tiles<NA>(acc, fc);
   __syncwarp();
   double* rout = a.r + ((size_t)seg * a.J + band) * a.nlags;
-#pragma unroll 1
-  for (int t = 0; t < NA / 4; ++t) {
-    const int k = lane + 32 * t;
-    if (k >= a.nlags) break;
-    double val = fold_lag(fc, t);
+  constexpr int NT = NA / 4;  // lags per lane: k = lane + 32 t
+  double val[NT];
 #pragma unroll
-    for (int g = 0; g < kCombMaxFam; ++g) {
-      if (g < a.nfam) {
-        const int b0 = a.ra[g * a.J + band], b1 = a.rb[g * a.J + band];
-        if (b1 > b0) {
-          const double* pg = a.p + (((size_t)seg * a.nfam + g) * a.nblk) * a.nlags + k;
-          double t;
-          if (a.mode[g] == kCombPrefix) t = pg[(size_t)(b1 - 1) * a.nlags];
-          else if (a.mode[g] == kCombSuffix) t = pg[(size_t)b0 * a.nlags];
-          else {
-            t = 0.0;
-            for (int m = b0; m < b1; m += 8) {
-              double v[8];
+  for (int t = 0; t < NT; ++t) val[t] = fold_lag(fc, t);
+  // family terms: all loads of a family are issued together (independent addresses), then consumed
 #pragma unroll
-              for (int u = 0; u < 8; ++u) v[u] = (m + u < b1) ? pg[(size_t)(m + u) * a.nlags] : 0.0;
-              t += ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+  for (int g = 0; g < kCombMaxFam; ++g) {
+    if (g < a.nfam) {
+      const int b0 = a.ra[g * a.J + band], b1 = a.rb[g * a.J + band];
+      if (b1 > b0) {
+        const double w = a.wsq[(size_t)band * a.nfam + g];
+        const double* pg = a.p + (((size_t)seg * a.nfam + g) * a.nblk) * a.nlags + lane;
+        if (a.mode[g] != kCombRange) {
+          const double* row = pg + (size_t)((a.mode[g] == kCombPrefix) ? b1 - 1 : b0) * a.nlags;
+          double v[NT];
+#pragma unroll
+          for (int t = 0; t < NT; ++t) v[t] = (lane + 32 * t < a.nlags) ? row[32 * t] : 0.0;
+#pragma unroll
+          for (int t = 0; t < NT; ++t) val[t] = fma(w, v[t], val[t]);
+        } else {
+          double sum[NT];
+#pragma unroll
+          for (int t = 0; t < NT; ++t) sum[t] = 0.0;
+          for (int m = b0; m < b1; m += 2) {
+            const double* r0p = pg + (size_t)m * a.nlags;
+            const bool two = m + 1 < b1;
+            double v0[NT], v1[NT];
+#pragma unroll
+            for (int t = 0; t < NT; ++t) {
+              const bool in = lane + 32 * t < a.nlags;
+              v0[t] = in ? r0p[32 * t] : 0.0;
+              v1[t] = (in && two) ? r0p[a.nlags + 32 * t] : 0.0;
             }
+#pragma unroll
+            for (int t = 0; t < NT; ++t) sum[t] += v0[t] + v1[t];
           }
-          val = fma(a.wsq[(size_t)band * a.nfam + g], t, val);
+#pragma unroll
+          for (int t = 0; t < NT; ++t) val[t] = fma(w, sum[t], val[t]);
         }
       }
     }
-    rout[k] = val;
   }
+#pragma unroll
+  for (int t = 0; t < NT; ++t)
+    if (lane + 32 * t < a.nlags) rout[lane + 32 * t] = val[t];
 }
 
 }  // namespace fdlp
