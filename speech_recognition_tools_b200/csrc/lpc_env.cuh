@@ -317,11 +317,23 @@ __global__ void __launch_bounds__(kEnvWarps * 32) envelope_dmma_kernel(const Env
   const double* pa = a.ms + (size_t)(task0 + lc) * a.Lp + lr;
   // B[row = lane%4][col = lane/4] = basis[k0 + lane%4][t0 + lane/4]
   const double* pb = a.basis + (size_t)lr * a.ldb + t_base + lc;
-  for (int k0 = 0; k0 < a.Lp; k0 += 4) {
-    const double af = __ldg(pa + k0);
-    const double* pbk = pb + (size_t)k0 * a.ldb;
+  // software pipeline: the A fragment and the NT basis fragments of step k0+4 are loaded while step k0 computes
+  double af = __ldg(pa);
+  double bf[NT];
 #pragma unroll
-    for (int i = 0; i < NT; ++i) dmma884(acc[i][0], acc[i][1], af, __ldg(pbk + 8 * i));
+  for (int i = 0; i < NT; ++i) bf[i] = __ldg(pb + 8 * i);
+  for (int k0 = 0; k0 < a.Lp; k0 += 4) {
+    const int kn = (k0 + 4 < a.Lp) ? k0 + 4 : k0;
+    const double afn = __ldg(pa + kn);
+    const double* pbk = pb + (size_t)kn * a.ldb;
+    double bn[NT];
+#pragma unroll
+    for (int i = 0; i < NT; ++i) bn[i] = __ldg(pbk + 8 * i);
+#pragma unroll
+    for (int i = 0; i < NT; ++i) dmma884(acc[i][0], acc[i][1], af, bf[i]);
+    af = afn;
+#pragma unroll
+    for (int i = 0; i < NT; ++i) bf[i] = bn[i];
   }
   // C[row = lane/4][col = 2*(lane%4) + {0,1}]
   const int task = task0 + lc;
