@@ -203,33 +203,38 @@ __device__ __forceinline__ double fold_lag(const FoldCtx& f, int t) {
 }
 
 struct FamArgs {
-  const double* dct;   // [n_seg, ld]
-  const double* tmpl;  // [nfam, ld] templates, circular extension like fbank
-  double* p;           // [n_seg, nfam, nblk, nlags]
-  int n_seg, ld, nfam, nblk, nlags;
-  int nsteps_total;    // N / 32
-  int q;               // a block is q * U steps of 32 samples (U = (NA + 4) / 4)
-  int bpc, nchunk;     // blocks per warp task, tasks per (segment, family)
+  const double* dct;          // [n_seg, ld]
+  const double* tmpl;         // [nfam, ld] templates, circular extension like fbank
+  double* p;                  // [n_seg, nblk_total, nlags] block sums, blocks of all families numbered consecutively
+  const int32_t* bend;        // [nblk_total] end step (exclusive, steps of 32 samples) of each block
+  const int32_t* task_fam;    // [ntask] template of the task
+  const int32_t* task_blk0;   // [ntask] first block
+  const int32_t* task_blk1;   // [ntask] one past the last block
+  const int32_t* task_step0;  // [ntask] first step (= start of the first block)
+  int n_seg, ld, nlags, nblk_total, ntask;
 };
 
+// Blocks have variable length: their boundaries are the steps where some band's filter enters or leaves a
+// region of the template (plan analysis), so every band's range is a union of whole blocks and the direct
+// remainder is only the look-ahead window around each region boundary.  A warp owns a run of consecutive blocks
+// of one (segment, template); the accumulators are flushed whenever the step counter reaches a block end.
 template <int NA>
 __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel(const FamArgs a) {
   constexpr int RS = NA + 4;
   constexpr int U = RS / 4;
-  extern __shared__ __align__(16) double cs[];  // [kAcWarps][NA][kFoldStride]
+  extern __shared__ __align__(16) double cs[];  // [kAcWarps][NA + 1][kFoldStride]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const long long task = (long long)blockIdx.x * kAcWarps + warp;
-  const int per_seg = a.nfam * a.nchunk;
-  if (task >= (long long)a.n_seg * per_seg) return;  // warps are independent: no block-wide barrier below
-  const int seg = (int)(task / per_seg);
-  const int rem = (int)(task % per_seg);
-  const int chunk = rem / a.nfam, fam = rem % a.nfam;  // neighbouring warps share the rows of c
-  const int blk0 = chunk * a.bpc;
-  const int blk1 = min(a.nblk, blk0 + a.bpc);
-  const int spb = U * a.q;
+  const long long gw = (long long)blockIdx.x * kAcWarps + warp;
+  if (gw >= (long long)a.n_seg * a.ntask) return;  // warps are independent: no block-wide barrier below
+  const int seg = (int)(gw / a.ntask);
+  const int task = (int)(gw % a.ntask);  // tasks are sorted by first step: neighbouring warps share rows of c
+  const int fam = a.task_fam[task];
+  const int blk1 = a.task_blk1[task];
+  int blk = a.task_blk0[task];
+  int step = a.task_step0[task];
   const int lr = lane & 3, lc = lane >> 2;
   const int lane_off = (lr << 3) + lc;
-  const int m_lo = blk0 * spb * 4;
+  const int m_lo = step * 4;
 
   const double* __restrict__ pc = a.dct + (size_t)seg * a.ld + (size_t)m_lo * 8 + lane_off;
   const double* __restrict__ pf = a.tmpl + (size_t)fam * a.ld + (size_t)m_lo * 8 + lane_off;
@@ -245,41 +250,45 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel
   for (int i = NA; i < RS; ++i) ring[i] = 0.0;
 
   const FoldCtx fc = fold_ctx(cs + (size_t)warp * fold_smem_doubles(NA), lane);
-  int step = blk0 * spb;
   // the rows of c come from HBM (the templates stay in L1/L2): pull them into L1 two groups of U steps ahead
   const double* cpf = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + NA + 4 + 8 * U) * 8 + lane * 16;
   const int pf_lanes = (U * 32 * 8 + 127) / 128;
-  for (int blk = blk0; blk < blk1; ++blk) {
-    double acc[NA][2];
+  int next_end = a.bend[blk];
+  double acc[NA][2];
 #pragma unroll
-    for (int i = 0; i < NA; ++i) acc[i][0] = acc[i][1] = 0.0;
-    for (int g = 0; g < a.q; ++g) {
-      if (lane < pf_lanes) prefetch_l1(cpf);
-      cpf += U * 32;
+  for (int i = 0; i < NA; ++i) acc[i][0] = acc[i][1] = 0.0;
+  while (blk < blk1) {
+    if (lane < pf_lanes) prefetch_l1(cpf);
+    cpf += U * 32;
 #pragma unroll
-      for (int s = 0; s < U; ++s) {
-        if (step + s < a.nsteps_total) {
+    for (int s = 0; s < U; ++s) {
+      if (blk < blk1) {
 #pragma unroll
-          for (int t = 0; t < 4; ++t) ring[(4 * s + NA + t) % RS] = qf[t] * qc[t];
-          const double afrag = ring[(4 * s) % RS];
-          pc += 32;
-          pf += 32;
+        for (int t = 0; t < 4; ++t) ring[(4 * s + NA + t) % RS] = qf[t] * qc[t];
+        const double afrag = ring[(4 * s) % RS];
+        pc += 32;
+        pf += 32;
 #pragma unroll
-          for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
+        for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
 #pragma unroll
-          for (int i = 0; i < NA; ++i) dmma884(acc[i][0], acc[i][1], afrag, ring[(4 * s + i) % RS]);
+        for (int i = 0; i < NA; ++i) dmma884(acc[i][0], acc[i][1], afrag, ring[(4 * s + i) % RS]);
+        ++step;
+        if (step == next_end) {
+          // flush: C tiles -> shared (warp-private), diagonal sums -> P[seg][blk][0..nlags)
+          fold_store_tiles<NA>(acc, fc);
+          __syncwarp();
+          double* pout = a.p + ((size_t)seg * a.nblk_total + blk) * a.nlags + lane;
+#pragma unroll
+          for (int t = 0; t < NA / 4; ++t)
+            if (lane + 32 * t < a.nlags) pout[32 * t] = fold_lag(fc, t);
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < NA; ++i) acc[i][0] = acc[i][1] = 0.0;
+          ++blk;
+          if (blk < blk1) next_end = a.bend[blk];
         }
       }
-      step += U;
     }
-    // flush: C tiles -> shared (warp-private), diagonal sums -> P[seg][fam][blk][0..nlags)
-    fold_store_tiles<NA>(acc, fc);
-    __syncwarp();
-    double* pout = a.p + (((size_t)seg * a.nfam + fam) * a.nblk + blk) * a.nlags + lane;
-#pragma unroll
-    for (int t = 0; t < NA / 4; ++t)
-      if (lane + 32 * t < a.nlags) pout[32 * t] = fold_lag(fc, t);
-    __syncwarp();
   }
 }
 
@@ -294,11 +303,11 @@ constexpr int kCombRange = 0, kCombPrefix = 1, kCombSuffix = 2;
 constexpr int kCombMaxFam = 3;
 
 struct ScanArgs {
-  double* p;                   // [n_seg, nfam, nblk, nlags], scanned in place for prefix / suffix families
-  int32_t mode[kCombMaxFam];   // kComb*
-  int32_t end[kCombMaxFam];    // suffix mode: common end block
-  int32_t scan_fam[kCombMaxFam];  // families that need a scan
-  int n_scan, n_seg, nfam, nblk, nlags;
+  double* p;                   // [n_seg, nblk_total, nlags], scanned in place for prefix / suffix families
+  int32_t mode[kCombMaxFam];   // kComb* of the scanned families (indexed by scan slot)
+  int32_t boff[kCombMaxFam];   // first block of the family
+  int32_t nblk[kCombMaxFam];   // blocks of the family
+  int n_scan, n_seg, nblk_total, nlags;
 };
 
 // grid (n_seg * n_scan), one thread per lag
@@ -307,25 +316,23 @@ __global__ void __launch_bounds__(160) family_scan_kernel(const ScanArgs a) {
   if (k >= a.nlags) return;
   const int seg = blockIdx.x / a.n_scan;
   const int which = blockIdx.x % a.n_scan;
-  int g = a.scan_fam[0], mode = a.mode[0], end = a.end[0];
+  int mode = a.mode[0], boff = a.boff[0], nblk = a.nblk[0];
 #pragma unroll
   for (int i = 1; i < kCombMaxFam; ++i)
-    if (which == i) { g = a.scan_fam[i]; }
-#pragma unroll
-  for (int i = 0; i < kCombMaxFam; ++i)
-    if (g == i) { mode = a.mode[i]; end = a.end[i]; }
-  double* pg = a.p + (((size_t)seg * a.nfam + g) * a.nblk) * a.nlags + k;
+    if (which == i) { mode = a.mode[i]; boff = a.boff[i]; nblk = a.nblk[i]; }
+  double* pg = a.p + ((size_t)seg * a.nblk_total + boff) * a.nlags + k;
+  const int end = nblk;
   const size_t st = a.nlags;
   double run = 0.0;
   if (mode == kCombPrefix) {
-    for (int m0 = 0; m0 < a.nblk; m0 += 8) {
+    for (int m0 = 0; m0 < nblk; m0 += 8) {
       double v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = (m0 + u < a.nblk) ? pg[(size_t)(m0 + u) * st] : 0.0;
+      for (int u = 0; u < 8; ++u) v[u] = (m0 + u < nblk) ? pg[(size_t)(m0 + u) * st] : 0.0;
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
         run += v[u];
-        if (m0 + u < a.nblk) pg[(size_t)(m0 + u) * st] = run;
+        if (m0 + u < nblk) pg[(size_t)(m0 + u) * st] = run;
       }
     }
   } else {
@@ -353,12 +360,13 @@ struct AcRangeArgs {
   double* r;             // [n_seg, J, nlags]  (written: direct remainder + family terms)
   int J, nlags, n_seg, ld;
   // family terms gathered in the epilogue
-  const double* p;       // [n_seg, nfam, nblk, nlags] block sums (prefix / suffix families already scanned)
-  const int32_t* ra;     // [nfam, J] first block of the band's range
+  const double* p;       // [n_seg, nblk_total, nlags] block sums (prefix / suffix families already scanned)
+  const int32_t* ra;     // [nfam, J] first block of the band's range (family-local index)
   const int32_t* rb;     // [nfam, J] one past the last block
   const double* wsq;     // [J, nfam] squared template weights
   int32_t mode[kCombMaxFam];
-  int nfam, nblk;
+  int32_t boff[kCombMaxFam];  // first block of each family in p
+  int nfam, nblk_total;
 };
 
 template <int NA>
@@ -380,7 +388,7 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
       if (g < a.nfam) {
         const int b0 = a.ra[g * a.J + band], b1 = a.rb[g * a.J + band];
         if (b1 > b0) {
-          const double* pg = a.p + (((size_t)seg * a.nfam + g) * a.nblk) * a.nlags;
+          const double* pg = a.p + ((size_t)seg * a.nblk_total + a.boff[g]) * a.nlags;
           const int r0 = (a.mode[g] == kCombPrefix) ? b1 - 1 : b0;
           const int nrow = (a.mode[g] == kCombRange) ? b1 - b0 : 1;
           for (int idx = lane; idx < nrow * lines; idx += 32)
@@ -449,7 +457,7 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
       const int b0 = a.ra[g * a.J + band], b1 = a.rb[g * a.J + band];
       if (b1 > b0) {
         const double w = a.wsq[(size_t)band * a.nfam + g];
-        const double* pg = a.p + (((size_t)seg * a.nfam + g) * a.nblk) * a.nlags + lane;
+        const double* pg = a.p + ((size_t)seg * a.nblk_total + a.boff[g]) * a.nlags + lane;
         if (a.mode[g] != kCombRange) {
           const double* row = pg + (size_t)((a.mode[g] == kCombPrefix) ? b1 - 1 : b0) * a.nlags;
           double v[NT];

@@ -174,11 +174,12 @@ struct fdlp_plan {
   // family decomposition of the autocorrelation (autocorr.cuh): templates, per-band block classes, direct ranges
   bool fam_ok = false;       // the plan found templates and may use the family path
   int ac_mode = 0;           // 0: family path when available, 1: always the direct per-band kernel
-  int nfam = 0, nblk = 0, fam_q = 1, fam_bpc = 1, fam_nchunk = 1, blk_len = 0;
-  int32_t comb_mode[3] = {0, 0, 0}, comb_nband[3] = {0, 0, 0}, comb_end[3] = {0, 0, 0};
-  size_t fam_smem = 0, comb_smem = 0;
+  int nfam = 0, nblk = 0 /* blocks of all templates */, fam_ntask = 0;
+  int32_t comb_mode[3] = {0, 0, 0}, comb_nband[3] = {0, 0, 0}, comb_boff[3] = {0, 0, 0}, comb_nblk[3] = {0, 0, 0};
+  size_t fam_smem = 0;
   double *d_tmpl = nullptr, *d_wsq = nullptr, *d_p = nullptr;
-  int32_t *d_order = nullptr, *d_ra = nullptr, *d_rb = nullptr, *d_nrng = nullptr, *d_rng = nullptr;
+  int32_t *d_bend = nullptr, *d_ra = nullptr, *d_rb = nullptr, *d_nrng = nullptr, *d_rng = nullptr;
+  int32_t *d_task_fam = nullptr, *d_task_blk0 = nullptr, *d_task_blk1 = nullptr, *d_task_step0 = nullptr;
   int cap_seg_p = 0;
   cudaEvent_t ev_ac[4] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t ev_lpc = nullptr;  // between the LPC/cepstrum kernel and the envelope kernel
@@ -203,7 +204,8 @@ static void plan_free(fdlp_plan* p) {
   cudaFree(p->d_weights); cudaFree(p->d_inv_n); cudaFree(p->d_basis); cudaFree(p->d_wratio);
   cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_alpha); cudaFree(p->d_ms);
   cudaFree(p->d_tmpl); cudaFree(p->d_wsq); cudaFree(p->d_p);
-  cudaFree(p->d_order); cudaFree(p->d_ra); cudaFree(p->d_rb); cudaFree(p->d_nrng); cudaFree(p->d_rng);
+  cudaFree(p->d_bend); cudaFree(p->d_ra); cudaFree(p->d_rb); cudaFree(p->d_nrng); cudaFree(p->d_rng);
+  cudaFree(p->d_task_fam); cudaFree(p->d_task_blk0); cudaFree(p->d_task_blk1); cudaFree(p->d_task_step0);
   for (int i = 0; i < 4; ++i) if (p->ev_ac[i]) cudaEventDestroy(p->ev_ac[i]);
   if (p->ev_lpc) cudaEventDestroy(p->ev_lpc);
   for (int i = 0; i < 5; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
@@ -248,14 +250,10 @@ static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, cons
   const double alp = prm.fbank_args[1], bet = prm.fbank_args[3], warp = prm.fbank_args[4];
   const int fixed = (int)prm.fbank_args[2];
   const int nfam = (fixed == 1) ? 3 : 2;
-  const int U = (p->na + 4) / 4;
-  int q = 1;
-  if (const char* e = getenv("FDLP_FAM_Q")) q = std::max(1, atoi(e));
-  const int blk_len = 32 * U * q;
-  const int nblk = (N + blk_len - 1) / blk_len;
-  if (nblk < 4) return 0;
+  const int ST = N / 32;       // steps of 32 samples (4 rows of 8): the granularity of the DMMA loops
   const int look = 8 * p->na;  // lags the DMMA tiles evaluate
   const double tol = 1e-12;
+  if (ST < 64) return 0;
 
   // templates (same expressions as make_cochlear_fbank)
   const double f_max = prm.srate / 2.0;
@@ -267,108 +265,135 @@ static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, cons
     tm[(size_t)N + n] = pow(10.0, -bet * b);
     if (nfam > 2) tm[(size_t)2 * N + n] = pow(10.0, alp * b);
   }
-  // cls[j][m]: family of block m for band j (regardless of the tail_eps support: a skirt continues as the same
-  // template outside it, and the running sums below include those blocks for free), -1 = no template fits
-  std::vector<int8_t> cls((size_t)J * nblk, (int8_t)-1);
+
+  // ---- per (band, template): the run of steps [ta, tb) whose samples, with their look-ahead, are w * T_g ----
+  // (regardless of the tail_eps support: a skirt continues as the same template outside it, and the running
+  // sums include those blocks for free)
+  std::vector<int32_t> ta((size_t)nfam * J, 0), tb((size_t)nfam * J, 0);
   std::vector<double> wsq((size_t)J * nfam, 0.0);
-  std::vector<int32_t> ra((size_t)nfam * J, 0), rb((size_t)nfam * J, 0), order((size_t)nfam * J, 0);
   std::vector<int32_t> nrng(J, 0), rng((size_t)J * kMaxRanges * 2, 0);
   int64_t direct_taps = 0;
+  std::vector<char> claimed(ST);
   for (int j = 0; j < J; ++j) {
     const double* F = &p->h_fbank[(size_t)j * N];
-    std::vector<double> wref(nfam, 0.0);
-    for (int m = 0; m < nblk; ++m) {
-      const int s = m * blk_len, e = std::min(N, s + blk_len);
-      if (e + look > N) continue;  // the look-ahead wraps around N: not a single region
-      for (int g = 0; g < nfam; ++g) {
-        const double* T = &tm[(size_t)g * N];
-        const double w = wref[g] > 0 ? wref[g] : F[s] / T[s];
+    std::fill(claimed.begin(), claimed.end(), 0);
+    for (int g = 0; g < nfam; ++g) {
+      const double* T = &tm[(size_t)g * N];
+      double wref = 0.0;
+      int first = -1, last = -1;
+      for (int t = 0; t < ST; ++t) {
+        const int s0 = 32 * t, e0 = s0 + 32;
+        if (e0 + look > N) break;  // the look-ahead wraps around N: not a single region
+        if (claimed[t]) continue;
+        const double w = wref > 0 ? wref : F[s0] / T[s0];
         if (!(w > 0) || !std::isfinite(w)) continue;
         bool ok = true;
-        for (int n = s; n < e + look && ok; ++n) ok = fabs(F[n] - w * T[n]) <= tol * w * T[n];
-        if (ok) { cls[(size_t)j * nblk + m] = (int8_t)g; wref[g] = w; break; }
+        for (int n = s0; n < e0 + look && ok; ++n) ok = fabs(F[n] - w * T[n]) <= tol * w * T[n];
+        if (!ok) continue;
+        if (first >= 0 && t != last + 1) return 0;  // not one contiguous run: keep the direct path
+        if (first < 0) first = t;
+        last = t;
+        wref = w;
+        claimed[t] = 1;
       }
+      wsq[(size_t)j * nfam + g] = wref * wref;
+      ta[(size_t)g * J + j] = first >= 0 ? first : 0;
+      tb[(size_t)g * J + j] = first >= 0 ? last + 1 : 0;
     }
-    for (int g = 0; g < nfam; ++g) {
-      wsq[(size_t)j * nfam + g] = wref[g] * wref[g];
-      // the blocks of one family must be one contiguous run
-      int first = -1, last = -1, count = 0;
-      for (int m = 0; m < nblk; ++m)
-        if (cls[(size_t)j * nblk + m] == g) { if (first < 0) first = m; last = m; ++count; }
-      if (count > 0 && count != last - first + 1) return 0;
-      ra[(size_t)g * J + j] = count ? first : 0;
-      rb[(size_t)g * J + j] = count ? last + 1 : 0;
-    }
-    // blocks inside the support that no template fits: merged into row ranges for the direct kernel
-    const int s_lo = row_lo[j] * 8, s_hi = row_hi[j] * 8;
+    // steps inside the support that no template covers: merged into row ranges for the direct kernel
+    const int t_lo = row_lo[j] / 4, t_hi = row_hi[j] / 4;
     int nr = 0;
-    for (int m = 0; m < nblk;) {
-      const int s = m * blk_len, e = std::min(N, s + blk_len);
-      const bool direct = cls[(size_t)j * nblk + m] < 0 && e > s_lo && s < s_hi;
-      if (!direct) { ++m; continue; }
-      int m2 = m;
-      while (m2 < nblk && cls[(size_t)j * nblk + m2] < 0 && std::min(N, (m2 + 1) * blk_len) > s_lo && m2 * blk_len < s_hi) ++m2;
+    for (int t = t_lo; t < t_hi;) {
+      if (claimed[t]) { ++t; continue; }
+      int t2 = t;
+      while (t2 < t_hi && !claimed[t2]) ++t2;
       if (nr >= kMaxRanges) return 0;  // too fragmented: keep the direct path for the whole plan
-      const int e2 = std::min(N, m2 * blk_len);
-      rng[((size_t)j * kMaxRanges + nr) * 2] = s / 8;
-      rng[((size_t)j * kMaxRanges + nr) * 2 + 1] = e2 / 8;
-      direct_taps += e2 - s;
+      rng[((size_t)j * kMaxRanges + nr) * 2] = 4 * t;
+      rng[((size_t)j * kMaxRanges + nr) * 2 + 1] = 4 * t2;
+      direct_taps += 32 * (t2 - t);
       ++nr;
-      m = m2;
+      t = t2;
     }
     nrng[j] = nr;
   }
-  // combination mode per family: prefix sums when every range starts at block 0, suffix sums when every range
-  // ends at the same block, plain short range sums otherwise
-  int32_t mode[kCombMaxFam] = {0, 0, 0}, nband[kCombMaxFam] = {0, 0, 0}, endb[kCombMaxFam] = {0, 0, 0};
+
+  // ---- blocks: per template, the intervals between consecutive run boundaries of any band ----
+  std::vector<int32_t> bend, ra((size_t)nfam * J, 0), rb((size_t)nfam * J, 0);
+  int32_t mode[kCombMaxFam] = {0, 0, 0}, nband[kCombMaxFam] = {0, 0, 0}, boff[kCombMaxFam] = {0, 0, 0},
+          nblk_g[kCombMaxFam] = {0, 0, 0};
+  std::vector<int32_t> task_fam, task_blk0, task_blk1, task_step0;
+  int64_t fam_taps = 0;
+  int chunk_steps = 150;
+  if (const char* e = getenv("FDLP_FAM_CHUNK")) chunk_steps = std::max(8, atoi(e));
   for (int g = 0; g < nfam; ++g) {
-    std::vector<int> bands;
-    bool all_a0 = true, all_b_same = true;
-    int bend = -1;
+    std::vector<int> cuts;
+    for (int j = 0; j < J; ++j)
+      if (tb[(size_t)g * J + j] > ta[(size_t)g * J + j]) {
+        cuts.push_back(ta[(size_t)g * J + j]);
+        cuts.push_back(tb[(size_t)g * J + j]);
+        ++nband[g];
+      }
+    std::sort(cuts.begin(), cuts.end());
+    cuts.erase(std::unique(cuts.begin(), cuts.end()), cuts.end());
+    boff[g] = (int32_t)bend.size();
+    if (cuts.size() < 2) continue;
+    nblk_g[g] = (int32_t)cuts.size() - 1;
+    for (size_t i = 1; i < cuts.size(); ++i) bend.push_back(cuts[i]);
+    fam_taps += 32LL * (cuts.back() - cuts.front());
+    bool all_a0 = true, all_b_end = true;
     for (int j = 0; j < J; ++j) {
-      const int a0 = ra[(size_t)g * J + j], b0 = rb[(size_t)g * J + j];
+      const int a0 = ta[(size_t)g * J + j], b0 = tb[(size_t)g * J + j];
       if (b0 <= a0) continue;
-      bands.push_back(j);
-      if (a0 != 0) all_a0 = false;
-      if (bend < 0) bend = b0; else if (b0 != bend) all_b_same = false;
+      ra[(size_t)g * J + j] = (int32_t)(std::lower_bound(cuts.begin(), cuts.end(), a0) - cuts.begin());
+      rb[(size_t)g * J + j] = (int32_t)(std::lower_bound(cuts.begin(), cuts.end(), b0) - cuts.begin());
+      if (a0 != cuts.front()) all_a0 = false;
+      if (b0 != cuts.back()) all_b_end = false;
     }
-    nband[g] = (int)bands.size();
-    if (all_a0 && !bands.empty()) {
-      mode[g] = kCombPrefix;
-      std::stable_sort(bands.begin(), bands.end(), [&](int x, int y) { return rb[(size_t)g * J + x] < rb[(size_t)g * J + y]; });
-    } else if (all_b_same && !bands.empty()) {
-      mode[g] = kCombSuffix;
-      endb[g] = bend;
-      std::stable_sort(bands.begin(), bands.end(), [&](int x, int y) { return ra[(size_t)g * J + x] > ra[(size_t)g * J + y]; });
-    } else {
-      mode[g] = kCombRange;
+    mode[g] = all_a0 ? kCombPrefix : (all_b_end ? kCombSuffix : kCombRange);
+    // warp tasks: runs of whole blocks of about chunk_steps steps
+    int b0 = 0;
+    while (b0 < nblk_g[g]) {
+      int b1 = b0 + 1;
+      while (b1 < nblk_g[g] && cuts[b1] - cuts[b0] < chunk_steps) ++b1;
+      if (nblk_g[g] - b1 > 0 && cuts[nblk_g[g]] - cuts[b1] < chunk_steps / 2) b1 = nblk_g[g];  // no tiny last task
+      task_fam.push_back(g);
+      task_blk0.push_back(boff[g] + b0);
+      task_blk1.push_back(boff[g] + b1);
+      task_step0.push_back(cuts[b0]);
+      b0 = b1;
     }
-    for (size_t i = 0; i < bands.size(); ++i) order[(size_t)g * J + i] = bands[i];
   }
-  for (int g = 0; g < kCombMaxFam; ++g) { p->comb_mode[g] = mode[g]; p->comb_nband[g] = nband[g]; p->comb_end[g] = endb[g]; }
+  const int nblk_total = (int)bend.size();
+  if (nblk_total == 0) return 0;
   // worthwhile only if the shared work plus the direct remainder is well below the per-band total
-  const int64_t fam_taps = (int64_t)nfam * N;
   if ((fam_taps + direct_taps) * 2 > p->g.support_taps) return 0;
+  {  // neighbouring warps should share rows of c: order the tasks by their first step
+    std::vector<int> idx(task_fam.size());
+    for (size_t i = 0; i < idx.size(); ++i) idx[i] = (int)i;
+    std::stable_sort(idx.begin(), idx.end(), [&](int x, int y) { return task_step0[x] < task_step0[y]; });
+    auto permute = [&](std::vector<int32_t>& v) { std::vector<int32_t> o(v.size()); for (size_t i = 0; i < idx.size(); ++i) o[i] = v[idx[i]]; v.swap(o); };
+    permute(task_fam); permute(task_blk0); permute(task_blk1); permute(task_step0);
+  }
+  for (int g = 0; g < kCombMaxFam; ++g) {
+    p->comb_mode[g] = mode[g]; p->comb_nband[g] = nband[g]; p->comb_boff[g] = boff[g]; p->comb_nblk[g] = nblk_g[g];
+  }
 
   std::vector<double> tpad((size_t)nfam * p->ld);
   for (int g = 0; g < nfam; ++g)
     for (int k = 0; k < p->ld; ++k) tpad[(size_t)g * p->ld + k] = tm[(size_t)g * N + (k % N)];
   int rc;
-  if ((rc = upload(&p->d_tmpl, tpad)) || (rc = upload(&p->d_wsq, wsq)) || (rc = upload(&p->d_order, order)) ||
+  if ((rc = upload(&p->d_tmpl, tpad)) || (rc = upload(&p->d_wsq, wsq)) || (rc = upload(&p->d_bend, bend)) ||
       (rc = upload(&p->d_ra, ra)) || (rc = upload(&p->d_rb, rb)) || (rc = upload(&p->d_nrng, nrng)) ||
-      (rc = upload(&p->d_rng, rng)))
+      (rc = upload(&p->d_rng, rng)) || (rc = upload(&p->d_task_fam, task_fam)) ||
+      (rc = upload(&p->d_task_blk0, task_blk0)) || (rc = upload(&p->d_task_blk1, task_blk1)) ||
+      (rc = upload(&p->d_task_step0, task_step0)))
     return rc;
-  p->nfam = nfam; p->nblk = nblk; p->fam_q = q; p->blk_len = blk_len;
-  int bpc = 25;
-  if (const char* e = getenv("FDLP_FAM_BPC")) bpc = std::max(1, atoi(e));
-  p->fam_bpc = std::min(bpc, nblk);
-  p->fam_nchunk = (nblk + p->fam_bpc - 1) / p->fam_bpc;
+  p->nfam = nfam; p->nblk = nblk_total; p->fam_ntask = (int)task_fam.size();
   p->fam_smem = (size_t)kAcWarps * fold_smem_doubles(p->na) * sizeof(double);
-  p->comb_smem = (size_t)J * p->g.nlags * sizeof(double);
   p->g.family_taps = fam_taps;
   p->g.direct_taps = direct_taps;
   p->g.nfam = nfam;
-  p->g.block_len = blk_len;
+  p->g.block_len = (int32_t)(fam_taps / nblk_total);  // average block length in samples
   p->fam_ok = p->g.nlags <= 160;
   return 0;
 }
@@ -595,7 +620,7 @@ extern "C" int fdlp_plan_get_fbank(const fdlp_plan* p, double* host_out) {
 extern "C" int64_t fdlp_plan_scratch_bytes(const fdlp_plan* p, int32_t n_seg) {
   if (!p) return -1;
   const int64_t J = p->prm.nfilters;
-  const int64_t fam = (p->fam_ok && p->ac_mode == 0) ? (int64_t)p->nfam * p->nblk * p->g.nlags : 0;
+  const int64_t fam = (p->fam_ok && p->ac_mode == 0) ? (int64_t)p->nblk * p->g.nlags : 0;
   return (int64_t)n_seg * 8 * ((int64_t)p->ld + J * p->g.nlags + J * p->g.kk + J * p->Lp + fam);
 }
 
@@ -651,7 +676,7 @@ static int launch_autocorr_direct(fdlp_plan* p, const double* dct, int n_seg, do
 static int ensure_family_scratch(fdlp_plan* p, int n_seg) {
   if (n_seg > p->cap_seg_p) {
     cudaFree(p->d_p); p->d_p = nullptr; p->cap_seg_p = 0;
-    FDLP_CUDA(cudaMalloc((void**)&p->d_p, (size_t)n_seg * p->nfam * p->nblk * p->g.nlags * sizeof(double)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_p, (size_t)n_seg * p->nblk * p->g.nlags * sizeof(double)));
     p->cap_seg_p = n_seg;
   }
   return 0;
@@ -663,23 +688,28 @@ static int launch_autocorr_family(fdlp_plan* p, const double* dct, int n_seg, do
   if (rc) return rc;
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev_ac[0], st));
   FamArgs f;
-  f.dct = dct; f.tmpl = p->d_tmpl; f.p = p->d_p; f.n_seg = n_seg; f.ld = p->ld; f.nfam = p->nfam; f.nblk = p->nblk;
-  f.nlags = p->g.nlags; f.nsteps_total = p->g.N / 32; f.q = p->fam_q; f.bpc = p->fam_bpc; f.nchunk = p->fam_nchunk;
-  const long long tasks = (long long)n_seg * p->nfam * p->fam_nchunk;
+  f.dct = dct; f.tmpl = p->d_tmpl; f.p = p->d_p; f.bend = p->d_bend; f.task_fam = p->d_task_fam;
+  f.task_blk0 = p->d_task_blk0; f.task_blk1 = p->d_task_blk1; f.task_step0 = p->d_task_step0;
+  f.n_seg = n_seg; f.ld = p->ld; f.nlags = p->g.nlags; f.nblk_total = p->nblk; f.ntask = p->fam_ntask;
+  const long long tasks = (long long)n_seg * p->fam_ntask;
   const dim3 gridA((unsigned)((tasks + kAcWarps - 1) / kAcWarps)), block(kAcWarps * 32);
   AcRangeArgs d;
   d.dct = dct; d.fbank = p->d_fbank; d.nrng = p->d_nrng; d.rng = p->d_rng; d.r = r;
   d.J = p->prm.nfilters; d.nlags = p->g.nlags; d.n_seg = n_seg; d.ld = p->ld;
   const int nbg = (d.J + kAcWarps - 1) / kAcWarps;
   const dim3 gridD((unsigned)((size_t)n_seg * nbg));
-  d.p = p->d_p; d.ra = p->d_ra; d.rb = p->d_rb; d.wsq = p->d_wsq; d.nfam = p->nfam; d.nblk = p->nblk;
+  d.p = p->d_p; d.ra = p->d_ra; d.rb = p->d_rb; d.wsq = p->d_wsq; d.nfam = p->nfam; d.nblk_total = p->nblk;
   ScanArgs c;
-  c.p = p->d_p; c.n_scan = 0; c.n_seg = n_seg; c.nfam = p->nfam; c.nblk = p->nblk; c.nlags = p->g.nlags;
+  c.p = p->d_p; c.n_scan = 0; c.n_seg = n_seg; c.nblk_total = p->nblk; c.nlags = p->g.nlags;
   for (int g = 0; g < kCombMaxFam; ++g) {
-    c.mode[g] = p->comb_mode[g]; c.end[g] = p->comb_end[g]; c.scan_fam[g] = 0; d.mode[g] = p->comb_mode[g];
+    c.mode[g] = 0; c.boff[g] = 0; c.nblk[g] = 0;
+    d.mode[g] = p->comb_mode[g]; d.boff[g] = p->comb_boff[g];
   }
   for (int g = 0; g < p->nfam; ++g)
-    if (p->comb_mode[g] != kCombRange && p->comb_nband[g] > 0) c.scan_fam[c.n_scan++] = g;
+    if (p->comb_mode[g] != kCombRange && p->comb_nband[g] > 0) {
+      c.mode[c.n_scan] = p->comb_mode[g]; c.boff[c.n_scan] = p->comb_boff[g]; c.nblk[c.n_scan] = p->comb_nblk[g];
+      ++c.n_scan;
+    }
   const dim3 gridC((unsigned)((size_t)n_seg * std::max(c.n_scan, 1))), blockC(160);
 #define RUN_FAM_A(NA_) case NA_: family_block_autocorr_kernel<NA_><<<gridA, block, p->fam_smem, st>>>(f); break;
 #define RUN_FAM_D(NA_) case NA_: autocorr_ranges_kernel<NA_><<<gridD, block, p->fam_smem, st>>>(d); break;

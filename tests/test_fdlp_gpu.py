@@ -206,7 +206,7 @@ def test_family_autocorrelation_matches_direct_kernel_and_oracle():
     x = synth.make_utterance("speechlike", 3, 7, 70000, 3.0)
     ex = extractor(**WSJ)
     g = ex.geom
-    assert g["nfam"] == 3 and g["block_len"] % 32 == 0
+    assert g["nfam"] == 3 and g["block_len"] >= 32
     assert (g["family_taps"] + g["direct_taps"]) * 4 < g["support_taps"]
     dct, _ = ex.stage_dct([x])
     r_fam = ex.stage_autocorr(dct).cpu().numpy()
