@@ -192,6 +192,8 @@ struct fdlp_plan {
   // (measured on B200: K3 and K4 CTAs do not become co-resident -- 19.6 + 3.8 ms alone, 23.1 ms together -- so
   // the pipeline brings nothing yet and is off by default; fdlp_plan_set_overlap turns it on)
   bool overlap = false;
+  int overlap_chunks = kMaxChunks;
+  int overlap_cap = 148;  // CTAs of the LPC kernel when it shares the SMs with the next chunk's autocorrelation
   cudaStream_t side = nullptr;
   cudaEvent_t ev_start = nullptr, ev_side = nullptr, ev_chunk[kMaxChunks] = {};
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -596,6 +598,13 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
     for (int i = 0; i < kMaxChunks && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&p->ev_chunk[i], cudaEventDisableTiming);
     if (e != cudaSuccess) { plan_free(p); return set_err(FDLP_E_CUDA, "stream/event creation: %s", cudaGetErrorString(e)); }
   }
+  {
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, p->device);
+    if (sms > 0) p->overlap_cap = sms;
+    if (const char* e = getenv("FDLP_OVERLAP_CAP")) p->overlap_cap = atoi(e);
+    if (const char* e = getenv("FDLP_OVERLAP_CHUNKS")) p->overlap_chunks = std::max(1, std::min(kMaxChunks, atoi(e)));
+  }
   *out = p;
   return FDLP_OK;
 }
@@ -739,7 +748,8 @@ static int launch_autocorr(fdlp_plan* p, const double* dct, int n_seg, double* r
 }
 
 static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out, double* gain_out, double* cep_out,
-                      double* env, int32_t* status, const int32_t* seg_utt, cudaStream_t st, size_t task0 = 0) {
+                      double* env, int32_t* status, const int32_t* seg_utt, cudaStream_t st, size_t task0 = 0,
+                      int grid_cap = 0) {
   LpcArgs a;
   a.r = r; a.n_tasks = n_seg * p->prm.nfilters; a.J = p->prm.nfilters;
   a.order = p->prm.order; a.nlags = p->g.nlags; a.L = p->g.L; a.Lp = p->Lp;
@@ -751,10 +761,12 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
   // register-resident kernel when the order and the cepstrum length fit 8 lanes x NS slots, else shared memory
   const int need = std::max(p->prm.order + 1, p->g.L);
   static const bool force_smem = getenv("FDLP_LPC_SMEM") != nullptr;
+  int lpc_grid = (a.n_tasks + 15) / 16;
+  if (grid_cap > 0) lpc_grid = std::min(lpc_grid, grid_cap);
   if (need <= 64 && !force_smem) {
-    lpc_cepstrum_reg_kernel<8><<<(a.n_tasks + 15) / 16, 128, 0, st>>>(a);
+    lpc_cepstrum_reg_kernel<8><<<lpc_grid, 128, 0, st>>>(a);
   } else if (need <= 160 && !force_smem) {
-    lpc_cepstrum_reg_kernel<20><<<(a.n_tasks + 15) / 16, 128, 0, st>>>(a);
+    lpc_cepstrum_reg_kernel<20><<<lpc_grid, 128, 0, st>>>(a);
   } else {
     const int tpc = p->lpc_threads / kLpcGroup;
     lpc_cepstrum_kernel<<<(a.n_tasks + tpc - 1) / tpc, p->lpc_threads, p->lpc_smem, st>>>(a);
@@ -801,7 +813,7 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
   const bool prof = p->profiling;
   const int J = p->prm.nfilters;
   int nchunk = 1;
-  if (p->overlap && !prof && p->side) nchunk = std::min(kMaxChunks, b->n_seg / 16);
+  if (p->overlap && !prof && p->side) nchunk = std::min(p->overlap_chunks, b->n_seg / 16);
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[0], st));
   if ((rc = launch_noise(p, b, st))) return rc;
   if (nchunk <= 1) {
@@ -826,7 +838,7 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
       FDLP_CUDA(cudaEventRecord(p->ev_chunk[c], st));
       FDLP_CUDA(cudaStreamWaitEvent(p->side, p->ev_chunk[c], 0));
       if ((rc = launch_lpc(p, r_c, ns, nullptr, nullptr, nullptr, p->d_env + (size_t)s0 * J * p->g.kk, b->status,
-                           b->seg_utt + s0, p->side, (size_t)s0 * J))) return rc;
+                           b->seg_utt + s0, p->side, (size_t)s0 * J, p->overlap_cap))) return rc;
     }
     FDLP_CUDA(cudaEventRecord(p->ev_side, p->side));
     FDLP_CUDA(cudaStreamWaitEvent(st, p->ev_side, 0));

@@ -180,7 +180,11 @@ __global__ void __launch_bounds__(128, (NS > 8) ? 3 : 5) lpc_cepstrum_reg_kernel
   const int gbase = lane & ~7;
   const int src_prev = gbase | ((g + 7) & 7);  // lane holding element i-1
   const int p = a.order, L = a.L;
-  int task = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+  // grid-stride over blocks of 16 solves: a capped grid (one CTA per SM) lets this kernel share the SMs with
+  // the DMMA-bound autocorrelation kernels of the next chunk when fdlp_forward pipelines chunks over two streams
+  const int n_vblocks = (a.n_tasks + 15) >> 4;
+  for (int vb = blockIdx.x; vb < n_vblocks; vb += gridDim.x) {
+  int task = (vb * (int)blockDim.x + (int)threadIdx.x) >> 3;
   const bool live = task < a.n_tasks;
   if (!live) task = a.n_tasks - 1;  // idle groups shadow the last task (keeps the shuffles uniform)
 
@@ -287,6 +291,7 @@ __global__ void __launch_bounds__(128, (NS > 8) ? 3 : 5) lpc_cepstrum_reg_kernel
     const int seg = task / a.J;
     atomicOr(a.status + (a.seg_utt ? a.seg_utt[seg] : seg), bad);
   }
+  }  // grid-stride loop
 }
 
 // ---------------------------------------------------------------------------------------------------
