@@ -959,12 +959,18 @@ struct mel_plan {
   int32_t* d_frame_utt = nullptr;
   int64_t cap_frames = 0;
   size_t smem = 0;
+  // warp-per-frame kernel (nfft/2 = 32 * R2, R2 in {16, 32})
+  int warp_r2 = 0, sms = 148;
+  size_t warp_smem = 0;
+  float* d_ham32 = nullptr;
+  float2 *d_tw4 = nullptr, *d_unpackA32 = nullptr;
 };
 
 static void mel_free(mel_plan* p) {
   if (!p) return;
   free_fft_tables(&p->fft);
   cudaFree(p->d_ham); cudaFree(p->d_fbank); cudaFree(p->d_lo); cudaFree(p->d_hi); cudaFree(p->d_frame_utt);
+  cudaFree(p->d_ham32); cudaFree(p->d_tw4); cudaFree(p->d_unpackA32);
   delete p;
 }
 
@@ -1005,6 +1011,38 @@ extern "C" int mel_plan_create(const mel_params* prm, mel_plan** out) {
   std::vector<double> ham = np_hamming(p->flen);
   if ((rc = upload(&p->d_ham, ham)) || (rc = upload(&p->d_fbank, f32)) || (rc = upload(&p->d_lo, lo)) ||
       (rc = upload(&p->d_hi, hi))) { mel_free(p); return rc; }
+  if ((p->n == 512 || p->n == 1024) && J <= 32 * kMelMaxBandsPerLane && !getenv("FDLP_MEL_CTA")) {
+    const int R2 = p->n / 32, n = p->n;
+    std::vector<float> ham32(ham.begin(), ham.end());
+    std::vector<float2> tw4((size_t)R2 * 32), A32(n + 1);
+    for (int k1 = 0; k1 < R2; ++k1)
+      for (int l = 0; l < 32; ++l) {
+        const long double ang = -2.0L * M_PIl * (long double)((k1 * l) % n) / n;
+        tw4[(size_t)k1 * 32 + l] = make_float2((float)cosl(ang), (float)sinl(ang));
+      }
+    for (int k = 0; k <= n; ++k) {
+      const long double ang = -2.0L * M_PIl * k / (2.0L * n);
+      A32[k] = make_float2((float)cosl(ang), (float)sinl(ang));
+    }
+    if ((rc = upload(&p->d_ham32, ham32)) || (rc = upload(&p->d_tw4, tw4)) || (rc = upload(&p->d_unpackA32, A32))) {
+      mel_free(p); return rc;
+    }
+    p->warp_r2 = R2;
+    p->warp_smem = (size_t)kMelWarps * (R2 * 33 + (n + 4) / 2) * sizeof(float2);
+    cudaError_t e2 = cudaSuccess;
+    if (R2 == 32) {
+      e2 = cudaFuncSetAttribute(mel_frames_warp_kernel<32, int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->warp_smem);
+      if (e2 == cudaSuccess) e2 = cudaFuncSetAttribute(mel_frames_warp_kernel<32, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->warp_smem);
+    } else {
+      e2 = cudaFuncSetAttribute(mel_frames_warp_kernel<16, int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->warp_smem);
+      if (e2 == cudaSuccess) e2 = cudaFuncSetAttribute(mel_frames_warp_kernel<16, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->warp_smem);
+    }
+    if (e2 != cudaSuccess) { mel_free(p); return set_err(FDLP_E_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e2)); }
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms > 0) p->sms = sms;
+  }
   p->smem = (size_t)prm->nfft * sizeof(float) + (size_t)(p->n + 1) * sizeof(float);
   cudaError_t e = cudaFuncSetAttribute(mel_frames_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(mel_frames_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem);
@@ -1033,6 +1071,28 @@ extern "C" int mel_forward(mel_plan* p, const mel_batch* b, void* stream) {
   }
   mel_frame_map_kernel<<<b->n_utt, 128, 0, st>>>(b->utt_frame_off, b->n_utt, p->d_frame_utt);
   FDLP_CUDA(cudaGetLastError());
+  if (b->wav_dtype != FDLP_WAV_INT16 && b->wav_dtype != FDLP_WAV_FLOAT32) return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
+  if (p->warp_r2 > 0) {
+    MelWarpArgs w;
+    memset(&w, 0, sizeof(w));
+    w.wav = b->wav; w.utt_wav_off = b->utt_wav_off; w.utt_frame_off = b->utt_frame_off; w.frame_utt = p->d_frame_utt;
+    w.n_frames = b->n_frames; w.flen = p->flen; w.shift = p->shift; w.nfft = p->prm.nfft; w.n = p->n;
+    w.ham = p->d_ham32; w.tw4 = p->d_tw4; w.unpackA = p->d_unpackA32; w.fbank = p->d_fbank;
+    w.band_lo = p->d_lo; w.band_hi = p->d_hi; w.feats = b->feats; w.cmvn = b->cmvn_acc;
+    w.J = p->prm.nfilters; w.power = p->prm.power;
+    const long long need = (b->n_frames + kMelWarps - 1) / kMelWarps;
+    const dim3 grid((unsigned)std::min<long long>(need, (long long)p->sms * 8)), block(kMelWarps * 32);
+    const bool i16 = b->wav_dtype == FDLP_WAV_INT16;
+    if (p->warp_r2 == 32) {
+      if (i16) mel_frames_warp_kernel<32, int16_t><<<grid, block, p->warp_smem, st>>>(w);
+      else mel_frames_warp_kernel<32, float><<<grid, block, p->warp_smem, st>>>(w);
+    } else {
+      if (i16) mel_frames_warp_kernel<16, int16_t><<<grid, block, p->warp_smem, st>>>(w);
+      else mel_frames_warp_kernel<16, float><<<grid, block, p->warp_smem, st>>>(w);
+    }
+    FDLP_CUDA(cudaGetLastError());
+    return FDLP_OK;
+  }
   MelArgs a;
   memset(&a, 0, sizeof(a));
   a.wav = b->wav; a.utt_wav_off = b->utt_wav_off; a.utt_frame_off = b->utt_frame_off; a.frame_utt = p->d_frame_utt;
