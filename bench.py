@@ -290,7 +290,9 @@ def run_ours(args):
         tp = os.path.join(ROOT, "profiles", "top_kernel_traffic.json")
         if os.path.exists(tp):
             try:
-                traffic = json.load(open(tp)).get(top)
+                td = json.load(open(tp))  # dram__bytes_read.sum + dram__bytes_write.sum per launch (ncu --set full)
+                if int(td.get("segments", -1)) == int(nseg):  # captured at this batch size only
+                    traffic = td["kernels"][top]["dram_bytes"]
             except Exception:  # noqa: BLE001
                 traffic = None
         roofline = {"bound": "tensor", "pipe": "fp64 (DMMA.8x8x4 / DFMA)", "kernel": top,

@@ -763,7 +763,12 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
   static const bool force_smem = getenv("FDLP_LPC_SMEM") != nullptr;
   int lpc_grid = (a.n_tasks + 15) / 16;
   if (grid_cap > 0) lpc_grid = std::min(lpc_grid, grid_cap);
-  if (need <= 64 && !force_smem) {
+  static const bool force_rot = getenv("FDLP_LPC_ROT") != nullptr;  // the rotation-per-order register kernel (A/B runs)
+  if (need <= 80 && !force_smem && !force_rot) {
+    lpc_cepstrum_blk_kernel<2><<<lpc_grid, 128, 0, st>>>(a);
+  } else if (need <= 160 && !force_smem && !force_rot) {
+    lpc_cepstrum_blk_kernel<4><<<lpc_grid, 128, 0, st>>>(a);
+  } else if (need <= 64 && !force_smem) {
     lpc_cepstrum_reg_kernel<8><<<lpc_grid, 128, 0, st>>>(a);
   } else if (need <= 160 && !force_smem) {
     lpc_cepstrum_reg_kernel<20><<<lpc_grid, 128, 0, st>>>(a);
@@ -962,15 +967,31 @@ struct mel_plan {
   // warp-per-frame kernel (nfft/2 = 32 * R2, R2 in {16, 32})
   int warp_r2 = 0, sms = 148;
   size_t warp_smem = 0;
-  float* d_ham32 = nullptr;
+  int warp_m1 = 0, wts_smem = 0;
+  float *d_ham32 = nullptr, *d_wts = nullptr;
   float2 *d_tw4 = nullptr, *d_unpackA32 = nullptr;
+  int4* d_band = nullptr;
 };
+
+template <int R2, int M1, typename S>
+static cudaError_t mel_warp_launch(const MelWarpArgs& w, dim3 grid, size_t smem, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(mel_frames_warp_kernel<R2, M1, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  mel_frames_warp_kernel<R2, M1, S><<<grid, kMelWarps * 32, smem, st>>>(w);
+  return cudaGetLastError();
+}
+template <int R2, typename S>
+static cudaError_t mel_warp_launch_m1(int m1, const MelWarpArgs& w, dim3 grid, size_t smem, cudaStream_t st) {
+  if (m1 == 5) return mel_warp_launch<R2, 5, S>(w, grid, smem, st);
+  if (m1 == 8 && R2 > 16) return mel_warp_launch<R2, 8, S>(w, grid, smem, st);
+  return mel_warp_launch<R2, 0, S>(w, grid, smem, st);
+}
 
 static void mel_free(mel_plan* p) {
   if (!p) return;
   free_fft_tables(&p->fft);
   cudaFree(p->d_ham); cudaFree(p->d_fbank); cudaFree(p->d_lo); cudaFree(p->d_hi); cudaFree(p->d_frame_utt);
-  cudaFree(p->d_ham32); cudaFree(p->d_tw4); cudaFree(p->d_unpackA32);
+  cudaFree(p->d_ham32); cudaFree(p->d_tw4); cudaFree(p->d_unpackA32); cudaFree(p->d_wts); cudaFree(p->d_band);
   delete p;
 }
 
@@ -1013,7 +1034,9 @@ extern "C" int mel_plan_create(const mel_params* prm, mel_plan** out) {
       (rc = upload(&p->d_hi, hi))) { mel_free(p); return rc; }
   if ((p->n == 512 || p->n == 1024) && J <= 32 * kMelMaxBandsPerLane && !getenv("FDLP_MEL_CTA")) {
     const int R2 = p->n / 32, n = p->n;
-    std::vector<float> ham32(ham.begin(), ham.end());
+    const int used = std::min(p->flen, prm->nfft);
+    std::vector<float> ham32((size_t)prm->nfft, 0.f);  // zero beyond the frame: the kernel loads whole 64-sample rows
+    for (int i = 0; i < used; ++i) ham32[i] = (float)ham[i];
     std::vector<float2> tw4((size_t)R2 * 32), A32(n + 1);
     for (int k1 = 0; k1 < R2; ++k1)
       for (int l = 0; l < 32; ++l) {
@@ -1024,20 +1047,24 @@ extern "C" int mel_plan_create(const mel_params* prm, mel_plan** out) {
       const long double ang = -2.0L * M_PIl * k / (2.0L * n);
       A32[k] = make_float2((float)cosl(ang), (float)sinl(ang));
     }
-    if ((rc = upload(&p->d_ham32, ham32)) || (rc = upload(&p->d_tw4, tw4)) || (rc = upload(&p->d_unpackA32, A32))) {
+    // band supports packed back to back: weight of (band j, bin b) at wts[band[j].z + b - band[j].x]
+    std::vector<float> wts;
+    std::vector<int4> band(J);
+    for (int j = 0; j < J; ++j) {
+      band[j] = make_int4(lo[j], hi[j] - lo[j], (int)wts.size(), 0);
+      for (int k = lo[j]; k < hi[j]; ++k) wts.push_back(f32[(size_t)j * nb + k]);
+    }
+    if (wts.empty()) wts.push_back(0.f);
+    if ((rc = upload(&p->d_ham32, ham32)) || (rc = upload(&p->d_tw4, tw4)) || (rc = upload(&p->d_unpackA32, A32)) ||
+        (rc = upload(&p->d_wts, wts)) || (rc = upload(&p->d_band, band))) {
       mel_free(p); return rc;
     }
     p->warp_r2 = R2;
-    p->warp_smem = (size_t)kMelWarps * (R2 * 33 + (n + 4) / 2) * sizeof(float2);
-    cudaError_t e2 = cudaSuccess;
-    if (R2 == 32) {
-      e2 = cudaFuncSetAttribute(mel_frames_warp_kernel<32, int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->warp_smem);
-      if (e2 == cudaSuccess) e2 = cudaFuncSetAttribute(mel_frames_warp_kernel<32, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->warp_smem);
-    } else {
-      e2 = cudaFuncSetAttribute(mel_frames_warp_kernel<16, int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->warp_smem);
-      if (e2 == cudaSuccess) e2 = cudaFuncSetAttribute(mel_frames_warp_kernel<16, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->warp_smem);
-    }
-    if (e2 != cudaSuccess) { mel_free(p); return set_err(FDLP_E_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e2)); }
+    const int rows = (used + 63) / 64;
+    p->warp_m1 = rows <= 5 ? 5 : (rows <= 8 && R2 > 16) ? 8 : 0;
+    // two CTAs per SM: stage the packed weights in shared memory when they fit beside the tiles
+    p->wts_smem = mel_warp_smem_bytes(R2, J, (int)wts.size()) <= 113 * 1024 ? (int)wts.size() : 0;
+    p->warp_smem = mel_warp_smem_bytes(R2, J, p->wts_smem);
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -1077,19 +1104,20 @@ extern "C" int mel_forward(mel_plan* p, const mel_batch* b, void* stream) {
     memset(&w, 0, sizeof(w));
     w.wav = b->wav; w.utt_wav_off = b->utt_wav_off; w.utt_frame_off = b->utt_frame_off; w.frame_utt = p->d_frame_utt;
     w.n_frames = b->n_frames; w.flen = p->flen; w.shift = p->shift; w.nfft = p->prm.nfft; w.n = p->n;
-    w.ham = p->d_ham32; w.tw4 = p->d_tw4; w.unpackA = p->d_unpackA32; w.fbank = p->d_fbank;
-    w.band_lo = p->d_lo; w.band_hi = p->d_hi; w.feats = b->feats; w.cmvn = b->cmvn_acc;
+    w.ham = p->d_ham32; w.tw4 = p->d_tw4; w.unpackA = p->d_unpackA32; w.wts = p->d_wts; w.band = p->d_band;
+    w.wts_smem = p->wts_smem; w.feats = b->feats; w.cmvn = b->cmvn_acc;
     w.J = p->prm.nfilters; w.power = p->prm.power;
     const long long need = (b->n_frames + kMelWarps - 1) / kMelWarps;
-    const dim3 grid((unsigned)std::min<long long>(need, (long long)p->sms * 8)), block(kMelWarps * 32);
+    const dim3 grid((unsigned)std::min<long long>(need, (long long)p->sms * 2));
     const bool i16 = b->wav_dtype == FDLP_WAV_INT16;
-    if (p->warp_r2 == 32) {
-      if (i16) mel_frames_warp_kernel<32, int16_t><<<grid, block, p->warp_smem, st>>>(w);
-      else mel_frames_warp_kernel<32, float><<<grid, block, p->warp_smem, st>>>(w);
-    } else {
-      if (i16) mel_frames_warp_kernel<16, int16_t><<<grid, block, p->warp_smem, st>>>(w);
-      else mel_frames_warp_kernel<16, float><<<grid, block, p->warp_smem, st>>>(w);
-    }
+    cudaError_t le;
+    if (p->warp_r2 == 32)
+      le = i16 ? mel_warp_launch_m1<32, int16_t>(p->warp_m1, w, grid, p->warp_smem, st)
+               : mel_warp_launch_m1<32, float>(p->warp_m1, w, grid, p->warp_smem, st);
+    else
+      le = i16 ? mel_warp_launch_m1<16, int16_t>(p->warp_m1, w, grid, p->warp_smem, st)
+               : mel_warp_launch_m1<16, float>(p->warp_m1, w, grid, p->warp_smem, st);
+    FDLP_CUDA(le);
     FDLP_CUDA(cudaGetLastError());
     return FDLP_OK;
   }

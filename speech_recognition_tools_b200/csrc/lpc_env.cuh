@@ -294,6 +294,240 @@ __global__ void __launch_bounds__(128, (NS > 8) ? 3 : 5) lpc_cepstrum_reg_kernel
   }  // grid-stride loop
 }
 
+// K4, blocked-cyclic register layout.  The rotation kernel above moves every register of the shifting vector
+// through a shuffle at every order (2 SHFL + 2 FSEL per 3 DFMA: the LSU pipe and the issue slots, not the FP64
+// pipe, set its time).  Here element i of a vector lives in group i / 40, lane (i % 40) / 5, register i % 5, so
+// a shift by one element stays inside the lane for four registers out of five.  Those four do not move at
+// all: the five registers of a (group, lane) form a circular buffer whose origin advances by one per order,
+// and because the order loop is unrolled by five every index is a compile-time constant.  Only the register
+// that leaves the lane goes through a shuffle: 2 SHFL + 2 FSEL per 15 DFMA.
+// Physical register q of the shifting vector holds logical position (q + rho) mod 5 after rho shifts.
+// One Levinson order m (T = m % 5, groups 0..PH hold elements 0..m):
+//   f' = f + k shift(b),  b' = shift(b) + k f,  acc' = sum_j b'_j r[j+1]
+template <int NG, int PH, int T>
+__device__ __forceinline__ void lev_order(double (&f)[NG][5], double (&b)[NG][5], const double (&rr)[NG][5],
+                                          double& acc, double& E, int& bad, const bool g0, const int src_prev) {
+  constexpr int C = 5;
+  if (E == 0.0 || !isfinite(E)) bad = FDLP_ST_SINGULAR;
+  const double k = -acc * __drcp_rn(E);
+  constexpr int qo = (C - T) % C;  // m - 1 shifts so far: logical 4 sits in register (4 - (m - 1)) mod 5
+  double tin[PH + 1];
+#pragma unroll
+  for (int G = 0; G <= PH; ++G) tin[G] = __shfl_sync(0xffffffffu, b[G][qo], src_prev);
+#pragma unroll
+  for (int G = PH; G >= 0; --G) {
+    const double from_prev_group = (G > 0) ? tin[G > 0 ? G - 1 : 0] : 0.0;
+    b[G][qo] = g0 ? from_prev_group : tin[G];
+  }
+  double part[PH + 1];
+#pragma unroll
+  for (int G = 0; G <= PH; ++G) {
+    part[G] = 0.0;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int q = (c - T + C) % C;  // after this order's shift logical c sits in register (c - m) mod 5
+      const double sb = b[G][q];
+      const double fo = f[G][c];
+      f[G][c] = fma(k, sb, fo);
+      const double nb = fma(k, fo, sb);
+      b[G][q] = nb;
+      part[G] = fma(nb, rr[G][c], part[G]);
+    }
+  }
+  double tot = part[0];
+#pragma unroll
+  for (int G = 1; G <= PH; ++G) tot += part[G];
+  acc = group_sum8(tot);
+  E *= (1.0 - k * k);
+}
+
+// One cepstrum step n (T = n % 5): y shifts by one with x[n] entering at element 0, v = x[n] + (1/n) sum mc y.
+// xg: group that holds element n of x (compile-time PH in the main loop, run-time in the tail).
+template <int NG, int PH, int T>
+__device__ __forceinline__ void cep_step(const double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5],
+                                         const int n, const int xg, const LpcArgs& a, double* msg, const int task,
+                                         const bool live, const int g, const int gbase, const int src_prev) {
+  constexpr int C = 5;
+  double xv = x[PH][T];
+  if (xg != PH) {
+#pragma unroll
+    for (int G = 0; G < PH; ++G) if (G == xg) xv = x[G][T];
+  }
+  const int xl = (n / C) & 7;
+  const double xn = (n <= a.order) ? __shfl_sync(0xffffffffu, xv, gbase | xl) : 0.0;
+  constexpr int qo = (1 - T + C) % C;  // n - 2 shifts so far
+  double tin[PH + 1];
+#pragma unroll
+  for (int G = 0; G <= PH; ++G) tin[G] = __shfl_sync(0xffffffffu, y[G][qo], src_prev);
+#pragma unroll
+  for (int G = PH; G >= 0; --G) {
+    const double from_prev_group = (G > 0) ? tin[G > 0 ? G - 1 : 0] : xn;
+    y[G][qo] = (g == 0) ? from_prev_group : tin[G];
+  }
+  double part[PH + 1];
+#pragma unroll
+  for (int G = 0; G <= PH; ++G) {
+    part[G] = 0.0;
+#pragma unroll
+    for (int c = 0; c < C; ++c) part[G] = fma(mc[G][c], y[G][(c - T + 1 + C) % C], part[G]);
+  }
+  double tot = part[0];
+#pragma unroll
+  for (int G = 1; G <= PH; ++G) tot += part[G];
+  const double v = fma(group_sum8(tot), __ldg(a.inv_n + n), xn);
+  const double vn = v * (double)n;
+#pragma unroll
+  for (int G = 0; G <= PH; ++G)
+    if (G == PH || G == xg) mc[G][T] = (g == xl && G == xg) ? vn : mc[G][T];
+  if (g == 0 && live) {
+    msg[n] = v * __ldg(a.weights + n);
+    if (a.cep_out) a.cep_out[(size_t)task * a.L + n] = v;
+  }
+}
+
+// blocks of five unguarded orders m = 5 qb + t for the blocks qb of phase PH (8 PH <= qb <= 8 PH + 7), then
+// the next phase
+template <int NG, int PH>
+__device__ __forceinline__ void lev_phase(double (&f)[NG][5], double (&b)[NG][5], const double (&rr)[NG][5],
+                                          double& acc, double& E, int& bad, const bool g0, const int src_prev,
+                                          const int qb_full) {
+  const int qb_lo = (PH == 0) ? 1 : 8 * PH;
+  const int qb_hi = (8 * PH + 7 < qb_full) ? 8 * PH + 7 : qb_full;
+#pragma unroll 1
+  for (int qb = qb_lo; qb <= qb_hi; ++qb) {
+    lev_order<NG, PH, 0>(f, b, rr, acc, E, bad, g0, src_prev);
+    lev_order<NG, PH, 1>(f, b, rr, acc, E, bad, g0, src_prev);
+    lev_order<NG, PH, 2>(f, b, rr, acc, E, bad, g0, src_prev);
+    lev_order<NG, PH, 3>(f, b, rr, acc, E, bad, g0, src_prev);
+    lev_order<NG, PH, 4>(f, b, rr, acc, E, bad, g0, src_prev);
+  }
+  if constexpr (PH + 1 < NG) lev_phase<NG, PH + 1>(f, b, rr, acc, E, bad, g0, src_prev, qb_full);
+}
+
+template <int NG, int PH>
+__device__ __forceinline__ void cep_phase(const double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5],
+                                          const int nb_full, const LpcArgs& a, double* msg, const int task,
+                                          const bool live, const int g, const int gbase, const int src_prev) {
+  const int qb_lo = (PH == 0) ? 1 : 8 * PH;
+  const int qb_hi = (8 * PH + 7 < nb_full) ? 8 * PH + 7 : nb_full;
+#pragma unroll 1
+  for (int qb = qb_lo; qb <= qb_hi; ++qb) {
+    const int n0 = 5 * qb;
+    cep_step<NG, PH, 0>(x, y, mc, n0, PH, a, msg, task, live, g, gbase, src_prev);
+    cep_step<NG, PH, 1>(x, y, mc, n0 + 1, PH, a, msg, task, live, g, gbase, src_prev);
+    cep_step<NG, PH, 2>(x, y, mc, n0 + 2, PH, a, msg, task, live, g, gbase, src_prev);
+    cep_step<NG, PH, 3>(x, y, mc, n0 + 3, PH, a, msg, task, live, g, gbase, src_prev);
+    cep_step<NG, PH, 4>(x, y, mc, n0 + 4, PH, a, msg, task, live, g, gbase, src_prev);
+  }
+  if constexpr (PH + 1 < NG) cep_phase<NG, PH + 1>(x, y, mc, nb_full, a, msg, task, live, g, gbase, src_prev);
+}
+
+template <int NG>
+__global__ void __launch_bounds__(128, (NG > 2) ? 3 : 5) lpc_cepstrum_blk_kernel(const LpcArgs a) {
+  constexpr int C = 5, GE = 8 * C;
+  const int lane = threadIdx.x & 31;
+  const int g = lane & 7;
+  const bool g0 = g == 0;
+  const int gbase = lane & ~7;
+  const int src_prev = gbase | ((g + 7) & 7);
+  const int p = a.order, L = a.L;
+  const int n_vblocks = (a.n_tasks + 15) >> 4;
+  for (int vb = blockIdx.x; vb < n_vblocks; vb += gridDim.x) {
+  int task = (vb * (int)blockDim.x + (int)threadIdx.x) >> 3;
+  const bool live = task < a.n_tasks;
+  if (!live) task = a.n_tasks - 1;  // idle groups shadow the last task (keeps the shuffles uniform)
+
+  const double* rg = a.r + (size_t)task * a.nlags;
+  double f[NG][C], b[NG][C], rr[NG][C];
+#pragma unroll
+  for (int G = 0; G < NG; ++G)
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const int i = GE * G + C * g + c;
+      rr[G][c] = (i + 1 < a.nlags) ? __ldg(rg + i + 1) : 0.0;
+      f[G][c] = 0.0;
+      b[G][c] = 0.0;
+    }
+  const double r0 = __ldg(rg);
+  if (g0) { f[0][0] = 1.0; b[0][0] = 1.0; }
+
+  // ---- Levinson-Durbin ----
+  // orders 1..4 peeled, then unguarded blocks of five orders m = 5 qb + t (no branch between the orders, so the
+  // registers stay where they are), then the p % 5 leftover orders
+  double E = r0;
+  int bad = 0;
+  double acc = __shfl_sync(0xffffffffu, rr[0][0], gbase);  // r[1]
+  if (p >= 1) lev_order<NG, 0, 1>(f, b, rr, acc, E, bad, g0, src_prev);
+  if (p >= 2) lev_order<NG, 0, 2>(f, b, rr, acc, E, bad, g0, src_prev);
+  if (p >= 3) lev_order<NG, 0, 3>(f, b, rr, acc, E, bad, g0, src_prev);
+  if (p >= 4) lev_order<NG, 0, 4>(f, b, rr, acc, E, bad, g0, src_prev);
+  const int qb_full = (p >= 4) ? (p - 4) / C : 0;  // last block whose five orders are all <= p
+  lev_phase<NG, 0>(f, b, rr, acc, E, bad, g0, src_prev, qb_full);
+  {
+    const int m0 = C * (qb_full + 1);
+    if (p >= 4 && m0 <= p) lev_order<NG, NG - 1, 0>(f, b, rr, acc, E, bad, g0, src_prev);
+    if (p >= 4 && m0 + 1 <= p) lev_order<NG, NG - 1, 1>(f, b, rr, acc, E, bad, g0, src_prev);
+    if (p >= 4 && m0 + 2 <= p) lev_order<NG, NG - 1, 2>(f, b, rr, acc, E, bad, g0, src_prev);
+    if (p >= 4 && m0 + 3 <= p) lev_order<NG, NG - 1, 3>(f, b, rr, acc, E, bad, g0, src_prev);
+  }
+
+  // ---- gain: gg = r[0] + sum_{i=0..p} a[i] * r[i+1]  (features.py:228) ----
+  double gpart = 0.0;
+#pragma unroll
+  for (int G = 0; G < NG; ++G)
+#pragma unroll
+    for (int c = 0; c < C; ++c) gpart = fma(f[G][c], rr[G][c], gpart);
+  const double gg = r0 + group_sum8(gpart);
+  if (!(gg > 0.0) || !isfinite(gg)) bad |= FDLP_ST_NONFINITE;
+  if (live) {
+    if (a.lpc_out) {
+#pragma unroll
+      for (int G = 0; G < NG; ++G)
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          const int i = GE * G + C * g + c;
+          if (i <= p) a.lpc_out[(size_t)task * (p + 1) + i] = f[G][c];
+        }
+    }
+    if (a.gain_out && g0) a.gain_out[task] = gg;
+  }
+
+  // ---- LPC -> cepstrum (features.py:233-246): x[i] = -a[i] (i >= 1), zero beyond the order ----
+  // rr := mc (m * cep[m] at element m, element 0 stays 0);  b := y, y^(n)_m = x[n - m]
+  double* msg = a.ms + (size_t)task * a.Lp;
+#pragma unroll
+  for (int G = 0; G < NG; ++G)
+#pragma unroll
+    for (int c = 0; c < C; ++c) { f[G][c] = -f[G][c]; b[G][c] = 0.0; rr[G][c] = 0.0; }
+  const double c0 = log(sqrt(gg));
+  const double c1 = (L > 1) ? __shfl_sync(0xffffffffu, f[0][1], gbase) : 0.0;  // x[1]
+  if (g0) { rr[0][1] = c1; b[0][0] = c1; }  // 1 * cep[1];  y^(1): element 0 = x[1]
+  if (g0 && live) {
+    msg[0] = c0 * a.weights[0];
+    if (L > 1) msg[1] = c1 * a.weights[1];
+    if (a.cep_out) { a.cep_out[(size_t)task * L] = c0; if (L > 1) a.cep_out[(size_t)task * L + 1] = c1; }
+  }
+  if (L > 2) cep_step<NG, 0, 2>(f, b, rr, 2, 0, a, msg, task, live, g, gbase, src_prev);
+  if (L > 3) cep_step<NG, 0, 3>(f, b, rr, 3, 0, a, msg, task, live, g, gbase, src_prev);
+  if (L > 4) cep_step<NG, 0, 4>(f, b, rr, 4, 0, a, msg, task, live, g, gbase, src_prev);
+  const int nb_full = (L >= 5) ? (L - 5) / C : 0;  // last block n = 5 qb .. 5 qb + 4 with 5 qb + 4 <= L - 1
+  cep_phase<NG, 0>(f, b, rr, nb_full, a, msg, task, live, g, gbase, src_prev);
+  {
+    const int n0 = C * (nb_full + 1), xg = (nb_full + 1) >> 3;
+    if (L >= 5 && n0 <= L - 1) cep_step<NG, NG - 1, 0>(f, b, rr, n0, xg, a, msg, task, live, g, gbase, src_prev);
+    if (L >= 5 && n0 + 1 <= L - 1) cep_step<NG, NG - 1, 1>(f, b, rr, n0 + 1, xg, a, msg, task, live, g, gbase, src_prev);
+    if (L >= 5 && n0 + 2 <= L - 1) cep_step<NG, NG - 1, 2>(f, b, rr, n0 + 2, xg, a, msg, task, live, g, gbase, src_prev);
+    if (L >= 5 && n0 + 3 <= L - 1) cep_step<NG, NG - 1, 3>(f, b, rr, n0 + 3, xg, a, msg, task, live, g, gbase, src_prev);
+  }
+  if (live && g0) for (int n = L; n < a.Lp; ++n) msg[n] = 0.0;
+
+  if (bad && live && a.status && g0) {
+    const int seg = task / a.J;
+    atomicOr(a.status + (a.seg_utt ? a.seg_utt[seg] : seg), bad);
+  }
+  }  // grid-stride loop
+}
+
 // ---------------------------------------------------------------------------------------------------
 // K5: env[task, t] = exp( sum_n ms[task, n] * cos(2 pi n t / M) ) * wratio[t],  t < kk
 // One warp owns 8 tasks (the DMMA M dimension) and NT blocks of 8 output frames; the cosine basis

@@ -131,6 +131,22 @@ __host__ __device__ constexpr int bitrev_c(int i, int bits) {
 }
 __host__ __device__ constexpr int ilog2_c(int n) { return n <= 1 ? 0 : 1 + ilog2_c(n >> 1); }
 
+// w^i for w = exp(-2 pi j / 32) as (c, s) with w^i = c - j s; i is a compile-time constant after unrolling
+__device__ __forceinline__ float w32c(int i) { i &= 31; return i < 16 ? kW32c[i] : -kW32c[i - 16]; }
+__device__ __forceinline__ float w32s(int i) { i &= 31; return i < 16 ? kW32s[i] : -kW32s[i - 16]; }
+
+// acc += z * (c - j s); the comparisons fold at compile time, so the trivial roots cost two adds
+__device__ __forceinline__ void cmac_w(float2& acc, const float2 z, const float c, const float s) {
+  if (s == 0.f && c == 1.f) { acc.x += z.x; acc.y += z.y; }
+  else if (s == 0.f && c == -1.f) { acc.x -= z.x; acc.y -= z.y; }
+  else if (c == 0.f && s == 1.f) { acc.x += z.y; acc.y -= z.x; }
+  else if (c == 0.f && s == -1.f) { acc.x -= z.y; acc.y += z.x; }
+  else {
+    acc.x = fmaf(z.y, s, fmaf(z.x, c, acc.x));
+    acc.y = fmaf(-z.x, s, fmaf(z.y, c, acc.y));
+  }
+}
+
 // forward DFT of N (16 or 32) points, natural order in and out, fully unrolled (all indices compile-time)
 template <int N, int LEN>
 __device__ __forceinline__ void fft_reg_stage(float2 (&a)[N]) {
@@ -140,10 +156,12 @@ __device__ __forceinline__ void fft_reg_stage(float2 (&a)[N]) {
     for (int k = 0; k < LEN / 2; ++k) {
       const float c = kW32c[(32 / LEN) * k], s = kW32s[(32 / LEN) * k];  // w = c - j s
       const float2 v = a[i + k + LEN / 2];
-      const float2 t = make_float2(v.x * c + v.y * s, v.y * c - v.x * s);
       const float2 u = a[i + k];
-      a[i + k] = make_float2(u.x + t.x, u.y + t.y);
-      a[i + k + LEN / 2] = make_float2(u.x - t.x, u.y - t.y);
+      float2 p = u, m = u;
+      cmac_w(p, v, c, s);
+      cmac_w(m, v, -c, -s);
+      a[i + k] = p;
+      a[i + k + LEN / 2] = m;
     }
   }
   if constexpr (LEN < N) fft_reg_stage<N, LEN * 2>(a);
@@ -160,6 +178,29 @@ __device__ __forceinline__ void fft_reg(float2 (&a)[N]) {
   fft_reg_stage<N, 2>(a);
 }
 
+// N-point DFT of a sequence whose rows m >= M are zero (short frames in a long FFT): direct sums split into the
+// even and odd rows, y[k] = E + O, y[k + N/2] = E - O
+template <int N, int M>
+__device__ __forceinline__ void dft_pruned(const float2 (&v)[M], float2 (&y)[N]) {
+#pragma unroll
+  for (int k = 0; k < N / 2; ++k) {
+    float2 E = v[0], O = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int m = 1; m < M; ++m) {
+      const int idx = (32 / N) * ((m * k) % N);
+      if (m & 1) {
+        if (m == 1) {
+          const float c = w32c(idx), s = w32s(idx);
+          if (s == 0.f) O = v[1];
+          else O = make_float2(fmaf(v[1].y, s, v[1].x * c), fmaf(-v[1].x, s, v[1].y * c));
+        } else cmac_w(O, v[m], w32c(idx), w32s(idx));
+      } else cmac_w(E, v[m], w32c(idx), w32s(idx));
+    }
+    y[k] = make_float2(E.x + O.x, E.y + O.y);
+    y[k + N / 2] = make_float2(E.x - O.x, E.y - O.y);
+  }
+}
+
 struct MelWarpArgs {
   const void* wav;
   const int64_t* utt_wav_off;
@@ -167,12 +208,12 @@ struct MelWarpArgs {
   const int32_t* frame_utt;  // [n_frames]
   int64_t n_frames;
   int flen, shift, nfft, n;  // n = nfft/2 = 32 * R2
-  const float* ham;          // [flen]
+  const float* ham;          // [nfft] window, zero beyond min(flen, nfft)
   const float2* tw4;         // [R2][32]  W_n^(k1 * lane)
   const float2* unpackA;     // [n+1] exp(-2 pi i k / nfft)
-  const float* fbank;        // [J, n+1]
-  const int32_t* band_lo;
-  const int32_t* band_hi;
+  const float* wts;          // filter weights: band j, bin b at wts[band[j].z + b - band[j].x]
+  const int4* band;          // [J] {first bin, bin count, offset into wts, 0}
+  int wts_smem;              // > 0: number of weights to stage in shared memory; 0: read wts from global
   float* feats;              // [n_frames, J]
   double* cmvn;              // [2, J+1] or null
   int J, power;
@@ -181,25 +222,93 @@ struct MelWarpArgs {
 constexpr int kMelWarps = 8;
 constexpr int kMelMaxBandsPerLane = 4;  // J <= 128
 
-template <int R2, typename S>
+__host__ __device__ constexpr size_t mel_warp_smem_bytes(int R2, int J, int wts_smem) {
+  // per warp tile [R2][33] float2 | twiddles [R2][32] float2 | unpack [n/2+1] float2 (+pad) | band int4[J] |
+  // band sums [warps][J] float | staged weights
+  return (size_t)kMelWarps * R2 * 33 * 8 + (size_t)R2 * 32 * 8 + (size_t)(16 * R2 + 2) * 8 + (size_t)J * 16 +
+         (size_t)kMelWarps * J * 4 + (size_t)wts_smem * 4;
+}
+
+template <typename S>
+__device__ __forceinline__ float2 load_pair(const S* p, bool aligned);
+template <>
+__device__ __forceinline__ float2 load_pair<int16_t>(const int16_t* p, bool aligned) {
+  if (aligned) {
+    const uint32_t u = __ldg(reinterpret_cast<const uint32_t*>(p));
+    return make_float2((float)(int16_t)(u & 0xffffu), (float)(int16_t)(u >> 16));
+  }
+  return make_float2((float)__ldg(p), (float)__ldg(p + 1));
+}
+template <>
+__device__ __forceinline__ float2 load_pair<float>(const float* p, bool) {
+  return make_float2(__ldg(p), __ldg(p + 1));
+}
+
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// |X[k]| and |X[n-k]| of the real transform from Z[k], Z[n-k] of the packed complex transform
+__device__ __forceinline__ void unpack_mag(const float2 zk, const float2 zc, const float2 A, float& pm, float& mm) {
+  const float ex = 0.5f * (zk.x + zc.x), ey = 0.5f * (zk.y - zc.y);
+  const float dx = 0.5f * (zk.x - zc.x), dy = 0.5f * (zk.y + zc.y);
+  const float adx = A.x * dx - A.y * dy, ady = A.x * dy + A.y * dx;
+  const float px = ex + ady, py = ey - adx, mx = ex - ady, my = ey + adx;
+  pm = sqrt_approx(px * px + py * py);
+  mm = sqrt_approx(mx * mx + my * my);
+}
+
+__device__ __forceinline__ float band_dot(const float* magf, const float* w, int lo, int cnt, int q) {
+  float s0 = 0.f, s1 = 0.f;
+  int t = q;
+  for (; t + 4 < cnt; t += 8) {
+    s0 = fmaf(magf[2 * (lo + t)], w[t], s0);
+    s1 = fmaf(magf[2 * (lo + t + 4)], w[t + 4], s1);
+  }
+  if (t < cnt) s0 = fmaf(magf[2 * (lo + t)], w[t], s0);
+  return s0 + s1;
+}
+
+// M1 > 0: only the first M1 packed rows (64 M1 samples) of a frame are non-zero and the first FFT step is the
+// pruned DFT; M1 == 0: any frame length, full R2-point FFT.
+template <int R2, int M1, typename S>
 __global__ void __launch_bounds__(kMelWarps * 32, 2) mel_frames_warp_kernel(const MelWarpArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int n = 32 * R2;
   constexpr int TS = 33;  // transpose row stride (float2)
+  constexpr int NV = M1 > 0 ? M1 : R2;
+  float2* tiles = reinterpret_cast<float2*>(smem_raw);
+  float2* s_tw = tiles + kMelWarps * R2 * TS;
+  float2* s_A = s_tw + R2 * 32;
+  int4* s_band = reinterpret_cast<int4*>(s_A + 16 * R2 + 2);
+  float* s_sum = reinterpret_cast<float*>(s_band + a.J) + warp * a.J;
+  float* s_wts = reinterpret_cast<float*>(s_band + a.J) + kMelWarps * a.J;
+  for (int i = threadIdx.x; i < R2 * 32; i += blockDim.x) s_tw[i] = a.tw4[i];
+  for (int i = threadIdx.x; i <= n / 2; i += blockDim.x) s_A[i] = a.unpackA[i];
+  for (int i = threadIdx.x; i < a.J; i += blockDim.x) s_band[i] = a.band[i];
+  for (int i = threadIdx.x; i < a.wts_smem; i += blockDim.x) s_wts[i] = a.wts[i];
+  __syncthreads();
   // per warp: transpose tile [R2][33] float2, reused for Z[n] (natural order) once every lane holds its row in
-  // registers, followed by mag[n+1] floats
-  constexpr int kWarpF2 = R2 * TS + (n + 4) / 2;
-  float2* tile = reinterpret_cast<float2*>(smem_raw) + (size_t)warp * kWarpF2;
+  // registers; the magnitudes then overwrite the real parts in place (|X[k]| at zl[k].x, k <= n)
+  float2* tile = tiles + (size_t)warp * R2 * TS;
   float2* zl = tile;
-  float* mag = reinterpret_cast<float*>(tile + R2 * TS);
+  const float* magf = reinterpret_cast<const float*>(tile);
   const int ext = (a.flen % 2 == 0) ? a.flen / 2 - 1 : (a.flen - 1) / 2;
   const int used = a.flen < a.nfft ? a.flen : a.nfft;  // fft(x, nfft) truncates longer frames
   const int m1_hi = (used + 63) / 64;                   // rows m1 with a non-zero sample (m = 32 m1 + lane < used/2)
+  float2 hw[NV];
+  if constexpr (M1 > 0) {
+#pragma unroll
+    for (int m1 = 0; m1 < M1; ++m1) hw[m1] = make_float2(__ldg(a.ham + 2 * (32 * m1 + lane)), __ldg(a.ham + 2 * (32 * m1 + lane) + 1));
+  }
   double cs1[kMelMaxBandsPerLane], cs2[kMelMaxBandsPerLane];
 #pragma unroll
   for (int i = 0; i < kMelMaxBandsPerLane; ++i) cs1[i] = cs2[i] = 0.0;
   long long nfr_done = 0;
+  const int g = lane >> 2, q = lane & 3;
 
   const long long wstride = (long long)gridDim.x * kMelWarps;
   for (long long fr = (long long)blockIdx.x * kMelWarps + warp; fr < a.n_frames; fr += wstride) {
@@ -209,23 +318,36 @@ __global__ void __launch_bounds__(kMelWarps * 32, 2) mel_frames_warp_kernel(cons
     const int64_t T = a.utt_wav_off[u + 1] - woff;
     const S* sig = reinterpret_cast<const S*>(a.wav) + woff;
     const int64_t q0 = (int64_t)kf * a.shift - ext;
-    float2 v[R2];
+    const int rows = M1 > 0 ? M1 : m1_hi;
+    const bool interior = q0 >= 0 && q0 + 64 * rows <= T;
+    const bool aligned = (reinterpret_cast<uintptr_t>(sig + q0) & 3) == 0;
+    float2 v[NV];
 #pragma unroll
-    for (int m1 = 0; m1 < R2; ++m1) {
+    for (int m1 = 0; m1 < NV; ++m1) {
       float2 z = make_float2(0.f, 0.f);
-      if (m1 < m1_hi) {
+      if (M1 > 0 || m1 < m1_hi) {
         const int i0 = 2 * (32 * m1 + lane);
-        if (i0 < used) z.x = (float)sig[reflect_index(q0 + i0, T)] * __ldg(a.ham + i0);
-        if (i0 + 1 < used) z.y = (float)sig[reflect_index(q0 + i0 + 1, T)] * __ldg(a.ham + i0 + 1);
+        float2 x;
+        if (interior) x = load_pair<S>(sig + q0 + i0, aligned);
+        else x = make_float2((float)sig[reflect_index(q0 + i0, T)], (float)sig[reflect_index(q0 + i0 + 1, T)]);
+        float2 h;
+        if constexpr (M1 > 0) h = hw[m1];
+        else h = make_float2(__ldg(a.ham + i0), __ldg(a.ham + i0 + 1));
+        z = make_float2(x.x * h.x, x.y * h.y);
       }
       v[m1] = z;
     }
-    fft_reg<R2>(v);
+    float2 y[R2];
+    if constexpr (M1 > 0) dft_pruned<R2, M1>(v, y);
+    else {
+#pragma unroll
+      for (int k1 = 0; k1 < R2; ++k1) y[k1] = v[k1];
+      fft_reg<R2>(y);
+    }
 #pragma unroll
     for (int k1 = 0; k1 < R2; ++k1) {
-      const float2 w = __ldg(a.tw4 + k1 * 32 + lane);
-      const float2 y = make_float2(v[k1].x * w.x - v[k1].y * w.y, v[k1].x * w.y + v[k1].y * w.x);
-      tile[k1 * TS + lane] = y;
+      const float2 w = s_tw[k1 * 32 + lane];
+      tile[k1 * TS + lane] = make_float2(y[k1].x * w.x - y[k1].y * w.y, y[k1].x * w.y + y[k1].y * w.x);
     }
     __syncwarp();
     if (lane < R2) {
@@ -238,30 +360,51 @@ __global__ void __launch_bounds__(kMelWarps * 32, 2) mel_frames_warp_kernel(cons
       for (int k2 = 0; k2 < 32; ++k2) zl[lane + R2 * k2] = c[k2];
     }
     __syncwarp();
-    // unpack the packed real transform: X[k] = E - j A D,  E = (Z[k] + conj Z[n-k]) / 2,  D = (Z[k] - conj Z[n-k]) / 2
-    for (int kq = lane; kq <= n; kq += 32) {
-      const float2 zk = zl[(kq == n) ? 0 : kq];
-      float2 zc = zl[(kq == 0) ? 0 : n - kq];
-      zc.y = -zc.y;
-      const float ex = 0.5f * (zk.x + zc.x), ey = 0.5f * (zk.y + zc.y);
-      const float dx = 0.5f * (zk.x - zc.x), dy = 0.5f * (zk.y - zc.y);
-      const float2 A = __ldg(a.unpackA + kq);
-      const float adx = A.x * dx - A.y * dy, ady = A.x * dy + A.y * dx;
-      const float vx = ex + ady, vy = ey - adx;
-      mag[kq] = sqrtf(vx * vx + vy * vy);
+    // unpack the packed real transform in place, bins k and n-k together:
+    //   X[k] = E - j A D,  X[n-k] = conj(E + j A D),  E = (Z[k] + conj Z[n-k]) / 2,  D = (Z[k] - conj Z[n-k]) / 2
+    for (int t0 = 0; t0 < n / 64; t0 += 4) {
+      float2 zk[4], zc[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int k = lane + 32 * (t0 + i);
+        zk[i] = zl[k];
+        zc[i] = zl[(n - k) & (n - 1)];
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int k = lane + 32 * (t0 + i);
+        float pm, mm;
+        unpack_mag(zk[i], zc[i], s_A[k], pm, mm);
+        zl[k].x = pm;
+        zl[n - k].x = mm;
+      }
+    }
+    if (lane == 0) {
+      float pm, mm;
+      unpack_mag(zl[n / 2], zl[n / 2], s_A[n / 2], pm, mm);
+      zl[n / 2].x = pm;
+    }
+    __syncwarp();
+    // filter bank: four lanes per band, eight bands per round; the band sums go through shared memory so that
+    // the log, the store and the CMVN sums run one band per lane
+    for (int j0 = 0; j0 < a.J; j0 += 8) {
+      const int j = j0 + g;
+      float s = 0.f;
+      if (j < a.J) {
+        const int4 bi = s_band[j];
+        if (a.wts_smem > 0) s = band_dot(magf, s_wts + bi.z, bi.x, bi.y, q);
+        else s = band_dot(magf, a.wts + bi.z, bi.x, bi.y, q);
+      }
+      s += __shfl_xor_sync(0xffffffffu, s, 1);
+      s += __shfl_xor_sync(0xffffffffu, s, 2);
+      if (q == 0 && j < a.J) s_sum[j] = s;
     }
     __syncwarp();
 #pragma unroll
     for (int i = 0; i < kMelMaxBandsPerLane; ++i) {
       const int j = lane + 32 * i;
       if (j < a.J) {
-        const int lo = a.band_lo[j], hi = a.band_hi[j];
-        const float* w = a.fbank + (size_t)j * (n + 1);
-        float s0 = 0.f, s1 = 0.f;
-        int b = lo;
-        for (; b + 1 < hi; b += 2) { s0 = fmaf(mag[b], __ldg(w + b), s0); s1 = fmaf(mag[b + 1], __ldg(w + b + 1), s1); }
-        if (b < hi) s0 = fmaf(mag[b], __ldg(w + b), s0);
-        const float s = s0 + s1;
+        const float s = s_sum[j];
         const float o = a.power ? s * s : log10f(s);
         a.feats[fr * a.J + j] = o;
         cs1[i] += (double)o;
