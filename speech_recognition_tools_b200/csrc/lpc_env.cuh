@@ -302,63 +302,104 @@ __global__ void __launch_bounds__(128, (NS > 8) ? 3 : 5) lpc_cepstrum_reg_kernel
 // and because the order loop is unrolled by five every index is a compile-time constant.  Only the register
 // that leaves the lane goes through a shuffle: 2 SHFL + 2 FSEL per 15 DFMA.
 // Physical register q of the shifting vector holds logical position (q + rho) mod 5 after rho shifts.
+// 64-bit shuffles as two explicit 32-bit halves
+__device__ __forceinline__ double shfl_idx_d(const double v, const int src) {
+  const int lo = __shfl_sync(0xffffffffu, __double2loint(v), src);
+  const int hi = __shfl_sync(0xffffffffu, __double2hiint(v), src);
+  return __hiloint2double(hi, lo);
+}
+__device__ __forceinline__ double shfl_xor_d(const double v, const int mask) {
+  const int lo = __shfl_xor_sync(0xffffffffu, __double2loint(v), mask);
+  const int hi = __shfl_xor_sync(0xffffffffu, __double2hiint(v), mask);
+  return __hiloint2double(hi, lo);
+}
+// sum over the 8 lanes of a group, bit-identical in every lane (each level adds a symmetric pair)
+__device__ __forceinline__ double group_sum8_d(double v) {
+  v += shfl_xor_d(v, 4);
+  v += shfl_xor_d(v, 2);
+  v += shfl_xor_d(v, 1);
+  return v;
+}
+
+// 1 / x for normal-range x: the MUFU seed and the two Newton steps of the library reciprocal without its
+// special-case branch.  x == 0, denormal, infinite or NaN give a non-finite result, which the recursion
+// carries to the end where it is reported as FDLP_ST_SINGULAR.
+__device__ __forceinline__ double rcp_newton(const double x) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double e = fma(-x, y, 1.0);
+  e = fma(e, e, e);
+  y = fma(y, e, y);
+  e = fma(-x, y, 1.0);
+  return fma(y, e, y);
+}
+
 // One Levinson order m (T = m % 5, groups 0..PH hold elements 0..m):
 //   f' = f + k shift(b),  b' = shift(b) + k f,  acc' = sum_j b'_j r[j+1]
+// (Forming acc' as S1 + k S2 from lane-local sums that do not need k shortens the serial chain but costs five
+// more DFMA per group and order; measured, the FP64 pipe then sets the time: 5.6 ms against 5.98 ms.)
 template <int NG, int PH, int T>
 __device__ __forceinline__ void lev_order(double (&f)[NG][5], double (&b)[NG][5], const double (&rr)[NG][5],
-                                          double& acc, double& E, int& bad, const bool g0, const int src_prev) {
+                                          double& acc, double& E, const bool g0, const int src_prev) {
   constexpr int C = 5;
-  if (E == 0.0 || !isfinite(E)) bad = FDLP_ST_SINGULAR;
-  const double k = -acc * __drcp_rn(E);
   constexpr int qo = (C - T) % C;  // m - 1 shifts so far: logical 4 sits in register (4 - (m - 1)) mod 5
   double tin[PH + 1];
 #pragma unroll
-  for (int G = 0; G <= PH; ++G) tin[G] = __shfl_sync(0xffffffffu, b[G][qo], src_prev);
+  for (int G = 0; G <= PH; ++G) tin[G] = shfl_idx_d(b[G][qo], src_prev);
 #pragma unroll
   for (int G = PH; G >= 0; --G) {
     const double from_prev_group = (G > 0) ? tin[G > 0 ? G - 1 : 0] : 0.0;
     b[G][qo] = g0 ? from_prev_group : tin[G];
   }
-  double part[PH + 1];
+  const double k = -acc * rcp_newton(E);
+  E *= (1.0 - k * k);
+  double pa[PH + 1], pb[PH + 1];  // two partial sums per group: 3 + 2 terms
 #pragma unroll
   for (int G = 0; G <= PH; ++G) {
-    part[G] = 0.0;
 #pragma unroll
     for (int c = 0; c < C; ++c) {
-      const int q = (c - T + C) % C;  // after this order's shift logical c sits in register (c - m) mod 5
+      const int q = (c - T + C) % C;  // after the shift logical c sits in register (c - m) mod 5
       const double sb = b[G][q];
       const double fo = f[G][c];
       f[G][c] = fma(k, sb, fo);
       const double nb = fma(k, fo, sb);
       b[G][q] = nb;
-      part[G] = fma(nb, rr[G][c], part[G]);
+      if (c == 0) pa[G] = nb * rr[G][c];
+      else if (c == 1) pb[G] = nb * rr[G][c];
+      else if (c & 1) pb[G] = fma(nb, rr[G][c], pb[G]);
+      else pa[G] = fma(nb, rr[G][c], pa[G]);
     }
   }
-  double tot = part[0];
-#pragma unroll
-  for (int G = 1; G <= PH; ++G) tot += part[G];
-  acc = group_sum8(tot);
-  E *= (1.0 - k * k);
+  // balanced sum of the 2 (PH + 1) partials
+  double t0 = pa[0] + pb[0];
+  if constexpr (PH >= 1) { const double t1 = pa[1] + pb[1]; t0 += t1; }
+  if constexpr (PH >= 2) {
+    double t2 = pa[2] + pb[2];
+    if constexpr (PH >= 3) { const double t3 = pa[3] + pb[3]; t2 += t3; }
+    t0 += t2;
+  }
+  acc = group_sum8_d(t0);
 }
 
 // One cepstrum step n (T = n % 5): y shifts by one with x[n] entering at element 0, v = x[n] + (1/n) sum mc y.
+// x[n] is not needed after this step, so cep[n] = v takes its place in x: the step has no store and no
+// divergent branch, and the kernel writes the whole cepstrum at the end.
 // xg: group that holds element n of x (compile-time PH in the main loop, run-time in the tail).
 template <int NG, int PH, int T>
-__device__ __forceinline__ void cep_step(const double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5],
-                                         const int n, const int xg, const LpcArgs& a, double* msg, const int task,
-                                         const bool live, const int g, const int gbase, const int src_prev) {
+__device__ __forceinline__ void cep_step(double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5], const int n,
+                                         const int xg, const LpcArgs& a, const int g, const int gbase,
+                                         const int src_prev) {
   constexpr int C = 5;
   double xv = x[PH][T];
-  if (xg != PH) {
 #pragma unroll
-    for (int G = 0; G < PH; ++G) if (G == xg) xv = x[G][T];
-  }
+  for (int G = 0; G < PH; ++G) xv = (G == xg) ? x[G][T] : xv;
   const int xl = (n / C) & 7;
-  const double xn = (n <= a.order) ? __shfl_sync(0xffffffffu, xv, gbase | xl) : 0.0;
+  double xn = shfl_idx_d(xv, gbase | xl);
+  xn = (n <= a.order) ? xn : 0.0;
   constexpr int qo = (1 - T + C) % C;  // n - 2 shifts so far
   double tin[PH + 1];
 #pragma unroll
-  for (int G = 0; G <= PH; ++G) tin[G] = __shfl_sync(0xffffffffu, y[G][qo], src_prev);
+  for (int G = 0; G <= PH; ++G) tin[G] = shfl_idx_d(y[G][qo], src_prev);
 #pragma unroll
   for (int G = PH; G >= 0; --G) {
     const double from_prev_group = (G > 0) ? tin[G > 0 ? G - 1 : 0] : xn;
@@ -369,19 +410,21 @@ __device__ __forceinline__ void cep_step(const double (&x)[NG][5], double (&y)[N
   for (int G = 0; G <= PH; ++G) {
     part[G] = 0.0;
 #pragma unroll
-    for (int c = 0; c < C; ++c) part[G] = fma(mc[G][c], y[G][(c - T + 1 + C) % C], part[G]);
+    for (int cc = 0; cc < C; ++cc) {  // element n - 1 (register (T - 1) mod 5), written by the previous step, goes last
+      const int c = (T + cc) % C;
+      part[G] = fma(mc[G][c], y[G][(c - T + 1 + C) % C], part[G]);
+    }
   }
   double tot = part[0];
 #pragma unroll
   for (int G = 1; G <= PH; ++G) tot += part[G];
-  const double v = fma(group_sum8(tot), __ldg(a.inv_n + n), xn);
+  const double v = fma(group_sum8_d(tot), __ldg(a.inv_n + n), xn);
   const double vn = v * (double)n;
 #pragma unroll
-  for (int G = 0; G <= PH; ++G)
-    if (G == PH || G == xg) mc[G][T] = (g == xl && G == xg) ? vn : mc[G][T];
-  if (g == 0 && live) {
-    msg[n] = v * __ldg(a.weights + n);
-    if (a.cep_out) a.cep_out[(size_t)task * a.L + n] = v;
+  for (int G = 0; G <= PH; ++G) {
+    const bool here = (g == xl) && (G == xg);
+    mc[G][T] = here ? vn : mc[G][T];
+    x[G][T] = here ? v : x[G][T];
   }
 }
 
@@ -389,37 +432,37 @@ __device__ __forceinline__ void cep_step(const double (&x)[NG][5], double (&y)[N
 // the next phase
 template <int NG, int PH>
 __device__ __forceinline__ void lev_phase(double (&f)[NG][5], double (&b)[NG][5], const double (&rr)[NG][5],
-                                          double& acc, double& E, int& bad, const bool g0, const int src_prev,
+                                          double& acc, double& E, const bool g0, const int src_prev,
                                           const int qb_full) {
   const int qb_lo = (PH == 0) ? 1 : 8 * PH;
   const int qb_hi = (8 * PH + 7 < qb_full) ? 8 * PH + 7 : qb_full;
 #pragma unroll 1
   for (int qb = qb_lo; qb <= qb_hi; ++qb) {
-    lev_order<NG, PH, 0>(f, b, rr, acc, E, bad, g0, src_prev);
-    lev_order<NG, PH, 1>(f, b, rr, acc, E, bad, g0, src_prev);
-    lev_order<NG, PH, 2>(f, b, rr, acc, E, bad, g0, src_prev);
-    lev_order<NG, PH, 3>(f, b, rr, acc, E, bad, g0, src_prev);
-    lev_order<NG, PH, 4>(f, b, rr, acc, E, bad, g0, src_prev);
+    lev_order<NG, PH, 0>(f, b, rr, acc, E, g0, src_prev);
+    lev_order<NG, PH, 1>(f, b, rr, acc, E, g0, src_prev);
+    lev_order<NG, PH, 2>(f, b, rr, acc, E, g0, src_prev);
+    lev_order<NG, PH, 3>(f, b, rr, acc, E, g0, src_prev);
+    lev_order<NG, PH, 4>(f, b, rr, acc, E, g0, src_prev);
   }
-  if constexpr (PH + 1 < NG) lev_phase<NG, PH + 1>(f, b, rr, acc, E, bad, g0, src_prev, qb_full);
+  if constexpr (PH + 1 < NG) lev_phase<NG, PH + 1>(f, b, rr, acc, E, g0, src_prev, qb_full);
 }
 
 template <int NG, int PH>
-__device__ __forceinline__ void cep_phase(const double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5],
-                                          const int nb_full, const LpcArgs& a, double* msg, const int task,
-                                          const bool live, const int g, const int gbase, const int src_prev) {
+__device__ __forceinline__ void cep_phase(double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5],
+                                          const int nb_full, const LpcArgs& a, const int g, const int gbase,
+                                          const int src_prev) {
   const int qb_lo = (PH == 0) ? 1 : 8 * PH;
   const int qb_hi = (8 * PH + 7 < nb_full) ? 8 * PH + 7 : nb_full;
 #pragma unroll 1
   for (int qb = qb_lo; qb <= qb_hi; ++qb) {
     const int n0 = 5 * qb;
-    cep_step<NG, PH, 0>(x, y, mc, n0, PH, a, msg, task, live, g, gbase, src_prev);
-    cep_step<NG, PH, 1>(x, y, mc, n0 + 1, PH, a, msg, task, live, g, gbase, src_prev);
-    cep_step<NG, PH, 2>(x, y, mc, n0 + 2, PH, a, msg, task, live, g, gbase, src_prev);
-    cep_step<NG, PH, 3>(x, y, mc, n0 + 3, PH, a, msg, task, live, g, gbase, src_prev);
-    cep_step<NG, PH, 4>(x, y, mc, n0 + 4, PH, a, msg, task, live, g, gbase, src_prev);
+    cep_step<NG, PH, 0>(x, y, mc, n0, PH, a, g, gbase, src_prev);
+    cep_step<NG, PH, 1>(x, y, mc, n0 + 1, PH, a, g, gbase, src_prev);
+    cep_step<NG, PH, 2>(x, y, mc, n0 + 2, PH, a, g, gbase, src_prev);
+    cep_step<NG, PH, 3>(x, y, mc, n0 + 3, PH, a, g, gbase, src_prev);
+    cep_step<NG, PH, 4>(x, y, mc, n0 + 4, PH, a, g, gbase, src_prev);
   }
-  if constexpr (PH + 1 < NG) cep_phase<NG, PH + 1>(x, y, mc, nb_full, a, msg, task, live, g, gbase, src_prev);
+  if constexpr (PH + 1 < NG) cep_phase<NG, PH + 1>(x, y, mc, nb_full, a, g, gbase, src_prev);
 }
 
 template <int NG>
@@ -457,19 +500,22 @@ __global__ void __launch_bounds__(128, (NG > 2) ? 3 : 5) lpc_cepstrum_blk_kernel
   double E = r0;
   int bad = 0;
   double acc = __shfl_sync(0xffffffffu, rr[0][0], gbase);  // r[1]
-  if (p >= 1) lev_order<NG, 0, 1>(f, b, rr, acc, E, bad, g0, src_prev);
-  if (p >= 2) lev_order<NG, 0, 2>(f, b, rr, acc, E, bad, g0, src_prev);
-  if (p >= 3) lev_order<NG, 0, 3>(f, b, rr, acc, E, bad, g0, src_prev);
-  if (p >= 4) lev_order<NG, 0, 4>(f, b, rr, acc, E, bad, g0, src_prev);
+  if (p >= 1) lev_order<NG, 0, 1>(f, b, rr, acc, E, g0, src_prev);
+  if (p >= 2) lev_order<NG, 0, 2>(f, b, rr, acc, E, g0, src_prev);
+  if (p >= 3) lev_order<NG, 0, 3>(f, b, rr, acc, E, g0, src_prev);
+  if (p >= 4) lev_order<NG, 0, 4>(f, b, rr, acc, E, g0, src_prev);
   const int qb_full = (p >= 4) ? (p - 4) / C : 0;  // last block whose five orders are all <= p
-  lev_phase<NG, 0>(f, b, rr, acc, E, bad, g0, src_prev, qb_full);
+  lev_phase<NG, 0>(f, b, rr, acc, E, g0, src_prev, qb_full);
   {
     const int m0 = C * (qb_full + 1);
-    if (p >= 4 && m0 <= p) lev_order<NG, NG - 1, 0>(f, b, rr, acc, E, bad, g0, src_prev);
-    if (p >= 4 && m0 + 1 <= p) lev_order<NG, NG - 1, 1>(f, b, rr, acc, E, bad, g0, src_prev);
-    if (p >= 4 && m0 + 2 <= p) lev_order<NG, NG - 1, 2>(f, b, rr, acc, E, bad, g0, src_prev);
-    if (p >= 4 && m0 + 3 <= p) lev_order<NG, NG - 1, 3>(f, b, rr, acc, E, bad, g0, src_prev);
+    if (p >= 4 && m0 <= p) lev_order<NG, NG - 1, 0>(f, b, rr, acc, E, g0, src_prev);
+    if (p >= 4 && m0 + 1 <= p) lev_order<NG, NG - 1, 1>(f, b, rr, acc, E, g0, src_prev);
+    if (p >= 4 && m0 + 2 <= p) lev_order<NG, NG - 1, 2>(f, b, rr, acc, E, g0, src_prev);
+    if (p >= 4 && m0 + 3 <= p) lev_order<NG, NG - 1, 3>(f, b, rr, acc, E, g0, src_prev);
   }
+
+  // a zero or non-finite prediction error at any order turns k, and with it E, into NaN for good
+  if (!isfinite(E) || r0 == 0.0) bad = FDLP_ST_SINGULAR;
 
   // ---- gain: gg = r[0] + sum_{i=0..p} a[i] * r[i+1]  (features.py:228) ----
   double gpart = 0.0;
@@ -501,25 +547,34 @@ __global__ void __launch_bounds__(128, (NG > 2) ? 3 : 5) lpc_cepstrum_blk_kernel
     for (int c = 0; c < C; ++c) { f[G][c] = -f[G][c]; b[G][c] = 0.0; rr[G][c] = 0.0; }
   const double c0 = log(sqrt(gg));
   const double c1 = (L > 1) ? __shfl_sync(0xffffffffu, f[0][1], gbase) : 0.0;  // x[1]
-  if (g0) { rr[0][1] = c1; b[0][0] = c1; }  // 1 * cep[1];  y^(1): element 0 = x[1]
-  if (g0 && live) {
-    msg[0] = c0 * a.weights[0];
-    if (L > 1) msg[1] = c1 * a.weights[1];
-    if (a.cep_out) { a.cep_out[(size_t)task * L] = c0; if (L > 1) a.cep_out[(size_t)task * L + 1] = c1; }
-  }
-  if (L > 2) cep_step<NG, 0, 2>(f, b, rr, 2, 0, a, msg, task, live, g, gbase, src_prev);
-  if (L > 3) cep_step<NG, 0, 3>(f, b, rr, 3, 0, a, msg, task, live, g, gbase, src_prev);
-  if (L > 4) cep_step<NG, 0, 4>(f, b, rr, 4, 0, a, msg, task, live, g, gbase, src_prev);
+  if (g0) { rr[0][1] = c1; b[0][0] = c1; f[0][0] = c0; f[0][1] = c1; }  // 1 * cep[1];  y^(1)_0 = x[1];  cep[0], cep[1]
+  if (L > 2) cep_step<NG, 0, 2>(f, b, rr, 2, 0, a, g, gbase, src_prev);
+  if (L > 3) cep_step<NG, 0, 3>(f, b, rr, 3, 0, a, g, gbase, src_prev);
+  if (L > 4) cep_step<NG, 0, 4>(f, b, rr, 4, 0, a, g, gbase, src_prev);
   const int nb_full = (L >= 5) ? (L - 5) / C : 0;  // last block n = 5 qb .. 5 qb + 4 with 5 qb + 4 <= L - 1
-  cep_phase<NG, 0>(f, b, rr, nb_full, a, msg, task, live, g, gbase, src_prev);
+  cep_phase<NG, 0>(f, b, rr, nb_full, a, g, gbase, src_prev);
   {
     const int n0 = C * (nb_full + 1), xg = (nb_full + 1) >> 3;
-    if (L >= 5 && n0 <= L - 1) cep_step<NG, NG - 1, 0>(f, b, rr, n0, xg, a, msg, task, live, g, gbase, src_prev);
-    if (L >= 5 && n0 + 1 <= L - 1) cep_step<NG, NG - 1, 1>(f, b, rr, n0 + 1, xg, a, msg, task, live, g, gbase, src_prev);
-    if (L >= 5 && n0 + 2 <= L - 1) cep_step<NG, NG - 1, 2>(f, b, rr, n0 + 2, xg, a, msg, task, live, g, gbase, src_prev);
-    if (L >= 5 && n0 + 3 <= L - 1) cep_step<NG, NG - 1, 3>(f, b, rr, n0 + 3, xg, a, msg, task, live, g, gbase, src_prev);
+    if (L >= 5 && n0 <= L - 1) cep_step<NG, NG - 1, 0>(f, b, rr, n0, xg, a, g, gbase, src_prev);
+    if (L >= 5 && n0 + 1 <= L - 1) cep_step<NG, NG - 1, 1>(f, b, rr, n0 + 1, xg, a, g, gbase, src_prev);
+    if (L >= 5 && n0 + 2 <= L - 1) cep_step<NG, NG - 1, 2>(f, b, rr, n0 + 2, xg, a, g, gbase, src_prev);
+    if (L >= 5 && n0 + 3 <= L - 1) cep_step<NG, NG - 1, 3>(f, b, rr, n0 + 3, xg, a, g, gbase, src_prev);
   }
-  if (live && g0) for (int n = L; n < a.Lp; ++n) msg[n] = 0.0;
+  // f now holds the cepstrum at elements 0 .. L-1: weighted copy for K5 (zero padded to Lp), plain copy on request
+  if (live) {
+#pragma unroll
+    for (int G = 0; G < NG; ++G)
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        const int i = GE * G + C * g + c;
+        if (i < L) {
+          msg[i] = f[G][c] * __ldg(a.weights + i);
+          if (a.cep_out) a.cep_out[(size_t)task * L + i] = f[G][c];
+        } else if (i < a.Lp) {
+          msg[i] = 0.0;
+        }
+      }
+  }
 
   if (bad && live && a.status && g0) {
     const int seg = task / a.J;
