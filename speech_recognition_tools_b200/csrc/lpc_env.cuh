@@ -447,22 +447,72 @@ __device__ __forceinline__ void lev_phase(double (&f)[NG][5], double (&b)[NG][5]
   if constexpr (PH + 1 < NG) lev_phase<NG, PH + 1>(f, b, rr, acc, E, g0, src_prev, qb_full);
 }
 
+// Five cepstrum steps n = n0 .. n0 + 4 (n0 a multiple of 5, >= 5).  The sum of step n splits into the terms
+// m < n0, which need nothing from this block: the five shifts of y, the five dot products against the mc of
+// earlier blocks and the five 8-lane sums are independent and pipeline; and the at most four terms m >= n0,
+// (m cep[m]) x[n - m] with n - m <= 4, which every lane evaluates redundantly from x[1..4] (xs) in a short
+// serial chain without any shuffle.  mc and cep of the block are written to their owner lane at the end.
+template <int NG, int PH>
+__device__ __forceinline__ void cep_block(double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5], const int n0,
+                                          const double (&xs)[4], const LpcArgs& a, const int g, const int gbase,
+                                          const int src_prev) {
+  constexpr int C = 5;
+  const int xl = (n0 / C) & 7;
+  double S[C], xnv[C];
+#pragma unroll
+  for (int T = 0; T < C; ++T) {
+    double xn = shfl_idx_d(x[PH][T], gbase | xl);
+    xn = (n0 + T <= a.order) ? xn : 0.0;
+    xnv[T] = xn;
+    const int qo = (1 - T + C) % C;  // n - 2 shifts so far
+    double tin[PH + 1];
+#pragma unroll
+    for (int G = 0; G <= PH; ++G) tin[G] = shfl_idx_d(y[G][qo], src_prev);
+#pragma unroll
+    for (int G = PH; G >= 0; --G) {
+      const double from_prev_group = (G > 0) ? tin[G > 0 ? G - 1 : 0] : xn;
+      y[G][qo] = (g == 0) ? from_prev_group : tin[G];
+    }
+    double pa[PH + 1], pb[PH + 1];
+#pragma unroll
+    for (int G = 0; G <= PH; ++G) {
+      pa[G] = mc[G][0] * y[G][(0 - T + 1 + C) % C];
+      pb[G] = mc[G][1] * y[G][(1 - T + 1 + C) % C];
+      pa[G] = fma(mc[G][2], y[G][(2 - T + 1 + C) % C], pa[G]);
+      pb[G] = fma(mc[G][3], y[G][(3 - T + 1 + C) % C], pb[G]);
+      pa[G] = fma(mc[G][4], y[G][(4 - T + 1 + C) % C], pa[G]);
+    }
+    double tot = pa[0] + pb[0];
+#pragma unroll
+    for (int G = 1; G <= PH; ++G) tot += pa[G] + pb[G];
+    S[T] = group_sum8_d(tot);
+  }
+  double v[C], vn[C];
+#pragma unroll
+  for (int T = 0; T < C; ++T) {
+    double fresh = S[T];
+#pragma unroll
+    for (int d = T; d >= 1; --d) fresh = fma(vn[T - d], xs[d - 1], fresh);  // newest term (d = 1) last
+    v[T] = fma(fresh, __ldg(a.inv_n + n0 + T), xnv[T]);
+    vn[T] = v[T] * (double)(n0 + T);
+  }
+  const bool here = g == xl;
+#pragma unroll
+  for (int T = 0; T < C; ++T) {
+    mc[PH][T] = here ? vn[T] : mc[PH][T];
+    x[PH][T] = here ? v[T] : x[PH][T];
+  }
+}
+
 template <int NG, int PH>
 __device__ __forceinline__ void cep_phase(double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5],
-                                          const int nb_full, const LpcArgs& a, const int g, const int gbase,
-                                          const int src_prev) {
+                                          const int nb_full, const double (&xs)[4], const LpcArgs& a, const int g,
+                                          const int gbase, const int src_prev) {
   const int qb_lo = (PH == 0) ? 1 : 8 * PH;
   const int qb_hi = (8 * PH + 7 < nb_full) ? 8 * PH + 7 : nb_full;
 #pragma unroll 1
-  for (int qb = qb_lo; qb <= qb_hi; ++qb) {
-    const int n0 = 5 * qb;
-    cep_step<NG, PH, 0>(x, y, mc, n0, PH, a, g, gbase, src_prev);
-    cep_step<NG, PH, 1>(x, y, mc, n0 + 1, PH, a, g, gbase, src_prev);
-    cep_step<NG, PH, 2>(x, y, mc, n0 + 2, PH, a, g, gbase, src_prev);
-    cep_step<NG, PH, 3>(x, y, mc, n0 + 3, PH, a, g, gbase, src_prev);
-    cep_step<NG, PH, 4>(x, y, mc, n0 + 4, PH, a, g, gbase, src_prev);
-  }
-  if constexpr (PH + 1 < NG) cep_phase<NG, PH + 1>(x, y, mc, nb_full, a, g, gbase, src_prev);
+  for (int qb = qb_lo; qb <= qb_hi; ++qb) cep_block<NG, PH>(x, y, mc, 5 * qb, xs, a, g, gbase, src_prev);
+  if constexpr (PH + 1 < NG) cep_phase<NG, PH + 1>(x, y, mc, nb_full, xs, a, g, gbase, src_prev);
 }
 
 template <int NG>
@@ -547,12 +597,15 @@ __global__ void __launch_bounds__(128, (NG > 2) ? 3 : 5) lpc_cepstrum_blk_kernel
     for (int c = 0; c < C; ++c) { f[G][c] = -f[G][c]; b[G][c] = 0.0; rr[G][c] = 0.0; }
   const double c0 = log(sqrt(gg));
   const double c1 = (L > 1) ? __shfl_sync(0xffffffffu, f[0][1], gbase) : 0.0;  // x[1]
+  double xs[4];  // x[1..4] in every lane (the in-block terms of cep_block)
+#pragma unroll
+  for (int d = 1; d <= 4; ++d) xs[d - 1] = (d <= p) ? shfl_idx_d(f[0][d], gbase) : 0.0;
   if (g0) { rr[0][1] = c1; b[0][0] = c1; f[0][0] = c0; f[0][1] = c1; }  // 1 * cep[1];  y^(1)_0 = x[1];  cep[0], cep[1]
   if (L > 2) cep_step<NG, 0, 2>(f, b, rr, 2, 0, a, g, gbase, src_prev);
   if (L > 3) cep_step<NG, 0, 3>(f, b, rr, 3, 0, a, g, gbase, src_prev);
   if (L > 4) cep_step<NG, 0, 4>(f, b, rr, 4, 0, a, g, gbase, src_prev);
   const int nb_full = (L >= 5) ? (L - 5) / C : 0;  // last block n = 5 qb .. 5 qb + 4 with 5 qb + 4 <= L - 1
-  cep_phase<NG, 0>(f, b, rr, nb_full, a, g, gbase, src_prev);
+  cep_phase<NG, 0>(f, b, rr, nb_full, xs, a, g, gbase, src_prev);
   {
     const int n0 = C * (nb_full + 1), xg = (nb_full + 1) >> 3;
     if (L >= 5 && n0 <= L - 1) cep_step<NG, NG - 1, 0>(f, b, rr, n0, xg, a, g, gbase, src_prev);
