@@ -30,7 +30,15 @@ struct DctArgs {
   int npass;
   int radix[kMaxRadixPasses];
   const double* ham;       // [N] np.hamming(N)
-  const double2* tw;       // [n] exp(-2 pi i k / n)
+  const double2* tw;       // [n] exp(-2 pi i k / n) (mel CTA kernel)
+  // split twiddle tables of the radix passes, staged in shared memory behind the data: for pass p with
+  // sub-transform length L_p, w_L^j = A_p[j >> 6] * B_p[j & 63], A_p[a] = exp(-2 pi i 64 a / L_p),
+  // B_p[b] = exp(-2 pi i b / L_p); tws holds A_p then B_p for every pass, tw_off[p] = start of A_p
+  const double2* tws;
+  int tws_n;                         // entries of tws
+  int tw_off[kMaxRadixPasses];
+  int tw_na[kMaxRadixPasses];        // entries of A_p
+  unsigned magic[kMaxRadixPasses];   // ceil(2^32 / (L_p / R_p)): b / sub == __umulhi(b, magic) for b < 2^20
   const int32_t* perm;     // [n] position of X[k] after the DIF passes
   const double2* unpackA;  // [n+1] exp(-2 pi i k / N)
   const double2* postB;    // [N]  exp(-i pi k / (2N)) * 2 / sqrt(2N)
@@ -108,6 +116,40 @@ __device__ __forceinline__ void fft_pass(cplx<T>* z, int n, int L, const double2
   __syncthreads();
 }
 
+// Same pass with every twiddle taken from the split tables in shared memory (no global loads inside the passes:
+// with the single strided table in global memory the kernel spent 46 % of its issue slots waiting on those
+// loads) and the powers w^2 .. w^(R-1) formed from w by multiplication.
+template <typename T, int R>
+__device__ __forceinline__ void fft_pass_s(cplx<T>* z, int n, int L, const double2* twA, const double2* twB,
+                                           unsigned magic) {
+  const int sub = L / R;
+  const int nb = n / R;
+  for (int b = threadIdx.x; b < nb; b += blockDim.x) {
+    int blk = b, j = 0;
+    if (sub > 1) { blk = (int)__umulhi((unsigned)b, magic); j = b - blk * sub; }
+    cplx<T>* p = z + blk * L + j;
+    cplx<T> a[R];
+#pragma unroll
+    for (int t = 0; t < R; ++t) a[t] = p[t * sub];
+    dft_small<T, R>(a);
+    p[0] = a[0];
+    if (sub > 1) {
+      const double2 wa = twA[j >> 6], wb = twB[j & 63];
+      const cplx<double> w1 = {wa.x * wb.x - wa.y * wb.y, wa.x * wb.y + wa.y * wb.x};
+      cplx<double> w = w1;
+#pragma unroll
+      for (int u = 1; u < R; ++u) {
+        p[u * sub] = cmul(a[u], cplx<T>{(T)w.x, (T)w.y});
+        if (u + 1 < R) w = cmul(w, w1);
+      }
+    } else {
+#pragma unroll
+      for (int u = 1; u < R; ++u) p[u] = a[u];
+    }
+  }
+  __syncthreads();
+}
+
 template <typename S>
 __device__ __forceinline__ double sample_to_double(S v) { return (double)v; }
 
@@ -126,6 +168,8 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* sv = reinterpret_cast<T*>(smem_raw);  // v[] (real view) == z[] (complex view)
   cplx<T>* z = reinterpret_cast<cplx<T>*>(smem_raw);
+  double2* stw = reinterpret_cast<double2*>(smem_raw + (size_t)a.N * sizeof(T));  // N * sizeof(T) is a multiple of 16
+  for (int i = threadIdx.x; i < a.tws_n; i += blockDim.x) stw[i] = a.tws[i];
 
   const int seg = a.seg0 + blockIdx.x;
   const int u = a.seg_utt[seg];
@@ -177,10 +221,12 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
   int L = a.n;
   for (int p = 0; p < a.npass; ++p) {
     const int R = a.radix[p];
-    if (R == 4) fft_pass<T, 4>(z, a.n, L, a.tw);
-    else if (R == 2) fft_pass<T, 2>(z, a.n, L, a.tw);
-    else if (R == 3) fft_pass<T, 3>(z, a.n, L, a.tw);
-    else fft_pass<T, 5>(z, a.n, L, a.tw);
+    const double2* twA = stw + a.tw_off[p];
+    const double2* twB = twA + a.tw_na[p];
+    if (R == 4) fft_pass_s<T, 4>(z, a.n, L, twA, twB, a.magic[p]);
+    else if (R == 2) fft_pass_s<T, 2>(z, a.n, L, twA, twB, a.magic[p]);
+    else if (R == 3) fft_pass_s<T, 3>(z, a.n, L, twA, twB, a.magic[p]);
+    else fft_pass_s<T, 5>(z, a.n, L, twA, twB, a.magic[p]);
     L /= R;
   }
 

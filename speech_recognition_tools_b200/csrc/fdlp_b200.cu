@@ -109,6 +109,11 @@ struct FftTables {
   double2* d_tw = nullptr;
   int32_t* d_perm = nullptr;
   double2* d_unpackA = nullptr;  // [n+1] exp(-2 pi i k / (2n))
+  // split per-pass twiddle tables (dct.cuh fft_pass_s)
+  double2* d_tws = nullptr;
+  int tws_n = 0;
+  int tw_off[kMaxRadixPasses], tw_na[kMaxRadixPasses];
+  unsigned magic[kMaxRadixPasses];
 };
 
 template <typename T>
@@ -137,15 +142,37 @@ static int build_fft_tables(int n, FftTables* t) {
     for (int q = 0; q < t->npass; ++q) { const int r = t->radix[q]; L /= r; pos += (kk % r) * L; kk /= r; }
     perm[k] = pos;
   }
+  std::vector<double2> tws;
+  {
+    int L = n;
+    for (int q = 0; q < t->npass; ++q) {
+      const int r = t->radix[q], sub = L / r;
+      const int na = (sub + 63) / 64;
+      t->tw_off[q] = (int)tws.size();
+      t->tw_na[q] = na;
+      t->magic[q] = sub > 1 ? (unsigned)((0x100000000ULL + (unsigned long long)sub - 1) / (unsigned long long)sub) : 0u;
+      for (int a = 0; a < na; ++a) {
+        const long double ang = -2.0L * M_PIl * (64.0L * a) / L;
+        tws.push_back(make_double2((double)cosl(ang), (double)sinl(ang)));
+      }
+      for (int b = 0; b < 64; ++b) {
+        const long double ang = -2.0L * M_PIl * b / L;
+        tws.push_back(make_double2((double)cosl(ang), (double)sinl(ang)));
+      }
+      L = sub;
+    }
+  }
+  t->tws_n = (int)tws.size();
   int rc;
   if ((rc = upload(&t->d_tw, tw))) return rc;
+  if ((rc = upload(&t->d_tws, tws))) return rc;
   if ((rc = upload(&t->d_perm, perm))) return rc;
   if ((rc = upload(&t->d_unpackA, A))) return rc;
   return 0;
 }
 static void free_fft_tables(FftTables* t) {
-  cudaFree(t->d_tw); cudaFree(t->d_perm); cudaFree(t->d_unpackA);
-  t->d_tw = nullptr; t->d_perm = nullptr; t->d_unpackA = nullptr;
+  cudaFree(t->d_tw); cudaFree(t->d_perm); cudaFree(t->d_unpackA); cudaFree(t->d_tws);
+  t->d_tw = nullptr; t->d_perm = nullptr; t->d_unpackA = nullptr; t->d_tws = nullptr;
 }
 
 }  // namespace fdlp
@@ -535,8 +562,9 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   int max_smem = 0;
   cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device);
   if (max_smem <= 0) max_smem = 227 * 1024;  // building / probing without a device
-  p->dct_fp64 = !prm->dct_fp32 && (size_t)N * 8 <= (size_t)max_smem;
-  p->dct_smem = (size_t)N * (p->dct_fp64 ? 8 : 4);
+  const size_t tws_bytes = (size_t)p->fft.tws_n * sizeof(double2);  // split twiddle tables staged behind the data
+  p->dct_fp64 = !prm->dct_fp32 && (size_t)N * 8 + tws_bytes <= (size_t)max_smem;
+  p->dct_smem = (size_t)N * (p->dct_fp64 ? 8 : 4) + tws_bytes;
   g.dct_is_fp64 = p->dct_fp64 ? 1 : 0;
   if (p->dct_smem > (size_t)max_smem) {
     plan_free(p);
@@ -647,6 +675,8 @@ static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld
   for (int i = 0; i < p->fft.npass; ++i) a.radix[i] = p->fft.radix[i];
   a.ham = p->d_ham; a.tw = p->fft.d_tw; a.perm = p->fft.d_perm; a.unpackA = p->fft.d_unpackA; a.postB = p->d_postB;
   a.out = out; a.out_ld = out_ld; a.out_pad = out_pad; a.seg0 = seg0;
+  a.tws = p->fft.d_tws; a.tws_n = p->fft.tws_n;
+  for (int i = 0; i < p->fft.npass; ++i) { a.tw_off[i] = p->fft.tw_off[i]; a.tw_na[i] = p->fft.tw_na[i]; a.magic[i] = p->fft.magic[i]; }
   a.vec_ok = (((uintptr_t)b->wav) % 16 == 0) ? 1 : 0;
   const dim3 grid(nseg), block(512);
   if (b->wav_dtype == FDLP_WAV_INT16) {
