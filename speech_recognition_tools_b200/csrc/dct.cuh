@@ -39,6 +39,14 @@ struct DctArgs {
   int tw_off[kMaxRadixPasses];
   int tw_na[kMaxRadixPasses];        // entries of A_p
   unsigned magic[kMaxRadixPasses];   // ceil(2^32 / (L_p / R_p)): b / sub == __umulhi(b, magic) for b < 2^20
+  // split tables of the unpack / post-twiddle step, staged behind tws: unpackA[k] = UA_hi[k >> 6] * UA_lo[k & 63],
+  // postB[k] = UB_hi[k >> 6] * UB_lo[k & 63] (scale in UB_lo); layout UA_hi[unp_na] UA_lo[64] UB_hi[unp_na] UB_lo[64]
+  const double2* unp;
+  int unp_na;
+  // split Hamming table, staged behind unp: np.hamming(N)[i] = 0.54 - 0.46 Re(HC[i >> 6] * HD[i & 63]),
+  // HC[a] = exp(j theta 64 a), HD[b] = exp(j theta b), theta = 2 pi / (N - 1); layout HC[ham_na] HD[64]
+  const double2* hamt;
+  int ham_na;
   const int32_t* perm;     // [n] position of X[k] after the DIF passes
   const double2* unpackA;  // [n+1] exp(-2 pi i k / N)
   const double2* postB;    // [N]  exp(-i pi k / (2N)) * 2 / sqrt(2N)
@@ -170,6 +178,11 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
   cplx<T>* z = reinterpret_cast<cplx<T>*>(smem_raw);
   double2* stw = reinterpret_cast<double2*>(smem_raw + (size_t)a.N * sizeof(T));  // N * sizeof(T) is a multiple of 16
   for (int i = threadIdx.x; i < a.tws_n; i += blockDim.x) stw[i] = a.tws[i];
+  double2* sunp = stw + a.tws_n;
+  for (int i = threadIdx.x; i < 2 * (a.unp_na + 64); i += blockDim.x) sunp[i] = a.unp[i];
+  double2* sham = sunp + 2 * (a.unp_na + 64);
+  for (int i = threadIdx.x; i < a.ham_na + 64; i += blockDim.x) sham[i] = a.hamt[i];
+  __syncthreads();
 
   const int seg = a.seg0 + blockIdx.x;
   const int u = a.seg_utt[seg];
@@ -183,35 +196,71 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
   const int16_t* nz = a.noise ? a.noise + a.utt_noise_off[u] : nullptr;
   const double alpha = a.noise ? a.utt_alpha[u] : 0.0;
 
-  // ---- load: coalesced / vectorised read of the windowed segment, scattered into Makhoul order ----
-  constexpr int VEC = 16 / (int)sizeof(S);
-  const int64_t g0 = woff + q_base;                 // global sample index of window sample 0 (may be < 0)
-  const int sh = (int)(((g0 % VEC) + VEC) % VEC);   // window sample i sits at global index g0+i; chunks start where that is 0 mod VEC
-  const int nchunk = (N + sh + VEC - 1) / VEC;
-  for (int c = threadIdx.x; c < nchunk; c += blockDim.x) {
-    const int i0 = c * VEC - sh;
-    const int64_t q0 = q_base + i0;
-    double v[VEC];
-    const bool interior = a.vec_ok && !nz && i0 >= 0 && i0 + VEC <= N && q0 >= 0 && q0 + VEC <= T_utt;
-    if (interior) {
-      const int4 raw = __ldg(reinterpret_cast<const int4*>(sig + q0));
-      const S* rs = reinterpret_cast<const S*>(&raw);
+  // ---- load: the windowed segment, scattered into Makhoul order ----
+  // A lane owns the sample pair (i, i+1), i = 2 * pair - sh, where sh makes the pair's global address even
+  // (4-byte / 8-byte aligned loads, 128 / 256 contiguous bytes per warp).  Consecutive lanes then write
+  // consecutive doubles of the ascending (even i) and of the descending (odd i) half of v[]: no bank conflicts.
+  // The loads of kLdBatch pairs are issued together (the segment comes from HBM: one load per trip left the
+  // kernel waiting on memory latency for a quarter of its time), and the window is formed from the split table
+  // in shared memory; i & 63 is the same for every pair of a thread (512 threads x 2 samples = 0 mod 64).
+  {
+    constexpr int kLdBatch = 8;
+    const int64_t g0 = woff + q_base;  // global sample index of window sample 0 (may be < 0)
+    const int sh = (int)(((g0 % 2) + 2) % 2);
+    const int npair = (N + sh + 1) / 2;
+    const bool pair_ok = a.vec_ok && !nz;
+    const double2 hd0 = sham[a.ham_na + ((2 * (int)threadIdx.x - sh) & 63)];
+    const double2 hd1 = sham[a.ham_na + ((2 * (int)threadIdx.x - sh + 1) & 63)];
+    for (int pb = threadIdx.x; pb < npair; pb += blockDim.x * kLdBatch) {
+      double v0[kLdBatch], v1[kLdBatch];
+      bool fast[kLdBatch];
+      if constexpr (sizeof(S) == 2) {
+        uint32_t raw[kLdBatch];
 #pragma unroll
-      for (int e = 0; e < VEC; ++e) v[e] = (double)rs[e];
-    } else {
+        for (int e = 0; e < kLdBatch; ++e) {
+          const int i0 = 2 * (pb + e * (int)blockDim.x) - sh;
+          const int64_t q0 = q_base + i0;
+          fast[e] = pair_ok && i0 >= 0 && i0 + 2 <= N && q0 >= 0 && q0 + 2 <= T_utt;
+          raw[e] = fast[e] ? __ldg(reinterpret_cast<const uint32_t*>(sig + q0)) : 0u;
+        }
 #pragma unroll
-      for (int e = 0; e < VEC; ++e) {
-        const int i = i0 + e;
-        v[e] = (i >= 0 && i < N) ? fetch_sample<S>(a, sig, q0 + e, T_utt, u, alpha, nz) : 0.0;
+        for (int e = 0; e < kLdBatch; ++e) {
+          v0[e] = (double)(int16_t)(raw[e] & 0xffffu);
+          v1[e] = (double)(int16_t)(raw[e] >> 16);
+        }
+      } else {
+        float2 raw[kLdBatch];
+#pragma unroll
+        for (int e = 0; e < kLdBatch; ++e) {
+          const int i0 = 2 * (pb + e * (int)blockDim.x) - sh;
+          const int64_t q0 = q_base + i0;
+          fast[e] = pair_ok && i0 >= 0 && i0 + 2 <= N && q0 >= 0 && q0 + 2 <= T_utt;
+          raw[e] = fast[e] ? __ldg(reinterpret_cast<const float2*>(sig + q0)) : make_float2(0.f, 0.f);
+        }
+#pragma unroll
+        for (int e = 0; e < kLdBatch; ++e) { v0[e] = (double)raw[e].x; v1[e] = (double)raw[e].y; }
       }
-    }
 #pragma unroll
-    for (int e = 0; e < VEC; ++e) {
-      const int i = i0 + e;
-      if (i >= 0 && i < N) {
-        const double xw = v[e] * __ldg(a.ham + i);
-        const int vi = (i & 1) ? (N - 1 - (i >> 1)) : (i >> 1);
-        sv[vi] = (T)xw;
+      for (int e = 0; e < kLdBatch; ++e) {
+        const int pi = pb + e * (int)blockDim.x;
+        if (pi < npair) {
+          const int i0 = 2 * pi - sh, i1 = i0 + 1;
+          const int64_t q0 = q_base + i0;
+          if (!fast[e]) {
+            v0[e] = (i0 >= 0 && i0 < N) ? fetch_sample<S>(a, sig, q0, T_utt, u, alpha, nz) : 0.0;
+            v1[e] = (i1 >= 0 && i1 < N) ? fetch_sample<S>(a, sig, q0 + 1, T_utt, u, alpha, nz) : 0.0;
+          }
+          if (i0 >= 0 && i0 < N) {
+            const double2 hc = sham[i0 >> 6];
+            const double w = 0.54 - 0.46 * (hc.x * hd0.x - hc.y * hd0.y);
+            sv[(i0 & 1) ? (N - 1 - (i0 >> 1)) : (i0 >> 1)] = (T)(v0[e] * w);
+          }
+          if (i1 >= 0 && i1 < N) {
+            const double2 hc = sham[i1 >> 6];
+            const double w = 0.54 - 0.46 * (hc.x * hd1.x - hc.y * hd1.y);
+            sv[(i1 & 1) ? (N - 1 - (i1 >> 1)) : (i1 >> 1)] = (T)(v1[e] * w);
+          }
+        }
       }
     }
   }
@@ -233,27 +282,41 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
   // ---- unpack to the length-N real FFT, Makhoul post-twiddle, scale, store ----
   double* out = a.out + (size_t)blockIdx.x * a.out_ld;
   const int n = a.n;
-  for (int kq = threadIdx.x; kq <= n; kq += blockDim.x) {
-    const int k1 = (kq == n) ? 0 : kq;
-    const int k2 = (kq == 0) ? 0 : n - kq;
-    const cplx<T> zk = z[a.perm[k1]];
-    cplx<T> zc = z[a.perm[k2]];
+  constexpr int kUnpBatch = 4;
+  for (int kb = threadIdx.x; kb <= n; kb += blockDim.x * kUnpBatch) {
+   int p1[kUnpBatch], p2[kUnpBatch];
+#pragma unroll
+   for (int e = 0; e < kUnpBatch; ++e) {  // the permutation indices come from L2: issue the loads of a batch together
+     const int kq = kb + e * (int)blockDim.x;
+     const bool in = kq <= n;
+     p1[e] = in ? __ldg(a.perm + ((kq == n) ? 0 : kq)) : 0;
+     p2[e] = in ? __ldg(a.perm + ((kq == 0) ? 0 : n - kq)) : 0;
+   }
+#pragma unroll
+   for (int e = 0; e < kUnpBatch; ++e) {
+    const int kq = kb + e * (int)blockDim.x;
+    if (kq > n) break;
+    const cplx<T> zk = z[p1[e]];
+    cplx<T> zc = z[p2[e]];
     zc.y = -zc.y;
     const cplx<double> Zk = {(double)zk.x, (double)zk.y}, Zc = {(double)zc.x, (double)zc.y};
     const cplx<double> E = {0.5 * (Zk.x + Zc.x), 0.5 * (Zk.y + Zc.y)};
     const cplx<double> D = {0.5 * (Zk.x - Zc.x), 0.5 * (Zk.y - Zc.y)};
-    const double2 A = __ldg(a.unpackA + kq);
+    const double2 ah = sunp[kq >> 6], al = sunp[a.unp_na + (kq & 63)];
+    const double2 A = make_double2(ah.x * al.x - ah.y * al.y, ah.x * al.y + ah.y * al.x);
     // V = E - j * A * D
     const cplx<double> AD = cmul(cplx<double>{A.x, A.y}, D);
     const cplx<double> V = {E.x + AD.y, E.y - AD.x};
-    const double2 B = __ldg(a.postB + kq);
+    const double2 bh = sunp[a.unp_na + 64 + (kq >> 6)], bl = sunp[2 * a.unp_na + 64 + (kq & 63)];
+    const double2 B = make_double2(bh.x * bl.x - bh.y * bl.y, bh.x * bl.y + bh.y * bl.x);
     const double yk = B.x * V.x - B.y * V.y;  // Re(B * V), B carries 2/sqrt(2N)
     out[kq] = yk;
     if (kq < a.out_pad) out[N + kq] = yk;
     if (kq > 0 && kq < n) {
-      const double2 B2 = __ldg(a.postB + (N - kq));
-      out[N - kq] = B2.x * V.x + B2.y * V.y;  // Re(B2 * conj(V))
+      // postB[N - kq] = -j conj(postB[kq]) = (-B.y, -B.x);  Re(B2 * conj(V)) = B2.x V.x + B2.y V.y
+      out[N - kq] = -(B.y * V.x + B.x * V.y);
     }
+   }
   }
 }
 

@@ -194,6 +194,10 @@ struct fdlp_plan {
   FftTables fft;
   double* d_ham = nullptr;
   double2* d_postB = nullptr;
+  double2* d_unp = nullptr;  // split unpack / post-twiddle tables
+  int unp_na = 0;
+  double2* d_hamt = nullptr;  // split Hamming table
+  int ham_na = 0;
   double* d_fbank = nullptr;
   int32_t *d_row_lo = nullptr, *d_row_hi = nullptr;
   double *d_weights = nullptr, *d_inv_n = nullptr, *d_basis = nullptr, *d_wratio = nullptr;
@@ -229,7 +233,7 @@ struct fdlp_plan {
 static void plan_free(fdlp_plan* p) {
   if (!p) return;
   free_fft_tables(&p->fft);
-  cudaFree(p->d_ham); cudaFree(p->d_postB); cudaFree(p->d_fbank); cudaFree(p->d_row_lo); cudaFree(p->d_row_hi);
+  cudaFree(p->d_ham); cudaFree(p->d_postB); cudaFree(p->d_unp); cudaFree(p->d_hamt); cudaFree(p->d_fbank); cudaFree(p->d_row_lo); cudaFree(p->d_row_hi);
   cudaFree(p->d_weights); cudaFree(p->d_inv_n); cudaFree(p->d_basis); cudaFree(p->d_wratio);
   cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_alpha); cudaFree(p->d_ms);
   cudaFree(p->d_tmpl); cudaFree(p->d_wsq); cudaFree(p->d_p);
@@ -490,6 +494,22 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
       B[k] = make_double2((double)(cosl(ang) * sc), (double)(sinl(ang) * sc));
     }
     if ((rc = upload(&p->d_ham, ham)) || (rc = upload(&p->d_postB, B))) { plan_free(p); return rc; }
+    // split tables for the unpack step (dct.cuh): k = 64 a + b
+    const int n = N / 2;
+    p->unp_na = n / 64 + 1;
+    std::vector<double2> U;
+    for (int a = 0; a < p->unp_na; ++a) { const long double ang = -2.0L * M_PIl * (64.0L * a) / N; U.push_back(make_double2((double)cosl(ang), (double)sinl(ang))); }
+    for (int b = 0; b < 64; ++b) { const long double ang = -2.0L * M_PIl * b / N; U.push_back(make_double2((double)cosl(ang), (double)sinl(ang))); }
+    for (int a = 0; a < p->unp_na; ++a) { const long double ang = -M_PIl * (64.0L * a) / (2.0L * N); U.push_back(make_double2((double)cosl(ang), (double)sinl(ang))); }
+    for (int b = 0; b < 64; ++b) { const long double ang = -M_PIl * b / (2.0L * N); U.push_back(make_double2((double)(cosl(ang) * sc), (double)(sinl(ang) * sc))); }
+    if ((rc = upload(&p->d_unp, U))) { plan_free(p); return rc; }
+    // split Hamming table (dct.cuh): i = 64 a + b
+    p->ham_na = (N + 63) / 64 + 1;
+    std::vector<double2> H;
+    const long double theta = N > 1 ? 2.0L * M_PIl / (N - 1) : 0.0L;
+    for (int a = 0; a < p->ham_na; ++a) H.push_back(make_double2((double)cosl(theta * 64.0L * a), (double)sinl(theta * 64.0L * a)));
+    for (int b = 0; b < 64; ++b) H.push_back(make_double2((double)cosl(theta * b), (double)sinl(theta * b)));
+    if ((rc = upload(&p->d_hamt, H))) { plan_free(p); return rc; }
   }
   {
     std::vector<double> full;
@@ -562,7 +582,8 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   int max_smem = 0;
   cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, p->device);
   if (max_smem <= 0) max_smem = 227 * 1024;  // building / probing without a device
-  const size_t tws_bytes = (size_t)p->fft.tws_n * sizeof(double2);  // split twiddle tables staged behind the data
+  // split twiddle and unpack tables staged behind the data
+  const size_t tws_bytes = ((size_t)p->fft.tws_n + 2 * (size_t)(p->unp_na + 64) + (size_t)(p->ham_na + 64)) * sizeof(double2);
   p->dct_fp64 = !prm->dct_fp32 && (size_t)N * 8 + tws_bytes <= (size_t)max_smem;
   p->dct_smem = (size_t)N * (p->dct_fp64 ? 8 : 4) + tws_bytes;
   g.dct_is_fp64 = p->dct_fp64 ? 1 : 0;
@@ -675,7 +696,7 @@ static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld
   for (int i = 0; i < p->fft.npass; ++i) a.radix[i] = p->fft.radix[i];
   a.ham = p->d_ham; a.tw = p->fft.d_tw; a.perm = p->fft.d_perm; a.unpackA = p->fft.d_unpackA; a.postB = p->d_postB;
   a.out = out; a.out_ld = out_ld; a.out_pad = out_pad; a.seg0 = seg0;
-  a.tws = p->fft.d_tws; a.tws_n = p->fft.tws_n;
+  a.tws = p->fft.d_tws; a.tws_n = p->fft.tws_n; a.unp = p->d_unp; a.unp_na = p->unp_na; a.hamt = p->d_hamt; a.ham_na = p->ham_na;
   for (int i = 0; i < p->fft.npass; ++i) { a.tw_off[i] = p->fft.tw_off[i]; a.tw_na[i] = p->fft.tw_na[i]; a.magic[i] = p->fft.magic[i]; }
   a.vec_ok = (((uintptr_t)b->wav) % 16 == 0) ? 1 : 0;
   const dim3 grid(nseg), block(512);
