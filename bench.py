@@ -221,7 +221,7 @@ def run_ours(args):
     # ---- end to end through the public API path: pinned host wav -> device, features -> pinned host ----
     idx_bytes = sum(int(v.numel() * v.element_size()) for k, v in lay.dev.items() if k == "_buf")
 
-    E2E_CHUNKS = int(os.environ.get("FDLP_E2E_CHUNKS", "4"))
+    E2E_CHUNKS = int(os.environ.get("FDLP_E2E_CHUNKS", "6"))
 
     def step_e2e():
         # FdlpExtractor.extract_host: samples pinned host -> device, index tables -> device, the kernels, features

@@ -185,14 +185,18 @@ class BatchLayout:
         return self
 
 
-def split_layout(lay: "BatchLayout", n_chunks: int):
-    """Cut a packed batch into up to `n_chunks` runs of whole utterances with about equal segment counts.
+def split_layout(lay: "BatchLayout", n_chunks: int, taper: bool = False):
+    """Cut a packed batch into up to `n_chunks` runs of whole utterances with about equal segment counts
+    (`taper`: segment counts in the ratio 1 : 2 : 3 ... 3 : 2 : 1, so that the first upload and the last
+    download of a copy / compute pipeline, which nothing overlaps, are short).
     Returns [(u0, u1, sub_layout)]; the sub-layout's offsets are relative to the chunk's first sample / segment /
     frame, so each chunk is a self-contained fdlp_batch over a slice of the packed buffers."""
     n_chunks = max(1, min(int(n_chunks), lay.n_utt))
+    wts = np.array([min(c + 1, n_chunks - c, 3) if taper else 1 for c in range(n_chunks)], dtype=np.float64)
+    cum = np.cumsum(wts) / wts.sum()
     bounds = [0]
     for c in range(1, n_chunks):
-        target = lay.n_seg * c / n_chunks
+        target = lay.n_seg * cum[c - 1]
         u = int(np.searchsorted(lay.utt_seg_off, target, side="left"))
         u = min(max(u, bounds[-1] + 1), lay.n_utt - (n_chunks - c))
         bounds.append(u)
@@ -432,8 +436,9 @@ class FdlpExtractor:
         return feats, status
 
     def extract_host(self, host_wav: torch.Tensor, lay: BatchLayout, feats_host: Optional[torch.Tensor] = None,
-                     n_chunks: int = 4, cmvn: Optional[torch.Tensor] = None, status: Optional[torch.Tensor] = None,
-                     wav_dev: Optional[torch.Tensor] = None, feats: Optional[torch.Tensor] = None):
+                     n_chunks: int = 6, cmvn: Optional[torch.Tensor] = None, status: Optional[torch.Tensor] = None,
+                     wav_dev: Optional[torch.Tensor] = None, feats: Optional[torch.Tensor] = None,
+                     taper: bool = True):
         """End-to-end call for a packed batch that lives in (pinned) HOST memory: samples go host -> device,
         features device -> host, and both copies overlap the kernels.  The batch is cut into `n_chunks` runs of
         whole utterances; chunk c+1 is uploaded on a copy stream while chunk c computes on the current stream
@@ -453,7 +458,7 @@ class FdlpExtractor:
         if not hasattr(self, "_s_in"):
             self._s_in, self._s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
         cur = torch.cuda.current_stream(dev)
-        chunks = split_layout(lay, n_chunks)
+        chunks = split_layout(lay, n_chunks, taper)
         ev0 = torch.cuda.Event()
         ev0.record(cur)
         self._s_in.wait_event(ev0)
