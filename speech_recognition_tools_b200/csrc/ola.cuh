@@ -39,22 +39,22 @@ __global__ void __launch_bounds__(256) ola_log_kernel(const OlaArgs a) {
   const int J = a.J, kk = a.kk, kkb2 = a.kkb2;
   constexpr int LD = kOlaFT + 1;
 
+  // Segments that can reach this tile: the pointers increase with the segment index, so the contributors of
+  // frames [f0, f0 + nf) are one contiguous run (2 or 3 segments); every thread finds it with the same scan.
+  int i_lo = nseg, i_hi = 0;  // later segments (i >= 1) with ptr_i < f0 + nf and ptr_i + kk > f0
+  for (int i = 1; i < nseg; ++i) {
+    const int ptr = a.seg_ptr[s0 + i];
+    if (ptr < f0 + nf && ptr + kk > f0) { i_lo = min(i_lo, i); i_hi = max(i_hi, i + 1); }
+  }
+  const int d1 = Fr < kkb2 ? Fr : kkb2;  // feats[:, 0:kkb2] += E[kkb2:]  (or feats[:, :] += E[kkb2:kkb2+Fr] when Fr < kkb2)
   for (int e = threadIdx.x; e < J * kOlaFT; e += blockDim.x) {
     const int j = e / kOlaFT, fl = e % kOlaFT;
     const int f = f0 + fl;
     double acc = 0.0;
     if (fl < nf) {
-      for (int i = 0; i < nseg; ++i) {
-        int t;
-        if (i == 0) {
-          // feats[:, 0:kkb2] += E[kkb2:]  (or feats[:, :] += E[kkb2:kkb2+Fr] when Fr < kkb2)
-          const int d1 = Fr < kkb2 ? Fr : kkb2;
-          t = (f < d1) ? kkb2 + f : -1;
-        } else {
-          const int ptr = a.seg_ptr[s0 + i];
-          t = f - ptr;
-          if (t < 0 || t >= kk) t = -1;
-        }
+      if (f < d1 && kkb2 + f < kk) acc += a.env[((size_t)s0 * J + j) * kk + kkb2 + f];  // segment 0 first: the reference's order
+      for (int i = i_lo; i < i_hi; ++i) {
+        const int t = f - a.seg_ptr[s0 + i];
         if (t >= 0 && t < kk) acc += a.env[((size_t)(s0 + i) * J + j) * kk + t];
       }
     }
@@ -62,14 +62,22 @@ __global__ void __launch_bounds__(256) ola_log_kernel(const OlaArgs a) {
   }
   __syncthreads();
 
-  for (int e = threadIdx.x; e < nf * J; e += blockDim.x) {
-    const int fl = e / J, j = e % J;
-    const double v = tile[j * LD + fl];
-    // np.clip propagates NaN; fmax would not
-    const double lg = isnan(v) ? v : log(v < 1e-14 ? 1e-14 : v);
-    const float o = (float)lg;
-    a.feats[(size_t)(foff + f0 + fl) * J + j] = o;
-    tile[j * LD + fl] = (double)o;  // keep the rounded value for the CMVN sums
+  {
+    // element e = fl * J + j for e = tid, tid + 256, ...: advance (fl, j) without a division per element
+    int fl = (int)threadIdx.x / J, j = (int)threadIdx.x % J;
+    const int dfl = (int)blockDim.x / J, dj = (int)blockDim.x % J;
+    float* frow = a.feats + (size_t)(foff + f0) * J;
+    for (; fl < nf;) {
+      const double v = tile[j * LD + fl];
+      // np.clip propagates NaN; fmax would not
+      const double lg = isnan(v) ? v : log(v < 1e-14 ? 1e-14 : v);
+      const float o = (float)lg;
+      frow[(size_t)fl * J + j] = o;
+      tile[j * LD + fl] = (double)o;  // keep the rounded value for the CMVN sums
+      fl += dfl;
+      j += dj;
+      if (j >= J) { j -= J; ++fl; }
+    }
   }
   if (a.cmvn) {
     __syncthreads();
