@@ -832,7 +832,7 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
   EnvArgs e;
   e.ms = a.ms; e.basis = p->d_basis; e.wratio = p->d_wratio; e.env = env;
   e.n_tasks = a.n_tasks; e.Lp = p->Lp; e.ldb = p->ldb; e.kk = p->g.kk;
-  const dim3 grid((a.n_tasks + 8 * kEnvWarps - 1) / (8 * kEnvWarps), p->env_ny);
+  const dim3 grid((a.n_tasks + 8 * kEnvMA * kEnvWarps - 1) / (8 * kEnvMA * kEnvWarps), p->env_ny);
   envelope_dmma_kernel<10><<<grid, kEnvWarps * 32, 0, st>>>(e);
   FDLP_CUDA(cudaGetLastError());
   return 0;

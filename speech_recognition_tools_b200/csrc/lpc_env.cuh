@@ -650,46 +650,63 @@ struct EnvArgs {
 
 constexpr int kEnvWarps = 4;
 
+constexpr int kEnvMA = 2;  // 8-task row blocks per warp: every basis fragment feeds kEnvMA DMMAs
+
 template <int NT>
 __global__ void __launch_bounds__(kEnvWarps * 32) envelope_dmma_kernel(const EnvArgs a) {
+  constexpr int MA = kEnvMA;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int lr = lane & 3, lc = lane >> 2;
-  const int task0 = (blockIdx.x * kEnvWarps + warp) * 8;
+  const int task0 = (blockIdx.x * kEnvWarps + warp) * 8 * MA;
   if (task0 >= a.n_tasks) return;
   const int t_base = blockIdx.y * NT * 8;
-  double acc[NT][2];
+  double acc[MA][NT][2];
 #pragma unroll
-  for (int i = 0; i < NT; ++i) acc[i][0] = acc[i][1] = 0.0;
-  // A[row = lane/4][col = lane%4] = ms[task0 + lane/4][k0 + lane%4]   (rows beyond n_tasks are padding)
-  const double* pa = a.ms + (size_t)(task0 + lc) * a.Lp + lr;
+  for (int m = 0; m < MA; ++m)
+#pragma unroll
+    for (int i = 0; i < NT; ++i) acc[m][i][0] = acc[m][i][1] = 0.0;
+  // A[row = lane/4][col = lane%4] = ms[task0 + 8 m + lane/4][k0 + lane%4]   (rows beyond n_tasks: clamped, discarded)
+  const double* pa[MA];
+#pragma unroll
+  for (int m = 0; m < MA; ++m) pa[m] = a.ms + (size_t)min(task0 + 8 * m + lc, a.n_tasks - 1) * a.Lp + lr;
   // B[row = lane%4][col = lane/4] = basis[k0 + lane%4][t0 + lane/4]
   const double* pb = a.basis + (size_t)lr * a.ldb + t_base + lc;
-  // software pipeline: the A fragment and the NT basis fragments of step k0+4 are loaded while step k0 computes
-  double af = __ldg(pa);
+  // software pipeline: the A fragments and the NT basis fragments of step k0+4 are loaded while step k0 computes
+  double af[MA];
+#pragma unroll
+  for (int m = 0; m < MA; ++m) af[m] = __ldg(pa[m]);
   double bf[NT];
 #pragma unroll
   for (int i = 0; i < NT; ++i) bf[i] = __ldg(pb + 8 * i);
   for (int k0 = 0; k0 < a.Lp; k0 += 4) {
     const int kn = (k0 + 4 < a.Lp) ? k0 + 4 : k0;
-    const double afn = __ldg(pa + kn);
+    double afn[MA];
+#pragma unroll
+    for (int m = 0; m < MA; ++m) afn[m] = __ldg(pa[m] + kn);
     const double* pbk = pb + (size_t)kn * a.ldb;
     double bn[NT];
 #pragma unroll
     for (int i = 0; i < NT; ++i) bn[i] = __ldg(pbk + 8 * i);
 #pragma unroll
-    for (int i = 0; i < NT; ++i) dmma884(acc[i][0], acc[i][1], af, bf[i]);
-    af = afn;
+    for (int i = 0; i < NT; ++i)
+#pragma unroll
+      for (int m = 0; m < MA; ++m) dmma884(acc[m][i][0], acc[m][i][1], af[m], bf[i]);
+#pragma unroll
+    for (int m = 0; m < MA; ++m) af[m] = afn[m];
 #pragma unroll
     for (int i = 0; i < NT; ++i) bf[i] = bn[i];
   }
   // C[row = lane/4][col = 2*(lane%4) + {0,1}]
-  const int task = task0 + lc;
-  if (task < a.n_tasks) {
 #pragma unroll
-    for (int i = 0; i < NT; ++i) {
-      const int t = t_base + 8 * i + 2 * lr;
-      if (t < a.kk) a.env[(size_t)task * a.kk + t] = exp(acc[i][0]) * __ldg(a.wratio + t);
-      if (t + 1 < a.kk) a.env[(size_t)task * a.kk + t + 1] = exp(acc[i][1]) * __ldg(a.wratio + t + 1);
+  for (int m = 0; m < MA; ++m) {
+    const int task = task0 + 8 * m + lc;
+    if (task < a.n_tasks) {
+#pragma unroll
+      for (int i = 0; i < NT; ++i) {
+        const int t = t_base + 8 * i + 2 * lr;
+        if (t < a.kk) a.env[(size_t)task * a.kk + t] = exp(acc[m][i][0]) * __ldg(a.wratio + t);
+        if (t + 1 < a.kk) a.env[(size_t)task * a.kk + t + 1] = exp(acc[m][i][1]) * __ldg(a.wratio + t + 1);
+      }
     }
   }
 }
