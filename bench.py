@@ -280,7 +280,7 @@ def run_ours(args):
             kern["autocorr_ranges_kernel"] = (kms["autocorr_direct"], 2.0 * g["nlags"] * g["direct_taps"] * nseg)
         else:
             kern["autocorr_dmma_kernel"] = (kms["autocorr_direct"], 2.0 * g["nlags"] * g["support_taps"] * nseg)
-        kern["lpc_cepstrum_reg_kernel"] = (kms["lpc_cepstrum"], (2.0 * p_ * p_ + 1.5 * L_ * L_) * J * nseg)
+        kern["lpc_cepstrum_blk_kernel"] = (kms["lpc_cepstrum"], (2.0 * p_ * p_ + 1.5 * L_ * L_) * J * nseg)
         kern["envelope_dmma_kernel"] = (kms["envelope_dmma_kernel"], 2.0 * L_ * kk_ * J * nseg)
         top = max(kern, key=lambda k: kern[k][0])
         top_ms, top_flops = kern[top]
