@@ -495,6 +495,9 @@ class FdlpExtractor:
                  return_status: bool = False):
         """Extract FDLP spectrograms for a list of mono waveforms.  Returns a list of [Fr_u, nfilters]
         float32 device tensors (views into one buffer), in input order."""
+        if len(wavs) == 0:  # an empty scp shard: nothing to extract
+            empty_status = torch.zeros(0, dtype=torch.int32, device=self.device)
+            return ([], empty_status) if return_status else []
         host, lengths = self.pack(wavs)
         lay = self.layout(lengths, jitter)
         wav_dev = host.to(self.device, non_blocking=True)

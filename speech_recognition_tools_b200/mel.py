@@ -124,6 +124,8 @@ class MelExtractor:
         return feats
 
     def __call__(self, wavs, cmvn: Optional[torch.Tensor] = None):
+        if len(wavs) == 0:
+            return []
         host, lengths = FdlpExtractor.pack(wavs)
         lay = self.layout(lengths)
         feats = self.forward_packed(host.to(self.device, non_blocking=True), lay, cmvn=cmvn)

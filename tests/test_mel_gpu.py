@@ -34,3 +34,19 @@ def test_mel_batch_equals_single():
     outs = ex(wavs)
     for w, o in zip(wavs, outs):
         assert torch.equal(ex([w])[0], o)
+
+
+def test_mel_empty_input_and_short_utterances():
+    """Empty input -> empty output; utterances shorter than one frame (reflect padding, one frame) match the oracle."""
+    from oracle import mel as omel
+    from speech_recognition_tools_b200.mel import MelConfig, MelExtractor
+    from speech_recognition_tools_b200 import synth
+    cfg = dict(nfilters=80, nfft=2048, fduration=0.02, frate=100, fbank_type="mel,1")
+    ex = MelExtractor(MelConfig(**cfg), device="cuda:0")
+    assert ex([]) == []
+    wavs = [synth.make_utterance("white", 3, i, T) for i, T in enumerate([2, 50, 161, 320, 1000])]
+    outs = ex(wavs)
+    for w, o in zip(wavs, outs):
+        ref = omel.mel_spectrogram(w, **cfg)
+        assert o.shape == ref.shape
+        np.testing.assert_allclose(o.cpu().numpy(), ref, rtol=0, atol=1e-4)
