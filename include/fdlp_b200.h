@@ -195,6 +195,12 @@ int mel_plan_destroy(mel_plan* plan);
 int mel_plan_get_fbank(const mel_plan* plan, double* host_out /*[nfilters, nfft/2+1]*/);
 int mel_forward(mel_plan* plan, const mel_batch* batch, void* stream);
 
+/* ---- --add_noise diff (computeFDLPSpectrogram.py:162-164): signal = convolve(signal, [1,2,3,2,0,-2,-5,-2,0,2,3,2,1],
+ *      mode='same') per utterance; the float32 result (exact for int16 input) is then fed to fdlp_forward ---- */
+int fdlp_diff_filter(const void* wav /*dev, packed*/, int32_t wav_dtype, const int64_t* utt_wav_off /*dev [n_utt+1]*/,
+                     int32_t n_utt, int64_t max_len /*longest utterance, samples*/, float* out /*dev, packed*/,
+                     void* stream);
+
 /* ---- CMVN apply (ESPnet dump.sh / Kaldi apply-cmvn, e2e/wsj/run_fdlp_e1.sh:293-303) ---- */
 int cmvn_apply(float* feats /*dev [n_frames, dim], in place*/, int64_t n_frames, int32_t dim,
                const double* stats /*dev [2, dim+1]*/, int32_t norm_vars, void* stream);

@@ -85,6 +85,7 @@ SYMBOLS = [
     ("mel_plan_get_fbank", C.c_int, [C.c_void_p, C.c_void_p]),
     ("mel_forward", C.c_int, [C.c_void_p, C.POINTER(MelBatch), C.c_void_p]),
     ("cmvn_apply", C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]),
+    ("fdlp_diff_filter", C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),
     ("fdlp_measure_fp64_peak", C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 ]
 

@@ -45,9 +45,10 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
     noise = None
     if add_noise and add_noise not in ("clean",):
         if add_noise == "diff":
-            raise NotImplementedError("--add_noise diff (13-tap FIR) is not implemented yet")
-        noise_info = add_noise.strip().split(",")
-        noise = (load_noise(noise_info[0]), float(noise_info[1]))
+            noise = "diff"  # computeFDLPSpectrogram.py:162-164: 13-tap FIR instead of a noise recording
+        else:
+            noise_info = add_noise.strip().split(",")
+            noise = (load_noise(noise_info[0]), float(noise_info[1]))
     if args.odd_mod_zero:
         print("%s: Ignoring odd modulations... " % sys.argv[0])
 
@@ -61,7 +62,9 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
         ids = [b[0] for b in batch]
         wavs = [b[1] for b in batch]
         nspec = None
-        if noise is not None:
+        if noise == "diff":
+            nspec = "diff"
+        elif noise is not None:
             draws = [np.random.rand() for _ in wavs]  # features.py:25, one draw per utterance in scp order
             nspec = NoiseSpec(samples=noise[0], snr_db=noise[1], rand=draws, mode="int16_wrap")
         outs, status = ex(wavs, jitter=_GlobalRandom(), noise=nspec, return_status=True)

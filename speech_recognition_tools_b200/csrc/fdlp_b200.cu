@@ -123,6 +123,17 @@ static int upload(T** dptr, const std::vector<T>& h) {
   return 0;
 }
 
+// The dynamic shared-memory limit is an attribute of the KERNEL, not of a plan: several plans live in one process
+// (different configurations), so the limit is only ever raised.
+template <typename K>
+static cudaError_t raise_smem_limit(K kern, size_t bytes) {
+  cudaFuncAttributes fa;
+  cudaError_t e = cudaFuncGetAttributes(&fa, kern);
+  if (e != cudaSuccess) return e;
+  if ((size_t)fa.maxDynamicSharedSizeBytes >= bytes) return cudaSuccess;
+  return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+}
+
 static int build_fft_tables(int n, FftTables* t) {
   t->n = n;
   if (factor_radices(n, t->radix, &t->npass) != 0)
@@ -603,7 +614,7 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   }
 #define SET_SMEM(kern, bytes)                                                                              \
   do {                                                                                                     \
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)); \
+    cudaError_t e = raise_smem_limit(kern, (size_t)(bytes));                                               \
     if (e != cudaSuccess) { plan_free(p); return set_err(FDLP_E_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e)); } \
   } while (0)
   if (p->dct_fp64) {
@@ -1026,7 +1037,7 @@ struct mel_plan {
 
 template <int R2, int M1, typename S>
 static cudaError_t mel_warp_launch(const MelWarpArgs& w, dim3 grid, size_t smem, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(mel_frames_warp_kernel<R2, M1, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = raise_smem_limit(mel_frames_warp_kernel<R2, M1, S>, smem);
   if (e != cudaSuccess) return e;
   mel_frames_warp_kernel<R2, M1, S><<<grid, kMelWarps * 32, smem, st>>>(w);
   return cudaGetLastError();
@@ -1122,8 +1133,8 @@ extern "C" int mel_plan_create(const mel_params* prm, mel_plan** out) {
     if (sms > 0) p->sms = sms;
   }
   p->smem = (size_t)prm->nfft * sizeof(float) + (size_t)(p->n + 1) * sizeof(float);
-  cudaError_t e = cudaFuncSetAttribute(mel_frames_kernel<int16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(mel_frames_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem);
+  cudaError_t e = raise_smem_limit(mel_frames_kernel<int16_t>, p->smem);
+  if (e == cudaSuccess) e = raise_smem_limit(mel_frames_kernel<float>, p->smem);
   if (e != cudaSuccess) { mel_free(p); return set_err(FDLP_E_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
   *out = p;
   return FDLP_OK;
@@ -1185,6 +1196,22 @@ extern "C" int mel_forward(mel_plan* p, const mel_batch* b, void* stream) {
   if (b->wav_dtype == FDLP_WAV_INT16) mel_frames_kernel<int16_t><<<grid, block, p->smem, st>>>(a);
   else if (b->wav_dtype == FDLP_WAV_FLOAT32) mel_frames_kernel<float><<<grid, block, p->smem, st>>>(a);
   else return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
+  FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
+// ================================================================ 'diff' augmentation
+extern "C" int fdlp_diff_filter(const void* wav, int32_t wav_dtype, const int64_t* utt_wav_off, int32_t n_utt,
+                                int64_t max_len, float* out, void* stream) {
+  if (n_utt < 0 || max_len < 0) return set_err(FDLP_E_ARG, "bad argument%s", "");
+  if (n_utt == 0 || max_len == 0) return FDLP_OK;
+  if (!wav || !utt_wav_off || !out) return set_err(FDLP_E_ARG, "null argument%s", "");
+  if (wav_dtype != FDLP_WAV_INT16 && wav_dtype != FDLP_WAV_FLOAT32) return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
+  if (n_utt > 65535) return set_err(FDLP_E_ARG, "too many utterances in one call%s", "");
+  DiffArgs a;
+  a.wav = wav; a.wav_dtype = wav_dtype; a.utt_wav_off = utt_wav_off; a.n_utt = n_utt; a.out = out;
+  const long long bx = std::min<long long>((max_len + 255) / 256, 1024);
+  diff_fir_kernel<<<dim3((unsigned)bx, (unsigned)n_utt), 256, 0, (cudaStream_t)stream>>>(a);
   FDLP_CUDA(cudaGetLastError());
   return FDLP_OK;
 }

@@ -76,4 +76,37 @@ __global__ void __launch_bounds__(256) noise_alpha_kernel(const NoiseArgs a) {
   }
 }
 
+// --add_noise diff (computeFDLPSpectrogram.py:162-164): signal = scipy.signal.convolve(signal, a, mode='same') with
+// the 13-tap kernel a = [1, 2, 3, 2, 0, -2, -5, -2, 0, 2, 3, 2, 1]:  out[q] = sum_t a[t] x[q + 6 - t], x zero outside
+// the utterance.  For int16 input the result is an integer below 2^20, so the float32 output is exact; for float32
+// input the sum is formed in float64 and rounded once.  HBM-bound: one read and one write of the batch.
+struct DiffArgs {
+  const void* wav;
+  int wav_dtype;
+  const int64_t* utt_wav_off;  // [n_utt+1]
+  int n_utt;
+  float* out;                  // [total samples]
+};
+
+__global__ void __launch_bounds__(256) diff_fir_kernel(const DiffArgs a) {
+  constexpr int kTaps = 13;
+  constexpr int kA[kTaps] = {1, 2, 3, 2, 0, -2, -5, -2, 0, 2, 3, 2, 1};
+  const int u = blockIdx.y;
+  const int64_t woff = a.utt_wav_off[u];
+  const int64_t T = a.utt_wav_off[u + 1] - woff;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < T; q += (int64_t)gridDim.x * blockDim.x) {
+    double acc = 0.0;
+#pragma unroll
+    for (int t = 0; t < kTaps; ++t) {
+      const int64_t i = q + 6 - t;
+      if (kA[t] != 0 && i >= 0 && i < T) {
+        const double x = (a.wav_dtype == FDLP_WAV_INT16) ? (double)reinterpret_cast<const int16_t*>(a.wav)[woff + i]
+                                                         : (double)reinterpret_cast<const float*>(a.wav)[woff + i];
+        acc += (double)kA[t] * x;
+      }
+    }
+    a.out[woff + q] = (float)acc;
+  }
+}
+
 }  // namespace fdlp

@@ -435,6 +435,22 @@ class FdlpExtractor:
             L.check(self._lib.fdlp_forward(self._plan, C.byref(b), C.c_void_p(stream)))
         return feats, status
 
+    def diff_filter(self, wav_dev: torch.Tensor, lay: BatchLayout) -> torch.Tensor:
+        """--add_noise diff (computeFDLPSpectrogram.py:162-164): the 13-tap FIR `convolve(signal, a, mode='same')`
+        applied per utterance to a packed device batch.  Returns a float32 packed batch (exact for int16 input)."""
+        lay.to(self.device)
+        out = torch.empty(wav_dev.numel(), dtype=torch.float32, device=self.device)
+        dt = L.FDLP_WAV_INT16 if wav_dev.dtype == torch.int16 else L.FDLP_WAV_FLOAT32
+        if wav_dev.dtype not in (torch.int16, torch.float32):
+            raise TypeError("waveforms must be int16 or float32")
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        with torch.cuda.device(self.device):
+            L.check(self._lib.fdlp_diff_filter(C.c_void_p(wav_dev.data_ptr()), dt,
+                                                C.c_void_p(lay.dev["utt_wav_off"].data_ptr()), lay.n_utt,
+                                                int(lay.lengths.max()) if lay.n_utt else 0,
+                                                C.c_void_p(out.data_ptr()), C.c_void_p(stream)))
+        return out
+
     def extract_host(self, host_wav: torch.Tensor, lay: BatchLayout, feats_host: Optional[torch.Tensor] = None,
                      n_chunks: int = 6, cmvn: Optional[torch.Tensor] = None, status: Optional[torch.Tensor] = None,
                      wav_dev: Optional[torch.Tensor] = None, feats: Optional[torch.Tensor] = None,
@@ -501,6 +517,11 @@ class FdlpExtractor:
         host, lengths = self.pack(wavs)
         lay = self.layout(lengths, jitter)
         wav_dev = host.to(self.device, non_blocking=True)
+        if isinstance(noise, str):
+            if noise != "diff":
+                raise ValueError("noise must be a NoiseSpec or the string 'diff'")
+            wav_dev = self.diff_filter(wav_dev, lay)
+            noise = None
         noise_dev = self._noise_to_device(noise, lay)
         feats, status = self.forward_packed(wav_dev, lay, cmvn=cmvn, noise_dev=noise_dev)
         outs = [feats[int(lay.utt_frame_off[u]):int(lay.utt_frame_off[u + 1])] for u in range(lay.n_utt)]

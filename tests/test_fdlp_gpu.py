@@ -42,7 +42,7 @@ def assert_feats_close(got, ref, atol=ATOL, rtol=RTOL):
     np.testing.assert_allclose(got[~fl_ref], ref[~fl_ref], rtol=rtol, atol=atol)
 
 
-@pytest.mark.parametrize("name", [n for n in golden_cases("fdlp") if n != "fdlp_opt_diff"])
+@pytest.mark.parametrize("name", golden_cases("fdlp"))
 def test_fdlp_matches_reference_golden(name):
     from speech_recognition_tools_b200.fdlp import NoiseSpec
     c = load_case(name)
@@ -50,7 +50,9 @@ def test_fdlp_matches_reference_golden(name):
     p, add_noise, lifter = split_params(meta)
     ex = extractor(lifter=lifter, **dict(FDLP_DEFAULTS, **p))
     noise = None
-    if add_noise and add_noise != "clean":
+    if add_noise == "diff":
+        noise = "diff"
+    elif add_noise and add_noise != "clean":
         nm, snr = add_noise.split(",")
         noise = NoiseSpec(samples=c["noise"]["data"], snr_db=float(snr), rand=meta["seed"])
     outs, st = ex([c["x"]], jitter=[meta["seed"]], noise=noise, return_status=True)
@@ -267,3 +269,16 @@ def test_edge_cases_empty_batch_and_utterances_shorter_than_a_segment():
         else:
             assert_feats_close(o.cpu().numpy(), ref)
         assert torch.equal(ex([w], jitter=[s])[0], o)
+
+
+def test_plans_of_different_sizes_coexist():
+    """The dynamic shared-memory limit belongs to the kernel, not to a plan: creating a smaller plan must not
+    break an older, larger one (regression: the limit was lowered by the most recent plan)."""
+    from speech_recognition_tools_b200.fdlp import FdlpConfig, FdlpExtractor
+    x = synth.make_utterance("white", 11, 0, 20000)
+    big = FdlpExtractor(FdlpConfig(**dict(FDLP_DEFAULTS, nfilters=24)), device="cuda:0")
+    ref = big([x], jitter=[3])[0].clone()
+    small = FdlpExtractor(FdlpConfig(**dict(FDLP_DEFAULTS, nfilters=8, order=20, coeff_num=20, coeff_range="1,20")),
+                          device="cuda:0")
+    small([x], jitter=[3])
+    assert torch.equal(big([x], jitter=[3])[0], ref)
