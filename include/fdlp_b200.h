@@ -50,6 +50,10 @@ extern "C" {
 #define FDLP_FBANK_COCHLEAR 1 /* createFbankCochlear(nfilters, 2N, srate, om_w, alp, fixed, bet, warp) :197-219 */
 #define FDLP_FBANK_CUSTOM 2   /* caller-supplied [nfilters, N+1] float64 rows (host pointer)                 */
 
+#define FDLP_WINDOW_HAMMING 0
+#define FDLP_WINDOW_HANNING 1
+#define FDLP_WINDOW_SQUARE 2
+
 #define FDLP_WAV_INT16 0
 #define FDLP_WAV_FLOAT32 1
 
@@ -76,6 +80,12 @@ typedef struct {
   const double* custom_fbank; /* host, [nfilters, N+1] when fbank_kind == FDLP_FBANK_CUSTOM, else NULL */
   int32_t dct_fp32;         /* 0: float64 shared-memory FFT when it fits (default); 1: force float32 */
   double tail_eps;          /* autocorrelation skips filter taps below tail_eps * max|F_j| (0: only exact zeros) */
+  /* modulation-spectrum extractor (computeModulationSpectrum.py): all zero for the FDLP spectrogram */
+  int32_t window_kind;      /* FDLP_WINDOW_*: getFrames window (computeFDLPSpectrogram.py:29 hamming,
+                               computeModulationSpectrum.py:31 hanning, :88-90 square) */
+  int32_t seg_shift;        /* > 0: segment shift in samples, int(srate / frate) (computeModulationSpectrum.py:143-144);
+                               0: derived from overlap_fraction */
+  int32_t cepstrum_mode;    /* 1: the plan emits cepstra (fdlp_modspec_forward): L = coeff_num, no truncation to M */
 } fdlp_params;
 
 /* Integer geometry derived exactly as the reference does (np.round = half-to-even). */
@@ -194,6 +204,14 @@ int mel_plan_create(const mel_params* params, mel_plan** out_plan);
 int mel_plan_destroy(mel_plan* plan);
 int mel_plan_get_fbank(const mel_plan* plan, double* host_out /*[nfilters, nfft/2+1]*/);
 int mel_forward(mel_plan* plan, const mel_batch* batch, void* stream);
+
+/* ---- modulation-spectrum features (computeModulationSpectrum.py:143-198, real-modulation path): per segment
+ *      (100 Hz shift, hanning window) and band the cepstrum of the sub-band LPC model; out[seg, j*feat_len + q] =
+ *      cep[seg, j, sel_idx[q]] * sel_scale[q] (absolute value if `absolute`).  Uses wav / utt_wav_off /
+ *      utt_seg_off / seg_utt / n_utt / n_seg / status of the batch; the plan must have cepstrum_mode = 1. ---- */
+int fdlp_modspec_forward(fdlp_plan* plan, const fdlp_batch* batch, const int32_t* sel_idx /*dev [feat_len]*/,
+                         const double* sel_scale /*dev [feat_len]*/, int32_t feat_len, int32_t absolute,
+                         float* out /*dev [n_seg, nfilters*feat_len]*/, void* stream);
 
 /* ---- --add_noise diff (computeFDLPSpectrogram.py:162-164): signal = convolve(signal, [1,2,3,2,0,-2,-5,-2,0,2,3,2,1],
  *      mode='same') per utterance; the float32 result (exact for int16 input) is then fed to fdlp_forward ---- */

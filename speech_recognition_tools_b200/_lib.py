@@ -15,6 +15,7 @@ FDLP_E_ARG, FDLP_E_CUDA, FDLP_E_UNSUPPORTED, FDLP_E_NOMEM = -1, -2, -3, -4
 FDLP_ST_SINGULAR, FDLP_ST_NONFINITE = 1, 2
 FDLP_FBANK_MEL, FDLP_FBANK_COCHLEAR, FDLP_FBANK_CUSTOM = 0, 1, 2
 FDLP_WAV_INT16, FDLP_WAV_FLOAT32 = 0, 1
+FDLP_WINDOW_HAMMING, FDLP_WINDOW_HANNING, FDLP_WINDOW_SQUARE = 0, 1, 2
 FDLP_NOISE_NONE, FDLP_NOISE_INT16_WRAP, FDLP_NOISE_FLOAT = 0, 1, 2
 
 
@@ -25,6 +26,7 @@ class FdlpParams(C.Structure):
         ("fbank_kind", C.c_int32), ("fbank_args", C.c_double * 5),
         ("weights", C.POINTER(C.c_double)), ("custom_fbank", C.POINTER(C.c_double)),
         ("dct_fp32", C.c_int32), ("tail_eps", C.c_double),
+        ("window_kind", C.c_int32), ("seg_shift", C.c_int32), ("cepstrum_mode", C.c_int32),
     ]
 
 
@@ -85,6 +87,7 @@ SYMBOLS = [
     ("mel_plan_get_fbank", C.c_int, [C.c_void_p, C.c_void_p]),
     ("mel_forward", C.c_int, [C.c_void_p, C.POINTER(MelBatch), C.c_void_p]),
     ("cmvn_apply", C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]),
+    ("fdlp_modspec_forward", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     ("fdlp_diff_filter", C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),
     ("fdlp_measure_fp64_peak", C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 ]

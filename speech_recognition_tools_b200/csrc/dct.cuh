@@ -47,6 +47,7 @@ struct DctArgs {
   // HC[a] = exp(j theta 64 a), HD[b] = exp(j theta b), theta = 2 pi / (N - 1); layout HC[ham_na] HD[64]
   const double2* hamt;
   int ham_na;
+  double win_a0, win_a1;  // window = a0 - a1 cos(theta i): hamming 0.54/0.46, hanning 0.5/0.5, square 1/0
   const int32_t* perm;     // [n] position of X[k] after the DIF passes
   const double2* unpackA;  // [n+1] exp(-2 pi i k / N)
   const double2* postB;    // [N]  exp(-i pi k / (2N)) * 2 / sqrt(2N)
@@ -252,12 +253,12 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
           }
           if (i0 >= 0 && i0 < N) {
             const double2 hc = sham[i0 >> 6];
-            const double w = 0.54 - 0.46 * (hc.x * hd0.x - hc.y * hd0.y);
+            const double w = a.win_a0 - a.win_a1 * (hc.x * hd0.x - hc.y * hd0.y);
             sv[(i0 & 1) ? (N - 1 - (i0 >> 1)) : (i0 >> 1)] = (T)(v0[e] * w);
           }
           if (i1 >= 0 && i1 < N) {
             const double2 hc = sham[i1 >> 6];
-            const double w = 0.54 - 0.46 * (hc.x * hd1.x - hc.y * hd1.y);
+            const double w = a.win_a0 - a.win_a1 * (hc.x * hd1.x - hc.y * hd1.y);
             sv[(i1 & 1) ? (N - 1 - (i1 >> 1)) : (i1 >> 1)] = (T)(v1[e] * w);
           }
         }

@@ -207,6 +207,8 @@ struct fdlp_plan {
   double2* d_postB = nullptr;
   double2* d_unp = nullptr;  // split unpack / post-twiddle tables
   int unp_na = 0;
+  double* d_cep = nullptr;    // [tasks, L] cepstra of fdlp_modspec_forward (cepstrum_mode plans)
+  size_t cap_cep = 0;
   double2* d_hamt = nullptr;  // split Hamming table
   int ham_na = 0;
   double* d_fbank = nullptr;
@@ -244,7 +246,7 @@ struct fdlp_plan {
 static void plan_free(fdlp_plan* p) {
   if (!p) return;
   free_fft_tables(&p->fft);
-  cudaFree(p->d_ham); cudaFree(p->d_postB); cudaFree(p->d_unp); cudaFree(p->d_hamt); cudaFree(p->d_fbank); cudaFree(p->d_row_lo); cudaFree(p->d_row_hi);
+  cudaFree(p->d_ham); cudaFree(p->d_postB); cudaFree(p->d_unp); cudaFree(p->d_hamt); cudaFree(p->d_cep); cudaFree(p->d_fbank); cudaFree(p->d_row_lo); cudaFree(p->d_row_hi);
   cudaFree(p->d_weights); cudaFree(p->d_inv_n); cudaFree(p->d_basis); cudaFree(p->d_wratio);
   cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_alpha); cudaFree(p->d_ms);
   cudaFree(p->d_tmpl); cudaFree(p->d_wsq); cudaFree(p->d_p);
@@ -463,11 +465,12 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   fdlp_geometry& g = p->g;
   g.N = (int)(prm->srate * prm->fduration);                  // features.py:134
   g.S = (int)(prm->srate / lfr);                             // features.py:135
+  if (prm->seg_shift > 0) g.S = prm->seg_shift;             // computeModulationSpectrum.py:143-144: int(srate / frate)
   g.M = 2 * (int)(prm->fduration * prm->frate);              // :201
   g.kk = (int)np_round_half_even(prm->fduration * prm->frate);       // :203
   g.kkb2 = (int)np_round_half_even(prm->fduration * prm->frate / 2); // :204
   g.kks = (int)np_round_half_even(prm->fduration * prm->frate * of); // :220
-  g.L = std::min(prm->coeff_num, g.M);
+  g.L = prm->cepstrum_mode ? prm->coeff_num : std::min(prm->coeff_num, g.M);
   g.nlags = prm->order + 2;
   const int N = g.N, J = prm->nfilters;
   if (N < 64 || N % 32 != 0 || g.S < 1 || g.M < 2 || g.kk < 1 || g.kk > g.M) {
@@ -517,6 +520,9 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
     // split Hamming table (dct.cuh): i = 64 a + b
     p->ham_na = (N + 63) / 64 + 1;
     std::vector<double2> H;
+    if (prm->window_kind < FDLP_WINDOW_HAMMING || prm->window_kind > FDLP_WINDOW_SQUARE) {
+      plan_free(p); return set_err(FDLP_E_ARG, "invalid window kind%s", "");
+    }
     const long double theta = N > 1 ? 2.0L * M_PIl / (N - 1) : 0.0L;
     for (int a = 0; a < p->ham_na; ++a) H.push_back(make_double2((double)cosl(theta * 64.0L * a), (double)sinl(theta * 64.0L * a)));
     for (int b = 0; b < 64; ++b) H.push_back(make_double2((double)cosl(theta * b), (double)sinl(theta * b)));
@@ -708,6 +714,8 @@ static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld
   a.ham = p->d_ham; a.tw = p->fft.d_tw; a.perm = p->fft.d_perm; a.unpackA = p->fft.d_unpackA; a.postB = p->d_postB;
   a.out = out; a.out_ld = out_ld; a.out_pad = out_pad; a.seg0 = seg0;
   a.tws = p->fft.d_tws; a.tws_n = p->fft.tws_n; a.unp = p->d_unp; a.unp_na = p->unp_na; a.hamt = p->d_hamt; a.ham_na = p->ham_na;
+  a.win_a0 = p->prm.window_kind == FDLP_WINDOW_HANNING ? 0.5 : p->prm.window_kind == FDLP_WINDOW_SQUARE ? 1.0 : 0.54;
+  a.win_a1 = p->prm.window_kind == FDLP_WINDOW_HANNING ? 0.5 : p->prm.window_kind == FDLP_WINDOW_SQUARE ? 0.0 : 0.46;
   for (int i = 0; i < p->fft.npass; ++i) { a.tw_off[i] = p->fft.tw_off[i]; a.tw_na[i] = p->fft.tw_na[i]; a.magic[i] = p->fft.magic[i]; }
   a.vec_ok = (((uintptr_t)b->wav) % 16 == 0) ? 1 : 0;
   const dim3 grid(nseg), block(512);
@@ -840,6 +848,7 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
   }
   FDLP_CUDA(cudaGetLastError());
   if (p->profiling && p->ev_lpc) FDLP_CUDA(cudaEventRecord(p->ev_lpc, st));
+  if (!env) return 0;  // cepstra only (fdlp_modspec_forward)
   EnvArgs e;
   e.ms = a.ms; e.basis = p->d_basis; e.wratio = p->d_wratio; e.env = env;
   e.n_tasks = a.n_tasks; e.Lp = p->Lp; e.ldb = p->ldb; e.kk = p->g.kk;
@@ -1196,6 +1205,36 @@ extern "C" int mel_forward(mel_plan* p, const mel_batch* b, void* stream) {
   if (b->wav_dtype == FDLP_WAV_INT16) mel_frames_kernel<int16_t><<<grid, block, p->smem, st>>>(a);
   else if (b->wav_dtype == FDLP_WAV_FLOAT32) mel_frames_kernel<float><<<grid, block, p->smem, st>>>(a);
   else return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
+  FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
+// ================================================================ modulation spectrum
+extern "C" int fdlp_modspec_forward(fdlp_plan* p, const fdlp_batch* b, const int32_t* sel_idx, const double* sel_scale,
+                                    int32_t feat_len, int32_t absolute, float* out, void* stream) {
+  if (!p || !b || feat_len < 0) return set_err(FDLP_E_ARG, "bad argument%s", "");
+  if (!p->prm.cepstrum_mode) return set_err(FDLP_E_ARG, "the plan was not created with cepstrum_mode = 1%s", "");
+  if (b->n_utt <= 0 || b->n_seg <= 0 || feat_len == 0) return FDLP_OK;
+  if (!b->wav || !b->utt_wav_off || !b->utt_seg_off || !b->seg_utt || !sel_idx || !sel_scale || !out)
+    return set_err(FDLP_E_ARG, "null batch pointer%s", "");
+  if (b->noise_mode != FDLP_NOISE_NONE) return set_err(FDLP_E_ARG, "noise mixing is not part of this path%s", "");
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = ensure_scratch(p, b->n_seg, b->n_utt);
+  if (rc) return rc;
+  const size_t tasks = (size_t)b->n_seg * p->prm.nfilters;
+  if (tasks > p->cap_cep) {
+    cudaFree(p->d_cep); p->d_cep = nullptr; p->cap_cep = 0;
+    FDLP_CUDA(cudaMalloc((void**)&p->d_cep, tasks * p->g.L * sizeof(double)));
+    p->cap_cep = tasks;
+  }
+  if ((rc = launch_dct(p, b, p->d_dct, p->ld, p->pad, st))) return rc;
+  if ((rc = launch_autocorr(p, p->d_dct, b->n_seg, p->d_r, st))) return rc;
+  if ((rc = launch_lpc(p, p->d_r, b->n_seg, nullptr, nullptr, p->d_cep, nullptr, b->status, b->seg_utt, st))) return rc;
+  ModspecGatherArgs g;
+  g.cep = p->d_cep; g.sel_idx = sel_idx; g.sel_scale = sel_scale; g.out = out;
+  g.n_tasks = (int64_t)tasks; g.L = p->g.L; g.feat_len = feat_len; g.absolute = absolute;
+  const long long blocks = std::min<long long>(((long long)tasks * feat_len + 255) / 256, 148LL * 16);
+  modspec_gather_kernel<<<(unsigned)blocks, 256, 0, st>>>(g);
   FDLP_CUDA(cudaGetLastError());
   return FDLP_OK;
 }

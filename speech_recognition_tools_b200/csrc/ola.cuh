@@ -95,6 +95,27 @@ __global__ void __launch_bounds__(256) ola_log_kernel(const OlaArgs a) {
   }
 }
 
+// modulation-spectrum output (computeModulationSpectrum.py:176-191): selected cepstral coefficients per band
+struct ModspecGatherArgs {
+  const double* cep;       // [n_tasks, L]
+  const int32_t* sel_idx;  // [feat_len]
+  const double* sel_scale; // [feat_len]
+  float* out;              // [n_tasks, feat_len]  == [n_seg, J * feat_len]
+  int64_t n_tasks;
+  int L, feat_len, absolute;
+};
+
+__global__ void __launch_bounds__(256) modspec_gather_kernel(const ModspecGatherArgs a) {
+  const int64_t total = a.n_tasks * a.feat_len;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t task = e / a.feat_len;
+    const int q = (int)(e - task * a.feat_len);
+    double v = a.cep[task * a.L + a.sel_idx[q]] * a.sel_scale[q];
+    if (a.absolute) v = fabs(v);
+    a.out[e] = (float)v;
+  }
+}
+
 // Kaldi apply-cmvn (--norm-vars) with global stats: x <- (x - mean) / sqrt(var)
 __global__ void cmvn_apply_kernel(float* feats, int64_t n, int dim, const double* stats, int norm_vars) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -101,3 +101,15 @@ def test_nseg_and_frame_count_formulas():
                                                       of=0.75, lfr=1 / (0.75 * 0.5))
     g = ofdlp.derived_sizes(1.5, 100, 0.25)
     assert (g["N"], g["S"], g["M"], g["kk"], g["kkb2"], g["kks"]) == (24000, 18000, 300, 150, 75, 112)
+
+
+@pytest.mark.parametrize("name", golden_cases("modspec"))
+def test_modspec_oracle_matches_reference(name):
+    """oracle/modspec.py == the unmodified computeModulationSpectrum.py on the committed fixtures."""
+    from oracle import modspec as omod
+    c = load_case(name)
+    p = dict(c["meta"]["params"])
+    got = omod.modulation_spectrum(c["x"], **p)
+    ref = c["feats"]
+    assert got.shape == ref.shape
+    np.testing.assert_allclose(got, ref, rtol=1e-6, atol=1e-9)
