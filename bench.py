@@ -34,6 +34,7 @@ from speech_recognition_tools_b200 import synth  # noqa: E402
 
 WSJ = dict(nfilters=80, order=150, fduration=1.5, frate=100, overlap_fraction=0.25, coeff_num=100,
            coeff_range="0,100", fbank_type="cochlear,1,1,1,2.5,1")
+_RESULT = []  # the one JSON line (rank 0), printed after stdout is restored
 MEL_RECIPE = dict(nfilters=80, nfft=2048, fduration=0.02, frate=100, fbank_type="mel,1")
 N_UTT = 1000
 METRIC = "audio-sec/sec (xRT) FDLP extraction"
@@ -355,7 +356,7 @@ def run_ours(args):
         dist.barrier()
         dist.destroy_process_group()
     if out is not None:
-        print(json.dumps(out))
+        _RESULT.append(json.dumps(out))
         sys.stdout.flush()
 
 
@@ -390,7 +391,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(out))
+    _RESULT.append(json.dumps(out))
     sys.stdout.flush()
 
 
@@ -401,10 +402,23 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     args = ap.parse_args()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_ours(args)
+    # stdout carries exactly one JSON line: libraries that write to file descriptor 1 (NCCL prints its version
+    # banner there) are pointed at stderr while the run is in progress
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        if args.impl == "reference":
+            run_reference(args)
+        else:
+            run_ours(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    if _RESULT:
+        print(_RESULT[0])
+        sys.stdout.flush()
 
 
 if __name__ == "__main__":
