@@ -836,7 +836,8 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
   static const bool force_rot = getenv("FDLP_LPC_ROT") != nullptr;  // the rotation-per-order register kernel (A/B runs)
   if (need <= 80 && !force_smem && !force_rot) {
     lpc_cepstrum_blk_kernel<2><<<lpc_grid, 128, 0, st>>>(a);
-  } else if (need <= 160 && !force_smem && !force_rot) {
+  } else if (p->prm.order + 1 <= 160 && !force_smem && !force_rot) {
+    // any cepstrum length: beyond 160 coefficients the kernel's vectors are circular (REVERB recipe: L = 300)
     lpc_cepstrum_blk_kernel<4><<<lpc_grid, 128, 0, st>>>(a);
   } else if (need <= 64 && !force_smem) {
     lpc_cepstrum_reg_kernel<8><<<lpc_grid, 128, 0, st>>>(a);

@@ -385,7 +385,10 @@ __device__ __forceinline__ void lev_order(double (&f)[NG][5], double (&b)[NG][5]
 // x[n] is not needed after this step, so cep[n] = v takes its place in x: the step has no store and no
 // divergent branch, and the kernel writes the whole cepstrum at the end.
 // xg: group that holds element n of x (compile-time PH in the main loop, run-time in the tail).
-template <int NG, int PH, int T>
+// WRAP (n >= 40 NG, which is > order): the vectors are circular over the 40 NG slots -- y_m = x[n - m] is non-zero
+// only for n - order <= m < n, so the 150 live values of y and of mc fit the ring; x[n] = 0 and the element that
+// leaves the last slot re-enters at slot 0.
+template <int NG, int PH, int T, bool WRAP = false>
 __device__ __forceinline__ void cep_step(double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5], const int n,
                                          const int xg, const LpcArgs& a, const int g, const int gbase,
                                          const int src_prev) {
@@ -394,15 +397,18 @@ __device__ __forceinline__ void cep_step(double (&x)[NG][5], double (&y)[NG][5],
 #pragma unroll
   for (int G = 0; G < PH; ++G) xv = (G == xg) ? x[G][T] : xv;
   const int xl = (n / C) & 7;
-  double xn = shfl_idx_d(xv, gbase | xl);
-  xn = (n <= a.order) ? xn : 0.0;
+  double xn = 0.0;
+  if constexpr (!WRAP) {
+    xn = shfl_idx_d(xv, gbase | xl);
+    xn = (n <= a.order) ? xn : 0.0;
+  }
   constexpr int qo = (1 - T + C) % C;  // n - 2 shifts so far
   double tin[PH + 1];
 #pragma unroll
   for (int G = 0; G <= PH; ++G) tin[G] = shfl_idx_d(y[G][qo], src_prev);
 #pragma unroll
   for (int G = PH; G >= 0; --G) {
-    const double from_prev_group = (G > 0) ? tin[G > 0 ? G - 1 : 0] : xn;
+    const double from_prev_group = (G > 0) ? tin[G > 0 ? G - 1 : 0] : (WRAP ? tin[PH] : xn);
     y[G][qo] = (g == 0) ? from_prev_group : tin[G];
   }
   double part[PH + 1];
@@ -452,30 +458,34 @@ __device__ __forceinline__ void lev_phase(double (&f)[NG][5], double (&b)[NG][5]
 // earlier blocks and the five 8-lane sums are independent and pipeline; and the at most four terms m >= n0,
 // (m cep[m]) x[n - m] with n - m <= 4, which every lane evaluates redundantly from x[1..4] (xs) in a short
 // serial chain without any shuffle.  mc and cep of the block are written to their owner lane at the end.
-template <int NG, int PH>
+template <int NG, int PH, bool WRAP = false>
 __device__ __forceinline__ void cep_block(double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5], const int n0,
                                           const double (&xs)[4], const LpcArgs& a, const int g, const int gbase,
                                           const int src_prev) {
   constexpr int C = 5;
+  constexpr int AG = WRAP ? NG - 1 : PH;  // last active group
   const int xl = (n0 / C) & 7;
   double S[C], xnv[C];
 #pragma unroll
   for (int T = 0; T < C; ++T) {
-    double xn = shfl_idx_d(x[PH][T], gbase | xl);
-    xn = (n0 + T <= a.order) ? xn : 0.0;
+    double xn = 0.0;
+    if constexpr (!WRAP) {
+      xn = shfl_idx_d(x[PH][T], gbase | xl);
+      xn = (n0 + T <= a.order) ? xn : 0.0;
+    }
     xnv[T] = xn;
     const int qo = (1 - T + C) % C;  // n - 2 shifts so far
-    double tin[PH + 1];
+    double tin[AG + 1];
 #pragma unroll
-    for (int G = 0; G <= PH; ++G) tin[G] = shfl_idx_d(y[G][qo], src_prev);
+    for (int G = 0; G <= AG; ++G) tin[G] = shfl_idx_d(y[G][qo], src_prev);
 #pragma unroll
-    for (int G = PH; G >= 0; --G) {
-      const double from_prev_group = (G > 0) ? tin[G > 0 ? G - 1 : 0] : xn;
+    for (int G = AG; G >= 0; --G) {
+      const double from_prev_group = (G > 0) ? tin[G > 0 ? G - 1 : 0] : (WRAP ? tin[AG] : xn);
       y[G][qo] = (g == 0) ? from_prev_group : tin[G];
     }
-    double pa[PH + 1], pb[PH + 1];
+    double pa[AG + 1], pb[AG + 1];
 #pragma unroll
-    for (int G = 0; G <= PH; ++G) {
+    for (int G = 0; G <= AG; ++G) {
       pa[G] = mc[G][0] * y[G][(0 - T + 1 + C) % C];
       pb[G] = mc[G][1] * y[G][(1 - T + 1 + C) % C];
       pa[G] = fma(mc[G][2], y[G][(2 - T + 1 + C) % C], pa[G]);
@@ -484,8 +494,12 @@ __device__ __forceinline__ void cep_block(double (&x)[NG][5], double (&y)[NG][5]
     }
     double tot = pa[0] + pb[0];
 #pragma unroll
-    for (int G = 1; G <= PH; ++G) tot += pa[G] + pb[G];
+    for (int G = 1; G <= AG; ++G) tot += pa[G] + pb[G];
     S[T] = group_sum8_d(tot);
+    // circular: slot n0 + T still holds mc[n0 + T - 40 NG].  The later steps of this block meet it against
+    // y = x[1..4] (the ring aliases x[d] and x[d + 40 NG]); that product belongs to the in-block terms below, so
+    // the slot is cleared once step T has passed it (steps before T need it: it pairs with x[40 NG - (T - T')]).
+    if constexpr (WRAP) mc[PH][T] = (g == xl) ? 0.0 : mc[PH][T];
   }
   double v[C], vn[C];
 #pragma unroll
@@ -513,6 +527,36 @@ __device__ __forceinline__ void cep_phase(double (&x)[NG][5], double (&y)[NG][5]
 #pragma unroll 1
   for (int qb = qb_lo; qb <= qb_hi; ++qb) cep_block<NG, PH>(x, y, mc, 5 * qb, xs, a, g, gbase, src_prev);
   if constexpr (PH + 1 < NG) cep_phase<NG, PH + 1>(x, y, mc, nb_full, xs, a, g, gbase, src_prev);
+}
+
+// one lap of the circular phase: blocks n0 = nbase + 5 qb', qb' = 8 PH .. 8 PH + 7, while the block ends before n_end
+template <int NG, int PH>
+__device__ __forceinline__ void cep_lap_phase(double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5],
+                                              const int nbase, const int n_end, const double (&xs)[4],
+                                              const LpcArgs& a, const int g, const int gbase, const int src_prev) {
+#pragma unroll 1
+  for (int qb = 8 * PH; qb <= 8 * PH + 7; ++qb) {
+    const int n0 = nbase + 5 * qb;
+    if (n0 + 4 >= n_end) break;
+    cep_block<NG, PH, true>(x, y, mc, n0, xs, a, g, gbase, src_prev);
+  }
+  if constexpr (PH + 1 < NG) cep_lap_phase<NG, PH + 1>(x, y, mc, nbase, n_end, xs, a, g, gbase, src_prev);
+}
+
+// cep[nbase + i], i = element index, for the elements below n_end: weighted copy for K5, plain copy on request
+template <int NG>
+__device__ __forceinline__ void cep_flush(const double (&x)[NG][5], const int nbase, const int n_end, const LpcArgs& a,
+                                          double* msg, const int task, const int g) {
+#pragma unroll
+  for (int G = 0; G < NG; ++G)
+#pragma unroll
+    for (int c = 0; c < 5; ++c) {
+      const int n = nbase + 40 * G + 5 * g + c;
+      if (n < n_end) {
+        msg[n] = x[G][c] * __ldg(a.weights + n);
+        if (a.cep_out) a.cep_out[(size_t)task * a.L + n] = x[G][c];
+      }
+    }
 }
 
 template <int NG>
@@ -601,33 +645,35 @@ __global__ void __launch_bounds__(128, (NG > 2) ? 3 : 5) lpc_cepstrum_blk_kernel
 #pragma unroll
   for (int d = 1; d <= 4; ++d) xs[d - 1] = (d <= p) ? shfl_idx_d(f[0][d], gbase) : 0.0;
   if (g0) { rr[0][1] = c1; b[0][0] = c1; f[0][0] = c0; f[0][1] = c1; }  // 1 * cep[1];  y^(1)_0 = x[1];  cep[0], cep[1]
-  if (L > 2) cep_step<NG, 0, 2>(f, b, rr, 2, 0, a, g, gbase, src_prev);
-  if (L > 3) cep_step<NG, 0, 3>(f, b, rr, 3, 0, a, g, gbase, src_prev);
-  if (L > 4) cep_step<NG, 0, 4>(f, b, rr, 4, 0, a, g, gbase, src_prev);
-  const int nb_full = (L >= 5) ? (L - 5) / C : 0;  // last block n = 5 qb .. 5 qb + 4 with 5 qb + 4 <= L - 1
+  // lap 0: steps n = 2 .. L0 - 1 with the vectors growing from slot 0
+  const int L0 = (L < GE * NG) ? L : GE * NG;
+  if (L0 > 2) cep_step<NG, 0, 2>(f, b, rr, 2, 0, a, g, gbase, src_prev);
+  if (L0 > 3) cep_step<NG, 0, 3>(f, b, rr, 3, 0, a, g, gbase, src_prev);
+  if (L0 > 4) cep_step<NG, 0, 4>(f, b, rr, 4, 0, a, g, gbase, src_prev);
+  const int nb_full = (L0 >= 5) ? (L0 - 5) / C : 0;  // last block n = 5 qb .. 5 qb + 4 with 5 qb + 4 <= L0 - 1
   cep_phase<NG, 0>(f, b, rr, nb_full, xs, a, g, gbase, src_prev);
   {
     const int n0 = C * (nb_full + 1), xg = (nb_full + 1) >> 3;
-    if (L >= 5 && n0 <= L - 1) cep_step<NG, NG - 1, 0>(f, b, rr, n0, xg, a, g, gbase, src_prev);
-    if (L >= 5 && n0 + 1 <= L - 1) cep_step<NG, NG - 1, 1>(f, b, rr, n0 + 1, xg, a, g, gbase, src_prev);
-    if (L >= 5 && n0 + 2 <= L - 1) cep_step<NG, NG - 1, 2>(f, b, rr, n0 + 2, xg, a, g, gbase, src_prev);
-    if (L >= 5 && n0 + 3 <= L - 1) cep_step<NG, NG - 1, 3>(f, b, rr, n0 + 3, xg, a, g, gbase, src_prev);
+    if (L0 >= 5 && n0 <= L0 - 1) cep_step<NG, NG - 1, 0>(f, b, rr, n0, xg, a, g, gbase, src_prev);
+    if (L0 >= 5 && n0 + 1 <= L0 - 1) cep_step<NG, NG - 1, 1>(f, b, rr, n0 + 1, xg, a, g, gbase, src_prev);
+    if (L0 >= 5 && n0 + 2 <= L0 - 1) cep_step<NG, NG - 1, 2>(f, b, rr, n0 + 2, xg, a, g, gbase, src_prev);
+    if (L0 >= 5 && n0 + 3 <= L0 - 1) cep_step<NG, NG - 1, 3>(f, b, rr, n0 + 3, xg, a, g, gbase, src_prev);
   }
-  // f now holds the cepstrum at elements 0 .. L-1: weighted copy for K5 (zero padded to Lp), plain copy on request
-  if (live) {
-#pragma unroll
-    for (int G = 0; G < NG; ++G)
-#pragma unroll
-      for (int c = 0; c < C; ++c) {
-        const int i = GE * G + C * g + c;
-        if (i < L) {
-          msg[i] = f[G][c] * __ldg(a.weights + i);
-          if (a.cep_out) a.cep_out[(size_t)task * L + i] = f[G][c];
-        } else if (i < a.Lp) {
-          msg[i] = 0.0;
-        }
-      }
+  // f now holds the cepstrum at elements 0 .. L0-1
+  if (live) cep_flush<NG>(f, 0, L0, a, msg, task, g);
+  // further laps (coeff_num > 40 NG, e.g. the REVERB recipe's 300 coefficients): circular vectors
+  for (int nbase = GE * NG; nbase < L; nbase += GE * NG) {
+    const int n_end = (L < nbase + GE * NG) ? L : nbase + GE * NG;
+    cep_lap_phase<NG, 0>(f, b, rr, nbase, n_end, xs, a, g, gbase, src_prev);
+    const int nblk = (n_end - nbase) / C;  // full blocks done above
+    const int n0 = nbase + C * nblk, xg = nblk >> 3;
+    if (n0 < n_end) cep_step<NG, NG - 1, 0, true>(f, b, rr, n0, xg, a, g, gbase, src_prev);
+    if (n0 + 1 < n_end) cep_step<NG, NG - 1, 1, true>(f, b, rr, n0 + 1, xg, a, g, gbase, src_prev);
+    if (n0 + 2 < n_end) cep_step<NG, NG - 1, 2, true>(f, b, rr, n0 + 2, xg, a, g, gbase, src_prev);
+    if (n0 + 3 < n_end) cep_step<NG, NG - 1, 3, true>(f, b, rr, n0 + 3, xg, a, g, gbase, src_prev);
+    if (live) cep_flush<NG>(f, nbase, n_end, a, msg, task, g);
   }
+  if (live && g0) for (int n = L; n < a.Lp; ++n) msg[n] = 0.0;
 
   if (bad && live && a.status && g0) {
     const int seg = task / a.J;
