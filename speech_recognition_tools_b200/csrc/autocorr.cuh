@@ -212,20 +212,29 @@ struct FamArgs {
   const int32_t* task_blk1;   // [ntask] one past the last block
   const int32_t* task_step0;  // [ntask] first step (= start of the first block)
   int n_seg, ld, nlags, nblk_total, ntask;
+  int lag_groups;             // MULTI: warps per (segment, task), each 8 (NA - 1) complete lags
 };
 
 // Blocks have variable length: their boundaries are the steps where some band's filter enters or leaves a
 // region of the template (plan analysis), so every band's range is a union of whole blocks and the direct
 // remainder is only the look-ahead window around each region boundary.  A warp owns a run of consecutive blocks
 // of one (segment, template); the accumulators are flushed whenever the step counter reaches a block end.
-template <int NA>
-__global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel(const FamArgs a) {
+// MULTI (more than 8 (NA - 1) lags, e.g. LPC order 300): lag group h of a task is a warp of its own whose B ring
+// starts NA - 1 rows ahead per group -- the groups overlap by one tile, so each holds both halves (super- and
+// sub-diagonal) of its 8 (NA - 1) lags -- and whose A fragment is loaded separately, as in autocorr_dmma_kernel.
+template <int NA, bool MULTI>
+__global__ void __launch_bounds__(kAcWarps * 32, MULTI ? 2 : 3) family_block_autocorr_kernel(const FamArgs a) {
   constexpr int RS = NA + 4;
   constexpr int U = RS / 4;
   extern __shared__ __align__(16) double cs[];  // [kAcWarps][NA + 1][kFoldStride]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const long long gw = (long long)blockIdx.x * kAcWarps + warp;
-  if (gw >= (long long)a.n_seg * a.ntask) return;  // warps are independent: no block-wide barrier below
+  long long gw = (long long)blockIdx.x * kAcWarps + warp;
+  const int lg = MULTI ? a.lag_groups : 1;
+  if (gw >= (long long)a.n_seg * a.ntask * lg) return;  // warps are independent: no block-wide barrier below
+  const int h = MULTI ? (int)(gw % lg) : 0;
+  if (MULTI) gw /= lg;
+  const int a_base = h * (NA - 1);
+  const int lag0 = 8 * a_base;
   const int seg = (int)(gw / a.ntask);
   const int task = (int)(gw % a.ntask);  // tasks are sorted by first step: neighbouring warps share rows of c
   const int fam = a.task_fam[task];
@@ -236,8 +245,12 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel
   const int lane_off = (lr << 3) + lc;
   const int m_lo = step * 4;
 
-  const double* __restrict__ pc = a.dct + (size_t)seg * a.ld + (size_t)m_lo * 8 + lane_off;
-  const double* __restrict__ pf = a.tmpl + (size_t)fam * a.ld + (size_t)m_lo * 8 + lane_off;
+  const double* __restrict__ pc = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + a_base) * 8 + lane_off;
+  const double* __restrict__ pf = a.tmpl + (size_t)fam * a.ld + (size_t)(m_lo + a_base) * 8 + lane_off;
+  const double* __restrict__ ac = a.dct + (size_t)seg * a.ld + (size_t)m_lo * 8 + lane_off;
+  const double* __restrict__ af = a.tmpl + (size_t)fam * a.ld + (size_t)m_lo * 8 + lane_off;
+  double paf = 0.0, pac = 0.0;
+  if (MULTI) { paf = __ldg(af); pac = __ldg(ac); }
   double ring[RS];
 #pragma unroll
   for (int i = 0; i < NA; ++i) ring[i] = __ldg(pf + 8 * i) * __ldg(pc + 8 * i);
@@ -251,7 +264,7 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel
 
   const FoldCtx fc = fold_ctx(cs + (size_t)warp * fold_smem_doubles(NA), lane);
   // the rows of c come from HBM (the templates stay in L1/L2): pull them into L1 two groups of U steps ahead
-  const double* cpf = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + NA + 4 + 8 * U) * 8 + lane * 16;
+  const double* cpf = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + a_base + NA + 4 + 8 * U) * 8 + lane * 16;
   const int pf_lanes = (U * 32 * 8 + 127) / 128;
   int next_end = a.bend[blk];
   double acc[NA][2];
@@ -265,11 +278,17 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel
       if (blk < blk1) {
 #pragma unroll
         for (int t = 0; t < 4; ++t) ring[(4 * s + NA + t) % RS] = qf[t] * qc[t];
-        const double afrag = ring[(4 * s) % RS];
+        const double afrag = MULTI ? paf * pac : ring[(4 * s) % RS];
         pc += 32;
         pf += 32;
 #pragma unroll
         for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
+        if (MULTI) {
+          ac += 32;
+          af += 32;
+          paf = __ldg(af);
+          pac = __ldg(ac);
+        }
 #pragma unroll
         for (int i = 0; i < NA; ++i) dmma884(acc[i][0], acc[i][1], afrag, ring[(4 * s + i) % RS]);
         ++step;
@@ -277,10 +296,10 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) family_block_autocorr_kernel
           // flush: C tiles -> shared (warp-private), diagonal sums -> P[seg][blk][0..nlags)
           fold_store_tiles<NA>(acc, fc);
           __syncwarp();
-          double* pout = a.p + ((size_t)seg * a.nblk_total + blk) * a.nlags + lane;
+          double* pout = a.p + ((size_t)seg * a.nblk_total + blk) * a.nlags + lag0 + lane;
 #pragma unroll
           for (int t = 0; t < NA / 4; ++t)
-            if (lane + 32 * t < a.nlags) pout[32 * t] = fold_lag(fc, t);
+            if ((!MULTI || lane + 32 * t < 8 * (NA - 1)) && lag0 + lane + 32 * t < a.nlags) pout[32 * t] = fold_lag(fc, t);
           __syncwarp();
 #pragma unroll
           for (int i = 0; i < NA; ++i) acc[i][0] = acc[i][1] = 0.0;
@@ -311,7 +330,7 @@ struct ScanArgs {
 };
 
 // grid (n_seg * n_scan), one thread per lag
-__global__ void __launch_bounds__(160) family_scan_kernel(const ScanArgs a) {
+__global__ void __launch_bounds__(640) family_scan_kernel(const ScanArgs a) {
   const int k = threadIdx.x;
   if (k >= a.nlags) return;
   const int seg = blockIdx.x / a.n_scan;
@@ -367,18 +386,24 @@ struct AcRangeArgs {
   int32_t mode[kCombMaxFam];
   int32_t boff[kCombMaxFam];  // first block of each family in p
   int nfam, nblk_total;
+  int lag_groups;             // MULTI: warps per (segment, band), see family_block_autocorr_kernel
 };
 
-template <int NA>
-__global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const AcRangeArgs a) {
+template <int NA, bool MULTI>
+__global__ void __launch_bounds__(kAcWarps * 32, MULTI ? 2 : 3) autocorr_ranges_kernel(const AcRangeArgs a) {
   constexpr int RS = NA + 4;
   constexpr int U = RS / 4;
   extern __shared__ __align__(16) double cs[];  // [kAcWarps][NA][kFoldStride]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int nbg = (a.J + kAcWarps - 1) / kAcWarps;
+  const int lg = MULTI ? a.lag_groups : 1;
+  const int nbg = (a.J * lg + kAcWarps - 1) / kAcWarps;
   const int seg = blockIdx.x / nbg;
-  const int band = (blockIdx.x % nbg) * kAcWarps + warp;
+  const int wid = (blockIdx.x % nbg) * kAcWarps + warp;
+  const int band = MULTI ? wid / lg : wid;
+  const int h = MULTI ? wid % lg : 0;
   if (band >= a.J) return;
+  const int a_base = h * (NA - 1);
+  const int lag0 = 8 * a_base;
   const int nr = a.nrng[band];
   // the family terms gathered in the epilogue live in HBM: start pulling their lines into L2 now
   {
@@ -407,8 +432,12 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
   for (int q = 0; q < nr; ++q) {
     const int m_lo = a.rng[(band * kMaxRanges + q) * 2], m_hi = a.rng[(band * kMaxRanges + q) * 2 + 1];
     const int nsteps = (m_hi - m_lo) >> 2;
-    const double* __restrict__ pc = a.dct + (size_t)seg * a.ld + (size_t)m_lo * 8 + lane_off;
-    const double* __restrict__ pf = a.fbank + (size_t)band * a.ld + (size_t)m_lo * 8 + lane_off;
+    const double* __restrict__ pc = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + a_base) * 8 + lane_off;
+    const double* __restrict__ pf = a.fbank + (size_t)band * a.ld + (size_t)(m_lo + a_base) * 8 + lane_off;
+    const double* __restrict__ ac = a.dct + (size_t)seg * a.ld + (size_t)m_lo * 8 + lane_off;
+    const double* __restrict__ af = a.fbank + (size_t)band * a.ld + (size_t)m_lo * 8 + lane_off;
+    double paf = 0.0, pac = 0.0;
+    if (MULTI) { paf = __ldg(af); pac = __ldg(ac); }
     if (q + 1 < nr) {  // the first rows of the next range: into L1 while this range computes
       const size_t nxt = (size_t)a.rng[(band * kMaxRanges + q + 1) * 2] * 8 + (lane & 15) * 16;
       if ((lane & 15) * 16 < (NA + 8) * 8)
@@ -430,11 +459,17 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
         if (s0 + s < nsteps) {
 #pragma unroll
           for (int t = 0; t < 4; ++t) ring[(4 * s + NA + t) % RS] = qf[t] * qc[t];
-          const double afrag = ring[(4 * s) % RS];
+          const double afrag = MULTI ? paf * pac : ring[(4 * s) % RS];
           pc += 32;
           pf += 32;
 #pragma unroll
           for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
+          if (MULTI) {
+            ac += 32;
+            af += 32;
+            paf = __ldg(af);
+            pac = __ldg(ac);
+          }
 #pragma unroll
           for (int i = 0; i < NA; ++i) dmma884(acc[i][0], acc[i][1], afrag, ring[(4 * s + i) % RS]);
         }
@@ -445,8 +480,9 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
   const FoldCtx fc = fold_ctx(cs + (size_t)warp * fold_smem_doubles(NA), lane);
   fold_store_tiles<NA>(acc, fc);
   __syncwarp();
-  double* rout = a.r + ((size_t)seg * a.J + band) * a.nlags;
-  constexpr int NT = NA / 4;  // lags per lane: k = lane + 32 t
+  double* rout = a.r + ((size_t)seg * a.J + band) * a.nlags + lag0;
+  constexpr int NT = NA / 4;  // lags per lane: k = lag0 + lane + 32 t
+  const int nl = (MULTI && a.nlags - lag0 > 8 * (NA - 1)) ? 8 * (NA - 1) : a.nlags - lag0;  // lags of this warp
   double val[NT];
 #pragma unroll
   for (int t = 0; t < NT; ++t) val[t] = fold_lag(fc, t);
@@ -457,12 +493,12 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
       const int b0 = a.ra[g * a.J + band], b1 = a.rb[g * a.J + band];
       if (b1 > b0) {
         const double w = a.wsq[(size_t)band * a.nfam + g];
-        const double* pg = a.p + ((size_t)seg * a.nblk_total + a.boff[g]) * a.nlags + lane;
+        const double* pg = a.p + ((size_t)seg * a.nblk_total + a.boff[g]) * a.nlags + lag0 + lane;
         if (a.mode[g] != kCombRange) {
           const double* row = pg + (size_t)((a.mode[g] == kCombPrefix) ? b1 - 1 : b0) * a.nlags;
           double v[NT];
 #pragma unroll
-          for (int t = 0; t < NT; ++t) v[t] = (lane + 32 * t < a.nlags) ? row[32 * t] : 0.0;
+          for (int t = 0; t < NT; ++t) v[t] = (lane + 32 * t < nl) ? row[32 * t] : 0.0;
 #pragma unroll
           for (int t = 0; t < NT; ++t) val[t] = fma(w, v[t], val[t]);
         } else {
@@ -475,7 +511,7 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
             double v0[NT], v1[NT];
 #pragma unroll
             for (int t = 0; t < NT; ++t) {
-              const bool in = lane + 32 * t < a.nlags;
+              const bool in = lane + 32 * t < nl;
               v0[t] = in ? r0p[32 * t] : 0.0;
               v1[t] = (in && two) ? r0p[a.nlags + 32 * t] : 0.0;
             }
@@ -490,7 +526,7 @@ __global__ void __launch_bounds__(kAcWarps * 32, 3) autocorr_ranges_kernel(const
   }
 #pragma unroll
   for (int t = 0; t < NT; ++t)
-    if (lane + 32 * t < a.nlags) rout[lane + 32 * t] = val[t];
+    if (lane + 32 * t < nl) rout[lane + 32 * t] = val[t];
 }
 
 }  // namespace fdlp

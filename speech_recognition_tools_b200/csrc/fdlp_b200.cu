@@ -217,6 +217,7 @@ struct fdlp_plan {
   int Lp = 0, ldb = 0, env_ny = 1, lpc_threads = 256;
   // family decomposition of the autocorrelation (autocorr.cuh): templates, per-band block classes, direct ranges
   bool fam_ok = false;       // the plan found templates and may use the family path
+  int fam_na = 0, fam_groups = 1;  // its lag blocking: fam_groups warps of fam_na tiles, 8 (fam_na - 1) lags each
   int ac_mode = 0;           // 0: family path when available, 1: always the direct per-band kernel
   int nfam = 0, nblk = 0 /* blocks of all templates */, fam_ntask = 0;
   int32_t comb_mode[3] = {0, 0, 0}, comb_nband[3] = {0, 0, 0}, comb_boff[3] = {0, 0, 0}, comb_nblk[3] = {0, 0, 0};
@@ -292,12 +293,16 @@ static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, cons
   const fdlp_params& prm = p->prm;
   const int N = p->g.N, J = prm.nfilters;
   p->fam_ok = false;
-  if (prm.fbank_kind != FDLP_FBANK_COCHLEAR || p->a_groups != 1) return 0;
+  if (prm.fbank_kind != FDLP_FBANK_COCHLEAR) return 0;
+  // one lag group of p->na tiles when the general kernel needs one; else groups of 20 tiles overlapping by one
+  p->fam_na = (p->a_groups == 1) ? p->na : 20;
+  p->fam_groups = (p->a_groups == 1) ? 1 : (p->g.nlags + 8 * (p->fam_na - 1) - 1) / (8 * (p->fam_na - 1));
+  if (p->fam_groups > 4) return 0;
   const double alp = prm.fbank_args[1], bet = prm.fbank_args[3], warp = prm.fbank_args[4];
   const int fixed = (int)prm.fbank_args[2];
   const int nfam = (fixed == 1) ? 3 : 2;
   const int ST = N / 32;       // steps of 32 samples (4 rows of 8): the granularity of the DMMA loops
-  const int look = 8 * p->na;  // lags the DMMA tiles evaluate
+  const int look = 8 * ((p->fam_groups - 1) * (p->fam_na - 1) + p->fam_na);  // lags the DMMA tiles evaluate
   const double tol = 1e-12;
   if (ST < 64) return 0;
 
@@ -435,12 +440,12 @@ static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, cons
       (rc = upload(&p->d_task_step0, task_step0)))
     return rc;
   p->nfam = nfam; p->nblk = nblk_total; p->fam_ntask = (int)task_fam.size();
-  p->fam_smem = (size_t)kAcWarps * fold_smem_doubles(p->na) * sizeof(double);
+  p->fam_smem = (size_t)kAcWarps * fold_smem_doubles(p->fam_na) * sizeof(double);
   p->g.family_taps = fam_taps;
   p->g.direct_taps = direct_taps;
   p->g.nfam = nfam;
   p->g.block_len = (int32_t)(fam_taps / nblk_total);  // average block length in samples
-  p->fam_ok = p->g.nlags <= 160;
+  p->fam_ok = true;
   return 0;
 }
 
@@ -488,7 +493,9 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   }
   p->a_groups = groups;
   p->na = (((na_total + groups - 1) / groups) + 3) & ~3;
-  p->pad = 8 * (p->na * groups + 12);
+  int ext_rows = p->na * groups;  // rows past N the fragment streams may read
+  if (groups > 1) ext_rows = std::max(ext_rows, 19 * ((g.nlags + 151) / 152 - 1) + 20);  // family lag groups (build_families)
+  p->pad = 8 * (ext_rows + 12);
   p->ld = N + p->pad;
   if (p->pad > N / 2) {
     plan_free(p);
@@ -645,12 +652,17 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   if (p->fam_ok) {
 #define SET_FAM(NA_)                                                        \
   case NA_:                                                                 \
-    SET_SMEM((family_block_autocorr_kernel<NA_>), p->fam_smem);             \
-    SET_SMEM((autocorr_ranges_kernel<NA_>), p->fam_smem);                   \
+    SET_SMEM((family_block_autocorr_kernel<NA_, false>), p->fam_smem);      \
+    SET_SMEM((autocorr_ranges_kernel<NA_, false>), p->fam_smem);            \
     break;
-    switch (p->na) {
-      SET_FAM(4) SET_FAM(8) SET_FAM(12) SET_FAM(16) SET_FAM(20)
-      default: p->fam_ok = false;
+    if (p->fam_groups > 1) {
+      SET_SMEM((family_block_autocorr_kernel<20, true>), p->fam_smem);
+      SET_SMEM((autocorr_ranges_kernel<20, true>), p->fam_smem);
+    } else {
+      switch (p->fam_na) {
+        SET_FAM(4) SET_FAM(8) SET_FAM(12) SET_FAM(16) SET_FAM(20)
+        default: p->fam_ok = false;
+      }
     }
 #undef SET_FAM
   }
@@ -770,12 +782,14 @@ static int launch_autocorr_family(fdlp_plan* p, const double* dct, int n_seg, do
   f.dct = dct; f.tmpl = p->d_tmpl; f.p = p->d_p; f.bend = p->d_bend; f.task_fam = p->d_task_fam;
   f.task_blk0 = p->d_task_blk0; f.task_blk1 = p->d_task_blk1; f.task_step0 = p->d_task_step0;
   f.n_seg = n_seg; f.ld = p->ld; f.nlags = p->g.nlags; f.nblk_total = p->nblk; f.ntask = p->fam_ntask;
-  const long long tasks = (long long)n_seg * p->fam_ntask;
+  f.lag_groups = p->fam_groups;
+  const long long tasks = (long long)n_seg * p->fam_ntask * p->fam_groups;
   const dim3 gridA((unsigned)((tasks + kAcWarps - 1) / kAcWarps)), block(kAcWarps * 32);
   AcRangeArgs d;
   d.dct = dct; d.fbank = p->d_fbank; d.nrng = p->d_nrng; d.rng = p->d_rng; d.r = r;
   d.J = p->prm.nfilters; d.nlags = p->g.nlags; d.n_seg = n_seg; d.ld = p->ld;
-  const int nbg = (d.J + kAcWarps - 1) / kAcWarps;
+  d.lag_groups = p->fam_groups;
+  const int nbg = (d.J * p->fam_groups + kAcWarps - 1) / kAcWarps;
   const dim3 gridD((unsigned)((size_t)n_seg * nbg));
   d.p = p->d_p; d.ra = p->d_ra; d.rb = p->d_rb; d.wsq = p->d_wsq; d.nfam = p->nfam; d.nblk_total = p->nblk;
   ScanArgs c;
@@ -789,21 +803,29 @@ static int launch_autocorr_family(fdlp_plan* p, const double* dct, int n_seg, do
       c.mode[c.n_scan] = p->comb_mode[g]; c.boff[c.n_scan] = p->comb_boff[g]; c.nblk[c.n_scan] = p->comb_nblk[g];
       ++c.n_scan;
     }
-  const dim3 gridC((unsigned)((size_t)n_seg * std::max(c.n_scan, 1))), blockC(160);
-#define RUN_FAM_A(NA_) case NA_: family_block_autocorr_kernel<NA_><<<gridA, block, p->fam_smem, st>>>(f); break;
-#define RUN_FAM_D(NA_) case NA_: autocorr_ranges_kernel<NA_><<<gridD, block, p->fam_smem, st>>>(d); break;
-  switch (p->na) {
-    RUN_FAM_A(4) RUN_FAM_A(8) RUN_FAM_A(12) RUN_FAM_A(16) RUN_FAM_A(20)
-    default: return set_err(FDLP_E_UNSUPPORTED, "unsupported lag blocking%s", "");
+  const dim3 gridC((unsigned)((size_t)n_seg * std::max(c.n_scan, 1))), blockC((unsigned)((p->g.nlags + 31) & ~31));
+#define RUN_FAM_A(NA_) case NA_: family_block_autocorr_kernel<NA_, false><<<gridA, block, p->fam_smem, st>>>(f); break;
+#define RUN_FAM_D(NA_) case NA_: autocorr_ranges_kernel<NA_, false><<<gridD, block, p->fam_smem, st>>>(d); break;
+  if (p->fam_groups > 1) {
+    family_block_autocorr_kernel<20, true><<<gridA, block, p->fam_smem, st>>>(f);
+  } else {
+    switch (p->fam_na) {
+      RUN_FAM_A(4) RUN_FAM_A(8) RUN_FAM_A(12) RUN_FAM_A(16) RUN_FAM_A(20)
+      default: return set_err(FDLP_E_UNSUPPORTED, "unsupported lag blocking%s", "");
+    }
   }
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev_ac[1], st));
   if (c.n_scan > 0) family_scan_kernel<<<gridC, blockC, 0, st>>>(c);
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev_ac[2], st));
-  switch (p->na) {
-    RUN_FAM_D(4) RUN_FAM_D(8) RUN_FAM_D(12) RUN_FAM_D(16) RUN_FAM_D(20)
-    default: return set_err(FDLP_E_UNSUPPORTED, "unsupported lag blocking%s", "");
+  if (p->fam_groups > 1) {
+    autocorr_ranges_kernel<20, true><<<gridD, block, p->fam_smem, st>>>(d);
+  } else {
+    switch (p->fam_na) {
+      RUN_FAM_D(4) RUN_FAM_D(8) RUN_FAM_D(12) RUN_FAM_D(16) RUN_FAM_D(20)
+      default: return set_err(FDLP_E_UNSUPPORTED, "unsupported lag blocking%s", "");
+    }
   }
 #undef RUN_FAM_A
 #undef RUN_FAM_D
@@ -875,7 +897,7 @@ static int launch_noise(fdlp_plan* p, const fdlp_batch* b, cudaStream_t st) {
   NoiseArgs a;
   a.wav = b->wav; a.wav_dtype = b->wav_dtype; a.utt_wav_off = b->utt_wav_off; a.noise = (const int16_t*)b->noise;
   a.utt_noise_off = b->utt_noise_off; a.utt_snr_db = b->utt_snr_db; a.utt_alpha = p->d_alpha; a.mode = b->noise_mode;
-  noise_alpha_kernel<<<b->n_utt, 256, 0, st>>>(a);
+  noise_alpha_kernel<<<b->n_utt, kNoiseThreads, 0, st>>>(a);
   FDLP_CUDA(cudaGetLastError());
   return 0;
 }

@@ -30,7 +30,42 @@ __device__ __forceinline__ long long wrap_sq16(int v) {
   return (long long)(short)(v * v);  // int16 * int16 -> int16 with wrap-around, as numpy does
 }
 
-__global__ void __launch_bounds__(256) noise_alpha_kernel(const NoiseArgs a) {
+constexpr int kNoiseThreads = 512;
+
+// sum of squares of T int16 samples at an arbitrarily aligned address: 16-byte loads (8 samples) over the aligned
+// body, scalar head and tail.  Integer (wrapped) sums are exact in any order; the float sums are float64.
+__device__ __forceinline__ void sum_sq_i16(const int16_t* __restrict__ p, const int64_t T, const bool wrap,
+                                           long long& isum, double& fsum) {
+  const int64_t mis = (int64_t)((16 - (reinterpret_cast<uintptr_t>(p) & 15)) & 15) >> 1;
+  const int64_t head = (mis < T) ? mis : T;
+  const int64_t nvec = (T - head) >> 3;
+  const uint4* __restrict__ v = reinterpret_cast<const uint4*>(p + head);
+  long long i0 = 0, i1 = 0;
+  double f0 = 0.0, f1 = 0.0;
+  for (int64_t i = threadIdx.x; i < nvec; i += kNoiseThreads) {
+    const uint4 q = __ldg(v + i);
+    const unsigned w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int lo = (short)(w[c] & 0xffffu), hi = (short)(w[c] >> 16);
+      if (wrap) { i0 += wrap_sq16(lo); i1 += wrap_sq16(hi); }
+      else { f0 += (double)(lo * lo); f1 += (double)(hi * hi); }
+    }
+  }
+  for (int64_t i = threadIdx.x; i < head; i += kNoiseThreads) {
+    const int sv = p[i];
+    if (wrap) i0 += wrap_sq16(sv); else f0 += (double)(sv * sv);
+  }
+  for (int64_t i = head + 8 * nvec + threadIdx.x; i < T; i += kNoiseThreads) {
+    const int sv = p[i];
+    if (wrap) i1 += wrap_sq16(sv); else f1 += (double)(sv * sv);
+  }
+  isum += i0 + i1;
+  fsum += f0 + f1;
+}
+
+// one CTA per utterance; HBM-bound (one read of the utterance and of its noise excerpt)
+__global__ void __launch_bounds__(kNoiseThreads) noise_alpha_kernel(const NoiseArgs a) {
   const int u = blockIdx.x;
   const int64_t woff = a.utt_wav_off[u];
   const int64_t T = a.utt_wav_off[u + 1] - woff;
@@ -38,25 +73,28 @@ __global__ void __launch_bounds__(256) noise_alpha_kernel(const NoiseArgs a) {
   long long is = 0, in = 0;
   double fs = 0.0, fn = 0.0;
   const bool wrap = (a.mode == FDLP_NOISE_INT16_WRAP);
+  sum_sq_i16(nz, T, wrap, in, fn);
   if (a.wav_dtype == FDLP_WAV_INT16) {
-    const int16_t* s = reinterpret_cast<const int16_t*>(a.wav) + woff;
-    for (int64_t i = threadIdx.x; i < T; i += blockDim.x) {
-      const int sv = s[i], nv = nz[i];
-      if (wrap) { is += wrap_sq16(sv); in += wrap_sq16(nv); }
-      else { fs += (double)sv * sv; fn += (double)nv * nv; }
-    }
+    sum_sq_i16(reinterpret_cast<const int16_t*>(a.wav) + woff, T, wrap, is, fs);
   } else {
     const float* s = reinterpret_cast<const float*>(a.wav) + woff;
-    for (int64_t i = threadIdx.x; i < T; i += blockDim.x) {
-      const float sv = s[i];
-      const int nv = nz[i];
-      // float32 signal: numpy squares in float32 (rounded), the noise is still int16
-      if (wrap) { fs += (double)__fmul_rn(sv, sv); in += wrap_sq16(nv); }
-      else { fs += (double)sv * sv; fn += (double)nv * nv; }
+    double f0 = 0.0, f1 = 0.0;
+    int64_t i = threadIdx.x;
+    for (; i + kNoiseThreads < T; i += 2 * kNoiseThreads) {
+      const float s0 = __ldg(s + i), s1 = __ldg(s + i + kNoiseThreads);
+      // float32 signal: numpy squares in float32 (rounded) before the float64 mean
+      if (wrap) { f0 += (double)__fmul_rn(s0, s0); f1 += (double)__fmul_rn(s1, s1); }
+      else { f0 += (double)s0 * s0; f1 += (double)s1 * s1; }
     }
+    if (i < T) {
+      const float s0 = __ldg(s + i);
+      f0 += wrap ? (double)__fmul_rn(s0, s0) : (double)s0 * s0;
+    }
+    fs = f0 + f1;
   }
-  __shared__ long long sh_i[2][8];
-  __shared__ double sh_f[2][8];
+  constexpr int kW = kNoiseThreads / 32;
+  __shared__ long long sh_i[2][kW];
+  __shared__ double sh_f[2][kW];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int o = 16; o > 0; o >>= 1) {
     is += __shfl_xor_sync(0xffffffffu, is, o);
@@ -69,7 +107,7 @@ __global__ void __launch_bounds__(256) noise_alpha_kernel(const NoiseArgs a) {
   if (threadIdx.x == 0) {
     long long tis = 0, tin = 0;
     double tfs = 0, tfn = 0;
-    for (int w = 0; w < 8; ++w) { tis += sh_i[0][w]; tin += sh_i[1][w]; tfs += sh_f[0][w]; tfn += sh_f[1][w]; }
+    for (int w = 0; w < kW; ++w) { tis += sh_i[0][w]; tin += sh_i[1][w]; tfs += sh_f[0][w]; tfn += sh_f[1][w]; }
     const double Es = ((double)tis + tfs) / (double)T;
     const double En = ((double)tin + tfn) / (double)T;
     a.utt_alpha[u] = sqrt(Es / (En * pow(10.0, a.utt_snr_db[u] / 10.0)));

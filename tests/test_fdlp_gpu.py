@@ -243,6 +243,36 @@ def test_family_autocorrelation_matches_direct_kernel_and_oracle():
     np.testing.assert_allclose(feats_fam, feats_dir, rtol=2e-7, atol=5e-6)
 
 
+@pytest.mark.parametrize("order,nfilters,fduration", [(300, 40, 2.0), (155, 30, 1.5), (301, 24, 1.5)])
+def test_family_autocorrelation_with_several_lag_groups(order, nfilters, fduration):
+    """LPC orders above 150 need more than 152 lags: the family kernels then run one warp per group of 152 lags
+    (autocorr.cuh MULTI).  Same checks as above against the direct kernel and the oracle's autocorrelation."""
+    kw = dict(nfilters=nfilters, order=order, fduration=fduration, frate=100, overlap_fraction=0.25, coeff_num=100,
+              coeff_range="0,100", fbank_type="cochlear,1,1,1,2.5,1")
+    x = synth.make_utterance("speechlike", 4, 2, 100000, 3.0)
+    ex = extractor(**kw)
+    g = ex.geom
+    assert g["nfam"] == 3 and g["family_taps"] > 0, "the plan did not take the family path"
+    dct, _ = ex.stage_dct([x])
+    r_fam = ex.stage_autocorr(dct).cpu().numpy()
+    feats_fam = ex([x], jitter=[2])[0].cpu().numpy()
+    ex.set_autocorr_mode("direct")
+    try:
+        r_dir = ex.stage_autocorr(dct).cpu().numpy()
+        feats_dir = ex([x], jitter=[2])[0].cpu().numpy()
+    finally:
+        ex.set_autocorr_mode("auto")
+    N = g["N"]
+    fb = ofdlp.make_fbank(kw["fbank_type"], nfilters, 2 * N, 16000)[:, :-1]
+    d = dct.cpu().numpy()
+    r_ref = np.stack([ofdlp.autocorr_circular(fb * d[i])[:, :order + 2] for i in range(d.shape[0])])
+    r0 = r_ref[:, :, :1]
+    assert r_fam.shape == r_ref.shape
+    assert np.max(np.abs(r_dir - r_ref) / r0) < 1e-12
+    assert np.max(np.abs(r_fam - r_ref) / r0) < 1e-12
+    np.testing.assert_allclose(feats_fam, feats_dir, rtol=2e-7, atol=5e-6)
+
+
 def test_extract_host_pipeline_equals_single_batch():
     """The chunked host->device->host pipeline (copies overlapping the kernels) must give bit-identical
     features and CMVN-independent results to one forward_packed over the whole batch."""
