@@ -857,10 +857,15 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
   if (grid_cap > 0) lpc_grid = std::min(lpc_grid, grid_cap);
   static const bool force_rot = getenv("FDLP_LPC_ROT") != nullptr;  // the rotation-per-order register kernel (A/B runs)
   if (need <= 80 && !force_smem && !force_rot) {
-    lpc_cepstrum_blk_kernel<2><<<lpc_grid, 128, 0, st>>>(a);
+    lpc_cepstrum_blk_kernel<2, 8><<<lpc_grid, 128, 0, st>>>(a);
   } else if (p->prm.order + 1 <= 160 && !force_smem && !force_rot) {
     // any cepstrum length: beyond 160 coefficients the kernel's vectors are circular (REVERB recipe: L = 300)
-    lpc_cepstrum_blk_kernel<4><<<lpc_grid, 128, 0, st>>>(a);
+    lpc_cepstrum_blk_kernel<4, 8><<<lpc_grid, 128, 0, st>>>(a);
+  } else if (p->prm.order + 1 <= 320 && !force_smem && !force_rot) {
+    // orders 160..319: 16 lanes per solve, 8 solves per CTA
+    int grid16 = (a.n_tasks + 7) / 8;
+    if (grid_cap > 0) grid16 = std::min(grid16, grid_cap);
+    lpc_cepstrum_blk_kernel<4, 16><<<grid16, 128, 0, st>>>(a);
   } else if (need <= 64 && !force_smem) {
     lpc_cepstrum_reg_kernel<8><<<lpc_grid, 128, 0, st>>>(a);
   } else if (need <= 160 && !force_smem) {

@@ -313,8 +313,10 @@ __device__ __forceinline__ double shfl_xor_d(const double v, const int mask) {
   const int hi = __shfl_xor_sync(0xffffffffu, __double2hiint(v), mask);
   return __hiloint2double(hi, lo);
 }
-// sum over the 8 lanes of a group, bit-identical in every lane (each level adds a symmetric pair)
-__device__ __forceinline__ double group_sum8_d(double v) {
+// sum over the LS (8 or 16) lanes of a solve, bit-identical in every lane (each level adds a symmetric pair)
+template <int LS>
+__device__ __forceinline__ double group_sum_d(double v) {
+  if constexpr (LS == 16) v += shfl_xor_d(v, 8);
   v += shfl_xor_d(v, 4);
   v += shfl_xor_d(v, 2);
   v += shfl_xor_d(v, 1);
@@ -338,7 +340,7 @@ __device__ __forceinline__ double rcp_newton(const double x) {
 //   f' = f + k shift(b),  b' = shift(b) + k f,  acc' = sum_j b'_j r[j+1]
 // (Forming acc' as S1 + k S2 from lane-local sums that do not need k shortens the serial chain but costs five
 // more DFMA per group and order; measured, the FP64 pipe then sets the time: 5.6 ms against 5.98 ms.)
-template <int NG, int PH, int T>
+template <int NG, int LS, int PH, int T>
 __device__ __forceinline__ void lev_order(double (&f)[NG][5], double (&b)[NG][5], const double (&rr)[NG][5],
                                           double& acc, double& E, const bool g0, const int src_prev) {
   constexpr int C = 5;
@@ -378,7 +380,7 @@ __device__ __forceinline__ void lev_order(double (&f)[NG][5], double (&b)[NG][5]
     if constexpr (PH >= 3) { const double t3 = pa[3] + pb[3]; t2 += t3; }
     t0 += t2;
   }
-  acc = group_sum8_d(t0);
+  acc = group_sum_d<LS>(t0);
 }
 
 // One cepstrum step n (T = n % 5): y shifts by one with x[n] entering at element 0, v = x[n] + (1/n) sum mc y.
@@ -388,7 +390,7 @@ __device__ __forceinline__ void lev_order(double (&f)[NG][5], double (&b)[NG][5]
 // WRAP (n >= 40 NG, which is > order): the vectors are circular over the 40 NG slots -- y_m = x[n - m] is non-zero
 // only for n - order <= m < n, so the 150 live values of y and of mc fit the ring; x[n] = 0 and the element that
 // leaves the last slot re-enters at slot 0.
-template <int NG, int PH, int T, bool WRAP = false>
+template <int NG, int LS, int PH, int T, bool WRAP = false>
 __device__ __forceinline__ void cep_step(double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5], const int n,
                                          const int xg, const LpcArgs& a, const int g, const int gbase,
                                          const int src_prev) {
@@ -396,7 +398,7 @@ __device__ __forceinline__ void cep_step(double (&x)[NG][5], double (&y)[NG][5],
   double xv = x[PH][T];
 #pragma unroll
   for (int G = 0; G < PH; ++G) xv = (G == xg) ? x[G][T] : xv;
-  const int xl = (n / C) & 7;
+  const int xl = (n / C) & (LS - 1);
   double xn = 0.0;
   if constexpr (!WRAP) {
     xn = shfl_idx_d(xv, gbase | xl);
@@ -424,7 +426,7 @@ __device__ __forceinline__ void cep_step(double (&x)[NG][5], double (&y)[NG][5],
   double tot = part[0];
 #pragma unroll
   for (int G = 1; G <= PH; ++G) tot += part[G];
-  const double v = fma(group_sum8_d(tot), __ldg(a.inv_n + n), xn);
+  const double v = fma(group_sum_d<LS>(tot), __ldg(a.inv_n + n), xn);
   const double vn = v * (double)n;
 #pragma unroll
   for (int G = 0; G <= PH; ++G) {
@@ -436,21 +438,21 @@ __device__ __forceinline__ void cep_step(double (&x)[NG][5], double (&y)[NG][5],
 
 // blocks of five unguarded orders m = 5 qb + t for the blocks qb of phase PH (8 PH <= qb <= 8 PH + 7), then
 // the next phase
-template <int NG, int PH>
+template <int NG, int LS, int PH>
 __device__ __forceinline__ void lev_phase(double (&f)[NG][5], double (&b)[NG][5], const double (&rr)[NG][5],
                                           double& acc, double& E, const bool g0, const int src_prev,
                                           const int qb_full) {
-  const int qb_lo = (PH == 0) ? 1 : 8 * PH;
-  const int qb_hi = (8 * PH + 7 < qb_full) ? 8 * PH + 7 : qb_full;
+  const int qb_lo = (PH == 0) ? 1 : LS * PH;
+  const int qb_hi = (LS * PH + LS - 1 < qb_full) ? LS * PH + LS - 1 : qb_full;
 #pragma unroll 1
   for (int qb = qb_lo; qb <= qb_hi; ++qb) {
-    lev_order<NG, PH, 0>(f, b, rr, acc, E, g0, src_prev);
-    lev_order<NG, PH, 1>(f, b, rr, acc, E, g0, src_prev);
-    lev_order<NG, PH, 2>(f, b, rr, acc, E, g0, src_prev);
-    lev_order<NG, PH, 3>(f, b, rr, acc, E, g0, src_prev);
-    lev_order<NG, PH, 4>(f, b, rr, acc, E, g0, src_prev);
+    lev_order<NG, LS, PH, 0>(f, b, rr, acc, E, g0, src_prev);
+    lev_order<NG, LS, PH, 1>(f, b, rr, acc, E, g0, src_prev);
+    lev_order<NG, LS, PH, 2>(f, b, rr, acc, E, g0, src_prev);
+    lev_order<NG, LS, PH, 3>(f, b, rr, acc, E, g0, src_prev);
+    lev_order<NG, LS, PH, 4>(f, b, rr, acc, E, g0, src_prev);
   }
-  if constexpr (PH + 1 < NG) lev_phase<NG, PH + 1>(f, b, rr, acc, E, g0, src_prev, qb_full);
+  if constexpr (PH + 1 < NG) lev_phase<NG, LS, PH + 1>(f, b, rr, acc, E, g0, src_prev, qb_full);
 }
 
 // Five cepstrum steps n = n0 .. n0 + 4 (n0 a multiple of 5, >= 5).  The sum of step n splits into the terms
@@ -458,13 +460,13 @@ __device__ __forceinline__ void lev_phase(double (&f)[NG][5], double (&b)[NG][5]
 // earlier blocks and the five 8-lane sums are independent and pipeline; and the at most four terms m >= n0,
 // (m cep[m]) x[n - m] with n - m <= 4, which every lane evaluates redundantly from x[1..4] (xs) in a short
 // serial chain without any shuffle.  mc and cep of the block are written to their owner lane at the end.
-template <int NG, int PH, bool WRAP = false>
+template <int NG, int LS, int PH, bool WRAP = false>
 __device__ __forceinline__ void cep_block(double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5], const int n0,
                                           const double (&xs)[4], const LpcArgs& a, const int g, const int gbase,
                                           const int src_prev) {
   constexpr int C = 5;
   constexpr int AG = WRAP ? NG - 1 : PH;  // last active group
-  const int xl = (n0 / C) & 7;
+  const int xl = (n0 / C) & (LS - 1);
   double S[C], xnv[C];
 #pragma unroll
   for (int T = 0; T < C; ++T) {
@@ -495,7 +497,7 @@ __device__ __forceinline__ void cep_block(double (&x)[NG][5], double (&y)[NG][5]
     double tot = pa[0] + pb[0];
 #pragma unroll
     for (int G = 1; G <= AG; ++G) tot += pa[G] + pb[G];
-    S[T] = group_sum8_d(tot);
+    S[T] = group_sum_d<LS>(tot);
     // circular: slot n0 + T still holds mc[n0 + T - 40 NG].  The later steps of this block meet it against
     // y = x[1..4] (the ring aliases x[d] and x[d + 40 NG]); that product belongs to the in-block terms below, so
     // the slot is cleared once step T has passed it (steps before T need it: it pairs with x[40 NG - (T - T')]).
@@ -518,40 +520,40 @@ __device__ __forceinline__ void cep_block(double (&x)[NG][5], double (&y)[NG][5]
   }
 }
 
-template <int NG, int PH>
+template <int NG, int LS, int PH>
 __device__ __forceinline__ void cep_phase(double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5],
                                           const int nb_full, const double (&xs)[4], const LpcArgs& a, const int g,
                                           const int gbase, const int src_prev) {
-  const int qb_lo = (PH == 0) ? 1 : 8 * PH;
-  const int qb_hi = (8 * PH + 7 < nb_full) ? 8 * PH + 7 : nb_full;
+  const int qb_lo = (PH == 0) ? 1 : LS * PH;
+  const int qb_hi = (LS * PH + LS - 1 < nb_full) ? LS * PH + LS - 1 : nb_full;
 #pragma unroll 1
-  for (int qb = qb_lo; qb <= qb_hi; ++qb) cep_block<NG, PH>(x, y, mc, 5 * qb, xs, a, g, gbase, src_prev);
-  if constexpr (PH + 1 < NG) cep_phase<NG, PH + 1>(x, y, mc, nb_full, xs, a, g, gbase, src_prev);
+  for (int qb = qb_lo; qb <= qb_hi; ++qb) cep_block<NG, LS, PH>(x, y, mc, 5 * qb, xs, a, g, gbase, src_prev);
+  if constexpr (PH + 1 < NG) cep_phase<NG, LS, PH + 1>(x, y, mc, nb_full, xs, a, g, gbase, src_prev);
 }
 
 // one lap of the circular phase: blocks n0 = nbase + 5 qb', qb' = 8 PH .. 8 PH + 7, while the block ends before n_end
-template <int NG, int PH>
+template <int NG, int LS, int PH>
 __device__ __forceinline__ void cep_lap_phase(double (&x)[NG][5], double (&y)[NG][5], double (&mc)[NG][5],
                                               const int nbase, const int n_end, const double (&xs)[4],
                                               const LpcArgs& a, const int g, const int gbase, const int src_prev) {
 #pragma unroll 1
-  for (int qb = 8 * PH; qb <= 8 * PH + 7; ++qb) {
+  for (int qb = LS * PH; qb <= LS * PH + LS - 1; ++qb) {
     const int n0 = nbase + 5 * qb;
     if (n0 + 4 >= n_end) break;
-    cep_block<NG, PH, true>(x, y, mc, n0, xs, a, g, gbase, src_prev);
+    cep_block<NG, LS, PH, true>(x, y, mc, n0, xs, a, g, gbase, src_prev);
   }
-  if constexpr (PH + 1 < NG) cep_lap_phase<NG, PH + 1>(x, y, mc, nbase, n_end, xs, a, g, gbase, src_prev);
+  if constexpr (PH + 1 < NG) cep_lap_phase<NG, LS, PH + 1>(x, y, mc, nbase, n_end, xs, a, g, gbase, src_prev);
 }
 
 // cep[nbase + i], i = element index, for the elements below n_end: weighted copy for K5, plain copy on request
-template <int NG>
+template <int NG, int LS>
 __device__ __forceinline__ void cep_flush(const double (&x)[NG][5], const int nbase, const int n_end, const LpcArgs& a,
                                           double* msg, const int task, const int g) {
 #pragma unroll
   for (int G = 0; G < NG; ++G)
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
-      const int n = nbase + 40 * G + 5 * g + c;
+      const int n = nbase + 5 * LS * G + 5 * g + c;
       if (n < n_end) {
         msg[n] = x[G][c] * __ldg(a.weights + n);
         if (a.cep_out) a.cep_out[(size_t)task * a.L + n] = x[G][c];
@@ -559,18 +561,20 @@ __device__ __forceinline__ void cep_flush(const double (&x)[NG][5], const int nb
     }
 }
 
-template <int NG>
+template <int NG, int LS>
 __global__ void __launch_bounds__(128, (NG > 2) ? 3 : 5) lpc_cepstrum_blk_kernel(const LpcArgs a) {
-  constexpr int C = 5, GE = 8 * C;
+  constexpr int C = 5, GE = LS * C;   // elements per group
+  constexpr int kLog = (LS == 16) ? 4 : 3;
+  constexpr int kTasks = 128 / LS;    // solves per CTA
   const int lane = threadIdx.x & 31;
-  const int g = lane & 7;
+  const int g = lane & (LS - 1);
   const bool g0 = g == 0;
-  const int gbase = lane & ~7;
-  const int src_prev = gbase | ((g + 7) & 7);
+  const int gbase = lane & ~(LS - 1);
+  const int src_prev = gbase | ((g + LS - 1) & (LS - 1));
   const int p = a.order, L = a.L;
-  const int n_vblocks = (a.n_tasks + 15) >> 4;
+  const int n_vblocks = (a.n_tasks + kTasks - 1) / kTasks;
   for (int vb = blockIdx.x; vb < n_vblocks; vb += gridDim.x) {
-  int task = (vb * (int)blockDim.x + (int)threadIdx.x) >> 3;
+  int task = (vb * (int)blockDim.x + (int)threadIdx.x) >> kLog;
   const bool live = task < a.n_tasks;
   if (!live) task = a.n_tasks - 1;  // idle groups shadow the last task (keeps the shuffles uniform)
 
@@ -594,18 +598,18 @@ __global__ void __launch_bounds__(128, (NG > 2) ? 3 : 5) lpc_cepstrum_blk_kernel
   double E = r0;
   int bad = 0;
   double acc = __shfl_sync(0xffffffffu, rr[0][0], gbase);  // r[1]
-  if (p >= 1) lev_order<NG, 0, 1>(f, b, rr, acc, E, g0, src_prev);
-  if (p >= 2) lev_order<NG, 0, 2>(f, b, rr, acc, E, g0, src_prev);
-  if (p >= 3) lev_order<NG, 0, 3>(f, b, rr, acc, E, g0, src_prev);
-  if (p >= 4) lev_order<NG, 0, 4>(f, b, rr, acc, E, g0, src_prev);
+  if (p >= 1) lev_order<NG, LS, 0, 1>(f, b, rr, acc, E, g0, src_prev);
+  if (p >= 2) lev_order<NG, LS, 0, 2>(f, b, rr, acc, E, g0, src_prev);
+  if (p >= 3) lev_order<NG, LS, 0, 3>(f, b, rr, acc, E, g0, src_prev);
+  if (p >= 4) lev_order<NG, LS, 0, 4>(f, b, rr, acc, E, g0, src_prev);
   const int qb_full = (p >= 4) ? (p - 4) / C : 0;  // last block whose five orders are all <= p
-  lev_phase<NG, 0>(f, b, rr, acc, E, g0, src_prev, qb_full);
+  lev_phase<NG, LS, 0>(f, b, rr, acc, E, g0, src_prev, qb_full);
   {
     const int m0 = C * (qb_full + 1);
-    if (p >= 4 && m0 <= p) lev_order<NG, NG - 1, 0>(f, b, rr, acc, E, g0, src_prev);
-    if (p >= 4 && m0 + 1 <= p) lev_order<NG, NG - 1, 1>(f, b, rr, acc, E, g0, src_prev);
-    if (p >= 4 && m0 + 2 <= p) lev_order<NG, NG - 1, 2>(f, b, rr, acc, E, g0, src_prev);
-    if (p >= 4 && m0 + 3 <= p) lev_order<NG, NG - 1, 3>(f, b, rr, acc, E, g0, src_prev);
+    if (p >= 4 && m0 <= p) lev_order<NG, LS, NG - 1, 0>(f, b, rr, acc, E, g0, src_prev);
+    if (p >= 4 && m0 + 1 <= p) lev_order<NG, LS, NG - 1, 1>(f, b, rr, acc, E, g0, src_prev);
+    if (p >= 4 && m0 + 2 <= p) lev_order<NG, LS, NG - 1, 2>(f, b, rr, acc, E, g0, src_prev);
+    if (p >= 4 && m0 + 3 <= p) lev_order<NG, LS, NG - 1, 3>(f, b, rr, acc, E, g0, src_prev);
   }
 
   // a zero or non-finite prediction error at any order turns k, and with it E, into NaN for good
@@ -617,7 +621,7 @@ __global__ void __launch_bounds__(128, (NG > 2) ? 3 : 5) lpc_cepstrum_blk_kernel
   for (int G = 0; G < NG; ++G)
 #pragma unroll
     for (int c = 0; c < C; ++c) gpart = fma(f[G][c], rr[G][c], gpart);
-  const double gg = r0 + group_sum8(gpart);
+  const double gg = r0 + group_sum_d<LS>(gpart);
   if (!(gg > 0.0) || !isfinite(gg)) bad |= FDLP_ST_NONFINITE;
   if (live) {
     if (a.lpc_out) {
@@ -647,31 +651,31 @@ __global__ void __launch_bounds__(128, (NG > 2) ? 3 : 5) lpc_cepstrum_blk_kernel
   if (g0) { rr[0][1] = c1; b[0][0] = c1; f[0][0] = c0; f[0][1] = c1; }  // 1 * cep[1];  y^(1)_0 = x[1];  cep[0], cep[1]
   // lap 0: steps n = 2 .. L0 - 1 with the vectors growing from slot 0
   const int L0 = (L < GE * NG) ? L : GE * NG;
-  if (L0 > 2) cep_step<NG, 0, 2>(f, b, rr, 2, 0, a, g, gbase, src_prev);
-  if (L0 > 3) cep_step<NG, 0, 3>(f, b, rr, 3, 0, a, g, gbase, src_prev);
-  if (L0 > 4) cep_step<NG, 0, 4>(f, b, rr, 4, 0, a, g, gbase, src_prev);
+  if (L0 > 2) cep_step<NG, LS, 0, 2>(f, b, rr, 2, 0, a, g, gbase, src_prev);
+  if (L0 > 3) cep_step<NG, LS, 0, 3>(f, b, rr, 3, 0, a, g, gbase, src_prev);
+  if (L0 > 4) cep_step<NG, LS, 0, 4>(f, b, rr, 4, 0, a, g, gbase, src_prev);
   const int nb_full = (L0 >= 5) ? (L0 - 5) / C : 0;  // last block n = 5 qb .. 5 qb + 4 with 5 qb + 4 <= L0 - 1
-  cep_phase<NG, 0>(f, b, rr, nb_full, xs, a, g, gbase, src_prev);
+  cep_phase<NG, LS, 0>(f, b, rr, nb_full, xs, a, g, gbase, src_prev);
   {
-    const int n0 = C * (nb_full + 1), xg = (nb_full + 1) >> 3;
-    if (L0 >= 5 && n0 <= L0 - 1) cep_step<NG, NG - 1, 0>(f, b, rr, n0, xg, a, g, gbase, src_prev);
-    if (L0 >= 5 && n0 + 1 <= L0 - 1) cep_step<NG, NG - 1, 1>(f, b, rr, n0 + 1, xg, a, g, gbase, src_prev);
-    if (L0 >= 5 && n0 + 2 <= L0 - 1) cep_step<NG, NG - 1, 2>(f, b, rr, n0 + 2, xg, a, g, gbase, src_prev);
-    if (L0 >= 5 && n0 + 3 <= L0 - 1) cep_step<NG, NG - 1, 3>(f, b, rr, n0 + 3, xg, a, g, gbase, src_prev);
+    const int n0 = C * (nb_full + 1), xg = (nb_full + 1) >> kLog;
+    if (L0 >= 5 && n0 <= L0 - 1) cep_step<NG, LS, NG - 1, 0>(f, b, rr, n0, xg, a, g, gbase, src_prev);
+    if (L0 >= 5 && n0 + 1 <= L0 - 1) cep_step<NG, LS, NG - 1, 1>(f, b, rr, n0 + 1, xg, a, g, gbase, src_prev);
+    if (L0 >= 5 && n0 + 2 <= L0 - 1) cep_step<NG, LS, NG - 1, 2>(f, b, rr, n0 + 2, xg, a, g, gbase, src_prev);
+    if (L0 >= 5 && n0 + 3 <= L0 - 1) cep_step<NG, LS, NG - 1, 3>(f, b, rr, n0 + 3, xg, a, g, gbase, src_prev);
   }
   // f now holds the cepstrum at elements 0 .. L0-1
-  if (live) cep_flush<NG>(f, 0, L0, a, msg, task, g);
+  if (live) cep_flush<NG, LS>(f, 0, L0, a, msg, task, g);
   // further laps (coeff_num > 40 NG, e.g. the REVERB recipe's 300 coefficients): circular vectors
   for (int nbase = GE * NG; nbase < L; nbase += GE * NG) {
     const int n_end = (L < nbase + GE * NG) ? L : nbase + GE * NG;
-    cep_lap_phase<NG, 0>(f, b, rr, nbase, n_end, xs, a, g, gbase, src_prev);
+    cep_lap_phase<NG, LS, 0>(f, b, rr, nbase, n_end, xs, a, g, gbase, src_prev);
     const int nblk = (n_end - nbase) / C;  // full blocks done above
-    const int n0 = nbase + C * nblk, xg = nblk >> 3;
-    if (n0 < n_end) cep_step<NG, NG - 1, 0, true>(f, b, rr, n0, xg, a, g, gbase, src_prev);
-    if (n0 + 1 < n_end) cep_step<NG, NG - 1, 1, true>(f, b, rr, n0 + 1, xg, a, g, gbase, src_prev);
-    if (n0 + 2 < n_end) cep_step<NG, NG - 1, 2, true>(f, b, rr, n0 + 2, xg, a, g, gbase, src_prev);
-    if (n0 + 3 < n_end) cep_step<NG, NG - 1, 3, true>(f, b, rr, n0 + 3, xg, a, g, gbase, src_prev);
-    if (live) cep_flush<NG>(f, nbase, n_end, a, msg, task, g);
+    const int n0 = nbase + C * nblk, xg = nblk >> kLog;
+    if (n0 < n_end) cep_step<NG, LS, NG - 1, 0, true>(f, b, rr, n0, xg, a, g, gbase, src_prev);
+    if (n0 + 1 < n_end) cep_step<NG, LS, NG - 1, 1, true>(f, b, rr, n0 + 1, xg, a, g, gbase, src_prev);
+    if (n0 + 2 < n_end) cep_step<NG, LS, NG - 1, 2, true>(f, b, rr, n0 + 2, xg, a, g, gbase, src_prev);
+    if (n0 + 3 < n_end) cep_step<NG, LS, NG - 1, 3, true>(f, b, rr, n0 + 3, xg, a, g, gbase, src_prev);
+    if (live) cep_flush<NG, LS>(f, nbase, n_end, a, msg, task, g);
   }
   if (live && g0) for (int n = L; n < a.Lp; ++n) msg[n] = 0.0;
 

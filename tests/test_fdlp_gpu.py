@@ -171,11 +171,13 @@ def test_long_segment_high_order_against_oracle():
     assert_feats_close(ex15([x], jitter=[3])[0].cpu().numpy(), ofdlp.fdlp_spectrogram(x, rng=random.Random(3), **kw15))
 
 
-@pytest.mark.parametrize("order,coeff_num", [(150, 300), (156, 500), (159, 485), (60, 200)])
+@pytest.mark.parametrize("order,coeff_num", [(150, 300), (156, 500), (159, 485), (60, 200),
+                                             (160, 100), (300, 500), (319, 330), (316, 600), (200, 321)])
 def test_circular_cepstrum_orders_up_to_159_any_length(order, coeff_num):
-    """More cepstral coefficients than the register kernel has slots (160): the LPC->cepstrum recursion
-    runs on circular vectors (lpc_env.cuh cep_lap_phase).  Orders 156..159 use every slot of the ring,
-    coeff_num 485/500 makes four laps with a ragged last one."""
+    """More cepstral coefficients than the register kernel has slots (160, or 320 with 16 lanes per solve for
+    orders 160..319): the LPC->cepstrum recursion runs on circular vectors (lpc_env.cuh cep_lap_phase).
+    Orders 156..159 / 316..319 use every slot of the ring, coeff_num 485/500 makes four laps with a ragged
+    last one."""
     kw = dict(nfilters=10, order=order, fduration=1.5, frate=400, overlap_fraction=0.25, coeff_num=coeff_num,
               coeff_range="1,%d" % coeff_num, fbank_type="mel,1")
     ex = extractor(**kw)
