@@ -165,6 +165,9 @@ def run_ours(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    # pinned staging buffers on the GPU's NUMA node (restored before the CPU baseline uses every core)
+    from speech_recognition_tools_b200.sharding import bind_host_to_gpu
+    old_affinity = bind_host_to_gpu(local_rank)
 
     wavs, lengths = build_workload(rank)
     audio_s = float(lengths.sum()) / 16000.0
@@ -330,6 +333,8 @@ def run_ours(args):
                     "hbm_gbs_algorithmic": mel_bytes / (mel_ms * 1e-3) / 1e9}
 
         # ---- CPU baseline: the oracle port on a bounded sample of the same workload ----
+        if old_affinity is not None:
+            os.sched_setaffinity(0, old_affinity)
         cores = os.cpu_count() or 1
         n_sample = min(len(wavs), max(cores * 3, 32))
         cpu_val, cpu_audio, cpu_dt = cpu_oracle_throughput(wavs[:n_sample], cores)

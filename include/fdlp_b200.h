@@ -219,6 +219,37 @@ int fdlp_diff_filter(const void* wav /*dev, packed*/, int32_t wav_dtype, const i
                      int32_t n_utt, int64_t max_len /*longest utterance, samples*/, float* out /*dev, packed*/,
                      void* stream);
 
+/* ---- MFCC features (computeMfccFeatures.py:111-131: signal / 2^15 [+ noise], Hamming frames, the reference's
+ *      (nfft/2 + 1)-point DFT magnitude against createFbank(nfilters, nfft, srate), log10, type-II DCT along the bands,
+ *      first `ncep` coefficients; optional spliceFeats context, features.py:157-169) ---- */
+typedef struct mfcc_plan mfcc_plan;
+typedef struct {
+  int32_t srate;
+  int32_t nfilters;      /* --nfilters (30) */
+  int32_t nfft;          /* --nfft (1024), even */
+  int32_t frate;         /* --frate (100) */
+  double fduration;      /* --fduration (0.02) */
+  int32_t ncep;          /* coefficients kept (13, computeMfccFeatures.py:127) */
+} mfcc_params;
+
+typedef struct {
+  const void* wav;              /* dev, packed int16 / float32 as read from the WAV (not normalised) */
+  int32_t wav_dtype;
+  int32_t n_utt;
+  int64_t n_frames;             /* sum_u frames(T_u), as for mel_batch */
+  const int64_t* utt_wav_off;   /* dev [n_utt+1] */
+  const int64_t* utt_frame_off; /* dev [n_utt+1] */
+  float* feats;                 /* dev [n_frames, ncep * (2 context + 1)] */
+  int32_t context;              /* --context (0: no splicing) */
+  const int16_t* noise;         /* dev noise recording or NULL (--add_noise type,snr: computeMfccFeatures.py:45-52) */
+  const int64_t* utt_noise_off; /* dev [n_utt] floor(rand * (len(noise) - T_u)) */
+  const double* utt_snr_db;     /* dev [n_utt] */
+} mfcc_batch;
+
+int mfcc_plan_create(const mfcc_params* params, mfcc_plan** out_plan);
+int mfcc_plan_destroy(mfcc_plan* plan);
+int mfcc_forward(mfcc_plan* plan, const mfcc_batch* batch, void* stream);
+
 /* ---- CMVN apply (ESPnet dump.sh / Kaldi apply-cmvn, e2e/wsj/run_fdlp_e1.sh:293-303) ---- */
 int cmvn_apply(float* feats /*dev [n_frames, dim], in place*/, int64_t n_frames, int32_t dim,
                const double* stats /*dev [2, dim+1]*/, int32_t norm_vars, void* stream);

@@ -62,6 +62,21 @@ class MelBatch(C.Structure):
     ]
 
 
+class MfccParams(C.Structure):
+    _fields_ = [
+        ("srate", C.c_int32), ("nfilters", C.c_int32), ("nfft", C.c_int32), ("frate", C.c_int32),
+        ("fduration", C.c_double), ("ncep", C.c_int32),
+    ]
+
+
+class MfccBatch(C.Structure):
+    _fields_ = [
+        ("wav", C.c_void_p), ("wav_dtype", C.c_int32), ("n_utt", C.c_int32), ("n_frames", C.c_int64),
+        ("utt_wav_off", C.c_void_p), ("utt_frame_off", C.c_void_p), ("feats", C.c_void_p), ("context", C.c_int32),
+        ("noise", C.c_void_p), ("utt_noise_off", C.c_void_p), ("utt_snr_db", C.c_void_p),
+    ]
+
+
 # every symbol include/fdlp_b200.h declares: (name, restype, argtypes)
 SYMBOLS = [
     ("fdlp_last_error", C.c_char_p, []),
@@ -86,6 +101,9 @@ SYMBOLS = [
     ("mel_plan_destroy", C.c_int, [C.c_void_p]),
     ("mel_plan_get_fbank", C.c_int, [C.c_void_p, C.c_void_p]),
     ("mel_forward", C.c_int, [C.c_void_p, C.POINTER(MelBatch), C.c_void_p]),
+    ("mfcc_plan_create", C.c_int, [C.POINTER(MfccParams), C.POINTER(C.c_void_p)]),
+    ("mfcc_plan_destroy", C.c_int, [C.c_void_p]),
+    ("mfcc_forward", C.c_int, [C.c_void_p, C.POINTER(MfccBatch), C.c_void_p]),
     ("cmvn_apply", C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]),
     ("fdlp_modspec_forward", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     ("fdlp_diff_filter", C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),

@@ -13,6 +13,7 @@
 #include "dct.cuh"
 #include "lpc_env.cuh"
 #include "mel.cuh"
+#include "mfcc.cuh"
 #include "noise.cuh"
 #include "ola.cuh"
 
@@ -1234,6 +1235,144 @@ extern "C" int mel_forward(mel_plan* p, const mel_batch* b, void* stream) {
   else if (b->wav_dtype == FDLP_WAV_FLOAT32) mel_frames_kernel<float><<<grid, block, p->smem, st>>>(a);
   else return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
   FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
+// ================================================================ MFCC
+struct mfcc_plan {
+  mfcc_params prm;
+  int flen = 0, shift = 0, P = 0, nb = 0, nbp = 0, used = 0;
+  float* d_ham = nullptr;
+  float2* d_tw = nullptr;
+  float* d_weff = nullptr;
+  double* d_dctb = nullptr;
+  int32_t* d_frame_utt = nullptr;
+  float* d_tmp = nullptr;      // unspliced features when a context is requested
+  int64_t cap_frames = 0, cap_tmp = 0;
+  double* d_alpha = nullptr;
+  int cap_utt = 0;
+  size_t smem = 0;
+};
+
+static void mfcc_free(mfcc_plan* p) {
+  if (!p) return;
+  cudaFree(p->d_ham); cudaFree(p->d_tw); cudaFree(p->d_weff); cudaFree(p->d_dctb); cudaFree(p->d_frame_utt);
+  cudaFree(p->d_tmp); cudaFree(p->d_alpha);
+  delete p;
+}
+
+extern "C" int mfcc_plan_create(const mfcc_params* prm, mfcc_plan** out) {
+  if (!prm || !out) return set_err(FDLP_E_ARG, "null argument%s", "");
+  *out = nullptr;
+  if (prm->nfilters < 1 || prm->nfft < 8 || (prm->nfft & 1) || prm->frate < 1 || !(prm->fduration > 0) ||
+      prm->ncep < 1 || prm->ncep > prm->nfilters)
+    return set_err(FDLP_E_ARG, "invalid mfcc_params%s", "");
+  mfcc_plan* p = new (std::nothrow) mfcc_plan();
+  if (!p) return set_err(FDLP_E_NOMEM, "out of host memory%s", "");
+  p->prm = *prm;
+  p->flen = (int)(prm->srate * prm->fduration);       // features.py:134
+  p->shift = (int)(prm->srate / (double)prm->frate);  // features.py:135
+  if (p->flen < 1 || p->shift < 1) { mfcc_free(p); return set_err(FDLP_E_ARG, "empty frames%s", ""); }
+  const int J = prm->nfilters;
+  p->P = prm->nfft / 2 + 1;                 // computeMfccFeatures.py:125  fft(time_frames, int(nfft / 2 + 1))
+  p->nb = p->P / 2 + 1;                     // |X[P-k]| = |X[k]|
+  p->nbp = p->nb | 1;
+  p->used = std::min(p->flen, p->P);
+  const std::vector<double> fb = make_mel_fbank(J, prm->nfft, prm->srate, 1.0);  // [J, P]  (:72)
+  std::vector<float> weff((size_t)J * p->nbp, 0.f);
+  for (int j = 0; j < J; ++j)
+    for (int k = 0; k < p->nb; ++k) {
+      double w = fb[(size_t)j * p->P + k];
+      if (k >= 1 && p->P - k != k) w += fb[(size_t)j * p->P + (p->P - k)];
+      weff[(size_t)j * p->nbp + k] = (float)w;
+    }
+  const std::vector<double> hw = np_hamming(p->flen);
+  std::vector<float> ham(p->used);
+  for (int i = 0; i < p->used; ++i) ham[i] = (float)(hw[i] / 32768.0);   // signal / np.power(2, 15)  (:113)
+  std::vector<float2> tw(p->P);
+  for (int m = 0; m < p->P; ++m) {
+    const double ang = -2.0 * M_PI * (double)m / (double)p->P;
+    tw[m] = make_float2((float)cos(ang), (float)sin(ang));
+  }
+  std::vector<double> dctb((size_t)prm->ncep * J);   // scipy.fftpack.dct type II: y[c] = 2 sum_j x[j] cos(pi c (2j+1) / (2J))
+  for (int c = 0; c < prm->ncep; ++c)
+    for (int j = 0; j < J; ++j) dctb[(size_t)c * J + j] = 2.0 * cos(M_PI * c * (2.0 * j + 1.0) / (2.0 * J));
+  int rc;
+  if ((rc = upload(&p->d_ham, ham)) || (rc = upload(&p->d_tw, tw)) || (rc = upload(&p->d_weff, weff)) ||
+      (rc = upload(&p->d_dctb, dctb))) {
+    mfcc_free(p);
+    return rc;
+  }
+  p->smem = mfcc_smem_bytes(p->used, p->P, p->nbp, J);
+  int dev = 0, max_smem = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  if (max_smem <= 0) max_smem = 227 * 1024;
+  if (p->smem + 2048 > (size_t)max_smem) { mfcc_free(p); return set_err(FDLP_E_UNSUPPORTED, "nfft too large for the MFCC kernel%s", ""); }
+  cudaError_t e = raise_smem_limit(mfcc_frames_kernel<int16_t>, p->smem);
+  if (e == cudaSuccess) e = raise_smem_limit(mfcc_frames_kernel<float>, p->smem);
+  if (e != cudaSuccess) { mfcc_free(p); return set_err(FDLP_E_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
+  *out = p;
+  return FDLP_OK;
+}
+
+extern "C" int mfcc_plan_destroy(mfcc_plan* p) { mfcc_free(p); return FDLP_OK; }
+
+extern "C" int mfcc_forward(mfcc_plan* p, const mfcc_batch* b, void* stream) {
+  if (!p || !b) return set_err(FDLP_E_ARG, "null argument%s", "");
+  if (b->n_utt <= 0 || b->n_frames <= 0) return FDLP_OK;
+  if (!b->wav || !b->utt_wav_off || !b->utt_frame_off || !b->feats) return set_err(FDLP_E_ARG, "null batch pointer%s", "");
+  if (b->wav_dtype != FDLP_WAV_INT16 && b->wav_dtype != FDLP_WAV_FLOAT32) return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
+  if (b->context < 0) return set_err(FDLP_E_ARG, "negative context%s", "");
+  if (b->noise && (!b->utt_noise_off || !b->utt_snr_db)) return set_err(FDLP_E_ARG, "noise mixing needs offsets and SNRs%s", "");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (b->n_frames > p->cap_frames) {
+    cudaFree(p->d_frame_utt); p->d_frame_utt = nullptr; p->cap_frames = 0;
+    FDLP_CUDA(cudaMalloc((void**)&p->d_frame_utt, (size_t)b->n_frames * sizeof(int32_t)));
+    p->cap_frames = b->n_frames;
+  }
+  if (b->context > 0 && b->n_frames > p->cap_tmp) {
+    cudaFree(p->d_tmp); p->d_tmp = nullptr; p->cap_tmp = 0;
+    FDLP_CUDA(cudaMalloc((void**)&p->d_tmp, (size_t)b->n_frames * p->prm.ncep * sizeof(float)));
+    p->cap_tmp = b->n_frames;
+  }
+  if (b->noise && b->n_utt > p->cap_utt) {
+    cudaFree(p->d_alpha); p->d_alpha = nullptr; p->cap_utt = 0;
+    FDLP_CUDA(cudaMalloc((void**)&p->d_alpha, (size_t)b->n_utt * sizeof(double)));
+    p->cap_utt = b->n_utt;
+  }
+  mel_frame_map_kernel<<<b->n_utt, 128, 0, st>>>(b->utt_frame_off, b->n_utt, p->d_frame_utt);
+  FDLP_CUDA(cudaGetLastError());
+  if (b->noise) {  // both signals are divided by 2^15 in the reference, which leaves alpha unchanged: true energies
+    NoiseArgs n;
+    n.wav = b->wav; n.wav_dtype = b->wav_dtype; n.utt_wav_off = b->utt_wav_off; n.noise = b->noise;
+    n.utt_noise_off = b->utt_noise_off; n.utt_snr_db = b->utt_snr_db; n.utt_alpha = p->d_alpha; n.mode = FDLP_NOISE_FLOAT;
+    noise_alpha_kernel<<<b->n_utt, kNoiseThreads, 0, st>>>(n);
+    FDLP_CUDA(cudaGetLastError());
+  }
+  MfccArgs a;
+  memset(&a, 0, sizeof(a));
+  a.wav = b->wav; a.wav_dtype = b->wav_dtype; a.utt_wav_off = b->utt_wav_off; a.utt_frame_off = b->utt_frame_off;
+  a.frame_utt = p->d_frame_utt; a.n_frames = b->n_frames;
+  a.flen = p->flen; a.shift = p->shift; a.P = p->P; a.nb = p->nb; a.nbp = p->nbp; a.used = p->used;
+  a.ham = p->d_ham; a.tw = p->d_tw; a.weff = p->d_weff; a.dctb = p->d_dctb;
+  a.feats = (b->context > 0) ? p->d_tmp : b->feats;
+  a.J = p->prm.nfilters; a.ncep = p->prm.ncep;
+  a.noise = b->noise; a.utt_noise_off = b->utt_noise_off; a.utt_alpha = p->d_alpha;
+  const long long tiles = (b->n_frames + kMfccFT - 1) / kMfccFT;
+  if (tiles > 2147483647LL) return set_err(FDLP_E_ARG, "too many frames in one batch%s", "");
+  const int threads = std::min(288, (p->nb + 31) / 32 * 32);
+  if (b->wav_dtype == FDLP_WAV_INT16) mfcc_frames_kernel<int16_t><<<(unsigned)tiles, threads, p->smem, st>>>(a);
+  else mfcc_frames_kernel<float><<<(unsigned)tiles, threads, p->smem, st>>>(a);
+  FDLP_CUDA(cudaGetLastError());
+  if (b->context > 0) {
+    SpliceArgs s;
+    s.in = p->d_tmp; s.out = b->feats; s.utt_frame_off = b->utt_frame_off; s.frame_utt = p->d_frame_utt;
+    s.n_frames = b->n_frames; s.D = p->prm.ncep; s.context = b->context;
+    const long long total = (long long)b->n_frames * s.D * (2 * s.context + 1);
+    splice_kernel<<<(unsigned)std::min<long long>((total + 255) / 256, 148LL * 16), 256, 0, st>>>(s);
+    FDLP_CUDA(cudaGetLastError());
+  }
   return FDLP_OK;
 }
 

@@ -8,7 +8,8 @@ batches bounded by a segment budget (scratch memory is proportional to segments)
 from __future__ import annotations
 
 import heapq
-from typing import List, Sequence
+import os
+from typing import List, Optional, Sequence, Set
 
 
 def assign_to_ranks(n_segments: Sequence[int], world_size: int) -> List[List[int]]:
@@ -40,3 +41,27 @@ def make_batches(utts: Sequence[int], n_segments: Sequence[int], max_segments: i
     if cur:
         batches.append(cur)
     return batches
+
+
+def bind_host_to_gpu(device_index: int) -> Optional[Set[int]]:
+    """Restrict the calling process to the CPUs NVML reports as local to CUDA device `device_index`, so that the
+    pinned staging buffers allocated afterwards (first touch) sit on the GPU's NUMA node.  With one process per GPU
+    the host<->device copies of eight ranks otherwise share one socket's memory controllers.  Returns the previous
+    affinity (to restore with os.sched_setaffinity) or None when nothing was changed (no NVML, one node, ...)."""
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+        handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(handle, words)
+        cpus = {64 * i + b for i, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1}
+        old = os.sched_getaffinity(0)
+        cpus &= old
+        if not cpus or cpus == old:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return old
+    except Exception:  # placement is an optimisation only
+        return None

@@ -113,3 +113,24 @@ def test_modspec_oracle_matches_reference(name):
     ref = c["feats"]
     assert got.shape == ref.shape
     np.testing.assert_allclose(got, ref, rtol=1e-6, atol=1e-9)
+
+
+@pytest.mark.parametrize("name", golden_cases("mfcc"))
+def test_mfcc_oracle_matches_reference(name):
+    """oracle/mfcc.py == the unmodified computeMfccFeatures.py on the committed fixtures."""
+    import json
+    import os
+    from oracle import mfcc as omfcc
+    from speech_recognition_tools_b200 import synth
+    from tests.golden_util import GOLDEN_DIR
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    meta = json.loads(str(z["meta"]))
+    sp = meta["input"]
+    x = synth.make_utterance(sp["kind"], sp["seed"], sp["utt"], sp["T"], sp.get("sigma_f", 30.0))
+    kw = dict(meta["params"])
+    if meta["noise"]:
+        nz = meta["noise"]
+        kw.update(noise=synth.noise_int16(nz["type"], nz["T"], seed=nz["seed"]), snr=nz["snr"], rand=nz["rand"])
+    out = omfcc.mfcc_features(x, **kw)
+    assert out.shape == z["feats"].shape
+    np.testing.assert_allclose(out, z["feats"], rtol=0, atol=1e-10)
