@@ -56,6 +56,9 @@ struct DctArgs {
   int out_pad;             // coefficients 0..out_pad-1 are repeated at N..N+out_pad-1 (circular extension)
   int vec_ok;              // wav base pointer is 16-byte aligned
   int seg0;                // first segment of this launch (chunked launches); out is indexed by blockIdx.x
+  // dct_half_kernel: split table of the first radix-2 stage, w_n^j = T1A[j >> 6] * T1B[j & 63], layout T1A[tw1_na] T1B[64]
+  const double2* tw1;
+  int tw1_na;
 };
 
 template <typename T>
@@ -318,6 +321,105 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
       out[N - kq] = -(B.y * V.x + B.x * V.y);
     }
    }
+  }
+}
+
+// Segments whose N float64 values do not fit in shared memory (N > ~28 k): two CTAs per segment, each holding one
+// half of the first decimation-in-frequency stage of the N/2-point transform,
+//     e[j] = z[j] + z[j + n/2]  -> Z[2k],      o[j] = (z[j] - z[j + n/2]) w_n^j  -> Z[2k+1],     j < n/2,
+// formed while the samples are loaded (first the samples that land in z[j], then, after a barrier, those of
+// z[j + n/2]: every slot is touched by one thread per phase).  The unpack step pairs Z[k] with Z[n - k], which have
+// the same parity (n is even), so each CTA finishes the DCT coefficients k = h (mod 2) on its own: no exchange
+// between the halves.  The passes, tables and permutation are those of an n/2-point plan.
+template <typename S>
+__global__ void __launch_bounds__(512) dct_half_kernel(const DctArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int N = a.N, n = a.n, n2 = a.n / 2;
+  double* sv = reinterpret_cast<double*>(smem_raw);
+  cplx<double>* z = reinterpret_cast<cplx<double>*>(smem_raw);
+  double2* stw = reinterpret_cast<double2*>(smem_raw + (size_t)n2 * sizeof(cplx<double>));
+  for (int i = threadIdx.x; i < a.tws_n; i += blockDim.x) stw[i] = a.tws[i];
+  double2* sunp = stw + a.tws_n;
+  for (int i = threadIdx.x; i < 2 * (a.unp_na + 64); i += blockDim.x) sunp[i] = a.unp[i];
+  double2* sham = sunp + 2 * (a.unp_na + 64);
+  for (int i = threadIdx.x; i < a.ham_na + 64; i += blockDim.x) sham[i] = a.hamt[i];
+  double2* st1 = sham + a.ham_na + 64;
+  for (int i = threadIdx.x; i < a.tw1_na + 64; i += blockDim.x) st1[i] = a.tw1[i];
+
+  const int seg_local = blockIdx.x >> 1, h = blockIdx.x & 1;
+  const int seg = a.seg0 + seg_local;
+  const int u = a.seg_utt[seg];
+  const int k = seg - a.utt_seg_off[u];
+  const int64_t woff = a.utt_wav_off[u];
+  const int64_t T_utt = a.utt_wav_off[u + 1] - woff;
+  const S* sig = reinterpret_cast<const S*>(a.wav) + woff;
+  const int ext = (N % 2 == 0) ? N / 2 - 1 : (N - 1) / 2;
+  const int64_t q_base = (int64_t)k * a.S - ext;
+  const int16_t* nz = a.noise ? a.noise + a.utt_noise_off[u] : nullptr;
+  const double alpha = a.noise ? a.utt_alpha[u] : 0.0;
+  __syncthreads();
+
+  for (int phase = 0; phase < 2; ++phase) {
+    for (int i = threadIdx.x; i < N; i += blockDim.x) {
+      const int idx = (i & 1) ? (N - 1 - (i >> 1)) : (i >> 1);  // Makhoul order: v[idx] = x[i]
+      const int m = idx >> 1;                                   // z[m] = v[2m] + j v[2m+1]
+      const int role = (m >= n2) ? 1 : 0;
+      if (role != phase) continue;
+      const int64_t q = q_base + i;
+      double v;
+      if (q >= 0 && q < T_utt) {
+        v = (double)sig[q];
+        if (nz) v += alpha * (double)nz[q];
+      } else {
+        v = fetch_sample<S>(a, sig, q, T_utt, u, alpha, nz);
+      }
+      const double2 hc = sham[i >> 6], hd = sham[a.ham_na + (i & 63)];
+      v *= a.win_a0 - a.win_a1 * (hc.x * hd.x - hc.y * hd.y);
+      const int slot = 2 * (m - role * n2) + (idx & 1);
+      if (phase == 0) sv[slot] = v;
+      else sv[slot] = h ? sv[slot] - v : sv[slot] + v;
+    }
+    __syncthreads();
+  }
+  if (h) {
+    for (int j = threadIdx.x; j < n2; j += blockDim.x) {
+      const double2 wa = st1[j >> 6], wb = st1[a.tw1_na + (j & 63)];
+      z[j] = cmul(z[j], cplx<double>{wa.x * wb.x - wa.y * wb.y, wa.x * wb.y + wa.y * wb.x});
+    }
+    __syncthreads();
+  }
+
+  int L = n2;
+  for (int p = 0; p < a.npass; ++p) {
+    const int R = a.radix[p];
+    const double2* twA = stw + a.tw_off[p];
+    const double2* twB = twA + a.tw_na[p];
+    if (R == 4) fft_pass_s<double, 4>(z, n2, L, twA, twB, a.magic[p]);
+    else if (R == 2) fft_pass_s<double, 2>(z, n2, L, twA, twB, a.magic[p]);
+    else if (R == 3) fft_pass_s<double, 3>(z, n2, L, twA, twB, a.magic[p]);
+    else fft_pass_s<double, 5>(z, n2, L, twA, twB, a.magic[p]);
+    L /= R;
+  }
+
+  // ---- unpack: the coefficients kq = h (mod 2), same arithmetic as dct_segments_kernel ----
+  double* out = a.out + (size_t)seg_local * a.out_ld;
+  for (int kq = 2 * (int)threadIdx.x + h; kq <= n; kq += 2 * (int)blockDim.x) {
+    const int k1 = (kq == n) ? 0 : kq, k2 = (kq == 0) ? 0 : n - kq;
+    const cplx<double> Zk = z[__ldg(a.perm + ((k1 - h) >> 1))];
+    cplx<double> Zc = z[__ldg(a.perm + ((k2 - h) >> 1))];
+    Zc.y = -Zc.y;
+    const cplx<double> E = {0.5 * (Zk.x + Zc.x), 0.5 * (Zk.y + Zc.y)};
+    const cplx<double> D = {0.5 * (Zk.x - Zc.x), 0.5 * (Zk.y - Zc.y)};
+    const double2 ah = sunp[kq >> 6], al = sunp[a.unp_na + (kq & 63)];
+    const double2 A = make_double2(ah.x * al.x - ah.y * al.y, ah.x * al.y + ah.y * al.x);
+    const cplx<double> AD = cmul(cplx<double>{A.x, A.y}, D);
+    const cplx<double> V = {E.x + AD.y, E.y - AD.x};
+    const double2 bh = sunp[a.unp_na + 64 + (kq >> 6)], bl = sunp[2 * a.unp_na + 64 + (kq & 63)];
+    const double2 B = make_double2(bh.x * bl.x - bh.y * bl.y, bh.x * bl.y + bh.y * bl.x);
+    const double yk = B.x * V.x - B.y * V.y;
+    out[kq] = yk;
+    if (kq < a.out_pad) out[N + kq] = yk;
+    if (kq > 0 && kq < n) out[N - kq] = -(B.y * V.x + B.x * V.y);
   }
 }
 

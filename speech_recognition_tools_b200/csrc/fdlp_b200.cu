@@ -201,6 +201,10 @@ struct fdlp_plan {
   int na = 0, a_groups = 1;  // autocorrelation lag blocking
   int pad = 0, ld = 0;       // circular extension (doubles) and row stride of the DCT / filterbank buffers
   bool dct_fp64 = true;
+  bool dct_half = false;     // float64 DCT with two CTAs per segment (dct_half_kernel): N float64 exceed shared memory
+  FftTables fft_half;        // plan of the N/4-point sub-transforms
+  double2* d_tw1 = nullptr;  // split table of the first radix-2 stage
+  int tw1_na = 0;
   size_t dct_smem = 0, ac_smem = 0, lpc_smem = 0, ola_smem = 0;
   std::vector<double> h_fbank;  // [J, N]
   FftTables fft;
@@ -248,6 +252,8 @@ struct fdlp_plan {
 static void plan_free(fdlp_plan* p) {
   if (!p) return;
   free_fft_tables(&p->fft);
+  free_fft_tables(&p->fft_half);
+  cudaFree(p->d_tw1);
   cudaFree(p->d_ham); cudaFree(p->d_postB); cudaFree(p->d_unp); cudaFree(p->d_hamt); cudaFree(p->d_cep); cudaFree(p->d_fbank); cudaFree(p->d_row_lo); cudaFree(p->d_row_hi);
   cudaFree(p->d_weights); cudaFree(p->d_inv_n); cudaFree(p->d_basis); cudaFree(p->d_wratio);
   cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_alpha); cudaFree(p->d_ms);
@@ -611,6 +617,26 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   const size_t tws_bytes = ((size_t)p->fft.tws_n + 2 * (size_t)(p->unp_na + 64) + (size_t)(p->ham_na + 64)) * sizeof(double2);
   p->dct_fp64 = !prm->dct_fp32 && (size_t)N * 8 + tws_bytes <= (size_t)max_smem;
   p->dct_smem = (size_t)N * (p->dct_fp64 ? 8 : 4) + tws_bytes;
+  if (!p->dct_fp64 && !prm->dct_fp32 && N % 4 == 0) {
+    // float64 does not fit one CTA: split the first radix-2 stage over two CTAs (dct.cuh dct_half_kernel)
+    int radix[kMaxRadixPasses], npass = 0;
+    if (factor_radices(N / 4, radix, &npass) == 0) {
+      if ((rc = build_fft_tables(N / 4, &p->fft_half))) { plan_free(p); return rc; }
+      const int n2 = N / 4;
+      p->tw1_na = (n2 + 63) / 64;
+      std::vector<double2> t1;
+      for (int a = 0; a < p->tw1_na; ++a) { const long double ang = -2.0L * M_PIl * (64.0L * a) / (N / 2); t1.push_back(make_double2((double)cosl(ang), (double)sinl(ang))); }
+      for (int b = 0; b < 64; ++b) { const long double ang = -2.0L * M_PIl * b / (N / 2); t1.push_back(make_double2((double)cosl(ang), (double)sinl(ang))); }
+      if ((rc = upload(&p->d_tw1, t1))) { plan_free(p); return rc; }
+      const size_t half_bytes = (size_t)n2 * 16 + ((size_t)p->fft_half.tws_n + 2 * (size_t)(p->unp_na + 64) +
+                                                  (size_t)(p->ham_na + 64) + (size_t)(p->tw1_na + 64)) * sizeof(double2);
+      if (half_bytes <= (size_t)max_smem) {
+        p->dct_half = true;
+        p->dct_fp64 = true;
+        p->dct_smem = half_bytes;
+      }
+    }
+  }
   g.dct_is_fp64 = p->dct_fp64 ? 1 : 0;
   if (p->dct_smem > (size_t)max_smem) {
     plan_free(p);
@@ -631,7 +657,10 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
     cudaError_t e = raise_smem_limit(kern, (size_t)(bytes));                                               \
     if (e != cudaSuccess) { plan_free(p); return set_err(FDLP_E_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e)); } \
   } while (0)
-  if (p->dct_fp64) {
+  if (p->dct_half) {
+    SET_SMEM((dct_half_kernel<int16_t>), p->dct_smem);
+    SET_SMEM((dct_half_kernel<float>), p->dct_smem);
+  } else if (p->dct_fp64) {
     SET_SMEM((dct_segments_kernel<double, int16_t>), p->dct_smem);
     SET_SMEM((dct_segments_kernel<double, float>), p->dct_smem);
   } else {
@@ -732,6 +761,17 @@ static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld
   for (int i = 0; i < p->fft.npass; ++i) { a.tw_off[i] = p->fft.tw_off[i]; a.tw_na[i] = p->fft.tw_na[i]; a.magic[i] = p->fft.magic[i]; }
   a.vec_ok = (((uintptr_t)b->wav) % 16 == 0) ? 1 : 0;
   const dim3 grid(nseg), block(512);
+  if (p->dct_half) {
+    const FftTables& f = p->fft_half;
+    a.npass = f.npass;
+    for (int i = 0; i < f.npass; ++i) { a.radix[i] = f.radix[i]; a.tw_off[i] = f.tw_off[i]; a.tw_na[i] = f.tw_na[i]; a.magic[i] = f.magic[i]; }
+    a.perm = f.d_perm; a.tws = f.d_tws; a.tws_n = f.tws_n; a.tw1 = p->d_tw1; a.tw1_na = p->tw1_na;
+    const dim3 grid2(2 * (unsigned)nseg);
+    if (b->wav_dtype == FDLP_WAV_INT16) dct_half_kernel<int16_t><<<grid2, block, p->dct_smem, st>>>(a);
+    else dct_half_kernel<float><<<grid2, block, p->dct_smem, st>>>(a);
+    FDLP_CUDA(cudaGetLastError());
+    return 0;
+  }
   if (b->wav_dtype == FDLP_WAV_INT16) {
     if (p->dct_fp64) dct_segments_kernel<double, int16_t><<<grid, block, p->dct_smem, st>>>(a);
     else dct_segments_kernel<float, int16_t><<<grid, block, p->dct_smem, st>>>(a);

@@ -161,10 +161,19 @@ def test_long_segment_high_order_against_oracle():
     x = synth.make_utterance("speechlike", 41, 0, 90000, 300.0)
     got = ex([x], jitter=[3])[0].cpu().numpy()
     ref = ofdlp.fdlp_spectrogram(x, rng=random.Random(3), **kw)
-    # N = 32000 float64 does not fit in shared memory: the DCT runs in float32 for this segment length
-    # (DESIGN.md); measured 3e-5 on this input, held to 2e-4 (product target 1e-3)
-    assert ex.geom["dct_is_fp64"] == 0
-    assert_feats_close(got, ref, atol=2e-4, rtol=1e-5)
+    # N = 32000 float64 values do not fit one CTA's shared memory: two CTAs per segment, each one half of the first
+    # radix-2 stage (dct.cuh dct_half_kernel), still float64
+    assert ex.geom["dct_is_fp64"] == 1
+    assert_feats_close(got, ref)
+    dct, _ = ex.stage_dct([x])
+    import scipy.fftpack
+    frames = ofdlp.get_frames(x, 16000, 1 / (0.75 * 2.0), 2.0, np.hamming)
+    dref = scipy.fftpack.dct(frames) / np.sqrt(2 * 32000)
+    assert np.max(np.abs(dct.cpu().numpy() - dref)) < 1e-9 * np.max(np.abs(dref))
+    # the float32 transform stays available (dct_fp32 = True): 3e-5 on this input, held to 2e-4
+    ex32 = extractor(dct_fp32=True, **kw)
+    assert ex32.geom["dct_is_fp64"] == 0
+    assert_feats_close(ex32([x], jitter=[3])[0].cpu().numpy(), ref, atol=2e-4, rtol=1e-5)
     kw15 = dict(kw, fduration=1.5)
     ex15 = extractor(**kw15)
     assert ex15.geom["dct_is_fp64"] == 1
