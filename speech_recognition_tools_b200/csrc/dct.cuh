@@ -39,6 +39,7 @@ struct DctArgs {
   int tw_off[kMaxRadixPasses];
   int tw_na[kMaxRadixPasses];        // entries of A_p
   unsigned magic[kMaxRadixPasses];   // ceil(2^32 / (L_p / R_p)): b / sub == __umulhi(b, magic) for b < 2^20
+  int fuse[kMaxRadixPasses];         // pass p and p + 1 run as one in-register pass of radix R_p * R_{p+1} (fft_pass2_s)
   // split tables of the unpack / post-twiddle step, staged behind tws: unpackA[k] = UA_hi[k >> 6] * UA_lo[k & 63],
   // postB[k] = UB_hi[k >> 6] * UB_lo[k & 63] (scale in UB_lo); layout UA_hi[unp_na] UA_lo[64] UB_hi[unp_na] UB_lo[64]
   const double2* unp;
@@ -162,6 +163,135 @@ __device__ __forceinline__ void fft_pass_s(cplx<T>* z, int n, int L, const doubl
   __syncthreads();
 }
 
+// cos / sin of 2 pi m / R as compile-time constants (octant reduction on the integer fraction, then 12 Taylor terms
+// on [0, pi/4]: below 1e-17)
+constexpr double kTwoPi = 6.283185307179586476925286766559;
+constexpr double cx_sin_small(double x) {
+  double term = x, sum = x;
+  const double x2 = x * x;
+  for (int i = 1; i < 12; ++i) { term *= -x2 / (double)((2 * i) * (2 * i + 1)); sum += term; }
+  return sum;
+}
+constexpr double cx_cos_small(double x) {
+  double term = 1.0, sum = 1.0;
+  const double x2 = x * x;
+  for (int i = 1; i < 12; ++i) { term *= -x2 / (double)((2 * i - 1) * (2 * i)); sum += term; }
+  return sum;
+}
+// which: 0 -> cos(2 pi m / R), 1 -> sin(2 pi m / R)
+constexpr double cx_trig(int m, int R, int which) {
+  m %= R;
+  if (m < 0) m += R;
+  int q = 4 * m;  // angle = 2 pi q / (4 R); quarter turn = R, half turn = 2 R
+  double sc = 1.0, ss = 1.0;
+  if (q > 2 * R) { q = 4 * R - q; ss = -1.0; }
+  if (q > R) { q = 2 * R - q; sc = -1.0; }
+  bool swap = false;
+  if (2 * q > R) { q = R - q; swap = true; }
+  const double x = kTwoPi * (double)q / (double)(4 * R);
+  const double c = swap ? cx_sin_small(x) : cx_cos_small(x);
+  const double sn = swap ? cx_cos_small(x) : cx_sin_small(x);
+  return which == 0 ? sc * c : ss * sn;
+}
+
+// Two consecutive decimation-in-frequency passes (radix R1 over length L, then radix R2 over length L / R1) done by one
+// thread on R1 * R2 elements in registers: the data layout, the twiddle tables and the output permutation are
+// those of the two separate passes, but shared memory is read and written once instead of twice.
+// Element (t, t2) sits at j + t * sub1 + t2 * sub2; the first-stage butterfly of column t2 is the one at
+// j + t2 * sub2, whose twiddle w_L^((j + t2 sub2) u) = w_L^(j u) * w_(R1 R2)^(t2 u) -- the second factor a constant.
+template <typename T, int R1, int R2>
+__device__ __forceinline__ void fft_pass2_s(cplx<T>* z, int n, int L, const double2* twA1, const double2* twB1,
+                                            const double2* twA2, const double2* twB2, unsigned magic2) {
+  constexpr int R = R1 * R2;
+  const int sub1 = L / R1, sub2 = sub1 / R2;
+  const int nb = n / R;
+  for (int b = threadIdx.x; b < nb; b += blockDim.x) {
+    int blk = b, j = 0;
+    if (sub2 > 1) { blk = (int)__umulhi((unsigned)b, magic2); j = b - blk * sub2; }
+    cplx<T>* p = z + blk * L + j;
+    cplx<T> a[R2][R1];
+#pragma unroll
+    for (int t2 = 0; t2 < R2; ++t2)
+#pragma unroll
+      for (int t = 0; t < R1; ++t) a[t2][t] = p[t * sub1 + t2 * sub2];
+    cplx<double> pw[R1];
+    {
+      const double2 wa = twA1[j >> 6], wb = twB1[j & 63];
+      pw[1] = {wa.x * wb.x - wa.y * wb.y, wa.x * wb.y + wa.y * wb.x};
+#pragma unroll
+      for (int u = 2; u < R1; ++u) pw[u] = cmul(pw[u - 1], pw[1]);
+    }
+#pragma unroll
+    for (int t2 = 0; t2 < R2; ++t2) {
+      dft_small<T, R1>(a[t2]);
+#pragma unroll
+      for (int u = 1; u < R1; ++u) {
+        cplx<double> w = pw[u];
+        if (t2 > 0) {
+          constexpr int kR = R;
+          const cplx<double> c = {cx_trig(t2 * u, kR, 0), -cx_trig(t2 * u, kR, 1)};
+          w = cmul(w, c);
+        }
+        a[t2][u] = cmul(a[t2][u], cplx<T>{(T)w.x, (T)w.y});
+      }
+    }
+    cplx<double> pw2[R2];
+    if (sub2 > 1) {
+      const double2 wa = twA2[j >> 6], wb = twB2[j & 63];
+      pw2[1] = {wa.x * wb.x - wa.y * wb.y, wa.x * wb.y + wa.y * wb.x};
+#pragma unroll
+      for (int u2 = 2; u2 < R2; ++u2) pw2[u2] = cmul(pw2[u2 - 1], pw2[1]);
+    }
+#pragma unroll
+    for (int u = 0; u < R1; ++u) {
+      cplx<T> c[R2];
+#pragma unroll
+      for (int t2 = 0; t2 < R2; ++t2) c[t2] = a[t2][u];
+      dft_small<T, R2>(c);
+      p[u * sub1] = c[0];
+#pragma unroll
+      for (int u2 = 1; u2 < R2; ++u2)
+        p[u * sub1 + u2 * sub2] = (sub2 > 1) ? cmul(c[u2], cplx<T>{(T)pw2[u2].x, (T)pw2[u2].y}) : c[u2];
+    }
+  }
+  __syncthreads();
+}
+
+// all passes of a plan (single and fused), tables in shared memory at stw
+template <typename T>
+__device__ __forceinline__ void fft_run_passes(cplx<T>* z, const int n, const DctArgs& a, const double2* stw) {
+  int L = n;
+  for (int p = 0; p < a.npass;) {
+    const int R = a.radix[p];
+    const double2* twA = stw + a.tw_off[p];
+    const double2* twB = twA + a.tw_na[p];
+    if (a.fuse[p]) {
+      const int R2 = a.radix[p + 1];
+      const double2* twA2 = stw + a.tw_off[p + 1];
+      const double2* twB2 = twA2 + a.tw_na[p + 1];
+      const unsigned mg = a.magic[p + 1];
+      switch (R * 8 + R2) {
+        case 4 * 8 + 4: fft_pass2_s<T, 4, 4>(z, n, L, twA, twB, twA2, twB2, mg); break;
+        case 5 * 8 + 3: fft_pass2_s<T, 5, 3>(z, n, L, twA, twB, twA2, twB2, mg); break;
+        case 5 * 8 + 2: fft_pass2_s<T, 5, 2>(z, n, L, twA, twB, twA2, twB2, mg); break;
+        case 4 * 8 + 3: fft_pass2_s<T, 4, 3>(z, n, L, twA, twB, twA2, twB2, mg); break;
+        case 4 * 8 + 2: fft_pass2_s<T, 4, 2>(z, n, L, twA, twB, twA2, twB2, mg); break;
+        case 3 * 8 + 3: fft_pass2_s<T, 3, 3>(z, n, L, twA, twB, twA2, twB2, mg); break;
+        default: fft_pass2_s<T, 3, 2>(z, n, L, twA, twB, twA2, twB2, mg); break;
+      }
+      L /= R * R2;
+      p += 2;
+    } else {
+      if (R == 4) fft_pass_s<T, 4>(z, n, L, twA, twB, a.magic[p]);
+      else if (R == 2) fft_pass_s<T, 2>(z, n, L, twA, twB, a.magic[p]);
+      else if (R == 3) fft_pass_s<T, 3>(z, n, L, twA, twB, a.magic[p]);
+      else fft_pass_s<T, 5>(z, n, L, twA, twB, a.magic[p]);
+      L /= R;
+      ++p;
+    }
+  }
+}
+
 template <typename S>
 __device__ __forceinline__ double sample_to_double(S v) { return (double)v; }
 
@@ -271,17 +401,7 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
   __syncthreads();
 
   // ---- N/2-point complex FFT, in place, decimation in frequency ----
-  int L = a.n;
-  for (int p = 0; p < a.npass; ++p) {
-    const int R = a.radix[p];
-    const double2* twA = stw + a.tw_off[p];
-    const double2* twB = twA + a.tw_na[p];
-    if (R == 4) fft_pass_s<T, 4>(z, a.n, L, twA, twB, a.magic[p]);
-    else if (R == 2) fft_pass_s<T, 2>(z, a.n, L, twA, twB, a.magic[p]);
-    else if (R == 3) fft_pass_s<T, 3>(z, a.n, L, twA, twB, a.magic[p]);
-    else fft_pass_s<T, 5>(z, a.n, L, twA, twB, a.magic[p]);
-    L /= R;
-  }
+  fft_run_passes<T>(z, a.n, a, stw);
 
   // ---- unpack to the length-N real FFT, Makhoul post-twiddle, scale, store ----
   double* out = a.out + (size_t)blockIdx.x * a.out_ld;
@@ -389,17 +509,7 @@ __global__ void __launch_bounds__(512) dct_half_kernel(const DctArgs a) {
     __syncthreads();
   }
 
-  int L = n2;
-  for (int p = 0; p < a.npass; ++p) {
-    const int R = a.radix[p];
-    const double2* twA = stw + a.tw_off[p];
-    const double2* twB = twA + a.tw_na[p];
-    if (R == 4) fft_pass_s<double, 4>(z, n2, L, twA, twB, a.magic[p]);
-    else if (R == 2) fft_pass_s<double, 2>(z, n2, L, twA, twB, a.magic[p]);
-    else if (R == 3) fft_pass_s<double, 3>(z, n2, L, twA, twB, a.magic[p]);
-    else fft_pass_s<double, 5>(z, n2, L, twA, twB, a.magic[p]);
-    L /= R;
-  }
+  fft_run_passes<double>(z, n2, a, stw);
 
   // ---- unpack: the coefficients kq = h (mod 2), same arithmetic as dct_segments_kernel ----
   double* out = a.out + (size_t)seg_local * a.out_ld;

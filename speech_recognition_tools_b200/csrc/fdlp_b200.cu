@@ -104,9 +104,30 @@ static int factor_radices(int n, int* radix, int* npass) {
   return 0;
 }
 
+// Orders the radices so that consecutive passes pair into in-register passes of radix R1 * R2 <= 16 (dct.cuh
+// fft_pass2_s): repeatedly the largest remaining factor with the largest partner that keeps the product <= 16,
+// fours first ((4,4) = 16).  fuse[p] = 1 marks pass p as fused with pass p + 1.  N/2 = 12000: (4,4) (5,3) (5,2) 5.
+static void pair_radices(int* radix, int npass, int* fuse) {
+  int cnt[6] = {0, 0, 0, 0, 0, 0};
+  for (int i = 0; i < npass; ++i) ++cnt[radix[i]];
+  int c = 0;
+  for (int i = 0; i < kMaxRadixPasses; ++i) fuse[i] = 0;
+  while (cnt[4] >= 2) { radix[c] = 4; radix[c + 1] = 4; fuse[c] = 1; c += 2; cnt[4] -= 2; }
+  for (int f1 = 5; f1 >= 2; --f1)
+    while (cnt[f1] > 0) {
+      --cnt[f1];
+      int f2 = 0;
+      for (int q = f1; q >= 2; --q)
+        if (cnt[q] > 0 && f1 * q <= 16 && !(f1 == 2 && q == 2) && !(f1 == 5 && q >= 4)) { f2 = q; break; }
+      if (f2) { --cnt[f2]; radix[c] = f1; radix[c + 1] = f2; fuse[c] = 1; c += 2; }
+      else radix[c++] = f1;
+    }
+}
+
 struct FftTables {
   int n = 0, npass = 0;
   int radix[kMaxRadixPasses];
+  int fuse[kMaxRadixPasses] = {};
   double2* d_tw = nullptr;
   int32_t* d_perm = nullptr;
   double2* d_unpackA = nullptr;  // [n+1] exp(-2 pi i k / (2n))
@@ -139,6 +160,8 @@ static int build_fft_tables(int n, FftTables* t) {
   t->n = n;
   if (factor_radices(n, t->radix, &t->npass) != 0)
     return set_err(FDLP_E_UNSUPPORTED, "FFT length %s%ld has a prime factor other than 2, 3, 5", "", n);
+  static const bool no_fuse = getenv("FDLP_DCT_NOFUSE") != nullptr;  // A/B runs
+  if (!no_fuse) pair_radices(t->radix, t->npass, t->fuse);
   std::vector<double2> tw(n), A(n + 1);
   for (int k = 0; k < n; ++k) {
     const long double ang = -2.0L * M_PIl * k / n;
@@ -758,13 +781,13 @@ static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld
   a.tws = p->fft.d_tws; a.tws_n = p->fft.tws_n; a.unp = p->d_unp; a.unp_na = p->unp_na; a.hamt = p->d_hamt; a.ham_na = p->ham_na;
   a.win_a0 = p->prm.window_kind == FDLP_WINDOW_HANNING ? 0.5 : p->prm.window_kind == FDLP_WINDOW_SQUARE ? 1.0 : 0.54;
   a.win_a1 = p->prm.window_kind == FDLP_WINDOW_HANNING ? 0.5 : p->prm.window_kind == FDLP_WINDOW_SQUARE ? 0.0 : 0.46;
-  for (int i = 0; i < p->fft.npass; ++i) { a.tw_off[i] = p->fft.tw_off[i]; a.tw_na[i] = p->fft.tw_na[i]; a.magic[i] = p->fft.magic[i]; }
+  for (int i = 0; i < p->fft.npass; ++i) { a.tw_off[i] = p->fft.tw_off[i]; a.tw_na[i] = p->fft.tw_na[i]; a.magic[i] = p->fft.magic[i]; a.fuse[i] = p->fft.fuse[i]; }
   a.vec_ok = (((uintptr_t)b->wav) % 16 == 0) ? 1 : 0;
   const dim3 grid(nseg), block(512);
   if (p->dct_half) {
     const FftTables& f = p->fft_half;
     a.npass = f.npass;
-    for (int i = 0; i < f.npass; ++i) { a.radix[i] = f.radix[i]; a.tw_off[i] = f.tw_off[i]; a.tw_na[i] = f.tw_na[i]; a.magic[i] = f.magic[i]; }
+    for (int i = 0; i < f.npass; ++i) { a.radix[i] = f.radix[i]; a.tw_off[i] = f.tw_off[i]; a.tw_na[i] = f.tw_na[i]; a.magic[i] = f.magic[i]; a.fuse[i] = f.fuse[i]; }
     a.perm = f.d_perm; a.tws = f.d_tws; a.tws_n = f.tws_n; a.tw1 = p->d_tw1; a.tw1_na = p->tw1_na;
     const dim3 grid2(2 * (unsigned)nseg);
     if (b->wav_dtype == FDLP_WAV_INT16) dct_half_kernel<int16_t><<<grid2, block, p->dct_smem, st>>>(a);
