@@ -224,6 +224,7 @@ struct fdlp_plan {
   int na = 0, a_groups = 1;  // autocorrelation lag blocking
   int pad = 0, ld = 0;       // circular extension (doubles) and row stride of the DCT / filterbank buffers
   bool dct_fp64 = true;
+  int dct_threads = 512;     // threads per DCT CTA (chosen for the butterfly counts of the passes)
   bool dct_half = false;     // float64 DCT with two CTAs per segment (dct_half_kernel): N float64 exceed shared memory
   FftTables fft_half;        // plan of the N/4-point sub-transforms
   double2* d_tw1 = nullptr;  // split table of the first radix-2 stage
@@ -783,7 +784,8 @@ static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld
   a.win_a1 = p->prm.window_kind == FDLP_WINDOW_HANNING ? 0.5 : p->prm.window_kind == FDLP_WINDOW_SQUARE ? 0.0 : 0.46;
   for (int i = 0; i < p->fft.npass; ++i) { a.tw_off[i] = p->fft.tw_off[i]; a.tw_na[i] = p->fft.tw_na[i]; a.magic[i] = p->fft.magic[i]; a.fuse[i] = p->fft.fuse[i]; }
   a.vec_ok = (((uintptr_t)b->wav) % 16 == 0) ? 1 : 0;
-  const dim3 grid(nseg), block(512);
+  static const int dct_threads_env = getenv("FDLP_DCT_THREADS") ? atoi(getenv("FDLP_DCT_THREADS")) : 0;
+  const dim3 grid(nseg), block(dct_threads_env >= 64 && dct_threads_env <= 512 ? (dct_threads_env & ~31) : p->dct_threads);
   if (p->dct_half) {
     const FftTables& f = p->fft_half;
     a.npass = f.npass;
