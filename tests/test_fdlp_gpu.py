@@ -197,6 +197,21 @@ def test_circular_cepstrum_orders_up_to_159_any_length(order, coeff_num):
     assert_feats_close(got, ref)
 
 
+@pytest.mark.parametrize("order,coeff_num,coeff_range", [(1, 2, "0,2"), (2, 3, "0,3"), (3, 10, "1,8"), (4, 4, "0,4"),
+                                                         (5, 30, "0,30"), (6, 5, "1,5"), (30, 30, "0,30"), (79, 80, "0,80"),
+                                                         (80, 81, "0,81")])
+def test_small_lpc_orders_and_short_cepstra(order, coeff_num, coeff_range):
+    """The recipes' modulation-spectrum runs use LPC orders 4, 5 and 30: the peeled first orders, the tail orders
+    and cepstra shorter or longer than the LPC vector of the register kernel (lpc_env.cuh) against the oracle."""
+    kw = dict(nfilters=6, order=order, fduration=0.5, frate=100, overlap_fraction=0.25, coeff_num=coeff_num,
+              coeff_range=coeff_range, fbank_type="mel,1")
+    ex = extractor(**kw)
+    x = synth.make_utterance("speechlike", 23, order, 30000, 300.0)
+    got = ex([x], jitter=[1])[0].cpu().numpy()
+    ref = ofdlp.fdlp_spectrogram(x, rng=random.Random(1), **kw)
+    assert_feats_close(got, ref)
+
+
 def test_tail_pruning_is_below_output_resolution():
     """The autocorrelation skips cochlear filter skirts below 1e-12 of the band maximum (48 % of the taps at the
     WSJ setting).  Against the exact-support plan (tail_eps = 0) on an input with an 80 dB hum far from
