@@ -254,6 +254,13 @@ int mfcc_forward(mfcc_plan* plan, const mfcc_batch* batch, void* stream);
 int cmvn_apply(float* feats /*dev [n_frames, dim], in place*/, int64_t n_frames, int32_t dim,
                const double* stats /*dev [2, dim+1]*/, int32_t norm_vars, void* stream);
 
+/* Synthetic white utterances written straight into a packed device batch (measurement input, SURVEY.md 8d: the
+ * 1000-hour workload is never stored).  Bit-identical to speech_recognition_tools_b200/synth.py white_int16(seed,
+ * utt_id[u], T_u, scale_q16).  No reference counterpart. */
+int fdlp_synth_white(int16_t* out /*dev, packed*/, const int64_t* utt_wav_off /*dev [n_utt+1]*/,
+                     const int64_t* utt_id /*dev [n_utt]*/, int32_t n_utt, int64_t max_len, uint64_t seed,
+                     int32_t scale_q16 /*5197: sigma ~ 3000*/, void* stream);
+
 /* FP64 pipe probe: runs a register-resident DFMA / DMMA loop and returns TFLOP/s (roofline denominator) */
 int fdlp_measure_fp64_peak(double* dfma_tflops, double* dmma_tflops);
 

@@ -107,6 +107,8 @@ SYMBOLS = [
     ("cmvn_apply", C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]),
     ("fdlp_modspec_forward", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     ("fdlp_diff_filter", C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),
+    ("fdlp_synth_white", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_uint64, C.c_int32,
+                                   C.c_void_p]),
     ("fdlp_measure_fp64_peak", C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 ]
 

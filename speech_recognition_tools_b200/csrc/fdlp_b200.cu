@@ -1488,6 +1488,18 @@ extern "C" int fdlp_diff_filter(const void* wav, int32_t wav_dtype, const int64_
 }
 
 // ================================================================ CMVN apply
+extern "C" int fdlp_synth_white(int16_t* out, const int64_t* utt_wav_off, const int64_t* utt_id, int32_t n_utt,
+                                int64_t max_len, uint64_t seed, int32_t scale_q16, void* stream) {
+  if (n_utt <= 0) return FDLP_OK;
+  if (!out || !utt_wav_off || !utt_id || max_len < 1 || n_utt > 65535) return set_err(FDLP_E_ARG, "invalid synth arguments%s", "");
+  SynthArgs a;
+  a.out = out; a.utt_wav_off = utt_wav_off; a.utt_id = utt_id; a.n_utt = n_utt; a.seed = seed; a.scale_q16 = scale_q16;
+  const dim3 grid((unsigned)std::min<int64_t>((max_len + 1023) / 1024, 64), (unsigned)n_utt);
+  synth_white_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
 extern "C" int cmvn_apply(float* feats, int64_t n_frames, int32_t dim, const double* stats, int32_t norm_vars, void* stream) {
   if (!feats || !stats || n_frames < 0 || dim < 1) return set_err(FDLP_E_ARG, "bad argument%s", "");
   if (n_frames == 0) return FDLP_OK;

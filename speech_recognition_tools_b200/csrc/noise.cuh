@@ -147,4 +147,34 @@ __global__ void __launch_bounds__(256) diff_fir_kernel(const DiffArgs a) {
   }
 }
 
+// Synthetic white utterances generated in place on the device (throughput sets are never stored):
+// the same counter-based integer arithmetic as speech_recognition_tools_b200/synth.py white_int16 -- splitmix64 of
+// (seed, utterance id, sample index), four 16-bit uniforms summed and centred, times scale_q16 / 65536 -- so the
+// stream is bit-identical to the numpy one the parity tests use.
+struct SynthArgs {
+  int16_t* out;                 // packed batch
+  const int64_t* utt_wav_off;   // [n_utt+1]
+  const int64_t* utt_id;        // [n_utt] utterance number in the hash
+  int n_utt;
+  unsigned long long seed;
+  int scale_q16;
+};
+
+__global__ void __launch_bounds__(256) synth_white_kernel(const SynthArgs a) {
+  const int u = blockIdx.y;
+  const int64_t woff = a.utt_wav_off[u];
+  const int64_t T = a.utt_wav_off[u + 1] - woff;
+  const unsigned long long key = (a.seed * 0xD1342543DE82EF95ULL) ^ ((unsigned long long)a.utt_id[u] * 0x2545F4914F6CDD1DULL);
+  for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < T; n += (int64_t)gridDim.x * blockDim.x) {
+    unsigned long long z = key + (unsigned long long)n + 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    z = z ^ (z >> 31);
+    const long long s = (long long)((z & 0xFFFF) + ((z >> 16) & 0xFFFF) + ((z >> 32) & 0xFFFF) + (z >> 48)) - 2 * 65535;
+    long long v = (s * a.scale_q16 + 32768) >> 16;
+    v = v < -32768 ? -32768 : (v > 32767 ? 32767 : v);
+    a.out[woff + n] = (int16_t)v;
+  }
+}
+
 }  // namespace fdlp

@@ -1,0 +1,163 @@
+#!/usr/bin/env python
+"""Dataset-scale run, SURVEY.md section 8(d) cfg #5: a LibriSpeech-shaped corpus (lognormal utterance lengths, mean
+12.3 s) of `--hours` hours, WSJ recipe parameters, sharded over the ranks by segment count, length-bucketed batches,
+white utterances generated on the device per batch (the corpus is never stored: 115 GB of int16 at 1000 h), global
+CMVN all-reduced at the end.
+
+  python tools/run_dataset.py --hours 1000                               # one GPU
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29533 \
+      tools/run_dataset.py --hours 1000
+
+Timed region (barrier + synchronize on both sides, max over ranks, device events and host wall clock): for every
+batch of the rank the host layout (overlap-add pointers, offsets), the upload of the index tables, the generation
+kernel, the seven FDLP kernels with the CMVN partial sums, and at the end the CMVN all-reduce.  Features stay on
+the owning rank and are overwritten by the next batch (the reference writes one ark per job; file output is not
+part of this measurement).  Before the timed region rank 0 checks a sample: device-generated samples == numpy
+generator bit for bit, features against the CPU oracle, CMVN sums against a float64 numpy sum.
+"""
+import argparse
+import json
+import os
+import random
+import sys
+import time
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from speech_recognition_tools_b200 import cmvn as cmvn_mod  # noqa: E402
+from speech_recognition_tools_b200 import sharding, synth  # noqa: E402
+from speech_recognition_tools_b200.fdlp import FdlpConfig, FdlpExtractor, segment_count  # noqa: E402
+
+WSJ = dict(nfilters=80, order=150, fduration=1.5, frate=100, overlap_fraction=0.25, coeff_num=100,
+           coeff_range="0,100", fbank_type="cochlear,1,1,1,2.5,1")
+SEED = 2024
+
+
+def corpus_lengths(hours, seed=5):
+    """clip(lognormal(mu = ln 12.3 s - sigma^2 / 2, sigma = 0.45), 1 s, 35 s) until `hours` hours are reached."""
+    rng = np.random.default_rng(seed)
+    sigma = 0.45
+    n = int(hours * 3600 / 12.3 * 1.05) + 16
+    d = np.clip(rng.lognormal(np.log(12.3) - sigma * sigma / 2, sigma, n), 1.0, 35.0)
+    keep = int(np.searchsorted(np.cumsum(d), hours * 3600.0)) + 1
+    return (d[:keep] * 16000).astype(np.int64)
+
+
+def sample_check(ex, lengths, n_check):
+    """rank 0, untimed: generator bit-exactness, features vs the oracle, CMVN sums vs numpy."""
+    from oracle import fdlp as ofdlp
+    idx = np.linspace(0, len(lengths) - 1, n_check).astype(int)
+    lens = lengths[idx]
+    wav, _ = synth.white_int16_device(SEED, idx, lens, ex.device)
+    host = wav.cpu().numpy()
+    off = np.concatenate([[0], np.cumsum(lens)])
+    exact = all(np.array_equal(host[off[i]:off[i + 1]], synth.white_int16(SEED, int(u), int(T)))
+                for i, (u, T) in enumerate(zip(idx, lens)))
+    lay = ex.layout(lens, jitter=[int(u) for u in idx])
+    acc = cmvn_mod.new_accumulator(WSJ["nfilters"], ex.device)
+    feats, status = ex.forward_packed(wav, lay, cmvn=acc)
+    f = feats.cpu().numpy()
+    foff = lay.utt_frame_off
+    fb = ofdlp.make_fbank(WSJ["fbank_type"], WSJ["nfilters"], 2 * ex.geom["N"], 16000)
+    worst = 0.0
+    for i in range(0, n_check, max(1, n_check // 6)):  # a handful through the CPU oracle (seconds each)
+        ref = ofdlp.fdlp_spectrogram(host[off[i]:off[i + 1]], fbank=fb, rng=random.Random(int(idx[i])), **WSJ)
+        got = f[foff[i]:foff[i + 1]]
+        m = ref > np.log(1e-14) + 1e-9
+        worst = max(worst, float(np.max(np.abs(got[m] - ref[m]))))
+    a = acc.cpu().numpy()
+    f64 = f.astype(np.float64)
+    ref_stats = np.zeros_like(a)
+    ref_stats[0, :-1], ref_stats[0, -1], ref_stats[1, :-1] = f64.sum(0), f64.shape[0], (f64 * f64).sum(0)
+    cm_rel = float(np.max(np.abs(a - ref_stats) / np.maximum(np.abs(ref_stats), 1e-300)))
+    return {"utterances": int(n_check), "generator_bit_exact": bool(exact), "features_max_abs_err_vs_oracle": worst,
+            "cmvn_rel_err_vs_float64_numpy": cm_rel, "flagged": int((status != 0).sum().item())}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--hours", type=float, default=1000.0)
+    ap.add_argument("--max_segments", type=int, default=16000, help="segment budget of one batch")
+    ap.add_argument("--check", type=int, default=24, help="utterances of the untimed parity sample (0: skip)")
+    args = ap.parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    ex = FdlpExtractor(FdlpConfig(**WSJ), device=dev)
+    g = ex.geom
+    lengths = corpus_lengths(args.hours)
+    nsegs = np.array([segment_count(int(T), g["N"], g["S"]) for T in lengths], dtype=np.int64)
+    shards = sharding.assign_to_ranks(nsegs, world)
+    mine = shards[rank]
+    batches = sharding.make_batches(mine, nsegs, args.max_segments)
+    check = sample_check(ex, lengths, args.check) if (rank == 0 and args.check > 0) else None
+
+    J = WSJ["nfilters"]
+    max_frames = max(int(np.ceil(lengths[b] * 100 / 16000).sum()) for b in batches)
+    feats = torch.empty((max_frames, J), dtype=torch.float32, device=dev)
+    acc = cmvn_mod.new_accumulator(J, dev)
+    status_total = 0
+
+    def one_batch(b):
+        lens = lengths[b]
+        lay = ex.layout(lens, jitter=int(b[0]))
+        wav, _ = synth.white_int16_device(SEED, b, lens, dev)
+        _, st = ex.forward_packed(wav, lay, feats=feats[:lay.n_frames], cmvn=acc)
+        return st
+
+    one_batch(batches[0])  # warm-up: scratch allocation of the largest shapes happens outside the timed region
+    one_batch(batches[-1])
+    acc.zero_()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    flagged = torch.zeros((), dtype=torch.int64, device=dev)
+    for b in batches:
+        st = one_batch(b)
+        flagged += (st != 0).sum()
+    cmvn_mod.all_reduce(acc)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    wall = time.perf_counter() - t0
+    dev_s = e0.elapsed_time(e1) * 1e-3
+    t = torch.tensor([wall, dev_s, float(nsegs[mine].sum()), float(flagged.item())], dtype=torch.float64, device=dev)
+    if world > 1:
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tmin = t.clone()
+        dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+        tsum = t.clone()
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+    else:
+        tmax = tmin = tsum = t
+    if rank == 0:
+        audio = float(lengths.sum()) / 16000.0
+        a = acc.cpu().numpy()
+        out = {"workload": "cfg5: LibriSpeech-shaped corpus, WSJ recipe parameters, white utterances generated on device",
+               "hours": audio / 3600.0, "utterances": int(len(lengths)), "segments": int(nsegs.sum()), "n_gpus": world,
+               "batches_per_rank": len(batches), "max_segments_per_batch": args.max_segments,
+               "seconds_wall_max_over_ranks": float(tmax[0]), "seconds_device_max_over_ranks": float(tmax[1]),
+               "xRT": audio / float(tmax[0]), "segment_imbalance": float(tmax[2] / (tsum[2] / world)) - 1.0,
+               "seconds_wall_min_over_ranks": float(tmin[0]), "flagged_utterances": int(tsum[3]),
+               "cmvn": {"frames": float(a[0, -1]), "mean_band0": float(a[0, 0] / a[0, -1]),
+                        "expected_frames": int(np.ceil(lengths * 100 / 16000).sum())},
+               "sample_check": check}
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
