@@ -353,3 +353,14 @@ def test_plans_of_different_sizes_coexist():
                           device="cuda:0")
     small([x], jitter=[3])
     assert torch.equal(big([x], jitter=[3])[0], ref)
+
+
+def test_device_white_generator_is_bit_identical_to_numpy():
+    """fdlp_synth_white (the on-device input of tools/run_dataset.py) == synth.white_int16, sample for sample."""
+    lens = [1, 2, 31, 4097, 70001]
+    ids = [0, 7, 123456, 3, 2 ** 40 + 5]
+    for seed in (0, 2024, 2 ** 63 + 11):
+        wav, off = synth.white_int16_device(seed, ids, lens, "cuda:0")
+        host, o = wav.cpu().numpy(), off.cpu().numpy()
+        for i, (u, T) in enumerate(zip(ids, lens)):
+            assert np.array_equal(host[o[i]:o[i + 1]], synth.white_int16(seed, u, T))
