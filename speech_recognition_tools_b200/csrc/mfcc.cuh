@@ -11,7 +11,7 @@
 // FMAs per frame (used = min(flen, P) samples, nb = P/2 + 1 distinct magnitudes because |X[P-k]| = |X[k]| for real
 // input; the filterbank columns k and P-k are folded on the host).  One CTA owns a tile of kMfccFT frames: thread k
 // keeps bin k of all frames in registers, frame samples are broadcast reads of shared memory, the twiddle
-// exp(-2 pi i (n k mod P) / P) comes from a P-entry shared table with the index advanced by k per sample.
+// exp(-2 pi i (n k mod P) / P) comes from a P-entry shared table every 16th sample and from a recurrence in between.
 // FP32 products and sums in the DFT and the filterbank (relative 1e-6), float64 from the logarithm on.
 #pragma once
 #include "common.cuh"
@@ -106,11 +106,21 @@ __global__ void __launch_bounds__(288) mfcc_frames_kernel(const MfccArgs a) {
     float re[FT], im[FT];
 #pragma unroll
     for (int f = 0; f < FT; ++f) re[f] = im[f] = 0.f;
-    int m = 0;  // (n * k) mod P
+    // twiddle exp(-2 pi i n k / P): read from the table every 16th sample, advanced by w_k = exp(-2 pi i k / P) in
+    // between (a gather per sample kept the shared-memory pipe as busy as the FMA pipe; 15 float32 products drift by
+    // 1e-6 at most before the next table value)
+    const float2 wk = tw[k];
+    const int k16 = (int)((16LL * k) % a.P);
+    int m = 0;  // (n * k) mod P at n = 0, 16, 32, ...
+    float2 w = make_float2(1.f, 0.f);
     for (int n = 0; n < a.used; ++n) {
-      const float2 w = tw[m];
-      m += k;
-      if (m >= a.P) m -= a.P;
+      if ((n & 15) == 0) {
+        w = tw[m];
+        m += k16;
+        if (m >= a.P) m -= a.P;
+      } else {
+        w = make_float2(w.x * wk.x - w.y * wk.y, w.x * wk.y + w.y * wk.x);
+      }
 #pragma unroll
       for (int f4 = 0; f4 < FT / 4; ++f4) {
         const float4 x = xs4[n * (FT / 4) + f4];
