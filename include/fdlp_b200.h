@@ -56,6 +56,7 @@ extern "C" {
 
 #define FDLP_WAV_INT16 0
 #define FDLP_WAV_FLOAT32 1
+#define FDLP_WAV_FLOAT64 2 /* fdlp_forward / fdlp_modspec_forward only: the waveform fdlp_reverb_forward returns */
 
 #define FDLP_NOISE_NONE 0
 #define FDLP_NOISE_INT16_WRAP 1 /* energies squared and averaged with int16 wrap-around, features.py:27-28 on int16 input */
@@ -218,6 +219,44 @@ int fdlp_modspec_forward(fdlp_plan* plan, const fdlp_batch* batch, const int32_t
 int fdlp_diff_filter(const void* wav /*dev, packed*/, int32_t wav_dtype, const int64_t* utt_wav_off /*dev [n_utt+1]*/,
                      int32_t n_utt, int64_t max_len /*longest utterance, samples*/, float* out /*dev, packed*/,
                      void* stream);
+
+/* ---- --add_reverb (features.py:110-115 addReverb, called at computeFDLPSpectrogram.py:168-170, computeMelSpectrum.py:143-145,
+ *      computeMfccFeatures.py:118-120): out = convolve(sig, rir) (full), xxc = correlate(sig, out, 'valid'),
+ *      indM = len(xxc) - argmax(xxc), result = out[indM : indM + len(sig)], per utterance, after the optional noise
+ *      mixing (same noise arrays as fdlp_batch).  `rir` is the HOST float64 impulse response as the reference
+ *      forms it (rir[:, 1] / 2^15, :76-87).  The batch is cut into blocks of `block` samples
+ *      (fdlp_reverb_plan_get_block): utt_blk_off[u+1] - utt_blk_off[u] = ceil((T_u + R - 1) / block), blk_utt = owner
+ *      of each block, both computed by the host like utt_seg_off / seg_utt.  The result has the packed layout of the
+ *      input, float64 (for fdlp_forward with FDLP_WAV_FLOAT64) or float32 (mel / MFCC paths); out_len[u] is T_u, or
+ *      T_u - 1 in the reference's corner case indM == R (the slice runs off the end of the convolution). ---- */
+typedef struct fdlp_reverb_plan fdlp_reverb_plan;
+typedef struct {
+  const void* wav;              /* dev, packed int16 or float32 */
+  int32_t wav_dtype;
+  int32_t n_utt;
+  const int64_t* utt_wav_off;   /* dev [n_utt+1] */
+  int64_t max_len;              /* longest utterance, samples */
+  int32_t n_blk;                /* total blocks */
+  const int32_t* utt_blk_off;   /* dev [n_utt+1] */
+  const int32_t* blk_utt;       /* dev [n_blk] */
+  int32_t noise_mode;           /* FDLP_NOISE_* ; the mix happens before the reverberation (:158-170) */
+  const void* noise;
+  const int64_t* utt_noise_off;
+  const double* utt_snr_db;
+  void* out;                    /* dev, packed like wav */
+  int32_t out_dtype;            /* FDLP_WAV_FLOAT32 or FDLP_WAV_FLOAT64 */
+  int32_t* ind;                 /* dev [n_utt] indM of each utterance, or NULL */
+  int64_t* out_len;             /* dev [n_utt] samples produced, or NULL */
+} fdlp_reverb_batch;
+
+int fdlp_reverb_plan_create(const double* rir /*host [R]*/, int32_t R, int32_t block /*0: auto*/, fdlp_reverb_plan** out_plan);
+int fdlp_reverb_plan_destroy(fdlp_reverb_plan* plan);
+int fdlp_reverb_plan_get_block(const fdlp_reverb_plan* plan, int32_t* block, int32_t* partitions);
+int fdlp_reverb_plan_set_profiling(fdlp_reverb_plan* plan, int32_t enable);
+/* CUDA-event durations of the most recent profiled forward: window spectra, convolution, correlation, alignment */
+int fdlp_reverb_plan_get_kernel_ms(fdlp_reverb_plan* plan, float* out4);
+int64_t fdlp_reverb_plan_scratch_bytes(const fdlp_reverb_plan* plan, int32_t n_blk);
+int fdlp_reverb_forward(fdlp_reverb_plan* plan, const fdlp_reverb_batch* batch, void* stream);
 
 /* ---- MFCC features (computeMfccFeatures.py:111-131: signal / 2^15 [+ noise], Hamming frames, the reference's
  *      (nfft/2 + 1)-point DFT magnitude against createFbank(nfilters, nfft, srate), log10, type-II DCT along the bands,

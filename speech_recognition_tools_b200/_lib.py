@@ -14,7 +14,7 @@ FDLP_OK = 0
 FDLP_E_ARG, FDLP_E_CUDA, FDLP_E_UNSUPPORTED, FDLP_E_NOMEM = -1, -2, -3, -4
 FDLP_ST_SINGULAR, FDLP_ST_NONFINITE = 1, 2
 FDLP_FBANK_MEL, FDLP_FBANK_COCHLEAR, FDLP_FBANK_CUSTOM = 0, 1, 2
-FDLP_WAV_INT16, FDLP_WAV_FLOAT32 = 0, 1
+FDLP_WAV_INT16, FDLP_WAV_FLOAT32, FDLP_WAV_FLOAT64 = 0, 1, 2
 FDLP_WINDOW_HAMMING, FDLP_WINDOW_HANNING, FDLP_WINDOW_SQUARE = 0, 1, 2
 FDLP_NOISE_NONE, FDLP_NOISE_INT16_WRAP, FDLP_NOISE_FLOAT = 0, 1, 2
 
@@ -77,6 +77,15 @@ class MfccBatch(C.Structure):
     ]
 
 
+class ReverbBatch(C.Structure):
+    _fields_ = [
+        ("wav", C.c_void_p), ("wav_dtype", C.c_int32), ("n_utt", C.c_int32), ("utt_wav_off", C.c_void_p),
+        ("max_len", C.c_int64), ("n_blk", C.c_int32), ("utt_blk_off", C.c_void_p), ("blk_utt", C.c_void_p),
+        ("noise_mode", C.c_int32), ("noise", C.c_void_p), ("utt_noise_off", C.c_void_p), ("utt_snr_db", C.c_void_p),
+        ("out", C.c_void_p), ("out_dtype", C.c_int32), ("ind", C.c_void_p), ("out_len", C.c_void_p),
+    ]
+
+
 # every symbol include/fdlp_b200.h declares: (name, restype, argtypes)
 SYMBOLS = [
     ("fdlp_last_error", C.c_char_p, []),
@@ -107,6 +116,13 @@ SYMBOLS = [
     ("cmvn_apply", C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]),
     ("fdlp_modspec_forward", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     ("fdlp_diff_filter", C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),
+    ("fdlp_reverb_plan_create", C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    ("fdlp_reverb_plan_destroy", C.c_int, [C.c_void_p]),
+    ("fdlp_reverb_plan_get_block", C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    ("fdlp_reverb_plan_set_profiling", C.c_int, [C.c_void_p, C.c_int32]),
+    ("fdlp_reverb_plan_get_kernel_ms", C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    ("fdlp_reverb_plan_scratch_bytes", C.c_int64, [C.c_void_p, C.c_int32]),
+    ("fdlp_reverb_forward", C.c_int, [C.c_void_p, C.POINTER(ReverbBatch), C.c_void_p]),
     ("fdlp_synth_white", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_uint64, C.c_int32,
                                    C.c_void_p]),
     ("fdlp_measure_fp64_peak", C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double)]),

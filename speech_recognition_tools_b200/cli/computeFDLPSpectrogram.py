@@ -21,6 +21,7 @@ from speech_recognition_tools_b200 import _lib  # noqa: E402
 from speech_recognition_tools_b200.cli.common import iter_scp, load_noise, write_lens  # noqa: E402
 from speech_recognition_tools_b200.fdlp import FdlpConfig, FdlpExtractor, NoiseSpec, segment_count  # noqa: E402
 from speech_recognition_tools_b200.kaldi_io import write_ark_scp  # noqa: E402
+from speech_recognition_tools_b200.reverb import Reverberator, load_rir  # noqa: E402
 
 MAX_SEGMENTS_PER_BATCH = 4096
 
@@ -38,10 +39,12 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
         raise NotImplementedError("only the Hamming window of the reference recipes is implemented")
     cfg = FdlpConfig.from_args(args)
     add_noise, add_reverb = args.add_noise, args.add_reverb
-    if add_reverb and add_reverb != "clean":
-        if add_reverb not in ("small_room", "medium_room", "large_room"):
-            raise ValueError("Invalid type of reverberation!")
-        raise NotImplementedError("--add_reverb needs ./RIR/*.wav, absent from the reference snapshot")
+    # computeFDLPSpectrogram.py:75-91: ./RIR/RIR_<room>_AnglA.wav, second channel, / 2^15; ValueError for an unknown
+    # room, the file-not-found error of scipy's reader when the recordings are not in the working directory
+    rir = load_rir(add_reverb)
+    if add_reverb == "clean":
+        print("%s: No reverberation added!" % sys.argv[0])
+    reverberator = None
     noise = None
     if add_noise and add_noise not in ("clean",):
         if add_noise == "diff":
@@ -67,7 +70,10 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
         elif noise is not None:
             draws = [np.random.rand() for _ in wavs]  # features.py:25, one draw per utterance in scp order
             nspec = NoiseSpec(samples=noise[0], snr_db=noise[1], rand=draws, mode="int16_wrap")
-        outs, status = ex(wavs, jitter=_GlobalRandom(), noise=nspec, return_status=True)
+        nonlocal reverberator
+        if rir is not None and reverberator is None:
+            reverberator = Reverberator(rir, device=ex.device)
+        outs, status = ex(wavs, jitter=_GlobalRandom(), noise=nspec, return_status=True, reverb=reverberator)
         st = status.cpu().numpy()
         for u, (k, o) in enumerate(zip(ids, outs)):
             all_feats[k] = o.cpu().numpy()

@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
           v0[e] = (double)(int16_t)(raw[e] & 0xffffu);
           v1[e] = (double)(int16_t)(raw[e] >> 16);
         }
-      } else {
+      } else if constexpr (sizeof(S) == 4) {
         float2 raw[kLdBatch];
 #pragma unroll
         for (int e = 0; e < kLdBatch; ++e) {
@@ -373,6 +373,15 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
         }
 #pragma unroll
         for (int e = 0; e < kLdBatch; ++e) { v0[e] = (double)raw[e].x; v1[e] = (double)raw[e].y; }
+      } else {  // float64 samples (the reverberated waveform, fdlp_reverb_forward)
+#pragma unroll
+        for (int e = 0; e < kLdBatch; ++e) {
+          const int i0 = 2 * (pb + e * (int)blockDim.x) - sh;
+          const int64_t q0 = q_base + i0;
+          fast[e] = pair_ok && i0 >= 0 && i0 + 2 <= N && q0 >= 0 && q0 + 2 <= T_utt;
+          const double2 raw = fast[e] ? __ldg(reinterpret_cast<const double2*>(sig + q0)) : make_double2(0.0, 0.0);
+          v0[e] = raw.x; v1[e] = raw.y;
+        }
       }
 #pragma unroll
       for (int e = 0; e < kLdBatch; ++e) {

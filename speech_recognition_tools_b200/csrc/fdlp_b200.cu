@@ -16,6 +16,7 @@
 #include "mfcc.cuh"
 #include "noise.cuh"
 #include "ola.cuh"
+#include "reverb.cuh"
 
 namespace fdlp {
 thread_local char g_err[512] = "";
@@ -684,12 +685,15 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   if (p->dct_half) {
     SET_SMEM((dct_half_kernel<int16_t>), p->dct_smem);
     SET_SMEM((dct_half_kernel<float>), p->dct_smem);
+    SET_SMEM((dct_half_kernel<double>), p->dct_smem);
   } else if (p->dct_fp64) {
     SET_SMEM((dct_segments_kernel<double, int16_t>), p->dct_smem);
     SET_SMEM((dct_segments_kernel<double, float>), p->dct_smem);
+    SET_SMEM((dct_segments_kernel<double, double>), p->dct_smem);
   } else {
     SET_SMEM((dct_segments_kernel<float, int16_t>), p->dct_smem);
     SET_SMEM((dct_segments_kernel<float, float>), p->dct_smem);
+    SET_SMEM((dct_segments_kernel<float, double>), p->dct_smem);
   }
   SET_SMEM(lpc_cepstrum_kernel, p->lpc_smem);
   SET_SMEM(ola_log_kernel, p->ola_smem);
@@ -793,6 +797,7 @@ static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld
     a.perm = f.d_perm; a.tws = f.d_tws; a.tws_n = f.tws_n; a.tw1 = p->d_tw1; a.tw1_na = p->tw1_na;
     const dim3 grid2(2 * (unsigned)nseg);
     if (b->wav_dtype == FDLP_WAV_INT16) dct_half_kernel<int16_t><<<grid2, block, p->dct_smem, st>>>(a);
+    else if (b->wav_dtype == FDLP_WAV_FLOAT64) dct_half_kernel<double><<<grid2, block, p->dct_smem, st>>>(a);
     else dct_half_kernel<float><<<grid2, block, p->dct_smem, st>>>(a);
     FDLP_CUDA(cudaGetLastError());
     return 0;
@@ -800,6 +805,9 @@ static int launch_dct(fdlp_plan* p, const fdlp_batch* b, double* out, int out_ld
   if (b->wav_dtype == FDLP_WAV_INT16) {
     if (p->dct_fp64) dct_segments_kernel<double, int16_t><<<grid, block, p->dct_smem, st>>>(a);
     else dct_segments_kernel<float, int16_t><<<grid, block, p->dct_smem, st>>>(a);
+  } else if (b->wav_dtype == FDLP_WAV_FLOAT64) {
+    if (p->dct_fp64) dct_segments_kernel<double, double><<<grid, block, p->dct_smem, st>>>(a);
+    else dct_segments_kernel<float, double><<<grid, block, p->dct_smem, st>>>(a);
   } else {
     if (p->dct_fp64) dct_segments_kernel<double, float><<<grid, block, p->dct_smem, st>>>(a);
     else dct_segments_kernel<float, float><<<grid, block, p->dct_smem, st>>>(a);
@@ -957,9 +965,12 @@ static int check_batch(const fdlp_plan* p, const fdlp_batch* b) {
   if (b->n_utt < 0 || b->n_seg < 0 || b->n_frames < 0) return set_err(FDLP_E_ARG, "negative batch sizes%s", "");
   if (b->n_seg > 0 && (!b->wav || !b->utt_wav_off || !b->utt_seg_off || !b->seg_utt))
     return set_err(FDLP_E_ARG, "null batch pointer%s", "");
-  if (b->wav_dtype != FDLP_WAV_INT16 && b->wav_dtype != FDLP_WAV_FLOAT32) return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
+  if (b->wav_dtype != FDLP_WAV_INT16 && b->wav_dtype != FDLP_WAV_FLOAT32 && b->wav_dtype != FDLP_WAV_FLOAT64)
+    return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
   if (b->noise_mode != FDLP_NOISE_NONE && (!b->noise || !b->utt_noise_off || !b->utt_snr_db))
     return set_err(FDLP_E_ARG, "noise mixing requested without noise arrays%s", "");
+  if (b->noise_mode != FDLP_NOISE_NONE && b->wav_dtype == FDLP_WAV_FLOAT64)
+    return set_err(FDLP_E_ARG, "float64 samples are the output of fdlp_reverb_forward, which mixes the noise itself%s", "");
   return 0;
 }
 
@@ -1484,6 +1495,179 @@ extern "C" int fdlp_diff_filter(const void* wav, int32_t wav_dtype, const int64_
   const long long bx = std::min<long long>((max_len + 255) / 256, 1024);
   diff_fir_kernel<<<dim3((unsigned)bx, (unsigned)n_utt), 256, 0, (cudaStream_t)stream>>>(a);
   FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
+// ================================================================ --add_reverb (features.py:110-115)
+struct fdlp_reverb_plan {
+  int R = 0, B = 0, F = 0, logF = 0, P = 0;
+  size_t smem = 0;
+  double2* d_tw = nullptr;
+  double2* d_H = nullptr;
+  // scratch, grown on demand
+  int cap_blk = 0, cap_utt = 0;
+  double2* d_X = nullptr;
+  double2* d_O = nullptr;
+  double* d_full = nullptr;
+  double* d_pmax = nullptr;
+  int32_t* d_parg = nullptr;
+  double* d_alpha = nullptr;
+  bool profiling = false;
+  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+};
+
+static void reverb_free(fdlp_reverb_plan* p) {
+  if (!p) return;
+  cudaFree(p->d_tw); cudaFree(p->d_H); cudaFree(p->d_X); cudaFree(p->d_O); cudaFree(p->d_full);
+  cudaFree(p->d_pmax); cudaFree(p->d_parg); cudaFree(p->d_alpha);
+  for (auto& e : p->ev) if (e) cudaEventDestroy(e);
+  delete p;
+}
+
+static void reverb_fill(const fdlp_reverb_plan* p, RvArgs& a) {
+  memset(&a, 0, sizeof(a));
+  a.R = p->R; a.B = p->B; a.F = p->F; a.logF = p->logF; a.P = p->P; a.tw = p->d_tw; a.H = p->d_H;
+  a.X = p->d_X; a.O = p->d_O; a.full = p->d_full; a.part_max = p->d_pmax; a.part_arg = p->d_parg;
+}
+
+extern "C" int fdlp_reverb_plan_create(const double* rir, int32_t R, int32_t block, fdlp_reverb_plan** out) {
+  if (!rir || !out || R < 1) return set_err(FDLP_E_ARG, "invalid impulse response%s", "");
+  if (block != 0 && (block < 64 || block > 4096 || (block & (block - 1))))
+    return set_err(FDLP_E_ARG, "block must be 0 (auto) or a power of two in 64..4096%s", "");
+  fdlp_reverb_plan* p = new (std::nothrow) fdlp_reverb_plan();
+  if (!p) return set_err(FDLP_E_NOMEM, "out of host memory%s", "");
+  p->R = R;
+  int B = block;
+  if (B == 0) { B = 64; while (B < R && B < 4096) B <<= 1; }
+  p->B = B; p->F = 2 * B; p->P = (R + B - 1) / B;
+  p->logF = 0;
+  while ((1 << p->logF) < p->F) ++p->logF;
+  const int na = p->F >> 6;
+  std::vector<double2> tw(na + 64);
+  for (int a = 0; a < na; ++a) {
+    const double th = -2.0 * M_PI * (64.0 * a) / p->F;
+    tw[a] = make_double2(cos(th), sin(th));
+  }
+  for (int b = 0; b < 64; ++b) {
+    const double th = -2.0 * M_PI * b / p->F;
+    tw[na + b] = make_double2(cos(th), sin(th));
+  }
+  p->smem = (size_t)p->F * sizeof(double2) + tw.size() * sizeof(double2);
+  int rc = upload(&p->d_tw, tw);
+  if (rc) { reverb_free(p); return rc; }
+  cudaError_t e = raise_smem_limit(rv_fwd_kernel<int16_t>, p->smem);
+  if (e == cudaSuccess) e = raise_smem_limit(rv_fwd_kernel<float>, p->smem);
+  if (e == cudaSuccess) e = raise_smem_limit(rv_conv_kernel, p->smem);
+  if (e == cudaSuccess) e = raise_smem_limit(rv_corr_kernel, p->smem);
+  if (e == cudaSuccess) e = raise_smem_limit(rv_rir_kernel, p->smem);
+  if (e != cudaSuccess) { reverb_free(p); return set_err(FDLP_E_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
+  double* d_rir = nullptr;
+  std::vector<double> h(rir, rir + R);
+  if ((rc = upload(&d_rir, h))) { reverb_free(p); return rc; }
+  if (cudaMalloc((void**)&p->d_H, (size_t)p->P * p->F * sizeof(double2)) != cudaSuccess) {
+    cudaFree(d_rir); reverb_free(p); return set_err(FDLP_E_NOMEM, "out of device memory%s", "");
+  }
+  RvArgs a;
+  reverb_fill(p, a);
+  rv_rir_kernel<<<p->P, kRvThreads, p->smem>>>(a, d_rir, p->d_H);
+  e = cudaDeviceSynchronize();
+  cudaFree(d_rir);
+  if (e != cudaSuccess) { reverb_free(p); return set_err(FDLP_E_CUDA, "impulse-response spectra: %s", cudaGetErrorString(e)); }
+  *out = p;
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_reverb_plan_destroy(fdlp_reverb_plan* p) {
+  reverb_free(p);
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_reverb_plan_get_block(const fdlp_reverb_plan* p, int32_t* block, int32_t* partitions) {
+  if (!p || !block) return set_err(FDLP_E_ARG, "null argument%s", "");
+  *block = p->B;
+  if (partitions) *partitions = p->P;
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_reverb_plan_set_profiling(fdlp_reverb_plan* p, int32_t enable) {
+  if (!p) return set_err(FDLP_E_ARG, "null argument%s", "");
+  if (enable && !p->ev[0])
+    for (auto& e : p->ev) FDLP_CUDA(cudaEventCreate(&e));
+  p->profiling = enable != 0;
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_reverb_plan_get_kernel_ms(fdlp_reverb_plan* p, float* out4) {
+  if (!p || !out4 || !p->ev[0]) return set_err(FDLP_E_ARG, "profiling was not enabled%s", "");
+  FDLP_CUDA(cudaEventSynchronize(p->ev[4]));
+  for (int i = 0; i < 4; ++i) FDLP_CUDA(cudaEventElapsedTime(&out4[i], p->ev[i], p->ev[i + 1]));
+  return FDLP_OK;
+}
+
+extern "C" int64_t fdlp_reverb_plan_scratch_bytes(const fdlp_reverb_plan* p, int32_t n_blk) {
+  if (!p) return 0;
+  return (int64_t)n_blk * ((int64_t)2 * p->F * sizeof(double2) + (int64_t)p->B * sizeof(double));
+}
+
+extern "C" int fdlp_reverb_forward(fdlp_reverb_plan* p, const fdlp_reverb_batch* b, void* stream) {
+  if (!p || !b) return set_err(FDLP_E_ARG, "null argument%s", "");
+  if (b->n_utt < 0 || b->n_blk < 0) return set_err(FDLP_E_ARG, "negative batch sizes%s", "");
+  if (b->n_utt == 0 || b->n_blk == 0) return FDLP_OK;
+  if (!b->wav || !b->utt_wav_off || !b->utt_blk_off || !b->blk_utt || !b->out)
+    return set_err(FDLP_E_ARG, "null batch pointer%s", "");
+  if (b->wav_dtype != FDLP_WAV_INT16 && b->wav_dtype != FDLP_WAV_FLOAT32) return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
+  if (b->out_dtype != FDLP_WAV_FLOAT32 && b->out_dtype != FDLP_WAV_FLOAT64) return set_err(FDLP_E_ARG, "bad output dtype%s", "");
+  if (b->noise_mode != FDLP_NOISE_NONE && (!b->noise || !b->utt_noise_off || !b->utt_snr_db))
+    return set_err(FDLP_E_ARG, "noise mixing requested without noise arrays%s", "");
+  if (b->n_utt > 65535) return set_err(FDLP_E_ARG, "too many utterances in one call%s", "");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (b->n_blk > p->cap_blk) {
+    FDLP_CUDA(cudaStreamSynchronize(st));
+    cudaFree(p->d_X); cudaFree(p->d_O); cudaFree(p->d_full);
+    p->d_X = p->d_O = nullptr; p->d_full = nullptr; p->cap_blk = 0;
+    FDLP_CUDA(cudaMalloc((void**)&p->d_X, (size_t)b->n_blk * p->F * sizeof(double2)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_O, (size_t)b->n_blk * p->F * sizeof(double2)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_full, (size_t)b->n_blk * p->B * sizeof(double)));
+    p->cap_blk = b->n_blk;
+  }
+  if (b->n_utt > p->cap_utt) {
+    FDLP_CUDA(cudaStreamSynchronize(st));
+    cudaFree(p->d_pmax); cudaFree(p->d_parg); cudaFree(p->d_alpha);
+    p->d_pmax = nullptr; p->d_parg = nullptr; p->d_alpha = nullptr; p->cap_utt = 0;
+    FDLP_CUDA(cudaMalloc((void**)&p->d_pmax, (size_t)b->n_utt * p->P * sizeof(double)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_parg, (size_t)b->n_utt * p->P * sizeof(int32_t)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_alpha, (size_t)b->n_utt * sizeof(double)));
+    p->cap_utt = b->n_utt;
+  }
+  RvArgs a;
+  reverb_fill(p, a);
+  a.wav = b->wav; a.wav_dtype = b->wav_dtype; a.utt_wav_off = b->utt_wav_off;
+  a.utt_blk_off = b->utt_blk_off; a.blk_utt = b->blk_utt;
+  a.out = b->out; a.out_dtype = b->out_dtype; a.ind = b->ind; a.out_len = b->out_len;
+  const bool prof = p->profiling;
+  if (b->noise_mode != FDLP_NOISE_NONE) {
+    NoiseArgs n;
+    n.wav = b->wav; n.wav_dtype = b->wav_dtype; n.utt_wav_off = b->utt_wav_off; n.noise = (const int16_t*)b->noise;
+    n.utt_noise_off = b->utt_noise_off; n.utt_snr_db = b->utt_snr_db; n.utt_alpha = p->d_alpha; n.mode = b->noise_mode;
+    noise_alpha_kernel<<<b->n_utt, kNoiseThreads, 0, st>>>(n);
+    FDLP_CUDA(cudaGetLastError());
+    a.noise = (const int16_t*)b->noise; a.utt_noise_off = b->utt_noise_off; a.utt_alpha = p->d_alpha;
+  }
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[0], st));
+  if (b->wav_dtype == FDLP_WAV_INT16) rv_fwd_kernel<int16_t><<<b->n_blk, kRvThreads, p->smem, st>>>(a);
+  else rv_fwd_kernel<float><<<b->n_blk, kRvThreads, p->smem, st>>>(a);
+  FDLP_CUDA(cudaGetLastError());
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[1], st));
+  rv_conv_kernel<<<b->n_blk, kRvThreads, p->smem, st>>>(a);
+  FDLP_CUDA(cudaGetLastError());
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[2], st));
+  rv_corr_kernel<<<dim3((unsigned)p->P, (unsigned)b->n_utt), kRvThreads, p->smem, st>>>(a);
+  FDLP_CUDA(cudaGetLastError());
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[3], st));
+  const long long bx = std::max<long long>(1, std::min<long long>((b->max_len + 1023) / 1024, 64));
+  rv_align_kernel<<<dim3((unsigned)bx, (unsigned)b->n_utt), 256, 0, st>>>(a);
+  FDLP_CUDA(cudaGetLastError());
+  if (prof) FDLP_CUDA(cudaEventRecord(p->ev[4], st));
   return FDLP_OK;
 }
 

@@ -375,7 +375,8 @@ class FdlpExtractor:
         b = L.FdlpBatch()
         d = lay.dev
         b.wav = wav_dev.data_ptr()
-        b.wav_dtype = L.FDLP_WAV_INT16 if wav_dev.dtype == torch.int16 else L.FDLP_WAV_FLOAT32
+        b.wav_dtype = {torch.int16: L.FDLP_WAV_INT16, torch.float32: L.FDLP_WAV_FLOAT32,
+                       torch.float64: L.FDLP_WAV_FLOAT64}[wav_dev.dtype]
         b.n_utt, b.n_seg, b.n_frames, b.max_utt_frames = lay.n_utt, lay.n_seg, lay.n_frames, lay.max_utt_frames
         b.utt_wav_off = d["utt_wav_off"].data_ptr()
         b.utt_seg_off = d["utt_seg_off"].data_ptr()
@@ -506,16 +507,34 @@ class FdlpExtractor:
         cur.wait_event(fin)
         return feats, feats_host, status
 
+    def reverberate(self, wav_dev: torch.Tensor, lay: BatchLayout, reverb, noise_dev=None):
+        """--add_reverb (computeFDLPSpectrogram.py:168-170): noise mixing (if any) then addReverb, on the device.
+        `reverb` is a reverb.Reverberator or the float64 impulse response.  Returns (float64 packed batch,
+        per-utterance lengths): an utterance comes back one sample shorter in the reference's corner case
+        indM == len(rir), and the packed batch is then re-packed to the new lengths."""
+        from .reverb import Reverberator
+        rv = reverb if isinstance(reverb, Reverberator) else Reverberator(reverb, device=self.device)
+        lay.to(self.device)
+        out, _, out_len = rv.forward_packed(wav_dev, lay.lengths, lay.dev["utt_wav_off"], noise_dev)
+        n = out_len.cpu().numpy()
+        if np.array_equal(n, lay.lengths):
+            return out, lay.lengths
+        parts = [out[int(lay.utt_wav_off[u]):int(lay.utt_wav_off[u]) + int(n[u])] for u in range(lay.n_utt)]
+        return torch.cat(parts), n
+
     def __call__(self, wavs: Sequence[Union[np.ndarray, torch.Tensor]], jitter=None,
                  noise: Optional[NoiseSpec] = None, cmvn: Optional[torch.Tensor] = None,
-                 return_status: bool = False):
+                 return_status: bool = False, reverb=None):
         """Extract FDLP spectrograms for a list of mono waveforms.  Returns a list of [Fr_u, nfilters]
-        float32 device tensors (views into one buffer), in input order."""
+        float32 device tensors (views into one buffer), in input order.  `reverb`: impulse response (float64 array,
+        reverb.load_rir) or a reverb.Reverberator for --add_reverb."""
         if len(wavs) == 0:  # an empty scp shard: nothing to extract
             empty_status = torch.zeros(0, dtype=torch.int32, device=self.device)
             return ([], empty_status) if return_status else []
         host, lengths = self.pack(wavs)
-        lay = self.layout(lengths, jitter)
+        # the overlap-add jitter draws belong to the final lengths: with reverberation the bookkeeping of the
+        # augmentation stage uses a throw-away layout
+        lay = self.layout(lengths, jitter if reverb is None else 0)
         wav_dev = host.to(self.device, non_blocking=True)
         if isinstance(noise, str):
             if noise != "diff":
@@ -523,6 +542,10 @@ class FdlpExtractor:
             wav_dev = self.diff_filter(wav_dev, lay)
             noise = None
         noise_dev = self._noise_to_device(noise, lay)
+        if reverb is not None:
+            wav_dev, lengths = self.reverberate(wav_dev, lay, reverb, noise_dev)
+            noise_dev = None
+            lay = self.layout(lengths, jitter)
         feats, status = self.forward_packed(wav_dev, lay, cmvn=cmvn, noise_dev=noise_dev)
         outs = [feats[int(lay.utt_frame_off[u]):int(lay.utt_frame_off[u + 1])] for u in range(lay.n_utt)]
         if return_status:

@@ -55,7 +55,7 @@ def test_fdlp_matches_reference_golden(name):
     elif add_noise and add_noise != "clean":
         nm, snr = add_noise.split(",")
         noise = NoiseSpec(samples=c["noise"]["data"], snr_db=float(snr), rand=meta["seed"])
-    outs, st = ex([c["x"]], jitter=[meta["seed"]], noise=noise, return_status=True)
+    outs, st = ex([c["x"]], jitter=[meta["seed"]], noise=noise, return_status=True, reverb=c["rir"])
     assert int(st.cpu()[0]) == 0
     assert_feats_close(outs[0].cpu().numpy(), c["feats"])
 

@@ -10,6 +10,7 @@ import pytest
 
 from oracle import fdlp as ofdlp
 from oracle import mel as omel
+from oracle import reverb as oreverb
 from tests.golden_util import FDLP_DEFAULTS, MEL_DEFAULTS, golden_cases, load_case, split_params
 
 FLOOR = np.log(1e-14)
@@ -27,6 +28,8 @@ def oracle_fdlp_from_case(c):
             name, snr = add_noise.split(",")
             rand = np.random.RandomState(meta["seed"]).rand()
             x = ofdlp.add_noise_to_wav(x, c["noise"]["data"], float(snr), rand=rand)
+    if c["rir"] is not None:
+        x = oreverb.add_reverb(x, c["rir"])
     return ofdlp.fdlp_spectrogram(x, lifter=lifter, rng=random.Random(meta["seed"]), **kw)
 
 
@@ -134,3 +137,14 @@ def test_mfcc_oracle_matches_reference(name):
     out = omfcc.mfcc_features(x, **kw)
     assert out.shape == z["feats"].shape
     np.testing.assert_allclose(out, z["feats"], rtol=0, atol=1e-10)
+
+
+@pytest.mark.parametrize("name", golden_cases("reverb"))
+def test_reverb_oracle_matches_reference(name):
+    """addReverb (features.py:110-115): alignment index exact, reverberated waveform to float64 round-off."""
+    c = load_case(name)
+    out, ind = oreverb.add_reverb(c["x"], c["rir"], return_index=True)
+    ref = c["z"]["out"]
+    assert ind == c["meta"]["ind"]
+    assert out.shape == ref.shape
+    np.testing.assert_allclose(out, ref, rtol=0, atol=1e-9 * max(1.0, np.abs(ref).max()))
