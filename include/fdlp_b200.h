@@ -224,9 +224,11 @@ int fdlp_diff_filter(const void* wav /*dev, packed*/, int32_t wav_dtype, const i
  *      computeMfccFeatures.py:118-120): out = convolve(sig, rir) (full), xxc = correlate(sig, out, 'valid'),
  *      indM = len(xxc) - argmax(xxc), result = out[indM : indM + len(sig)], per utterance, after the optional noise
  *      mixing (same noise arrays as fdlp_batch).  `rir` is the HOST float64 impulse response as the reference
- *      forms it (rir[:, 1] / 2^15, :76-87).  The batch is cut into blocks of `block` samples
- *      (fdlp_reverb_plan_get_block): utt_blk_off[u+1] - utt_blk_off[u] = ceil((T_u + R - 1) / block), blk_utt = owner
- *      of each block, both computed by the host like utt_seg_off / seg_utt.  The result has the packed layout of the
+ *      forms it (rir[:, 1] / 2^15, :76-87).  The convolution runs over blocks of `block` samples
+ *      (fdlp_reverb_plan_get_block), two blocks to a complex transform: utterance u has
+ *      D_u = ceil(ceil((T_u + R - 1) / block) / 2) block pairs and ceil(D_u / pairs_per_cta) convolution CTAs;
+ *      utt_pair_off / pair_utt and utt_conv_off / conv_utt are their prefix sums and owner tables, computed by the
+ *      host like utt_seg_off / seg_utt.  The result has the packed layout of the
  *      input, float64 (for fdlp_forward with FDLP_WAV_FLOAT64) or float32 (mel / MFCC paths); out_len[u] is T_u, or
  *      T_u - 1 in the reference's corner case indM == R (the slice runs off the end of the convolution). ---- */
 typedef struct fdlp_reverb_plan fdlp_reverb_plan;
@@ -236,9 +238,12 @@ typedef struct {
   int32_t n_utt;
   const int64_t* utt_wav_off;   /* dev [n_utt+1] */
   int64_t max_len;              /* longest utterance, samples */
-  int32_t n_blk;                /* total blocks */
-  const int32_t* utt_blk_off;   /* dev [n_utt+1] */
-  const int32_t* blk_utt;       /* dev [n_blk] */
+  int32_t n_pair;               /* total block pairs */
+  const int32_t* utt_pair_off;  /* dev [n_utt+1] */
+  const int32_t* pair_utt;      /* dev [n_pair] */
+  int32_t n_conv;               /* total convolution CTAs */
+  const int32_t* utt_conv_off;  /* dev [n_utt+1] */
+  const int32_t* conv_utt;      /* dev [n_conv] */
   int32_t noise_mode;           /* FDLP_NOISE_* ; the mix happens before the reverberation (:158-170) */
   const void* noise;
   const int64_t* utt_noise_off;
@@ -251,11 +256,11 @@ typedef struct {
 
 int fdlp_reverb_plan_create(const double* rir /*host [R]*/, int32_t R, int32_t block /*0: auto*/, fdlp_reverb_plan** out_plan);
 int fdlp_reverb_plan_destroy(fdlp_reverb_plan* plan);
-int fdlp_reverb_plan_get_block(const fdlp_reverb_plan* plan, int32_t* block, int32_t* partitions);
+int fdlp_reverb_plan_get_block(const fdlp_reverb_plan* plan, int32_t* block, int32_t* partitions, int32_t* pairs_per_cta);
 int fdlp_reverb_plan_set_profiling(fdlp_reverb_plan* plan, int32_t enable);
 /* CUDA-event durations of the most recent profiled forward: window spectra, convolution, correlation, alignment */
 int fdlp_reverb_plan_get_kernel_ms(fdlp_reverb_plan* plan, float* out4);
-int64_t fdlp_reverb_plan_scratch_bytes(const fdlp_reverb_plan* plan, int32_t n_blk);
+int64_t fdlp_reverb_plan_scratch_bytes(const fdlp_reverb_plan* plan, int32_t n_pair, int32_t n_utt);
 int fdlp_reverb_forward(fdlp_reverb_plan* plan, const fdlp_reverb_batch* batch, void* stream);
 
 /* ---- MFCC features (computeMfccFeatures.py:111-131: signal / 2^15 [+ noise], Hamming frames, the reference's

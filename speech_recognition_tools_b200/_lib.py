@@ -80,7 +80,8 @@ class MfccBatch(C.Structure):
 class ReverbBatch(C.Structure):
     _fields_ = [
         ("wav", C.c_void_p), ("wav_dtype", C.c_int32), ("n_utt", C.c_int32), ("utt_wav_off", C.c_void_p),
-        ("max_len", C.c_int64), ("n_blk", C.c_int32), ("utt_blk_off", C.c_void_p), ("blk_utt", C.c_void_p),
+        ("max_len", C.c_int64), ("n_pair", C.c_int32), ("utt_pair_off", C.c_void_p), ("pair_utt", C.c_void_p),
+        ("n_conv", C.c_int32), ("utt_conv_off", C.c_void_p), ("conv_utt", C.c_void_p),
         ("noise_mode", C.c_int32), ("noise", C.c_void_p), ("utt_noise_off", C.c_void_p), ("utt_snr_db", C.c_void_p),
         ("out", C.c_void_p), ("out_dtype", C.c_int32), ("ind", C.c_void_p), ("out_len", C.c_void_p),
     ]
@@ -118,10 +119,10 @@ SYMBOLS = [
     ("fdlp_diff_filter", C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),
     ("fdlp_reverb_plan_create", C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
     ("fdlp_reverb_plan_destroy", C.c_int, [C.c_void_p]),
-    ("fdlp_reverb_plan_get_block", C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    ("fdlp_reverb_plan_get_block", C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     ("fdlp_reverb_plan_set_profiling", C.c_int, [C.c_void_p, C.c_int32]),
     ("fdlp_reverb_plan_get_kernel_ms", C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
-    ("fdlp_reverb_plan_scratch_bytes", C.c_int64, [C.c_void_p, C.c_int32]),
+    ("fdlp_reverb_plan_scratch_bytes", C.c_int64, [C.c_void_p, C.c_int32, C.c_int32]),
     ("fdlp_reverb_forward", C.c_int, [C.c_void_p, C.POINTER(ReverbBatch), C.c_void_p]),
     ("fdlp_synth_white", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_uint64, C.c_int32,
                                    C.c_void_p]),

@@ -1501,6 +1501,7 @@ extern "C" int fdlp_diff_filter(const void* wav, int32_t wav_dtype, const int64_
 // ================================================================ --add_reverb (features.py:110-115)
 struct fdlp_reverb_plan {
   int R = 0, B = 0, F = 0, logF = 0, P = 0;
+  int conv_m = 2;  // block pairs per convolution CTA
   size_t smem = 0;
   double2* d_tw = nullptr;
   double2* d_H = nullptr;
@@ -1557,7 +1558,12 @@ extern "C" int fdlp_reverb_plan_create(const double* rir, int32_t R, int32_t blo
   if (rc) { reverb_free(p); return rc; }
   cudaError_t e = raise_smem_limit(rv_fwd_kernel<int16_t>, p->smem);
   if (e == cudaSuccess) e = raise_smem_limit(rv_fwd_kernel<float>, p->smem);
-  if (e == cudaSuccess) e = raise_smem_limit(rv_conv_kernel, p->smem);
+  if (const char* m = getenv("FDLP_RV_CONVM")) p->conv_m = atoi(m) == 1 ? 1 : 2;
+#define RV_CONV_SMEM(BINS)                                                                 \
+  if (e == cudaSuccess) e = raise_smem_limit(rv_conv_kernel<BINS, 1>, p->smem);           \
+  if (e == cudaSuccess) e = raise_smem_limit(rv_conv_kernel<BINS, 2>, p->smem);
+  RV_CONV_SMEM(1) RV_CONV_SMEM(2) RV_CONV_SMEM(4) RV_CONV_SMEM(8) RV_CONV_SMEM(16)
+#undef RV_CONV_SMEM
   if (e == cudaSuccess) e = raise_smem_limit(rv_corr_kernel, p->smem);
   if (e == cudaSuccess) e = raise_smem_limit(rv_rir_kernel, p->smem);
   if (e != cudaSuccess) { reverb_free(p); return set_err(FDLP_E_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
@@ -1582,10 +1588,12 @@ extern "C" int fdlp_reverb_plan_destroy(fdlp_reverb_plan* p) {
   return FDLP_OK;
 }
 
-extern "C" int fdlp_reverb_plan_get_block(const fdlp_reverb_plan* p, int32_t* block, int32_t* partitions) {
+extern "C" int fdlp_reverb_plan_get_block(const fdlp_reverb_plan* p, int32_t* block, int32_t* partitions,
+                                          int32_t* pairs_per_cta) {
   if (!p || !block) return set_err(FDLP_E_ARG, "null argument%s", "");
   *block = p->B;
   if (partitions) *partitions = p->P;
+  if (pairs_per_cta) *pairs_per_cta = p->conv_m;
   return FDLP_OK;
 }
 
@@ -1604,16 +1612,17 @@ extern "C" int fdlp_reverb_plan_get_kernel_ms(fdlp_reverb_plan* p, float* out4) 
   return FDLP_OK;
 }
 
-extern "C" int64_t fdlp_reverb_plan_scratch_bytes(const fdlp_reverb_plan* p, int32_t n_blk) {
+extern "C" int64_t fdlp_reverb_plan_scratch_bytes(const fdlp_reverb_plan* p, int32_t n_pair, int32_t n_utt) {
   if (!p) return 0;
-  return (int64_t)n_blk * ((int64_t)2 * p->F * sizeof(double2) + (int64_t)p->B * sizeof(double));
+  return ((int64_t)2 * n_pair + (int64_t)n_utt * (p->P - 1)) * p->F * (int64_t)sizeof(double2) +
+         (int64_t)2 * n_pair * p->B * (int64_t)sizeof(double);
 }
 
 extern "C" int fdlp_reverb_forward(fdlp_reverb_plan* p, const fdlp_reverb_batch* b, void* stream) {
   if (!p || !b) return set_err(FDLP_E_ARG, "null argument%s", "");
-  if (b->n_utt < 0 || b->n_blk < 0) return set_err(FDLP_E_ARG, "negative batch sizes%s", "");
-  if (b->n_utt == 0 || b->n_blk == 0) return FDLP_OK;
-  if (!b->wav || !b->utt_wav_off || !b->utt_blk_off || !b->blk_utt || !b->out)
+  if (b->n_utt < 0 || b->n_pair < 0 || b->n_conv < 0) return set_err(FDLP_E_ARG, "negative batch sizes%s", "");
+  if (b->n_utt == 0 || b->n_pair == 0) return FDLP_OK;
+  if (!b->wav || !b->utt_wav_off || !b->utt_pair_off || !b->pair_utt || !b->utt_conv_off || !b->conv_utt || !b->out)
     return set_err(FDLP_E_ARG, "null batch pointer%s", "");
   if (b->wav_dtype != FDLP_WAV_INT16 && b->wav_dtype != FDLP_WAV_FLOAT32) return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
   if (b->out_dtype != FDLP_WAV_FLOAT32 && b->out_dtype != FDLP_WAV_FLOAT64) return set_err(FDLP_E_ARG, "bad output dtype%s", "");
@@ -1621,28 +1630,26 @@ extern "C" int fdlp_reverb_forward(fdlp_reverb_plan* p, const fdlp_reverb_batch*
     return set_err(FDLP_E_ARG, "noise mixing requested without noise arrays%s", "");
   if (b->n_utt > 65535) return set_err(FDLP_E_ARG, "too many utterances in one call%s", "");
   cudaStream_t st = (cudaStream_t)stream;
-  if (b->n_blk > p->cap_blk) {
+  const size_t n_rows = (size_t)b->n_pair + (size_t)b->n_utt * (p->P - 1);
+  if (b->n_pair > p->cap_blk || b->n_utt > p->cap_utt) {
     FDLP_CUDA(cudaStreamSynchronize(st));
-    cudaFree(p->d_X); cudaFree(p->d_O); cudaFree(p->d_full);
-    p->d_X = p->d_O = nullptr; p->d_full = nullptr; p->cap_blk = 0;
-    FDLP_CUDA(cudaMalloc((void**)&p->d_X, (size_t)b->n_blk * p->F * sizeof(double2)));
-    FDLP_CUDA(cudaMalloc((void**)&p->d_O, (size_t)b->n_blk * p->F * sizeof(double2)));
-    FDLP_CUDA(cudaMalloc((void**)&p->d_full, (size_t)b->n_blk * p->B * sizeof(double)));
-    p->cap_blk = b->n_blk;
-  }
-  if (b->n_utt > p->cap_utt) {
-    FDLP_CUDA(cudaStreamSynchronize(st));
-    cudaFree(p->d_pmax); cudaFree(p->d_parg); cudaFree(p->d_alpha);
-    p->d_pmax = nullptr; p->d_parg = nullptr; p->d_alpha = nullptr; p->cap_utt = 0;
-    FDLP_CUDA(cudaMalloc((void**)&p->d_pmax, (size_t)b->n_utt * p->P * sizeof(double)));
-    FDLP_CUDA(cudaMalloc((void**)&p->d_parg, (size_t)b->n_utt * p->P * sizeof(int32_t)));
-    FDLP_CUDA(cudaMalloc((void**)&p->d_alpha, (size_t)b->n_utt * sizeof(double)));
-    p->cap_utt = b->n_utt;
+    cudaFree(p->d_X); cudaFree(p->d_O); cudaFree(p->d_full); cudaFree(p->d_pmax); cudaFree(p->d_parg); cudaFree(p->d_alpha);
+    p->d_X = p->d_O = nullptr; p->d_full = nullptr; p->d_pmax = nullptr; p->d_parg = nullptr; p->d_alpha = nullptr;
+    p->cap_blk = p->cap_utt = 0;
+    const int np = std::max(b->n_pair, p->cap_blk), nu = std::max(b->n_utt, p->cap_utt);
+    FDLP_CUDA(cudaMalloc((void**)&p->d_X, ((size_t)np + (size_t)nu * (p->P - 1)) * p->F * sizeof(double2)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_O, (size_t)np * p->F * sizeof(double2)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_full, (size_t)2 * np * p->B * sizeof(double)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_pmax, (size_t)nu * p->P * sizeof(double)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_parg, (size_t)nu * p->P * sizeof(int32_t)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_alpha, (size_t)nu * sizeof(double)));
+    p->cap_blk = np; p->cap_utt = nu;
   }
   RvArgs a;
   reverb_fill(p, a);
   a.wav = b->wav; a.wav_dtype = b->wav_dtype; a.utt_wav_off = b->utt_wav_off;
-  a.utt_blk_off = b->utt_blk_off; a.blk_utt = b->blk_utt;
+  a.utt_pair_off = b->utt_pair_off; a.pair_utt = b->pair_utt; a.n_pair = b->n_pair;
+  a.utt_conv_off = b->utt_conv_off; a.conv_utt = b->conv_utt;
   a.out = b->out; a.out_dtype = b->out_dtype; a.ind = b->ind; a.out_len = b->out_len;
   const bool prof = p->profiling;
   if (b->noise_mode != FDLP_NOISE_NONE) {
@@ -1654,11 +1661,23 @@ extern "C" int fdlp_reverb_forward(fdlp_reverb_plan* p, const fdlp_reverb_batch*
     a.noise = (const int16_t*)b->noise; a.utt_noise_off = b->utt_noise_off; a.utt_alpha = p->d_alpha;
   }
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[0], st));
-  if (b->wav_dtype == FDLP_WAV_INT16) rv_fwd_kernel<int16_t><<<b->n_blk, kRvThreads, p->smem, st>>>(a);
-  else rv_fwd_kernel<float><<<b->n_blk, kRvThreads, p->smem, st>>>(a);
+  if (b->wav_dtype == FDLP_WAV_INT16) rv_fwd_kernel<int16_t><<<(unsigned)n_rows, kRvThreads, p->smem, st>>>(a);
+  else rv_fwd_kernel<float><<<(unsigned)n_rows, kRvThreads, p->smem, st>>>(a);
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[1], st));
-  rv_conv_kernel<<<b->n_blk, kRvThreads, p->smem, st>>>(a);
+  {
+    const int bins = std::max(1, p->F / kRvThreads);
+#define RV_CONV_LAUNCH(BINS)                                                                              \
+    case BINS:                                                                                            \
+      if (p->conv_m == 2) rv_conv_kernel<BINS, 2><<<b->n_conv, kRvThreads, p->smem, st>>>(a);             \
+      else rv_conv_kernel<BINS, 1><<<b->n_conv, kRvThreads, p->smem, st>>>(a);                            \
+      break;
+    switch (bins) {
+      RV_CONV_LAUNCH(1) RV_CONV_LAUNCH(2) RV_CONV_LAUNCH(4) RV_CONV_LAUNCH(8) RV_CONV_LAUNCH(16)
+      default: return set_err(FDLP_E_UNSUPPORTED, "unsupported transform length%s", "");
+    }
+#undef RV_CONV_LAUNCH
+  }
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[2], st));
   rv_corr_kernel<<<dim3((unsigned)p->P, (unsigned)b->n_utt), kRvThreads, p->smem, st>>>(a);

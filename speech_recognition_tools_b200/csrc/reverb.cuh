@@ -19,6 +19,11 @@
 //   rv_corr_kernel   C_q  = sum_c conj(O_c) . X_{c-q} ; xxc at lags d = qB + B - e is Re IFFT(C_q)[e] / F, e = 1..B ;
 //                    per-(utterance, q) maximum
 //   rv_align_kernel  argmax over q, out[n] = full[indM + n]
+// Everything transformed is real, so two blocks share one complex transform: with D = half the blocks of the
+// utterance, Z_j = X_j + i X_{j+D} and OO_b = O_b + i O_{b+D}.  sum_q Z_{b-q} H_q inverts to block b in the real and
+// block b + D in the imaginary part (H_q is the spectrum of a real sequence); sum_c conj(OO_c) Z_{c-q} inverts to the
+// full correlation sum in the real part (conj(O_c) X_{c-q} + conj(O_{c+D}) X_{c+D-q}, both wanted) with the cross terms
+// of the packing in the imaginary part, which is dropped.  Nothing is ever unpacked.
 // float64 throughout: the FDLP path needs the waveform to better than 32 bits (NOTES_r01.md), and for int16 input
 // with an int16 / 2^15 impulse response the exact result is representable, so the error is the FFT's (1e-15 of peak).
 // Bound: HBM/L2 traffic of the spectra (16 F bytes per block and pass), see DESIGN.md section 4.6.
@@ -36,14 +41,17 @@ struct RvArgs {
   const int16_t* noise;         // optional noise mixing at load (features.py:24-31), as in the framing kernel
   const int64_t* utt_noise_off;
   const double* utt_alpha;
-  const int32_t* utt_blk_off;   // [n_utt+1] first block of each utterance; nb_u = ceil((T_u + R - 1) / B)
-  const int32_t* blk_utt;       // [n_blk]
+  const int32_t* utt_pair_off;  // [n_utt+1] first pair of each utterance; D_u = ceil(ceil((T_u + R - 1) / B) / 2)
+  const int32_t* pair_utt;      // [n_pair]
+  const int32_t* utt_conv_off;  // [n_utt+1] first convolution CTA of each utterance; ceil(D_u / pairs_per_cta) each
+  const int32_t* conv_utt;      // [n_conv]
+  int n_pair;
   int R, B, F, logF, P;         // P = ceil(R / B) partitions of the impulse response
   const double2* tw;            // split twiddles: w_F^k = tw[k >> 6] * tw[F/64 + (k & 63)]
   const double2* H;             // [P, F] spectra of the impulse-response partitions
-  double2* X;                   // [n_blk, F]
-  double2* O;                   // [n_blk, F]
-  double* full;                 // [n_blk * B]
+  double2* X;                   // [n_pair + n_utt (P-1), F] packed window spectra Z_j
+  double2* O;                   // [n_pair, F] packed spectra of the zero-padded convolution blocks
+  double* full;                 // [2 n_pair B] full convolution, utterance u at 2 pair_off[u] B
   double* part_max;             // [n_utt, P]
   int32_t* part_arg;            // [n_utt, P]
   void* out;                    // packed like wav
@@ -151,34 +159,50 @@ __device__ __forceinline__ double2* rv_stage_tables(const RvArgs& a, unsigned ch
   return stw;
 }
 
-// X_b: spectrum of the overlap-save window sig[(b-1)B .. (b+1)B) of the (noise-mixed) utterance.
+// Z_j = X_j + i X_{j+D}: spectrum of two overlap-save windows of the (noise-mixed) utterance packed into one complex
+// transform, X_j = FFT(sig[(j-1)B .. (j+1)B)), D = pairs of the utterance (half its blocks, rounded up),
+// j = -(P-1) .. D-1.  The impulse-response partitions and the blocks of the convolution are real sequences, so every
+// later step is linear over the two packed halves and nothing is ever unpacked (header comment).
+// CTAs [0, n_pair) take j >= 0; the remaining n_utt (P-1) CTAs the P-1 windows before the utterance, whose real half
+// is zero.  Row of Z_j of utterance u: pair_off[u] + u (P-1) + j + P-1.
 template <typename S>
 __global__ void __launch_bounds__(kRvThreads) rv_fwd_kernel(const RvArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double2* z = reinterpret_cast<double2*>(smem_raw);
   const double2* stw = rv_stage_tables(a, smem_raw);
-  const int blk = blockIdx.x;
-  const int u = a.blk_utt[blk];
-  const int b = blk - a.utt_blk_off[u];
+  int u, j;
+  if ((int)blockIdx.x < a.n_pair) {
+    u = a.pair_utt[blockIdx.x];
+    j = blockIdx.x - a.utt_pair_off[u];
+  } else {
+    const int r = blockIdx.x - a.n_pair;
+    u = r / (a.P - 1);
+    j = -1 - (r % (a.P - 1));
+  }
+  const int D = a.utt_pair_off[u + 1] - a.utt_pair_off[u];
   const int64_t woff = a.utt_wav_off[u];
   const int64_t T = a.utt_wav_off[u + 1] - woff;
   const S* sig = reinterpret_cast<const S*>(a.wav) + woff;
   const int16_t* nz = a.noise ? a.noise + a.utt_noise_off[u] : nullptr;
   const double alpha = a.noise ? a.utt_alpha[u] : 0.0;
-  const int64_t q0 = (int64_t)(b - 1) * a.B;
+  const int64_t q0 = (int64_t)(j - 1) * a.B, q1 = (int64_t)(j + D - 1) * a.B;
   for (int i = threadIdx.x; i < a.F; i += blockDim.x) {
-    const int64_t q = q0 + i;
-    double v = 0.0;
-    if (q >= 0 && q < T) {
-      v = (double)sig[q];
-      if (nz) v += alpha * (double)nz[q];
+    const int64_t qa = q0 + i, qb = q1 + i;
+    double va = 0.0, vb = 0.0;
+    if (qa >= 0 && qa < T) {
+      va = (double)sig[qa];
+      if (nz) va += alpha * (double)nz[qa];
     }
-    z[i] = make_double2(v, 0.0);
+    if (qb >= 0 && qb < T) {
+      vb = (double)sig[qb];
+      if (nz) vb += alpha * (double)nz[qb];
+    }
+    z[i] = make_double2(va, vb);
   }
   __syncthreads();
   rv_fft_dif(z, a.F, a.logF, stw);
-  double2* X = a.X + (size_t)blk * a.F;
-  for (int i = threadIdx.x; i < a.F; i += blockDim.x) X[i] = z[i];
+  double2* Z = a.X + ((size_t)a.utt_pair_off[u] + (size_t)u * (a.P - 1) + (size_t)(j + a.P - 1)) * a.F;
+  for (int i = threadIdx.x; i < a.F; i += blockDim.x) Z[i] = z[i];
 }
 
 // spectra of the impulse-response partitions: H_q = FFT([h[qB .. qB+B), 0 .. 0]); rir is a device float64 array
@@ -196,70 +220,117 @@ __global__ void __launch_bounds__(kRvThreads) rv_rir_kernel(const RvArgs a, cons
   for (int i = threadIdx.x; i < a.F; i += blockDim.x) H[(size_t)q * a.F + i] = z[i];
 }
 
-// Block b of the full convolution and its zero-padded spectrum.
-__global__ void __launch_bounds__(kRvThreads) rv_conv_kernel(const RvArgs a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  double2* z = reinterpret_cast<double2*>(smem_raw);
-  const double2* stw = rv_stage_tables(a, smem_raw);
-  const int blk = blockIdx.x;
-  const int u = a.blk_utt[blk];
-  const int b = blk - a.utt_blk_off[u];
-  const int64_t T = a.utt_wav_off[u + 1] - a.utt_wav_off[u];
+// Blocks b and b + D of the full convolution (real and imaginary half of one transform) and the packed spectrum of
+// the zero-padded pair.  A CTA takes kM (1 or 2) consecutive pairs: the P + kM - 1 spectra Z they share are read
+// once per bin, the accumulators of the later pairs wait in registers while the first goes through the transforms.
+constexpr int kRvMaxBins = 16;  // F <= 8192, 512 threads
+
+__device__ __forceinline__ void rv_conv_finish(const RvArgs& a, double2* z, const double2* stw, const int u, const int b,
+                                               const int D, const int64_t full_len) {
   const int F = a.F, B = a.B;
-  const int nq = min(a.P, b + 1);
-  const double2* __restrict__ Xb = a.X + (size_t)blk * F;
-  for (int k = threadIdx.x; k < F; k += blockDim.x) {
-    double2 acc0 = make_double2(0.0, 0.0), acc1 = acc0;
-    int q = 0;
-    for (; q + 1 < nq; q += 2) {
-      const double2 x0 = __ldg(Xb - (size_t)q * F + k), h0 = __ldg(a.H + (size_t)q * F + k);
-      const double2 x1 = __ldg(Xb - (size_t)(q + 1) * F + k), h1 = __ldg(a.H + (size_t)(q + 1) * F + k);
-      acc0 = rv_add(acc0, rv_cmul(x0, h0));
-      acc1 = rv_add(acc1, rv_cmul(x1, h1));
-    }
-    if (q < nq) acc0 = rv_add(acc0, rv_cmul(__ldg(Xb - (size_t)q * F + k), __ldg(a.H + (size_t)q * F + k)));
-    z[k] = rv_add(acc0, acc1);
-  }
-  __syncthreads();
   rv_fft_dit_inv(z, F, a.logF, stw);
   const double inv = 1.0 / (double)F;
-  const int64_t full_len = T + a.R - 1;
-  double* full = a.full + (size_t)blk * B;
+  double* full = a.full + (size_t)2 * a.utt_pair_off[u] * B;
   for (int i = threadIdx.x; i < B; i += blockDim.x) {  // a thread touches only z[i] and z[B + i]
-    const int64_t n = (int64_t)b * B + i;
-    const double v = (n < full_len) ? z[B + i].x * inv : 0.0;
-    full[i] = v;
-    z[i] = make_double2(v, 0.0);
+    const int64_t n0 = (int64_t)b * B + i, n1 = (int64_t)(b + D) * B + i;
+    const double2 y = z[B + i];
+    const double v0 = (n0 < full_len) ? y.x * inv : 0.0;
+    const double v1 = (n1 < full_len) ? y.y * inv : 0.0;
+    full[n0] = v0;
+    full[n1] = v1;
+    z[i] = make_double2(v0, v1);
     z[B + i] = make_double2(0.0, 0.0);
   }
   __syncthreads();
   rv_fft_dif(z, F, a.logF, stw);
-  double2* O = a.O + (size_t)blk * F;
+  double2* O = a.O + ((size_t)a.utt_pair_off[u] + b) * F;
   for (int i = threadIdx.x; i < F; i += blockDim.x) O[i] = z[i];
 }
 
+template <int kBins, int kM>
+__global__ void __launch_bounds__(kRvThreads) rv_conv_kernel(const RvArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double2* z = reinterpret_cast<double2*>(smem_raw);
+  const double2* stw = rv_stage_tables(a, smem_raw);
+  const int u = a.conv_utt[blockIdx.x];
+  const int b0 = (blockIdx.x - a.utt_conv_off[u]) * kM;
+  const int D = a.utt_pair_off[u + 1] - a.utt_pair_off[u];
+  const int64_t T = a.utt_wav_off[u + 1] - a.utt_wav_off[u];
+  const int64_t full_len = T + a.R - 1;
+  const int F = a.F, P = a.P;
+  const bool two = kM == 2 && b0 + 1 < D;
+  // row of Z_{b0 - q}, q = -1 .. P-1 (q = -1 is the newest window, used by pair b0 + 1 only)
+  const double2* __restrict__ Zb = a.X + ((size_t)a.utt_pair_off[u] + (size_t)u * (P - 1) + (size_t)(b0 + P - 1)) * F;
+  double2 held[kM == 2 ? kBins : 1];
+#pragma unroll
+  for (int i = 0; i < kBins; ++i) {
+    const int k = threadIdx.x + i * kRvThreads;
+    if (k < F) {
+      double2 acc0 = make_double2(0.0, 0.0), acc1 = acc0;
+      if constexpr (kM == 2) {
+        double2 znew = two ? __ldg(Zb + (size_t)F + k) : make_double2(0.0, 0.0);
+        for (int q = 0; q < P; ++q) {
+          const double2 h = __ldg(a.H + (size_t)q * F + k);
+          const double2 zc = __ldg(Zb - (size_t)q * F + k);
+          acc1 = rv_add(acc1, rv_cmul(znew, h));  // pair b0 + 1: Z_{b0 + 1 - q}
+          acc0 = rv_add(acc0, rv_cmul(zc, h));    // pair b0:     Z_{b0 - q}
+          znew = zc;
+        }
+        held[i] = acc1;
+      } else {
+        int q = 0;
+        for (; q + 1 < P; q += 2) {
+          const double2 h0 = __ldg(a.H + (size_t)q * F + k), z0 = __ldg(Zb - (size_t)q * F + k);
+          const double2 h1 = __ldg(a.H + (size_t)(q + 1) * F + k), z1 = __ldg(Zb - (size_t)(q + 1) * F + k);
+          acc0 = rv_add(acc0, rv_cmul(z0, h0));
+          acc1 = rv_add(acc1, rv_cmul(z1, h1));
+        }
+        if (q < P) acc0 = rv_add(acc0, rv_cmul(__ldg(Zb - (size_t)q * F + k), __ldg(a.H + (size_t)q * F + k)));
+        acc0 = rv_add(acc0, acc1);
+      }
+      z[k] = acc0;
+    }
+  }
+  __syncthreads();
+  rv_conv_finish(a, z, stw, u, b0, D, full_len);
+  if constexpr (kM == 2) {
+    if (two) {
+      __syncthreads();
+#pragma unroll
+      for (int i = 0; i < kBins; ++i) {
+        const int k = threadIdx.x + i * kRvThreads;
+        if (k < F) z[k] = held[i];
+      }
+      __syncthreads();
+      rv_conv_finish(a, z, stw, u, b0 + 1, D, full_len);
+    }
+  }
+}
+
 // One (utterance, lag partition q): xxc at lags d in [qB, qB + B) and its maximum (ties: the largest d, which is
-// the first index of the reference's xxc, i = R - 1 - d).
+// the first index of the reference's xxc, i = R - 1 - d).  sum_c conj(OO_c) Z_{c-q} over the packed spectra: its
+// inverse transform has the wanted correlation (both halves of every pair) in the real part and the cross terms of
+// the packing in the imaginary part.
 __global__ void __launch_bounds__(kRvThreads) rv_corr_kernel(const RvArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double2* z = reinterpret_cast<double2*>(smem_raw);
   const double2* stw = rv_stage_tables(a, smem_raw);
   const int q = blockIdx.x, u = blockIdx.y;
-  const int blk0 = a.utt_blk_off[u];
-  const int nb = a.utt_blk_off[u + 1] - blk0;
+  const int p0 = a.utt_pair_off[u];
+  const int D = a.utt_pair_off[u + 1] - p0;
   const int F = a.F, B = a.B;
-  const double2* __restrict__ O = a.O + (size_t)blk0 * F;
-  const double2* __restrict__ X = a.X + (size_t)blk0 * F;
+  const double2* __restrict__ O = a.O + (size_t)p0 * F;
+  const double2* __restrict__ Z = a.X + ((size_t)p0 + (size_t)u * (a.P - 1) + (size_t)(a.P - 1 - q)) * F;  // Z_{0 - q}
   for (int k = threadIdx.x; k < F; k += blockDim.x) {
     double2 acc0 = make_double2(0.0, 0.0), acc1 = acc0;
-    int c = q;
-    for (; c + 1 < nb; c += 2) {
-      const double2 o0 = __ldg(O + (size_t)c * F + k), x0 = __ldg(X + (size_t)(c - q) * F + k);
-      const double2 o1 = __ldg(O + (size_t)(c + 1) * F + k), x1 = __ldg(X + (size_t)(c + 1 - q) * F + k);
+    int c = 0;
+    for (; c + 1 < D; c += 2) {
+      const double2 o0 = __ldg(O + (size_t)c * F + k), x0 = __ldg(Z + (size_t)c * F + k);
+      const double2 o1 = __ldg(O + (size_t)(c + 1) * F + k), x1 = __ldg(Z + (size_t)(c + 1) * F + k);
       acc0 = rv_add(acc0, rv_cmulc(x0, o0));
       acc1 = rv_add(acc1, rv_cmulc(x1, o1));
     }
-    if (c < nb) acc0 = rv_add(acc0, rv_cmulc(__ldg(X + (size_t)(c - q) * F + k), __ldg(O + (size_t)c * F + k)));
+    if (c < D) acc0 = rv_add(acc0, rv_cmulc(__ldg(Z + (size_t)c * F + k), __ldg(O + (size_t)c * F + k)));
     z[k] = rv_add(acc0, acc1);
   }
   __syncthreads();
@@ -312,7 +383,7 @@ __global__ void __launch_bounds__(256) rv_align_kernel(const RvArgs a) {
     if (a.ind) a.ind[u] = indM;
     if (a.out_len) a.out_len[u] = n_out;
   }
-  const double* __restrict__ full = a.full + (size_t)a.utt_blk_off[u] * a.B + indM;
+  const double* __restrict__ full = a.full + (size_t)2 * a.utt_pair_off[u] * a.B + indM;
   for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < T; n += (int64_t)gridDim.x * blockDim.x) {
     const double v = (n < n_out) ? full[n] : 0.0;
     if (a.out_dtype == FDLP_WAV_FLOAT64) reinterpret_cast<double*>(a.out)[woff + n] = v;

@@ -60,9 +60,9 @@ class Reverberator:
         with torch.cuda.device(self.device):
             L.check(self._lib.fdlp_reverb_plan_create(self.rir.ctypes.data_as(C.c_void_p), int(self.rir.size),
                                                       int(block), C.byref(self._plan)))
-        b, p = C.c_int32(), C.c_int32()
-        L.check(self._lib.fdlp_reverb_plan_get_block(self._plan, C.byref(b), C.byref(p)))
-        self.block, self.partitions = int(b.value), int(p.value)
+        b, p, m = C.c_int32(), C.c_int32(), C.c_int32()
+        L.check(self._lib.fdlp_reverb_plan_get_block(self._plan, C.byref(b), C.byref(p), C.byref(m)))
+        self.block, self.partitions, self.pairs_per_cta = int(b.value), int(p.value), int(m.value)
 
     def close(self):
         if getattr(self, "_plan", None) and self._plan.value:
@@ -86,16 +86,19 @@ class Reverberator:
         L.check(self._lib.fdlp_reverb_plan_get_kernel_ms(self._plan, out))
         return dict(zip(self.KERNELS, [float(v) for v in out]))
 
-    def scratch_bytes(self, n_blk: int) -> int:
-        return int(self._lib.fdlp_reverb_plan_scratch_bytes(self._plan, int(n_blk)))
+    def scratch_bytes(self, n_pair: int, n_utt: int) -> int:
+        return int(self._lib.fdlp_reverb_plan_scratch_bytes(self._plan, int(n_pair), int(n_utt)))
 
     def block_layout(self, lengths: Sequence[int]):
-        """Block tables of a batch: nb_u = ceil((T_u + R - 1) / block)."""
+        """Tables of a batch: D_u = ceil(ceil((T_u + R - 1) / block) / 2) block pairs per utterance and
+        ceil(D_u / pairs_per_cta) convolution CTAs.  Returns (utt_pair_off, pair_utt, utt_conv_off, conv_utt)."""
         lengths = np.asarray(lengths, dtype=np.int64)
         nb = (lengths + self.rir.size - 1 + self.block - 1) // self.block
-        utt_blk_off = np.concatenate([[0], np.cumsum(nb)]).astype(np.int32)
-        blk_utt = np.repeat(np.arange(len(lengths), dtype=np.int32), nb).astype(np.int32)
-        return utt_blk_off, blk_utt
+        D = (nb + 1) // 2
+        nc = (D + self.pairs_per_cta - 1) // self.pairs_per_cta
+        ids = np.arange(len(lengths), dtype=np.int32)
+        return (np.concatenate([[0], np.cumsum(D)]).astype(np.int32), np.repeat(ids, D).astype(np.int32),
+                np.concatenate([[0], np.cumsum(nc)]).astype(np.int32), np.repeat(ids, nc).astype(np.int32))
 
     def forward_packed(self, wav_dev: torch.Tensor, lengths: Sequence[int], utt_wav_off_dev: Optional[torch.Tensor] = None,
                        noise_dev=None, out_dtype=torch.float64):
@@ -116,18 +119,16 @@ class Reverberator:
             return out, ind[:0], out_len[:0]
         if utt_wav_off_dev is None:
             utt_wav_off_dev = torch.from_numpy(np.concatenate([[0], np.cumsum(lengths)]).astype(np.int64)).to(dev)
-        utt_blk_off, blk_utt = self.block_layout(lengths)
-        blk_off_dev = torch.from_numpy(utt_blk_off).to(dev)
-        blk_utt_dev = torch.from_numpy(blk_utt).to(dev)
+        tabs = [torch.from_numpy(t).to(dev) for t in self.block_layout(lengths)]
         b = L.ReverbBatch()
         b.wav = wav_dev.data_ptr()
         b.wav_dtype = L.FDLP_WAV_INT16 if wav_dev.dtype == torch.int16 else L.FDLP_WAV_FLOAT32
         b.n_utt = n_utt
         b.utt_wav_off = utt_wav_off_dev.data_ptr()
         b.max_len = int(lengths.max())
-        b.n_blk = int(utt_blk_off[-1])
-        b.utt_blk_off = blk_off_dev.data_ptr()
-        b.blk_utt = blk_utt_dev.data_ptr()
+        b.n_pair, b.n_conv = int(tabs[1].numel()), int(tabs[3].numel())
+        b.utt_pair_off, b.pair_utt = tabs[0].data_ptr(), tabs[1].data_ptr()
+        b.utt_conv_off, b.conv_utt = tabs[2].data_ptr(), tabs[3].data_ptr()
         if noise_dev is None:
             b.noise_mode = L.FDLP_NOISE_NONE
         else:
@@ -142,7 +143,7 @@ class Reverberator:
         stream = torch.cuda.current_stream(dev).cuda_stream
         with torch.cuda.device(dev):
             L.check(self._lib.fdlp_reverb_forward(self._plan, C.byref(b), C.c_void_p(stream)))
-        self._keep = (blk_off_dev, blk_utt_dev, utt_wav_off_dev)  # alive until the next call: the launch is asynchronous
+        self._keep = (tabs, utt_wav_off_dev)  # alive until the next call: the launch is asynchronous
         return out, ind, out_len
 
     def __call__(self, wavs: Sequence[Union[np.ndarray, torch.Tensor]], out_dtype=torch.float64):
