@@ -30,7 +30,7 @@ def splice_feats(feats, context):
 
 
 def mfcc_features(signal, *, nfilters=30, nfft=1024, fduration=0.02, frate=100, context=None, srate=16000,
-                  noise=None, snr=None, rand=None, ncep=13, window=np.hamming):
+                  noise=None, snr=None, rand=None, ncep=13, window=np.hamming, reverb=None):
     """computeMfccFeatures.py:111-131.  `signal` (and `noise`) as read from the WAV (int16 or float32): both are
     divided by 2^15 (:40,:113).  Note the transform length: fft(frames, nfft/2+1) is an (nfft/2+1)-POINT DFT of
     the frame (513 points for nfft = 1024, frame truncated or zero-padded to that length) whose every bin --
@@ -38,6 +38,9 @@ def mfcc_features(signal, *, nfilters=30, nfft=1024, fduration=0.02, frate=100, 
     sig = np.asarray(signal) / np.power(2, 15)
     if noise is not None:
         sig = add_noise_normalised(sig, np.asarray(noise) / np.power(2, 15), float(snr), float(rand))
+    if reverb is not None:
+        from oracle.reverb import add_reverb
+        sig = add_reverb(sig, reverb)                                    # :118-120
     fbank = make_fbank("mel,1", nfilters, nfft, srate)                   # :72  createFbank(nfilters, nfft, srate)
     time_frames = get_frames(sig, srate, frate, fduration, window)       # :121-122
     spec = np.abs(scipy.fftpack.fft(time_frames, int(nfft / 2 + 1), axis=1))

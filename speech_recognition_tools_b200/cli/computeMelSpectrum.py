@@ -13,6 +13,7 @@ if _ROOT not in sys.path:
 
 from speech_recognition_tools_b200.cli.common import iter_scp, write_lens  # noqa: E402
 from speech_recognition_tools_b200.kaldi_io import write_ark_scp  # noqa: E402
+from speech_recognition_tools_b200.reverb import Reverberator, load_rir  # noqa: E402
 from speech_recognition_tools_b200.mel import MelConfig, MelExtractor  # noqa: E402
 
 MAX_SAMPLES_PER_BATCH = 64 * 1024 * 1024
@@ -42,14 +43,16 @@ def compute_mel_spectrum(args, srate=16000, window=np.hamming, return_feats=Fals
     if args.spectrum_type not in ("log", "power"):
         print("Spectrum type not supported! ")
         sys.exit(1)
-    if (args.add_noise and args.add_noise != "clean") or (args.add_reverb and args.add_reverb != "clean"):
-        raise NotImplementedError("noise / reverb augmentation is implemented on the FDLP path only")
+    if args.add_noise and args.add_noise != "clean":
+        raise NotImplementedError("noise mixing is implemented on the FDLP and MFCC paths only")
+    rir = load_rir(args.add_reverb)  # computeMelSpectrum.py:74-90: ./RIR/RIR_<room>_AnglA.wav, channel 1, / 2^15
     ex = MelExtractor(MelConfig.from_args(args))
+    reverberator = Reverberator(rir, device=ex.device) if rir is not None else None
     all_feats, all_lens = {}, {}
 
     def flush(batch):
         if batch:
-            outs = ex([b[1] for b in batch])
+            outs = ex([b[1] for b in batch], reverb=reverberator)
             for (k, _), o in zip(batch, outs):
                 all_feats[k] = o.cpu().numpy()
                 all_lens[k] = int(o.shape[0])

@@ -14,6 +14,7 @@ if _ROOT not in sys.path:
 from speech_recognition_tools_b200.cli.common import iter_scp, load_noise  # noqa: E402
 from speech_recognition_tools_b200.fdlp import NoiseSpec  # noqa: E402
 from speech_recognition_tools_b200.kaldi_io import write_ark_scp  # noqa: E402
+from speech_recognition_tools_b200.reverb import Reverberator, load_rir  # noqa: E402
 from speech_recognition_tools_b200.mfcc import MfccConfig, MfccExtractor  # noqa: E402
 
 MAX_SAMPLES_PER_BATCH = 64 * 1024 * 1024
@@ -37,11 +38,12 @@ def get_args(argv=None):
 def extractMelEnergyFeats(args, srate=16000, window=np.hamming, return_feats=False):
     if window is not np.hamming:
         raise NotImplementedError("only the Hamming window of the reference is implemented")
+    rir = None
     if args.add_reverb:
         if args.add_reverb == "clean":
             print("%s: No reverberation added!" % sys.argv[0])
-        elif args.add_reverb in ("small_room", "large_room"):
-            raise NotImplementedError("--add_reverb needs the reference's ./RIR recordings, which are not distributed")
+        elif args.add_reverb in ("small_room", "large_room"):  # computeMfccFeatures.py:81-88 has no medium room
+            rir = load_rir(args.add_reverb)
         else:
             raise ValueError("Invalid type of reverberation!")
     noise = None
@@ -49,6 +51,7 @@ def extractMelEnergyFeats(args, srate=16000, window=np.hamming, return_feats=Fal
         noise_info = args.add_noise.strip().split(",")
         noise = (load_noise(noise_info[0]), float(noise_info[1]))
     ex = MfccExtractor(MfccConfig.from_args(args))
+    rir_plan = [Reverberator(rir, device=ex.device)] if rir is not None else []
     all_feats = {}
 
     def flush(batch):
@@ -56,7 +59,7 @@ def extractMelEnergyFeats(args, srate=16000, window=np.hamming, return_feats=Fal
             nspec = None
             if noise is not None:  # one np.random.rand() per utterance, in scp order (computeMfccFeatures.py:46)
                 nspec = NoiseSpec(samples=noise[0], snr_db=noise[1], rand=[np.random.rand() for _ in batch])
-            outs = ex([b[1] for b in batch], noise=nspec)
+            outs = ex([b[1] for b in batch], noise=nspec, reverb=rir_plan[0] if rir_plan else None)
             for (k, _), o in zip(batch, outs):
                 all_feats[k] = o.cpu().numpy()
 

@@ -1501,7 +1501,8 @@ extern "C" int fdlp_diff_filter(const void* wav, int32_t wav_dtype, const int64_
 // ================================================================ --add_reverb (features.py:110-115)
 struct fdlp_reverb_plan {
   int R = 0, B = 0, F = 0, logF = 0, P = 0;
-  int conv_m = 2;  // block pairs per convolution CTA
+  int conv_m = 1;  // block pairs per convolution CTA (2 halves the spectrum reads but holds accumulators in
+                   // registers: one CTA per SM instead of three, slower at F = 4096)
   size_t smem = 0;
   double2* d_tw = nullptr;
   double2* d_H = nullptr;
@@ -1510,6 +1511,7 @@ struct fdlp_reverb_plan {
   double2* d_X = nullptr;
   double2* d_O = nullptr;
   double* d_full = nullptr;
+  double2* d_C = nullptr;
   double* d_pmax = nullptr;
   int32_t* d_parg = nullptr;
   double* d_alpha = nullptr;
@@ -1519,7 +1521,7 @@ struct fdlp_reverb_plan {
 
 static void reverb_free(fdlp_reverb_plan* p) {
   if (!p) return;
-  cudaFree(p->d_tw); cudaFree(p->d_H); cudaFree(p->d_X); cudaFree(p->d_O); cudaFree(p->d_full);
+  cudaFree(p->d_tw); cudaFree(p->d_H); cudaFree(p->d_X); cudaFree(p->d_O); cudaFree(p->d_full); cudaFree(p->d_C);
   cudaFree(p->d_pmax); cudaFree(p->d_parg); cudaFree(p->d_alpha);
   for (auto& e : p->ev) if (e) cudaEventDestroy(e);
   delete p;
@@ -1528,7 +1530,7 @@ static void reverb_free(fdlp_reverb_plan* p) {
 static void reverb_fill(const fdlp_reverb_plan* p, RvArgs& a) {
   memset(&a, 0, sizeof(a));
   a.R = p->R; a.B = p->B; a.F = p->F; a.logF = p->logF; a.P = p->P; a.tw = p->d_tw; a.H = p->d_H;
-  a.X = p->d_X; a.O = p->d_O; a.full = p->d_full; a.part_max = p->d_pmax; a.part_arg = p->d_parg;
+  a.X = p->d_X; a.O = p->d_O; a.C = p->d_C; a.full = p->d_full; a.part_max = p->d_pmax; a.part_arg = p->d_parg;
 }
 
 extern "C" int fdlp_reverb_plan_create(const double* rir, int32_t R, int32_t block, fdlp_reverb_plan** out) {
@@ -1539,7 +1541,7 @@ extern "C" int fdlp_reverb_plan_create(const double* rir, int32_t R, int32_t blo
   if (!p) return set_err(FDLP_E_NOMEM, "out of host memory%s", "");
   p->R = R;
   int B = block;
-  if (B == 0) { B = 64; while (B < R && B < 4096) B <<= 1; }
+  if (B == 0) { B = 64; while (8 * B < R && B < 2048) B <<= 1; }  // about 8 partitions; 2048 measured best at R = 16000
   p->B = B; p->F = 2 * B; p->P = (R + B - 1) / B;
   p->logF = 0;
   while ((1 << p->logF) < p->F) ++p->logF;
@@ -1558,7 +1560,7 @@ extern "C" int fdlp_reverb_plan_create(const double* rir, int32_t R, int32_t blo
   if (rc) { reverb_free(p); return rc; }
   cudaError_t e = raise_smem_limit(rv_fwd_kernel<int16_t>, p->smem);
   if (e == cudaSuccess) e = raise_smem_limit(rv_fwd_kernel<float>, p->smem);
-  if (const char* m = getenv("FDLP_RV_CONVM")) p->conv_m = atoi(m) == 1 ? 1 : 2;
+  if (const char* m = getenv("FDLP_RV_CONVM")) p->conv_m = atoi(m) == 2 ? 2 : 1;
 #define RV_CONV_SMEM(BINS)                                                                 \
   if (e == cudaSuccess) e = raise_smem_limit(rv_conv_kernel<BINS, 1>, p->smem);           \
   if (e == cudaSuccess) e = raise_smem_limit(rv_conv_kernel<BINS, 2>, p->smem);
@@ -1615,7 +1617,7 @@ extern "C" int fdlp_reverb_plan_get_kernel_ms(fdlp_reverb_plan* p, float* out4) 
 extern "C" int64_t fdlp_reverb_plan_scratch_bytes(const fdlp_reverb_plan* p, int32_t n_pair, int32_t n_utt) {
   if (!p) return 0;
   return ((int64_t)2 * n_pair + (int64_t)n_utt * (p->P - 1)) * p->F * (int64_t)sizeof(double2) +
-         (int64_t)2 * n_pair * p->B * (int64_t)sizeof(double);
+         (int64_t)2 * n_pair * p->B * (int64_t)sizeof(double) + (int64_t)n_utt * p->P * p->F * (int64_t)sizeof(double2);
 }
 
 extern "C" int fdlp_reverb_forward(fdlp_reverb_plan* p, const fdlp_reverb_batch* b, void* stream) {
@@ -1634,12 +1636,14 @@ extern "C" int fdlp_reverb_forward(fdlp_reverb_plan* p, const fdlp_reverb_batch*
   if (b->n_pair > p->cap_blk || b->n_utt > p->cap_utt) {
     FDLP_CUDA(cudaStreamSynchronize(st));
     cudaFree(p->d_X); cudaFree(p->d_O); cudaFree(p->d_full); cudaFree(p->d_pmax); cudaFree(p->d_parg); cudaFree(p->d_alpha);
-    p->d_X = p->d_O = nullptr; p->d_full = nullptr; p->d_pmax = nullptr; p->d_parg = nullptr; p->d_alpha = nullptr;
+    cudaFree(p->d_C);
+    p->d_X = p->d_O = p->d_C = nullptr; p->d_full = nullptr; p->d_pmax = nullptr; p->d_parg = nullptr; p->d_alpha = nullptr;
     p->cap_blk = p->cap_utt = 0;
     const int np = std::max(b->n_pair, p->cap_blk), nu = std::max(b->n_utt, p->cap_utt);
     FDLP_CUDA(cudaMalloc((void**)&p->d_X, ((size_t)np + (size_t)nu * (p->P - 1)) * p->F * sizeof(double2)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_O, (size_t)np * p->F * sizeof(double2)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_full, (size_t)2 * np * p->B * sizeof(double)));
+    FDLP_CUDA(cudaMalloc((void**)&p->d_C, (size_t)nu * p->P * p->F * sizeof(double2)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_pmax, (size_t)nu * p->P * sizeof(double)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_parg, (size_t)nu * p->P * sizeof(int32_t)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_alpha, (size_t)nu * sizeof(double)));
@@ -1680,6 +1684,9 @@ extern "C" int fdlp_reverb_forward(fdlp_reverb_plan* p, const fdlp_reverb_batch*
   }
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[2], st));
+  rv_corr_mac_kernel<<<dim3((unsigned)((p->F + kRvThreads - 1) / kRvThreads), (unsigned)((p->P + kRvQ - 1) / kRvQ),
+                            (unsigned)b->n_utt), kRvThreads, 0, st>>>(a);
+  FDLP_CUDA(cudaGetLastError());
   rv_corr_kernel<<<dim3((unsigned)p->P, (unsigned)b->n_utt), kRvThreads, p->smem, st>>>(a);
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[3], st));

@@ -52,6 +52,7 @@ struct RvArgs {
   double2* X;                   // [n_pair + n_utt (P-1), F] packed window spectra Z_j
   double2* O;                   // [n_pair, F] packed spectra of the zero-padded convolution blocks
   double* full;                 // [2 n_pair B] full convolution, utterance u at 2 pair_off[u] B
+  double2* C;                   // [n_utt, P, F] correlation spectra
   double* part_max;             // [n_utt, P]
   int32_t* part_arg;            // [n_utt, P]
   void* out;                    // packed like wav
@@ -307,32 +308,53 @@ __global__ void __launch_bounds__(kRvThreads) rv_conv_kernel(const RvArgs a) {
   }
 }
 
-// One (utterance, lag partition q): xxc at lags d in [qB, qB + B) and its maximum (ties: the largest d, which is
-// the first index of the reference's xxc, i = R - 1 - d).  sum_c conj(OO_c) Z_{c-q} over the packed spectra: its
-// inverse transform has the wanted correlation (both halves of every pair) in the real part and the cross terms of
-// the packing in the imaginary part.
+// Correlation spectra C_q = sum_c conj(OO_c) Z_{c-q} for kQ consecutive lag partitions at once: a thread owns one
+// bin and walks the pairs of the utterance, keeping the last kQ window spectra of its bin in a register ring, so every
+// row of OO and Z is read once per group of kQ partitions instead of once per partition.  The inverse transform has the
+// wanted correlation (both halves of every pair) in the real part and the cross terms of the packing in the imaginary
+// part.  grid = (ceil(F / threads), ceil(P / kQ), n_utt); L2/HBM-bound streaming of 2 D rows per utterance and group.
+constexpr int kRvQ = 8;
+
+__global__ void __launch_bounds__(kRvThreads) rv_corr_mac_kernel(const RvArgs a) {
+  const int k = blockIdx.x * kRvThreads + threadIdx.x;
+  const int q0 = blockIdx.y * kRvQ, u = blockIdx.z;
+  const int F = a.F, P = a.P;
+  if (k >= F) return;
+  const int p0 = a.utt_pair_off[u];
+  const int D = a.utt_pair_off[u + 1] - p0;
+  const double2* __restrict__ O = a.O + (size_t)p0 * F + k;
+  const double2* __restrict__ Z = a.X + ((size_t)p0 + (size_t)u * (P - 1) + (size_t)(P - 1)) * F + k;  // Z_0
+  double2 acc[kRvQ], ring[kRvQ];
+#pragma unroll
+  for (int i = 0; i < kRvQ; ++i) {
+    acc[i] = make_double2(0.0, 0.0);
+    // ring[i] = Z_{c - q0 - i} at step c; before the first step the entries i >= 1 hold Z_{-1 - q0 - (i-1)}
+    ring[i] = (i >= 1 && q0 + i <= P - 1) ? __ldg(Z - (ptrdiff_t)(q0 + i) * F) : make_double2(0.0, 0.0);
+  }
+#pragma unroll 2
+  for (int c = 0; c < D; ++c) {
+    const double2 o = __ldg(O + (size_t)c * F);
+    ring[0] = __ldg(Z + (ptrdiff_t)(c - q0) * F);
+#pragma unroll
+    for (int i = 0; i < kRvQ; ++i) acc[i] = rv_add(acc[i], rv_cmulc(ring[i], o));
+#pragma unroll
+    for (int i = kRvQ - 1; i >= 1; --i) ring[i] = ring[i - 1];
+  }
+#pragma unroll
+  for (int i = 0; i < kRvQ; ++i)
+    if (q0 + i < P) a.C[((size_t)u * P + q0 + i) * F + k] = acc[i];
+}
+
+// One (utterance, lag partition q): xxc at lags d in [qB, qB + B) from C_q and its maximum (ties: the largest d, which
+// is the first index of the reference's xxc, i = R - 1 - d).
 __global__ void __launch_bounds__(kRvThreads) rv_corr_kernel(const RvArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double2* z = reinterpret_cast<double2*>(smem_raw);
   const double2* stw = rv_stage_tables(a, smem_raw);
   const int q = blockIdx.x, u = blockIdx.y;
-  const int p0 = a.utt_pair_off[u];
-  const int D = a.utt_pair_off[u + 1] - p0;
   const int F = a.F, B = a.B;
-  const double2* __restrict__ O = a.O + (size_t)p0 * F;
-  const double2* __restrict__ Z = a.X + ((size_t)p0 + (size_t)u * (a.P - 1) + (size_t)(a.P - 1 - q)) * F;  // Z_{0 - q}
-  for (int k = threadIdx.x; k < F; k += blockDim.x) {
-    double2 acc0 = make_double2(0.0, 0.0), acc1 = acc0;
-    int c = 0;
-    for (; c + 1 < D; c += 2) {
-      const double2 o0 = __ldg(O + (size_t)c * F + k), x0 = __ldg(Z + (size_t)c * F + k);
-      const double2 o1 = __ldg(O + (size_t)(c + 1) * F + k), x1 = __ldg(Z + (size_t)(c + 1) * F + k);
-      acc0 = rv_add(acc0, rv_cmulc(x0, o0));
-      acc1 = rv_add(acc1, rv_cmulc(x1, o1));
-    }
-    if (c < D) acc0 = rv_add(acc0, rv_cmulc(__ldg(Z + (size_t)c * F + k), __ldg(O + (size_t)c * F + k)));
-    z[k] = rv_add(acc0, acc1);
-  }
+  const double2* __restrict__ C = a.C + ((size_t)u * a.P + q) * F;
+  for (int k = threadIdx.x; k < F; k += blockDim.x) z[k] = C[k];
   __syncthreads();
   rv_fft_dit_inv(z, F, a.logF, stw);
   double best = -INFINITY;

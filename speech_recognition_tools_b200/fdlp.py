@@ -512,15 +512,10 @@ class FdlpExtractor:
         `reverb` is a reverb.Reverberator or the float64 impulse response.  Returns (float64 packed batch,
         per-utterance lengths): an utterance comes back one sample shorter in the reference's corner case
         indM == len(rir), and the packed batch is then re-packed to the new lengths."""
-        from .reverb import Reverberator
-        rv = reverb if isinstance(reverb, Reverberator) else Reverberator(reverb, device=self.device)
+        from .reverb import reverberate_packed
         lay.to(self.device)
-        out, _, out_len = rv.forward_packed(wav_dev, lay.lengths, lay.dev["utt_wav_off"], noise_dev)
-        n = out_len.cpu().numpy()
-        if np.array_equal(n, lay.lengths):
-            return out, lay.lengths
-        parts = [out[int(lay.utt_wav_off[u]):int(lay.utt_wav_off[u]) + int(n[u])] for u in range(lay.n_utt)]
-        return torch.cat(parts), n
+        return reverberate_packed(reverb, wav_dev, lay.lengths, self.device, torch.float64, noise_dev,
+                                  lay.dev["utt_wav_off"])
 
     def __call__(self, wavs: Sequence[Union[np.ndarray, torch.Tensor]], jitter=None,
                  noise: Optional[NoiseSpec] = None, cmvn: Optional[torch.Tensor] = None,

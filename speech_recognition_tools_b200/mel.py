@@ -123,12 +123,18 @@ class MelExtractor:
             L.check(self._lib.mel_forward(self._plan, C.byref(b), C.c_void_p(stream)))
         return feats
 
-    def __call__(self, wavs, cmvn: Optional[torch.Tensor] = None):
+    def __call__(self, wavs, cmvn: Optional[torch.Tensor] = None, reverb=None):
+        """`reverb`: impulse response or reverb.Reverberator for --add_reverb (computeMelSpectrum.py:143-145); the
+        reverberated waveform reaches the framing kernel as float32."""
         if len(wavs) == 0:
             return []
         host, lengths = FdlpExtractor.pack(wavs)
+        wav_dev = host.to(self.device, non_blocking=True)
+        if reverb is not None:
+            from .reverb import reverberate_packed
+            wav_dev, lengths = reverberate_packed(reverb, wav_dev, lengths, self.device, torch.float32)
         lay = self.layout(lengths)
-        feats = self.forward_packed(host.to(self.device, non_blocking=True), lay, cmvn=cmvn)
+        feats = self.forward_packed(wav_dev, lay, cmvn=cmvn)
         return [feats[int(lay.utt_frame_off[u]):int(lay.utt_frame_off[u + 1])] for u in range(lay.n_utt)]
 
 

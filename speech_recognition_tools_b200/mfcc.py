@@ -123,15 +123,22 @@ class MfccExtractor:
             L.check(self._lib.mfcc_forward(self._plan, C.byref(b), C.c_void_p(stream)))
         return feats
 
-    def __call__(self, wavs, noise: Optional[NoiseSpec] = None):
+    def __call__(self, wavs, noise: Optional[NoiseSpec] = None, reverb=None):
         """List of mono waveforms (int16 / float32 as read from the WAV) -> list of [F_u, 13 (2 context + 1)]
-        float32 device tensors."""
+        float32 device tensors.  `reverb`: impulse response or reverb.Reverberator (computeMfccFeatures.py:118-120;
+        the reference reverberates signal / 2^15, which is the reverberated signal / 2^15 exactly)."""
         if len(wavs) == 0:
             return []
         host, lengths = FdlpExtractor.pack(wavs)
+        wav_dev = host.to(self.device, non_blocking=True)
+        if reverb is not None:
+            if noise is not None:
+                raise NotImplementedError("MFCC: noise mixing followed by reverberation is not implemented")
+            from .reverb import reverberate_packed
+            wav_dev, lengths = reverberate_packed(reverb, wav_dev, lengths, self.device, torch.float32)
         lay = self.layout(lengths)
         noise_dev = self._noise_to_device(noise, lay)
-        feats = self.forward_packed(host.to(self.device, non_blocking=True), lay, noise_dev=noise_dev)
+        feats = self.forward_packed(wav_dev, lay, noise_dev=noise_dev)
         return [feats[int(lay.utt_frame_off[u]):int(lay.utt_frame_off[u + 1])] for u in range(lay.n_utt)]
 
 

@@ -158,3 +158,18 @@ class Reverberator:
         off = np.concatenate([[0], np.cumsum(lengths)])
         n = out_len.cpu().numpy()
         return [out[int(off[u]):int(off[u]) + int(n[u])] for u in range(len(lengths))]
+
+
+def reverberate_packed(reverb, wav_dev: torch.Tensor, lengths, device, out_dtype=torch.float64, noise_dev=None,
+                       utt_wav_off_dev=None):
+    """Shared by the extractors' --add_reverb paths: `reverb` is a Reverberator or an impulse response.  Returns the
+    reverberated packed batch and its per-utterance lengths; utterances that come back one sample short (indM ==
+    len(rir), features.py:113-114) are re-packed."""
+    rv = reverb if isinstance(reverb, Reverberator) else Reverberator(reverb, device=device)
+    lengths = np.asarray(lengths, dtype=np.int64)
+    out, _, out_len = rv.forward_packed(wav_dev, lengths, utt_wav_off_dev, noise_dev, out_dtype)
+    n = out_len.cpu().numpy()
+    if np.array_equal(n, lengths):
+        return out, lengths
+    off = np.concatenate([[0], np.cumsum(lengths)])
+    return torch.cat([out[int(off[u]):int(off[u]) + int(n[u])] for u in range(len(lengths))]), n

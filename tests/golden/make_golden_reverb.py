@@ -48,6 +48,44 @@ def feat_case(name, params, spec, room, R, seed=0, rir_seed=11):
     print("%-28s out=%s min=%.5f max=%.5f" % (name, out.shape, np.nanmin(out), np.nanmax(out)))
 
 
+def mel_case(name, params, spec, room, R, rir_seed=11):
+    x = G.make_input(spec)
+    with tempfile.TemporaryDirectory() as d:
+        os.makedirs(os.path.join(d, "RIR"))
+        wavfile.write(os.path.join(d, RIR_FILES[room]), 16000, synth.rir_int16(room, R, rir_seed))
+        out = G.run_reference("mel", dict(params, add_reverb=room), x, 0, d)
+    meta = dict(name=name, kind="mel", params=dict(params, add_reverb=room), input=spec, seed=0, noise=None,
+                input_sha1=G.sha(x), room=room, R=R, rir_seed=rir_seed)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), feats=out, meta=np.array(json.dumps(meta)))
+    print("%-28s out=%s min=%.5f max=%.5f" % (name, out.shape, np.nanmin(out), np.nanmax(out)))
+
+
+def mfcc_case(name, params, spec, room, R, rir_seed=11):
+    import argparse
+    import make_golden_mfcc as M  # imports the reference MFCC script and installs its capture shim
+    x = G.make_input(spec)
+    cwd = os.getcwd()
+    with tempfile.TemporaryDirectory() as d:
+        os.makedirs(os.path.join(d, "RIR"))
+        wavfile.write(os.path.join(d, RIR_FILES[room]), 16000, synth.rir_int16(room, R, rir_seed))
+        wav = os.path.join(d, "u.wav")
+        wavfile.write(wav, 16000, x)
+        scp = os.path.join(d, "wav.scp")
+        with open(scp, "w") as f:
+            f.write("utt1 %s\n" % wav)
+        os.chdir(d)
+        try:
+            args = argparse.Namespace(scp=scp, outfile=os.path.join(d, "out"), **dict(M.DEFAULTS, **params, add_reverb=room))
+            M.ref_mfcc.extractMelEnergyFeats(args)
+        finally:
+            os.chdir(cwd)
+        out = M._captured["utt1"]
+    meta = dict(name=name, kind="mfcc", params=params, input=spec, noise=None, input_sha1=G.sha(x), room=room, R=R,
+                rir_seed=rir_seed)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), feats=out, meta=np.array(json.dumps(meta)))
+    print("%-28s out=%s min=%.5f max=%.5f" % (name, out.shape, np.nanmin(out), np.nanmax(out)))
+
+
 def main():
     unit_case("reverb_small_white", dict(kind="white", seed=30, utt=0, T=3000), "small_room", 700)
     unit_case("reverb_medium_speech", dict(kind="speechlike", seed=31, utt=1, T=20000, sigma_f=30.0), "medium_room", 5000)
@@ -57,6 +95,10 @@ def main():
     feat_case("fdlp_addreverb_cfg1", {}, dict(kind="white", seed=35, utt=5, T=40001), "small_room", 4000, seed=3)
     feat_case("fdlp_addreverb_wsj", G.WSJ, dict(kind="speechlike", seed=36, utt=6, T=64000, sigma_f=30.0),
               "large_room", 12000, seed=4)
+    mel_case("mel_addreverb_recipe", G.MEL_RECIPE, dict(kind="speechlike", seed=37, utt=7, T=30000, sigma_f=30.0),
+             "medium_room", 6000)
+    mfcc_case("mfcc_addreverb_default", {}, dict(kind="speechlike", seed=38, utt=8, T=20000, sigma_f=30.0),
+              "large_room", 5000)
 
 
 if __name__ == "__main__":

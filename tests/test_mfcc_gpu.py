@@ -33,7 +33,10 @@ def test_mfcc_matches_reference_golden(name):
     if meta["noise"]:
         nz = meta["noise"]
         noise = NoiseSpec(synth.noise_int16(nz["type"], nz["T"], seed=nz["seed"]), nz["snr"], rand=[nz["rand"]])
-    got = ex([x], noise=noise)[0].cpu().numpy().astype(np.float64)
+    rir = None
+    if meta.get("room"):
+        rir = synth.rir_int16(meta["room"], meta["R"], meta["rir_seed"])[:, 1] / 2.0 ** 15
+    got = ex([x], noise=noise, reverb=rir)[0].cpu().numpy().astype(np.float64)
     assert got.shape == ref.shape
     np.testing.assert_allclose(got, ref, rtol=0, atol=ATOL)
     ex.close()

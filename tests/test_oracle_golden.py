@@ -52,7 +52,8 @@ def test_mel_oracle_matches_reference(name):
     c = load_case(name)
     p, _, _ = split_params(c["meta"])
     kw = dict(MEL_DEFAULTS, **p)
-    got = omel.mel_spectrogram(c["x"], **kw)
+    x = c["x"] if c["rir"] is None else oreverb.add_reverb(c["x"], c["rir"])
+    got = omel.mel_spectrogram(x, **kw)
     assert got.shape == c["feats"].shape
     np.testing.assert_allclose(got, c["feats"], rtol=1e-12, atol=1e-12)
 
@@ -134,6 +135,9 @@ def test_mfcc_oracle_matches_reference(name):
     if meta["noise"]:
         nz = meta["noise"]
         kw.update(noise=synth.noise_int16(nz["type"], nz["T"], seed=nz["seed"]), snr=nz["snr"], rand=nz["rand"])
+    if meta.get("room"):  # computeMfccFeatures.py:113-120: signal / 2^15, then addReverb
+        rir = synth.rir_int16(meta["room"], meta["R"], meta["rir_seed"])[:, 1] / np.power(2, 15)
+        kw.update(reverb=rir)
     out = omfcc.mfcc_features(x, **kw)
     assert out.shape == z["feats"].shape
     np.testing.assert_allclose(out, z["feats"], rtol=0, atol=1e-10)

@@ -45,7 +45,7 @@ for B in blocks:
                           pairs_per_cta=M, n_pair=n_pair, ms_per_step=ms, xRT=audio / (ms * 1e-3), kernel_ms=acc,
                           scratch_gb=rv.scratch_bytes(n_pair, n_utt) / 1e9,
                           spectrum_gb=dict(fwd=rows * F * 16e-9, conv=(n_conv * (2 * P + M - 1) + n_pair) * F * 16e-9,
-                                           corr=2.0 * n_pair * P * F * 16e-9),
+                                           corr=(2.0 * n_pair * -(-P // 8) + 2.0 * n_utt * P) * F * 16e-9),
                           transforms=dict(fwd=rows, conv=2 * n_pair, corr=n_utt * P))))
     rv.close()
     del rv
