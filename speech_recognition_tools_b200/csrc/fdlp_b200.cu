@@ -1555,7 +1555,7 @@ extern "C" int fdlp_reverb_plan_create(const double* rir, int32_t R, int32_t blo
     const double th = -2.0 * M_PI * b / p->F;
     tw[na + b] = make_double2(cos(th), sin(th));
   }
-  p->smem = (size_t)p->F * sizeof(double2) + tw.size() * sizeof(double2);
+  p->smem = (size_t)(p->F + (p->F >> 6)) * sizeof(double2) + tw.size() * sizeof(double2);  // rows of 64, pitch 65
   int rc = upload(&p->d_tw, tw);
   if (rc) { reverb_free(p); return rc; }
   cudaError_t e = raise_smem_limit(rv_fwd_kernel<int16_t>, p->smem);

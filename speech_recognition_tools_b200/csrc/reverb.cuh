@@ -75,6 +75,26 @@ __device__ __forceinline__ double2 rv_tw(const double2* stw, int na, int k) {
   return rv_cmul(stw[k >> 6], stw[na + (k & 63)]);
 }
 
+// Shared-memory layout of a transform: element i lives at RVI(i) = i + (i >> 6), i.e. rows of 64 elements with a
+// pitch of 65.  Passes whose butterflies span several rows run with consecutive lanes on consecutive elements of a
+// row; passes inside a row (sub-transform length <= 64) run with consecutive lanes on consecutive ROWS, a stride of
+// 65 x 16 bytes that spreads a quarter warp over all 32 banks, and all lanes of a warp share their twiddles.  (Without
+// the pitch the last two radix-4 passes were 4-way and 2-way bank conflicted: 7.7 k conflicts per transform.)
+#define RVI(i) ((i) + ((i) >> 6))
+
+// butterfly t of a radix-4 pass of span L = 4q -> index of its first element
+__device__ __forceinline__ void rv_bfly_index(const int t, const int q, const int logF, int& j, int& base) {
+  if (q > 16) {
+    j = t & (q - 1);
+    base = (t - j) * 4 + j;  // group * L + j
+  } else {
+    const int lr = logF - 6;  // log2(rows)
+    const int rho = t & ((1 << lr) - 1), beta = t >> lr;
+    j = beta & (q - 1);
+    base = (rho << 6) + (beta - j) * 4 + j;
+  }
+}
+
 // In-place forward FFT of z[0..F): natural order in, digit-reversed order out (radix 4, one leading radix-2 pass
 // when log2 F is odd).  Ends with a __syncthreads().
 __device__ void rv_fft_dif(double2* z, const int F, const int logF, const double2* stw) {
@@ -83,9 +103,9 @@ __device__ void rv_fft_dif(double2* z, const int F, const int logF, const double
   if (logF & 1) {
     const int half = F >> 1;
     for (int j = threadIdx.x; j < half; j += blockDim.x) {
-      const double2 a = z[j], b = z[j + half];
-      z[j] = rv_add(a, b);
-      z[j + half] = rv_cmul(rv_sub(a, b), rv_tw(stw, na, j));
+      const double2 a = z[RVI(j)], b = z[RVI(j + half)];
+      z[RVI(j)] = rv_add(a, b);
+      z[RVI(j + half)] = rv_cmul(rv_sub(a, b), rv_tw(stw, na, j));
     }
     L = half;
     __syncthreads();
@@ -93,22 +113,23 @@ __device__ void rv_fft_dif(double2* z, const int F, const int logF, const double
   while (L >= 4) {
     const int q = L >> 2, mul = F / L;
     for (int t = threadIdx.x; t < (F >> 2); t += blockDim.x) {
-      const int j = t & (q - 1);
-      const int base = (t - j) * 4 + j;  // group * L + j
-      const double2 a0 = z[base], a1 = z[base + q], a2 = z[base + 2 * q], a3 = z[base + 3 * q];
+      int j, base;
+      rv_bfly_index(t, q, logF, j, base);
+      const int i0 = RVI(base), i1 = RVI(base + q), i2 = RVI(base + 2 * q), i3 = RVI(base + 3 * q);
+      const double2 a0 = z[i0], a1 = z[i1], a2 = z[i2], a3 = z[i3];
       const double2 t0 = rv_add(a0, a2), t1 = rv_sub(a0, a2), t2 = rv_add(a1, a3);
       const double2 d = rv_sub(a1, a3);
       const double2 t3 = make_double2(d.y, -d.x);  // -i (a1 - a3)
-      z[base] = rv_add(t0, t2);
+      z[i0] = rv_add(t0, t2);
       if (q == 1) {  // last pass: all twiddles are 1
-        z[base + 1] = rv_add(t1, t3);
-        z[base + 2] = rv_sub(t0, t2);
-        z[base + 3] = rv_sub(t1, t3);
+        z[i1] = rv_add(t1, t3);
+        z[i2] = rv_sub(t0, t2);
+        z[i3] = rv_sub(t1, t3);
       } else {
         const int e = j * mul;
-        z[base + q] = rv_cmul(rv_add(t1, t3), rv_tw(stw, na, e));
-        z[base + 2 * q] = rv_cmul(rv_sub(t0, t2), rv_tw(stw, na, 2 * e));
-        z[base + 3 * q] = rv_cmul(rv_sub(t1, t3), rv_tw(stw, na, 3 * e));
+        z[i1] = rv_cmul(rv_add(t1, t3), rv_tw(stw, na, e));
+        z[i2] = rv_cmul(rv_sub(t0, t2), rv_tw(stw, na, 2 * e));
+        z[i3] = rv_cmul(rv_sub(t1, t3), rv_tw(stw, na, 3 * e));
       }
     }
     L = q;
@@ -123,9 +144,10 @@ __device__ void rv_fft_dit_inv(double2* z, const int F, const int logF, const do
   for (int L = 4; L <= Ltop; L <<= 2) {
     const int q = L >> 2, mul = F / L;
     for (int t = threadIdx.x; t < (F >> 2); t += blockDim.x) {
-      const int j = t & (q - 1);
-      const int base = (t - j) * 4 + j;
-      double2 u0 = z[base], u1 = z[base + q], u2 = z[base + 2 * q], u3 = z[base + 3 * q];
+      int j, base;
+      rv_bfly_index(t, q, logF, j, base);
+      const int i0 = RVI(base), i1 = RVI(base + q), i2 = RVI(base + 2 * q), i3 = RVI(base + 3 * q);
+      double2 u0 = z[i0], u1 = z[i1], u2 = z[i2], u3 = z[i3];
       if (q != 1) {
         const int e = j * mul;
         u1 = rv_cmulc(u1, rv_tw(stw, na, e));
@@ -135,26 +157,26 @@ __device__ void rv_fft_dit_inv(double2* z, const int F, const int logF, const do
       const double2 s0 = rv_add(u0, u2), s1 = rv_sub(u0, u2), s2 = rv_add(u1, u3);
       const double2 d = rv_sub(u1, u3);
       const double2 s3 = make_double2(-d.y, d.x);  // i (u1 - u3)
-      z[base] = rv_add(s0, s2);
-      z[base + q] = rv_add(s1, s3);
-      z[base + 2 * q] = rv_sub(s0, s2);
-      z[base + 3 * q] = rv_sub(s1, s3);
+      z[i0] = rv_add(s0, s2);
+      z[i1] = rv_add(s1, s3);
+      z[i2] = rv_sub(s0, s2);
+      z[i3] = rv_sub(s1, s3);
     }
     __syncthreads();
   }
   if (logF & 1) {
     const int half = F >> 1;
     for (int j = threadIdx.x; j < half; j += blockDim.x) {
-      const double2 y0 = z[j], y1 = rv_cmulc(z[j + half], rv_tw(stw, na, j));
-      z[j] = rv_add(y0, y1);
-      z[j + half] = rv_sub(y0, y1);
+      const double2 y0 = z[RVI(j)], y1 = rv_cmulc(z[RVI(j + half)], rv_tw(stw, na, j));
+      z[RVI(j)] = rv_add(y0, y1);
+      z[RVI(j + half)] = rv_sub(y0, y1);
     }
     __syncthreads();
   }
 }
 
 __device__ __forceinline__ double2* rv_stage_tables(const RvArgs& a, unsigned char* smem_raw) {
-  double2* stw = reinterpret_cast<double2*>(smem_raw + (size_t)a.F * sizeof(double2));
+  double2* stw = reinterpret_cast<double2*>(smem_raw + (size_t)(a.F + (a.F >> 6)) * sizeof(double2));
   const int ntw = (a.F >> 6) + 64;
   for (int i = threadIdx.x; i < ntw; i += blockDim.x) stw[i] = a.tw[i];
   return stw;
@@ -198,12 +220,12 @@ __global__ void __launch_bounds__(kRvThreads) rv_fwd_kernel(const RvArgs a) {
       vb = (double)sig[qb];
       if (nz) vb += alpha * (double)nz[qb];
     }
-    z[i] = make_double2(va, vb);
+    z[RVI(i)] = make_double2(va, vb);
   }
   __syncthreads();
   rv_fft_dif(z, a.F, a.logF, stw);
   double2* Z = a.X + ((size_t)a.utt_pair_off[u] + (size_t)u * (a.P - 1) + (size_t)(j + a.P - 1)) * a.F;
-  for (int i = threadIdx.x; i < a.F; i += blockDim.x) Z[i] = z[i];
+  for (int i = threadIdx.x; i < a.F; i += blockDim.x) Z[i] = z[RVI(i)];
 }
 
 // spectra of the impulse-response partitions: H_q = FFT([h[qB .. qB+B), 0 .. 0]); rir is a device float64 array
@@ -214,11 +236,11 @@ __global__ void __launch_bounds__(kRvThreads) rv_rir_kernel(const RvArgs a, cons
   const int q = blockIdx.x;
   for (int i = threadIdx.x; i < a.F; i += blockDim.x) {
     const int j = q * a.B + i;
-    z[i] = make_double2((i < a.B && j < a.R) ? rir[j] : 0.0, 0.0);
+    z[RVI(i)] = make_double2((i < a.B && j < a.R) ? rir[j] : 0.0, 0.0);
   }
   __syncthreads();
   rv_fft_dif(z, a.F, a.logF, stw);
-  for (int i = threadIdx.x; i < a.F; i += blockDim.x) H[(size_t)q * a.F + i] = z[i];
+  for (int i = threadIdx.x; i < a.F; i += blockDim.x) H[(size_t)q * a.F + i] = z[RVI(i)];
 }
 
 // Blocks b and b + D of the full convolution (real and imaginary half of one transform) and the packed spectrum of
@@ -234,18 +256,18 @@ __device__ __forceinline__ void rv_conv_finish(const RvArgs& a, double2* z, cons
   double* full = a.full + (size_t)2 * a.utt_pair_off[u] * B;
   for (int i = threadIdx.x; i < B; i += blockDim.x) {  // a thread touches only z[i] and z[B + i]
     const int64_t n0 = (int64_t)b * B + i, n1 = (int64_t)(b + D) * B + i;
-    const double2 y = z[B + i];
+    const double2 y = z[RVI(B + i)];
     const double v0 = (n0 < full_len) ? y.x * inv : 0.0;
     const double v1 = (n1 < full_len) ? y.y * inv : 0.0;
     full[n0] = v0;
     full[n1] = v1;
-    z[i] = make_double2(v0, v1);
-    z[B + i] = make_double2(0.0, 0.0);
+    z[RVI(i)] = make_double2(v0, v1);
+    z[RVI(B + i)] = make_double2(0.0, 0.0);
   }
   __syncthreads();
   rv_fft_dif(z, F, a.logF, stw);
   double2* O = a.O + ((size_t)a.utt_pair_off[u] + b) * F;
-  for (int i = threadIdx.x; i < F; i += blockDim.x) O[i] = z[i];
+  for (int i = threadIdx.x; i < F; i += blockDim.x) O[i] = z[RVI(i)];
 }
 
 template <int kBins, int kM>
@@ -289,7 +311,7 @@ __global__ void __launch_bounds__(kRvThreads) rv_conv_kernel(const RvArgs a) {
         if (q < P) acc0 = rv_add(acc0, rv_cmul(__ldg(Zb - (size_t)q * F + k), __ldg(a.H + (size_t)q * F + k)));
         acc0 = rv_add(acc0, acc1);
       }
-      z[k] = acc0;
+      z[RVI(k)] = acc0;
     }
   }
   __syncthreads();
@@ -300,7 +322,7 @@ __global__ void __launch_bounds__(kRvThreads) rv_conv_kernel(const RvArgs a) {
 #pragma unroll
       for (int i = 0; i < kBins; ++i) {
         const int k = threadIdx.x + i * kRvThreads;
-        if (k < F) z[k] = held[i];
+        if (k < F) z[RVI(k)] = held[i];
       }
       __syncthreads();
       rv_conv_finish(a, z, stw, u, b0 + 1, D, full_len);
@@ -354,7 +376,7 @@ __global__ void __launch_bounds__(kRvThreads) rv_corr_kernel(const RvArgs a) {
   const int q = blockIdx.x, u = blockIdx.y;
   const int F = a.F, B = a.B;
   const double2* __restrict__ C = a.C + ((size_t)u * a.P + q) * F;
-  for (int k = threadIdx.x; k < F; k += blockDim.x) z[k] = C[k];
+  for (int k = threadIdx.x; k < F; k += blockDim.x) z[RVI(k)] = C[k];
   __syncthreads();
   rv_fft_dit_inv(z, F, a.logF, stw);
   double best = -INFINITY;
@@ -362,7 +384,7 @@ __global__ void __launch_bounds__(kRvThreads) rv_corr_kernel(const RvArgs a) {
   for (int e = 1 + threadIdx.x; e <= B; e += blockDim.x) {
     const int d = q * B + B - e;
     if (d < a.R) {
-      const double v = z[e].x;
+      const double v = z[RVI(e)].x;
       if (v > best || (v == best && d > best_d)) { best = v; best_d = d; }
     }
   }
