@@ -332,6 +332,47 @@ def run_ours(args):
         mel_info = {"value": audio_s / (mel_ms * 1e-3), "unit": UNIT, "ms_per_step": mel_ms,
                     "hbm_gbs_algorithmic": mel_bytes / (mel_ms * 1e-3) / 1e9}
 
+        # ---- --add_reverb augmentation on the same batch: reverberation alone and followed by the extraction ----
+        from speech_recognition_tools_b200.reverb import Reverberator
+        R_RIR = 16000
+        rv = Reverberator(synth.rir_int16("large_room", R_RIR)[:, 1] / 2.0 ** 15, device=dev)
+        rv.set_profiling(True)
+        off_dev = lay.dev["utt_wav_off"]
+        for _ in range(2):
+            rwav, _, _ = rv.forward_packed(wav_dev, lens, off_dev)
+            ex.forward_packed(rwav, lay, feats=feats, status=status)
+        torch.cuda.synchronize(dev)
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        rv_ms = rv_step_ms = 0.0
+        rv_kernels = {}
+        for _ in range(3):
+            e0.record()
+            rwav, _, _ = rv.forward_packed(wav_dev, lens, off_dev)
+            e1.record()
+            ex.forward_packed(rwav, lay, feats=feats, status=status)
+            e2.record()
+            torch.cuda.synchronize(dev)
+            rv_ms += e0.elapsed_time(e1) / 3
+            rv_step_ms += e0.elapsed_time(e2) / 3
+            for k, v in rv.kernel_ms().items():
+                rv_kernels[k] = rv_kernels.get(k, 0.0) + v / 3
+        pair_off, pair_utt, _, _ = rv.block_layout(lens)
+        rows = len(pair_utt) + len(lens) * (rv.partitions - 1)
+        spec_bytes = 16.0 * 2 * rv.block
+        reverb_info = {"rir_samples": R_RIR, "block": rv.block, "partitions": rv.partitions,
+                       "reverb_ms": rv_ms, "reverb_xrt": audio_s / (rv_ms * 1e-3),
+                       "reverb_plus_fdlp_ms": rv_step_ms, "reverb_plus_fdlp_xrt": audio_s / (rv_step_ms * 1e-3),
+                       "kernel_ms": rv_kernels,
+                       # the two transform kernels are bound by shared-memory bandwidth (ncu: l1tex 92 %), the
+                       # correlation and alignment kernels by HBM: bytes each must move / its time
+                       "hbm_gbs": {"rv_corr_kernel": (2 * len(pair_utt) * -(-rv.partitions // 8) + 2 * len(lens) * rv.partitions)
+                                   * spec_bytes / (rv_kernels["rv_corr_kernel"] * 1e-3) / 1e9,
+                                   "rv_align_kernel": 16.0 * float(sum(lens)) / (rv_kernels["rv_align_kernel"] * 1e-3) / 1e9},
+                       "transforms_per_step": rows + 2 * len(pair_utt) + len(lens) * rv.partitions,
+                       "scratch_gb": rv.scratch_bytes(len(pair_utt), len(lens)) / 1e9}
+        rv.close()
+        del rwav
+
         # ---- CPU baseline: the oracle port on a bounded sample of the same workload ----
         if old_affinity is not None:
             os.sched_setaffinity(0, old_affinity)
@@ -356,6 +397,7 @@ def run_ours(args):
                     "features out, %d utterance chunks: copies overlap the kernels)" % E2E_CHUNKS},
             "gpu_launches": (7 if ex.geom["nfam"] > 0 else 5) * args.steps * world,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "mel_baseline": mel_info,
+            "add_reverb": reverb_info,
         }
     if world > 1:
         dist.barrier()
