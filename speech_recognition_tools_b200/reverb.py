@@ -112,7 +112,7 @@ class Reverberator:
         lengths = np.asarray(lengths, dtype=np.int64)
         n_utt = len(lengths)
         dev = self.device
-        out = torch.zeros(wav_dev.numel(), dtype=out_dtype, device=dev)
+        out = torch.empty(wav_dev.numel(), dtype=out_dtype, device=dev)  # rv_align_kernel writes every sample
         ind = torch.zeros(max(n_utt, 1), dtype=torch.int32, device=dev)
         out_len = torch.zeros(max(n_utt, 1), dtype=torch.int64, device=dev)
         if n_utt == 0:
