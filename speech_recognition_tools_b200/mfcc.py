@@ -132,10 +132,17 @@ class MfccExtractor:
         host, lengths = FdlpExtractor.pack(wavs)
         wav_dev = host.to(self.device, non_blocking=True)
         if reverb is not None:
-            if noise is not None:
-                raise NotImplementedError("MFCC: noise mixing followed by reverberation is not implemented")
             from .reverb import reverberate_packed
-            wav_dev, lengths = reverberate_packed(reverb, wav_dev, lengths, self.device, torch.float32)
+            nd = None
+            if noise is not None:
+                # the mix happens before the reverberation (:115-120).  Its coefficient is a ratio of mean squares, the
+                # same for signal / 2^15 and noise / 2^15 as for the raw samples: the reverberation kernel's
+                # float-energy mix on the raw samples, times 2^-15 in the MFCC kernel, is the reference's waveform
+                if wav_dev.dtype != torch.int16:
+                    raise NotImplementedError("noise mixing followed by reverberation needs int16 samples")
+                nd = dict(self._noise_to_device(noise, self.layout(lengths)), mode=L.FDLP_NOISE_FLOAT)
+                noise = None
+            wav_dev, lengths = reverberate_packed(reverb, wav_dev, lengths, self.device, torch.float32, nd)
         lay = self.layout(lengths)
         noise_dev = self._noise_to_device(noise, lay)
         feats = self.forward_packed(wav_dev, lay, noise_dev=noise_dev)

@@ -84,3 +84,20 @@ def test_mfcc_cli_shim_writes_kaldi_ark(tmp_path):
         ref = omfcc.mfcc_features(x, nfilters=26)
         np.testing.assert_allclose(feats[k], ref, rtol=0, atol=ATOL)
         np.testing.assert_allclose(ark[k], feats[k], rtol=0, atol=1e-6)
+
+
+def test_noise_then_reverb_against_oracle():
+    """computeMfccFeatures.py:113-120: signal / 2^15, noise mix, then addReverb."""
+    from oracle import mfcc as omfcc
+    from speech_recognition_tools_b200 import synth
+    from speech_recognition_tools_b200.fdlp import NoiseSpec
+    from speech_recognition_tools_b200.mfcc import MfccConfig, MfccExtractor
+    x = synth.make_utterance("speechlike", 46, 0, 24000, 30.0)
+    nz = synth.noise_int16("factory1", 70000, seed=5)
+    rir = synth.rir_int16("small_room", 2500)[:, 1] / 2.0 ** 15
+    ex = MfccExtractor(MfccConfig(), device="cuda:0")
+    got = ex([x], noise=NoiseSpec(nz, 12.0, rand=[0.37]), reverb=rir)[0].cpu().numpy().astype(np.float64)
+    ref = omfcc.mfcc_features(x, noise=nz, snr=12.0, rand=0.37, reverb=rir)
+    assert got.shape == ref.shape
+    np.testing.assert_allclose(got, ref, rtol=0, atol=ATOL)
+    ex.close()
