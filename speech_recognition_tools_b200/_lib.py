@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfdlp_b200.so")
+# FDLP_B200_LIB: another build of the same library (A/B runs of compile-time kernel variants)
+LIB_PATH = os.environ.get("FDLP_B200_LIB") or os.path.join(_HERE, "libfdlp_b200.so")
 
 FDLP_OK = 0
 FDLP_E_ARG, FDLP_E_CUDA, FDLP_E_UNSUPPORTED, FDLP_E_NOMEM = -1, -2, -3, -4

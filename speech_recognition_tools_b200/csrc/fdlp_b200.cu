@@ -1561,9 +1561,8 @@ extern "C" int fdlp_reverb_plan_create(const double* rir, int32_t R, int32_t blo
   cudaError_t e = raise_smem_limit(rv_fwd_kernel<int16_t>, p->smem);
   if (e == cudaSuccess) e = raise_smem_limit(rv_fwd_kernel<float>, p->smem);
   if (const char* m = getenv("FDLP_RV_CONVM")) p->conv_m = atoi(m) == 2 ? 2 : 1;
-#define RV_CONV_SMEM(BINS)                                                                 \
-  if (e == cudaSuccess) e = raise_smem_limit(rv_conv_kernel<BINS, 1>, p->smem);           \
-  if (e == cudaSuccess) e = raise_smem_limit(rv_conv_kernel<BINS, 2>, p->smem);
+  if (e == cudaSuccess) e = raise_smem_limit(rv_conv_kernel<1, 1>, p->smem);
+#define RV_CONV_SMEM(BINS) if (e == cudaSuccess) e = raise_smem_limit(rv_conv_kernel<BINS, 2>, p->smem);
   RV_CONV_SMEM(1) RV_CONV_SMEM(2) RV_CONV_SMEM(4) RV_CONV_SMEM(8) RV_CONV_SMEM(16)
 #undef RV_CONV_SMEM
   if (e == cudaSuccess) e = raise_smem_limit(rv_corr_kernel, p->smem);
@@ -1669,13 +1668,12 @@ extern "C" int fdlp_reverb_forward(fdlp_reverb_plan* p, const fdlp_reverb_batch*
   else rv_fwd_kernel<float><<<(unsigned)n_rows, kRvThreads, p->smem, st>>>(a);
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[1], st));
-  {
+  if (p->conv_m == 1) {
+    // radix-16 transforms (128 registers): 256 threads so that two CTAs share an SM; 512 at F = 8192 (one CTA fits)
+    rv_conv_kernel<1, 1><<<b->n_conv, p->F <= 4096 ? 256 : kRvThreads, p->smem, st>>>(a);
+  } else {
     const int bins = std::max(1, p->F / kRvThreads);
-#define RV_CONV_LAUNCH(BINS)                                                                              \
-    case BINS:                                                                                            \
-      if (p->conv_m == 2) rv_conv_kernel<BINS, 2><<<b->n_conv, kRvThreads, p->smem, st>>>(a);             \
-      else rv_conv_kernel<BINS, 1><<<b->n_conv, kRvThreads, p->smem, st>>>(a);                            \
-      break;
+#define RV_CONV_LAUNCH(BINS) case BINS: rv_conv_kernel<BINS, 2><<<b->n_conv, kRvThreads, p->smem, st>>>(a); break;
     switch (bins) {
       RV_CONV_LAUNCH(1) RV_CONV_LAUNCH(2) RV_CONV_LAUNCH(4) RV_CONV_LAUNCH(8) RV_CONV_LAUNCH(16)
       default: return set_err(FDLP_E_UNSUPPORTED, "unsupported transform length%s", "");

@@ -32,7 +32,18 @@
 
 namespace fdlp {
 
-constexpr int kRvThreads = 512;
+#ifndef FDLP_RV_THREADS
+#define FDLP_RV_THREADS 512
+#endif
+constexpr int kRvThreads = FDLP_RV_THREADS;
+#ifndef FDLP_RV_MINB
+#define FDLP_RV_MINB 1
+#endif
+// The transforms exist in two forms: radix-4 passes (60 registers: two 512-thread CTAs per SM) and pairs of radix-4
+// passes fused into in-register radix-16 passes (half the trips through shared memory, 128 registers).  Measured on the
+// bench batch (tools/ab_reverb.sh): the window kernel is faster with radix 4 at 512 threads (2.12 vs 2.18 / 2.81 ms),
+// the convolution kernel with radix 16 at 256 threads, two CTAs per SM (3.89 vs 4.52 ms); at F = 8192 radix 16 with
+// 512 threads wins everywhere.  Both produce the same element order (a fused pass IS two radix-4 passes).
 
 struct RvArgs {
   const void* wav;
@@ -95,8 +106,126 @@ __device__ __forceinline__ void rv_bfly_index(const int t, const int q, const in
   }
 }
 
+// ---- radix-16 pass = two consecutive radix-4 passes (spans L and L/4) on 16 registers: one trip through shared
+// memory instead of two.  Element r = s + 4m of a butterfly sits at base + r q16 (q16 = L/16); stage A is the radix-4
+// butterfly over m (constant twiddles w_16^{r1 s}), stage B the one over s; the j-dependent twiddles of both passes
+// commute to the end: output (r1, r2), stored at base + (4 r1 + r2) q16, is multiplied by w_L^{(r1 + 4 r2) j}.
+__device__ __forceinline__ double2 rv_w16(int k) {  // exp(-2 pi i k / 16), k in {1, 2, 3, 4, 6, 9}
+  constexpr double c = 0.92387953251128674, s = 0.38268343236508978, h = 0.70710678118654752;
+  switch (k) {
+    case 1: return make_double2(c, -s);
+    case 2: return make_double2(h, -h);
+    case 3: return make_double2(s, -c);
+    case 4: return make_double2(0.0, -1.0);
+    case 6: return make_double2(-h, -h);
+    case 9: return make_double2(-c, s);
+    default: return make_double2(1.0, 0.0);
+  }
+}
+
+__device__ __forceinline__ void rv_bfly4_fwd(double2& a0, double2& a1, double2& a2, double2& a3) {
+  const double2 t0 = rv_add(a0, a2), t1 = rv_sub(a0, a2), t2 = rv_add(a1, a3);
+  const double2 d = rv_sub(a1, a3);
+  const double2 t3 = make_double2(d.y, -d.x);  // -i (a1 - a3)
+  a0 = rv_add(t0, t2); a1 = rv_add(t1, t3); a2 = rv_sub(t0, t2); a3 = rv_sub(t1, t3);
+}
+__device__ __forceinline__ void rv_bfly4_inv(double2& u0, double2& u1, double2& u2, double2& u3) {
+  const double2 s0 = rv_add(u0, u2), s1 = rv_sub(u0, u2), s2 = rv_add(u1, u3);
+  const double2 d = rv_sub(u1, u3);
+  const double2 s3 = make_double2(-d.y, d.x);  // i (u1 - u3)
+  u0 = rv_add(s0, s2); u1 = rv_add(s1, s3); u2 = rv_sub(s0, s2); u3 = rv_sub(s1, s3);
+}
+
+// butterfly t of a radix-16 pass of span L = 16 q16 -> j and the index of its first element (lanes along a row when
+// the butterfly spans rows, across rows when it lies inside one)
+__device__ __forceinline__ void rv_bfly16_index(const int t, const int q16, const int logF, int& j, int& base) {
+  if (q16 > 4) {
+    j = t & (q16 - 1);
+    base = (t - j) * 16 + j;
+  } else {
+    const int lr = logF - 6;
+    const int rho = t & ((1 << lr) - 1), beta = t >> lr;
+    j = beta & (q16 - 1);
+    base = (rho << 6) + (beta - j) * 16 + j;
+  }
+}
+
+// the 15 output twiddles w^(r1 + 4 r2), w = w_L^j: tw[4 r1 + r2]
+__device__ __forceinline__ void rv_tw16(const double2 w1, double2* tw) {
+  const double2 a2 = rv_cmul(w1, w1), a3 = rv_cmul(a2, w1);
+  const double2 b1 = rv_cmul(a2, a2), b2 = rv_cmul(b1, b1), b3 = rv_cmul(b2, b1);
+  tw[0] = make_double2(1.0, 0.0); tw[1] = b1; tw[2] = b2; tw[3] = b3;
+  tw[4] = w1; tw[5] = rv_cmul(w1, b1); tw[6] = rv_cmul(w1, b2); tw[7] = rv_cmul(w1, b3);
+  tw[8] = a2; tw[9] = rv_cmul(a2, b1); tw[10] = rv_cmul(a2, b2); tw[11] = rv_cmul(a2, b3);
+  tw[12] = a3; tw[13] = rv_cmul(a3, b1); tw[14] = rv_cmul(a3, b2); tw[15] = rv_cmul(a3, b3);
+}
+
+__device__ __forceinline__ void rv_pass16_fwd(double2* z, const int F, const int logF, const int L, const double2* stw) {
+  const int q16 = L >> 4, mul = F / L, na = F >> 6;
+  for (int t = threadIdx.x; t < (F >> 4); t += blockDim.x) {
+    int j, base;
+    rv_bfly16_index(t, q16, logF, j, base);
+    double2 v[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) v[r] = z[RVI(base + r * q16)];
+#pragma unroll
+    for (int sI = 0; sI < 4; ++sI) {  // stage A over m: v[sI + 4m]
+      rv_bfly4_fwd(v[sI], v[sI + 4], v[sI + 8], v[sI + 12]);
+      if (sI > 0) {
+        v[sI + 4] = rv_cmul(v[sI + 4], rv_w16(1 * sI));
+        v[sI + 8] = (2 * sI == 4) ? make_double2(v[sI + 8].y, -v[sI + 8].x) : rv_cmul(v[sI + 8], rv_w16(2 * sI));
+        v[sI + 12] = rv_cmul(v[sI + 12], rv_w16(3 * sI));
+      }
+    }
+    // after stage A, v[sI + 4 r1] = y[s][r1]; stage B over s for each r1
+#pragma unroll
+    for (int r1 = 0; r1 < 4; ++r1) rv_bfly4_fwd(v[4 * r1], v[4 * r1 + 1], v[4 * r1 + 2], v[4 * r1 + 3]);
+    if (q16 > 1) {
+      double2 tw[16];
+      rv_tw16(rv_tw(stw, na, j * mul), tw);
+#pragma unroll
+      for (int r = 1; r < 16; ++r) v[r] = rv_cmul(v[r], tw[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < 16; ++r) z[RVI(base + r * q16)] = v[r];
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void rv_pass16_inv(double2* z, const int F, const int logF, const int L, const double2* stw) {
+  const int q16 = L >> 4, mul = F / L, na = F >> 6;
+  for (int t = threadIdx.x; t < (F >> 4); t += blockDim.x) {
+    int j, base;
+    rv_bfly16_index(t, q16, logF, j, base);
+    double2 v[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) v[r] = z[RVI(base + r * q16)];
+    if (q16 > 1) {
+      double2 tw[16];
+      rv_tw16(rv_tw(stw, na, j * mul), tw);
+#pragma unroll
+      for (int r = 1; r < 16; ++r) v[r] = rv_cmulc(v[r], tw[r]);
+    }
+#pragma unroll
+    for (int r1 = 0; r1 < 4; ++r1) rv_bfly4_inv(v[4 * r1], v[4 * r1 + 1], v[4 * r1 + 2], v[4 * r1 + 3]);
+#pragma unroll
+    for (int sI = 0; sI < 4; ++sI) {
+      if (sI > 0) {
+        v[sI + 4] = rv_cmulc(v[sI + 4], rv_w16(1 * sI));
+        v[sI + 8] = (2 * sI == 4) ? make_double2(-v[sI + 8].y, v[sI + 8].x) : rv_cmulc(v[sI + 8], rv_w16(2 * sI));
+        v[sI + 12] = rv_cmulc(v[sI + 12], rv_w16(3 * sI));
+      }
+      rv_bfly4_inv(v[sI], v[sI + 4], v[sI + 8], v[sI + 12]);
+    }
+#pragma unroll
+    for (int r = 0; r < 16; ++r) z[RVI(base + r * q16)] = v[r];
+  }
+  __syncthreads();
+}
+
 // In-place forward FFT of z[0..F): natural order in, digit-reversed order out (radix 4, one leading radix-2 pass
 // when log2 F is odd).  Ends with a __syncthreads().
+template <bool kR16>
 __device__ void rv_fft_dif(double2* z, const int F, const int logF, const double2* stw) {
   const int na = F >> 6;
   int L = F;
@@ -109,6 +238,10 @@ __device__ void rv_fft_dif(double2* z, const int F, const int logF, const double
     }
     L = half;
     __syncthreads();
+  }
+  while (kR16 && L >= 16) {
+    rv_pass16_fwd(z, F, logF, L, stw);
+    L >>= 4;
   }
   while (L >= 4) {
     const int q = L >> 2, mul = F / L;
@@ -141,10 +274,19 @@ __device__ void rv_fft_dif(double2* z, const int F, const int logF, const double
 }
 
 // In-place inverse of rv_fft_dif without the 1/F factor: digit-reversed order in, natural order out.
+template <bool kR16>
 __device__ void rv_fft_dit_inv(double2* z, const int F, const int logF, const double2* stw) {
   const int na = F >> 6;
   const int Ltop = (logF & 1) ? (F >> 1) : F;
-  for (int L = 4; L <= Ltop; L <<= 2) {
+  // the forward transform fuses pairs of radix-4 passes from the top: spans Ltop, Ltop/16, ...; a single radix-4 pass of
+  // span 4 is left when Ltop is an odd power of 4
+  int L0 = 4;
+  if (kR16) {
+    int Lf = Ltop;
+    while (Lf >= 16) Lf >>= 4;  // Lf = 4 (a radix-4 pass of span 4 remains) or 1
+    L0 = (Lf == 4) ? 8 : 1;     // 8: run the span-4 pass below, then the fused ones; 1: fused passes only
+  }
+  for (int L = 4; L <= (kR16 ? (L0 == 8 ? 4 : 0) : Ltop); L <<= 2) {
     const int q = L >> 2, mul = F / L;
     for (int t = threadIdx.x; t < (F >> 2); t += blockDim.x) {
       int j, base;
@@ -167,6 +309,9 @@ __device__ void rv_fft_dit_inv(double2* z, const int F, const int logF, const do
       z[i3] = rv_sub(s1, s3);
     }
     __syncthreads();
+  }
+  if (kR16) {
+    for (int L = (L0 == 8) ? 64 : 16; L <= Ltop; L <<= 4) rv_pass16_inv(z, F, logF, L, stw);
   }
   if (logF & 1) {
     const int half = F >> 1;
@@ -193,7 +338,7 @@ __device__ __forceinline__ double2* rv_stage_tables(const RvArgs& a, unsigned ch
 // CTAs [0, n_pair) take j >= 0; the remaining n_utt (P-1) CTAs the P-1 windows before the utterance, whose real half
 // is zero.  Row of Z_j of utterance u: pair_off[u] + u (P-1) + j + P-1.
 template <typename S>
-__global__ void __launch_bounds__(kRvThreads) rv_fwd_kernel(const RvArgs a) {
+__global__ void __launch_bounds__(kRvThreads, FDLP_RV_MINB) rv_fwd_kernel(const RvArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double2* z = reinterpret_cast<double2*>(smem_raw);
   const double2* stw = rv_stage_tables(a, smem_raw);
@@ -227,13 +372,13 @@ __global__ void __launch_bounds__(kRvThreads) rv_fwd_kernel(const RvArgs a) {
     z[RVI(i)] = make_double2(va, vb);
   }
   __syncthreads();
-  rv_fft_dif(z, a.F, a.logF, stw);
+  rv_fft_dif<false>(z, a.F, a.logF, stw);
   double2* Z = a.X + ((size_t)a.utt_pair_off[u] + (size_t)u * (a.P - 1) + (size_t)(j + a.P - 1)) * a.F;
   for (int i = threadIdx.x; i < a.F; i += blockDim.x) Z[i] = z[RVI(i)];
 }
 
 // spectra of the impulse-response partitions: H_q = FFT([h[qB .. qB+B), 0 .. 0]); rir is a device float64 array
-__global__ void __launch_bounds__(kRvThreads) rv_rir_kernel(const RvArgs a, const double* __restrict__ rir, double2* H) {
+__global__ void __launch_bounds__(kRvThreads, FDLP_RV_MINB) rv_rir_kernel(const RvArgs a, const double* __restrict__ rir, double2* H) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double2* z = reinterpret_cast<double2*>(smem_raw);
   const double2* stw = rv_stage_tables(a, smem_raw);
@@ -243,19 +388,20 @@ __global__ void __launch_bounds__(kRvThreads) rv_rir_kernel(const RvArgs a, cons
     z[RVI(i)] = make_double2((i < a.B && j < a.R) ? rir[j] : 0.0, 0.0);
   }
   __syncthreads();
-  rv_fft_dif(z, a.F, a.logF, stw);
+  rv_fft_dif<false>(z, a.F, a.logF, stw);
   for (int i = threadIdx.x; i < a.F; i += blockDim.x) H[(size_t)q * a.F + i] = z[RVI(i)];
 }
 
 // Blocks b and b + D of the full convolution (real and imaginary half of one transform) and the packed spectrum of
 // the zero-padded pair.  A CTA takes kM (1 or 2) consecutive pairs: the P + kM - 1 spectra Z they share are read
 // once per bin, the accumulators of the later pairs wait in registers while the first goes through the transforms.
-constexpr int kRvMaxBins = 16;  // F <= 8192, 512 threads
+constexpr int kRvMaxBins = 8192 / kRvThreads;  // F <= 8192
 
+template <bool kR16>
 __device__ __forceinline__ void rv_conv_finish(const RvArgs& a, double2* z, const double2* stw, const int u, const int b,
                                                const int D, const int64_t full_len) {
   const int F = a.F, B = a.B;
-  rv_fft_dit_inv(z, F, a.logF, stw);
+  rv_fft_dit_inv<kR16>(z, F, a.logF, stw);
   const double inv = 1.0 / (double)F;
   double* full = a.full + (size_t)2 * a.utt_pair_off[u] * B;
   for (int i = threadIdx.x; i < B; i += blockDim.x) {  // a thread touches only z[i] and z[B + i]
@@ -269,13 +415,13 @@ __device__ __forceinline__ void rv_conv_finish(const RvArgs& a, double2* z, cons
     z[RVI(B + i)] = make_double2(0.0, 0.0);
   }
   __syncthreads();
-  rv_fft_dif(z, F, a.logF, stw);
+  rv_fft_dif<kR16>(z, F, a.logF, stw);
   double2* O = a.O + ((size_t)a.utt_pair_off[u] + b) * F;
   for (int i = threadIdx.x; i < F; i += blockDim.x) O[i] = z[RVI(i)];
 }
 
 template <int kBins, int kM>
-__global__ void __launch_bounds__(kRvThreads) rv_conv_kernel(const RvArgs a) {
+__global__ void __launch_bounds__(kRvThreads, FDLP_RV_MINB) rv_conv_kernel(const RvArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double2* z = reinterpret_cast<double2*>(smem_raw);
   const double2* stw = rv_stage_tables(a, smem_raw);
@@ -289,12 +435,25 @@ __global__ void __launch_bounds__(kRvThreads) rv_conv_kernel(const RvArgs a) {
   // row of Z_{b0 - q}, q = -1 .. P-1 (q = -1 is the newest window, used by pair b0 + 1 only)
   const double2* __restrict__ Zb = a.X + ((size_t)a.utt_pair_off[u] + (size_t)u * (P - 1) + (size_t)(b0 + P - 1)) * F;
   double2 held[kM == 2 ? kBins : 1];
-#pragma unroll
-  for (int i = 0; i < kBins; ++i) {
-    const int k = threadIdx.x + i * kRvThreads;
-    if (k < F) {
+  if constexpr (kM == 1) {  // any thread count (launched with 256 threads at F <= 4096)
+    for (int k = threadIdx.x; k < F; k += blockDim.x) {
       double2 acc0 = make_double2(0.0, 0.0), acc1 = acc0;
-      if constexpr (kM == 2) {
+      int q = 0;
+      for (; q + 1 < P; q += 2) {
+        const double2 h0 = __ldg(a.H + (size_t)q * F + k), z0 = __ldg(Zb - (size_t)q * F + k);
+        const double2 h1 = __ldg(a.H + (size_t)(q + 1) * F + k), z1 = __ldg(Zb - (size_t)(q + 1) * F + k);
+        acc0 = rv_add(acc0, rv_cmul(z0, h0));
+        acc1 = rv_add(acc1, rv_cmul(z1, h1));
+      }
+      if (q < P) acc0 = rv_add(acc0, rv_cmul(__ldg(Zb - (size_t)q * F + k), __ldg(a.H + (size_t)q * F + k)));
+      z[RVI(k)] = rv_add(acc0, acc1);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < kBins; ++i) {
+      const int k = threadIdx.x + i * kRvThreads;
+      if (k < F) {
+        double2 acc0 = make_double2(0.0, 0.0), acc1 = acc0;
         double2 znew = two ? __ldg(Zb + (size_t)F + k) : make_double2(0.0, 0.0);
         for (int q = 0; q < P; ++q) {
           const double2 h = __ldg(a.H + (size_t)q * F + k);
@@ -304,22 +463,12 @@ __global__ void __launch_bounds__(kRvThreads) rv_conv_kernel(const RvArgs a) {
           znew = zc;
         }
         held[i] = acc1;
-      } else {
-        int q = 0;
-        for (; q + 1 < P; q += 2) {
-          const double2 h0 = __ldg(a.H + (size_t)q * F + k), z0 = __ldg(Zb - (size_t)q * F + k);
-          const double2 h1 = __ldg(a.H + (size_t)(q + 1) * F + k), z1 = __ldg(Zb - (size_t)(q + 1) * F + k);
-          acc0 = rv_add(acc0, rv_cmul(z0, h0));
-          acc1 = rv_add(acc1, rv_cmul(z1, h1));
-        }
-        if (q < P) acc0 = rv_add(acc0, rv_cmul(__ldg(Zb - (size_t)q * F + k), __ldg(a.H + (size_t)q * F + k)));
-        acc0 = rv_add(acc0, acc1);
+        z[RVI(k)] = acc0;
       }
-      z[RVI(k)] = acc0;
     }
   }
   __syncthreads();
-  rv_conv_finish(a, z, stw, u, b0, D, full_len);
+  rv_conv_finish<kM == 1>(a, z, stw, u, b0, D, full_len);
   if constexpr (kM == 2) {
     if (two) {
       __syncthreads();
@@ -329,7 +478,7 @@ __global__ void __launch_bounds__(kRvThreads) rv_conv_kernel(const RvArgs a) {
         if (k < F) z[RVI(k)] = held[i];
       }
       __syncthreads();
-      rv_conv_finish(a, z, stw, u, b0 + 1, D, full_len);
+      rv_conv_finish<false>(a, z, stw, u, b0 + 1, D, full_len);
     }
   }
 }
@@ -341,7 +490,7 @@ __global__ void __launch_bounds__(kRvThreads) rv_conv_kernel(const RvArgs a) {
 // part.  grid = (ceil(F / threads), ceil(P / kQ), n_utt); L2/HBM-bound streaming of 2 D rows per utterance and group.
 constexpr int kRvQ = 8;
 
-__global__ void __launch_bounds__(kRvThreads) rv_corr_mac_kernel(const RvArgs a) {
+__global__ void __launch_bounds__(kRvThreads, FDLP_RV_MINB) rv_corr_mac_kernel(const RvArgs a) {
   const int k = blockIdx.x * kRvThreads + threadIdx.x;
   const int q0 = blockIdx.y * kRvQ, u = blockIdx.z;
   const int F = a.F, P = a.P;
@@ -373,7 +522,7 @@ __global__ void __launch_bounds__(kRvThreads) rv_corr_mac_kernel(const RvArgs a)
 
 // One (utterance, lag partition q): xxc at lags d in [qB, qB + B) from C_q and its maximum (ties: the largest d, which
 // is the first index of the reference's xxc, i = R - 1 - d).
-__global__ void __launch_bounds__(kRvThreads) rv_corr_kernel(const RvArgs a) {
+__global__ void __launch_bounds__(kRvThreads, FDLP_RV_MINB) rv_corr_kernel(const RvArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double2* z = reinterpret_cast<double2*>(smem_raw);
   const double2* stw = rv_stage_tables(a, smem_raw);
@@ -382,7 +531,7 @@ __global__ void __launch_bounds__(kRvThreads) rv_corr_kernel(const RvArgs a) {
   const double2* __restrict__ C = a.C + ((size_t)u * a.P + q) * F;
   for (int k = threadIdx.x; k < F; k += blockDim.x) z[RVI(k)] = C[k];
   __syncthreads();
-  rv_fft_dit_inv(z, F, a.logF, stw);
+  rv_fft_dit_inv<false>(z, F, a.logF, stw);
   double best = -INFINITY;
   int best_d = -1;
   for (int e = 1 + threadIdx.x; e <= B; e += blockDim.x) {

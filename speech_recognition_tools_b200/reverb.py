@@ -44,6 +44,20 @@ def load_rir(add_reverb: str, rir_dir: Optional[str] = None) -> Optional[np.ndar
     return rir[:, 1] / np.power(2, 15)
 
 
+def block_layout(lengths: Sequence[int], R: int, block: int, pairs_per_cta: int = 1):
+    """Index tables of a packed batch for fdlp_reverb_forward (include/fdlp_b200.h): utterance u has
+    ceil((T_u + R - 1) / block) blocks of the full convolution, two to a complex transform:
+    D_u = ceil(blocks / 2) pairs and ceil(D_u / pairs_per_cta) convolution CTAs.
+    Returns (utt_pair_off [n+1], pair_utt [sum D], utt_conv_off [n+1], conv_utt [sum CTAs]), all int32."""
+    lengths = np.asarray(lengths, dtype=np.int64)
+    nb = (lengths + R - 1 + block - 1) // block
+    D = (nb + 1) // 2
+    nc = (D + pairs_per_cta - 1) // pairs_per_cta
+    ids = np.arange(len(lengths), dtype=np.int32)
+    return (np.concatenate([[0], np.cumsum(D)]).astype(np.int32), np.repeat(ids, D).astype(np.int32),
+            np.concatenate([[0], np.cumsum(nc)]).astype(np.int32), np.repeat(ids, nc).astype(np.int32))
+
+
 class Reverberator:
     """One impulse response on one device.  `forward_packed` reverberates a packed device batch; calling the object
     with a list of waveforms returns a list of float64 device tensors."""
@@ -90,15 +104,7 @@ class Reverberator:
         return int(self._lib.fdlp_reverb_plan_scratch_bytes(self._plan, int(n_pair), int(n_utt)))
 
     def block_layout(self, lengths: Sequence[int]):
-        """Tables of a batch: D_u = ceil(ceil((T_u + R - 1) / block) / 2) block pairs per utterance and
-        ceil(D_u / pairs_per_cta) convolution CTAs.  Returns (utt_pair_off, pair_utt, utt_conv_off, conv_utt)."""
-        lengths = np.asarray(lengths, dtype=np.int64)
-        nb = (lengths + self.rir.size - 1 + self.block - 1) // self.block
-        D = (nb + 1) // 2
-        nc = (D + self.pairs_per_cta - 1) // self.pairs_per_cta
-        ids = np.arange(len(lengths), dtype=np.int32)
-        return (np.concatenate([[0], np.cumsum(D)]).astype(np.int32), np.repeat(ids, D).astype(np.int32),
-                np.concatenate([[0], np.cumsum(nc)]).astype(np.int32), np.repeat(ids, nc).astype(np.int32))
+        return block_layout(lengths, self.rir.size, self.block, self.pairs_per_cta)
 
     def forward_packed(self, wav_dev: torch.Tensor, lengths: Sequence[int], utt_wav_off_dev: Optional[torch.Tensor] = None,
                        noise_dev=None, out_dtype=torch.float64):

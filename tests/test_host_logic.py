@@ -110,3 +110,20 @@ def test_synth_is_deterministic_and_never_silent():
     assert s.dtype == np.int16 and np.abs(s).max() > 1000
     for k in range(0, 48000 - 8000, 6000):
         assert np.any(s[k:k + 8000] != 0)
+
+
+def test_reverb_block_layout_covers_the_full_convolution():
+    """Host tables of fdlp_reverb_forward: the pairs of an utterance cover all T + R - 1 samples of the full
+    convolution (features.py:111), owners and prefix sums are consistent."""
+    from speech_recognition_tools_b200.reverb import block_layout, load_rir
+    lengths = np.array([2, 63, 64, 65, 2048, 2049, 40001, 240000])
+    for R, B, m in ((1, 64, 1), (3, 64, 1), (700, 128, 2), (16000, 2048, 1), (48000, 4096, 2)):
+        pair_off, pair_utt, conv_off, conv_utt = block_layout(lengths, R, B, m)
+        D = np.diff(pair_off)
+        assert np.all(2 * D * B >= lengths + R - 1) and np.all(2 * (D - 1) * B < lengths + R - 1 + B)
+        assert np.array_equal(np.bincount(pair_utt, minlength=len(lengths)), D)
+        assert np.array_equal(np.diff(conv_off), -(-D // m))
+        assert np.array_equal(np.bincount(conv_utt, minlength=len(lengths)), np.diff(conv_off))
+    assert load_rir(None) is None and load_rir("clean") is None
+    with pytest.raises(ValueError):  # computeFDLPSpectrogram.py:90-91
+        load_rir("cathedral")
