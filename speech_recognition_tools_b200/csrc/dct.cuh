@@ -342,7 +342,7 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
     const int64_t g0 = woff + q_base;  // global sample index of window sample 0 (may be < 0)
     const int sh = (int)(((g0 % 2) + 2) % 2);
     const int npair = (N + sh + 1) / 2;
-    const bool pair_ok = a.vec_ok && !nz;
+    const bool pair_ok = a.vec_ok;  // with noise mixing the noise excerpt (arbitrary offset) is read with scalar loads
     const double2 hd0 = sham[a.ham_na + ((2 * (int)threadIdx.x - sh) & 63)];
     const double2 hd1 = sham[a.ham_na + ((2 * (int)threadIdx.x - sh + 1) & 63)];
     for (int pb = threadIdx.x; pb < npair; pb += blockDim.x * kLdBatch) {
@@ -382,6 +382,17 @@ __global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
           const double2 raw = fast[e] ? __ldg(reinterpret_cast<const double2*>(sig + q0)) : make_double2(0.0, 0.0);
           v0[e] = raw.x; v1[e] = raw.y;
         }
+      }
+      if (nz) {  // sig + alpha * noise (features.py:29-31) on the fast pairs; the loads of a batch are issued together
+        int n0[kLdBatch], n1[kLdBatch];
+#pragma unroll
+        for (int e = 0; e < kLdBatch; ++e) {
+          const int64_t q0 = q_base + 2 * (pb + e * (int)blockDim.x) - sh;
+          n0[e] = fast[e] ? (int)__ldg(nz + q0) : 0;
+          n1[e] = fast[e] ? (int)__ldg(nz + q0 + 1) : 0;
+        }
+#pragma unroll
+        for (int e = 0; e < kLdBatch; ++e) { v0[e] += alpha * (double)n0[e]; v1[e] += alpha * (double)n1[e]; }
       }
 #pragma unroll
       for (int e = 0; e < kLdBatch; ++e) {

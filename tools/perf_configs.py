@@ -45,7 +45,7 @@ def time_steps(fn, steps, warmup):
     return e0.elapsed_time(e1) / steps
 
 
-def run(name, cfg, wavs, noise=None, steps=5, warmup=3, note=""):
+def run(name, cfg, wavs, noise=None, steps=5, warmup=3, note="", rir=None):
     t0 = time.time()
     ex = FdlpExtractor(FdlpConfig(**cfg))
     t_plan = time.time() - t0
@@ -54,6 +54,19 @@ def run(name, cfg, wavs, noise=None, steps=5, warmup=3, note=""):
     wav = host.to(ex.device)
     noise_dev = ex._noise_to_device(noise, lay) if noise is not None else None
     feats = torch.empty((lay.n_frames, cfg["nfilters"]), dtype=torch.float32, device=ex.device)
+    rv_ms = None
+    if rir is not None:  # --add_reverb: noise mix + reverberation (float64 waveform), then the extraction
+        from speech_recognition_tools_b200.reverb import Reverberator
+        rv = Reverberator(rir, device=ex.device)
+
+        def both():
+            w64, _, _ = rv.forward_packed(wav, lens, lay.dev["utt_wav_off"], noise_dev)
+            ex.forward_packed(w64, lay, feats=feats)
+        rv_ms = time_steps(lambda: rv.forward_packed(wav, lens, lay.dev["utt_wav_off"], noise_dev), steps, warmup)
+        total_ms = time_steps(both, steps, warmup)
+        wav, _, _ = rv.forward_packed(wav, lens, lay.dev["utt_wav_off"], noise_dev)
+        noise_dev = None
+        note = (note + "; " if note else "") + "reverberation alone %.2f ms, with the extraction %.2f ms" % (rv_ms, total_ms)
     ms = time_steps(lambda: ex.forward_packed(wav, lay, feats=feats, noise_dev=noise_dev), steps, warmup)
     ex.set_profiling(True)
     ex.forward_packed(wav, lay, feats=feats, noise_dev=noise_dev)
@@ -63,7 +76,8 @@ def run(name, cfg, wavs, noise=None, steps=5, warmup=3, note=""):
     _, status = ex.forward_packed(wav, lay, feats=feats, noise_dev=noise_dev)
     out = {"workload": name, "params": {k: cfg[k] for k in ("nfilters", "order", "fduration", "coeff_num")},
            "utterances": len(wavs), "audio_s": round(audio, 1), "segments": int(lay.n_seg),
-           "ms_per_step": round(ms, 3), "xRT": round(audio / ms * 1e3), "stage_ms": stage,
+           "ms_per_step": round(ms + (rv_ms or 0.0), 3), "xRT": round(audio / (ms + (rv_ms or 0.0)) * 1e3),
+           "reverb_ms": None if rv_ms is None else round(rv_ms, 3), "stage_ms": stage,
            "plan_create_s": round(t_plan, 2), "dct_is_fp64": int(ex.geom["dct_is_fp64"]),
            "flagged_utts": int((status != 0).sum().item()), "finite": bool(torch.isfinite(feats).all().item()),
            "note": note}
@@ -115,6 +129,10 @@ def main():
                            noise=NoiseSpec(noise, snr, rand=np.random.RandomState(5), mode=mode),
                            note="one noise recording per job as in the reference (--add_noise type,snr); per-stream snr"))
         res.append(run("cfg3 REVERB recipe, 125 x 8 channel streams, clean", REVERB, wavs))
+        rir = synth.rir_int16("large_room", 16000)[:, 1] / 2.0 ** 15
+        res.append(run("cfg3 REVERB recipe, 125 x 8 channel streams, noise mix (float) then --add_reverb (1 s response)",
+                       REVERB, wavs, noise=NoiseSpec(noise, snr, rand=np.random.RandomState(5), mode="float"), rir=rir,
+                       note="synthetic room response (synth.rir_int16); one response per job as in the reference"))
     if "4" in which:
         wavs = [synth.make_utterance("speechlike" if u % 2 else "white", 9, u, 480000, 30.0) for u in range(256)]
         for fdur, J, p, C in ((1.5, 80, 150, 100), (2.0, 128, 300, 300), (3.0, 128, 300, 300)):
