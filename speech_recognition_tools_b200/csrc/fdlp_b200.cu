@@ -1637,8 +1637,8 @@ extern "C" int fdlp_reverb_forward(fdlp_reverb_plan* p, const fdlp_reverb_batch*
     cudaFree(p->d_X); cudaFree(p->d_O); cudaFree(p->d_full); cudaFree(p->d_pmax); cudaFree(p->d_parg); cudaFree(p->d_alpha);
     cudaFree(p->d_C);
     p->d_X = p->d_O = p->d_C = nullptr; p->d_full = nullptr; p->d_pmax = nullptr; p->d_parg = nullptr; p->d_alpha = nullptr;
+    const int np = std::max(b->n_pair, p->cap_blk), nu = std::max(b->n_utt, p->cap_utt);  // capacities only grow
     p->cap_blk = p->cap_utt = 0;
-    const int np = std::max(b->n_pair, p->cap_blk), nu = std::max(b->n_utt, p->cap_utt);
     FDLP_CUDA(cudaMalloc((void**)&p->d_X, ((size_t)np + (size_t)nu * (p->P - 1)) * p->F * sizeof(double2)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_O, (size_t)np * p->F * sizeof(double2)));
     FDLP_CUDA(cudaMalloc((void**)&p->d_full, (size_t)2 * np * p->B * sizeof(double)));

@@ -121,3 +121,16 @@ def test_cli_add_reverb_reads_rir_directory(tmp_path):
     assert load_rir("clean") is None and load_rir(None) is None
     with pytest.raises(ValueError):
         load_rir("cathedral")
+
+
+def test_one_plan_serves_batches_of_changing_shape():
+    """The plan's scratch grows on demand (pairs and utterances independently): a long utterance, many short ones,
+    the long one again -- every result equal to the oracle's."""
+    rir = synth.rir_int16("small_room", 600)[:, 1] / 2.0 ** 15
+    rv = reverberator(rir, 128)
+    long_wav = [synth.make_utterance("white", 50, 0, 30000)]
+    short = [synth.make_utterance("white", 50, 1 + i, 200 + 7 * i) for i in range(60)]
+    for wavs in (long_wav, short, long_wav, short[:3]):
+        outs = rv(wavs)
+        for x, o in zip(wavs, outs):
+            assert_wave_close(o.cpu().numpy(), oreverb.add_reverb(x, rir))
