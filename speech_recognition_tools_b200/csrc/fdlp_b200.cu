@@ -225,6 +225,9 @@ struct fdlp_plan {
   int na = 0, a_groups = 1;  // autocorrelation lag blocking
   int pad = 0, ld = 0;       // circular extension (doubles) and row stride of the DCT / filterbank buffers
   bool dct_fp64 = true;
+  // envelope -> overlap-add hand-over in float32 (half the traffic of the largest intermediate; the output is float32
+  // and a frame sums at most two envelope values, so this costs ~1e-7 in the log features); FDLP_ENV_F64=1 for A/B runs
+  bool env_f32 = getenv("FDLP_ENV_F64") == nullptr;
   int dct_threads = 512;     // threads per DCT CTA (chosen for the butterfly counts of the passes)
   bool dct_half = false;     // float64 DCT with two CTAs per segment (dct_half_kernel): N float64 exceed shared memory
   FftTables fft_half;        // plan of the N/4-point sub-transforms
@@ -696,7 +699,8 @@ extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
     SET_SMEM((dct_segments_kernel<float, double>), p->dct_smem);
   }
   SET_SMEM(lpc_cepstrum_kernel, p->lpc_smem);
-  SET_SMEM(ola_log_kernel, p->ola_smem);
+  SET_SMEM(ola_log_kernel<float>, p->ola_smem);
+  SET_SMEM(ola_log_kernel<double>, p->ola_smem);
 #define SET_AC(NA_)                                                                     \
   case NA_:                                                                             \
     if (p->a_groups > 1) SET_SMEM((autocorr_dmma_kernel<NA_, true>), p->ac_smem);       \
@@ -914,8 +918,8 @@ static int launch_autocorr(fdlp_plan* p, const double* dct, int n_seg, double* r
 }
 
 static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out, double* gain_out, double* cep_out,
-                      double* env, int32_t* status, const int32_t* seg_utt, cudaStream_t st, size_t task0 = 0,
-                      int grid_cap = 0) {
+                      void* env, int32_t* status, const int32_t* seg_utt, cudaStream_t st, size_t task0 = 0,
+                      int grid_cap = 0, bool env_f32 = false) {
   LpcArgs a;
   a.r = r; a.n_tasks = n_seg * p->prm.nfilters; a.J = p->prm.nfilters;
   a.order = p->prm.order; a.nlags = p->g.nlags; a.L = p->g.L; a.Lp = p->Lp;
@@ -955,7 +959,8 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
   e.ms = a.ms; e.basis = p->d_basis; e.wratio = p->d_wratio; e.env = env;
   e.n_tasks = a.n_tasks; e.Lp = p->Lp; e.ldb = p->ldb; e.kk = p->g.kk;
   const dim3 grid((a.n_tasks + 8 * kEnvMA * kEnvWarps - 1) / (8 * kEnvMA * kEnvWarps), p->env_ny);
-  envelope_dmma_kernel<10><<<grid, kEnvWarps * 32, 0, st>>>(e);
+  if (env_f32) envelope_dmma_kernel<10, float><<<grid, kEnvWarps * 32, 0, st>>>(e);
+  else envelope_dmma_kernel<10, double><<<grid, kEnvWarps * 32, 0, st>>>(e);
   FDLP_CUDA(cudaGetLastError());
   return 0;
 }
@@ -1002,7 +1007,8 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
     if (prof) FDLP_CUDA(cudaEventRecord(p->ev[1], st));
     if ((rc = launch_autocorr(p, p->d_dct, b->n_seg, p->d_r, st, prof))) return rc;
     if (prof) FDLP_CUDA(cudaEventRecord(p->ev[2], st));
-    if ((rc = launch_lpc(p, p->d_r, b->n_seg, nullptr, nullptr, nullptr, p->d_env, b->status, b->seg_utt, st))) return rc;
+    if ((rc = launch_lpc(p, p->d_r, b->n_seg, nullptr, nullptr, nullptr, p->d_env, b->status, b->seg_utt, st, 0, 0,
+                         p->env_f32))) return rc;
     if (prof) FDLP_CUDA(cudaEventRecord(p->ev[3], st));
   } else {
     // The serial recursions of K4 are latency bound and leave the FP64 pipe idle; K3 saturates it.  Chunks of
@@ -1018,8 +1024,10 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
       if ((rc = launch_autocorr(p, dct_c, ns, r_c, st))) return rc;
       FDLP_CUDA(cudaEventRecord(p->ev_chunk[c], st));
       FDLP_CUDA(cudaStreamWaitEvent(p->side, p->ev_chunk[c], 0));
-      if ((rc = launch_lpc(p, r_c, ns, nullptr, nullptr, nullptr, p->d_env + (size_t)s0 * J * p->g.kk, b->status,
-                           b->seg_utt + s0, p->side, (size_t)s0 * J, p->overlap_cap))) return rc;
+      void* env_c = p->env_f32 ? (void*)((float*)p->d_env + (size_t)s0 * J * p->g.kk)
+                               : (void*)(p->d_env + (size_t)s0 * J * p->g.kk);
+      if ((rc = launch_lpc(p, r_c, ns, nullptr, nullptr, nullptr, env_c, b->status,
+                           b->seg_utt + s0, p->side, (size_t)s0 * J, p->overlap_cap, p->env_f32))) return rc;
     }
     FDLP_CUDA(cudaEventRecord(p->ev_side, p->side));
     FDLP_CUDA(cudaStreamWaitEvent(st, p->ev_side, 0));
@@ -1032,7 +1040,8 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
   if (max_tiles < 1) max_tiles = 1;
   if (max_tiles > 65535) return set_err(FDLP_E_ARG, "utterance too long%s", "");
   const dim3 grid(b->n_utt, (unsigned)max_tiles), block(256);
-  ola_log_kernel<<<grid, block, p->ola_smem, st>>>(o);
+  if (p->env_f32) ola_log_kernel<float><<<grid, block, p->ola_smem, st>>>(o);
+  else ola_log_kernel<double><<<grid, block, p->ola_smem, st>>>(o);
   FDLP_CUDA(cudaGetLastError());
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[4], st));
   return FDLP_OK;

@@ -694,7 +694,7 @@ struct EnvArgs {
   const double* ms;      // [n_tasks_padded, Lp]
   const double* basis;   // [Lp, ldb]
   const double* wratio;  // [kk]
-  double* env;           // [n_tasks, kk]
+  void* env;             // [n_tasks, kk], float64 (stage API) or float32 (hand-over to the overlap-add kernel)
   int n_tasks, Lp, ldb, kk;
 };
 
@@ -702,8 +702,9 @@ constexpr int kEnvWarps = 4;
 
 constexpr int kEnvMA = 2;  // 8-task row blocks per warp: every basis fragment feeds kEnvMA DMMAs
 
-template <int NT>
+template <int NT, typename ET>
 __global__ void __launch_bounds__(kEnvWarps * 32) envelope_dmma_kernel(const EnvArgs a) {
+  ET* __restrict__ env = reinterpret_cast<ET*>(a.env);
   constexpr int MA = kEnvMA;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int lr = lane & 3, lc = lane >> 2;
@@ -754,8 +755,8 @@ __global__ void __launch_bounds__(kEnvWarps * 32) envelope_dmma_kernel(const Env
 #pragma unroll
       for (int i = 0; i < NT; ++i) {
         const int t = t_base + 8 * i + 2 * lr;
-        if (t < a.kk) a.env[(size_t)task * a.kk + t] = exp(acc[m][i][0]) * __ldg(a.wratio + t);
-        if (t + 1 < a.kk) a.env[(size_t)task * a.kk + t + 1] = exp(acc[m][i][1]) * __ldg(a.wratio + t + 1);
+        if (t < a.kk) env[(size_t)task * a.kk + t] = (ET)(exp(acc[m][i][0]) * __ldg(a.wratio + t));
+        if (t + 1 < a.kk) env[(size_t)task * a.kk + t + 1] = (ET)(exp(acc[m][i][1]) * __ldg(a.wratio + t + 1));
       }
     }
   }

@@ -16,7 +16,7 @@
 namespace fdlp {
 
 struct OlaArgs {
-  const double* env;             // [n_seg, J, kk]
+  const void* env;               // [n_seg, J, kk] float32 (fdlp_forward) or float64
   const int32_t* utt_seg_off;    // [n_utt+1]
   const int64_t* utt_frame_off;  // [n_utt+1]
   const int32_t* seg_ptr;        // [n_seg]
@@ -27,7 +27,9 @@ struct OlaArgs {
 
 constexpr int kOlaFT = 64;  // frames per block
 
+template <typename ET>
 __global__ void __launch_bounds__(256) ola_log_kernel(const OlaArgs a) {
+  const ET* __restrict__ env = reinterpret_cast<const ET*>(a.env);
   extern __shared__ __align__(16) double tile[];  // [J][FT+1]
   const int u = blockIdx.x;
   const int64_t foff = a.utt_frame_off[u];
@@ -52,10 +54,10 @@ __global__ void __launch_bounds__(256) ola_log_kernel(const OlaArgs a) {
     const int f = f0 + fl;
     double acc = 0.0;
     if (fl < nf) {
-      if (f < d1 && kkb2 + f < kk) acc += a.env[((size_t)s0 * J + j) * kk + kkb2 + f];  // segment 0 first: the reference's order
+      if (f < d1 && kkb2 + f < kk) acc += (double)env[((size_t)s0 * J + j) * kk + kkb2 + f];  // segment 0 first: the reference's order
       for (int i = i_lo; i < i_hi; ++i) {
         const int t = f - a.seg_ptr[s0 + i];
-        if (t >= 0 && t < kk) acc += a.env[((size_t)(s0 + i) * J + j) * kk + t];
+        if (t >= 0 && t < kk) acc += (double)env[((size_t)(s0 + i) * J + j) * kk + t];
       }
     }
     tile[j * LD + fl] = acc;
