@@ -240,11 +240,14 @@ def _as_rngs(jitter, n_utt):
 class NoiseSpec:
     """--add_noise 'type,snr' (features.py:24-44): `samples` is the int16 noise recording, `snr_db` a scalar or
     per-utterance array, `rand` the per-utterance uniform draws standing for `np.random.rand()` (or a
-    np.random.RandomState consumed sequentially, or an int seed)."""
-    samples: Union[np.ndarray, torch.Tensor]
+    np.random.RandomState consumed sequentially, or an int seed).  A multi-condition batch (REVERB-shaped streams,
+    one noise type per stream) passes a LIST of recordings as `samples` and `which[u]` = the recording of utterance u;
+    the reference takes one `type,snr` per job, so such a batch equals one reference job per stream."""
+    samples: Union[np.ndarray, torch.Tensor, Sequence[Union[np.ndarray, torch.Tensor]]]
     snr_db: Union[float, Sequence[float]]
     rand: Union[None, int, np.random.RandomState, Sequence[float]] = None
     mode: str = "int16_wrap"  # 'int16_wrap' = the reference's numpy dtype semantics; 'float' = true energies
+    which: Optional[Sequence[int]] = None
 
 
 # --------------------------------------------------------------------------- extractor
@@ -398,12 +401,17 @@ class FdlpExtractor:
     def _noise_to_device(self, noise: Optional[NoiseSpec], lay: BatchLayout):
         if noise is None:
             return None
-        ns = noise.samples
-        if not isinstance(ns, torch.Tensor):
-            ns = torch.from_numpy(np.ascontiguousarray(ns))
-        if ns.dtype != torch.int16:
+        recs = noise.samples if isinstance(noise.samples, (list, tuple)) else [noise.samples]
+        recs = [r if isinstance(r, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(r)) for r in recs]
+        if any(r.dtype != torch.int16 or r.dim() != 1 for r in recs):
             raise TypeError("noise recording must be int16 (scipy.io.wavfile.read of noises/<type>.wav)")
         n_utt = lay.n_utt
+        which = np.zeros(n_utt, dtype=np.int64) if noise.which is None else np.asarray(noise.which, dtype=np.int64)
+        if which.shape != (n_utt,) or (n_utt and (which.min() < 0 or which.max() >= len(recs))):
+            raise ValueError("NoiseSpec.which needs one recording index per utterance")
+        rec_len = np.array([int(r.numel()) for r in recs], dtype=np.int64)
+        rec_base = np.concatenate([[0], np.cumsum(rec_len)])[:-1]
+        ns = recs[0] if len(recs) == 1 else torch.cat(recs)
         rand = noise.rand
         if rand is None or isinstance(rand, (int, np.integer)):
             rand = np.random.RandomState(0 if rand is None else int(rand))
@@ -411,10 +419,10 @@ class FdlpExtractor:
             draws = np.array([rand.rand() for _ in range(n_utt)])
         else:
             draws = np.asarray(list(rand), dtype=np.float64)
-        Tn = int(ns.numel())
-        if n_utt and Tn <= int(lay.lengths.max()):
+        Tn = rec_len[which]
+        if n_utt and np.any(Tn <= lay.lengths):
             raise ValueError("noise recording must be longer than every utterance (features.py:25-26)")
-        off = np.floor(draws * (Tn - lay.lengths)).astype(np.int64)  # features.py:25
+        off = rec_base[which] + np.floor(draws * (Tn - lay.lengths)).astype(np.int64)  # features.py:25
         snr = np.broadcast_to(np.asarray(noise.snr_db, dtype=np.float64), (n_utt,)).copy()
         mode = {"int16_wrap": L.FDLP_NOISE_INT16_WRAP, "float": L.FDLP_NOISE_FLOAT}[noise.mode]
         return dict(mode=mode, samples=ns.to(self.device, non_blocking=True),

@@ -107,7 +107,9 @@ def run_reference(kind, params, x, seed, workdir, noise=None):
     return _captured["utt1"]
 
 
-def case(name, kind, params, spec, seed=0, noise=None, extra=None):
+def case(name, kind, params, spec, seed=0, noise=None, extra=None, feats_dtype=None):
+    """feats_dtype="float32": store the reference output rounded to float32 (long utterances: the product's output
+    type, half the fixture size); default float64 as the reference returns it."""
     x = make_input(spec)
     with tempfile.TemporaryDirectory() as d:
         lifter = None
@@ -123,7 +125,7 @@ def case(name, kind, params, spec, seed=0, noise=None, extra=None):
             noise_obj = dict(name=noise["name"], data=synth.noise_int16(noise["name"], noise["T"]))
         out = run_reference(kind, p, x, seed, d, noise_obj)
     meta = dict(name=name, kind=kind, params=params, input=spec, seed=seed, noise=noise, input_sha1=sha(x))
-    arrays = dict(feats=out, meta=np.array(json.dumps(meta)))
+    arrays = dict(feats=out.astype(feats_dtype) if feats_dtype else out, meta=np.array(json.dumps(meta)))
     if extra:
         arrays.update(extra)
     path = os.path.join(HERE, name + ".npz")

@@ -364,3 +364,49 @@ def test_device_white_generator_is_bit_identical_to_numpy():
         host, o = wav.cpu().numpy(), off.cpu().numpy()
         for i, (u, T) in enumerate(zip(ids, lens)):
             assert np.array_equal(host[o[i]:o[i + 1]], synth.white_int16(seed, u, T))
+
+
+def test_reverb_shaped_ragged_batch_with_per_stream_noise():
+    """BASELINE configs[2]: REVERB-recipe streams of different lengths (1, 2, 3 and 5 segments), each with its own
+    noise type, SNR and excerpt offset, mixed in ONE ragged batch through per-stream arrays (features.py:24-44 is
+    one `type,snr` per job: every stream's golden is one run of the unmodified reference)."""
+    from speech_recognition_tools_b200.fdlp import NoiseSpec
+    names = [n for n in golden_cases("fdlp") if n.startswith("fdlp_rvb_stream")]
+    assert len(names) == 4
+    cases = [load_case(n) for n in names]
+    p, _, _ = split_params(cases[0]["meta"])
+    ex = extractor(**dict(FDLP_DEFAULTS, **p))
+    snr = [float(c["meta"]["params"]["add_noise"].split(",")[1]) for c in cases]
+    rand = [np.random.RandomState(c["meta"]["seed"]).rand() for c in cases]
+    spec = NoiseSpec(samples=[c["noise"]["data"] for c in cases], snr_db=snr, rand=rand, which=list(range(4)))
+    outs, st = ex([c["x"] for c in cases], jitter=[c["meta"]["seed"] for c in cases], noise=spec, return_status=True)
+    assert int(st.abs().sum()) == 0
+    for c, o in zip(cases, outs):
+        assert_feats_close(o.cpu().numpy(), c["feats"])
+    # and the reverse order gives the same per-stream results bit for bit (no cross-stream state)
+    rev = NoiseSpec(samples=[c["noise"]["data"] for c in cases][::-1], snr_db=snr[::-1], rand=rand[::-1],
+                    which=list(range(4)))
+    outs2 = ex([c["x"] for c in cases][::-1], jitter=[c["meta"]["seed"] for c in cases][::-1], noise=rev)
+    for a, b in zip(outs, outs2[::-1]):
+        assert torch.equal(a, b)
+
+
+def test_long_utterances_pointer_trace_and_floor_set():
+    """LibriSpeech-shaped lengths (configs[4]): 30 s / 35 s utterances with the WSJ recipe -- the pointer trace of the
+    layout must be the one the reference walks (computeFDLPSpectrogram.py:207-225: +37 after segment 0, then
+    +112 + randrange(2) per segment) and the never-written frames must be exactly the reference's."""
+    ex = extractor(**WSJ)
+    for name in ("fdlp_wsj_speech30_35s", "fdlp_wsj_white_30s"):
+        c = load_case(name)
+        T, seed = len(c["x"]), c["meta"]["seed"]
+        lay = ex.layout([T], jitter=[seed])
+        rng = random.Random(seed)
+        nseg = -(-(T - 1) // 18000)
+        assert lay.n_seg == nseg and lay.n_frames == c["feats"].shape[0] == -(-T * 100 // 16000)
+        ptr, want = 0, []
+        for i in range(nseg):
+            want.append(ptr)
+            ptr += (112 - 75) if i == 0 else 112 + rng.randrange(2)
+        assert list(lay.seg_ptr) == want
+        got = ex([c["x"]], jitter=[seed])[0].cpu().numpy()
+        assert np.array_equal(got[:, 0] <= FLOOR + 1e-4, c["feats"][:, 0] <= FLOOR + 1e-9)
