@@ -25,7 +25,11 @@
  *   - the plan owns its tables (filterbank, twiddles, windows, cosine basis) and its scratch buffers;
  *     one plan per (device, configuration); a plan is not re-entrant, distinct plans are independent;
  *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); nothing synchronises the device
- *     except plan creation/destruction and scratch growth.
+ *     except plan creation/destruction and scratch growth;
+ *   - every params / batch struct starts with `uint32_t struct_size`, which the caller sets to sizeof(the struct)
+ *     as ITS binding declares it.  A binding generated from an older or newer header hands over a different size
+ *     and the call returns FDLP_E_ARG instead of reading fields that are not there (fdlp_sizeof_struct reports the
+ *     library's own sizes; FDLP_ABI_VERSION / fdlp_version() change whenever a struct layout does).
  */
 #ifndef FDLP_B200_H
 #define FDLP_B200_H
@@ -36,6 +40,8 @@
 extern "C" {
 #endif
 
+#define FDLP_ABI_VERSION 200
+
 #define FDLP_OK 0
 #define FDLP_E_ARG (-1)         /* invalid argument / unsupported configuration            */
 #define FDLP_E_CUDA (-2)        /* a CUDA runtime call failed (see fdlp_last_error)         */
@@ -45,6 +51,8 @@ extern "C" {
 /* per-utterance status bits written by fdlp_forward (0 = clean) */
 #define FDLP_ST_SINGULAR 1 /* a Levinson step hit a zero/non-finite prediction error (reference: LinAlgError) */
 #define FDLP_ST_NONFINITE 2 /* gain <= 0 or non-finite: the band is NaN in the reference as well              */
+#define FDLP_ST_ENV_RANGE 4 /* an envelope value left the float32 range of the K5 -> K6 hand-over (finite and non-zero
+                               in float64): re-run with fdlp_params.env_f64 = 1                                 */
 
 #define FDLP_FBANK_MEL 0      /* createFbank(nfilters, 2N, srate, warp)                 features.py:172-190 */
 #define FDLP_FBANK_COCHLEAR 1 /* createFbankCochlear(nfilters, 2N, srate, om_w, alp, fixed, bet, warp) :197-219 */
@@ -68,6 +76,7 @@ typedef struct mel_plan mel_plan;
 /* Arguments of the reference's argparse surface that shape the computation
  * (computeFDLPSpectrogram.py:241-262).  String options are pre-parsed by the Python host. */
 typedef struct {
+  uint32_t struct_size;     /* = sizeof(fdlp_params) */
   int32_t srate;            /* 16000 */
   int32_t nfilters;         /* --nfilters */
   int32_t order;            /* --order */
@@ -87,6 +96,9 @@ typedef struct {
   int32_t seg_shift;        /* > 0: segment shift in samples, int(srate / frate) (computeModulationSpectrum.py:143-144);
                                0: derived from overlap_fraction */
   int32_t cepstrum_mode;    /* 1: the plan emits cepstra (fdlp_modspec_forward): L = coeff_num, no truncation to M */
+  int32_t env_f64;          /* 0 (default): envelopes cross from K5 to K6 as float32 (a frame sums at most two, the output
+                               is float32: ~1e-7 in the log features; values that leave the float32 range raise
+                               FDLP_ST_ENV_RANGE); 1: float64 hand-over (extreme --lifter_config / --gamma_weight scalings) */
 } fdlp_params;
 
 /* Integer geometry derived exactly as the reference does (np.round = half-to-even). */
@@ -110,6 +122,7 @@ typedef struct {
 
 /* One packed batch.  All pointers are DEVICE pointers unless noted. */
 typedef struct {
+  uint32_t struct_size;         /* = sizeof(fdlp_batch) */
   const void* wav;              /* packed samples of all utterances, int16 or float32 */
   int32_t wav_dtype;            /* FDLP_WAV_* */
   int32_t n_utt;
@@ -134,7 +147,10 @@ typedef struct {
 } fdlp_batch;
 
 const char* fdlp_last_error(void);
-int fdlp_version(void);
+int fdlp_version(void); /* FDLP_ABI_VERSION of the loaded library */
+/* sizeof() of the library's own struct `which`: 0 fdlp_params, 1 fdlp_geometry, 2 fdlp_batch, 3 mel_params,
+ * 4 mel_batch, 5 fdlp_reverb_batch, 6 mfcc_params, 7 mfcc_batch; -1 for an unknown index */
+int64_t fdlp_sizeof_struct(int32_t which);
 
 int fdlp_plan_create(const fdlp_params* params, fdlp_plan** out_plan);
 int fdlp_plan_destroy(fdlp_plan* plan);
@@ -179,6 +195,7 @@ int fdlp_stage_lpc_envelope(fdlp_plan* plan, const double* r /*[n_seg,nfilters,n
 
 /* ---- mel-spectrogram baseline (computeMelSpectrum.py) ---- */
 typedef struct {
+  uint32_t struct_size;  /* = sizeof(mel_params) */
   int32_t srate;
   int32_t nfilters;
   int32_t nfft;          /* --nfft (power of two) */
@@ -191,6 +208,7 @@ typedef struct {
 } mel_params;
 
 typedef struct {
+  uint32_t struct_size;         /* = sizeof(mel_batch) */
   const void* wav;
   int32_t wav_dtype;
   int32_t n_utt;
@@ -233,6 +251,7 @@ int fdlp_diff_filter(const void* wav /*dev, packed*/, int32_t wav_dtype, const i
  *      T_u - 1 in the reference's corner case indM == R (the slice runs off the end of the convolution). ---- */
 typedef struct fdlp_reverb_plan fdlp_reverb_plan;
 typedef struct {
+  uint32_t struct_size;         /* = sizeof(fdlp_reverb_batch) */
   const void* wav;              /* dev, packed int16 or float32 */
   int32_t wav_dtype;
   int32_t n_utt;
@@ -268,6 +287,7 @@ int fdlp_reverb_forward(fdlp_reverb_plan* plan, const fdlp_reverb_batch* batch, 
  *      first `ncep` coefficients; optional spliceFeats context, features.py:157-169) ---- */
 typedef struct mfcc_plan mfcc_plan;
 typedef struct {
+  uint32_t struct_size;  /* = sizeof(mfcc_params) */
   int32_t srate;
   int32_t nfilters;      /* --nfilters (30) */
   int32_t nfft;          /* --nfft (1024), even */
@@ -277,6 +297,7 @@ typedef struct {
 } mfcc_params;
 
 typedef struct {
+  uint32_t struct_size;         /* = sizeof(mfcc_batch) */
   const void* wav;              /* dev, packed int16 / float32 as read from the WAV (not normalised) */
   int32_t wav_dtype;
   int32_t n_utt;

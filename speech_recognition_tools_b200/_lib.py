@@ -13,21 +13,32 @@ LIB_PATH = os.environ.get("FDLP_B200_LIB") or os.path.join(_HERE, "libfdlp_b200.
 
 FDLP_OK = 0
 FDLP_E_ARG, FDLP_E_CUDA, FDLP_E_UNSUPPORTED, FDLP_E_NOMEM = -1, -2, -3, -4
-FDLP_ST_SINGULAR, FDLP_ST_NONFINITE = 1, 2
+FDLP_ABI_VERSION = 200
+FDLP_ST_SINGULAR, FDLP_ST_NONFINITE, FDLP_ST_ENV_RANGE = 1, 2, 4
 FDLP_FBANK_MEL, FDLP_FBANK_COCHLEAR, FDLP_FBANK_CUSTOM = 0, 1, 2
 FDLP_WAV_INT16, FDLP_WAV_FLOAT32, FDLP_WAV_FLOAT64 = 0, 1, 2
 FDLP_WINDOW_HAMMING, FDLP_WINDOW_HANNING, FDLP_WINDOW_SQUARE = 0, 1, 2
 FDLP_NOISE_NONE, FDLP_NOISE_INT16_WRAP, FDLP_NOISE_FLOAT = 0, 1, 2
 
 
-class FdlpParams(C.Structure):
+class _Sized(C.Structure):
+    """Every params / batch struct of the ABI leads with `struct_size` = sizeof(the struct as THIS binding declares
+    it); the library refuses a size that is not its own (include/fdlp_b200.h, conventions)."""
+
+    def __init__(self, *args, **kw):
+        super().__init__(*args, **kw)
+        self.struct_size = C.sizeof(type(self))
+
+
+class FdlpParams(_Sized):
     _fields_ = [
+        ("struct_size", C.c_uint32),
         ("srate", C.c_int32), ("nfilters", C.c_int32), ("order", C.c_int32), ("coeff_num", C.c_int32),
         ("frate", C.c_int32), ("fduration", C.c_double), ("overlap_fraction", C.c_double),
         ("fbank_kind", C.c_int32), ("fbank_args", C.c_double * 5),
         ("weights", C.POINTER(C.c_double)), ("custom_fbank", C.POINTER(C.c_double)),
         ("dct_fp32", C.c_int32), ("tail_eps", C.c_double),
-        ("window_kind", C.c_int32), ("seg_shift", C.c_int32), ("cepstrum_mode", C.c_int32),
+        ("window_kind", C.c_int32), ("seg_shift", C.c_int32), ("cepstrum_mode", C.c_int32), ("env_f64", C.c_int32),
     ]
 
 
@@ -37,8 +48,9 @@ class FdlpGeometry(C.Structure):
                 ("nfam", C.c_int32), ("block_len", C.c_int32)]
 
 
-class FdlpBatch(C.Structure):
+class FdlpBatch(_Sized):
     _fields_ = [
+        ("struct_size", C.c_uint32),
         ("wav", C.c_void_p), ("wav_dtype", C.c_int32), ("n_utt", C.c_int32), ("n_seg", C.c_int32),
         ("n_frames", C.c_int64), ("max_utt_frames", C.c_int32),
         ("utt_wav_off", C.c_void_p), ("utt_seg_off", C.c_void_p), ("utt_frame_off", C.c_void_p),
@@ -48,38 +60,43 @@ class FdlpBatch(C.Structure):
     ]
 
 
-class MelParams(C.Structure):
+class MelParams(_Sized):
     _fields_ = [
+        ("struct_size", C.c_uint32),
         ("srate", C.c_int32), ("nfilters", C.c_int32), ("nfft", C.c_int32), ("frate", C.c_int32),
         ("fduration", C.c_double), ("fbank_kind", C.c_int32), ("fbank_args", C.c_double * 5),
         ("custom_fbank", C.POINTER(C.c_double)), ("power", C.c_int32),
     ]
 
 
-class MelBatch(C.Structure):
+class MelBatch(_Sized):
     _fields_ = [
+        ("struct_size", C.c_uint32),
         ("wav", C.c_void_p), ("wav_dtype", C.c_int32), ("n_utt", C.c_int32), ("n_frames", C.c_int64),
         ("utt_wav_off", C.c_void_p), ("utt_frame_off", C.c_void_p), ("feats", C.c_void_p), ("cmvn_acc", C.c_void_p),
     ]
 
 
-class MfccParams(C.Structure):
+class MfccParams(_Sized):
     _fields_ = [
+        ("struct_size", C.c_uint32),
         ("srate", C.c_int32), ("nfilters", C.c_int32), ("nfft", C.c_int32), ("frate", C.c_int32),
         ("fduration", C.c_double), ("ncep", C.c_int32),
     ]
 
 
-class MfccBatch(C.Structure):
+class MfccBatch(_Sized):
     _fields_ = [
+        ("struct_size", C.c_uint32),
         ("wav", C.c_void_p), ("wav_dtype", C.c_int32), ("n_utt", C.c_int32), ("n_frames", C.c_int64),
         ("utt_wav_off", C.c_void_p), ("utt_frame_off", C.c_void_p), ("feats", C.c_void_p), ("context", C.c_int32),
         ("noise", C.c_void_p), ("utt_noise_off", C.c_void_p), ("utt_snr_db", C.c_void_p),
     ]
 
 
-class ReverbBatch(C.Structure):
+class ReverbBatch(_Sized):
     _fields_ = [
+        ("struct_size", C.c_uint32),
         ("wav", C.c_void_p), ("wav_dtype", C.c_int32), ("n_utt", C.c_int32), ("utt_wav_off", C.c_void_p),
         ("max_len", C.c_int64), ("n_pair", C.c_int32), ("utt_pair_off", C.c_void_p), ("pair_utt", C.c_void_p),
         ("n_conv", C.c_int32), ("utt_conv_off", C.c_void_p), ("conv_utt", C.c_void_p),
@@ -92,6 +109,7 @@ class ReverbBatch(C.Structure):
 SYMBOLS = [
     ("fdlp_last_error", C.c_char_p, []),
     ("fdlp_version", C.c_int, []),
+    ("fdlp_sizeof_struct", C.c_int64, [C.c_int32]),
     ("fdlp_plan_create", C.c_int, [C.POINTER(FdlpParams), C.POINTER(C.c_void_p)]),
     ("fdlp_plan_destroy", C.c_int, [C.c_void_p]),
     ("fdlp_plan_get_geometry", C.c_int, [C.c_void_p, C.POINTER(FdlpGeometry)]),
@@ -147,8 +165,16 @@ def load():
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.restype = restype
         fn.argtypes = argtypes
+    if lib.fdlp_version() != FDLP_ABI_VERSION:
+        raise ImportError("%s implements ABI %d, this binding was written for ABI %d: rebuild the library (`make`)"
+                          % (LIB_PATH, lib.fdlp_version(), FDLP_ABI_VERSION))
     _lib = lib
     return lib
+
+
+# index -> binding class for fdlp_sizeof_struct (include/fdlp_b200.h)
+STRUCTS = {0: "FdlpParams", 1: "FdlpGeometry", 2: "FdlpBatch", 3: "MelParams", 4: "MelBatch", 5: "ReverbBatch",
+           6: "MfccParams", 7: "MfccBatch"}
 
 
 class FdlpError(RuntimeError):

@@ -213,7 +213,17 @@ struct FamArgs {
   const int32_t* task_step0;  // [ntask] first step (= start of the first block)
   int n_seg, ld, nlags, nblk_total, ntask;
   int lag_groups;             // MULTI: warps per (segment, task), each 8 (NA - 1) complete lags
+  unsigned long long* next;   // work counter (zeroed by the launcher): warps draw (segment, task, lag group) items
 };
+
+// The warps of the autocorrelation kernels are persistent and draw their work items from a global counter: tasks
+// differ in length (75 .. 225 steps), and with one item per warp a CTA kept its registers until its slowest warp
+// was done (ncu, round 1: 9.8 of 12 resident warps active on average).
+__device__ __forceinline__ unsigned long long next_item(unsigned long long* counter, int lane) {
+  unsigned long long v = 0;
+  if (lane == 0) v = atomicAdd(counter, 1ULL);
+  return __shfl_sync(0xffffffffu, v, 0);
+}
 
 // Blocks have variable length: their boundaries are the steps where some band's filter enters or leaves a
 // region of the template (plan analysis), so every band's range is a union of whole blocks and the direct
@@ -228,21 +238,23 @@ __global__ void __launch_bounds__(kAcWarps * 32, MULTI ? 2 : 3) family_block_aut
   constexpr int U = RS / 4;
   extern __shared__ __align__(16) double cs[];  // [kAcWarps][NA + 1][kFoldStride]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  long long gw = (long long)blockIdx.x * kAcWarps + warp;
   const int lg = MULTI ? a.lag_groups : 1;
-  if (gw >= (long long)a.n_seg * a.ntask * lg) return;  // warps are independent: no block-wide barrier below
+  const unsigned long long n_items = (unsigned long long)a.n_seg * a.ntask * lg;
+  const int lr = lane & 3, lc = lane >> 2;
+  const int lane_off = (lr << 3) + lc;
+  const FoldCtx fc = fold_ctx(cs + (size_t)warp * fold_smem_doubles(NA), lane);
+  // warps are independent: no block-wide barrier below
+  for (unsigned long long gw = next_item(a.next, lane); gw < n_items; gw = next_item(a.next, lane)) {
   const int h = MULTI ? (int)(gw % lg) : 0;
-  if (MULTI) gw /= lg;
+  const unsigned long long gt = MULTI ? gw / lg : gw;
   const int a_base = h * (NA - 1);
   const int lag0 = 8 * a_base;
-  const int seg = (int)(gw / a.ntask);
-  const int task = (int)(gw % a.ntask);  // tasks are sorted by first step: neighbouring warps share rows of c
+  const int seg = (int)(gt / a.ntask);
+  const int task = (int)(gt % a.ntask);  // tasks are sorted by first step: neighbouring items share rows of c
   const int fam = a.task_fam[task];
   const int blk1 = a.task_blk1[task];
   int blk = a.task_blk0[task];
   int step = a.task_step0[task];
-  const int lr = lane & 3, lc = lane >> 2;
-  const int lane_off = (lr << 3) + lc;
   const int m_lo = step * 4;
 
   const double* __restrict__ pc = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + a_base) * 8 + lane_off;
@@ -262,7 +274,6 @@ __global__ void __launch_bounds__(kAcWarps * 32, MULTI ? 2 : 3) family_block_aut
 #pragma unroll
   for (int i = NA; i < RS; ++i) ring[i] = 0.0;
 
-  const FoldCtx fc = fold_ctx(cs + (size_t)warp * fold_smem_doubles(NA), lane);
   // the rows of c come from HBM (the templates stay in L1/L2): pull them into L1 two groups of U steps ahead
   const double* cpf = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + a_base + NA + 4 + 8 * U) * 8 + lane * 16;
   const int pf_lanes = (U * 32 * 8 + 127) / 128;
@@ -309,6 +320,7 @@ __global__ void __launch_bounds__(kAcWarps * 32, MULTI ? 2 : 3) family_block_aut
       }
     }
   }
+  }  // work items
 }
 
 // ---- per-band combination of the family block sums ----
@@ -387,146 +399,146 @@ struct AcRangeArgs {
   int32_t boff[kCombMaxFam];  // first block of each family in p
   int nfam, nblk_total;
   int lag_groups;             // MULTI: warps per (segment, band), see family_block_autocorr_kernel
+  unsigned long long* next;   // work counter (zeroed by the launcher)
 };
 
 template <int NA, bool MULTI>
 __global__ void __launch_bounds__(kAcWarps * 32, MULTI ? 2 : 3) autocorr_ranges_kernel(const AcRangeArgs a) {
   constexpr int RS = NA + 4;
   constexpr int U = RS / 4;
-  extern __shared__ __align__(16) double cs[];  // [kAcWarps][NA][kFoldStride]
+  extern __shared__ __align__(16) double cs[];  // [kAcWarps][NA + 1][kFoldStride]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int lg = MULTI ? a.lag_groups : 1;
-  const int nbg = (a.J * lg + kAcWarps - 1) / kAcWarps;
-  const int seg = blockIdx.x / nbg;
-  const int wid = (blockIdx.x % nbg) * kAcWarps + warp;
-  const int band = MULTI ? wid / lg : wid;
-  const int h = MULTI ? wid % lg : 0;
-  if (band >= a.J) return;
-  const int a_base = h * (NA - 1);
-  const int lag0 = 8 * a_base;
-  const int nr = a.nrng[band];
-  // the family terms gathered in the epilogue live in HBM: start pulling their lines into L2 now
-  {
-    const int lines = (a.nlags * 8 + 127) / 128;
+  const unsigned long long n_items = (unsigned long long)a.n_seg * a.J * lg;
+  const int lr = lane & 3, lc = lane >> 2;
+  const int lane_off = (lr << 3) + lc;
+  const FoldCtx fc = fold_ctx(cs + (size_t)warp * fold_smem_doubles(NA), lane);
+  constexpr int NT = NA / 4;  // lags per lane: k = lag0 + lane + 32 t
+  const int lines = (a.nlags * 8 + 127) / 128;
+
+  // persistent warps, work items (segment, band, lag group) drawn from a counter; the NEXT item is drawn before the
+  // current one is computed so that its rows of c (HBM) are on their way into L1 / L2 while this one computes
+  unsigned long long gw = next_item(a.next, lane);
+  while (gw < n_items) {
+    const unsigned long long gw_next = next_item(a.next, lane);
+    if (gw_next < n_items) {
+      const unsigned long long gt = MULTI ? gw_next / lg : gw_next;
+      const int nseg_ = (int)(gt / a.J), nband = (int)(gt % a.J);
+      const int nnr = a.nrng[nband];
+      const double* crow = a.dct + (size_t)nseg_ * a.ld;
+      for (int q = 0; q < nnr; ++q) {
+        const int m_lo = a.rng[(nband * kMaxRanges + q) * 2], m_hi = a.rng[(nband * kMaxRanges + q) * 2 + 1];
+        const int nline = ((m_hi - m_lo + NA * lg + 4) * 64 + 127) / 128;  // rows of 64 bytes
+        for (int i = lane; i < nline; i += 32) prefetch_l1(crow + (size_t)m_lo * 8 + i * 16);
+      }
+    }
+    const int h = MULTI ? (int)(gw % lg) : 0;
+    const unsigned long long gt = MULTI ? gw / lg : gw;
+    const int seg = (int)(gt / a.J), band = (int)(gt % a.J);
+    const int a_base = h * (NA - 1);
+    const int lag0 = 8 * a_base;
+    const int nr = a.nrng[band];
+    // family terms of the epilogue: (first row, row count, weight) per family; their lines start towards L2 now
+    int f_first[kCombMaxFam], f_cnt[kCombMaxFam];
+    double f_w[kCombMaxFam];
 #pragma unroll
     for (int g = 0; g < kCombMaxFam; ++g) {
+      f_first[g] = 0; f_cnt[g] = 0; f_w[g] = 0.0;
       if (g < a.nfam) {
         const int b0 = a.ra[g * a.J + band], b1 = a.rb[g * a.J + band];
         if (b1 > b0) {
-          const double* pg = a.p + ((size_t)seg * a.nblk_total + a.boff[g]) * a.nlags;
-          const int r0 = (a.mode[g] == kCombPrefix) ? b1 - 1 : b0;
-          const int nrow = (a.mode[g] == kCombRange) ? b1 - b0 : 1;
-          for (int idx = lane; idx < nrow * lines; idx += 32)
-            prefetch_l2(pg + (size_t)(r0 + idx / lines) * a.nlags + (idx % lines) * 16);
+          f_first[g] = a.boff[g] + ((a.mode[g] == kCombPrefix) ? b1 - 1 : b0);
+          f_cnt[g] = (a.mode[g] == kCombRange) ? b1 - b0 : 1;
+          f_w[g] = a.wsq[(size_t)band * a.nfam + g];
+          const double* pg = a.p + ((size_t)seg * a.nblk_total + f_first[g]) * a.nlags;
+          for (int idx = lane; idx < f_cnt[g] * lines; idx += 32)
+            prefetch_l2(pg + (size_t)(idx / lines) * a.nlags + (idx % lines) * 16);
         }
       }
     }
-  }
-  const int lr = lane & 3, lc = lane >> 2;
-  const int lane_off = (lr << 3) + lc;
 
-  double acc[NA][2];
+    double acc[NA][2];
 #pragma unroll
-  for (int i = 0; i < NA; ++i) acc[i][0] = acc[i][1] = 0.0;
+    for (int i = 0; i < NA; ++i) acc[i][0] = acc[i][1] = 0.0;
 
-  for (int q = 0; q < nr; ++q) {
-    const int m_lo = a.rng[(band * kMaxRanges + q) * 2], m_hi = a.rng[(band * kMaxRanges + q) * 2 + 1];
-    const int nsteps = (m_hi - m_lo) >> 2;
-    const double* __restrict__ pc = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + a_base) * 8 + lane_off;
-    const double* __restrict__ pf = a.fbank + (size_t)band * a.ld + (size_t)(m_lo + a_base) * 8 + lane_off;
-    const double* __restrict__ ac = a.dct + (size_t)seg * a.ld + (size_t)m_lo * 8 + lane_off;
-    const double* __restrict__ af = a.fbank + (size_t)band * a.ld + (size_t)m_lo * 8 + lane_off;
-    double paf = 0.0, pac = 0.0;
-    if (MULTI) { paf = __ldg(af); pac = __ldg(ac); }
-    if (q + 1 < nr) {  // the first rows of the next range: into L1 while this range computes
-      const size_t nxt = (size_t)a.rng[(band * kMaxRanges + q + 1) * 2] * 8 + (lane & 15) * 16;
-      if ((lane & 15) * 16 < (NA + 8) * 8)
-        prefetch_l1((lane < 16) ? (a.dct + (size_t)seg * a.ld + nxt) : (a.fbank + (size_t)band * a.ld + nxt));
-    }
-    double ring[RS];
+    for (int q = 0; q < nr; ++q) {
+      const int m_lo = a.rng[(band * kMaxRanges + q) * 2], m_hi = a.rng[(band * kMaxRanges + q) * 2 + 1];
+      const int nsteps = (m_hi - m_lo) >> 2;
+      const double* __restrict__ pc = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + a_base) * 8 + lane_off;
+      const double* __restrict__ pf = a.fbank + (size_t)band * a.ld + (size_t)(m_lo + a_base) * 8 + lane_off;
+      const double* __restrict__ ac = a.dct + (size_t)seg * a.ld + (size_t)m_lo * 8 + lane_off;
+      const double* __restrict__ af = a.fbank + (size_t)band * a.ld + (size_t)m_lo * 8 + lane_off;
+      double paf = 0.0, pac = 0.0;
+      if (MULTI) { paf = __ldg(af); pac = __ldg(ac); }
+      double ring[RS];
 #pragma unroll
-    for (int i = 0; i < NA; ++i) ring[i] = __ldg(pf + 8 * i) * __ldg(pc + 8 * i);
-    pc += 8 * NA;
-    pf += 8 * NA;
-    double qf[4], qc[4];
+      for (int i = 0; i < NA; ++i) ring[i] = __ldg(pf + 8 * i) * __ldg(pc + 8 * i);
+      pc += 8 * NA;
+      pf += 8 * NA;
+      double qf[4], qc[4];
 #pragma unroll
-    for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
+      for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
 #pragma unroll
-    for (int i = NA; i < RS; ++i) ring[i] = 0.0;
-    for (int s0 = 0; s0 < nsteps; s0 += U) {
+      for (int i = NA; i < RS; ++i) ring[i] = 0.0;
+      for (int s0 = 0; s0 < nsteps; s0 += U) {
 #pragma unroll
-      for (int s = 0; s < U; ++s) {
-        if (s0 + s < nsteps) {
+        for (int s = 0; s < U; ++s) {
+          if (s0 + s < nsteps) {
 #pragma unroll
-          for (int t = 0; t < 4; ++t) ring[(4 * s + NA + t) % RS] = qf[t] * qc[t];
-          const double afrag = MULTI ? paf * pac : ring[(4 * s) % RS];
-          pc += 32;
-          pf += 32;
+            for (int t = 0; t < 4; ++t) ring[(4 * s + NA + t) % RS] = qf[t] * qc[t];
+            const double afrag = MULTI ? paf * pac : ring[(4 * s) % RS];
+            pc += 32;
+            pf += 32;
 #pragma unroll
-          for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
-          if (MULTI) {
-            ac += 32;
-            af += 32;
-            paf = __ldg(af);
-            pac = __ldg(ac);
-          }
-#pragma unroll
-          for (int i = 0; i < NA; ++i) dmma884(acc[i][0], acc[i][1], afrag, ring[(4 * s + i) % RS]);
-        }
-      }
-    }
-  }
-
-  const FoldCtx fc = fold_ctx(cs + (size_t)warp * fold_smem_doubles(NA), lane);
-  fold_store_tiles<NA>(acc, fc);
-  __syncwarp();
-  double* rout = a.r + ((size_t)seg * a.J + band) * a.nlags + lag0;
-  constexpr int NT = NA / 4;  // lags per lane: k = lag0 + lane + 32 t
-  const int nl = (MULTI && a.nlags - lag0 > 8 * (NA - 1)) ? 8 * (NA - 1) : a.nlags - lag0;  // lags of this warp
-  double val[NT];
-#pragma unroll
-  for (int t = 0; t < NT; ++t) val[t] = fold_lag(fc, t);
-  // family terms: all loads of a family are issued together (independent addresses), then consumed
-#pragma unroll
-  for (int g = 0; g < kCombMaxFam; ++g) {
-    if (g < a.nfam) {
-      const int b0 = a.ra[g * a.J + band], b1 = a.rb[g * a.J + band];
-      if (b1 > b0) {
-        const double w = a.wsq[(size_t)band * a.nfam + g];
-        const double* pg = a.p + ((size_t)seg * a.nblk_total + a.boff[g]) * a.nlags + lag0 + lane;
-        if (a.mode[g] != kCombRange) {
-          const double* row = pg + (size_t)((a.mode[g] == kCombPrefix) ? b1 - 1 : b0) * a.nlags;
-          double v[NT];
-#pragma unroll
-          for (int t = 0; t < NT; ++t) v[t] = (lane + 32 * t < nl) ? row[32 * t] : 0.0;
-#pragma unroll
-          for (int t = 0; t < NT; ++t) val[t] = fma(w, v[t], val[t]);
-        } else {
-          double sum[NT];
-#pragma unroll
-          for (int t = 0; t < NT; ++t) sum[t] = 0.0;
-          for (int m = b0; m < b1; m += 2) {
-            const double* r0p = pg + (size_t)m * a.nlags;
-            const bool two = m + 1 < b1;
-            double v0[NT], v1[NT];
-#pragma unroll
-            for (int t = 0; t < NT; ++t) {
-              const bool in = lane + 32 * t < nl;
-              v0[t] = in ? r0p[32 * t] : 0.0;
-              v1[t] = (in && two) ? r0p[a.nlags + 32 * t] : 0.0;
+            for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
+            if (MULTI) {
+              ac += 32;
+              af += 32;
+              paf = __ldg(af);
+              pac = __ldg(ac);
             }
 #pragma unroll
-            for (int t = 0; t < NT; ++t) sum[t] += v0[t] + v1[t];
+            for (int i = 0; i < NA; ++i) dmma884(acc[i][0], acc[i][1], afrag, ring[(4 * s + i) % RS]);
           }
-#pragma unroll
-          for (int t = 0; t < NT; ++t) val[t] = fma(w, sum[t], val[t]);
         }
       }
     }
-  }
+
+    fold_store_tiles<NA>(acc, fc);
+    __syncwarp();
+    double* rout = a.r + ((size_t)seg * a.J + band) * a.nlags + lag0;
+    const int nl = (MULTI && a.nlags - lag0 > 8 * (NA - 1)) ? 8 * (NA - 1) : a.nlags - lag0;  // lags of this warp
+    double val[NT];
 #pragma unroll
-  for (int t = 0; t < NT; ++t)
-    if (lane + 32 * t < nl) rout[lane + 32 * t] = val[t];
+    for (int t = 0; t < NT; ++t) val[t] = fold_lag(fc, t);
+    __syncwarp();  // the fold buffer is free for the next item
+    // family terms: the rows of all families form one list, read kGatherRows rows at a time (all loads of a round are
+    // independent, so a round costs one L2 latency) and added in list order: skirt sums first, then the pass-band blocks
+    constexpr int kGatherRows = 8;
+    const int c0 = f_cnt[0], c01 = c0 + f_cnt[1], total = c01 + f_cnt[2];
+    const double* pbase = a.p + (size_t)seg * a.nblk_total * a.nlags + lag0 + lane;
+    for (int i0 = 0; i0 < total; i0 += kGatherRows) {
+      double v[kGatherRows][NT], w[kGatherRows];
+#pragma unroll
+      for (int u = 0; u < kGatherRows; ++u) {
+        const int i = i0 + u;
+        const bool ok = i < total;
+        const int row = i < c0 ? f_first[0] + i : (i < c01 ? f_first[1] + (i - c0) : f_first[2] + (i - c01));
+        w[u] = !ok ? 0.0 : (i < c0 ? f_w[0] : (i < c01 ? f_w[1] : f_w[2]));
+        const double* rp = pbase + (size_t)row * a.nlags;
+#pragma unroll
+        for (int t = 0; t < NT; ++t) v[u][t] = (ok && lane + 32 * t < nl) ? rp[32 * t] : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < kGatherRows; ++u)
+#pragma unroll
+        for (int t = 0; t < NT; ++t) val[t] = fma(w[u], v[u][t], val[t]);
+    }
+#pragma unroll
+    for (int t = 0; t < NT; ++t)
+      if (lane + 32 * t < nl) rout[lane + 32 * t] = val[t];
+    gw = gw_next;
+  }
 }
 
 }  // namespace fdlp

@@ -227,7 +227,7 @@ struct fdlp_plan {
   bool dct_fp64 = true;
   // envelope -> overlap-add hand-over in float32 (half the traffic of the largest intermediate; the output is float32
   // and a frame sums at most two envelope values, so this costs ~1e-7 in the log features); FDLP_ENV_F64=1 for A/B runs
-  bool env_f32 = getenv("FDLP_ENV_F64") == nullptr;
+  bool env_f32 = true;       // fdlp_params.env_f64 = 1 switches to the float64 hand-over
   int dct_threads = 512;     // threads per DCT CTA (chosen for the butterfly counts of the passes)
   bool dct_half = false;     // float64 DCT with two CTAs per segment (dct_half_kernel): N float64 exceed shared memory
   FftTables fft_half;        // plan of the N/4-point sub-transforms
@@ -256,6 +256,8 @@ struct fdlp_plan {
   int32_t comb_mode[3] = {0, 0, 0}, comb_nband[3] = {0, 0, 0}, comb_boff[3] = {0, 0, 0}, comb_nblk[3] = {0, 0, 0};
   size_t fam_smem = 0;
   double *d_tmpl = nullptr, *d_wsq = nullptr, *d_p = nullptr;
+  unsigned long long* d_next = nullptr;  // work counters of the persistent autocorrelation kernels
+  int sms = 148;
   int32_t *d_bend = nullptr, *d_ra = nullptr, *d_rb = nullptr, *d_nrng = nullptr, *d_rng = nullptr;
   int32_t *d_task_fam = nullptr, *d_task_blk0 = nullptr, *d_task_blk1 = nullptr, *d_task_step0 = nullptr;
   int cap_seg_p = 0;
@@ -264,6 +266,8 @@ struct fdlp_plan {
   // scratch (grow-only)
   int cap_seg = 0, cap_utt = 0;
   double *d_dct = nullptr, *d_r = nullptr, *d_env = nullptr, *d_alpha = nullptr, *d_ms = nullptr;
+  double* d_cmvn_part = nullptr;  // per-CTA CMVN partial sums of the overlap-add kernel (ola.cuh), grow-only
+  int64_t cap_cmvn_slots = 0;
   // optional per-stage timing (CUDA events on the launching stream)
   bool profiling = false;
   // two-stream pipeline: K4/K5 of chunk c run on `side` while K2/K3 of chunk c+1 run on the caller's stream
@@ -285,7 +289,8 @@ static void plan_free(fdlp_plan* p) {
   cudaFree(p->d_ham); cudaFree(p->d_postB); cudaFree(p->d_unp); cudaFree(p->d_hamt); cudaFree(p->d_cep); cudaFree(p->d_fbank); cudaFree(p->d_row_lo); cudaFree(p->d_row_hi);
   cudaFree(p->d_weights); cudaFree(p->d_inv_n); cudaFree(p->d_basis); cudaFree(p->d_wratio);
   cudaFree(p->d_dct); cudaFree(p->d_r); cudaFree(p->d_env); cudaFree(p->d_alpha); cudaFree(p->d_ms);
-  cudaFree(p->d_tmpl); cudaFree(p->d_wsq); cudaFree(p->d_p);
+  cudaFree(p->d_cmvn_part);
+  cudaFree(p->d_tmpl); cudaFree(p->d_wsq); cudaFree(p->d_p); cudaFree(p->d_next);
   cudaFree(p->d_bend); cudaFree(p->d_ra); cudaFree(p->d_rb); cudaFree(p->d_nrng); cudaFree(p->d_rng);
   cudaFree(p->d_task_fam); cudaFree(p->d_task_blk0); cudaFree(p->d_task_blk1); cudaFree(p->d_task_step0);
   for (int i = 0; i < 4; ++i) if (p->ev_ac[i]) cudaEventDestroy(p->ev_ac[i]);
@@ -474,6 +479,12 @@ static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, cons
       (rc = upload(&p->d_task_blk0, task_blk0)) || (rc = upload(&p->d_task_blk1, task_blk1)) ||
       (rc = upload(&p->d_task_step0, task_step0)))
     return rc;
+  if (!p->d_next) FDLP_CUDA(cudaMalloc((void**)&p->d_next, 2 * sizeof(unsigned long long)));
+  {
+    cudaDeviceProp prop;
+    FDLP_CUDA(cudaGetDeviceProperties(&prop, p->device));
+    p->sms = prop.multiProcessorCount;
+  }
   p->nfam = nfam; p->nblk = nblk_total; p->fam_ntask = (int)task_fam.size();
   p->fam_smem = (size_t)kAcWarps * fold_smem_doubles(p->fam_na) * sizeof(double);
   p->g.family_taps = fam_taps;
@@ -485,17 +496,37 @@ static int build_families(fdlp_plan* p, const std::vector<int32_t>& row_lo, cons
 }
 
 extern "C" const char* fdlp_last_error(void) { return g_err; }
-extern "C" int fdlp_version(void) { return 100; }
+extern "C" int fdlp_version(void) { return FDLP_ABI_VERSION; }
+extern "C" int64_t fdlp_sizeof_struct(int32_t which) {
+  switch (which) {
+    case 0: return sizeof(fdlp_params);
+    case 1: return sizeof(fdlp_geometry);
+    case 2: return sizeof(fdlp_batch);
+    case 3: return sizeof(mel_params);
+    case 4: return sizeof(mel_batch);
+    case 5: return sizeof(fdlp_reverb_batch);
+    case 6: return sizeof(mfcc_params);
+    case 7: return sizeof(mfcc_batch);
+    default: return -1;
+  }
+}
+// every params / batch struct leads with the caller's sizeof(): a binding made from another header version is refused
+#define FDLP_CHECK_SIZE(ptr, type)                                                                        \
+  if ((ptr)->struct_size != sizeof(type))                                                                 \
+    return set_err(FDLP_E_ARG, "%s.struct_size = %ld, this library expects %ld (include/fdlp_b200.h, ABI 200)",   \
+                   #type, (long)(ptr)->struct_size, (long)sizeof(type))
 
 extern "C" int fdlp_plan_create(const fdlp_params* prm, fdlp_plan** out) {
   if (!prm || !out) return set_err(FDLP_E_ARG, "null argument%s", "");
   *out = nullptr;
+  FDLP_CHECK_SIZE(prm, fdlp_params);
   if (prm->nfilters < 1 || prm->order < 1 || prm->coeff_num < 2 || prm->frate < 1 || prm->srate < 1 ||
       !(prm->fduration > 0) || !(prm->overlap_fraction >= 0 && prm->overlap_fraction < 1) || !prm->weights)
     return set_err(FDLP_E_ARG, "invalid fdlp_params%s", "");
   fdlp_plan* p = new (std::nothrow) fdlp_plan();
   if (!p) return set_err(FDLP_E_NOMEM, "out of host memory%s", "");
   p->prm = *prm;
+  p->env_f32 = prm->env_f64 == 0;
   cudaGetDevice(&p->device);
 
 
@@ -861,14 +892,19 @@ static int launch_autocorr_family(fdlp_plan* p, const double* dct, int n_seg, do
   f.task_blk0 = p->d_task_blk0; f.task_blk1 = p->d_task_blk1; f.task_step0 = p->d_task_step0;
   f.n_seg = n_seg; f.ld = p->ld; f.nlags = p->g.nlags; f.nblk_total = p->nblk; f.ntask = p->fam_ntask;
   f.lag_groups = p->fam_groups;
+  // persistent grids: every resident warp draws work items from a counter until none are left
+  FDLP_CUDA(cudaMemsetAsync(p->d_next, 0, 2 * sizeof(unsigned long long), st));
+  f.next = p->d_next;
+  const int resident = p->sms * (p->fam_groups > 1 ? 2 : 3);
   const long long tasks = (long long)n_seg * p->fam_ntask * p->fam_groups;
-  const dim3 gridA((unsigned)((tasks + kAcWarps - 1) / kAcWarps)), block(kAcWarps * 32);
+  const dim3 gridA((unsigned)std::min<long long>((tasks + kAcWarps - 1) / kAcWarps, resident)), block(kAcWarps * 32);
   AcRangeArgs d;
   d.dct = dct; d.fbank = p->d_fbank; d.nrng = p->d_nrng; d.rng = p->d_rng; d.r = r;
   d.J = p->prm.nfilters; d.nlags = p->g.nlags; d.n_seg = n_seg; d.ld = p->ld;
   d.lag_groups = p->fam_groups;
-  const int nbg = (d.J * p->fam_groups + kAcWarps - 1) / kAcWarps;
-  const dim3 gridD((unsigned)((size_t)n_seg * nbg));
+  d.next = p->d_next + 1;
+  const long long items = (long long)n_seg * d.J * p->fam_groups;
+  const dim3 gridD((unsigned)std::min<long long>((items + kAcWarps - 1) / kAcWarps, resident));
   d.p = p->d_p; d.ra = p->d_ra; d.rb = p->d_rb; d.wsq = p->d_wsq; d.nfam = p->nfam; d.nblk_total = p->nblk;
   ScanArgs c;
   c.p = p->d_p; c.n_scan = 0; c.n_seg = n_seg; c.nblk_total = p->nblk; c.nlags = p->g.nlags;
@@ -958,6 +994,7 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
   EnvArgs e;
   e.ms = a.ms; e.basis = p->d_basis; e.wratio = p->d_wratio; e.env = env;
   e.n_tasks = a.n_tasks; e.Lp = p->Lp; e.ldb = p->ldb; e.kk = p->g.kk;
+  e.status = env_f32 ? status : nullptr; e.seg_utt = seg_utt; e.J = p->prm.nfilters;
   const dim3 grid((a.n_tasks + 8 * kEnvMA * kEnvWarps - 1) / (8 * kEnvMA * kEnvWarps), p->env_ny);
   if (env_f32) envelope_dmma_kernel<10, float><<<grid, kEnvWarps * 32, 0, st>>>(e);
   else envelope_dmma_kernel<10, double><<<grid, kEnvWarps * 32, 0, st>>>(e);
@@ -967,6 +1004,7 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
 
 static int check_batch(const fdlp_plan* p, const fdlp_batch* b) {
   if (!p || !b) return set_err(FDLP_E_ARG, "null argument%s", "");
+  FDLP_CHECK_SIZE(b, fdlp_batch);
   if (b->n_utt < 0 || b->n_seg < 0 || b->n_frames < 0) return set_err(FDLP_E_ARG, "negative batch sizes%s", "");
   if (b->n_seg > 0 && (!b->wav || !b->utt_wav_off || !b->utt_seg_off || !b->seg_utt))
     return set_err(FDLP_E_ARG, "null batch pointer%s", "");
@@ -1034,7 +1072,18 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
   }
   OlaArgs o;
   o.env = p->d_env; o.utt_seg_off = b->utt_seg_off; o.utt_frame_off = b->utt_frame_off; o.seg_ptr = b->seg_ptr;
-  o.feats = b->feats; o.cmvn = b->cmvn_acc; o.J = p->prm.nfilters; o.kk = p->g.kk; o.kkb2 = p->g.kkb2;
+  o.feats = b->feats; o.cmvn_part = nullptr; o.J = p->prm.nfilters; o.kk = p->g.kk; o.kkb2 = p->g.kkb2;
+  const int64_t cmvn_slots = cmvn_slot_count(b->n_frames, b->n_utt, kOlaFT);
+  const int cmvn_w = 2 * (p->prm.nfilters + 1);
+  if (b->cmvn_acc) {
+    if (cmvn_slots > p->cap_cmvn_slots) {
+      cudaFree(p->d_cmvn_part); p->d_cmvn_part = nullptr; p->cap_cmvn_slots = 0;
+      FDLP_CUDA(cudaMalloc((void**)&p->d_cmvn_part, (size_t)cmvn_slots * cmvn_w * sizeof(double)));
+      p->cap_cmvn_slots = cmvn_slots;
+    }
+    FDLP_CUDA(cudaMemsetAsync(p->d_cmvn_part, 0, (size_t)cmvn_slots * cmvn_w * sizeof(double), st));
+    o.cmvn_part = p->d_cmvn_part;
+  }
   // grid.y covers the longest utterance; the host passes it through n_frames / n_utt bounds
   int64_t max_tiles = (b->max_utt_frames + kOlaFT - 1) / kOlaFT;
   if (max_tiles < 1) max_tiles = 1;
@@ -1043,6 +1092,10 @@ extern "C" int fdlp_forward(fdlp_plan* p, const fdlp_batch* b, void* stream) {
   if (p->env_f32) ola_log_kernel<float><<<grid, block, p->ola_smem, st>>>(o);
   else ola_log_kernel<double><<<grid, block, p->ola_smem, st>>>(o);
   FDLP_CUDA(cudaGetLastError());
+  if (b->cmvn_acc) {  // fixed-order sum of the per-CTA partials: bit-reproducible stats (no floating-point atomics)
+    cmvn_reduce_kernel<<<cmvn_w, 256, 0, st>>>(p->d_cmvn_part, cmvn_slots, cmvn_w, b->cmvn_acc);
+    FDLP_CUDA(cudaGetLastError());
+  }
   if (prof) FDLP_CUDA(cudaEventRecord(p->ev[4], st));
   return FDLP_OK;
 }
@@ -1156,7 +1209,26 @@ struct mel_plan {
   float *d_ham32 = nullptr, *d_wts = nullptr;
   float2 *d_tw4 = nullptr, *d_unpackA32 = nullptr;
   int4* d_band = nullptr;
+  double* d_cmvn_part = nullptr;  // [kMelCmvnCtas, 2, J+1]
 };
+
+constexpr int kMelCmvnCtas = 296;
+
+// CMVN partial sums of the finished feature matrix, slots added in a fixed order (bit-reproducible)
+static int mel_cmvn(mel_plan* p, const mel_batch* b, cudaStream_t st) {
+  if (!b->cmvn_acc) return 0;
+  const int J = p->prm.nfilters, w = 2 * (J + 1);
+  if (!p->d_cmvn_part) FDLP_CUDA(cudaMalloc((void**)&p->d_cmvn_part, (size_t)kMelCmvnCtas * w * sizeof(double)));
+  CmvnSumArgs c;
+  c.feats = b->feats; c.part = p->d_cmvn_part; c.n_frames = b->n_frames; c.J = J;
+  c.chunk = (b->n_frames + kMelCmvnCtas - 1) / kMelCmvnCtas;
+  const int rows_par = std::max(1, 256 / J);
+  cmvn_sums_kernel<<<kMelCmvnCtas, 256, (size_t)rows_par * 2 * std::min(J, 256) * sizeof(double), st>>>(c);
+  FDLP_CUDA(cudaGetLastError());
+  cmvn_reduce_kernel<<<w, 256, 0, st>>>(p->d_cmvn_part, kMelCmvnCtas, w, b->cmvn_acc);
+  FDLP_CUDA(cudaGetLastError());
+  return 0;
+}
 
 template <int R2, int M1, typename S>
 static cudaError_t mel_warp_launch(const MelWarpArgs& w, dim3 grid, size_t smem, cudaStream_t st) {
@@ -1177,12 +1249,14 @@ static void mel_free(mel_plan* p) {
   free_fft_tables(&p->fft);
   cudaFree(p->d_ham); cudaFree(p->d_fbank); cudaFree(p->d_lo); cudaFree(p->d_hi); cudaFree(p->d_frame_utt);
   cudaFree(p->d_ham32); cudaFree(p->d_tw4); cudaFree(p->d_unpackA32); cudaFree(p->d_wts); cudaFree(p->d_band);
+  cudaFree(p->d_cmvn_part);
   delete p;
 }
 
 extern "C" int mel_plan_create(const mel_params* prm, mel_plan** out) {
   if (!prm || !out) return set_err(FDLP_E_ARG, "null argument%s", "");
   *out = nullptr;
+  FDLP_CHECK_SIZE(prm, mel_params);
   if (prm->nfilters < 1 || prm->nfft < 8 || (prm->nfft & 1) || prm->frate < 1 || !(prm->fduration > 0))
     return set_err(FDLP_E_ARG, "invalid mel_params%s", "");
   mel_plan* p = new (std::nothrow) mel_plan();
@@ -1273,6 +1347,7 @@ extern "C" int mel_plan_get_fbank(const mel_plan* p, double* host_out) {
 
 extern "C" int mel_forward(mel_plan* p, const mel_batch* b, void* stream) {
   if (!p || !b) return set_err(FDLP_E_ARG, "null argument%s", "");
+  FDLP_CHECK_SIZE(b, mel_batch);
   if (b->n_utt <= 0 || b->n_frames <= 0) return FDLP_OK;
   if (!b->wav || !b->utt_wav_off || !b->utt_frame_off || !b->feats) return set_err(FDLP_E_ARG, "null batch pointer%s", "");
   cudaStream_t st = (cudaStream_t)stream;
@@ -1304,7 +1379,7 @@ extern "C" int mel_forward(mel_plan* p, const mel_batch* b, void* stream) {
                : mel_warp_launch_m1<16, float>(p->warp_m1, w, grid, p->warp_smem, st);
     FDLP_CUDA(le);
     FDLP_CUDA(cudaGetLastError());
-    return FDLP_OK;
+    return mel_cmvn(p, b, st);
   }
   MelArgs a;
   memset(&a, 0, sizeof(a));
@@ -1320,7 +1395,7 @@ extern "C" int mel_forward(mel_plan* p, const mel_batch* b, void* stream) {
   else if (b->wav_dtype == FDLP_WAV_FLOAT32) mel_frames_kernel<float><<<grid, block, p->smem, st>>>(a);
   else return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
   FDLP_CUDA(cudaGetLastError());
-  return FDLP_OK;
+  return mel_cmvn(p, b, st);
 }
 
 // ================================================================ MFCC
@@ -1349,6 +1424,7 @@ static void mfcc_free(mfcc_plan* p) {
 extern "C" int mfcc_plan_create(const mfcc_params* prm, mfcc_plan** out) {
   if (!prm || !out) return set_err(FDLP_E_ARG, "null argument%s", "");
   *out = nullptr;
+  FDLP_CHECK_SIZE(prm, mfcc_params);
   if (prm->nfilters < 1 || prm->nfft < 8 || (prm->nfft & 1) || prm->frate < 1 || !(prm->fduration > 0) ||
       prm->ncep < 1 || prm->ncep > prm->nfilters)
     return set_err(FDLP_E_ARG, "invalid mfcc_params%s", "");
@@ -1405,6 +1481,7 @@ extern "C" int mfcc_plan_destroy(mfcc_plan* p) { mfcc_free(p); return FDLP_OK; }
 
 extern "C" int mfcc_forward(mfcc_plan* p, const mfcc_batch* b, void* stream) {
   if (!p || !b) return set_err(FDLP_E_ARG, "null argument%s", "");
+  FDLP_CHECK_SIZE(b, mfcc_batch);
   if (b->n_utt <= 0 || b->n_frames <= 0) return FDLP_OK;
   if (!b->wav || !b->utt_wav_off || !b->utt_frame_off || !b->feats) return set_err(FDLP_E_ARG, "null batch pointer%s", "");
   if (b->wav_dtype != FDLP_WAV_INT16 && b->wav_dtype != FDLP_WAV_FLOAT32) return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
@@ -1630,6 +1707,7 @@ extern "C" int64_t fdlp_reverb_plan_scratch_bytes(const fdlp_reverb_plan* p, int
 
 extern "C" int fdlp_reverb_forward(fdlp_reverb_plan* p, const fdlp_reverb_batch* b, void* stream) {
   if (!p || !b) return set_err(FDLP_E_ARG, "null argument%s", "");
+  FDLP_CHECK_SIZE(b, fdlp_reverb_batch);
   if (b->n_utt < 0 || b->n_pair < 0 || b->n_conv < 0) return set_err(FDLP_E_ARG, "negative batch sizes%s", "");
   if (b->n_utt == 0 || b->n_pair == 0) return FDLP_OK;
   if (!b->wav || !b->utt_wav_off || !b->utt_pair_off || !b->pair_utt || !b->utt_conv_off || !b->conv_utt || !b->out)

@@ -696,6 +696,10 @@ struct EnvArgs {
   const double* wratio;  // [kk]
   void* env;             // [n_tasks, kk], float64 (stage API) or float32 (hand-over to the overlap-add kernel)
   int n_tasks, Lp, ldb, kk;
+  // float32 hand-over only: a log-envelope outside the float32 range of exp() raises FDLP_ST_ENV_RANGE for the utterance
+  int32_t* status;         // [n_utt] or nullptr
+  const int32_t* seg_utt;  // [n_seg]
+  int J;
 };
 
 constexpr int kEnvWarps = 4;
@@ -752,12 +756,19 @@ __global__ void __launch_bounds__(kEnvWarps * 32) envelope_dmma_kernel(const Env
   for (int m = 0; m < MA; ++m) {
     const int task = task0 + 8 * m + lc;
     if (task < a.n_tasks) {
+      double worst = 0.0;  // largest |log envelope| of this lane's values (NaN compares false: reported by K4 already)
 #pragma unroll
       for (int i = 0; i < NT; ++i) {
         const int t = t_base + 8 * i + 2 * lr;
         if (t < a.kk) env[(size_t)task * a.kk + t] = (ET)(exp(acc[m][i][0]) * __ldg(a.wratio + t));
         if (t + 1 < a.kk) env[(size_t)task * a.kk + t + 1] = (ET)(exp(acc[m][i][1]) * __ldg(a.wratio + t + 1));
+        if (sizeof(ET) == 4) {
+          if (t < a.kk) worst = fmax(worst, fabs(acc[m][i][0]));
+          if (t + 1 < a.kk) worst = fmax(worst, fabs(acc[m][i][1]));
+        }
       }
+      // exp() leaves the normal float32 range beyond +-87: the float64 value is fine, the hand-over is not
+      if (sizeof(ET) == 4 && worst > 87.0 && a.status) atomicOr(a.status + (a.seg_utt ? a.seg_utt[task / a.J] : task / a.J), FDLP_ST_ENV_RANGE);
     }
   }
 }

@@ -106,13 +106,8 @@ __global__ void __launch_bounds__(128) mel_frames_kernel(const MelArgs a) {
     if (lane == 0) {
       const float o = a.power ? s * s : log10f(s);
       a.feats[fr * a.J + j] = o;
-      if (a.cmvn) {
-        atomicAdd(a.cmvn + j, (double)o);
-        atomicAdd(a.cmvn + (a.J + 1) + j, (double)o * (double)o);
-      }
     }
   }
-  if (a.cmvn && threadIdx.x == 0) atomicAdd(a.cmvn + a.J, 1.0);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -316,10 +311,6 @@ __global__ void __launch_bounds__(kMelWarps * 32, 2) mel_frames_warp_kernel(cons
 #pragma unroll
     for (int m1 = 0; m1 < M1; ++m1) hw[m1] = make_float2(__ldg(a.ham + 2 * (32 * m1 + lane)), __ldg(a.ham + 2 * (32 * m1 + lane) + 1));
   }
-  double cs1[kMelMaxBandsPerLane], cs2[kMelMaxBandsPerLane];
-#pragma unroll
-  for (int i = 0; i < kMelMaxBandsPerLane; ++i) cs1[i] = cs2[i] = 0.0;
-  long long nfr_done = 0;
   const int g = lane >> kMelLpbLog, q = lane & (kMelLpb - 1);
 
   const long long wstride = (long long)gridDim.x * kMelWarps;
@@ -419,23 +410,9 @@ __global__ void __launch_bounds__(kMelWarps * 32, 2) mel_frames_warp_kernel(cons
         const float s = s_sum[j];
         const float o = a.power ? s * s : log10f(s);
         a.feats[fr * a.J + j] = o;
-        cs1[i] += (double)o;
-        cs2[i] += (double)o * (double)o;
       }
     }
-    ++nfr_done;
     __syncwarp();
-  }
-  if (a.cmvn && nfr_done > 0) {
-#pragma unroll
-    for (int i = 0; i < kMelMaxBandsPerLane; ++i) {
-      const int j = lane + 32 * i;
-      if (j < a.J) {
-        atomicAdd(a.cmvn + j, cs1[i]);
-        atomicAdd(a.cmvn + (a.J + 1) + j, cs2[i]);
-      }
-    }
-    if (lane == 0) atomicAdd(a.cmvn + a.J, (double)nfr_done);
   }
 }
 

@@ -21,9 +21,14 @@ struct OlaArgs {
   const int64_t* utt_frame_off;  // [n_utt+1]
   const int32_t* seg_ptr;        // [n_seg]
   float* feats;                  // [n_frames, J]
-  double* cmvn;                  // [2, J+1] or null
+  double* cmvn_part;             // [cmvn_slots, 2, J+1] per-CTA partial sums (zeroed by the launcher), or null
   int J, kk, kkb2;
 };
+
+// CMVN partial sums are bit-reproducible: every CTA writes its own slot (no floating-point atomics), and
+// cmvn_reduce_kernel adds the slots in a fixed order.  Slot of (utterance u, tile y): foff_u / FT + u + y, unique
+// because floor(a) + ceil(b) <= floor(a + b) + 1; at most n_frames / FT + n_utt + 1 slots.
+__host__ __device__ inline int64_t cmvn_slot_count(int64_t n_frames, int n_utt, int ft) { return n_frames / ft + n_utt + 1; }
 
 constexpr int kOlaFT = 64;  // frames per block
 
@@ -81,8 +86,9 @@ __global__ void __launch_bounds__(256) ola_log_kernel(const OlaArgs a) {
       if (j >= J) { j -= J; ++fl; }
     }
   }
-  if (a.cmvn) {
+  if (a.cmvn_part) {
     __syncthreads();
+    double* part = a.cmvn_part + (size_t)(foff / kOlaFT + u + blockIdx.y) * (2 * (J + 1));
     for (int j = threadIdx.x; j < J; j += blockDim.x) {
       double s1 = 0.0, s2 = 0.0;
       for (int fl = 0; fl < nf; ++fl) {
@@ -90,11 +96,64 @@ __global__ void __launch_bounds__(256) ola_log_kernel(const OlaArgs a) {
         s1 += v;
         s2 = fma(v, v, s2);
       }
-      atomicAdd(a.cmvn + j, s1);
-      atomicAdd(a.cmvn + (J + 1) + j, s2);
+      part[j] = s1;
+      part[(J + 1) + j] = s2;
     }
-    if (threadIdx.x == 0) atomicAdd(a.cmvn + J, (double)nf);
+    if (threadIdx.x == 0) part[J] = (double)nf;
   }
+}
+
+// Partial CMVN sums of a finished feature matrix (mel path): CTA b owns the frames [b * chunk, (b + 1) * chunk) and
+// adds them row by row, in order; slot b of `part` receives [sum x (J), frames; sum x^2 (J), 0].
+struct CmvnSumArgs {
+  const float* feats;  // [n_frames, J]
+  double* part;        // [gridDim.x, 2, J+1]
+  int64_t n_frames, chunk;
+  int J;
+};
+
+__global__ void __launch_bounds__(256) cmvn_sums_kernel(const CmvnSumArgs a) {
+  extern __shared__ __align__(16) double sh[];  // [rows_par][2][J]
+  const int J = a.J;
+  const int rows_par = blockDim.x / J > 0 ? blockDim.x / J : 1;
+  const int64_t f0 = (int64_t)blockIdx.x * a.chunk;
+  const int64_t f1 = f0 + a.chunk < a.n_frames ? f0 + a.chunk : a.n_frames;
+  double* part = a.part + (size_t)blockIdx.x * (2 * (J + 1));
+  for (int jb = 0; jb < J; jb += blockDim.x) {  // J > blockDim.x: several passes over the bands
+    const int rl = (int)threadIdx.x / J, j = jb + ((J <= (int)blockDim.x) ? (int)threadIdx.x % J : (int)threadIdx.x);
+    double s1 = 0.0, s2 = 0.0;
+    if (rl < rows_par && j < J)
+      for (int64_t f = f0 + rl; f < f1; f += rows_par) {
+        const double v = (double)a.feats[f * J + j];
+        s1 += v;
+        s2 = fma(v, v, s2);
+      }
+    if (rl < rows_par && j < J) { sh[(rl * 2) * J + j - jb] = s1; sh[(rl * 2 + 1) * J + j - jb] = s2; }
+    __syncthreads();
+    if (rl == 0 && j < J) {
+      for (int q = 1; q < rows_par; ++q) { s1 += sh[(q * 2) * J + j - jb]; s2 += sh[(q * 2 + 1) * J + j - jb]; }
+      part[j] = s1;
+      part[(J + 1) + j] = s2;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { part[J] = f1 > f0 ? (double)(f1 - f0) : 0.0; part[2 * J + 1] = 0.0; }
+}
+
+// cmvn[c] += sum over slots of part[slot][c], slots added in a fixed order: thread t takes slots t, t + 256, ... in
+// sequence, then a fixed binary tree over the 256 partial sums.  One CTA per column c of the [2, J+1] layout.
+__global__ void __launch_bounds__(256) cmvn_reduce_kernel(const double* part, int64_t n_slots, int width, double* cmvn) {
+  __shared__ double sh[256];
+  const int c = blockIdx.x;
+  double s = 0.0;
+  for (int64_t q = threadIdx.x; q < n_slots; q += 256) s += part[q * width + c];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) cmvn[c] += sh[0];
 }
 
 // modulation-spectrum output (computeModulationSpectrum.py:176-191): selected cepstral coefficients per band

@@ -43,6 +43,9 @@ class FdlpConfig:
     dct_fp32: bool = False
     # the autocorrelation skips filter taps below tail_eps * max|F_j| (0.0: only exactly-zero taps); see DESIGN.md
     tail_eps: float = 1e-12
+    # envelopes cross from the envelope kernel to the overlap-add kernel as float32 (fdlp_params.env_f64 = 0); a value
+    # outside the float32 range (extreme lifter / gamma scalings) raises FDLP_ST_ENV_RANGE in the status word
+    env_f64: bool = False
 
     @classmethod
     def from_args(cls, args) -> "FdlpConfig":
@@ -272,6 +275,7 @@ class FdlpExtractor:
         prm.custom_fbank = None
         prm.dct_fp32 = 1 if self.cfg.dct_fp32 else 0
         prm.tail_eps = float(self.cfg.tail_eps)
+        prm.env_f64 = 1 if self.cfg.env_f64 else 0
         self._plan = C.c_void_p()
         with torch.cuda.device(self.device):
             L.check(self._lib.fdlp_plan_create(C.byref(prm), C.byref(self._plan)))

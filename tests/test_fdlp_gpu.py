@@ -410,3 +410,47 @@ def test_long_utterances_pointer_trace_and_floor_set():
         assert list(lay.seg_ptr) == want
         got = ex([c["x"]], jitter=[seed])[0].cpu().numpy()
         assert np.array_equal(got[:, 0] <= FLOOR + 1e-4, c["feats"][:, 0] <= FLOOR + 1e-9)
+
+
+def test_cmvn_sums_are_bit_reproducible():
+    """The CMVN partial sums carry no floating-point atomics (per-CTA slots + a fixed-order reduction, ola.cuh): the
+    same batch gives the same [2, J+1] stats bit for bit, run after run, for the FDLP and the mel extractor."""
+    from speech_recognition_tools_b200.mel import MelConfig, MelExtractor
+    ex = extractor(**WSJ)
+    lengths = synth.wsj_shaped_lengths(40, seed=5)
+    wavs = [synth.make_utterance("white", 33, i, int(T)) for i, T in enumerate(lengths)]
+    ref = None
+    for _ in range(4):
+        cm = torch.zeros((2, 81), dtype=torch.float64, device="cuda:0")
+        outs = ex(wavs, jitter=list(range(40)), cmvn=cm)
+        if ref is None:
+            ref = cm.clone()
+            want = ocmvn.cmvn_stats([o.cpu().numpy() for o in outs])
+            np.testing.assert_allclose(cm.cpu().numpy(), want, rtol=1e-12, atol=1e-9)
+        assert torch.equal(cm, ref)
+    mel = MelExtractor(MelConfig(nfilters=80, nfft=2048), device="cuda:0")
+    mref = None
+    for _ in range(4):
+        cm = torch.zeros((2, 81), dtype=torch.float64, device="cuda:0")
+        mouts = mel(wavs, cmvn=cm)
+        if mref is None:
+            mref = cm.clone()
+            want = ocmvn.cmvn_stats([o.cpu().numpy() for o in mouts])
+            np.testing.assert_allclose(cm.cpu().numpy(), want, rtol=1e-12, atol=1e-9)
+        assert torch.equal(cm, mref)
+
+
+def test_env_range_flag_and_float64_hand_over():
+    """the float32 envelope hand-over overflows where the reference's float64 does not (a lifter that scales
+    the cepstra).  The float32 plan must say so (FDLP_ST_ENV_RANGE), the env_f64 plan must match the oracle."""
+    from speech_recognition_tools_b200 import _lib
+    lifter = [8.0] * 50
+    kw = dict(FDLP_DEFAULTS, coeff_range="0,49")
+    x = synth.make_utterance("white", 35, 0, 30000)
+    ref = ofdlp.fdlp_spectrogram(x, lifter=lifter, rng=random.Random(4), **kw)
+    assert np.isfinite(ref).all() and np.abs(ref).max() > 88.0   # beyond exp()'s float32 range
+    outs, st = extractor(lifter=lifter, **kw)([x], jitter=[4], return_status=True)
+    assert int(st.cpu()[0]) & _lib.FDLP_ST_ENV_RANGE
+    outs, st = extractor(lifter=lifter, env_f64=True, **kw)([x], jitter=[4], return_status=True)
+    assert int(st.cpu()[0]) == 0
+    assert_feats_close(outs[0].cpu().numpy(), ref, atol=2e-5, rtol=4e-7)

@@ -27,7 +27,96 @@ def test_library_loads_and_exports_every_declared_symbol():
     assert declared == bound, (declared ^ bound)
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.fdlp_version() >= 100
+    assert lib.fdlp_version() == _lib.FDLP_ABI_VERSION == int(re.search(r"#define FDLP_ABI_VERSION (\d+)", header).group(1))
+
+
+HEADER_STRUCTS = {"fdlp_params": "FdlpParams", "fdlp_geometry": "FdlpGeometry", "fdlp_batch": "FdlpBatch",
+                  "mel_params": "MelParams", "mel_batch": "MelBatch", "fdlp_reverb_batch": "ReverbBatch",
+                  "mfcc_params": "MfccParams", "mfcc_batch": "MfccBatch"}
+C_TO_CTYPES = {"uint32_t": "c_uint32", "int32_t": "c_int32", "int64_t": "c_int64", "double": "c_double"}
+
+
+def _header_fields(header, cname):
+    """[(field, ctypes type name)] of `typedef struct { ... } cname;` in include/fdlp_b200.h."""
+    body = re.search(r"typedef struct \{((?:(?!typedef struct).)*?)\}\s*%s;" % cname, header, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    out = []
+    for decl in body.split(";"):
+        decl = " ".join(decl.split())
+        if not decl:
+            continue
+        m = re.match(r"(const )?(\w+)(\s*\*)?\s*(\w+)(\[(\d+)\])?$", decl)
+        assert m, decl
+        base, ptr, name, arr = m.group(2), m.group(3), m.group(4), m.group(6)
+        if ptr:
+            t = "pointer"
+        elif arr:
+            t = "%s*%s" % (C_TO_CTYPES[base], arr)
+        else:
+            t = C_TO_CTYPES[base]
+        out.append((name, t))
+    return out
+
+
+def _binding_fields(cls):
+    import ctypes as C
+    out = []
+    for name, t in cls._fields_:
+        if t is C.c_void_p or (isinstance(t, type) and issubclass(t, C._Pointer)):
+            out.append((name, "pointer"))
+        elif isinstance(t, type) and issubclass(t, C.Array):
+            out.append((name, "c_%s*%d" % ({"d": "double"}[t._type_._type_], t._length_)))
+        else:
+            size, signed = C.sizeof(t), t(-1).value < 0 if t is not C.c_double else True
+            out.append((name, "c_double" if t is C.c_double else "c_%sint%d" % ("" if signed else "u", 8 * size)))
+    return out
+
+
+@pytest.mark.parametrize("cname", sorted(HEADER_STRUCTS))
+def test_binding_structs_match_the_header_field_by_field(cname):
+    """include/fdlp_b200.h is the contract; _lib.py must declare the same fields in the same order with the same
+    types, and the library's own sizeof() must equal ctypes.sizeof (VERDICT r1 weak #10 / ADVICE: a stale stub made
+    the library read past the end of fdlp_params)."""
+    import ctypes as C
+    header = open(os.path.join(ROOT, "include", "fdlp_b200.h")).read()
+    cls = getattr(_lib, HEADER_STRUCTS[cname])
+    assert _header_fields(header, cname) == _binding_fields(cls)
+    which = [k for k, v in _lib.STRUCTS.items() if v == HEADER_STRUCTS[cname]][0]
+    assert _lib.load().fdlp_sizeof_struct(which) == C.sizeof(cls)
+    if cname != "fdlp_geometry":  # every struct the caller fills leads with struct_size
+        assert cls._fields_[0][0] == "struct_size" and cls().struct_size == C.sizeof(cls)
+
+
+def test_integration_md_stub_is_the_generated_one():
+    import subprocess
+    import sys
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    gen = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "gen_binding_stub.py")], check=True,
+                         capture_output=True, text=True).stdout.strip()
+    assert gen in doc, "INTEGRATION.md is stale: run python tools/gen_binding_stub.py --write"
+
+
+def test_wrong_struct_size_is_refused_before_anything_is_read():
+    """A binding made from another header version (shorter or longer struct) gets FDLP_E_ARG, no CUDA call needed."""
+    import ctypes as C
+    lib = _lib.load()
+    w = np.ones(50)
+    for delta in (-12, 4):
+        prm = _lib.FdlpParams()
+        prm.srate, prm.nfilters, prm.order, prm.coeff_num, prm.frate = 16000, 20, 50, 50, 100
+        prm.fduration, prm.overlap_fraction = 0.5, 0.25
+        prm.fbank_args = (C.c_double * 5)(1, 0, 0, 0, 0)
+        prm.weights = w.ctypes.data_as(C.POINTER(C.c_double))
+        prm.struct_size = C.sizeof(prm) + delta
+        plan = C.c_void_p()
+        assert lib.fdlp_plan_create(C.byref(prm), C.byref(plan)) == _lib.FDLP_E_ARG
+        assert b"struct_size" in lib.fdlp_last_error() and not plan.value
+    mp = _lib.MelParams()
+    mp.struct_size = 8
+    assert lib.mel_plan_create(C.byref(mp), C.byref(plan)) == _lib.FDLP_E_ARG
+    fp = _lib.MfccParams()
+    fp.struct_size = 0
+    assert lib.mfcc_plan_create(C.byref(fp), C.byref(plan)) == _lib.FDLP_E_ARG
 
 
 def test_product_never_imports_the_oracle():
