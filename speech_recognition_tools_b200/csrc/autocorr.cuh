@@ -258,9 +258,12 @@ __global__ void __launch_bounds__(kAcWarps * 32, MULTI ? 2 : 3) family_block_aut
   const int m_lo = step * 4;
 
   const double* __restrict__ pc = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + a_base) * 8 + lane_off;
-  const double* __restrict__ pf = a.tmpl + (size_t)fam * a.ld + (size_t)(m_lo + a_base) * 8 + lane_off;
+  // template 0 is the pass band (all ones): its fragments are read from the first rows of the template at every step,
+  // which stay in L1, instead of streaming 192 KB of ones through it
+  const int tstep = fam == 0 ? 0 : 32;
+  const double* __restrict__ pf = a.tmpl + (size_t)fam * a.ld + (fam == 0 ? (size_t)0 : (size_t)(m_lo + a_base) * 8) + lane_off;
   const double* __restrict__ ac = a.dct + (size_t)seg * a.ld + (size_t)m_lo * 8 + lane_off;
-  const double* __restrict__ af = a.tmpl + (size_t)fam * a.ld + (size_t)m_lo * 8 + lane_off;
+  const double* __restrict__ af = a.tmpl + (size_t)fam * a.ld + (fam == 0 ? (size_t)0 : (size_t)m_lo * 8) + lane_off;
   double paf = 0.0, pac = 0.0;
   if (MULTI) { paf = __ldg(af); pac = __ldg(ac); }
   double ring[RS];
@@ -275,14 +278,18 @@ __global__ void __launch_bounds__(kAcWarps * 32, MULTI ? 2 : 3) family_block_aut
   for (int i = NA; i < RS; ++i) ring[i] = 0.0;
 
   // the rows of c come from HBM (the templates stay in L1/L2): pull them into L1 two groups of U steps ahead
-  const double* cpf = a.dct + (size_t)seg * a.ld + (size_t)(m_lo + a_base + NA + 4 + 8 * U) * 8 + lane * 16;
+  // (lanes 0..pf_lanes-1: rows of c; the next pf_lanes lanes: the same rows of a skirt template, which comes from L2)
   const int pf_lanes = (U * 32 * 8 + 127) / 128;
+  const double* cpf = (lane < pf_lanes || fam == 0)
+                          ? a.dct + (size_t)seg * a.ld + (size_t)(m_lo + a_base + NA + 4 + 8 * U) * 8 + lane * 16
+                          : a.tmpl + (size_t)fam * a.ld + (size_t)(m_lo + a_base + NA + 4 + 8 * U) * 8 + (lane - pf_lanes) * 16;
+  const int pf_active = fam == 0 ? pf_lanes : 2 * pf_lanes;
   int next_end = a.bend[blk];
   double acc[NA][2];
 #pragma unroll
   for (int i = 0; i < NA; ++i) acc[i][0] = acc[i][1] = 0.0;
   while (blk < blk1) {
-    if (lane < pf_lanes) prefetch_l1(cpf);
+    if (lane < pf_active) prefetch_l1(cpf);
     cpf += U * 32;
 #pragma unroll
     for (int s = 0; s < U; ++s) {
@@ -291,26 +298,34 @@ __global__ void __launch_bounds__(kAcWarps * 32, MULTI ? 2 : 3) family_block_aut
         for (int t = 0; t < 4; ++t) ring[(4 * s + NA + t) % RS] = qf[t] * qc[t];
         const double afrag = MULTI ? paf * pac : ring[(4 * s) % RS];
         pc += 32;
-        pf += 32;
+        pf += tstep;
 #pragma unroll
         for (int t = 0; t < 4; ++t) { qf[t] = __ldg(pf + 8 * t); qc[t] = __ldg(pc + 8 * t); }
         if (MULTI) {
           ac += 32;
-          af += 32;
+          af += tstep;
           paf = __ldg(af);
           pac = __ldg(ac);
         }
 #pragma unroll
         for (int i = 0; i < NA; ++i) dmma884(acc[i][0], acc[i][1], afrag, ring[(4 * s + i) % RS]);
         ++step;
+#ifdef FDLP_X_NOFLUSH  // timing experiment only (wrong results): the ceiling of the DMMA phase without per-block flushes
+        if (step == next_end && blk + 1 < blk1) { ++blk; next_end = a.bend[blk]; } else
+#endif
         if (step == next_end) {
           // flush: C tiles -> shared (warp-private), diagonal sums -> P[seg][blk][0..nlags)
           fold_store_tiles<NA>(acc, fc);
           __syncwarp();
           double* pout = a.p + ((size_t)seg * a.nblk_total + blk) * a.nlags + lag0 + lane;
+          // all shared-memory loads of the fold are issued before the first sum (only the stores are predicated):
+          // one load latency + one adder tree per flush instead of one per group of 32 lags
+          double fv[NA / 4];
+#pragma unroll
+          for (int t = 0; t < NA / 4; ++t) fv[t] = fold_lag(fc, t);
 #pragma unroll
           for (int t = 0; t < NA / 4; ++t)
-            if ((!MULTI || lane + 32 * t < 8 * (NA - 1)) && lag0 + lane + 32 * t < a.nlags) pout[32 * t] = fold_lag(fc, t);
+            if ((!MULTI || lane + 32 * t < 8 * (NA - 1)) && lag0 + lane + 32 * t < a.nlags) pout[32 * t] = fv[t];
           __syncwarp();
 #pragma unroll
           for (int i = 0; i < NA; ++i) acc[i][0] = acc[i][1] = 0.0;
