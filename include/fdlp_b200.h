@@ -319,6 +319,19 @@ int mfcc_forward(mfcc_plan* plan, const mfcc_batch* batch, void* stream);
 int cmvn_apply(float* feats /*dev [n_frames, dim], in place*/, int64_t n_frames, int32_t dim,
                const double* stats /*dev [2, dim+1]*/, int32_t norm_vars, void* stream);
 
+/* ---- allocation-free CMVN accumulation.  NO COUNTERPART IN THE REFERENCE: added
+ *      for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ *      allocation).  stats[2, dim+1] += [sum x (dim), n_frames; sum x^2 (dim), 0] over feats[n_frames, dim] -- the same
+ *      kernels and summation order as the `cmvn_acc` argument of mel_forward (bit-identical results) -- with the per-CTA
+ *      partial sums in a file-scope device array of 296 x 2 x (FDLP_NOALLOC_MAX_DIM + 1) doubles = 1.2 MB that every GPU
+ *      loading the library holds until exit.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library
+ *      routine); dim > FDLP_NOALLOC_MAX_DIM returns FDLP_E_ARG.  All calls on a device share the array: each call
+ *      overwrites every slot it later reads, so it needs no clearing between calls, but two calls that OVERLAP on the GPU
+ *      (different streams, no ordering between them) race -- order them on one stream or with events. ---- */
+#define FDLP_NOALLOC_MAX_DIM 255
+int cmvn_accumulate_noalloc(const float* feats /*dev [n_frames, dim]*/, int64_t n_frames, int32_t dim,
+                            double* stats /*dev [2, dim+1], ADDED to (caller zeroes)*/, void* stream);
+
 /* Synthetic white utterances written straight into a packed device batch (measurement input, SURVEY.md 8d: the
  * 1000-hour workload is never stored).  Bit-identical to speech_recognition_tools_b200/synth.py white_int16(seed,
  * utt_id[u], T_u, scale_q16).  No reference counterpart. */

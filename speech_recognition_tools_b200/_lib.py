@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("FDLP_B200_LIB") or os.path.join(_HERE, "libfdlp_b200.
 FDLP_OK = 0
 FDLP_E_ARG, FDLP_E_CUDA, FDLP_E_UNSUPPORTED, FDLP_E_NOMEM = -1, -2, -3, -4
 FDLP_ABI_VERSION = 200
+FDLP_NOALLOC_MAX_DIM = 255
 FDLP_ST_SINGULAR, FDLP_ST_NONFINITE, FDLP_ST_ENV_RANGE = 1, 2, 4
 FDLP_FBANK_MEL, FDLP_FBANK_COCHLEAR, FDLP_FBANK_CUSTOM = 0, 1, 2
 FDLP_WAV_INT16, FDLP_WAV_FLOAT32, FDLP_WAV_FLOAT64 = 0, 1, 2
@@ -134,6 +135,7 @@ SYMBOLS = [
     ("mfcc_plan_destroy", C.c_int, [C.c_void_p]),
     ("mfcc_forward", C.c_int, [C.c_void_p, C.POINTER(MfccBatch), C.c_void_p]),
     ("cmvn_apply", C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]),
+    ("cmvn_accumulate_noalloc", C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     ("fdlp_modspec_forward", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     ("fdlp_diff_filter", C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),
     ("fdlp_reverb_plan_create", C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),

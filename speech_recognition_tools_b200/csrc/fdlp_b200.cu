@@ -5,6 +5,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -1802,6 +1803,61 @@ extern "C" int cmvn_apply(float* feats, int64_t n_frames, int32_t dim, const dou
   const int64_t blocks = (total + 255) / 256;
   if (blocks > 2147483647LL) return set_err(FDLP_E_ARG, "too many elements%s", "");
   cmvn_apply_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(feats, n_frames, dim, stats, norm_vars);
+  FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
+// ================================================================ allocation-free CMVN accumulation
+// cmvn_accumulate_noalloc: the CMVN partial sums of a finished feature matrix (the same two kernels mel_forward runs
+// for its `cmvn_acc` argument, cmvn_sums_kernel + cmvn_reduce_kernel) for callers that cannot call cudaMalloc: CUDA graph
+// capture, tight serving loops, harnesses that forbid allocation.  The per-CTA partial-sum slots live in a file-scope
+// device array instead of plan scratch.  Every GPU that loads the library holds these kNoAllocBytes until exit.
+constexpr int kNoAllocMaxDim = FDLP_NOALLOC_MAX_DIM;
+constexpr size_t kNoAllocDoubles = (size_t)kMelCmvnCtas * 2 * (kNoAllocMaxDim + 1);  // 296 x 2 x 256 doubles = 1.2 MB
+static __device__ __align__(256) double g_noalloc_cmvn_part[kNoAllocDoubles];
+
+// In host code `g_noalloc_cmvn_part` is only a stand-in for the symbol, not a device address: the address is taken once
+// per device, with that device current, through cudaGetSymbolAddress, and that pointer is what the kernels receive.
+constexpr int kNoAllocMaxDevices = 64;
+static double* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+static std::mutex g_noalloc_mutex;
+
+static int noalloc_scratch(double** out) {
+  int dev = -1;
+  FDLP_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return set_err(FDLP_E_ARG, "device index beyond %s", "64");
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[dev]) {
+    double* ptr = nullptr;
+    FDLP_CUDA(cudaGetSymbolAddress((void**)&ptr, g_noalloc_cmvn_part));
+    if (!ptr) return set_err(FDLP_E_CUDA, "cudaGetSymbolAddress returned a null address%s", "");
+    g_noalloc_ptr[dev] = ptr;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+
+extern "C" int cmvn_accumulate_noalloc(const float* feats, int64_t n_frames, int32_t dim, double* stats, void* stream) {
+  if (!feats || !stats || n_frames < 0 || dim < 1) return set_err(FDLP_E_ARG, "bad argument%s", "");
+  if (dim > kNoAllocMaxDim)
+    return set_err(FDLP_E_ARG,
+                   "cmvn_accumulate_noalloc: dim = %s%ld exceeds FDLP_NOALLOC_MAX_DIM = %ld (the static scratch array); use the "
+                   "cmvn_acc argument of mel_forward / fdlp_forward instead", "", (long)dim, (long)kNoAllocMaxDim);
+  if (n_frames == 0) return FDLP_OK;
+  double* part = nullptr;
+  int rc = noalloc_scratch(&part);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int w = 2 * (dim + 1);
+  CmvnSumArgs c;
+  c.feats = feats; c.part = part; c.n_frames = n_frames; c.J = dim;
+  c.chunk = (n_frames + kMelCmvnCtas - 1) / kMelCmvnCtas;
+  const int rows_par = std::max(1, 256 / dim);
+  // every one of the kMelCmvnCtas slots, all w entries of it, is written by this launch before the reduction reads it:
+  // nothing of the previous call's contents survives into the result, so the array needs no clearing
+  cmvn_sums_kernel<<<kMelCmvnCtas, 256, (size_t)rows_par * 2 * std::min(dim, 256) * sizeof(double), st>>>(c);
+  FDLP_CUDA(cudaGetLastError());
+  cmvn_reduce_kernel<<<w, 256, 0, st>>>(part, kMelCmvnCtas, w, stats);
   FDLP_CUDA(cudaGetLastError());
   return FDLP_OK;
 }

@@ -1,4 +1,4 @@
 cd $GRAFT_REPO_ROOT
-python -m pytest tests -m gpu -x -q -k "fdlp" 2>&1 | tail -5 > gpurun_out/r2_t3.log
-python tools/perf_step.py 1000 > gpurun_out/r2_step3.log 2>&1
-FDLP_B200_LIB=build_variants/lib_noflush.so python tools/perf_step.py 1000 > gpurun_out/r2_step3_noflush.log 2>&1
+python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -15 > gpurun_out/r2_na_alone.log
+python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/r2_na_all.log
+compute-sanitizer --tool memcheck python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -8 > gpurun_out/r2_na_memcheck.log
