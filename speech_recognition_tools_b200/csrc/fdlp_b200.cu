@@ -896,7 +896,8 @@ static int launch_autocorr_family(fdlp_plan* p, const double* dct, int n_seg, do
   // persistent grids: every resident warp draws work items from a counter until none are left
   FDLP_CUDA(cudaMemsetAsync(p->d_next, 0, 2 * sizeof(unsigned long long), st));
   f.next = p->d_next;
-  const int resident = p->sms * (p->fam_groups > 1 ? 2 : 3);
+  static const int ac_ctas_env = getenv("FDLP_AC_CTAS") ? atoi(getenv("FDLP_AC_CTAS")) : 0;  // A/B runs: CTAs per SM
+  const int resident = p->sms * (ac_ctas_env > 0 ? ac_ctas_env : (p->fam_groups > 1 ? 2 : 3));
   const long long tasks = (long long)n_seg * p->fam_ntask * p->fam_groups;
   const dim3 gridA((unsigned)std::min<long long>((tasks + kAcWarps - 1) / kAcWarps, resident)), block(kAcWarps * 32);
   AcRangeArgs d;
