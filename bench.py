@@ -10,9 +10,9 @@ Workload (BASELINE.json configs[1], SURVEY.md 8d cfg #2): 1000 synthetic utteran
 Multi-GPU: utterances are sharded, one batch per rank (weak scaling); the only collective is the
 global-CMVN all-reduce of 2 x (J+1) float64 sums at the end of every step.
 
-Prints ONE JSON line (rank 0).  `--impl reference` times the CPU oracle port (oracle/fdlp.py, the numpy
-restatement of the reference; the reference itself is Python and is not present on the GPU box) on a
-bounded sample of the same workload with all host cores.
+Prints ONE JSON line (rank 0).  `--impl reference` times the reference's own getFeats (oracle/_ref: its three
+files copied unmodified by oracle/make_ref.sh; else the numpy port oracle/fdlp.py) on a bounded sample of the same
+workload with all host cores.
 """
 from __future__ import annotations
 
@@ -96,6 +96,67 @@ def cpu_oracle_throughput(wavs, cores: int, pool=None):
     return audio / dt, audio, dt
 
 
+# --------------------------------------------------------------------------- the reference itself (oracle/_ref)
+def _ref_one(args):
+    """One utterance through the UNMODIFIED reference getFeats (oracle/ref_runner.py)."""
+    os.environ.setdefault("OMP_NUM_THREADS", "1")  # e2e/wsj/path.sh:22
+    x, seed = args
+    from oracle import ref_runner
+    before = ref_runner.fbank_build_seconds()
+    out = ref_runner.fdlp_spectrogram(x, seed=seed, **{k: v for k, v in WSJ.items() if k != "frate"}, frate=WSJ["frate"])
+    return out.shape[0], ref_runner.fbank_build_seconds() - before
+
+
+def reference_available():
+    try:
+        from oracle import ref_runner
+        return ref_runner.available()
+    except Exception:  # noqa: BLE001
+        return False
+
+
+def cpu_reference_throughput(wavs, cores: int, pool=None):
+    """Audio-seconds per wall-second of the reference's own getFeats on `wavs`, one process per core
+    (OMP_NUM_THREADS=1, one shard per process, like the --nj job arrays).  The one-time createFbankCochlear build
+    (6 s per process) happens in a warm-up call and is reported separately."""
+    audio = sum(len(w) for w in wavs) / 16000.0
+    own = pool is None
+    fb = None
+    if own:
+        pool = ProcessPoolExecutor(max_workers=cores, mp_context=mp.get_context('spawn'))
+        warm = list(pool.map(_ref_one, [(wavs[0][:40000], 0)] * (2 * cores)))
+        fb = max(w[1] for w in warm)
+    t0 = time.perf_counter()
+    res = list(pool.map(_ref_one, [(w, i) for i, w in enumerate(wavs)], chunksize=1))
+    dt = time.perf_counter() - t0
+    late_builds = sum(1 for r in res if r[1] > 0)  # a worker that missed the warm-up built its filterbank in the timed part
+    if own:
+        pool.shutdown()
+    return audio / dt, audio, dt, fb, late_builds
+
+
+def cpu_arm(sample, cores):
+    """cpu_baseline record: kind "reference" when oracle/_ref travelled with the snapshot, the port's number beside it."""
+    port_val, cpu_audio, port_dt = cpu_oracle_throughput(sample, cores)
+    rec = {"value": port_val, "unit": UNIT, "cores": cores, "kind": "port",
+           "sample": "first %d utterances of the workload (%.0f audio-s) in %.1f s wall, one process per core, "
+                     "OMP_NUM_THREADS=1" % (len(sample), cpu_audio, port_dt)}
+    if reference_available():
+        try:
+            val, audio, dt, fb, late = cpu_reference_throughput(sample, cores)
+            rec = {"value": val, "unit": UNIT, "cores": cores, "kind": "reference",
+                   "sample": "first %d utterances of the workload (%.0f audio-s) in %.1f s wall through the UNMODIFIED "
+                             "reference getFeats (oracle/_ref, copied by oracle/make_ref.sh), one process per core, "
+                             "OMP_NUM_THREADS=1; the one-time createFbankCochlear build (%.1f s per process) is outside "
+                             "the timed part%s" % (len(sample), audio, dt, fb or 0.0,
+                                                   "" if not late else " except in %d late worker(s)" % late),
+                   "fbank_build_s": fb, "port_value": port_val,
+                   "port_note": "oracle/fdlp.py (numpy restatement, batches the per-band FFTs) on the same sample"}
+        except Exception as e:  # noqa: BLE001
+            rec["reference_error"] = repr(e)
+    return rec
+
+
 # --------------------------------------------------------------------------- clocks
 class ClockSampler:
     """Samples SM clock and throttle reasons with NVML while the timed region runs."""
@@ -146,13 +207,223 @@ class ClockSampler:
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+# --------------------------------------------------------------------------- per-kernel accounting
+def kernel_flops(g, cfg, n_seg):
+    """ALGORITHMIC FP64 flops per launch of every kernel of fdlp_forward.
+    family block sums 2 (p+2) family_taps per segment (band-independent, shared by the J bands); direct remainder
+    2 (p+2) direct_taps per segment; per-band kernel (mel / custom filterbanks) 2 (p+2) support_taps per segment;
+    LPC + cepstrum (2 p^2 + 1.5 L^2) and envelope 2 L kk per (segment, band); DCT 2.5 N log2 N + 6 N per segment."""
+    J, p_, L_, kk_, N = cfg["nfilters"], cfg["order"], g["L"], g["kk"], g["N"]
+    f = {"dct_segments_kernel": (2.5 * N * np.log2(N) + 6.0 * N) * n_seg,
+         "lpc_cepstrum": (2.0 * p_ * p_ + 1.5 * L_ * L_) * J * n_seg,
+         "envelope_dmma_kernel": 2.0 * L_ * kk_ * J * n_seg}
+    if g["nfam"] > 0:
+        f["family_block_autocorr_kernel"] = 2.0 * g["nlags"] * g["family_taps"] * n_seg
+        f["autocorr_direct"] = 2.0 * g["nlags"] * g["direct_taps"] * n_seg
+    else:
+        f["autocorr_direct"] = 2.0 * g["nlags"] * g["support_taps"] * n_seg
+    return f
+
+
+KERNEL_NAMES = {"dct_segments_kernel": "dct_segments_kernel", "family_block_autocorr_kernel": "family_block_autocorr_kernel",
+                "family_scan_kernel": "family_scan_kernel", "autocorr_direct": "autocorr_ranges_kernel",
+                "lpc_cepstrum": "lpc_cepstrum_blk_kernel", "envelope_dmma_kernel": "envelope_dmma_kernel",
+                "ola_log_kernel": "ola_log_kernel"}
+
+
+def profile_kernels(ex, step, n=5):
+    """Per-kernel CUDA-event times (recorded inside fdlp_forward on the launching stream), averaged over n steps."""
+    ex.set_profiling(True)
+    kms = {}
+    for _ in range(n):
+        step()
+        for k, v in ex.kernel_ms().items():
+            kms[k] = kms.get(k, 0.0) + v / n
+    ex.set_profiling(False)
+    return kms
+
+
+def kernel_table(g, cfg, n_seg, kms, peak, step_ms):
+    fl = kernel_flops(g, cfg, n_seg)
+    if g["nfam"] == 0:
+        KERNEL_NAMES_local = dict(KERNEL_NAMES, autocorr_direct="autocorr_dmma_kernel")
+    else:
+        KERNEL_NAMES_local = KERNEL_NAMES
+    table = {}
+    for k, ms in kms.items():
+        if ms <= 0:
+            continue
+        e = {"ms": ms, "share_of_step": ms / step_ms}
+        if k in fl:
+            e["algorithmic_tflops"] = fl[k] / (ms * 1e-3) / 1e12
+            e["frac"] = e["algorithmic_tflops"] / peak
+        table[KERNEL_NAMES_local[k]] = e
+    total = float(sum(fl.values()))
+    return table, total, {KERNEL_NAMES_local[k]: v for k, v in fl.items()}
+
+
+def fp64_peak():
+    import ctypes as C
+
+    from speech_recognition_tools_b200 import _lib
+    lib = _lib.load()
+    dfma, dmma = C.c_double(), C.c_double()
+    _lib.check(lib.fdlp_measure_fp64_peak(C.byref(dfma), C.byref(dmma)))
+    return dfma.value, dmma.value
+
+
+def resident_block(name, cfg, wavs, dev, peak, noise=None, steps=5, warmup=3):
+    """One more workload of BASELINE.json `configs`, batch resident in HBM, same CUDA-event method as the main line:
+    step time, xRT and the per-kernel roofline fractions (no host copies; parity of these shapes is in tests/)."""
+    import torch
+
+    from speech_recognition_tools_b200.fdlp import FdlpConfig, FdlpExtractor
+    ex = FdlpExtractor(FdlpConfig(**cfg), device=dev)
+    host, lens = ex.pack(wavs)
+    lay = ex.layout(lens, jitter=0).to(dev)
+    wav = host.to(dev)
+    nd = ex._noise_to_device(noise, lay) if noise is not None else None
+    feats = torch.empty((lay.n_frames, cfg["nfilters"]), dtype=torch.float32, device=dev)
+    status = torch.zeros(lay.n_utt, dtype=torch.int32, device=dev)
+
+    def step():
+        ex.forward_packed(wav, lay, feats=feats, status=status, noise_dev=nd)
+
+    for _ in range(warmup):
+        step()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    kms = profile_kernels(ex, step, 3)
+    table, total_flops, _ = kernel_table(ex.geom, cfg, lay.n_seg, kms, peak, ms)
+    audio = float(np.sum(lens)) / 16000.0
+    out = {"workload": name, "params": cfg, "utterances": len(wavs), "audio_seconds": audio, "segments": int(lay.n_seg),
+           "ms_per_step": ms, "value": audio / (ms * 1e-3), "unit": UNIT,
+           "step_frac": total_flops / (ms * 1e-3) / 1e12 / peak, "kernels": table,
+           "utterances_with_status": int((status != 0).sum().item())}
+    ex.close()
+    del feats, wav
+    torch.cuda.empty_cache()
+    return out
+
+
+def multi_gpu_check(ex, wavs, lay, feats, cmvn_reduced, dev, world, rank):
+    """Correctness of the N-rank step (sharded output == single-GPU output bit for bit, all-reduced
+    CMVN == single-process FP64 sum):
+      * the all-reduced stats hold the frame count of every rank's batch and equal the float64 sums torch computes
+        from the ranks' feature matrices (all-reduced the same way), to 1e-12;
+      * every rank extracts the SAME probe batch (the first 48 utterances of rank 0's workload, broadcast from rank 0)
+        and the SHA-1 digests of the feature bytes agree across ranks, i.e. any GPU of the job reproduces rank 0's
+        output bit for bit;
+      * `feature_sha1` of rank 0's own batch goes into the JSON line: the N = 1 run extracts the same batch, so the
+        lines of a scaling run can be compared with each other."""
+    import hashlib
+
+    import torch
+    import torch.distributed as dist
+    J = feats.shape[1]
+    res = {}
+    frames = torch.tensor([float(lay.n_frames)], dtype=torch.float64, device=dev)
+    fsum = torch.zeros((2, J), dtype=torch.float64, device=dev)
+    f64 = feats.double()
+    fsum[0], fsum[1] = f64.sum(0), (f64 * f64).sum(0)
+    del f64
+    if world > 1:
+        dist.all_reduce(frames)
+        dist.all_reduce(fsum)
+    c = cmvn_reduced
+    ok_count = float(c[0, J].item()) == float(frames.item())
+    err = float(((c[:, :J] - fsum).abs() / fsum.abs().clamp_min(1e-300)).max().item())
+    res["cmvn_frames"] = float(c[0, J].item())
+    res["cmvn_frames_expected"] = float(frames.item())
+    res["cmvn_max_rel_err_vs_fp64_sum"] = err
+    # probe batch: same samples on every rank
+    n_probe = min(48, len(wavs))
+    if rank == 0:
+        lens_t = torch.tensor([len(w) for w in wavs[:n_probe]], dtype=torch.int64, device=dev)
+    else:
+        lens_t = torch.zeros(n_probe, dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.broadcast(lens_t, 0)
+    lens_p = [int(v) for v in lens_t.cpu()]
+    if rank == 0:
+        samples = torch.from_numpy(np.concatenate(wavs[:n_probe])).to(dev)
+    else:
+        samples = torch.zeros(sum(lens_p), dtype=torch.int16, device=dev)
+    if world > 1:
+        dist.broadcast(samples, 0)
+    play = ex.layout(lens_p, jitter=12345).to(dev)
+    pf, _ = ex.forward_packed(samples, play)
+    digest = hashlib.sha1(pf.cpu().numpy().tobytes()).digest()
+    dig_t = torch.tensor(list(digest), dtype=torch.int64, device=dev)
+    if world > 1:
+        alld = [torch.zeros_like(dig_t) for _ in range(world)]
+        dist.all_gather(alld, dig_t)
+    else:
+        alld = [dig_t]
+    same = all(bool(torch.equal(d, alld[0])) for d in alld)
+    res["probe_utterances"] = n_probe
+    res["probe_digests_equal_on_all_ranks"] = same
+    res["probe_sha1"] = digest.hex()
+    res["feature_sha1"] = hashlib.sha1(feats.cpu().numpy().tobytes()).hexdigest() if rank == 0 else None
+    res["status"] = "ok" if (ok_count and err <= 1e-12 and same) else "FAILED"
+    return res
+
+
+def cli_e2e(wavs, audio_s, dev_index):
+    """The boundary the recipes call (make_FDLPspectrum_feats.sh:141-157): `computeFDLPSpectrogram.py <scp> <out> ...`
+    on an scp of WAV files, Kaldi ark/scp/len out.  WAVs and outputs live on tmpfs; the shim runs in this process
+    (python + torch start-up, ~6 s per process, is excluded), twice: the first run creates the plan (filterbank,
+    family analysis, tables), the second is the steady state of a long shard."""
+    import contextlib
+    import io
+    import shutil
+    import tempfile
+
+    from scipy.io import wavfile
+
+    from speech_recognition_tools_b200.cli import computeFDLPSpectrogram as cf
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+    d = tempfile.mkdtemp(prefix="fdlp_cli_", dir=base)
+    try:
+        with open(os.path.join(d, "wav.scp"), "w") as f:
+            for u, w in enumerate(wavs):
+                path = os.path.join(d, "u%04d.wav" % u)
+                wavfile.write(path, 16000, w)
+                f.write("utt%04d %s\n" % (u, path))
+        argv = [os.path.join(d, "wav.scp"), os.path.join(d, "out"), "--write_utt2num_frames",
+                "--fbank_type=" + WSJ["fbank_type"], "--gamma_weight=None", "--add_reverb=clean", "--add_noise=clean",
+                "--coeff_num=%d" % WSJ["coeff_num"], "--coeff_range=" + WSJ["coeff_range"], "--order=%d" % WSJ["order"],
+                "--overlap_fraction=0.25", "--nfilters=%d" % WSJ["nfilters"], "--fduration=1.5", "--frate=100"]
+        args = cf.get_parser().parse_args(argv)
+        walls = []
+        for _ in range(3):
+            sink = io.StringIO()
+            t0 = time.perf_counter()
+            with contextlib.redirect_stdout(sink):
+                cf.getFeats(args)
+            walls.append(time.perf_counter() - t0)
+        ark_bytes = os.path.getsize(os.path.join(d, "out.ark"))
+        best = min(walls[1:])
+        return {"value": audio_s / best, "unit": UNIT, "wall_s": best, "first_run_wall_s": walls[0],
+                "wav_files": len(wavs), "ark_bytes": ark_bytes, "storage": "tmpfs" if base else "tmp",
+                "api": "cli/computeFDLPSpectrogram.py getFeats(args): scp of WAV files -> ark/scp/len (reader threads, "
+                       "copy/compute overlap, incremental ark writer); in-process, best of 2 runs after the first"}
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+
+
 # --------------------------------------------------------------------------- our arm
 def run_ours(args):
     import torch
     import torch.distributed as dist
 
-    from speech_recognition_tools_b200 import _lib
-    from speech_recognition_tools_b200.fdlp import FdlpConfig, FdlpExtractor
+    from speech_recognition_tools_b200.fdlp import FdlpConfig, FdlpExtractor, NoiseSpec
     from speech_recognition_tools_b200.mel import MelConfig, MelExtractor
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -222,14 +493,32 @@ def run_ours(args):
     value = total_audio / (ms_per_step * 1e-3)
     bad_status = int((status != 0).sum().item())
 
-    # ---- end to end through the public API path: pinned host wav -> device, features -> pinned host ----
+    # ---- correctness of the N-rank step (features of the last timed step, all-reduced stats) ----
+    mgc = multi_gpu_check(ex, wavs, lay, feats, cmvn, dev, world, rank)
+
+    # ---- end to end through the public API: a list of host waveforms in, pinned-host features out.  Inside the timed
+    #      region, every step: the batch layout (segment / frame tables, 7000 jitter draws), packing the utterances
+    #      into pinned staging memory, host -> device copies, the kernels, device -> host copy of the features. ----
+    E2E_CHUNKS = int(os.environ.get("FDLP_E2E_CHUNKS", "6"))
     idx_bytes = sum(int(v.numel() * v.element_size()) for k, v in lay.dev.items() if k == "_buf")
 
-    E2E_CHUNKS = int(os.environ.get("FDLP_E2E_CHUNKS", "6"))
-
     def step_e2e():
-        # FdlpExtractor.extract_host: samples pinned host -> device, index tables -> device, the kernels, features
-        # device -> pinned host, in E2E_CHUNKS runs of whole utterances so that the copies overlap the kernels
+        cmvn.zero_()
+        ex.extract_list(wavs, jitter=rank, feats_host=feats_host, cmvn=cmvn, status=status, n_chunks=E2E_CHUNKS,
+                        wav_dev=wav_dev, feats=feats)
+        if world > 1:
+            dist.all_reduce(cmvn)
+        torch.cuda.current_stream(dev).synchronize()
+
+    for _ in range(3):
+        step_e2e()
+    e2e_steps = max(3, min(args.steps, 10))
+    e2e_ms = timed(step_e2e, e2e_steps) / e2e_steps
+    e2e_value = total_audio / (e2e_ms * 1e-3)
+    h2d = int(host_wav.numel() * host_wav.element_size()) + idx_bytes
+    d2h = int(feats_host.numel() * 4)
+
+    def step_e2e_packed():  # round-1 definition, kept for comparison: packed pinned buffer + layout made beforehand
         cmvn.zero_()
         ex.extract_host(host_wav, lay, feats_host=feats_host, n_chunks=E2E_CHUNKS, cmvn=cmvn, status=status,
                         wav_dev=wav_dev, feats=feats)
@@ -238,81 +527,85 @@ def run_ours(args):
         torch.cuda.current_stream(dev).synchronize()
 
     for _ in range(2):
-        step_e2e()
-    e2e_steps = max(3, min(args.steps, 10))
-    e2e_ms = timed(step_e2e, e2e_steps) / e2e_steps
-    e2e_value = total_audio / (e2e_ms * 1e-3)
-    h2d = int(host_wav.numel() * host_wav.element_size()) + idx_bytes
-    d2h = int(feats_host.numel() * 4)
+        step_e2e_packed()
+    e2e_packed_ms = timed(step_e2e_packed, e2e_steps) / e2e_steps
 
-    # ---- per-stage device times of the dominant kernel (CUDA events inside fdlp_forward, same stream) ----
-    ex.set_profiling(True)
-    stage = {"dct": 0.0, "autocorr": 0.0, "lpc_env": 0.0, "ola": 0.0}
-    ac_ms = {"family_blocks": 0.0, "combine": 0.0, "direct": 0.0}
-    kms = {}
-    nprof = 5
-    for _ in range(nprof):
-        step_resident()
-        s = ex.stage_ms()
-        for k in stage:
-            stage[k] += s[k] / nprof
-        s = ex.autocorr_ms()
-        for k in ac_ms:
-            ac_ms[k] += s[k] / nprof
-        for k, v in ex.kernel_ms().items():
-            kms[k] = kms.get(k, 0.0) + v / nprof
-    ex.set_profiling(False)
+    kms = profile_kernels(ex, step_resident, 5)
 
     out = None
     if rank == 0:
-        lib = _lib.load()
-        import ctypes as C
-        dfma, dmma = C.c_double(), C.c_double()
-        _lib.check(lib.fdlp_measure_fp64_peak(C.byref(dfma), C.byref(dmma)))
-        peak = max(dfma.value, dmma.value)
+        dfma, dmma = fp64_peak()
+        peak = max(dfma, dmma)
         g = ex.geom
-        p_, L_, kk_ = WSJ["order"], g["L"], g["kk"]
-        # ALGORITHMIC flops per launch of each FP64 kernel.  Autocorrelation, family path:
-        #   block sums   2 (p+2) * nfam * N          per segment  (band-independent, shared by the J bands)
-        #   direct part  2 (p+2) * sum_j direct_j    per segment  (blocks that straddle a filter-region boundary)
-        # direct path (mel / custom filterbanks): 2 (p+2) * sum_j len(supp_j) per segment.
-        # LPC + cepstrum + envelope: (2 p^2 + 1.5 L^2 + 2 L kk) per (segment, band).
         nseg = lay.n_seg
-        kern = {}
-        if g["nfam"] > 0:
-            kern["family_block_autocorr_kernel"] = (kms["family_block_autocorr_kernel"], 2.0 * g["nlags"] * g["family_taps"] * nseg)
-            kern["autocorr_ranges_kernel"] = (kms["autocorr_direct"], 2.0 * g["nlags"] * g["direct_taps"] * nseg)
-        else:
-            kern["autocorr_dmma_kernel"] = (kms["autocorr_direct"], 2.0 * g["nlags"] * g["support_taps"] * nseg)
-        kern["lpc_cepstrum_blk_kernel"] = (kms["lpc_cepstrum"], (2.0 * p_ * p_ + 1.5 * L_ * L_) * J * nseg)
-        kern["envelope_dmma_kernel"] = (kms["envelope_dmma_kernel"], 2.0 * L_ * kk_ * J * nseg)
-        top = max(kern, key=lambda k: kern[k][0])
-        top_ms, top_flops = kern[top]
+        table, step_flops, fl = kernel_table(g, WSJ, nseg, kms, peak, ms_per_step)
+        flop_kernels = {k: v for k, v in table.items() if "frac" in v}
+        top = max(flop_kernels, key=lambda k: flop_kernels[k]["ms"])
+        top_ms, top_flops = table[top]["ms"], fl[top]
         achieved = top_flops / (top_ms * 1e-3) / 1e12
-        ac_flops_support = 2.0 * g["nlags"] * g["support_taps"] * nseg
-        traffic = None
+        step_tflops = step_flops / (ms_per_step * 1e-3) / 1e12
+        # SURVEY.md 8(d) counts the autocorrelation over the dense support of every band (W_seg = 591.9 MFLOP / segment
+        # at these parameters); the family decomposition removes most of those flops algebraically
+        survey_w_seg = 2.0 * g["nlags"] * J * g["N"] + 2.0 * J * WSJ["order"] ** 2 + 1.5 * J * g["L"] ** 2 \
+            + 2.0 * J * g["L"] * g["kk"] + (2.5 * g["N"] * np.log2(g["N"]) + 6 * g["N"])
+        survey_tflops = survey_w_seg * nseg / (ms_per_step * 1e-3) / 1e12
+        traffic = traffic_step = None
         tp = os.path.join(ROOT, "profiles", "top_kernel_traffic.json")
         if os.path.exists(tp):
             try:
                 td = json.load(open(tp))  # dram__bytes_read.sum + dram__bytes_write.sum per launch (ncu --set full)
                 if int(td.get("segments", -1)) == int(nseg):  # captured at this batch size only
-                    traffic = td["kernels"][top]["dram_bytes"]
+                    traffic = td["kernels"].get(top, {}).get("dram_bytes")
+                    traffic_step = float(sum(v["dram_bytes"] for v in td["kernels"].values()))
             except Exception:  # noqa: BLE001
                 traffic = None
-        roofline = {"bound": "tensor", "pipe": "fp64 (DMMA.8x8x4 / DFMA)", "kernel": top,
-                    "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                    "traffic": traffic, "peak_source": "fdlp_measure_fp64_peak, measured live on this GPU "
-                    "(MEASURED_PEAKS.json has no FP64 entry); dfma=%.2f dmma=%.2f" % (dfma.value, dmma.value),
-                    "algorithmic_flops_per_launch": top_flops, "top_kernel_ms": top_ms,
-                    "kernels": {k: {"ms": v[0], "algorithmic_tflops": v[1] / (v[0] * 1e-3) / 1e12 if v[0] > 0 else None,
-                                    "frac": (v[1] / (v[0] * 1e-3) / 1e12 / peak) if v[0] > 0 else None}
-                                for k, v in kern.items()},
-                    "autocorr": {"ms": stage["autocorr"], "family_combine_ms": ac_ms["combine"],
-                                 "per_band_support_flops": ac_flops_support,
-                                 "per_band_equivalent_tflops": ac_flops_support / (stage["autocorr"] * 1e-3) / 1e12,
-                                 "note": "per-band-equivalent = flops a per-band direct evaluation over the filters' "
-                                         "support would execute; the family decomposition shares most of them"},
-                    "stage_ms": stage, "kernel_ms": kms, "share_of_step": top_ms / sum(stage.values())}
+        roofline = {
+            "bound": "tensor", "pipe": "fp64 (DMMA.8x8x4 / DFMA)", "kernel": top,
+            "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+            "traffic": traffic, "share_of_step": top_ms / ms_per_step,
+            "peak_source": "fdlp_measure_fp64_peak, measured live on this GPU (MEASURED_PEAKS.json has no FP64 entry); "
+                           "dfma=%.2f dmma=%.2f" % (dfma, dmma),
+            "algorithmic_flops_per_launch": top_flops, "top_kernel_ms": top_ms,
+            # the whole step, not one kernel: algorithmic FP64 flops of all kernels / step time / peak
+            "step_frac": step_tflops / peak, "step_tflops": step_tflops, "step_flops": step_flops,
+            "survey_w_seg_tflops": survey_tflops,
+            "survey_w_seg_note": "SURVEY.md 8(d)'s W_seg counts the autocorrelation over the dense support of all %d bands "
+                                 "(%.1f MFLOP / segment); the family decomposition + tail cut evaluate %.1f MFLOP / segment "
+                                 "for the same result, so W_seg / step time = %.0f TFLOP/s = %.1fx the FP64 peak is not a "
+                                 "utilisation: step_frac (executed algorithmic flops) is"
+                                 % (J, survey_w_seg / 1e6, step_flops / nseg / 1e6, survey_tflops, survey_tflops / peak),
+            "algorithmic_bytes": h2d + d2h, "traffic_step_bytes": traffic_step,
+            "traffic_note": "dram bytes of all kernels of one step (ncu, profiles/top_kernel_traffic.json) against the "
+                            "samples in + features out; the difference is float64 scratch (dct, block sums, lags, cepstra, "
+                            "envelopes) written and re-read between kernels",
+            "kernels": table}
+
+        # ---- the other configs of BASELINE.json, resident, with their own per-kernel fractions ----
+        extra = []
+        try:
+            names = ["babble", "buccaneer1", "car", "pink"]
+            lens3 = synth.wsj_shaped_lengths(125, seed=77)
+            streams = []
+            for s_, T in enumerate(lens3):
+                src = synth.white_int16(3, s_, int(T) + 64).astype(np.float64)
+                for c_ in range(8):  # 8 channels = 8 mono streams: delayed, attenuated copies of the source
+                    streams.append(np.round((1.0 - 0.06 * c_) * src[7 * c_:7 * c_ + int(T)]).astype(np.int16))
+            rs = np.random.RandomState(11)
+            noise = NoiseSpec(samples=[synth.noise_int16(n, 20 * 16000) for n in names],
+                              snr_db=rs.uniform(0.0, 40.0, len(streams)), rand=rs.rand(len(streams)),
+                              which=[i % len(names) for i in range(len(streams))], mode="int16_wrap")
+            extra.append(resident_block("configs[2]: REVERB-shaped, 125 utterances x 8 channel streams, REVERB recipe "
+                                        "params (coeff_num 450 -> L = 300), per-stream noise type / SNR / offset",
+                                        dict(WSJ, coeff_num=450, coeff_range="1,450"), streams, dev, peak, noise=noise))
+            long_wavs = [synth.white_int16(9, u, 480000) for u in range(64)]
+            extra.append(resident_block("configs[3]: long-segment stress, 64 utterances x 30 s, 3.0 s segments, 128 cochlear "
+                                        "bands, LPC order 300, 300 cepstral coefficients",
+                                        dict(nfilters=128, order=300, fduration=3.0, frate=100, overlap_fraction=0.25,
+                                             coeff_num=300, coeff_range="0,300", fbank_type=WSJ["fbank_type"]),
+                                        long_wavs, dev, peak, steps=3, warmup=2))
+            del long_wavs, streams
+        except Exception as e:  # noqa: BLE001 -- the main line must not depend on the extra blocks
+            extra.append({"error": repr(e)})
 
         # ---- mel-spectrogram baseline path on the same batch (BASELINE.json configs[1]) ----
         mel = MelExtractor(MelConfig(**MEL_RECIPE), device=dev)
@@ -329,8 +622,15 @@ def run_ours(args):
         torch.cuda.synchronize(dev)
         mel_ms = e0.elapsed_time(e1) / 5
         mel_bytes = host_wav.numel() * 2 + mfeats.numel() * 4
+        hbm_peak = None
+        try:
+            hbm_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+        except Exception:  # noqa: BLE001
+            hbm_peak = 6540.8  # MEASURED_PEAKS.json of the build container (driver-written); absent on this box
         mel_info = {"value": audio_s / (mel_ms * 1e-3), "unit": UNIT, "ms_per_step": mel_ms,
-                    "hbm_gbs_algorithmic": mel_bytes / (mel_ms * 1e-3) / 1e9}
+                    "hbm_gbs_algorithmic": mel_bytes / (mel_ms * 1e-3) / 1e9, "hbm_peak_gbs": hbm_peak,
+                    "frac_of_hbm": mel_bytes / (mel_ms * 1e-3) / 1e9 / hbm_peak}
+        del mfeats
 
         # ---- --add_reverb augmentation on the same batch: reverberation alone and followed by the extraction ----
         from speech_recognition_tools_b200.reverb import Reverberator
@@ -372,16 +672,22 @@ def run_ours(args):
                        "scratch_gb": rv.scratch_bytes(len(pair_utt), len(lens)) / 1e9}
         rv.close()
         del rwav
+        torch.cuda.empty_cache()
 
-        # ---- CPU baseline: the oracle port on a bounded sample of the same workload ----
+        # ---- the boundary the recipes call: scp of WAV files -> ark/scp/len through the CLI shim ----
         if old_affinity is not None:
             os.sched_setaffinity(0, old_affinity)
+        try:
+            e2e_cli = cli_e2e(wavs, audio_s, local_rank)
+            e2e_cli["ratio_to_e2e"] = e2e_cli["value"] / (audio_s / (e2e_ms * 1e-3))
+        except Exception as e:  # noqa: BLE001
+            e2e_cli = {"error": repr(e)}
+
+        # ---- CPU baseline on a bounded sample of the same workload: the reference's own getFeats (oracle/_ref, copied
+        #      unmodified by oracle/make_ref.sh) when it travelled with the snapshot, and the numpy port beside it ----
         cores = os.cpu_count() or 1
-        n_sample = min(len(wavs), max(cores * 3, 32))
-        cpu_val, cpu_audio, cpu_dt = cpu_oracle_throughput(wavs[:n_sample], cores)
-        cpu_baseline = {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port",
-                        "sample": "first %d utterances of the workload (%.0f audio-s) in %.1f s wall, one process "
-                                  "per core, OMP_NUM_THREADS=1" % (n_sample, cpu_audio, cpu_dt)}
+        n_sample = min(len(wavs), max(cores * 2, 32))
+        cpu_baseline = cpu_arm(wavs[:n_sample], cores)
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -393,11 +699,18 @@ def run_ours(args):
                        "sharding": "utterances sharded across ranks, no data-path collective; CMVN all-reduce per step",
                        "utterances_with_status": bad_status},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
-                    "ms_per_step": e2e_ms, "api": "FdlpExtractor.extract_host (pinned host samples in, pinned host "
-                    "features out, %d utterance chunks: copies overlap the kernels)" % E2E_CHUNKS},
-            "gpu_launches": (7 if ex.geom["nfam"] > 0 else 5) * args.steps * world,
+                    "ms_per_step": e2e_ms,
+                    "api": "FdlpExtractor.extract_list: a list of host int16 arrays in, pinned host features out; inside "
+                           "the timed region: batch layout (segment / frame tables, jitter draws), packing into pinned "
+                           "staging memory, %d utterance chunks whose copies overlap the kernels" % E2E_CHUNKS,
+                    "packed_input_ms_per_step": e2e_packed_ms,
+                    "packed_input_note": "round-1 definition (FdlpExtractor.extract_host on an already packed pinned "
+                                         "buffer with the layout made beforehand), for comparison"},
+            "e2e_cli": e2e_cli,
+            "gpu_launches": ((7 if ex.geom["nfam"] > 0 else 5) + 1) * args.steps * world,
+            "multi_gpu_check": mgc["status"], "multi_gpu_check_detail": mgc,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "mel_baseline": mel_info,
-            "add_reverb": reverb_info,
+            "add_reverb": reverb_info, "other_configs": extra,
         }
     if world > 1:
         dist.barrier()
@@ -409,32 +722,52 @@ def run_ours(args):
 
 # --------------------------------------------------------------------------- reference arm
 def run_reference(args):
+    """`--impl reference`: the reference's own CPU implementation of the path on this box's host cores -- the UNMODIFIED
+    getFeats from oracle/_ref when that copy is present, else the numpy port in oracle/fdlp.py -- each step a bounded
+    sample of the rank-0 workload.  Rank 0 alone runs it."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cores = os.cpu_count() or 1
     n_sample = max(cores * 2, 16)
     wavs, lengths = build_workload(0, n_utt=n_sample, workers=min(cores, 16))
+    use_ref = reference_available()
+    one = _ref_one if use_ref else _oracle_one
     pool = ProcessPoolExecutor(max_workers=cores, mp_context=mp.get_context('spawn'))
-    list(pool.map(_oracle_one, [(wavs[0][:40000], 0)] * cores))
+    t0 = time.perf_counter()
+    warm_res = list(pool.map(one, [(wavs[0][:40000], 0)] * (2 * cores)))  # start workers, build the filterbank once each
+    setup_s = time.perf_counter() - t0
+    fb = max((w[1] for w in warm_res), default=0.0) if use_ref else None
+    run = (lambda: cpu_reference_throughput(wavs, cores, pool)[:3]) if use_ref else (lambda: cpu_oracle_throughput(wavs, cores, pool))
     warm = max(args.warmup, 1)
     for _ in range(min(warm, 1)):
-        cpu_oracle_throughput(wavs, cores, pool)
+        run()
     t_audio, t_wall = 0.0, 0.0
     for _ in range(args.steps):
-        _, a, dt = cpu_oracle_throughput(wavs, cores, pool)
+        _, a, dt = run()
         t_audio += a
         t_wall += dt
     pool.shutdown()
     value = t_audio / t_wall
-    sample = ("each step = first %d utterances of the rank-0 workload (%.0f audio-s), oracle/fdlp.py (numpy/scipy "
-              "restatement of the reference, float64), one process per core, OMP_NUM_THREADS=1" % (n_sample, t_audio / args.steps))
+    if use_ref:
+        kind = "reference"
+        sample = ("each step = first %d utterances of the rank-0 workload (%.0f audio-s) through the UNMODIFIED reference "
+                  "getFeats (oracle/_ref: features.py, computeFDLPSpectrogram.py copied by oracle/make_ref.sh; shims: "
+                  "in-memory capture instead of Kaldi copy-feats, seeded RNGs, memoised createFbankCochlear), one process "
+                  "per core, OMP_NUM_THREADS=1; one-time setup outside the timed steps: %.1f s, of which "
+                  "createFbankCochlear %.1f s per process" % (n_sample, t_audio / args.steps, setup_s, fb or 0.0))
+    else:
+        kind = "port"
+        sample = ("each step = first %d utterances of the rank-0 workload (%.0f audio-s), oracle/fdlp.py (numpy/scipy "
+                  "restatement of the reference, float64; oracle/_ref did not travel with this snapshot), one process per "
+                  "core, OMP_NUM_THREADS=1" % (n_sample, t_audio / args.steps))
     out = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": warm, "ms_per_step": 1e3 * t_wall / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "params": WSJ, "note": "CPU reference arm runs on rank 0 only, on a bounded sample"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
+                         "fbank_build_s": fb},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

@@ -18,12 +18,14 @@ if _ROOT not in sys.path:
     sys.path.insert(0, _ROOT)
 
 from speech_recognition_tools_b200 import _lib  # noqa: E402
-from speech_recognition_tools_b200.cli.common import iter_scp, load_noise, write_lens  # noqa: E402
+from speech_recognition_tools_b200.cli.common import load_noise, write_lens  # noqa: E402
 from speech_recognition_tools_b200.fdlp import FdlpConfig, FdlpExtractor, NoiseSpec, segment_count  # noqa: E402
-from speech_recognition_tools_b200.kaldi_io import write_ark_scp  # noqa: E402
 from speech_recognition_tools_b200.reverb import Reverberator, load_rir  # noqa: E402
 
-MAX_SEGMENTS_PER_BATCH = 4096
+MAX_SEGMENTS_PER_BATCH = int(os.environ.get("FDLP_CLI_MAX_SEGMENTS", "8192"))
+
+
+_PLANS = {}
 
 
 class _GlobalRandom:
@@ -35,6 +37,19 @@ class _GlobalRandom:
 
 
 def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
+    """The reference's entry point (computeFDLPSpectrogram.py:29-237) on the GPU.  Beyond the reference:
+    * launched under torchrun (RANK / WORLD_SIZE / LOCAL_RANK) every rank takes a balanced share of the scp, writes
+      `<outfile>.<JOB>.ark/.scp/.len` (JOB = rank + 1, the wrapper's naming) and rank 0 writes the merged
+      `<outfile>.scp/.len` plus the all-reduced `<outfile>.cmvn.ark` (compute-cmvn-stats, e2e/wsj/run_fdlp_e1.sh:280);
+    * FDLP_JITTER_SEED=<int> draws the overlap-add jitter per utterance from Random(crc32(uttid) ^ f(seed)) instead of
+      the process-wide stream, so that results do not depend on batching or on the rank that owns the utterance;
+    * FDLP_WRITE_CMVN=1 writes `<outfile>.cmvn.ark` in a single-process run too."""
+    import torch
+
+    from speech_recognition_tools_b200 import cmvn as cmvn_mod
+    from speech_recognition_tools_b200.cli import pipeline as pl
+    from speech_recognition_tools_b200.fdlp import batch_layout
+    from speech_recognition_tools_b200.kaldi_io import write_cmvn_ark
     if window is not np.hamming:
         raise NotImplementedError("only the Hamming window of the reference recipes is implemented")
     cfg = FdlpConfig.from_args(args)
@@ -55,53 +70,83 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
     if args.odd_mod_zero:
         print("%s: Ignoring odd modulations... " % sys.argv[0])
 
-    ex = FdlpExtractor(cfg)
-    g = ex.geom
-    all_feats, all_lens, bad = {}, {}, []
+    rank, world, local_rank = pl.dist_env()
+    device = None
+    if world > 1:
+        import torch.distributed as dist
+        device = torch.device("cuda:%d" % local_rank)
+        torch.cuda.set_device(device)
+        if not dist.is_initialized():
+            dist.init_process_group("nccl", device_id=device)
+    # one plan per (configuration, device) and process: a second getFeats call in the same process (tests, bench.py's
+    # e2e_cli, a wrapper that loops over shards) reuses filterbank, tables and scratch
+    key = (repr(cfg), str(device))
+    ex = _PLANS.get(key)
+    if ex is None:
+        ex = _PLANS[key] = FdlpExtractor(cfg, device=device)
+    g, J = ex.geom, cfg.nfilters
 
-    def flush(batch):
-        if not batch:
-            return
-        ids = [b[0] for b in batch]
-        wavs = [b[1] for b in batch]
-        nspec = None
-        if noise == "diff":
-            nspec = "diff"
-        elif noise is not None:
-            draws = [np.random.rand() for _ in wavs]  # features.py:25, one draw per utterance in scp order
-            nspec = NoiseSpec(samples=noise[0], snr_db=noise[1], rand=draws, mode="int16_wrap")
-        nonlocal reverberator
-        if rir is not None and reverberator is None:
-            reverberator = Reverberator(rir, device=ex.device)
-        outs, status = ex(wavs, jitter=_GlobalRandom(), noise=nspec, return_status=True, reverb=reverberator)
-        st = status.cpu().numpy()
-        for u, (k, o) in enumerate(zip(ids, outs)):
-            all_feats[k] = o.cpu().numpy()
-            all_lens[k] = int(o.shape[0])
-            if st[u] & _lib.FDLP_ST_SINGULAR:
-                bad.append(k)
+    def seg_count(T):
+        return segment_count(T, g["N"], g["S"])
 
-    batch, nseg, dtype = [], 0, None
-    for uttid, signal in iter_scp(args.scp, args.scp_type, srate):
-        print("%s: Computing Features for file: %s" % (sys.argv[0], uttid))
-        sys.stdout.flush()
-        n = segment_count(len(signal), g["N"], g["S"])
-        if batch and (nseg + n > MAX_SEGMENTS_PER_BATCH or signal.dtype != dtype):
-            flush(batch)
-            batch, nseg = [], 0
-        batch.append((uttid, signal))
-        nseg += n
-        dtype = signal.dtype
-    flush(batch)
-    ex.close()
-    if bad:
-        # the reference raises numpy.linalg.LinAlgError('Singular principal minor') at the first such utterance
-        raise np.linalg.LinAlgError("Singular principal minor in utterance(s): %s" % " ".join(bad))
-    write_ark_scp(all_feats.items(), args.outfile + ".ark", args.outfile + ".scp")
+    entries = pl.parse_scp(args.scp)
+    mine = pl.shard_entries(entries, world, rank, seg_count, args.scp_type) if world > 1 else entries
+    outbase = args.outfile if world == 1 else "%s.%d" % (args.outfile, rank + 1)
+    seed_env = os.environ.get("FDLP_JITTER_SEED")
+    acc = cmvn_mod.new_accumulator(J, ex.device)
+    overlapped = rir is None and noise != "diff"  # samples go to the kernels as they are: copies overlap the compute
+
+    with pl.HostPipeline(mine, args.scp_type, srate, seg_count, MAX_SEGMENTS_PER_BATCH, outbase + ".ark",
+                         outbase + ".scp", singular_bit=_lib.FDLP_ST_SINGULAR, keep=return_feats) as pipe:
+        for hb in pipe:
+            n_utt = len(hb.ids)
+            jitter = _GlobalRandom() if seed_env is None else [pl.utt_seed(int(seed_env), k) for k in hb.ids]
+            nspec = None
+            if noise == "diff":
+                nspec = "diff"
+            elif noise is not None:
+                draws = [np.random.rand() for _ in range(n_utt)]  # features.py:25, one draw per utterance in scp order
+                nspec = NoiseSpec(samples=noise[0], snr_db=noise[1], rand=draws, mode="int16_wrap")
+            st_host = torch.empty(n_utt, dtype=torch.int32, pin_memory=True)
+            if overlapped:
+                lay = batch_layout(hb.lengths, g, cfg.frate, cfg.srate, jitter)
+                nd = ex._noise_to_device(nspec, lay) if nspec is not None else None
+                feats_host = pipe.feats_buffer(hb, lay.n_frames, J)
+                status = torch.zeros(n_utt, dtype=torch.int32, device=ex.device)
+                ex.extract_host(hb.wav, lay, feats_host=feats_host, cmvn=acc, status=status, noise_dev=nd,
+                                n_chunks=max(1, min(6, lay.n_seg // 256)))
+                frame_off = lay.utt_frame_off
+            else:
+                if rir is not None and reverberator is None:
+                    reverberator = Reverberator(rir, device=ex.device)
+                off = np.concatenate([[0], np.cumsum(hb.lengths)])
+                wavs = [hb.wav[int(off[u]):int(off[u + 1])] for u in range(n_utt)]
+                outs, status = ex(wavs, jitter=jitter, noise=nspec, return_status=True, reverb=reverberator, cmvn=acc)
+                frame_off = np.concatenate([[0], np.cumsum([o.shape[0] for o in outs])])  # reverberation may drop a sample
+                feats_host = pipe.feats_buffer(hb, int(frame_off[-1]), J)
+                feats_host.copy_(torch.cat(outs), non_blocking=True)  # one device-to-host copy per batch
+            st_host.copy_(status, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(torch.cuda.current_stream(ex.device))
+            pipe.submit(hb, done, feats_host, frame_off, st_host)
+    all_lens, bad, kept = pipe.lens, pipe.bad, pipe.kept
     if args.write_utt2num_frames:
-        write_lens(args.outfile, all_lens)
+        write_lens(outbase, {k: all_lens[k] for k, _ in mine if k in all_lens})
+    if world > 1:
+        import torch.distributed as dist
+        cmvn_mod.all_reduce(acc)
+        dist.barrier()
+        if rank == 0:
+            pl.merge_rank_outputs(args.outfile, entries, world, args.write_utt2num_frames)
+    if (world > 1 and rank == 0) or (world == 1 and os.environ.get("FDLP_WRITE_CMVN")):
+        # Kaldi's documented stats layout; parity unpinned -- Kaldi is not on this box
+        write_cmvn_ark(acc.cpu().numpy(), args.outfile + ".cmvn.ark")
+    if bad:
+        # the reference raises numpy.linalg.LinAlgError('Singular principal minor') at the first such utterance; here
+        # the shard is complete on disk (the singular bands are NaN) and the error names the utterances
+        raise np.linalg.LinAlgError("Singular principal minor in utterance(s): %s" % " ".join(bad))
     if return_feats:
-        return all_feats
+        return kept
 
 
 def get_parser():

@@ -147,6 +147,76 @@ def ola_pointers(nseg: int, Fr: int, kk: int, kkb2: int, kks: int, rng) -> List[
     return ptrs
 
 
+def ola_pointers_batch(nsegs: np.ndarray, frs: np.ndarray, kk: int, kkb2: int, kks: int, rngs) -> np.ndarray:
+    """`ola_pointers` for a whole batch at once (utterance-major): the same draws in the same order -- one
+    `randrange(2)` per segment i >= 1 of every utterance, the last included (computeFDLPSpectrogram.py:225) -- the
+    same pointer trace and the same ValueError where the reference's slice assignment would raise; the arithmetic
+    around the draws is numpy instead of a Python loop per segment (1000 utterances: 0.1 s -> 5 ms)."""
+    nsegs = np.asarray(nsegs, dtype=np.int64)
+    frs = np.asarray(frs, dtype=np.int64)
+    total = int(nsegs.sum())
+    if total == 0:
+        return np.zeros(0, dtype=np.int32)
+    has = nsegs > 0
+    if (kk - kkb2) != kkb2 and np.any(has & (frs >= kkb2)):
+        raise ValueError("operands could not be broadcast together with shapes (%d,) (%d,) "
+                         "(odd fduration*frate is not supported by the reference either)" % (kkb2, kk - kkb2))
+    seg_off = np.concatenate([[0], np.cumsum(nsegs)])
+    first = seg_off[:-1][has]
+    is_first = np.zeros(total, dtype=bool)
+    is_first[first] = True
+    ndraw = np.maximum(nsegs - 1, 0)
+    if all(r is rngs[0] for r in rngs):  # one generator consumed sequentially over the utterances
+        rr = rngs[0].randrange
+        bits = np.fromiter((rr(2) for _ in range(int(ndraw.sum()))), dtype=np.int64, count=int(ndraw.sum()))
+    else:
+        bits = np.fromiter((r.randrange(2) for r, n in zip(rngs, ndraw) for _ in range(int(n))), dtype=np.int64,
+                           count=int(ndraw.sum()))
+    inc = np.full(total, kks, dtype=np.int64)   # added after segment i: kks + randrange(2) for i >= 1 ...
+    inc[~is_first] += bits
+    inc[is_first] = kks - kkb2                   # ... and kks - kkb2 after segment 0
+    excl = np.cumsum(inc) - inc
+    ptr = excl - np.repeat(excl[first], nsegs[has])
+    i = np.arange(total) - np.repeat(seg_off[:-1][has], nsegs[has])
+    nseg_r, fr_r = np.repeat(nsegs[has], nsegs[has]), np.repeat(frs[has], nsegs[has])
+    late = (i > 0) & (i >= nseg_r - 2)
+    n_left = fr_r - ptr
+    bad = (late & (n_left < 0) & (kk + n_left > 1)) | ((i > 0) & ~late & (ptr + kk > fr_r))
+    if bad.any():
+        b = int(np.argmax(bad))
+        if late[b]:
+            raise ValueError("operands could not be broadcast together with shapes (0,) (%d,): "
+                             "overlap-add pointer ran past the utterance (reference raises too)" % (kk + n_left[b]))
+        raise ValueError("operands could not be broadcast together with shapes (%d,) (%d,): "
+                         "overlap-add pointer ran past the utterance (reference raises too)"
+                         % (max(0, int(n_left[b])), kk))
+    return ptr.astype(np.int32)
+
+
+def batch_layout(lengths, geom, frate: int, srate: int, jitter=None) -> "BatchLayout":
+    """Index tables of one packed batch from the utterance lengths: segment / frame counts (features.py:134-154,
+    computeFDLPSpectrogram.py:182) and the overlap-add pointer trace with its jitter (:207-225).  `geom` needs N, S, kk,
+    kkb2, kks.  Pure host arithmetic (no device access): the CLI pipeline runs it while the GPU works on the previous batch."""
+    lengths = np.asarray(lengths, dtype=np.int64)
+    n_utt = len(lengths)
+    if n_utt and lengths.min() < 2:
+        raise ValueError("utterances need at least 2 samples")
+    rngs = _as_rngs(jitter, n_utt)
+    lim = lengths - 1 if geom["N"] % 2 == 0 else lengths
+    nsegs = np.maximum(0, -(-lim // geom["S"])).astype(np.int64)
+    frs = np.ceil(lengths * frate / srate).astype(np.int64)
+    seg_ptr = ola_pointers_batch(nsegs, frs, geom["kk"], geom["kkb2"], geom["kks"], rngs)
+    return BatchLayout(
+        lengths=lengths,
+        utt_wav_off=np.concatenate([[0], np.cumsum(lengths)]).astype(np.int64),
+        utt_seg_off=np.concatenate([[0], np.cumsum(nsegs)]).astype(np.int32),
+        utt_frame_off=np.concatenate([[0], np.cumsum(frs)]).astype(np.int64),
+        seg_utt=np.repeat(np.arange(n_utt, dtype=np.int32), nsegs).astype(np.int32),
+        seg_ptr=seg_ptr,
+        n_utt=n_utt, n_seg=int(nsegs.sum()), n_frames=int(frs.sum()),
+        max_utt_frames=int(frs.max()) if n_utt else 0)
+
+
 # --------------------------------------------------------------------------- batch bookkeeping
 @dataclass
 class BatchLayout:
@@ -284,6 +354,9 @@ class FdlpExtractor:
         self.geom = {n: getattr(g, n) for n, _ in L.FdlpGeometry._fields_}
 
     def close(self):
+        if getattr(self, "_pack_pool", None) is not None:
+            self._pack_pool.shutdown(wait=False)
+            self._pack_pool = None
         if getattr(self, "_plan", None) and self._plan.value:
             with torch.cuda.device(self.device):
                 self._lib.fdlp_plan_destroy(self._plan)
@@ -341,27 +414,7 @@ class FdlpExtractor:
 
     # ---- bookkeeping
     def layout(self, lengths: Sequence[int], jitter=None) -> BatchLayout:
-        g = self.geom
-        lengths = np.asarray(lengths, dtype=np.int64)
-        n_utt = len(lengths)
-        if n_utt and lengths.min() < 2:
-            raise ValueError("utterances need at least 2 samples")
-        rngs = _as_rngs(jitter, n_utt)
-        nsegs = np.array([segment_count(int(T), g["N"], g["S"]) for T in lengths], dtype=np.int64)
-        frs = np.array([frame_count(int(T), self.cfg.frate, self.cfg.srate) for T in lengths], dtype=np.int64)
-        seg_ptr = []
-        for u in range(n_utt):
-            seg_ptr.extend(ola_pointers(int(nsegs[u]), int(frs[u]), g["kk"], g["kkb2"], g["kks"], rngs[u]))
-        lay = BatchLayout(
-            lengths=lengths,
-            utt_wav_off=np.concatenate([[0], np.cumsum(lengths)]).astype(np.int64),
-            utt_seg_off=np.concatenate([[0], np.cumsum(nsegs)]).astype(np.int32),
-            utt_frame_off=np.concatenate([[0], np.cumsum(frs)]).astype(np.int64),
-            seg_utt=np.repeat(np.arange(n_utt, dtype=np.int32), nsegs).astype(np.int32),
-            seg_ptr=np.asarray(seg_ptr, dtype=np.int32),
-            n_utt=n_utt, n_seg=int(nsegs.sum()), n_frames=int(frs.sum()),
-            max_utt_frames=int(frs.max()) if n_utt else 0)
-        return lay
+        return batch_layout(lengths, self.geom, self.cfg.frate, self.cfg.srate, jitter)
 
     @staticmethod
     def pack(wavs: Sequence[Union[np.ndarray, torch.Tensor]]):
@@ -467,13 +520,15 @@ class FdlpExtractor:
     def extract_host(self, host_wav: torch.Tensor, lay: BatchLayout, feats_host: Optional[torch.Tensor] = None,
                      n_chunks: int = 6, cmvn: Optional[torch.Tensor] = None, status: Optional[torch.Tensor] = None,
                      wav_dev: Optional[torch.Tensor] = None, feats: Optional[torch.Tensor] = None,
-                     taper: bool = True):
+                     taper: bool = True, noise_dev=None, fill=None):
         """End-to-end call for a packed batch that lives in (pinned) HOST memory: samples go host -> device,
         features device -> host, and both copies overlap the kernels.  The batch is cut into `n_chunks` runs of
         whole utterances; chunk c+1 is uploaded on a copy stream while chunk c computes on the current stream
         and the features of chunk c-1 are downloaded on a third stream.  Results are identical to one
-        forward_packed over the whole batch (utterances are independent).  Returns (feats_dev, feats_host, status);
-        the current stream waits for the last download."""
+        forward_packed over the whole batch (utterances are independent).  `fill(u0, u1, w0, w1)`, if given, is called
+        right before chunk [u0, u1) is uploaded and must have put its samples into host_wav[w0:w1] when it returns
+        (extract_list packs a list of arrays this way, chunk by chunk, while the device is busy).
+        Returns (feats_dev, feats_host, status); the current stream waits for the last download."""
         dev = self.device
         J = self.cfg.nfilters
         if wav_dev is None:
@@ -492,10 +547,12 @@ class FdlpExtractor:
         ev0.record(cur)
         self._s_in.wait_event(ev0)
         self._s_out.wait_event(ev0)
-        ev_in = []
-        with torch.cuda.stream(self._s_in):
-            for u0, u1, sub in chunks:
-                w0, w1 = int(lay.utt_wav_off[u0]), int(lay.utt_wav_off[u1])
+        for u0, u1, sub in chunks:
+            w0, w1 = int(lay.utt_wav_off[u0]), int(lay.utt_wav_off[u1])
+            f0, f1 = int(lay.utt_frame_off[u0]), int(lay.utt_frame_off[u1])
+            if fill is not None:
+                fill(u0, u1, w0, w1)  # the host packs this chunk while the device works on the previous ones
+            with torch.cuda.stream(self._s_in):
                 wav_dev[w0:w1].copy_(host_wav[w0:w1], non_blocking=True)
                 # the framing kernel uses 16-byte loads when the batch base pointer is 16-byte aligned:
                 # hand it the slice from the aligned sample below w0 and shift the offsets instead
@@ -503,21 +560,60 @@ class FdlpExtractor:
                 sub.to(dev)
                 e = torch.cuda.Event()
                 e.record(self._s_in)
-                ev_in.append(e)
-        for (u0, u1, sub), e in zip(chunks, ev_in):
-            w0, w1 = int(lay.utt_wav_off[u0]), int(lay.utt_wav_off[u1])
-            f0, f1 = int(lay.utt_frame_off[u0]), int(lay.utt_frame_off[u1])
             cur.wait_event(e)
-            self.forward_packed(wav_dev[w0 - (w0 % 8):w1], sub, feats=feats[f0:f1], cmvn=cmvn, status=status[u0:u1])
+            nd = None
+            if noise_dev is not None:  # per-utterance noise tables of this chunk (the recording itself is shared)
+                nd = dict(noise_dev, off=noise_dev["off"][u0:u1], snr=noise_dev["snr"][u0:u1])
+            self.forward_packed(wav_dev[w0 - (w0 % 8):w1], sub, feats=feats[f0:f1], cmvn=cmvn, status=status[u0:u1],
+                                noise_dev=nd)
             done = torch.cuda.Event()
             done.record(cur)
             self._s_out.wait_event(done)
             with torch.cuda.stream(self._s_out):
                 feats_host[f0:f1].copy_(feats[f0:f1], non_blocking=True)
+        self._last_upload = e if chunks else None
         fin = torch.cuda.Event()
         fin.record(self._s_out)
         cur.wait_event(fin)
         return feats, feats_host, status
+
+    def extract_list(self, wavs: Sequence[np.ndarray], jitter=None, feats_host: Optional[torch.Tensor] = None,
+                     cmvn: Optional[torch.Tensor] = None, status: Optional[torch.Tensor] = None, n_chunks: int = 6,
+                     wav_dev: Optional[torch.Tensor] = None, feats: Optional[torch.Tensor] = None, threads: int = 8):
+        """The whole host side of one batch: a list of (unpinned) int16 / float32 numpy waveforms in, pinned-host
+        features out.  Layout (segment / frame tables, jitter draws) first -- it needs the lengths only -- then the
+        utterances are packed into a grow-only pinned staging buffer chunk by chunk, by `threads` workers (numpy
+        copies release the GIL), each chunk right before its upload, so packing overlaps the device work of the
+        chunks before it.  Returns (lay, feats_dev, feats_host, status)."""
+        from concurrent.futures import ThreadPoolExecutor
+        wavs = [np.ascontiguousarray(w) for w in wavs]
+        dt = wavs[0].dtype
+        if dt not in (np.int16, np.float32) or any(w.dtype != dt or w.ndim != 1 for w in wavs):
+            raise TypeError("waveforms must be mono and all int16 or all float32 (what scipy.io.wavfile.read returns)")
+        lay = batch_layout([len(w) for w in wavs], self.geom, self.cfg.frate, self.cfg.srate, jitter)
+        total = int(lay.utt_wav_off[-1])
+        if getattr(self, "_last_upload", None) is not None:
+            self._last_upload.synchronize()  # the previous call's uploads have left the staging buffer
+        tdt = torch.int16 if dt == np.int16 else torch.float32
+        st = getattr(self, "_staging", None)
+        if st is None or st.dtype != tdt or st.numel() < total:
+            self._staging = st = torch.empty(int(total * 1.1) + 1024, dtype=tdt, pin_memory=True)
+        if getattr(self, "_pack_pool", None) is None:
+            self._pack_pool = ThreadPoolExecutor(max_workers=max(1, threads))
+        flat = st.numpy()
+        off = lay.utt_wav_off
+
+        def put(lo, hi):
+            for u in range(lo, hi):
+                flat[off[u]:off[u + 1]] = wavs[u]
+
+        def fill(u0, u1, w0, w1):
+            step = max(4, (u1 - u0 + threads - 1) // threads)
+            list(self._pack_pool.map(lambda lo: put(lo, min(lo + step, u1)), range(u0, u1, step)))
+
+        f, fh, s_ = self.extract_host(st[:total], lay, feats_host=feats_host, n_chunks=n_chunks, cmvn=cmvn, status=status,
+                                      wav_dev=wav_dev, feats=feats, fill=fill)
+        return lay, f, fh, s_
 
     def reverberate(self, wav_dev: torch.Tensor, lay: BatchLayout, reverb, noise_dev=None):
         """--add_reverb (computeFDLPSpectrogram.py:168-170): noise mixing (if any) then addReverb, on the device.

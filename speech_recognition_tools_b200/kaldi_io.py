@@ -33,6 +33,69 @@ def write_ark_scp(feats: Iterable[Tuple[str, np.ndarray]], ark_path: str, scp_pa
             scp.write("%s %s:%d\n" % (key, ark_path, off))
 
 
+class ArkWriter:
+    """Incremental ark/scp writer: one `write_batch` per extracted batch, so memory stays bounded and the output
+    written so far survives a later failure (the reference builds the whole dict and writes at the end,
+    computeFDLPSpectrogram.py:228-230).  A batch is a float32 [n_frames, dim] matrix holding the utterances back to
+    back; headers and matrices go out through os.pwritev at precomputed offsets, from `threads` workers when a pool
+    is given (the syscalls release the GIL: tmpfs / page-cache copies run in parallel)."""
+
+    def __init__(self, ark_path: str, scp_path: str, pool=None, threads: int = 4, scp_ark_name: str = None):
+        import os
+        self.ark_path, self.scp_name = ark_path, scp_ark_name or ark_path
+        self._fd = os.open(ark_path, os.O_WRONLY | os.O_CREAT | os.O_TRUNC, 0o644)
+        self._scp = open(scp_path, "w")
+        self._pos = 0
+        self._pool, self._threads = pool, max(1, threads)
+
+    def write_batch(self, keys, mat: np.ndarray, frame_off) -> None:
+        import os
+        if mat.dtype != np.float32 or mat.ndim != 2 or not mat.flags.c_contiguous:
+            raise ValueError("batch matrix must be C-contiguous float32 [n_frames, dim]")
+        dim = mat.shape[1]
+        flat = memoryview(mat.reshape(-1)).cast("B")
+        bufs, lines, pos = [], [], self._pos
+        cols = b"\4" + struct.pack("<i", dim)
+        for u, key in enumerate(keys):
+            f0, f1 = int(frame_off[u]), int(frame_off[u + 1])
+            kb = key.encode("utf-8") + b" "
+            hdr = kb + b"\0BFM \4" + struct.pack("<i", f1 - f0) + cols
+            lines.append("%s %s:%d\n" % (key, self.scp_name, pos + len(kb)))
+            bufs.append((pos, hdr, flat[f0 * dim * 4:f1 * dim * 4]))
+            pos += len(hdr) + (f1 - f0) * dim * 4
+
+        def put(group):
+            for off, hdr, body in group:
+                iov, done, want = [hdr, body], 0, len(hdr) + len(body)
+                while done < want:  # pwritev may write less than asked (2 GB limit, signals)
+                    n = os.pwritev(self._fd, iov, off + done)
+                    done += n
+                    if done < want:
+                        joined = bytes(hdr) + bytes(body) if done < len(hdr) else None
+                        iov = [memoryview(joined)[done:]] if joined is not None else [body[done - len(hdr):]]
+
+        if self._pool is not None and len(bufs) >= 2 * self._threads:
+            k = (len(bufs) + self._threads - 1) // self._threads
+            list(self._pool.map(put, [bufs[i:i + k] for i in range(0, len(bufs), k)]))
+        else:
+            put(bufs)
+        self._pos = pos
+        self._scp.write("".join(lines))
+
+    def close(self) -> None:
+        import os
+        if self._fd is not None:
+            os.close(self._fd)
+            self._fd = None
+            self._scp.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
 def read_ark(ark_path: str) -> Dict[str, np.ndarray]:
     out = {}
     with open(ark_path, "rb") as f:

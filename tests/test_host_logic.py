@@ -10,7 +10,7 @@ import pytest
 
 from oracle import fdlp as ofdlp
 from speech_recognition_tools_b200 import _lib, synth
-from speech_recognition_tools_b200.fdlp import (FdlpConfig, build_weights, frame_count, ola_pointers,
+from speech_recognition_tools_b200.fdlp import (FdlpConfig, batch_layout, build_weights, frame_count, ola_pointers,
                                                 parse_fbank_type, segment_count)
 from speech_recognition_tools_b200.mel import mel_frame_count
 
@@ -216,3 +216,49 @@ def test_reverb_block_layout_covers_the_full_convolution():
     assert load_rir(None) is None and load_rir("clean") is None
     with pytest.raises(ValueError):  # computeFDLPSpectrogram.py:90-91
         load_rir("cathedral")
+
+
+@pytest.mark.parametrize("fdur", [0.5, 1.5])
+def test_vectorised_batch_layout_equals_the_per_segment_loop(fdur):
+    """batch_layout / ola_pointers_batch draw the jitter in the reference's order (computeFDLPSpectrogram.py:225) and
+    give the trace, counts and errors of the scalar restatement, for one generator over the batch and for
+    per-utterance seeds."""
+    g = ofdlp.derived_sizes(fdur, 100, 0.25)
+    rng = np.random.default_rng(5)
+    hi = 150000 if fdur == 0.5 else 560000  # default parameters can overflow beyond ~10 s (SURVEY.md fact 5)
+    lengths = [2, 3, 100, g["S"], g["S"] + 1, g["S"] + 2, 2 * g["S"] + 1] + [int(t) for t in rng.integers(2, hi, 200)]
+
+    def scalar(rngs):
+        out = []
+        for T, r in zip(lengths, rngs):
+            out += ola_pointers(segment_count(T, g["N"], g["S"]), frame_count(T, 100, 16000), g["kk"], g["kkb2"],
+                                g["kks"], r)
+        return out
+
+    one = random.Random(11)
+    lay = batch_layout(lengths, g, 100, 16000, jitter=random.Random(11))
+    assert list(lay.seg_ptr) == scalar([one] * len(lengths))
+    assert lay.n_seg == sum(segment_count(T, g["N"], g["S"]) for T in lengths)
+    assert list(np.diff(lay.utt_frame_off)) == [frame_count(T, 100, 16000) for T in lengths]
+    seeds = list(range(100, 100 + len(lengths)))
+    lay2 = batch_layout(lengths, g, 100, 16000, jitter=seeds)
+    assert list(lay2.seg_ptr) == scalar([random.Random(s) for s in seeds])
+    # the generator is left in the same state as after the loop
+    a, b = random.Random(3), random.Random(3)
+    batch_layout(lengths, g, 100, 16000, jitter=a)
+    scalar([b] * len(lengths))
+    assert a.random() == b.random()
+    if fdur == 0.5:  # both raise, or neither, on lengths where the reference's pointer drifts past the utterance
+        for T in range(150000, 330000, 3331):
+            for seed in (0, 1):
+                try:
+                    ola_pointers(segment_count(T, g["N"], g["S"]), frame_count(T, 100, 16000), g["kk"], g["kkb2"], g["kks"],
+                                 random.Random(seed))
+                    raised = False
+                except ValueError:
+                    raised = True
+                if raised:
+                    with pytest.raises(ValueError, match="overlap-add pointer ran past"):
+                        batch_layout([T], g, 100, 16000, jitter=[seed])
+                else:
+                    batch_layout([T], g, 100, 16000, jitter=[seed])
