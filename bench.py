@@ -356,7 +356,7 @@ def multi_gpu_check(ex, wavs, lay, feats, cmvn_reduced, dev, world, rank):
     else:
         samples = torch.zeros(sum(lens_p), dtype=torch.int16, device=dev)
     if world > 1:
-        dist.broadcast(samples, 0)
+        dist.broadcast(samples.view(torch.uint8), 0)  # NCCL has no int16: the same bytes
     play = ex.layout(lens_p, jitter=12345).to(dev)
     pf, _ = ex.forward_packed(samples, play)
     digest = hashlib.sha1(pf.cpu().numpy().tobytes()).digest()
@@ -402,12 +402,18 @@ def cli_e2e(wavs, audio_s, dev_index):
                 "--overlap_fraction=0.25", "--nfilters=%d" % WSJ["nfilters"], "--fduration=1.5", "--frate=100"]
         args = cf.get_parser().parse_args(argv)
         walls = []
-        for _ in range(3):
-            sink = io.StringIO()
-            t0 = time.perf_counter()
-            with contextlib.redirect_stdout(sink):
-                cf.getFeats(args)
-            walls.append(time.perf_counter() - t0)
+        # under torchrun this process carries RANK / WORLD_SIZE: the shim would take them for its own sharded mode (and wait
+        # for the other ranks in its barrier).  Here it runs as the single-process command the wrapper launches per shard.
+        saved = {k: os.environ.pop(k) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK") if k in os.environ}
+        try:
+            for _ in range(3):
+                sink = io.StringIO()
+                t0 = time.perf_counter()
+                with contextlib.redirect_stdout(sink):
+                    cf.getFeats(args)
+                walls.append(time.perf_counter() - t0)
+        finally:
+            os.environ.update(saved)
         ark_bytes = os.path.getsize(os.path.join(d, "out.ark"))
         best = min(walls[1:])
         return {"value": audio_s / best, "unit": UNIT, "wall_s": best, "first_run_wall_s": walls[0],

@@ -22,7 +22,7 @@ from speech_recognition_tools_b200.cli.common import load_noise, write_lens  # n
 from speech_recognition_tools_b200.fdlp import FdlpConfig, FdlpExtractor, NoiseSpec, segment_count  # noqa: E402
 from speech_recognition_tools_b200.reverb import Reverberator, load_rir  # noqa: E402
 
-MAX_SEGMENTS_PER_BATCH = int(os.environ.get("FDLP_CLI_MAX_SEGMENTS", "8192"))
+MAX_SEGMENTS_PER_BATCH = int(os.environ.get("FDLP_CLI_MAX_SEGMENTS", "2048"))  # several batches per shard: the three pipeline stages overlap
 
 
 _PLANS = {}
@@ -30,6 +30,8 @@ _PLANS = {}
 
 class _GlobalRandom:
     """`random.randrange(2)` of computeFDLPSpectrogram.py:225 on the module-level generator."""
+
+    mt_instance = random._inst  # the generator behind random.randrange / random.seed (bulk jitter draws, fdlp.py)
 
     @staticmethod
     def randrange(n):
@@ -107,7 +109,7 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
             elif noise is not None:
                 draws = [np.random.rand() for _ in range(n_utt)]  # features.py:25, one draw per utterance in scp order
                 nspec = NoiseSpec(samples=noise[0], snr_db=noise[1], rand=draws, mode="int16_wrap")
-            st_host = torch.empty(n_utt, dtype=torch.int32, pin_memory=True)
+            st_host = pipe.status_buffer(hb, n_utt)
             if overlapped:
                 lay = batch_layout(hb.lengths, g, cfg.frate, cfg.srate, jitter)
                 nd = ex._noise_to_device(nspec, lay) if nspec is not None else None
@@ -130,6 +132,8 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
             done.record(torch.cuda.current_stream(ex.device))
             pipe.submit(hb, done, feats_host, frame_off, st_host)
     all_lens, bad, kept = pipe.lens, pipe.bad, pipe.kept
+    if os.environ.get("FDLP_CLI_TRACE"):
+        print("%s: stage seconds %s" % (sys.argv[0], {k: round(v, 4) for k, v in pipe.timings().items()}), file=sys.stderr)
     if args.write_utt2num_frames:
         write_lens(outbase, {k: all_lens[k] for k, _ in mine if k in all_lens})
     if world > 1:

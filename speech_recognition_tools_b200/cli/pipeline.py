@@ -131,6 +131,11 @@ class _Buffers:
             self.wav[tdt] = cur
         return cur[:n]
 
+    def get_status(self, n):
+        if getattr(self, "status", None) is None or self.status.numel() < n:
+            self.status = torch.empty(max(n, 4096), dtype=torch.int32, pin_memory=torch.cuda.is_available())
+        return self.status[:n]
+
     def get_feats(self, n_frames, dim):
         n = n_frames * dim
         if self.feats is None or self.feats.numel() < n:
@@ -163,6 +168,7 @@ class BatchReader(threading.Thread):
         self.prog = prog or sys.argv[0]
         self.announce = announce
         self.stop = threading.Event()
+        self.t_probe = self.t_read = self.t_wait = 0.0  # seconds in header probes / sample reads / waiting for a buffer set
 
     def _open(self, uttid, spec):
         info = None
@@ -186,7 +192,11 @@ class BatchReader(threading.Thread):
         return _Item(uttid, int(signal.shape[0]), np.dtype(signal.dtype).newbyteorder("<"), array=signal)
 
     def _emit(self, items):
+        import time
+        t0 = time.perf_counter()
         bs = self.free_q.get()
+        t1 = time.perf_counter()
+        self.t_wait += t1 - t0
         total = sum(it.n for it in items)
         wav = self.bufsets[bs].get_wav(total, items[0].dtype)
         flat = wav.numpy()
@@ -214,6 +224,7 @@ class BatchReader(threading.Thread):
 
         step = max(8, (len(items) + 4 * N_IO_THREADS - 1) // (4 * N_IO_THREADS))
         list(self.pool.map(lambda lo: fill(lo, min(lo + step, len(items))), range(0, len(items), step)))
+        self.t_read += time.perf_counter() - t1
         if self.announce:  # computeFDLPSpectrogram.py:126, one line per utterance
             sys.stdout.write("".join("%s: Computing Features for file: %s\n" % (self.prog, it.uttid) for it in items))
             sys.stdout.flush()
@@ -221,12 +232,15 @@ class BatchReader(threading.Thread):
                                  wav=wav, bufset=bs))
 
     def run(self):
+        import time
         try:
             pend, nseg, dtype = [], 0, None
             for uttid, spec in self.entries:
                 if self.stop.is_set():
                     return
+                tp = time.perf_counter()
                 it = self._open(uttid, spec)
+                self.t_probe += time.perf_counter() - tp
                 if it is None:
                     continue
                 if it.n < 2:
@@ -255,6 +269,7 @@ class BatchWriter(threading.Thread):
         self.in_q = queue.Queue()
         self.lens, self.bad, self.error = {}, [], None
         self.kept = {} if keep else None  # uttid -> matrix copy (return_feats of the in-module entry points)
+        self.t_sync = self.t_write = 0.0
 
     def run(self):
         while True:
@@ -264,10 +279,15 @@ class BatchWriter(threading.Thread):
             event, ids, feats, frame_off, status, bs = job
             try:
                 if self.error is None:
+                    import time
+                    t0 = time.perf_counter()
                     if event is not None:
                         event.synchronize()
+                    t1 = time.perf_counter()
                     mat = feats.numpy() if isinstance(feats, torch.Tensor) else feats
                     self.w.write_batch(ids, mat, frame_off)
+                    self.t_sync += t1 - t0
+                    self.t_write += time.perf_counter() - t1
                     if self.kept is not None:
                         for u, k in enumerate(ids):
                             self.kept[k] = mat[int(frame_off[u]):int(frame_off[u + 1])].copy()
@@ -290,6 +310,17 @@ class BatchWriter(threading.Thread):
             raise self.error
 
 
+_BUFSETS: List[_Buffers] = []
+_POOL = None
+
+
+def _shared_pool():
+    global _POOL
+    if _POOL is None:
+        _POOL = ThreadPoolExecutor(max_workers=N_IO_THREADS)
+    return _POOL
+
+
 class HostPipeline:
     """Reader + writer around a main-thread loop:
 
@@ -303,15 +334,17 @@ class HostPipeline:
     def __init__(self, entries, scp_type, srate, seg_count_fn, max_segments, ark_path, scp_path, n_bufsets=3,
                  prog=None, scp_ark_name=None, announce=True, singular_bit=1, keep=False):
         from ..kaldi_io import ArkWriter
-        self.pool = ThreadPoolExecutor(max_workers=N_IO_THREADS)
-        self.bufsets = [_Buffers() for _ in range(n_bufsets)]
+        self.pool = _shared_pool()
+        while len(_BUFSETS) < n_bufsets:  # pinned staging memory is kept for the life of the process: pinning
+            _BUFSETS.append(_Buffers())    # 100 MB costs ~20 ms, as much as extracting the batch it holds
+        self.bufsets = _BUFSETS[:n_bufsets]
         self.free_q = queue.Queue()
         for i in range(n_bufsets):
             self.free_q.put(i)
         self.q = queue.Queue()
         self.reader = BatchReader(entries, scp_type, srate, seg_count_fn, max_segments, self.bufsets, self.free_q, self.q,
                                   self.pool, prog, announce)
-        self.writer = BatchWriter(ArkWriter(ark_path, scp_path, pool=self.pool, threads=min(8, N_IO_THREADS),
+        self.writer = BatchWriter(ArkWriter(ark_path, scp_path, pool=self.pool, threads=N_IO_THREADS,
                                             scp_ark_name=scp_ark_name), self.free_q, singular_bit, keep)
 
     def __enter__(self):
@@ -331,6 +364,9 @@ class HostPipeline:
     def feats_buffer(self, hb, n_frames, dim):
         return self.bufsets[hb.bufset].get_feats(n_frames, dim)
 
+    def status_buffer(self, hb, n_utt):
+        return self.bufsets[hb.bufset].get_status(n_utt)
+
     def submit(self, hb, event, feats_host, frame_off, status_host):
         self.writer.in_q.put((event, hb.ids, feats_host, np.asarray(frame_off), status_host, hb.bufset))
 
@@ -346,7 +382,7 @@ class HostPipeline:
                 self.writer.join(timeout=10)
                 self.writer.w.close()
         finally:
-            self.pool.shutdown(wait=False)
+            pass  # the I/O pool and the pinned buffers are shared by later calls in this process
         return False
 
     @property
@@ -356,6 +392,12 @@ class HostPipeline:
     @property
     def kept(self):
         return self.writer.kept
+
+    def timings(self):
+        """Seconds per stage (they overlap): header probes, sample reads, reader waiting for a buffer set, writer
+        waiting for the device, ark writes."""
+        r, w = self.reader, self.writer
+        return dict(probe=r.t_probe, read=r.t_read, reader_wait=r.t_wait, writer_sync=w.t_sync, write=w.t_write)
 
     @property
     def bad(self):

@@ -147,6 +147,49 @@ def ola_pointers(nseg: int, Fr: int, kk: int, kkb2: int, kks: int, rng) -> List[
     return ptrs
 
 
+def _randrange2_bulk(rng, n: int) -> np.ndarray:
+    """`[rng.randrange(2) for _ in range(n)]` for a Mersenne-Twister `random.Random`, from two bulk `getrandbits`
+    calls instead of n Python calls, leaving the generator in exactly the state the loop leaves it in.
+    CPython: randrange(2) -> _randbelow(2) -> k = (2).bit_length() = 2; r = getrandbits(2) until r < 2, and
+    getrandbits(k <= 32) is the top k bits of one 32-bit output; getrandbits(32 m) is m outputs, least significant
+    word first.  Checked against the loop once per process on a copy of the generator (other interpreters / subclasses:
+    the loop itself)."""
+    if n <= 0:
+        return np.zeros(0, dtype=np.int64)
+    inst = getattr(rng, "mt_instance", rng)  # a wrapper around the module-level generator exposes it
+    if type(inst) is not _random.Random or not _bulk_ok():
+        rr = rng.randrange
+        return np.fromiter((rr(2) for _ in range(n)), dtype=np.int64, count=n)
+    state = inst.getstate()
+    words = 2 * n + 64
+    while True:
+        raw = inst.getrandbits(32 * words).to_bytes(4 * words, "little")
+        top = np.frombuffer(raw, dtype="<u4") >> 30
+        acc = np.flatnonzero(top < 2)
+        if acc.size >= n:
+            break
+        inst.setstate(state)
+        words *= 2
+    used = int(acc[n - 1]) + 1       # outputs the loop would have consumed
+    inst.setstate(state)
+    inst.getrandbits(32 * used)      # advance by exactly that many
+    return top[acc[:n]].astype(np.int64)
+
+
+_BULK_OK = None
+
+
+def _bulk_ok() -> bool:
+    global _BULK_OK
+    if _BULK_OK is None:
+        _BULK_OK = True  # (set first: the check below goes through _randrange2_bulk itself)
+        a, b = _random.Random(987654321), _random.Random(987654321)
+        fast = _randrange2_bulk(a, 257)
+        slow = [b.randrange(2) for _ in range(257)]
+        _BULK_OK = list(fast) == slow and a.getstate() == b.getstate()
+    return _BULK_OK
+
+
 def ola_pointers_batch(nsegs: np.ndarray, frs: np.ndarray, kk: int, kkb2: int, kks: int, rngs) -> np.ndarray:
     """`ola_pointers` for a whole batch at once (utterance-major): the same draws in the same order -- one
     `randrange(2)` per segment i >= 1 of every utterance, the last included (computeFDLPSpectrogram.py:225) -- the
@@ -167,11 +210,9 @@ def ola_pointers_batch(nsegs: np.ndarray, frs: np.ndarray, kk: int, kkb2: int, k
     is_first[first] = True
     ndraw = np.maximum(nsegs - 1, 0)
     if all(r is rngs[0] for r in rngs):  # one generator consumed sequentially over the utterances
-        rr = rngs[0].randrange
-        bits = np.fromiter((rr(2) for _ in range(int(ndraw.sum()))), dtype=np.int64, count=int(ndraw.sum()))
+        bits = _randrange2_bulk(rngs[0], int(ndraw.sum()))
     else:
-        bits = np.fromiter((r.randrange(2) for r, n in zip(rngs, ndraw) for _ in range(int(n))), dtype=np.int64,
-                           count=int(ndraw.sum()))
+        bits = np.concatenate([_randrange2_bulk(r, int(n)) for r, n in zip(rngs, ndraw)] + [np.zeros(0, dtype=np.int64)])
     inc = np.full(total, kks, dtype=np.int64)   # added after segment i: kks + randrange(2) for i >= 1 ...
     inc[~is_first] += bits
     inc[is_first] = kks - kkb2                   # ... and kks - kkb2 after segment 0
@@ -607,12 +648,35 @@ class FdlpExtractor:
             for u in range(lo, hi):
                 flat[off[u]:off[u + 1]] = wavs[u]
 
+        # the packer runs ahead of the uploads in a thread of its own: chunk after chunk, each spread over the pool;
+        # extract_host's `fill` hook only waits for the chunk it is about to upload
+        import threading
+        chunks = split_layout(lay, n_chunks, True)
+        ready = {u0: threading.Event() for u0, _, _ in chunks}
+        failure = []
+
+        def packer():
+            try:
+                for u0, u1, _ in chunks:
+                    step = max(4, (u1 - u0 + threads - 1) // threads)
+                    list(self._pack_pool.map(lambda lo, u1=u1, step=step: put(lo, min(lo + step, u1)), range(u0, u1, step)))
+                    ready[u0].set()
+            except BaseException as e:  # noqa: BLE001
+                failure.append(e)
+                for ev in ready.values():
+                    ev.set()
+
+        th = threading.Thread(target=packer, daemon=True)
+        th.start()
+
         def fill(u0, u1, w0, w1):
-            step = max(4, (u1 - u0 + threads - 1) // threads)
-            list(self._pack_pool.map(lambda lo: put(lo, min(lo + step, u1)), range(u0, u1, step)))
+            ready[u0].wait()
+            if failure:
+                raise failure[0]
 
         f, fh, s_ = self.extract_host(st[:total], lay, feats_host=feats_host, n_chunks=n_chunks, cmvn=cmvn, status=status,
-                                      wav_dev=wav_dev, feats=feats, fill=fill)
+                                      wav_dev=wav_dev, feats=feats, fill=fill, taper=True)
+        th.join()
         return lay, f, fh, s_
 
     def reverberate(self, wav_dev: torch.Tensor, lay: BatchLayout, reverb, noise_dev=None):

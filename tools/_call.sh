@@ -1,4 +1,2 @@
 cd $GRAFT_REPO_ROOT
-python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -15 > gpurun_out/r2_na_alone.log
-python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/r2_na_all.log
-compute-sanitizer --tool memcheck python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -8 > gpurun_out/r2_na_memcheck.log
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29555 bench.py --gpus 2 --steps 10 --warmup 3 > gpurun_out/r2_bench11_2gpu.json 2> gpurun_out/r2_bench11_2gpu.err
