@@ -238,6 +238,15 @@ int fdlp_diff_filter(const void* wav /*dev, packed*/, int32_t wav_dtype, const i
                      int32_t n_utt, int64_t max_len /*longest utterance, samples*/, float* out /*dev, packed*/,
                      void* stream);
 
+/* ---- --add_noise type,snr as a waveform of its own (add_noise_to_wav, features.py:24-31: alpha from the energies,
+ *      then sig + alpha * noise[off : off + T]); computeMelSpectrum.py:134-141 mixes before framing.  fdlp_forward fuses the
+ *      same mix into its framing load; this entry point serves the paths that take a waveform (mel).  utt_alpha: device
+ *      scratch of n_utt doubles supplied by the caller, left holding the mixing coefficients.  float32 result. ---- */
+int fdlp_noise_mix(const void* wav /*dev, packed*/, int32_t wav_dtype, const int64_t* utt_wav_off /*dev [n_utt+1]*/,
+                   int32_t n_utt, int64_t max_len, const int16_t* noise /*dev*/, const int64_t* utt_noise_off /*dev [n_utt]*/,
+                   const double* utt_snr_db /*dev [n_utt]*/, int32_t noise_mode /*FDLP_NOISE_INT16_WRAP | FDLP_NOISE_FLOAT*/,
+                   double* utt_alpha /*dev [n_utt], out*/, float* out /*dev, packed*/, void* stream);
+
 /* ---- --add_reverb (features.py:110-115 addReverb, called at computeFDLPSpectrogram.py:168-170, computeMelSpectrum.py:143-145,
  *      computeMfccFeatures.py:118-120): out = convolve(sig, rir) (full), xxc = correlate(sig, out, 'valid'),
  *      indM = len(xxc) - argmax(xxc), result = out[indM : indM + len(sig)], per utterance, after the optional noise

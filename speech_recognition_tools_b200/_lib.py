@@ -138,6 +138,8 @@ SYMBOLS = [
     ("cmvn_accumulate_noalloc", C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     ("fdlp_modspec_forward", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     ("fdlp_diff_filter", C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),
+    ("fdlp_noise_mix", C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
+                                 C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("fdlp_reverb_plan_create", C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
     ("fdlp_reverb_plan_destroy", C.c_int, [C.c_void_p]),
     ("fdlp_reverb_plan_get_block", C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),

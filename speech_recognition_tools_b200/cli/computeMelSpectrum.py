@@ -11,7 +11,8 @@ _ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__
 if _ROOT not in sys.path:
     sys.path.insert(0, _ROOT)
 
-from speech_recognition_tools_b200.cli.common import iter_scp, write_lens  # noqa: E402
+from speech_recognition_tools_b200.cli.common import iter_scp, load_noise, write_lens  # noqa: E402
+from speech_recognition_tools_b200.fdlp import NoiseSpec  # noqa: E402
 from speech_recognition_tools_b200.kaldi_io import write_ark_scp  # noqa: E402
 from speech_recognition_tools_b200.reverb import Reverberator, load_rir  # noqa: E402
 from speech_recognition_tools_b200.mel import MelConfig, MelExtractor  # noqa: E402
@@ -43,8 +44,13 @@ def compute_mel_spectrum(args, srate=16000, window=np.hamming, return_feats=Fals
     if args.spectrum_type not in ("log", "power"):
         print("Spectrum type not supported! ")
         sys.exit(1)
+    noise = None  # computeMelSpectrum.py:69-72,134-141
     if args.add_noise and args.add_noise != "clean":
-        raise NotImplementedError("noise mixing is implemented on the FDLP and MFCC paths only")
+        if args.add_noise == "diff":
+            noise = "diff"
+        else:
+            noise_info = args.add_noise.strip().split(",")
+            noise = (load_noise(noise_info[0]), float(noise_info[1]))
     rir = load_rir(args.add_reverb)  # computeMelSpectrum.py:74-90: ./RIR/RIR_<room>_AnglA.wav, channel 1, / 2^15
     ex = MelExtractor(MelConfig.from_args(args))
     reverberator = Reverberator(rir, device=ex.device) if rir is not None else None
@@ -52,7 +58,11 @@ def compute_mel_spectrum(args, srate=16000, window=np.hamming, return_feats=Fals
 
     def flush(batch):
         if batch:
-            outs = ex([b[1] for b in batch], reverb=reverberator)
+            nspec = noise
+            if isinstance(noise, tuple):
+                draws = [np.random.rand() for _ in batch]  # features.py:25, one draw per utterance in scp order
+                nspec = NoiseSpec(samples=noise[0], snr_db=noise[1], rand=draws, mode="int16_wrap")
+            outs = ex([b[1] for b in batch], reverb=reverberator, noise=nspec)
             for (k, _), o in zip(batch, outs):
                 all_feats[k] = o.cpu().numpy()
                 all_lens[k] = int(o.shape[0])

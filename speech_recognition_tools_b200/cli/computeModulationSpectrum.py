@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Drop-in for /root/reference/src/featgen/computeModulationSpectrum.py (same flags :206-224, same outputs),
 computed by libfdlp_b200.so on the GPU.  `getFeats(args)` keeps the reference's signature.  The complex-modulation
-path (`--complex_modulation`) and reverberation are not implemented and raise."""
+path (`--complex_modulation`: complex LPC on the ifft, used by no recipe or wrapper of the reference) raises."""
 import argparse
 import os
 import sys
@@ -15,6 +15,7 @@ if _ROOT not in sys.path:
 from speech_recognition_tools_b200.cli.common import iter_scp  # noqa: E402
 from speech_recognition_tools_b200.kaldi_io import write_ark_scp  # noqa: E402
 from speech_recognition_tools_b200.modspec import ModSpecConfig, ModSpecExtractor  # noqa: E402
+from speech_recognition_tools_b200.reverb import Reverberator, load_rir  # noqa: E402
 
 MAX_UTTS_PER_BATCH = 64
 
@@ -46,22 +47,26 @@ def get_args(argv=None):
 def getFeats(args, srate=16000, window=np.hanning, return_feats=False):
     if window is not np.hanning:
         raise NotImplementedError("only np.hanning (and --no_window) of the reference are implemented")
-    if args.add_reverb and args.add_reverb != "clean":
-        if args.add_reverb not in ("small_room", "large_room"):
-            raise ValueError("Invalid type of reverberation!")
-        raise NotImplementedError("reverberation needs ./RIR/*.wav, which the reference snapshot does not ship")
+    # computeModulationSpectrum.py:94-105: ./RIR/RIR_{SmallRoom1_near,LargeRoom1_far}_AnglA.wav, channel 1, / 2^15
+    # (this script knows no medium_room); ValueError for any other name
+    if args.add_reverb and args.add_reverb not in ("clean", "small_room", "large_room"):
+        raise ValueError("Invalid type of reverberation!")
+    rir = load_rir(args.add_reverb)
+    if args.add_reverb == "clean":
+        print("%s: No reverberation added!" % sys.argv[0])
     cfg = ModSpecConfig(nfilters=args.nfilters, coeff_0=args.coeff_0, coeff_n=args.coeff_n, keep_even=args.keep_even,
                         order=args.order, fduration=args.fduration, frate=args.frate, fbank_type=args.fbank_type,
                         no_window=args.no_window, complex_modulation=args.complex_modulation,
                         compensate_noise=args.compensate_noise, absolute_value=args.absolute_value,
                         set_unity_gain=getattr(args, "set_unity_gain", False), srate=srate)
     ex = ModSpecExtractor(cfg)
+    reverberator = Reverberator(rir, device=ex.device) if rir is not None else None
     all_feats = {}
     batch = []
 
     def flush():
         if batch:
-            outs = ex([b[1] for b in batch])
+            outs = ex([b[1] for b in batch], reverb=reverberator)
             for (k, _), o in zip(batch, outs):
                 all_feats[k] = o.cpu().numpy()
             del batch[:]

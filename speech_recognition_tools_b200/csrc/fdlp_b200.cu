@@ -1586,6 +1586,31 @@ extern "C" int fdlp_diff_filter(const void* wav, int32_t wav_dtype, const int64_
   return FDLP_OK;
 }
 
+extern "C" int fdlp_noise_mix(const void* wav, int32_t wav_dtype, const int64_t* utt_wav_off, int32_t n_utt,
+                              int64_t max_len, const int16_t* noise, const int64_t* utt_noise_off,
+                              const double* utt_snr_db, int32_t noise_mode, double* utt_alpha, float* out, void* stream) {
+  if (n_utt < 0 || max_len < 0) return set_err(FDLP_E_ARG, "bad argument%s", "");
+  if (n_utt == 0 || max_len == 0) return FDLP_OK;
+  if (!wav || !utt_wav_off || !noise || !utt_noise_off || !utt_snr_db || !utt_alpha || !out)
+    return set_err(FDLP_E_ARG, "null argument%s", "");
+  if (wav_dtype != FDLP_WAV_INT16 && wav_dtype != FDLP_WAV_FLOAT32) return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
+  if (noise_mode != FDLP_NOISE_INT16_WRAP && noise_mode != FDLP_NOISE_FLOAT) return set_err(FDLP_E_ARG, "bad noise mode%s", "");
+  if (n_utt > 65535) return set_err(FDLP_E_ARG, "too many utterances in one call%s", "");
+  cudaStream_t st = (cudaStream_t)stream;
+  NoiseArgs a;
+  a.wav = wav; a.wav_dtype = wav_dtype; a.utt_wav_off = utt_wav_off; a.noise = noise; a.utt_noise_off = utt_noise_off;
+  a.utt_snr_db = utt_snr_db; a.utt_alpha = utt_alpha; a.mode = noise_mode;
+  noise_alpha_kernel<<<n_utt, kNoiseThreads, 0, st>>>(a);
+  FDLP_CUDA(cudaGetLastError());
+  NoiseMixArgs m;
+  m.wav = wav; m.wav_dtype = wav_dtype; m.utt_wav_off = utt_wav_off; m.noise = noise; m.utt_noise_off = utt_noise_off;
+  m.utt_alpha = utt_alpha; m.out = out;
+  const long long bx = std::min<long long>((max_len + 255) / 256, 1024);
+  noise_mix_kernel<<<dim3((unsigned)bx, (unsigned)n_utt), 256, 0, st>>>(m);
+  FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
 // ================================================================ --add_reverb (features.py:110-115)
 struct fdlp_reverb_plan {
   int R = 0, B = 0, F = 0, logF = 0, P = 0;

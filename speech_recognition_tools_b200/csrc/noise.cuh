@@ -114,6 +114,31 @@ __global__ void __launch_bounds__(kNoiseThreads) noise_alpha_kernel(const NoiseA
   }
 }
 
+// add_noise_to_wav's last line, features.py:31: sig + alpha * ns, as a waveform of its own (the FDLP path fuses this
+// into the framing load; the mel path takes the mixed float32 waveform).  float64 sum rounded once.
+struct NoiseMixArgs {
+  const void* wav;
+  int wav_dtype;
+  const int64_t* utt_wav_off;   // [n_utt+1]
+  const int16_t* noise;
+  const int64_t* utt_noise_off; // [n_utt]
+  const double* utt_alpha;      // [n_utt] from noise_alpha_kernel
+  float* out;                   // packed like wav
+};
+
+__global__ void __launch_bounds__(256) noise_mix_kernel(const NoiseMixArgs a) {
+  const int u = blockIdx.y;
+  const int64_t woff = a.utt_wav_off[u];
+  const int64_t T = a.utt_wav_off[u + 1] - woff;
+  const int16_t* nz = a.noise + a.utt_noise_off[u];
+  const double alpha = a.utt_alpha[u];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < T; i += (int64_t)gridDim.x * blockDim.x) {
+    const double s = a.wav_dtype == FDLP_WAV_INT16 ? (double)reinterpret_cast<const int16_t*>(a.wav)[woff + i]
+                                                    : (double)reinterpret_cast<const float*>(a.wav)[woff + i];
+    a.out[woff + i] = (float)(s + alpha * (double)nz[i]);
+  }
+}
+
 // --add_noise diff (computeFDLPSpectrogram.py:162-164): signal = scipy.signal.convolve(signal, a, mode='same') with
 // the 13-tap kernel a = [1, 2, 3, 2, 0, -2, -5, -2, 0, 2, 3, 2, 1]:  out[q] = sum_t a[t] x[q + 6 - t], x zero outside
 // the utterance.  For int16 input the result is an integer below 2^20, so the float32 output is exact; for float32

@@ -364,6 +364,40 @@ class NoiseSpec:
     which: Optional[Sequence[int]] = None
 
 
+def noise_to_device(noise: Optional["NoiseSpec"], lengths, device):
+    """Device tables of --add_noise for one batch: the recording(s), per-utterance excerpt offsets
+    floor(rand * (len(noise) - T)) (features.py:25) and SNRs."""
+    if noise is None:
+        return None
+    lengths = np.asarray(lengths, dtype=np.int64)
+    recs = noise.samples if isinstance(noise.samples, (list, tuple)) else [noise.samples]
+    recs = [r if isinstance(r, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(r)) for r in recs]
+    if any(r.dtype != torch.int16 or r.dim() != 1 for r in recs):
+        raise TypeError("noise recording must be int16 (scipy.io.wavfile.read of noises/<type>.wav)")
+    n_utt = len(lengths)
+    which = np.zeros(n_utt, dtype=np.int64) if noise.which is None else np.asarray(noise.which, dtype=np.int64)
+    if which.shape != (n_utt,) or (n_utt and (which.min() < 0 or which.max() >= len(recs))):
+        raise ValueError("NoiseSpec.which needs one recording index per utterance")
+    rec_len = np.array([int(r.numel()) for r in recs], dtype=np.int64)
+    rec_base = np.concatenate([[0], np.cumsum(rec_len)])[:-1]
+    ns = recs[0] if len(recs) == 1 else torch.cat(recs)
+    rand = noise.rand
+    if rand is None or isinstance(rand, (int, np.integer)):
+        rand = np.random.RandomState(0 if rand is None else int(rand))
+    if isinstance(rand, np.random.RandomState):
+        draws = np.array([rand.rand() for _ in range(n_utt)])
+    else:
+        draws = np.asarray(list(rand), dtype=np.float64)
+    Tn = rec_len[which]
+    if n_utt and np.any(Tn <= lengths):
+        raise ValueError("noise recording must be longer than every utterance (features.py:25-26)")
+    off = rec_base[which] + np.floor(draws * (Tn - lengths)).astype(np.int64)  # features.py:25
+    snr = np.broadcast_to(np.asarray(noise.snr_db, dtype=np.float64), (n_utt,)).copy()
+    mode = {"int16_wrap": L.FDLP_NOISE_INT16_WRAP, "float": L.FDLP_NOISE_FLOAT}[noise.mode]
+    return dict(mode=mode, samples=ns.to(device, non_blocking=True),
+                off=torch.from_numpy(off).to(device), snr=torch.from_numpy(snr).to(device))
+
+
 # --------------------------------------------------------------------------- extractor
 class FdlpExtractor:
     """One plan (filterbank, twiddles, scratch) on one device; call it with a list of waveforms."""
@@ -496,35 +530,8 @@ class FdlpExtractor:
         b.status = status.data_ptr() if status is not None else None
         return b
 
-    def _noise_to_device(self, noise: Optional[NoiseSpec], lay: BatchLayout):
-        if noise is None:
-            return None
-        recs = noise.samples if isinstance(noise.samples, (list, tuple)) else [noise.samples]
-        recs = [r if isinstance(r, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(r)) for r in recs]
-        if any(r.dtype != torch.int16 or r.dim() != 1 for r in recs):
-            raise TypeError("noise recording must be int16 (scipy.io.wavfile.read of noises/<type>.wav)")
-        n_utt = lay.n_utt
-        which = np.zeros(n_utt, dtype=np.int64) if noise.which is None else np.asarray(noise.which, dtype=np.int64)
-        if which.shape != (n_utt,) or (n_utt and (which.min() < 0 or which.max() >= len(recs))):
-            raise ValueError("NoiseSpec.which needs one recording index per utterance")
-        rec_len = np.array([int(r.numel()) for r in recs], dtype=np.int64)
-        rec_base = np.concatenate([[0], np.cumsum(rec_len)])[:-1]
-        ns = recs[0] if len(recs) == 1 else torch.cat(recs)
-        rand = noise.rand
-        if rand is None or isinstance(rand, (int, np.integer)):
-            rand = np.random.RandomState(0 if rand is None else int(rand))
-        if isinstance(rand, np.random.RandomState):
-            draws = np.array([rand.rand() for _ in range(n_utt)])
-        else:
-            draws = np.asarray(list(rand), dtype=np.float64)
-        Tn = rec_len[which]
-        if n_utt and np.any(Tn <= lay.lengths):
-            raise ValueError("noise recording must be longer than every utterance (features.py:25-26)")
-        off = rec_base[which] + np.floor(draws * (Tn - lay.lengths)).astype(np.int64)  # features.py:25
-        snr = np.broadcast_to(np.asarray(noise.snr_db, dtype=np.float64), (n_utt,)).copy()
-        mode = {"int16_wrap": L.FDLP_NOISE_INT16_WRAP, "float": L.FDLP_NOISE_FLOAT}[noise.mode]
-        return dict(mode=mode, samples=ns.to(self.device, non_blocking=True),
-                    off=torch.from_numpy(off).to(self.device), snr=torch.from_numpy(snr).to(self.device))
+    def _noise_to_device(self, noise: Optional[NoiseSpec], lay):
+        return noise_to_device(noise, lay.lengths, self.device)
 
     # ---- the hot path
     def forward_packed(self, wav_dev: torch.Tensor, lay: BatchLayout, feats: Optional[torch.Tensor] = None,

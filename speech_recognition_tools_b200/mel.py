@@ -123,13 +123,45 @@ class MelExtractor:
             L.check(self._lib.mel_forward(self._plan, C.byref(b), C.c_void_p(stream)))
         return feats
 
-    def __call__(self, wavs, cmvn: Optional[torch.Tensor] = None, reverb=None):
-        """`reverb`: impulse response or reverb.Reverberator for --add_reverb (computeMelSpectrum.py:143-145); the
-        reverberated waveform reaches the framing kernel as float32."""
+    def mix_noise(self, wav_dev: torch.Tensor, lengths, noise):
+        """--add_noise on the mel path (computeMelSpectrum.py:134-141): `noise` is 'diff' (13-tap FIR,
+        fdlp_diff_filter) or a fdlp.NoiseSpec (add_noise_to_wav, features.py:24-31: fdlp_noise_mix).  Returns the float32
+        packed batch the framing kernel then reads."""
+        from .fdlp import noise_to_device
+        lengths = np.asarray(lengths, dtype=np.int64)
+        off = torch.from_numpy(np.concatenate([[0], np.cumsum(lengths)]).astype(np.int64)).to(self.device)
+        out = torch.empty(wav_dev.numel(), dtype=torch.float32, device=self.device)
+        dt = L.FDLP_WAV_INT16 if wav_dev.dtype == torch.int16 else L.FDLP_WAV_FLOAT32
+        if wav_dev.dtype not in (torch.int16, torch.float32):
+            raise TypeError("waveforms must be int16 or float32")
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        max_len = int(lengths.max()) if len(lengths) else 0
+        with torch.cuda.device(self.device):
+            if isinstance(noise, str):
+                if noise != "diff":
+                    raise ValueError("noise must be a NoiseSpec or the string 'diff'")
+                L.check(self._lib.fdlp_diff_filter(C.c_void_p(wav_dev.data_ptr()), dt, C.c_void_p(off.data_ptr()),
+                                                    len(lengths), max_len, C.c_void_p(out.data_ptr()), C.c_void_p(stream)))
+            else:
+                nd = noise_to_device(noise, lengths, self.device)
+                alpha = torch.empty(max(len(lengths), 1), dtype=torch.float64, device=self.device)
+                L.check(self._lib.fdlp_noise_mix(C.c_void_p(wav_dev.data_ptr()), dt, C.c_void_p(off.data_ptr()),
+                                                  len(lengths), max_len, C.c_void_p(nd["samples"].data_ptr()),
+                                                  C.c_void_p(nd["off"].data_ptr()), C.c_void_p(nd["snr"].data_ptr()),
+                                                  nd["mode"], C.c_void_p(alpha.data_ptr()), C.c_void_p(out.data_ptr()),
+                                                  C.c_void_p(stream)))
+        return out
+
+    def __call__(self, wavs, cmvn: Optional[torch.Tensor] = None, reverb=None, noise=None):
+        """`noise`: 'diff' or a fdlp.NoiseSpec for --add_noise (applied first, computeMelSpectrum.py:134-141);
+        `reverb`: impulse response or reverb.Reverberator for --add_reverb (:143-145); the augmented waveform reaches the
+        framing kernel as float32."""
         if len(wavs) == 0:
             return []
         host, lengths = FdlpExtractor.pack(wavs)
         wav_dev = host.to(self.device, non_blocking=True)
+        if noise is not None:
+            wav_dev = self.mix_noise(wav_dev, lengths, noise)
         if reverb is not None:
             from .reverb import reverberate_packed
             wav_dev, lengths = reverberate_packed(reverb, wav_dev, lengths, self.device, torch.float32)

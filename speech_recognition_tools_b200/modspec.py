@@ -133,7 +133,8 @@ class ModSpecExtractor:
         b = L.FdlpBatch()
         d = lay.dev
         b.wav = wav_dev.data_ptr()
-        b.wav_dtype = L.FDLP_WAV_INT16 if wav_dev.dtype == torch.int16 else L.FDLP_WAV_FLOAT32
+        b.wav_dtype = {torch.int16: L.FDLP_WAV_INT16, torch.float32: L.FDLP_WAV_FLOAT32,
+                       torch.float64: L.FDLP_WAV_FLOAT64}[wav_dev.dtype]  # float64: the reverberated waveform
         b.n_utt, b.n_seg, b.n_frames, b.max_utt_frames = lay.n_utt, lay.n_seg, lay.n_frames, lay.max_utt_frames
         b.utt_wav_off = d["utt_wav_off"].data_ptr()
         b.utt_seg_off = d["utt_seg_off"].data_ptr()
@@ -151,9 +152,13 @@ class ModSpecExtractor:
         return out, status
 
     def __call__(self, wavs: Sequence[Union[np.ndarray, torch.Tensor]], return_status: bool = False,
-                 max_segments: int = 20000):
+                 max_segments: int = 20000, reverb=None, unity_gain: bool = False):
         """List of mono waveforms -> list of [frame_num_u, nfilters*feat_len] float32 device tensors.  Utterances are
-        processed in runs of at most `max_segments` segments (a 10 s utterance has 1000 half-second segments)."""
+        processed in runs of at most `max_segments` segments (a 10 s utterance has 1000 half-second segments).
+        `reverb`: impulse response or reverb.Reverberator for --add_reverb (computeModulationSpectrum.py:94-105,146-148:
+        addReverb before framing; the float64 result goes to the framing kernel).  `unity_gain`: the LPC gain is taken as
+        1, i.e. c0 = log(sqrt(1)) = 0 (computeModulationSpectrum_segments.py:96-97; the other coefficients do not
+        depend on the gain)."""
         if len(wavs) == 0:
             return ([], torch.zeros(0, dtype=torch.int32, device=self.device)) if return_status else []
         outs, sts = [], []
@@ -167,8 +172,15 @@ class ModSpecExtractor:
                 nseg += n
                 j += 1
             host, lengths = FdlpExtractor.pack(wavs[i:j])
+            wav_dev = host.to(self.device, non_blocking=True)
+            if reverb is not None:
+                from .reverb import reverberate_packed
+                wav_dev, lengths = reverberate_packed(reverb, wav_dev, lengths, self.device, torch.float64)
             lay = self.layout(lengths)
-            feats, st = self.forward_packed(host.to(self.device, non_blocking=True), lay)
+            feats, st = self.forward_packed(wav_dev, lay)
+            if unity_gain and 0 in self._idx:
+                pos = int(np.flatnonzero(self._idx == 0)[0])
+                feats.view(lay.n_seg, self.cfg.nfilters, self.feat_len)[:, :, pos] = 0.0
             outs.extend(feats[int(lay.utt_seg_off[u]):int(lay.utt_seg_off[u + 1])] for u in range(lay.n_utt))
             sts.append(st[:lay.n_utt])
             i = j

@@ -170,3 +170,27 @@ def test_fdlp_cli_two_ranks_equal_one_process(tmp_path):
     s1, s2 = stats(one + ".cmvn.ark"), stats(two + ".cmvn.ark")
     np.testing.assert_allclose(s2, s1, rtol=1e-12, atol=1e-9)
     assert s2[0, 80] == sum(v.shape[0] for v in a.values())
+
+
+def test_mel_cli_add_noise_matches_reference_golden(tmp_path, monkeypatch):
+    """computeMelSpectrum.py --add_noise type,snr (:69-72,134-141) through the shim, same np.random.seed as the reference."""
+    from speech_recognition_tools_b200.cli import computeMelSpectrum as cm
+    c = load_case("mel_noise_babble10")
+    os.makedirs(tmp_path / "noises")
+    wavfile.write(str(tmp_path / "noises" / "babble.wav"), 16000, c["noise"]["data"])
+    wavfile.write(str(tmp_path / "u.wav"), 16000, c["x"])
+    with open(tmp_path / "wav.scp", "w") as f:
+        f.write("utt1 %s\n" % (tmp_path / "u.wav"))
+    monkeypatch.chdir(tmp_path)
+    args = cm.get_args([str(tmp_path / "wav.scp"), str(tmp_path / "m"), "--nfilters", "80", "--nfft", "2048",
+                        "--add_noise", "babble,10"])
+    np.random.seed(c["meta"]["seed"])
+    feats = cm.compute_mel_spectrum(args, return_feats=True)
+    np.testing.assert_allclose(feats["utt1"], c["feats"], rtol=0, atol=1e-4)
+    c2 = load_case("mel_noise_diff")
+    wavfile.write(str(tmp_path / "d.wav"), 16000, c2["x"])
+    with open(tmp_path / "d.scp", "w") as f:
+        f.write("utt1 %s\n" % (tmp_path / "d.wav"))
+    feats = cm.compute_mel_spectrum(cm.get_args([str(tmp_path / "d.scp"), str(tmp_path / "d"), "--add_noise", "diff"]),
+                                    return_feats=True)
+    np.testing.assert_allclose(feats["utt1"], c2["feats"], rtol=0, atol=1e-4)

@@ -11,11 +11,17 @@ pytestmark = pytest.mark.gpu
 @pytest.mark.parametrize("name", golden_cases("mel"))
 def test_mel_matches_reference_golden(name):
     from speech_recognition_tools_b200.mel import MelConfig, MelExtractor
+    from speech_recognition_tools_b200.fdlp import NoiseSpec
     c = load_case(name)
-    p, _, _ = split_params(c["meta"])
+    p, add_noise, _ = split_params(c["meta"])
     kw = dict(MEL_DEFAULTS, **p)
     ex = MelExtractor(MelConfig(**kw), device="cuda:0")
-    got = ex([c["x"]], reverb=c["rir"])[0].cpu().numpy().astype(np.float64)
+    noise = None
+    if add_noise == "diff":  # computeMelSpectrum.py:134-139
+        noise = "diff"
+    elif add_noise and add_noise != "clean":  # :140-141: add_noise_to_wav with numpy's dtype semantics
+        noise = NoiseSpec(samples=c["noise"]["data"], snr_db=float(add_noise.split(",")[1]), rand=c["meta"]["seed"])
+    got = ex([c["x"]], reverb=c["rir"], noise=noise)[0].cpu().numpy().astype(np.float64)
     ref = c["feats"]
     assert got.shape == ref.shape
     if kw["spectrum_type"] == "power":

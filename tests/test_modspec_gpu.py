@@ -14,8 +14,10 @@ pytestmark = pytest.mark.gpu
 def test_modspec_matches_reference_golden(name):
     from speech_recognition_tools_b200.modspec import ModSpecConfig, ModSpecExtractor
     c = load_case(name)
-    ex = ModSpecExtractor(ModSpecConfig(**c["meta"]["params"]), device="cuda:0")
-    outs, st = ex([c["x"]], return_status=True)
+    prm = dict(c["meta"]["params"])
+    prm.pop("add_reverb", None)  # computeModulationSpectrum.py:146-148: addReverb with the case's ./RIR recording
+    ex = ModSpecExtractor(ModSpecConfig(**prm), device="cuda:0")
+    outs, st = ex([c["x"]], return_status=True, reverb=c["rir"])
     assert int(st.cpu()[0]) == 0
     got = outs[0].cpu().numpy().astype(np.float64)
     assert got.shape == c["feats"].shape
@@ -64,3 +66,39 @@ def test_modspec_cli_matches_golden(tmp_path):
     cli.getFeats(args)
     got = dict(read_ark(str(tmp_path / "out.ark")))["utt1"]
     np.testing.assert_allclose(got, c["feats"], rtol=2e-6, atol=2e-6)
+
+
+@pytest.mark.parametrize("name", ["modsegs_default", "modsegs_unity_reverb"])
+def test_modspec_segments_cli_matches_reference_golden(name, tmp_path, monkeypatch):
+    """cli/computeModulationSpectrum_segments.py == the unmodified computeModulationSpectrum_segments.py on a scp of two
+    recordings and a Kaldi segments file (segments of both, out of order; --set_unity_gain; --add_reverb)."""
+    import json
+    import os
+    from scipy.io import wavfile
+    from speech_recognition_tools_b200 import synth
+    from speech_recognition_tools_b200.cli import computeModulationSpectrum_segments as cli
+    from speech_recognition_tools_b200.kaldi_io import read_ark
+    from tests.golden_util import GOLDEN_DIR
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    meta = json.loads(str(z["meta"]))
+    os.makedirs(tmp_path / "RIR")
+    wavfile.write(str(tmp_path / "RIR" / "RIR_LargeRoom1_far_AnglA.wav"), 16000,
+                  synth.rir_int16(meta["room"], meta["R"], meta["rir_seed"]))
+    with open(tmp_path / "wav.scp", "w") as f:
+        for i, sp in enumerate(meta["inputs"]):
+            x = synth.make_utterance(sp["kind"], sp["seed"], sp["utt"], sp["T"], sp.get("sigma_f", 30.0))
+            wavfile.write(str(tmp_path / ("w%d.wav" % (i + 1))), 16000, x)
+            f.write("w%d %s\n" % (i + 1, tmp_path / ("w%d.wav" % (i + 1))))
+    with open(tmp_path / "segments", "w") as f:
+        for s_ in meta["segments"]:
+            f.write("%s %s %g %g\n" % tuple(s_))
+    argv = [str(tmp_path / "wav.scp"), str(tmp_path / "segments"), str(tmp_path / "o")]
+    for k, v in meta["params"].items():
+        argv += ["--%s" % k] if v is True else ["--%s=%s" % (k, v)]
+    monkeypatch.chdir(tmp_path)
+    cli.getFeats(cli.get_args(argv))
+    ark = read_ark(str(tmp_path / "o.ark"))
+    assert list(ark) == [s_[0] for s_ in meta["segments"]]
+    for seg_id in ark:
+        assert ark[seg_id].shape == z[seg_id].shape
+        np.testing.assert_allclose(ark[seg_id], z[seg_id], rtol=2e-6, atol=2e-6)

@@ -50,9 +50,16 @@ def test_fdlp_oracle_matches_reference(name):
 @pytest.mark.parametrize("name", golden_cases("mel"))
 def test_mel_oracle_matches_reference(name):
     c = load_case(name)
-    p, _, _ = split_params(c["meta"])
+    p, add_noise, _ = split_params(c["meta"])
     kw = dict(MEL_DEFAULTS, **p)
-    x = c["x"] if c["rir"] is None else oreverb.add_reverb(c["x"], c["rir"])
+    x = c["x"]
+    if add_noise == "diff":  # computeMelSpectrum.py:134-139
+        x = ofdlp.diff_filter(x)
+    elif add_noise and add_noise != "clean":  # :140-141
+        rand = np.random.RandomState(c["meta"]["seed"]).rand()
+        x = ofdlp.add_noise_to_wav(x, c["noise"]["data"], float(add_noise.split(",")[1]), rand=rand)
+    if c["rir"] is not None:
+        x = oreverb.add_reverb(x, c["rir"])
     got = omel.mel_spectrogram(x, **kw)
     assert got.shape == c["feats"].shape
     np.testing.assert_allclose(got, c["feats"], rtol=1e-12, atol=1e-12)
@@ -113,7 +120,9 @@ def test_modspec_oracle_matches_reference(name):
     from oracle import modspec as omod
     c = load_case(name)
     p = dict(c["meta"]["params"])
-    got = omod.modulation_spectrum(c["x"], **p)
+    p.pop("add_reverb", None)
+    x = c["x"] if c["rir"] is None else oreverb.add_reverb(c["x"], c["rir"])  # computeModulationSpectrum.py:146-148
+    got = omod.modulation_spectrum(x, **p)
     ref = c["feats"]
     assert got.shape == ref.shape
     np.testing.assert_allclose(got, ref, rtol=1e-6, atol=1e-9)
@@ -152,3 +161,34 @@ def test_reverb_oracle_matches_reference(name):
     assert ind == c["meta"]["ind"]
     assert out.shape == ref.shape
     np.testing.assert_allclose(out, ref, rtol=0, atol=1e-9 * max(1.0, np.abs(ref).max()))
+
+
+@pytest.mark.parametrize("name", ["modsegs_default", "modsegs_unity_reverb"])
+def test_modspec_segments_oracle_matches_reference(name):
+    """computeModulationSpectrum_segments.py:24-118 restated with the oracle pieces: cut, / 2^15, addReverb, hanning
+    frames, mel bands, the first nmodulations cepstral coefficients (c0 = 0 under --set_unity_gain)."""
+    import json
+    import os
+    from oracle import modspec as omod
+    from speech_recognition_tools_b200 import synth
+    from tests.golden_util import GOLDEN_DIR
+    z = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    meta = json.loads(str(z["meta"]))
+    prm = dict(dict(nfilters=15, nmodulations=12, order=50, fduration=0.5, frate=100), **meta["params"])
+    wavs = {"w%d" % (i + 1): synth.make_utterance(sp["kind"], sp["seed"], sp["utt"], sp["T"], sp.get("sigma_f", 30.0))
+            for i, sp in enumerate(meta["inputs"])}
+    rir = None
+    if prm.get("add_reverb"):
+        rir = synth.rir_int16(meta["room"], meta["R"], meta["rir_seed"])[:, 1] / np.power(2, 15)
+    for seg_id, wav_id, t0, t1 in meta["segments"]:
+        x = wavs[wav_id][int(float(t0) * 16000):int(float(t1) * 16000)] / np.power(2, 15)
+        if rir is not None:
+            x = oreverb.add_reverb(x, rir)
+        got = omod.modulation_spectrum(x, nfilters=prm["nfilters"], coeff_0=1, coeff_n=prm["nmodulations"],
+                                       order=prm["order"], fduration=prm["fduration"], frate=prm["frate"])
+        if prm.get("set_unity_gain"):
+            got = got.reshape(got.shape[0], prm["nfilters"], prm["nmodulations"]).copy()
+            got[:, :, 0] = 0.0
+            got = got.reshape(got.shape[0], -1)
+        assert got.shape == z[seg_id].shape
+        np.testing.assert_allclose(got, z[seg_id], rtol=1e-6, atol=1e-8)

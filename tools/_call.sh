@@ -1,2 +1,2 @@
 cd $GRAFT_REPO_ROOT
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29555 bench.py --gpus 2 --steps 10 --warmup 3 > gpurun_out/r2_bench11_2gpu.json 2> gpurun_out/r2_bench11_2gpu.err
+timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -25 > gpurun_out/r2_t12.log
