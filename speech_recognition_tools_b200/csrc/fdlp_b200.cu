@@ -14,6 +14,7 @@
 #include "dct.cuh"
 #include "lpc_env.cuh"
 #include "mel.cuh"
+#include "mel_mma.cuh"
 #include "mfcc.cuh"
 #include "noise.cuh"
 #include "ola.cuh"
@@ -1212,6 +1213,11 @@ struct mel_plan {
   float2 *d_tw4 = nullptr, *d_unpackA32 = nullptr;
   int4* d_band = nullptr;
   double* d_cmvn_part = nullptr;  // [kMelCmvnCtas, 2, J+1]
+  // second-generation kernel (mel_mma.cuh): nfft = 2048, magnitudes in registers, filterbank on the tensor cores
+  bool mma_ok = false;
+  MelMmaArgs mma;             // tile tables filled at plan creation, pointers per call
+  float2* d_lane_tw = nullptr;
+  float4* d_bfrag = nullptr;
 };
 
 constexpr int kMelCmvnCtas = 296;
@@ -1251,7 +1257,7 @@ static void mel_free(mel_plan* p) {
   free_fft_tables(&p->fft);
   cudaFree(p->d_ham); cudaFree(p->d_fbank); cudaFree(p->d_lo); cudaFree(p->d_hi); cudaFree(p->d_frame_utt);
   cudaFree(p->d_ham32); cudaFree(p->d_tw4); cudaFree(p->d_unpackA32); cudaFree(p->d_wts); cudaFree(p->d_band);
-  cudaFree(p->d_cmvn_part);
+  cudaFree(p->d_cmvn_part); cudaFree(p->d_lane_tw); cudaFree(p->d_bfrag);
   delete p;
 }
 
@@ -1330,6 +1336,81 @@ extern "C" int mel_plan_create(const mel_params* prm, mel_plan** out) {
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (sms > 0) p->sms = sms;
+    // mel_mma.cuh (magnitudes in registers, filterbank as a banded 3xTF32 GEMM) is an evidenced experiment, not the
+    // default: it takes the shared-memory pipe from 79 % to 29 % busy but is issue-bound at 2700 instructions per frame
+    // (3.9 ms against 3.7 ms for mel_frames_warp_kernel on the bench batch); FDLP_MEL_MMA=1 selects it
+    if (n == 1024 && J <= 8 * kMmaMaxTiles && getenv("FDLP_MEL_MMA")) {
+      // ---- tables of mel_frames_mma_kernel ----
+      std::vector<float2> ltw(5 * 32);
+      for (int l = 0; l < 32; ++l) {
+        const int mult[4] = {1, 8, 16, 24};
+        for (int q = 0; q < 4; ++q) {
+          const long double ang = -2.0L * M_PIl * (long double)((mult[q] * l) % n) / n;
+          ltw[q * 32 + l] = make_float2((float)cosl(ang), (float)sinl(ang));
+        }
+        const long double ang = -2.0L * M_PIl * l / (2.0L * n);
+        ltw[4 * 32 + l] = make_float2((float)cosl(ang), (float)sinl(ang));
+      }
+      auto rna_tf32 = [](float x) {  // cvt.rna.tf32.f32: 10 mantissa bits, nearest, ties away from zero
+        uint32_t b;
+        memcpy(&b, &x, 4);
+        b = (b + 0x1000u) & ~0x1FFFu;
+        float r;
+        memcpy(&r, &b, 4);
+        return r;
+      };
+      MelMmaArgs& m = p->mma;
+      memset(&m, 0, sizeof(m));
+      const int ntile = (J + 7) / 8;
+      std::vector<int> t_k0(ntile, 0), t_nk(ntile, 0), order(ntile);
+      for (int ti = 0; ti < ntile; ++ti) {
+        int klo = nb, khi = 0;
+        for (int j = 8 * ti; j < std::min(J, 8 * ti + 8); ++j)
+          if (hi[j] > lo[j]) { klo = std::min(klo, (int)lo[j]); khi = std::max(khi, (int)hi[j]); }
+        if (khi > klo) { t_k0[ti] = klo / 8 * 8; t_nk[ti] = (khi - t_k0[ti] + 7) / 8; }
+        order[ti] = ti;
+      }
+      // longest tiles first, each to the least loaded warp
+      std::sort(order.begin(), order.end(), [&](int x, int y) { return t_nk[x] != t_nk[y] ? t_nk[x] > t_nk[y] : x < y; });
+      std::vector<std::vector<int>> per_warp(kMmaWarps);
+      std::vector<int> load(kMmaWarps, 0);
+      for (int ti : order) {
+        int w = 0;
+        for (int x = 1; x < kMmaWarps; ++x) if (load[x] < load[w]) w = x;
+        per_warp[w].push_back(ti);
+        load[w] += t_nk[ti] + 2;
+      }
+      std::vector<float4> bfrag;
+      int slot = 0;
+      for (int w = 0; w < kMmaWarps; ++w) {
+        m.warp_tile0[w] = slot;
+        for (int ti : per_warp[w]) {
+          m.tile_n0[slot] = 8 * ti; m.tile_k0[slot] = t_k0[ti]; m.tile_nk[slot] = t_nk[ti];
+          m.tile_b0[slot] = (int)(bfrag.size() / 32);
+          for (int s_ = 0; s_ < t_nk[ti]; ++s_)
+            for (int l = 0; l < 32; ++l) {
+              const int j = 8 * ti + (l >> 2), kk = t_k0[ti] + 8 * s_ + (l & 3);
+              // (x 0.5: the kernel's magnitudes carry the factor 2 of the unscaled real-transform unpack)
+              auto wv = [&](int k) { return (j < J && k < nb) ? 0.5f * f32[(size_t)j * nb + k] : 0.f; };
+              const float b0 = wv(kk), b1 = wv(kk + 4);
+              const float h0 = rna_tf32(b0), h1 = rna_tf32(b1);
+              bfrag.push_back(make_float4(h0, h1, rna_tf32(b0 - h0), rna_tf32(b1 - h1)));
+            }
+          ++slot;
+        }
+      }
+      m.warp_tile0[kMmaWarps] = slot;
+      if (bfrag.empty()) bfrag.push_back(make_float4(0.f, 0.f, 0.f, 0.f));
+      if ((rc = upload(&p->d_lane_tw, ltw)) || (rc = upload(&p->d_bfrag, bfrag))) { mel_free(p); return rc; }
+      cudaError_t ea = cudaSuccess;
+#define MMA_SMEM(M1_)                                                                              \
+      if (ea == cudaSuccess) ea = raise_smem_limit(mel_frames_mma_kernel<M1_, int16_t>, mel_mma_smem_bytes()); \
+      if (ea == cudaSuccess) ea = raise_smem_limit(mel_frames_mma_kernel<M1_, float>, mel_mma_smem_bytes());
+      MMA_SMEM(5) MMA_SMEM(8) MMA_SMEM(0)
+#undef MMA_SMEM
+      if (ea != cudaSuccess) { mel_free(p); return set_err(FDLP_E_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(ea)); }
+      p->mma_ok = true;
+    }
   }
   p->smem = (size_t)prm->nfft * sizeof(float) + (size_t)(p->n + 1) * sizeof(float);
   cudaError_t e = raise_smem_limit(mel_frames_kernel<int16_t>, p->smem);
@@ -1361,6 +1442,24 @@ extern "C" int mel_forward(mel_plan* p, const mel_batch* b, void* stream) {
   mel_frame_map_kernel<<<b->n_utt, 128, 0, st>>>(b->utt_frame_off, b->n_utt, p->d_frame_utt);
   FDLP_CUDA(cudaGetLastError());
   if (b->wav_dtype != FDLP_WAV_INT16 && b->wav_dtype != FDLP_WAV_FLOAT32) return set_err(FDLP_E_ARG, "bad wav dtype%s", "");
+  if (p->mma_ok) {
+    MelMmaArgs m = p->mma;
+    m.wav = b->wav; m.utt_wav_off = b->utt_wav_off; m.utt_frame_off = b->utt_frame_off; m.frame_utt = p->d_frame_utt;
+    m.n_frames = b->n_frames; m.flen = p->flen; m.shift = p->shift; m.nfft = p->prm.nfft;
+    m.ham = p->d_ham32; m.lane_tw = p->d_lane_tw; m.bfrag = p->d_bfrag; m.feats = b->feats;
+    m.J = p->prm.nfilters; m.power = p->prm.power;
+    const long long rounds = (b->n_frames + kMmaFrames - 1) / kMmaFrames;
+    const dim3 grid((unsigned)std::min<long long>(rounds, (long long)p->sms * 2)), block(kMmaWarps * 32);
+    const bool i16 = b->wav_dtype == FDLP_WAV_INT16;
+    const size_t sm = mel_mma_smem_bytes();
+#define MMA_RUN(M1_)                                                                      \
+    if (i16) mel_frames_mma_kernel<M1_, int16_t><<<grid, block, sm, st>>>(m);             \
+    else mel_frames_mma_kernel<M1_, float><<<grid, block, sm, st>>>(m);
+    if (p->warp_m1 == 5) { MMA_RUN(5) } else if (p->warp_m1 == 8) { MMA_RUN(8) } else { MMA_RUN(0) }
+#undef MMA_RUN
+    FDLP_CUDA(cudaGetLastError());
+    return mel_cmvn(p, b, st);
+  }
   if (p->warp_r2 > 0) {
     MelWarpArgs w;
     memset(&w, 0, sizeof(w));

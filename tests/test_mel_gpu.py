@@ -56,3 +56,30 @@ def test_mel_empty_input_and_short_utterances():
         ref = omel.mel_spectrogram(w, **cfg)
         assert o.shape == ref.shape
         np.testing.assert_allclose(o.cpu().numpy(), ref, rtol=0, atol=1e-4)
+
+
+def test_mel_mma_variant_matches_reference_goldens(monkeypatch):
+    """mel_mma.cuh (FDLP_MEL_MMA=1): magnitudes kept in registers, filterbank as a banded 3xTF32 GEMM on the tensor
+    cores.  Not the default (it is not faster), but it must give the same features: the recipe-shaped goldens
+    (nfft 2048) within the 1e-4 log10 tolerance, and within 2e-5 of the default kernel."""
+    from speech_recognition_tools_b200.mel import MelConfig, MelExtractor
+    for name in ("mel_recipe_speech", "mel_recipe_power", "mel_noise_babble10"):
+        c = load_case(name)
+        p, add_noise, _ = split_params(c["meta"])
+        if add_noise and add_noise != "clean":
+            continue
+        kw = dict(MEL_DEFAULTS, **p)
+        base = MelExtractor(MelConfig(**kw), device="cuda:0")
+        ref = base([c["x"]])[0].cpu().numpy().astype(np.float64)
+        monkeypatch.setenv("FDLP_MEL_MMA", "1")
+        ex = MelExtractor(MelConfig(**kw), device="cuda:0")
+        monkeypatch.delenv("FDLP_MEL_MMA")
+        got = ex([c["x"]])[0].cpu().numpy().astype(np.float64)
+        if kw["spectrum_type"] == "power":
+            np.testing.assert_allclose(got, c["feats"], rtol=2e-5)
+            np.testing.assert_allclose(got, ref, rtol=1e-5)
+        else:
+            np.testing.assert_allclose(got, c["feats"], rtol=0, atol=1e-4)
+            np.testing.assert_allclose(got, ref, rtol=0, atol=2e-5)
+        ex.close()
+        base.close()
