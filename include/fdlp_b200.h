@@ -157,6 +157,10 @@ int fdlp_plan_destroy(fdlp_plan* plan);
 int fdlp_plan_get_geometry(const fdlp_plan* plan, fdlp_geometry* out);
 /* copy the plan's filterbank ([nfilters, N], last column already dropped) to a host buffer */
 int fdlp_plan_get_fbank(const fdlp_plan* plan, double* host_out);
+/* the filterbank builders on their own (host only): createFbank / createFbankCochlear(nfilters, nfft, srate, ...)
+ * (features.py:172-219) as float64 [nfilters, floor(nfft/2 + 1)], fbank_args as in fdlp_params */
+int fdlp_make_fbank(int32_t fbank_kind, const double* fbank_args /*host [5]*/, int32_t nfilters, int32_t nfft,
+                    int32_t srate, double* host_out);
 /* bytes of scratch the plan will hold for a batch of n_seg segments */
 int64_t fdlp_plan_scratch_bytes(const fdlp_plan* plan, int32_t n_seg);
 
@@ -231,6 +235,25 @@ int mel_forward(mel_plan* plan, const mel_batch* batch, void* stream);
 int fdlp_modspec_forward(fdlp_plan* plan, const fdlp_batch* batch, const int32_t* sel_idx /*dev [feat_len]*/,
                          const double* sel_scale /*dev [feat_len]*/, int32_t feat_len, int32_t absolute,
                          float* out /*dev [n_seg, nfilters*feat_len]*/, void* stream);
+
+/* ---- --complex_modulation of the same extractor (computeModulationSpectrum.py:45-48, :150-152, :164-173;
+ *      features.py:222-246 with keepreal=False).  Three steps, the middle one the caller's:
+ *      (1) fdlp_stage_frames: the plan's windowed, reflect-padded frames (getFrames) as float64 [n_seg, N];
+ *      (2) the caller takes ifft(frames)[:, :N/2] (scipy.fftpack.ifft: 1/N scaling) -- a library FFT;
+ *      (3) fdlp_modspec_complex_forward: per (frame, band) the filterbank taps [row_lo, row_hi) of fbank [nfilters, M]
+ *          (createFbank(nfilters, N, ...)[:, :-1], see fdlp_make_fbank) times the
+ *          spectrum, its circular complex autocorrelation, the Hermitian Toeplitz solve, the complex cepstrum
+ *          c[0..coeff_n-1], and out[seg, j*feat_len + q] = |c[sel_idx[q]] * sel_scale[q]| (absolute, feat_len = n_sel)
+ *          or the real parts in [0, n_sel) and the imaginary parts in [n_sel, 2 n_sel) (feat_len = 2 n_sel).
+ *          max_width = max(row_hi - row_lo); status [n_utt] is OR-ed into through seg_utt (may be NULL).  All
+ *          pointers are device pointers; nothing is allocated. ---- */
+int fdlp_stage_frames(fdlp_plan* plan, const fdlp_batch* batch, double* frames_out /*dev [n_seg, N]*/, void* stream);
+int fdlp_modspec_complex_forward(const double* spec /*dev [n_seg, spec_ld] complex128 (re, im)*/, int64_t spec_ld /*complex elements per row*/,
+                            int64_t n_seg, const int32_t* seg_utt /*dev [n_seg]*/, int32_t M, const double* fbank /*dev [nfilters, M]*/,
+                            const int32_t* row_lo /*dev [nfilters]*/, const int32_t* row_hi /*dev [nfilters]*/, int32_t max_width,
+                            int32_t nfilters, int32_t order, int32_t coeff_n, const int32_t* sel_idx /*dev [n_sel]*/,
+                            const double* sel_scale /*dev [n_sel]*/, int32_t n_sel, int32_t absolute,
+                            float* out /*dev [n_seg, nfilters*feat_len]*/, int32_t* status /*dev [n_utt] or NULL*/, void* stream);
 
 /* ---- --add_noise diff (computeFDLPSpectrogram.py:162-164): signal = convolve(signal, [1,2,3,2,0,-2,-5,-2,0,2,3,2,1],
  *      mode='same') per utterance; the float32 result (exact for int16 input) is then fed to fdlp_forward ---- */

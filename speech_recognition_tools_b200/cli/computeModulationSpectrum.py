@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Drop-in for /root/reference/src/featgen/computeModulationSpectrum.py (same flags :206-224, same outputs),
-computed by libfdlp_b200.so on the GPU.  `getFeats(args)` keeps the reference's signature.  The complex-modulation
-path (`--complex_modulation`: complex LPC on the ifft, used by no recipe or wrapper of the reference) raises."""
+computed by libfdlp_b200.so on the GPU.  `getFeats(args)` keeps the reference's signature; `--complex_modulation`
+(complex LPC on the frames' ifft) is supported (modspec.py)."""
 import argparse
 import os
 import sys

@@ -16,6 +16,7 @@
 #include "mel.cuh"
 #include "mel_mma.cuh"
 #include "mfcc.cuh"
+#include "modspec_cplx.cuh"
 #include "noise.cuh"
 #include "ola.cuh"
 #include "reverb.cuh"
@@ -796,6 +797,18 @@ extern "C" int fdlp_plan_get_geometry(const fdlp_plan* p, fdlp_geometry* out) {
 extern "C" int fdlp_plan_get_fbank(const fdlp_plan* p, double* host_out) {
   if (!p || !host_out) return set_err(FDLP_E_ARG, "null argument%s", "");
   memcpy(host_out, p->h_fbank.data(), p->h_fbank.size() * sizeof(double));
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_make_fbank(int32_t fbank_kind, const double* fbank_args, int32_t nfilters, int32_t nfft, int32_t srate,
+                               double* host_out) {
+  if (!fbank_args || !host_out || nfilters < 1 || nfft < 2 || srate < 1) return set_err(FDLP_E_ARG, "bad argument%s", "");
+  std::vector<double> f;
+  if (fbank_kind == FDLP_FBANK_MEL) f = make_mel_fbank(nfilters, nfft, srate, fbank_args[0]);
+  else if (fbank_kind == FDLP_FBANK_COCHLEAR)
+    f = make_cochlear_fbank(nfilters, nfft, srate, fbank_args[0], fbank_args[1], (int)fbank_args[2], fbank_args[3], fbank_args[4]);
+  else return set_err(FDLP_E_ARG, "fbank_kind must be FDLP_FBANK_MEL or FDLP_FBANK_COCHLEAR%s", "");
+  memcpy(host_out, f.data(), f.size() * sizeof(double));
   return FDLP_OK;
 }
 
@@ -1665,6 +1678,65 @@ extern "C" int fdlp_modspec_forward(fdlp_plan* p, const fdlp_batch* b, const int
   g.n_tasks = (int64_t)tasks; g.L = p->g.L; g.feat_len = feat_len; g.absolute = absolute;
   const long long blocks = std::min<long long>(((long long)tasks * feat_len + 255) / 256, 148LL * 16);
   modspec_gather_kernel<<<(unsigned)blocks, 256, 0, st>>>(g);
+  FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
+// ---- complex-modulation path (computeModulationSpectrum.py --complex_modulation) ----
+extern "C" int fdlp_stage_frames(fdlp_plan* p, const fdlp_batch* b, double* frames_out, void* stream) {
+  int rc = check_batch(p, b);
+  if (rc) return rc;
+  if (!frames_out) return set_err(FDLP_E_ARG, "null output%s", "");
+  if (b->noise_mode != FDLP_NOISE_NONE) return set_err(FDLP_E_ARG, "noise mixing is not part of this path%s", "");
+  if (b->n_seg == 0) return FDLP_OK;
+  FramesArgs a;
+  a.wav = b->wav; a.utt_wav_off = b->utt_wav_off; a.utt_seg_off = b->utt_seg_off; a.seg_utt = b->seg_utt;
+  a.N = p->g.N; a.S = p->g.S; a.out = frames_out; a.n_seg = b->n_seg;
+  a.a0 = p->prm.window_kind == FDLP_WINDOW_HANNING ? 0.5 : p->prm.window_kind == FDLP_WINDOW_SQUARE ? 1.0 : 0.54;
+  a.a1 = p->prm.window_kind == FDLP_WINDOW_HANNING ? 0.5 : p->prm.window_kind == FDLP_WINDOW_SQUARE ? 0.0 : 0.46;
+  const unsigned blocks = (unsigned)std::min<long long>(b->n_seg, 148LL * 16);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (b->wav_dtype == FDLP_WAV_INT16) window_frames_kernel<int16_t><<<blocks, 256, 0, st>>>(a);
+  else if (b->wav_dtype == FDLP_WAV_FLOAT32) window_frames_kernel<float><<<blocks, 256, 0, st>>>(a);
+  else window_frames_kernel<double><<<blocks, 256, 0, st>>>(a);
+  FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_modspec_complex_forward(const double* spec, int64_t spec_ld, int64_t n_seg, const int32_t* seg_utt,
+                                       int32_t M, const double* fbank, const int32_t* row_lo, const int32_t* row_hi,
+                                       int32_t max_width, int32_t nfilters, int32_t order, int32_t coeff_n,
+                                       const int32_t* sel_idx, const double* sel_scale, int32_t n_sel,
+                                       int32_t absolute, float* out, int32_t* status, void* stream) {
+  if (n_seg < 0 || M < 4 || spec_ld < M || nfilters < 1 || n_sel < 0 || max_width < 1 || max_width > M)
+    return set_err(FDLP_E_ARG, "bad size%s", "");
+  if (order < 1 || order + 2 > M || order > 4096 || coeff_n < 2 || coeff_n > 4096)
+    return set_err(FDLP_E_ARG, "need 1 <= order <= M - 2 and 2 <= coeff_n (order %s%ld)", "", (long)order);
+  if (n_seg == 0 || n_sel == 0) return FDLP_OK;
+  if (!spec || !seg_utt || !fbank || !row_lo || !row_hi || !sel_idx || !sel_scale || !out)
+    return set_err(FDLP_E_ARG, "null pointer%s", "");
+  CplxModspecArgs a;
+  a.spec = reinterpret_cast<const double2*>(spec); a.ld = spec_ld; a.fbank = fbank; a.row_lo = row_lo; a.row_hi = row_hi;
+  a.M = M; a.J = nfilters; a.order = order; a.lim = coeff_n; a.n_sel = n_sel; a.absolute = absolute ? 1 : 0;
+  a.max_width = max_width; a.sel_idx = sel_idx; a.sel_scale = sel_scale; a.out = out; a.status = status;
+  a.seg_utt = seg_utt; a.n_tasks = n_seg * (int64_t)nfilters;
+  const size_t smem = sizeof(double2) * ((size_t)max_width + (order + 2) + (std::max(order, coeff_n) + 2) + coeff_n);
+  if (smem > 227 * 1024) return set_err(FDLP_E_UNSUPPORTED, "band of %s%ld taps does not fit in shared memory", "", (long)max_width);
+  static std::mutex mu;
+  static size_t attr_smem[64] = {0};
+  int dev = 0;
+  FDLP_CUDA(cudaGetDevice(&dev));
+  if (smem > 48 * 1024) {
+    std::lock_guard<std::mutex> lk(mu);
+    if (dev < 64 && attr_smem[dev] < smem) {
+      FDLP_CUDA(cudaFuncSetAttribute(modspec_complex_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+      attr_smem[dev] = 227 * 1024;
+    }
+  }
+  const int threads = std::max(64, (order + 2 + 31) / 32 * 32);
+  if (threads > 1024) return set_err(FDLP_E_UNSUPPORTED, "order %s%ld needs more than 1024 lags per CTA", "", (long)order);
+  const unsigned blocks = (unsigned)std::min<long long>(a.n_tasks, 148LL * 32);
+  modspec_complex_kernel<<<blocks, threads, smem, (cudaStream_t)stream>>>(a);
   FDLP_CUDA(cudaGetLastError());
   return FDLP_OK;
 }

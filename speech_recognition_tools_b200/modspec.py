@@ -1,5 +1,6 @@
 """FDLP modulation-spectrum features: the host-side mirror of
-`/root/reference/src/featgen/computeModulationSpectrum.py` (`getFeats`, lines 31-203), real-modulation path.
+`/root/reference/src/featgen/computeModulationSpectrum.py` (`getFeats`, lines 31-203), real-modulation path and
+`--complex_modulation`.
 
 Per utterance the reference takes 0.5 s frames every 10 ms (`getFrames(signal, srate, frate, fduration,
 np.hanning)`), their DCT, and for every (frame, band) the sub-band LPC model and its cepstrum
@@ -7,6 +8,12 @@ np.hanning)`), their DCT, and for every (frame, band) the sub-band LPC model and
 coefficients `mod_spec[coeff_0-1:coeff_n]` of all bands, band-major.  That is K1-K4 of the FDLP-spectrogram
 path with a different window, a segment shift of `int(srate / frate)` samples and the cepstrum instead of the
 envelope, so it runs on the same plan (`cepstrum_mode`) and kernels; `fdlp_modspec_forward` adds the gather.
+
+`--complex_modulation` (:45-48, :150-152, :164-173) replaces the DCT by the first half of the frames' inverse FFT, the
+filterbank by one over int(fduration*srate) points, and the real LPC model by a complex one: `fdlp_stage_frames` (the
+plan's framing), a cuFFT transform through torch.fft (library code, like the reference's scipy call), then
+`fdlp_modspec_complex_forward` (csrc/modspec_cplx.cuh: band product, circular autocorrelation, Hermitian Levinson-Durbin,
+complex cepstrum, selection).
 
 There is no CPU fallback: the extractor needs libfdlp_b200.so and a CUDA device."""
 import ctypes as C
@@ -47,8 +54,14 @@ def feature_selection(cfg: ModSpecConfig):
         raise ValueError("need 1 <= coeff_0 <= coeff_n")
     idx = np.arange(cfg.coeff_0 - 1, cfg.coeff_n)
     scale = np.ones(cfg.coeff_n)
+    if cfg.complex_modulation and cfg.keep_even and not cfg.absolute_value:
+        # :64-71 sizes each_feat from coeff_num, :171-172 fills it with 2*coeff_num values: the reference stops with
+        # "could not broadcast input array" on the first frame
+        raise ValueError("--keep_even with --complex_modulation needs --absolute_value (the reference fails there: "
+                         "computeModulationSpectrum.py:64-71 vs :171-185)")
     if cfg.compensate_noise:
-        scale = np.linspace(0, coeff_num / (2 * cfg.fduration), cfg.coeff_n)
+        fmax = coeff_num / cfg.fduration if cfg.complex_modulation else coeff_num / (2 * cfg.fduration)   # :80-86
+        scale = np.linspace(0, fmax, cfg.coeff_n)
     if cfg.keep_even:
         idx = idx[1::2] if cfg.coeff_0 % 2 == 0 else idx[0::2]
     return idx.astype(np.int32), scale[idx].astype(np.float64)
@@ -59,15 +72,15 @@ class ModSpecExtractor:
 
     def __init__(self, cfg: Optional[ModSpecConfig] = None, device=None, **kwargs):
         self.cfg = cfg if cfg is not None else ModSpecConfig(**kwargs)
-        if self.cfg.complex_modulation:
-            raise NotImplementedError("--complex_modulation (complex LPC on the ifft) is not implemented")
         if not torch.cuda.is_available():
             raise RuntimeError("ModSpecExtractor needs a CUDA device (sm_100a); there is no CPU fallback")
         self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
         self._lib = L.load()
         kind, fargs = parse_fbank_type(self.cfg.fbank_type)
         self._idx, self._scale = feature_selection(self.cfg)
-        self.feat_len = int(len(self._idx))
+        self.feat_len = int(len(self._idx))     # per band; twice that for complex cepstra without --absolute_value
+        if self.cfg.complex_modulation and not self.cfg.absolute_value:
+            self.feat_len *= 2
         self._weights = np.ones(self.cfg.coeff_n, dtype=np.float64)
         prm = L.FdlpParams()
         prm.srate, prm.nfilters, prm.order = self.cfg.srate, self.cfg.nfilters, self.cfg.order
@@ -90,6 +103,28 @@ class ModSpecExtractor:
         self.geom = {n: getattr(g, n) for n, _ in L.FdlpGeometry._fields_}
         self._idx_dev = torch.from_numpy(self._idx).to(self.device)
         self._scale_dev = torch.from_numpy(self._scale).to(self.device)
+        if self.cfg.complex_modulation:
+            self._init_complex(prm)
+
+    def _init_complex(self, prm):
+        """Filterbank of the complex path: createFbank(nfilters, int(fduration*srate), ...)[:, :-1] (:45-48, :162); its
+        taps above tail_eps * max are the bands' supports."""
+        N = self.geom["N"]
+        if N % 2 or self.cfg.order + 2 > N // 2:
+            raise ValueError("--complex_modulation needs an even int(fduration*srate) and order <= it/2 - 2")
+        full = np.empty((self.cfg.nfilters, N // 2 + 1), dtype=np.float64)
+        args = np.array([prm.fbank_args[i] for i in range(5)], dtype=np.float64)
+        L.check(self._lib.fdlp_make_fbank(prm.fbank_kind, args.ctypes.data_as(C.c_void_p), self.cfg.nfilters, N,
+                                          self.cfg.srate, full.ctypes.data_as(C.c_void_p)))
+        fb = np.ascontiguousarray(full[:, :-1])
+        keep = np.abs(fb) > self.cfg.tail_eps * np.abs(fb).max(axis=1, keepdims=True)
+        if not keep.any(axis=1).all():
+            raise ValueError("a band of the filterbank is empty")
+        lo = keep.argmax(axis=1).astype(np.int32)
+        hi = (keep.shape[1] - keep[:, ::-1].argmax(axis=1)).astype(np.int32)
+        self._cfb = torch.from_numpy(fb).to(self.device)
+        self._clo, self._chi = torch.from_numpy(lo).to(self.device), torch.from_numpy(hi).to(self.device)
+        self._cwidth = int((hi - lo).max())
 
     def close(self):
         if getattr(self, "_plan", None) and self._plan.value:
@@ -144,6 +179,22 @@ class ModSpecExtractor:
         b.noise_mode = L.FDLP_NOISE_NONE
         b.status = status.data_ptr()
         stream = torch.cuda.current_stream(self.device).cuda_stream
+        if self.cfg.complex_modulation:
+            N = self.geom["N"]
+            frames = torch.empty((lay.n_seg, N), dtype=torch.float64, device=self.device)
+            with torch.cuda.device(self.device):
+                L.check(self._lib.fdlp_stage_frames(self._plan, C.byref(b), C.c_void_p(frames.data_ptr()), C.c_void_p(stream)))
+                # ifft of a real frame: conj(rfft) / N; bins 0 .. N/2-1 (computeModulationSpectrum.py:150-151)
+                spec = torch.fft.rfft(frames, dim=1).conj().resolve_conj()
+                spec.mul_(1.0 / N)
+                L.check(self._lib.fdlp_modspec_complex_forward(
+                    C.c_void_p(spec.data_ptr()), spec.shape[1], lay.n_seg, C.c_void_p(d["seg_utt"].data_ptr()), N // 2,
+                    C.c_void_p(self._cfb.data_ptr()), C.c_void_p(self._clo.data_ptr()), C.c_void_p(self._chi.data_ptr()),
+                    self._cwidth, self.cfg.nfilters, self.cfg.order, self.cfg.coeff_n,
+                    C.c_void_p(self._idx_dev.data_ptr()), C.c_void_p(self._scale_dev.data_ptr()), int(len(self._idx)),
+                    1 if self.cfg.absolute_value else 0, C.c_void_p(out.data_ptr()), C.c_void_p(status.data_ptr()),
+                    C.c_void_p(stream)))
+            return out, status
         with torch.cuda.device(self.device):
             L.check(self._lib.fdlp_modspec_forward(self._plan, C.byref(b), C.c_void_p(self._idx_dev.data_ptr()),
                                                    C.c_void_p(self._scale_dev.data_ptr()), self.feat_len,
@@ -180,7 +231,10 @@ class ModSpecExtractor:
             feats, st = self.forward_packed(wav_dev, lay)
             if unity_gain and 0 in self._idx:
                 pos = int(np.flatnonzero(self._idx == 0)[0])
-                feats.view(lay.n_seg, self.cfg.nfilters, self.feat_len)[:, :, pos] = 0.0
+                v = feats.view(lay.n_seg, self.cfg.nfilters, self.feat_len)
+                v[:, :, pos] = 0.0
+                if self.cfg.complex_modulation and not self.cfg.absolute_value:
+                    v[:, :, len(self._idx) + pos] = 0.0
             outs.extend(feats[int(lay.utt_seg_off[u]):int(lay.utt_seg_off[u + 1])] for u in range(lay.n_utt))
             sts.append(st[:lay.n_utt])
             i = j

@@ -53,7 +53,25 @@ def case(name, params, spec):
     print("%-28s out=%s min=%.5f max=%.5f" % (name, out.shape, np.nanmin(out), np.nanmax(out)))
 
 
+def complex_cases():
+    """--complex_modulation: ifft frames, complex Hermitian LPC, complex cepstrum (computeModulationSpectrum.py:150-151,
+    :164-173).  keep_even without --absolute_value is not here: the reference sizes each_feat from coeff_num but fills
+    it with 2*coeff_num values there and stops with a ValueError."""
+    case("modspec_complex_default", dict(complex_modulation=True), dict(kind="white", seed=34, utt=4, T=6400))
+    case("modspec_complex_abs_comp", dict(complex_modulation=True, compensate_noise=True, absolute_value=True, coeff_0=1,
+                                          coeff_n=20, nfilters=8), dict(kind="white", seed=35, utt=5, T=3000))
+    case("modspec_complex_cochlear_even", dict(complex_modulation=True, fbank_type="cochlear,0.2,2.5,1,2.5,1", nfilters=10,
+                                               coeff_0=6, coeff_n=25, keep_even=True, absolute_value=True, order=40),
+         dict(kind="speechlike", seed=36, utt=6, T=4001, sigma_f=30.0))
+    case("modspec_complex_square_short", dict(complex_modulation=True, no_window=True, nfilters=6, coeff_0=5, coeff_n=15),
+         dict(kind="white", seed=37, utt=7, T=500))
+    case("modspec_complex_speech_pad", dict(complex_modulation=True, order=20, coeff_0=1, coeff_n=30, fduration=0.25,
+                                            nfilters=12), dict(kind="speechlike", seed=38, utt=8, T=5000, sigma_f=60.0))
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "complex":
+        return complex_cases()
     case("modspec_default_white", {}, dict(kind="white", seed=30, utt=0, T=6400))
     case("modspec_cochlear_even", dict(fbank_type="cochlear,0.2,2.5,1,2.5,1", nfilters=10, coeff_0=6, coeff_n=25,
                                        keep_even=True, order=40),
@@ -62,6 +80,7 @@ def main():
          dict(kind="white", seed=32, utt=2, T=3000))
     case("modspec_square_window_short", dict(no_window=True, nfilters=6, coeff_0=5, coeff_n=15, keep_even=True),
          dict(kind="white", seed=33, utt=3, T=500))
+    complex_cases()
 
 
 if __name__ == "__main__":

@@ -262,3 +262,25 @@ def test_vectorised_batch_layout_equals_the_per_segment_loop(fdur):
                         batch_layout([T], g, 100, 16000, jitter=[seed])
                 else:
                     batch_layout([T], g, 100, 16000, jitter=[seed])
+
+
+def test_make_fbank_entry_point_matches_reference_fixtures():
+    """fdlp_make_fbank (host only, no device work): createFbank / createFbankCochlear values of the unmodified
+    reference (tests/golden/fbanks.npz, written by tests/golden/make_golden.py)."""
+    import ctypes as C
+    lib = _lib.load()
+    z = np.load(os.path.join(ROOT, "tests", "golden", "fbanks.npz"))
+
+    def build(kind, args, J, nfft):
+        out = np.empty((J, nfft // 2 + 1), dtype=np.float64)
+        a = np.array(list(args) + [0.0] * (5 - len(args)), dtype=np.float64)
+        assert lib.fdlp_make_fbank(kind, a.ctypes.data_as(C.c_void_p), J, nfft, 16000, out.ctypes.data_as(C.c_void_p)) == 0
+        return out
+    mel = build(_lib.FDLP_FBANK_MEL, [1.0], 20, 16000)
+    np.testing.assert_allclose(mel[:, ::53], z["mel20_16000"], rtol=0, atol=1e-15)
+    np.testing.assert_allclose(build(_lib.FDLP_FBANK_MEL, [1.0], 80, 2048), z["mel80_2048"], rtol=0, atol=1e-15)
+    coch = build(_lib.FDLP_FBANK_COCHLEAR, [1.0, 1.0, 1, 2.5, 1.0], 80, 48000)
+    np.testing.assert_allclose(coch[:, ::53], z["coch80_48000"], rtol=1e-12, atol=0)
+    nf = build(_lib.FDLP_FBANK_COCHLEAR, [0.2, 2.5, 0, 2.5, 1.3], 12, 4000)
+    np.testing.assert_allclose(nf, z["coch12_4000_nonfixed"], rtol=1e-12, atol=0)
+    assert lib.fdlp_make_fbank(7, np.zeros(5).ctypes.data_as(C.c_void_p), 4, 64, 16000, nf.ctypes.data_as(C.c_void_p)) == _lib.FDLP_E_ARG

@@ -102,3 +102,48 @@ def test_modspec_segments_cli_matches_reference_golden(name, tmp_path, monkeypat
     for seg_id in ark:
         assert ark[seg_id].shape == z[seg_id].shape
         np.testing.assert_allclose(ark[seg_id], z[seg_id], rtol=2e-6, atol=2e-6)
+
+
+def test_modspec_complex_batch_equals_single_and_oracle(tmp_path):
+    """--complex_modulation on a ragged batch (one utterance shorter than a frame; int16 and float32 input; dense
+    cochlear bands / mel bands with exact zeros): batch == single bit for bit, == oracle/modspec.py; then the
+    same through the CLI shim."""
+    from oracle import modspec as omod
+    from speech_recognition_tools_b200 import synth
+    from speech_recognition_tools_b200.modspec import ModSpecConfig, ModSpecExtractor
+    for kw in (dict(nfilters=9, coeff_0=2, coeff_n=24, order=36, fbank_type="cochlear,0.2,2.5,1,2.5,1", fduration=0.25),
+               dict(nfilters=7, coeff_0=1, coeff_n=12, order=16, fbank_type="mel,1", absolute_value=True,
+                    compensate_noise=True, fduration=0.1)):
+        ex = ModSpecExtractor(ModSpecConfig(complex_modulation=True, **kw), device="cuda:0")
+        wavs = [synth.make_utterance("white" if i % 2 else "speechlike", 17, i, T, 40.0) for i, T in enumerate([900, 2500, 5001])]
+        if "absolute_value" in kw:   # float32 input in the second configuration (a batch has one sample type)
+            wavs = [w.astype(np.float32) for w in wavs]
+        outs, st = ex(wavs, return_status=True)
+        assert not st.cpu().numpy().any()
+        split = ex(wavs, max_segments=10)
+        for w, o, s in zip(wavs, outs, split):
+            assert torch.equal(ex([w])[0], o) and torch.equal(s, o)
+            ref = omod.modulation_spectrum_complex(w, **kw)
+            assert o.shape == ref.shape
+            np.testing.assert_allclose(o.cpu().numpy(), ref, rtol=2e-6, atol=2e-6)
+        ex.close()
+
+
+def test_modspec_complex_cli_matches_golden(tmp_path):
+    from scipy.io import wavfile
+    from speech_recognition_tools_b200.cli import computeModulationSpectrum as cli
+    from speech_recognition_tools_b200.kaldi_io import read_ark
+    c = load_case("modspec_complex_speech_pad")
+    wav = tmp_path / "u.wav"
+    wavfile.write(str(wav), 16000, c["x"])
+    scp = tmp_path / "wav.scp"
+    scp.write_text("utt1 %s\n" % wav)
+    p = c["meta"]["params"]
+    argv = [str(scp), str(tmp_path / "out"), "--complex_modulation", "--order", str(p["order"]), "--coeff_0", str(p["coeff_0"]),
+            "--coeff_n", str(p["coeff_n"]), "--fduration", str(p["fduration"]), "--nfilters", str(p["nfilters"])]
+    cli.getFeats(cli.get_args(argv))
+    got = dict(read_ark(str(tmp_path / "out.ark")))["utt1"]
+    assert got.shape == c["feats"].shape
+    np.testing.assert_allclose(got, c["feats"], rtol=2e-6, atol=2e-6)
+    with pytest.raises(ValueError):
+        cli.getFeats(cli.get_args(argv + ["--keep_even"]))

@@ -122,10 +122,29 @@ def test_modspec_oracle_matches_reference(name):
     p = dict(c["meta"]["params"])
     p.pop("add_reverb", None)
     x = c["x"] if c["rir"] is None else oreverb.add_reverb(c["x"], c["rir"])  # computeModulationSpectrum.py:146-148
-    got = omod.modulation_spectrum(x, **p)
+    if p.pop("complex_modulation", False):
+        got = omod.modulation_spectrum_complex(x, **p)  # :150-152, :164-173
+    else:
+        got = omod.modulation_spectrum(x, **p)
     ref = c["feats"]
     assert got.shape == ref.shape
     np.testing.assert_allclose(got, ref, rtol=1e-6, atol=1e-9)
+
+
+def test_modspec_complex_keep_even_needs_absolute_value():
+    """The reference sizes a band's slot from coeff_num and fills it with 2*coeff_num values when --keep_even meets
+    --complex_modulation without --absolute_value (computeModulationSpectrum.py:64-71 vs :171-185) and stops with a
+    ValueError; the oracle and the host mirror refuse the combination up front."""
+    from oracle import modspec as omod
+    from speech_recognition_tools_b200.modspec import ModSpecConfig, feature_selection
+    with pytest.raises(ValueError):
+        omod.modulation_spectrum_complex(np.zeros(400, dtype=np.int16), keep_even=True)
+    with pytest.raises(ValueError):
+        feature_selection(ModSpecConfig(complex_modulation=True, keep_even=True))
+    idx, scale = feature_selection(ModSpecConfig(complex_modulation=True, keep_even=True, absolute_value=True,
+                                                 compensate_noise=True, coeff_0=6, coeff_n=25))
+    assert list(idx) == list(range(5, 25))[1::2]
+    np.testing.assert_array_equal(scale, np.linspace(0, 20 / 0.5, 25)[idx])
 
 
 @pytest.mark.parametrize("name", golden_cases("mfcc"))
