@@ -50,6 +50,7 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
 
     from speech_recognition_tools_b200 import cmvn as cmvn_mod
     from speech_recognition_tools_b200.cli import pipeline as pl
+    pl.trace("start")
     from speech_recognition_tools_b200.fdlp import batch_layout
     from speech_recognition_tools_b200.kaldi_io import write_cmvn_ark
     if window is not np.hamming:
@@ -92,15 +93,21 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
         return segment_count(T, g["N"], g["S"])
 
     entries = pl.parse_scp(args.scp)
+    pl.trace("scp_parsed")
     mine = pl.shard_entries(entries, world, rank, seg_count, args.scp_type) if world > 1 else entries
     outbase = args.outfile if world == 1 else "%s.%d" % (args.outfile, rank + 1)
     seed_env = os.environ.get("FDLP_JITTER_SEED")
     acc = cmvn_mod.new_accumulator(J, ex.device)
     overlapped = rir is None and noise != "diff"  # samples go to the kernels as they are: copies overlap the compute
 
+    def n_frames(T):  # computeFDLPSpectrogram.py:182; reverberation may change the length by a sample: no reservation then
+        return -(-T * cfg.frate // cfg.srate)
+
     with pl.HostPipeline(mine, args.scp_type, srate, seg_count, MAX_SEGMENTS_PER_BATCH, outbase + ".ark",
-                         outbase + ".scp", singular_bit=_lib.FDLP_ST_SINGULAR, keep=return_feats) as pipe:
+                         outbase + ".scp", singular_bit=_lib.FDLP_ST_SINGULAR, keep=return_feats,
+                         frames_fn=n_frames if overlapped else None, dim=J) as pipe:
         for hb in pipe:
+            pl.trace("m_got")
             n_utt = len(hb.ids)
             jitter = _GlobalRandom() if seed_env is None else [pl.utt_seed(int(seed_env), k) for k in hb.ids]
             nspec = None
@@ -112,6 +119,7 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
             st_host = pipe.status_buffer(hb, n_utt)
             if overlapped:
                 lay = batch_layout(hb.lengths, g, cfg.frate, cfg.srate, jitter)
+                pl.trace("m_layout")
                 nd = ex._noise_to_device(nspec, lay) if nspec is not None else None
                 feats_host = pipe.feats_buffer(hb, lay.n_frames, J)
                 status = torch.zeros(n_utt, dtype=torch.int32, device=ex.device)
@@ -131,7 +139,9 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
             done = torch.cuda.Event()
             done.record(torch.cuda.current_stream(ex.device))
             pipe.submit(hb, done, feats_host, frame_off, st_host)
+            pl.trace("m_submitted")
     all_lens, bad, kept = pipe.lens, pipe.bad, pipe.kept
+    pl.trace("pipe_closed")
     if os.environ.get("FDLP_CLI_TRACE"):
         print("%s: stage seconds %s" % (sys.argv[0], {k: round(v, 4) for k, v in pipe.timings().items()}), file=sys.stderr)
     if args.write_utt2num_frames:
@@ -145,6 +155,9 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
     if (world > 1 and rank == 0) or (world == 1 and os.environ.get("FDLP_WRITE_CMVN")):
         # Kaldi's documented stats layout; parity unpinned -- Kaldi is not on this box
         write_cmvn_ark(acc.cpu().numpy(), args.outfile + ".cmvn.ark")
+    pl.trace("done")
+    if os.environ.get("FDLP_CLI_TRACE"):
+        pl.dump_trace(sys.argv[0])
     if bad:
         # the reference raises numpy.linalg.LinAlgError('Singular principal minor') at the first such utterance; here
         # the shard is complete on disk (the singular bands are NaN) and the error names the utterances

@@ -31,7 +31,27 @@ from typing import List, Optional
 import numpy as np
 import torch
 
-N_IO_THREADS = max(2, min(16, (os.cpu_count() or 4)))
+from ..fdlp import host_threads
+
+N_IO_THREADS = host_threads(16)
+
+_TRACE: list = []
+
+
+def trace(name: str) -> None:
+    """FDLP_CLI_TRACE=1: (seconds, thread, event) marks of one run, printed by the shim at the end."""
+    if os.environ.get("FDLP_CLI_TRACE"):
+        import time
+        _TRACE.append((time.perf_counter(), threading.current_thread().name, name))
+
+
+def dump_trace(prog: str) -> None:
+    if not _TRACE:
+        return
+    t0 = _TRACE[0][0]
+    print("%s: trace (ms) %s" % (prog, " | ".join("%.1f %s %s" % ((t - t0) * 1e3, th[:6], n) for t, th, n in _TRACE)),
+          file=sys.stderr)
+    del _TRACE[:]
 
 
 def parse_scp(scp_path: str):
@@ -158,7 +178,7 @@ class BatchReader(threading.Thread):
     `None` ends the stream; an exception instance is passed through for the consumer to raise."""
 
     def __init__(self, entries, scp_type, srate, seg_count_fn, max_segments, bufsets, free_q, out_q, pool,
-                 prog=None, announce=True):
+                 prog=None, announce=True, reserve=None):
         super().__init__(daemon=True)
         if scp_type not in ("wav", "segment"):  # computeFDLPSpectrogram.py:153-154
             raise ValueError("Invalid type of scp type, it should be either wav or segment")
@@ -167,6 +187,7 @@ class BatchReader(threading.Thread):
         self.bufsets, self.free_q, self.out_q, self.pool = bufsets, free_q, out_q, pool
         self.prog = prog or sys.argv[0]
         self.announce = announce
+        self.reserve = reserve  # f(items) -> None: the writer reserves the batch's place in the ark (runs beside the reads)
         self.stop = threading.Event()
         self.t_probe = self.t_read = self.t_wait = 0.0  # seconds in header probes / sample reads / waiting for a buffer set
 
@@ -196,6 +217,7 @@ class BatchReader(threading.Thread):
         t0 = time.perf_counter()
         bs = self.free_q.get()
         t1 = time.perf_counter()
+        trace("read_begin")
         self.t_wait += t1 - t0
         total = sum(it.n for it in items)
         wav = self.bufsets[bs].get_wav(total, items[0].dtype)
@@ -223,7 +245,11 @@ class BatchReader(threading.Thread):
                     os.close(fd)
 
         step = max(8, (len(items) + 4 * N_IO_THREADS - 1) // (4 * N_IO_THREADS))
+        res = self.pool.submit(self.reserve, items) if self.reserve is not None else None
         list(self.pool.map(lambda lo: fill(lo, min(lo + step, len(items))), range(0, len(items), step)))
+        if res is not None:
+            res.result()
+        trace("read_end")
         self.t_read += time.perf_counter() - t1
         if self.announce:  # computeFDLPSpectrogram.py:126, one line per utterance
             sys.stdout.write("".join("%s: Computing Features for file: %s\n" % (self.prog, it.uttid) for it in items))
@@ -281,11 +307,14 @@ class BatchWriter(threading.Thread):
                 if self.error is None:
                     import time
                     t0 = time.perf_counter()
+                    trace("w_wait")
                     if event is not None:
                         event.synchronize()
                     t1 = time.perf_counter()
+                    trace("w_synced")
                     mat = feats.numpy() if isinstance(feats, torch.Tensor) else feats
                     self.w.write_batch(ids, mat, frame_off)
+                    trace("w_written")
                     self.t_sync += t1 - t0
                     self.t_write += time.perf_counter() - t1
                     if self.kept is not None:
@@ -332,7 +361,9 @@ class HostPipeline:
     """
 
     def __init__(self, entries, scp_type, srate, seg_count_fn, max_segments, ark_path, scp_path, n_bufsets=3,
-                 prog=None, scp_ark_name=None, announce=True, singular_bit=1, keep=False):
+                 prog=None, scp_ark_name=None, announce=True, singular_bit=1, keep=False, frames_fn=None, dim=0):
+        """`frames_fn(n_samples) -> n_frames` and `dim`, when the caller knows them before extraction, let the reader
+        reserve a batch's pages in the ark while it reads the batch (ArkWriter.prealloc)."""
         from ..kaldi_io import ArkWriter
         self.pool = _shared_pool()
         while len(_BUFSETS) < n_bufsets:  # pinned staging memory is kept for the life of the process: pinning
@@ -342,10 +373,14 @@ class HostPipeline:
         for i in range(n_bufsets):
             self.free_q.put(i)
         self.q = queue.Queue()
+        ark = ArkWriter(ark_path, scp_path, pool=self.pool, threads=N_IO_THREADS, scp_ark_name=scp_ark_name)
+        reserve = None
+        if frames_fn is not None and dim > 0:
+            def reserve(items):
+                ark.prealloc(sum(ArkWriter.entry_bytes(it.uttid, int(frames_fn(it.n)), dim) for it in items))
         self.reader = BatchReader(entries, scp_type, srate, seg_count_fn, max_segments, self.bufsets, self.free_q, self.q,
-                                  self.pool, prog, announce)
-        self.writer = BatchWriter(ArkWriter(ark_path, scp_path, pool=self.pool, threads=N_IO_THREADS,
-                                            scp_ark_name=scp_ark_name), self.free_q, singular_bit, keep)
+                                  self.pool, prog, announce, reserve)
+        self.writer = BatchWriter(ark, self.free_q, singular_bit, keep)
 
     def __enter__(self):
         self.reader.start()

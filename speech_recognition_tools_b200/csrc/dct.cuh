@@ -305,8 +305,11 @@ __device__ __forceinline__ double fetch_sample(const DctArgs& a, const S* sig, i
   return v;
 }
 
+#ifndef FDLP_DCT_MAXT
+#define FDLP_DCT_MAXT 512
+#endif
 template <typename T, typename S>
-__global__ void __launch_bounds__(512) dct_segments_kernel(const DctArgs a) {
+__global__ void __launch_bounds__(FDLP_DCT_MAXT) dct_segments_kernel(const DctArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* sv = reinterpret_cast<T*>(smem_raw);  // v[] (real view) == z[] (complex view)
   cplx<T>* z = reinterpret_cast<cplx<T>*>(smem_raw);

@@ -399,6 +399,19 @@ def noise_to_device(noise: Optional["NoiseSpec"], lengths, device):
 
 
 # --------------------------------------------------------------------------- extractor
+def host_threads(cap: int) -> int:
+    """Worker threads of the host-side copy stages: the cores this process may use, shared between the ranks torchrun
+    started on this node (LOCAL_WORLD_SIZE), at least 2, at most `cap`.  On the 8-GPU boxes of this pool (32 vCPUs) that
+    is 4 per rank: more threads than cores only delays the thread that drives the GPU."""
+    import os
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 4
+    ranks = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1") or 1))
+    return max(2, min(cap, cores // ranks))
+
+
 class FdlpExtractor:
     """One plan (filterbank, twiddles, scratch) on one device; call it with a list of waveforms."""
 
@@ -627,13 +640,16 @@ class FdlpExtractor:
 
     def extract_list(self, wavs: Sequence[np.ndarray], jitter=None, feats_host: Optional[torch.Tensor] = None,
                      cmvn: Optional[torch.Tensor] = None, status: Optional[torch.Tensor] = None, n_chunks: int = 6,
-                     wav_dev: Optional[torch.Tensor] = None, feats: Optional[torch.Tensor] = None, threads: int = 8):
+                     wav_dev: Optional[torch.Tensor] = None, feats: Optional[torch.Tensor] = None,
+                     threads: Optional[int] = None):
         """The whole host side of one batch: a list of (unpinned) int16 / float32 numpy waveforms in, pinned-host
         features out.  Layout (segment / frame tables, jitter draws) first -- it needs the lengths only -- then the
         utterances are packed into a grow-only pinned staging buffer chunk by chunk, by `threads` workers (numpy
         copies release the GIL), each chunk right before its upload, so packing overlaps the device work of the
         chunks before it.  Returns (lay, feats_dev, feats_host, status)."""
         from concurrent.futures import ThreadPoolExecutor
+        if threads is None:
+            threads = host_threads(8)
         wavs = [np.ascontiguousarray(w) for w in wavs]
         dt = wavs[0].dtype
         if dt not in (np.int16, np.float32) or any(w.dtype != dt or w.ndim != 1 for w in wavs):

@@ -33,12 +33,30 @@ def write_ark_scp(feats: Iterable[Tuple[str, np.ndarray]], ark_path: str, scp_pa
             scp.write("%s %s:%d\n" % (key, ark_path, off))
 
 
+def _linux_fallocate():
+    """fallocate(2) through ctypes (the call releases the GIL): returns f(fd, offset, length) -> bool, or None.
+    posix_fallocate is not used because glibc emulates it by writing zeros where the filesystem has no support."""
+    import ctypes
+    import ctypes.util
+    try:
+        libc = ctypes.CDLL(ctypes.util.find_library("c") or "libc.so.6", use_errno=True)
+        fn = libc.fallocate
+    except (OSError, AttributeError):
+        return None
+    fn.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int64, ctypes.c_int64]
+    fn.restype = ctypes.c_int
+    return lambda fd, off, n: fn(fd, 0, off, n) == 0
+
+
 class ArkWriter:
     """Incremental ark/scp writer: one `write_batch` per extracted batch, so memory stays bounded and the output
     written so far survives a later failure (the reference builds the whole dict and writes at the end,
     computeFDLPSpectrogram.py:228-230).  A batch is a float32 [n_frames, dim] matrix holding the utterances back to
     back; with a thread pool the batch is copied into a shared mapping of the grown file by `threads` workers (numpy
-    copies release the GIL), else it goes out through os.pwritev."""
+    copies release the GIL), else it goes out through os.pwritev.  `prealloc(nbytes)` (any thread, ahead of the
+    batches) backs the next `nbytes` of the file with pages: on tmpfs two thirds of a fresh mapping's copy time is the
+    kernel allocating and clearing pages one fault at a time (272 MB: 45 ms, against 17 ms for one fallocate call plus
+    22 ms for the copy, tools/tmpfs_write_probe.py), and the reader thread knows a batch's size before it is computed."""
 
     def __init__(self, ark_path: str, scp_path: str, pool=None, threads: int = 4, scp_ark_name: str = None):
         import os
@@ -47,6 +65,26 @@ class ArkWriter:
         self._scp = open(scp_path, "w")
         self._pos = 0
         self._pool, self._threads = pool, max(1, threads)
+        import threading
+        self._lock = threading.Lock()   # file size changes: fallocate (prealloc) and ftruncate (write_batch, close)
+        self._size = 0                  # current file size
+        self._falloc = _linux_fallocate()
+
+    @staticmethod
+    def entry_bytes(key: str, n_frames: int, dim: int) -> int:
+        """Bytes of one ark entry: key, space, '\\0B', 'FM ', two int32 with their size bytes, the matrix."""
+        return len(key.encode("utf-8")) + 1 + 15 + n_frames * dim * 4
+
+    def prealloc(self, nbytes: int) -> None:
+        """Reserve pages for the next `nbytes` beyond what is reserved so far (a hint: sizes need not be exact, the
+        file is cut to its real length on close).  No-op where fallocate is not supported."""
+        if self._falloc is None or nbytes <= 0 or self._fd is None:
+            return
+        with self._lock:
+            if self._falloc(self._fd, self._size, nbytes):
+                self._size += nbytes
+            else:
+                self._falloc = None
 
     def write_batch(self, keys, mat: np.ndarray, frame_off) -> None:
         import os
@@ -71,7 +109,11 @@ class ArkWriter:
             import mmap
             gran = mmap.ALLOCATIONGRANULARITY
             base = self._pos // gran * gran
-            os.ftruncate(self._fd, pos)
+            if pos > self._size:
+                with self._lock:
+                    if pos > self._size:
+                        os.ftruncate(self._fd, pos)
+                        self._size = pos
             mm = mmap.mmap(self._fd, pos - base, access=mmap.ACCESS_WRITE, offset=base)
             try:
                 dst = np.frombuffer(mm, dtype=np.uint8)
@@ -96,14 +138,19 @@ class ArkWriter:
                     if done < want:
                         joined = bytes(hdr) + bytes(body)
                         iov = [memoryview(joined)[done:]]
+            with self._lock:
+                self._size = max(self._size, pos)
         self._pos = pos
         self._scp.write("".join(lines))
 
     def close(self) -> None:
         import os
         if self._fd is not None:
-            os.close(self._fd)
-            self._fd = None
+            with self._lock:
+                if self._size != self._pos:
+                    os.ftruncate(self._fd, self._pos)  # reserved beyond what was written
+                os.close(self._fd)
+                self._fd = None
             self._scp.close()
 
     def __enter__(self):

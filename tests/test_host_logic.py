@@ -284,3 +284,32 @@ def test_make_fbank_entry_point_matches_reference_fixtures():
     nf = build(_lib.FDLP_FBANK_COCHLEAR, [0.2, 2.5, 0, 2.5, 1.3], 12, 4000)
     np.testing.assert_allclose(nf, z["coch12_4000_nonfixed"], rtol=1e-12, atol=0)
     assert lib.fdlp_make_fbank(7, np.zeros(5).ctypes.data_as(C.c_void_p), 4, 64, 16000, nf.ctypes.data_as(C.c_void_p)) == _lib.FDLP_E_ARG
+
+
+def test_ark_writer_prealloc_is_only_a_hint(tmp_path):
+    """ArkWriter.prealloc reserves pages ahead of the batches (fallocate); too much, too little or none at all must give
+    the same bytes, and the file ends at its real length."""
+    from concurrent.futures import ThreadPoolExecutor
+    from speech_recognition_tools_b200.kaldi_io import ArkWriter, read_ark
+    rng = np.random.default_rng(5)
+    frames = [int(v) for v in rng.integers(1, 400, 40)]
+    off = np.concatenate([[0], np.cumsum(frames)])
+    mat = rng.standard_normal((int(off[-1]), 7)).astype(np.float32)
+    keys = ["utt%03d" % i for i in range(40)]
+    exact = sum(ArkWriter.entry_bytes(k, f, 7) for k, f in zip(keys, frames))
+    blobs = {}
+    with ThreadPoolExecutor(4) as pool:
+        for name, hint in (("none", 0), ("exact", exact), ("short", exact // 3), ("long", 2 * exact + 12345)):
+            ark, scp = str(tmp_path / (name + ".ark")), str(tmp_path / (name + ".scp"))
+            w = ArkWriter(ark, scp, pool=pool, threads=4, scp_ark_name="x.ark")
+            w.prealloc(hint)
+            w.write_batch(keys[:25], mat[:off[25]], off[:26])
+            w.prealloc(hint // 2)
+            w.write_batch(keys[25:], mat[off[25]:], off[25:] - off[25])   # second batch: small, takes the pwritev path
+            w.close()
+            blobs[name] = (open(ark, "rb").read(), open(scp).read())
+            assert len(blobs[name][0]) == exact
+    assert blobs["exact"] == blobs["none"] == blobs["short"] == blobs["long"]
+    got = read_ark(str(tmp_path / "long.ark"))
+    for i, k in enumerate(keys):
+        np.testing.assert_array_equal(got[k], mat[off[i]:off[i + 1]])

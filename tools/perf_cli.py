@@ -32,7 +32,7 @@ def main():
         argv = [os.path.join(d, "wav.scp"), os.path.join(d, "out"), "--write_utt2num_frames", "--fbank_type=" + W["fbank_type"],
                 "--coeff_num=100", "--coeff_range=0,100", "--order=150", "--nfilters=80", "--fduration=1.5"]
         args = cf.get_parser().parse_args(argv)
-        for max_seg in (8192, 4096, 2048, 1024):
+        for max_seg in (int(a) for a in (sys.argv[2].split(",") if len(sys.argv) > 2 else "8192,4096,2048,1024".split(","))):
             cf.MAX_SEGMENTS_PER_BATCH = max_seg
             for rep in range(3):
                 t0 = time.perf_counter()

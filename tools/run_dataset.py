@@ -12,8 +12,9 @@ Timed region (barrier + synchronize on both sides, max over ranks, device events
 batch of the rank the host layout (overlap-add pointers, offsets), the upload of the index tables, the generation
 kernel, the seven FDLP kernels with the CMVN partial sums, and at the end the CMVN all-reduce.  Features stay on
 the owning rank and are overwritten by the next batch (the reference writes one ark per job; file output is not
-part of this measurement).  Before the timed region rank 0 checks a sample: device-generated samples == numpy
-generator bit for bit, features against the CPU oracle, CMVN sums against a float64 numpy sum.
+part of this measurement).  Before the timed region EVERY rank checks a sample of its own shard: device-generated
+samples == numpy generator bit for bit, features against the CPU oracle, CMVN sums against a float64 numpy sum; rank 0
+gathers the per-rank results into "sample_check" (worst case over the ranks, and the list).
 """
 import argparse
 import json
@@ -47,10 +48,13 @@ def corpus_lengths(hours, seed=5):
     return (d[:keep] * 16000).astype(np.int64)
 
 
-def sample_check(ex, lengths, n_check):
-    """rank 0, untimed: generator bit-exactness, features vs the oracle, CMVN sums vs numpy."""
+def sample_check(ex, lengths, pool, n_check, n_oracle):
+    """Untimed, on every rank: `n_check` utterances spread over `pool` (the rank's shard): generator bit-exactness,
+    CMVN sums vs numpy, and `n_oracle` of them through the CPU oracle."""
     from oracle import fdlp as ofdlp
-    idx = np.linspace(0, len(lengths) - 1, n_check).astype(int)
+    pool = np.sort(np.asarray(pool))
+    n_check = min(n_check, len(pool))
+    idx = pool[np.linspace(0, len(pool) - 1, n_check).astype(int)]
     lens = lengths[idx]
     wav, _ = synth.white_int16_device(SEED, idx, lens, ex.device)
     host = wav.cpu().numpy()
@@ -64,7 +68,7 @@ def sample_check(ex, lengths, n_check):
     foff = lay.utt_frame_off
     fb = ofdlp.make_fbank(WSJ["fbank_type"], WSJ["nfilters"], 2 * ex.geom["N"], 16000)
     worst = 0.0
-    for i in range(0, n_check, max(1, n_check // 6)):  # a handful through the CPU oracle (seconds each)
+    for i in np.linspace(0, n_check - 1, min(n_oracle, n_check)).astype(int):  # a handful through the CPU oracle (seconds each)
         ref = ofdlp.fdlp_spectrogram(host[off[i]:off[i + 1]], fbank=fb, rng=random.Random(int(idx[i])), **WSJ)
         got = f[foff[i]:foff[i + 1]]
         m = ref > np.log(1e-14) + 1e-9
@@ -74,8 +78,9 @@ def sample_check(ex, lengths, n_check):
     ref_stats = np.zeros_like(a)
     ref_stats[0, :-1], ref_stats[0, -1], ref_stats[1, :-1] = f64.sum(0), f64.shape[0], (f64 * f64).sum(0)
     cm_rel = float(np.max(np.abs(a - ref_stats) / np.maximum(np.abs(ref_stats), 1e-300)))
-    return {"utterances": int(n_check), "generator_bit_exact": bool(exact), "features_max_abs_err_vs_oracle": worst,
-            "cmvn_rel_err_vs_float64_numpy": cm_rel, "flagged": int((status != 0).sum().item())}
+    return {"utterances": int(n_check), "through_oracle": int(min(n_oracle, n_check)), "generator_bit_exact": bool(exact),
+            "features_max_abs_err_vs_oracle": worst, "cmvn_rel_err_vs_float64_numpy": cm_rel,
+            "flagged": int((status != 0).sum().item())}
 
 
 def main():
@@ -99,7 +104,20 @@ def main():
     shards = sharding.assign_to_ranks(nsegs, world)
     mine = shards[rank]
     batches = sharding.make_batches(mine, nsegs, args.max_segments)
-    check = sample_check(ex, lengths, args.check) if (rank == 0 and args.check > 0) else None
+    check = None
+    if args.check > 0:
+        mine_check = sample_check(ex, lengths, mine, max(4, args.check // world), max(1, 6 // world))
+        if world > 1:
+            per_rank = [None] * world
+            dist.all_gather_object(per_rank, mine_check)
+        else:
+            per_rank = [mine_check]
+        check = {"utterances": sum(c["utterances"] for c in per_rank),
+                 "through_oracle": sum(c["through_oracle"] for c in per_rank),
+                 "generator_bit_exact": all(c["generator_bit_exact"] for c in per_rank),
+                 "features_max_abs_err_vs_oracle": max(c["features_max_abs_err_vs_oracle"] for c in per_rank),
+                 "cmvn_rel_err_vs_float64_numpy": max(c["cmvn_rel_err_vs_float64_numpy"] for c in per_rank),
+                 "flagged": sum(c["flagged"] for c in per_rank), "per_rank": per_rank}
 
     J = WSJ["nfilters"]
     max_frames = max(int(np.ceil(lengths[b] * 100 / 16000).sum()) for b in batches)
