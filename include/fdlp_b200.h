@@ -255,6 +255,17 @@ int fdlp_modspec_complex_forward(const double* spec /*dev [n_seg, spec_ld] compl
                             const double* sel_scale /*dev [n_sel]*/, int32_t n_sel, int32_t absolute,
                             float* out /*dev [n_seg, nfilters*feat_len]*/, int32_t* status /*dev [n_utt] or NULL*/, void* stream);
 
+/* ---- host-side WAV ingest of the CLI shim (no device work; computeFDLPSpectrogram.py:129-152 reads each file with
+ *      scipy.io.wavfile.read).  fdlp_wav_probe: info[i] = {sample rate, format, byte offset of the samples, number of
+ *      samples}, format 0 = PCM16, 1 = IEEE float32, -1 = not a plain mono RIFF file of those two kinds (or unreadable):
+ *      the caller falls back to the reference's reader.  fdlp_wav_read: nbytes[i] bytes at data_off[i] of file i to
+ *      dst_base + dst_off[i] (pinned staging memory); status[i] = 0, or 1 when the file could not be read in full.
+ *      Both spread the files over `threads` host threads. ---- */
+int fdlp_wav_probe(const char* const* paths, int32_t n, int32_t threads, int64_t* info /*host [n, 4]*/);
+int fdlp_wav_read(const char* const* paths, const int64_t* data_off /*host [n]*/, const int64_t* nbytes /*host [n]*/,
+                  const int64_t* dst_off /*host [n]*/, void* dst_base /*host*/, int32_t n, int32_t threads,
+                  int32_t* status /*host [n]*/);
+
 /* ---- --add_noise diff (computeFDLPSpectrogram.py:162-164): signal = convolve(signal, [1,2,3,2,0,-2,-5,-2,0,2,3,2,1],
  *      mode='same') per utterance; the float32 result (exact for int16 input) is then fed to fdlp_forward ---- */
 int fdlp_diff_filter(const void* wav /*dev, packed*/, int32_t wav_dtype, const int64_t* utt_wav_off /*dev [n_utt+1]*/,

@@ -142,6 +142,8 @@ SYMBOLS = [
     ("fdlp_modspec_complex_forward", C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                           C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    ("fdlp_wav_probe", C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
+    ("fdlp_wav_read", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     ("fdlp_diff_filter", C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]),
     ("fdlp_noise_mix", C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),

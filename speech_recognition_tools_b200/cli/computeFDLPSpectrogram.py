@@ -106,6 +106,7 @@ def getFeats(args, srate=16000, window=np.hamming, return_feats=False):
     with pl.HostPipeline(mine, args.scp_type, srate, seg_count, MAX_SEGMENTS_PER_BATCH, outbase + ".ark",
                          outbase + ".scp", singular_bit=_lib.FDLP_ST_SINGULAR, keep=return_feats,
                          frames_fn=n_frames if overlapped else None, dim=J) as pipe:
+        pl.trace("pipe_open")
         for hb in pipe:
             pl.trace("m_got")
             n_utt = len(hb.ids)

@@ -31,9 +31,13 @@ from typing import List, Optional
 import numpy as np
 import torch
 
+from .. import _lib
 from ..fdlp import host_threads
 
+_WAV_DTYPES = (np.dtype("<i2"), np.dtype("<f4"))  # fdlp_wav_probe formats
+
 N_IO_THREADS = host_threads(16)
+N_RW_THREADS = max(2, N_IO_THREADS // 2)  # the reader's preads and the writer's copies run at the same time
 
 _TRACE: list = []
 
@@ -187,6 +191,7 @@ class BatchReader(threading.Thread):
         self.bufsets, self.free_q, self.out_q, self.pool = bufsets, free_q, out_q, pool
         self.prog = prog or sys.argv[0]
         self.announce = announce
+        self.n_emitted = 0
         self.reserve = reserve  # f(items) -> None: the writer reserves the batch's place in the ark (runs beside the reads)
         self.stop = threading.Event()
         self.t_probe = self.t_read = self.t_wait = 0.0  # seconds in header probes / sample reads / waiting for a buffer set
@@ -212,6 +217,34 @@ class BatchReader(threading.Thread):
             signal = signal.astype(np.float32)
         return _Item(uttid, int(signal.shape[0]), np.dtype(signal.dtype).newbyteorder("<"), array=signal)
 
+    def _opened(self, window=256):
+        """(uttid, _Item or None) in scp order.  The RIFF headers of a window of plain paths are probed in one library
+        call (fdlp_wav_probe, host threads); pipes, segments and files the probe does not take go through `_open`."""
+        import ctypes as C
+        import time
+        lib = _lib.load()
+        for w0 in range(0, len(self.entries), window):
+            tp = time.perf_counter()
+            chunk = self.entries[w0:w0 + window]
+            items = [None] * len(chunk)
+            plain = [k for k, (_, spec) in enumerate(chunk) if self.scp_type == "wav" and spec and spec[-1] != "|"]
+            if plain:
+                paths = (C.c_char_p * len(plain))(*[os.fsencode(chunk[k][1]) for k in plain])
+                info = np.zeros((len(plain), 4), dtype=np.int64)
+                _lib.check(lib.fdlp_wav_probe(paths, len(plain), N_IO_THREADS, info.ctypes.data))
+                for r, k in enumerate(plain):
+                    sr, fmt, off, n = (int(v) for v in info[r])
+                    if fmt >= 0:
+                        assert sr == self.srate, "Input file has different sampling rate."
+                        items[k] = _Item(chunk[k][0], n, _WAV_DTYPES[fmt], path=chunk[k][1], data_off=off)
+            self.t_probe += time.perf_counter() - tp
+            for k, (uttid, spec) in enumerate(chunk):
+                if items[k] is None:
+                    tp = time.perf_counter()
+                    items[k] = self._open(uttid, spec)
+                    self.t_probe += time.perf_counter() - tp
+                yield uttid, items[k]
+
     def _emit(self, items):
         import time
         t0 = time.perf_counter()
@@ -222,31 +255,25 @@ class BatchReader(threading.Thread):
         total = sum(it.n for it in items)
         wav = self.bufsets[bs].get_wav(total, items[0].dtype)
         flat = wav.numpy()
-        raw = memoryview(flat).cast("B")
         isz = flat.dtype.itemsize
         offs = np.concatenate([[0], np.cumsum([it.n for it in items])])
 
-        def fill(lo, hi):
-            for k in range(lo, hi):
-                it = items[k]
-                if it.array is not None:
-                    flat[offs[k]:offs[k + 1]] = it.array
-                    continue
-                fd = os.open(it.path, os.O_RDONLY)
-                try:
-                    want, got = it.n * isz, 0
-                    dst = raw[offs[k] * isz:offs[k + 1] * isz]
-                    while got < want:
-                        n = os.preadv(fd, [dst[got:]], it.data_off + got)
-                        if n <= 0:
-                            raise IOError("%s: file shrank while it was read" % it.path)
-                        got += n
-                finally:
-                    os.close(fd)
-
-        step = max(8, (len(items) + 4 * N_IO_THREADS - 1) // (4 * N_IO_THREADS))
         res = self.pool.submit(self.reserve, items) if self.reserve is not None else None
-        list(self.pool.map(lambda lo: fill(lo, min(lo + step, len(items))), range(0, len(items), step)))
+        for k, it in enumerate(items):  # already decoded (pipes, segments, files the probe did not take)
+            if it.array is not None:
+                flat[offs[k]:offs[k + 1]] = it.array
+        files = [k for k, it in enumerate(items) if it.array is None]
+        if files:  # plain files: pread straight into the pinned buffer, spread over host threads inside the library
+            import ctypes as C
+            paths = (C.c_char_p * len(files))(*[os.fsencode(items[k].path) for k in files])
+            src_off = np.array([items[k].data_off for k in files], dtype=np.int64)
+            nbytes = np.array([items[k].n * isz for k in files], dtype=np.int64)
+            dst_off = np.array([offs[k] * isz for k in files], dtype=np.int64)
+            status = np.zeros(len(files), dtype=np.int32)
+            _lib.check(_lib.load().fdlp_wav_read(paths, src_off.ctypes.data, nbytes.ctypes.data, dst_off.ctypes.data,
+                                                 wav.data_ptr(), len(files), N_RW_THREADS, status.ctypes.data))
+            if status.any():
+                raise IOError("%s: file shrank while it was read" % items[files[int(np.flatnonzero(status)[0])]].path)
         if res is not None:
             res.result()
         trace("read_end")
@@ -254,6 +281,7 @@ class BatchReader(threading.Thread):
         if self.announce:  # computeFDLPSpectrogram.py:126, one line per utterance
             sys.stdout.write("".join("%s: Computing Features for file: %s\n" % (self.prog, it.uttid) for it in items))
             sys.stdout.flush()
+        self.n_emitted += 1
         self.out_q.put(HostBatch(ids=[it.uttid for it in items], lengths=[it.n for it in items], dtype=items[0].dtype,
                                  wav=wav, bufset=bs))
 
@@ -261,19 +289,18 @@ class BatchReader(threading.Thread):
         import time
         try:
             pend, nseg, dtype = [], 0, None
-            for uttid, spec in self.entries:
+            for uttid, it in self._opened():
                 if self.stop.is_set():
                     return
-                tp = time.perf_counter()
-                it = self._open(uttid, spec)
-                self.t_probe += time.perf_counter() - tp
                 if it is None:
                     continue
                 if it.n < 2:
                     print("%s: skipping %s (fewer than 2 samples)" % (self.prog, uttid), file=sys.stderr)
                     continue
                 n = self.seg_count_fn(it.n)
-                if pend and (nseg + n > self.max_segments or it.dtype != dtype):
+                # the first batches are small (a quarter, then half of the budget): the device starts sooner
+                budget = min(self.max_segments, max(256, self.max_segments >> max(0, 2 - self.n_emitted)))
+                if pend and (nseg + n > budget or it.dtype != dtype):
                     self._emit(pend)
                     pend, nseg = [], 0
                 pend.append(it)
@@ -373,7 +400,7 @@ class HostPipeline:
         for i in range(n_bufsets):
             self.free_q.put(i)
         self.q = queue.Queue()
-        ark = ArkWriter(ark_path, scp_path, pool=self.pool, threads=N_IO_THREADS, scp_ark_name=scp_ark_name)
+        ark = ArkWriter(ark_path, scp_path, pool=self.pool, threads=N_RW_THREADS, scp_ark_name=scp_ark_name)
         reserve = None
         if frames_fn is not None and dim > 0:
             def reserve(items):

@@ -20,6 +20,7 @@
 #include "noise.cuh"
 #include "ola.cuh"
 #include "reverb.cuh"
+#include "wav_io.cuh"
 
 namespace fdlp {
 thread_local char g_err[512] = "";
@@ -1738,6 +1739,23 @@ extern "C" int fdlp_modspec_complex_forward(const double* spec, int64_t spec_ld,
   const unsigned blocks = (unsigned)std::min<long long>(a.n_tasks, 148LL * 32);
   modspec_complex_kernel<<<blocks, threads, smem, (cudaStream_t)stream>>>(a);
   FDLP_CUDA(cudaGetLastError());
+  return FDLP_OK;
+}
+
+// ================================================================ host-side WAV ingest (CLI pipeline)
+extern "C" int fdlp_wav_probe(const char* const* paths, int32_t n, int32_t threads, int64_t* info) {
+  if (n < 0 || (n > 0 && (!paths || !info))) return set_err(FDLP_E_ARG, "bad argument%s", "");
+  run_indexed(n, threads, [&](int i) { wav_probe_one(paths[i], info + 4 * (size_t)i); });
+  return FDLP_OK;
+}
+
+extern "C" int fdlp_wav_read(const char* const* paths, const int64_t* data_off, const int64_t* nbytes, const int64_t* dst_off,
+                             void* dst_base, int32_t n, int32_t threads, int32_t* status) {
+  if (n < 0 || (n > 0 && (!paths || !data_off || !nbytes || !dst_off || !dst_base || !status)))
+    return set_err(FDLP_E_ARG, "bad argument%s", "");
+  run_indexed(n, threads, [&](int i) {
+    status[i] = wav_read_one(paths[i], data_off[i], nbytes[i], static_cast<unsigned char*>(dst_base) + dst_off[i]);
+  });
   return FDLP_OK;
 }
 

@@ -33,19 +33,22 @@ def write_ark_scp(feats: Iterable[Tuple[str, np.ndarray]], ark_path: str, scp_pa
             scp.write("%s %s:%d\n" % (key, ark_path, off))
 
 
+_FALLOCATE = []
+
+
 def _linux_fallocate():
     """fallocate(2) through ctypes (the call releases the GIL): returns f(fd, offset, length) -> bool, or None.
     posix_fallocate is not used because glibc emulates it by writing zeros where the filesystem has no support."""
-    import ctypes
-    import ctypes.util
-    try:
-        libc = ctypes.CDLL(ctypes.util.find_library("c") or "libc.so.6", use_errno=True)
-        fn = libc.fallocate
-    except (OSError, AttributeError):
-        return None
-    fn.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int64, ctypes.c_int64]
-    fn.restype = ctypes.c_int
-    return lambda fd, off, n: fn(fd, 0, off, n) == 0
+    if not _FALLOCATE:
+        import ctypes
+        try:
+            fn = ctypes.CDLL(None, use_errno=True).fallocate  # the C library the interpreter is linked against
+            fn.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int64, ctypes.c_int64]
+            fn.restype = ctypes.c_int
+            _FALLOCATE.append(lambda fd, off, n: fn(fd, 0, off, n) == 0)
+        except (OSError, AttributeError):
+            _FALLOCATE.append(None)
+    return _FALLOCATE[0]
 
 
 class ArkWriter:

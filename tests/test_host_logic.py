@@ -313,3 +313,67 @@ def test_ark_writer_prealloc_is_only_a_hint(tmp_path):
     got = read_ark(str(tmp_path / "long.ark"))
     for i, k in enumerate(keys):
         np.testing.assert_array_equal(got[k], mat[off[i]:off[i + 1]])
+
+
+def test_native_wav_probe_and_read_match_scipy_and_the_python_probe(tmp_path):
+    """fdlp_wav_probe / fdlp_wav_read (host-only entry points of the CLI reader): same verdicts as pipeline.probe_wav on
+    PCM16, float32, stereo, a file with a LIST chunk before the data, a truncated file, a non-WAV and a missing file;
+    samples equal scipy.io.wavfile.read."""
+    import ctypes as C
+    import struct
+    from scipy.io import wavfile
+    from speech_recognition_tools_b200.cli import pipeline as pl
+    lib = _lib.load()
+    rng = np.random.default_rng(11)
+    a16 = rng.integers(-3000, 3000, 5000).astype(np.int16)
+    a32 = rng.standard_normal(3001).astype(np.float32)
+    files = {}
+    for name, data in (("pcm16", a16), ("f32", a32), ("stereo", np.stack([a16, a16], axis=1)), ("u8", (a16 // 64 + 128).astype(np.uint8))):
+        files[name] = str(tmp_path / (name + ".wav"))
+        wavfile.write(files[name], 16000, data)
+    raw = open(files["pcm16"], "rb").read()
+    lst = b"LIST" + struct.pack("<I", 10) + b"INFOabcdef"
+    body = raw[12:36] + lst + raw[36:]
+    files["list"] = str(tmp_path / "list.wav")
+    open(files["list"], "wb").write(b"RIFF" + struct.pack("<I", len(body) + 4) + b"WAVE" + body)
+    files["cut"] = str(tmp_path / "cut.wav")
+    open(files["cut"], "wb").write(raw[:44 + 2001])        # data chunk says 10000 bytes, 2001 are there
+    files["text"] = str(tmp_path / "text.wav")
+    open(files["text"], "wb").write(b"not a wav file at all, but longer than forty-four bytes for sure.")
+    files["missing"] = str(tmp_path / "missing.wav")
+    names = list(files)
+    paths = (C.c_char_p * len(names))(*[os.fsencode(files[n]) for n in names])
+    info = np.zeros((len(names), 4), dtype=np.int64)
+    for threads in (1, 4):
+        info[:] = -7
+        assert lib.fdlp_wav_probe(paths, len(names), threads, info.ctypes.data) == 0
+        for r, n in enumerate(names):
+            py = pl.probe_wav(files[n])
+            if py is None:
+                assert info[r, 1] == -1, n
+            else:
+                fmt = 0 if py.dtype == np.dtype("<i2") else 1
+                assert tuple(info[r]) == (py.srate, fmt, py.data_off, py.n_samples), n
+    got = dict(zip(names, info))
+    assert got["pcm16"][3] == 5000 and got["f32"][3] == 3001 and got["list"][3] == 5000 and got["cut"][3] == 1000
+    assert all(got[n][1] == -1 for n in ("stereo", "u8", "text", "missing"))
+    # read the four plain files back to back into one buffer
+    take = ["pcm16", "list", "cut", "f32"]
+    nbytes = np.array([got[n][3] * (4 if n == "f32" else 2) for n in take], dtype=np.int64)
+    dst_off = np.concatenate([[0], np.cumsum(nbytes)[:-1]]).astype(np.int64)
+    src_off = np.array([got[n][2] for n in take], dtype=np.int64)
+    buf = np.zeros(int(nbytes.sum()), dtype=np.uint8)
+    status = np.full(len(take), 9, dtype=np.int32)
+    p2 = (C.c_char_p * len(take))(*[os.fsencode(files[n]) for n in take])
+    assert lib.fdlp_wav_read(p2, src_off.ctypes.data, nbytes.ctypes.data, dst_off.ctypes.data, buf.ctypes.data, len(take), 3,
+                             status.ctypes.data) == 0
+    assert not status.any()
+    np.testing.assert_array_equal(buf[:10000].view(np.int16), a16)
+    np.testing.assert_array_equal(buf[10000:20000].view(np.int16), a16)
+    np.testing.assert_array_equal(buf[20000:22000].view(np.int16), a16[:1000])
+    np.testing.assert_array_equal(buf[22000:].view(np.float32), wavfile.read(files["f32"])[1])
+    # asking for more than the file holds is reported per file
+    nbytes[2] += 64
+    assert lib.fdlp_wav_read(p2, src_off.ctypes.data, nbytes.ctypes.data, dst_off.ctypes.data, buf.ctypes.data, 3, 2,
+                             status.ctypes.data) == 0
+    assert list(status[:3]) == [0, 0, 1]

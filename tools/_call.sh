@@ -1,3 +1,2 @@
 mkdir -p gpurun_out
-timeout 400 python tools/perf_cli.py 1000 2048 > gpurun_out/perf_cli.log 2>&1
-grep -v "Computing Features" gpurun_out/perf_cli.log | tail -12
+timeout 900 python -m pytest tests/test_cli_gpu.py tests/test_fdlp_gpu.py -x -q -m gpu 2>&1 | tail -3

@@ -35,6 +35,9 @@ def main():
         for max_seg in (int(a) for a in (sys.argv[2].split(",") if len(sys.argv) > 2 else "8192,4096,2048,1024".split(","))):
             cf.MAX_SEGMENTS_PER_BATCH = max_seg
             for rep in range(3):
+                for ext in (".ark", ".scp", ".len"):
+                    if os.path.exists(os.path.join(d, "out" + ext)):
+                        os.unlink(os.path.join(d, "out" + ext))
                 t0 = time.perf_counter()
                 with contextlib.redirect_stdout(io.StringIO()):
                     cf.getFeats(args)
