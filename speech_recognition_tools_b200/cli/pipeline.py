@@ -418,6 +418,7 @@ class HostPipeline:
         while True:
             hb = self.q.get()
             if hb is None:
+                self.writer.w.set_threads(N_IO_THREADS)  # the reader is done: its threads go to the writer's copies
                 return
             if isinstance(hb, BaseException):
                 raise hb

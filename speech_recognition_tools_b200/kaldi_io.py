@@ -73,6 +73,9 @@ class ArkWriter:
         self._size = 0                  # current file size
         self._falloc = _linux_fallocate()
 
+    def set_threads(self, threads: int) -> None:
+        self._threads = max(1, threads)
+
     @staticmethod
     def entry_bytes(key: str, n_frames: int, dim: int) -> int:
         """Bytes of one ark entry: key, space, '\\0B', 'FM ', two int32 with their size bytes, the matrix."""

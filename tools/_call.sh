@@ -1,2 +1,3 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_cli_gpu.py tests/test_fdlp_gpu.py -x -q -m gpu 2>&1 | tail -3
+timeout 400 python tools/perf_cli.py 1000 2048,1536,3072 > gpurun_out/perf_cli.log 2>&1
+grep -v "Computing Features" gpurun_out/perf_cli.log | grep "wall" | grep -v "rep=0"
