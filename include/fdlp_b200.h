@@ -356,6 +356,10 @@ typedef struct {
 
 int mfcc_plan_create(const mfcc_params* params, mfcc_plan** out_plan);
 int mfcc_plan_destroy(mfcc_plan* plan);
+/* The 513-point transform of the default configuration (nfft 1024, 320-sample frames, <= 32 bands) runs as a 3xTF32 GEMM
+ * on the tensor cores (tcgen05 / TMA / tensor memory, csrc/mfcc_tc.cuh); other configurations, enable = 0 and
+ * FDLP_MFCC_TC=0 use the FP32-pipe kernel.  Returns 1 if the plan uses the tensor-core kernel after the call, else 0. */
+int mfcc_plan_set_tensor_cores(mfcc_plan* plan, int32_t enable);
 int mfcc_forward(mfcc_plan* plan, const mfcc_batch* batch, void* stream);
 
 /* ---- CMVN apply (ESPnet dump.sh / Kaldi apply-cmvn, e2e/wsj/run_fdlp_e1.sh:293-303) ---- */

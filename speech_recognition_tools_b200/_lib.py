@@ -133,6 +133,7 @@ SYMBOLS = [
     ("mel_forward", C.c_int, [C.c_void_p, C.POINTER(MelBatch), C.c_void_p]),
     ("mfcc_plan_create", C.c_int, [C.POINTER(MfccParams), C.POINTER(C.c_void_p)]),
     ("mfcc_plan_destroy", C.c_int, [C.c_void_p]),
+    ("mfcc_plan_set_tensor_cores", C.c_int, [C.c_void_p, C.c_int32]),
     ("mfcc_forward", C.c_int, [C.c_void_p, C.POINTER(MfccBatch), C.c_void_p]),
     ("cmvn_apply", C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]),
     ("cmvn_accumulate_noalloc", C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
@@ -192,6 +193,13 @@ class FdlpError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__("libfdlp_b200 error %d: %s" % (code, msg))
         self.code = code
+
+
+def check_count(rc):
+    """For entry points that return a non-negative count / flag, or a negative FDLP_E_* code."""
+    if rc < 0:
+        check(rc)
+    return rc
 
 
 def check(rc):

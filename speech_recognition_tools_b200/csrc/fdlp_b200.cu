@@ -16,6 +16,7 @@
 #include "mel.cuh"
 #include "mel_mma.cuh"
 #include "mfcc.cuh"
+#include "mfcc_tc.cuh"
 #include "modspec_cplx.cuh"
 #include "noise.cuh"
 #include "ola.cuh"
@@ -987,8 +988,13 @@ static int launch_lpc(fdlp_plan* p, const double* r, int n_seg, double* lpc_out,
   int lpc_grid = (a.n_tasks + 15) / 16;
   if (grid_cap > 0) lpc_grid = std::min(lpc_grid, grid_cap);
   static const bool force_rot = getenv("FDLP_LPC_ROT") != nullptr;  // the rotation-per-order register kernel (A/B runs)
+  static const bool force_l16 = getenv("FDLP_LPC_L16") != nullptr;  // A/B: 16 lanes per solve for orders below 160
   if (need <= 80 && !force_smem && !force_rot) {
     lpc_cepstrum_blk_kernel<2, 8><<<lpc_grid, 128, 0, st>>>(a);
+  } else if (p->prm.order + 1 <= 160 && force_l16 && !force_smem && !force_rot) {
+    int grid16 = (a.n_tasks + 7) / 8;
+    if (grid_cap > 0) grid16 = std::min(grid16, grid_cap);
+    lpc_cepstrum_blk_kernel<2, 16><<<grid16, 128, 0, st>>>(a);
   } else if (p->prm.order + 1 <= 160 && !force_smem && !force_rot) {
     // any cepstrum length: beyond 160 coefficients the kernel's vectors are circular (REVERB recipe: L = 300)
     lpc_cepstrum_blk_kernel<4, 8><<<lpc_grid, 128, 0, st>>>(a);
@@ -1527,13 +1533,95 @@ struct mfcc_plan {
   double* d_alpha = nullptr;
   int cap_utt = 0;
   size_t smem = 0;
+  // tensor-core path (csrc/mfcc_tc.cuh): nfft = 1024 (513-point transform), 320-sample frames, <= 32 bands
+  bool tc_ok = false;   // the configuration fits the tensor-core kernel and its tables are built
+  bool tc_on = true;    // mfcc_plan_set_tensor_cores / FDLP_MFCC_TC=0
+  float *d_bh = nullptr, *d_bl = nullptr, *d_wT = nullptr, *d_w0 = nullptr;
+  double* d_dctb32 = nullptr;
+  float *d_ah = nullptr, *d_al = nullptr, *d_dc = nullptr;
+  int64_t cap_tc = 0;
+  CUtensorMap tm_bh, tm_bl;
+  int sms = 148;
 };
 
 static void mfcc_free(mfcc_plan* p) {
   if (!p) return;
   cudaFree(p->d_ham); cudaFree(p->d_tw); cudaFree(p->d_weff); cudaFree(p->d_dctb); cudaFree(p->d_frame_utt);
   cudaFree(p->d_tmp); cudaFree(p->d_alpha);
+  cudaFree(p->d_bh); cudaFree(p->d_bl); cudaFree(p->d_wT); cudaFree(p->d_w0); cudaFree(p->d_dctb32);
+  cudaFree(p->d_ah); cudaFree(p->d_al); cudaFree(p->d_dc);
   delete p;
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn tensor_map_encoder() {
+  static EncodeTiledFn fn = []() -> EncodeTiledFn {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    return (EncodeTiledFn)f;
+  }();
+  return fn;
+}
+// float32 matrix [rows, 320] row-major -> boxes of {32 floats, box_rows rows} with the 128-byte swizzle
+static bool mfcc_tmap(CUtensorMap* tm, const float* ptr, uint64_t rows, uint32_t box_rows) {
+  EncodeTiledFn fn = tensor_map_encoder();
+  if (!fn) return false;
+  cuuint64_t dims[2] = {(cuuint64_t)tc::kK, rows};
+  cuuint64_t strides[1] = {(cuuint64_t)tc::kK * sizeof(float)};
+  cuuint32_t box[2] = {(cuuint32_t)tc::kBK, box_rows};
+  cuuint32_t es[2] = {1, 1};
+  return fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// tables of the tensor-core path: B = cos | -sin of bins 1..256 cut into a TF32 part and the remainder, the folded
+// filterbank transposed (bin-major, 32 bands), the DCT basis padded to 32 bands
+static int mfcc_tc_setup(mfcc_plan* p, const std::vector<float>& weff, const std::vector<double>& dctb) {
+  const int J = p->prm.nfilters;
+  if (p->P != 2 * tc::kUnits * tc::kBinsUnit + 1 || p->used != tc::kK || J > tc::kJP) return 0;
+  const int ncol = tc::kUnits * tc::kNUnit;
+  std::vector<float> bh((size_t)ncol * tc::kK), bl((size_t)ncol * tc::kK);
+  for (int col = 0; col < ncol; ++col) {
+    const int u = col / tc::kNUnit, part = (col % tc::kNUnit) / tc::kBinsUnit, i = col % tc::kBinsUnit;
+    const int k = 1 + u * tc::kBinsUnit + i;
+    for (int n = 0; n < tc::kK; ++n) {
+      const double ang = 2.0 * M_PI * (double)(((long long)n * k) % p->P) / (double)p->P;
+      const float v = (float)(part == 0 ? cos(ang) : -sin(ang));
+      uint32_t bits;
+      memcpy(&bits, &v, 4);
+      bits &= 0xffffe000u;
+      float hi;
+      memcpy(&hi, &bits, 4);
+      bh[(size_t)col * tc::kK + n] = hi;
+      bl[(size_t)col * tc::kK + n] = v - hi;
+    }
+  }
+  std::vector<float> wT((size_t)tc::kUnits * tc::kBinsUnit * tc::kJP, 0.f), w0(tc::kJP, 0.f);
+  for (int j = 0; j < J; ++j) {
+    w0[j] = weff[(size_t)j * p->nbp];
+    for (int k = 1; k < p->nb; ++k) wT[(size_t)(k - 1) * tc::kJP + j] = weff[(size_t)j * p->nbp + k];
+  }
+  std::vector<double> d32((size_t)p->prm.ncep * tc::kJP, 0.0);
+  for (int c = 0; c < p->prm.ncep; ++c)
+    for (int j = 0; j < J; ++j) d32[(size_t)c * tc::kJP + j] = dctb[(size_t)c * J + j];
+  int rc;
+  if ((rc = upload(&p->d_bh, bh)) || (rc = upload(&p->d_bl, bl)) || (rc = upload(&p->d_wT, wT)) || (rc = upload(&p->d_w0, w0)) ||
+      (rc = upload(&p->d_dctb32, d32)))
+    return rc;
+  if (!mfcc_tmap(&p->tm_bh, p->d_bh, ncol, tc::kNUnit) || !mfcc_tmap(&p->tm_bl, p->d_bl, ncol, tc::kNUnit)) return 0;
+  if (cudaFuncSetAttribute(tc::mfcc_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemBytes) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  p->tc_ok = true;
+  return 0;
 }
 
 extern "C" int mfcc_plan_create(const mfcc_params* prm, mfcc_plan** out) {
@@ -1588,11 +1676,19 @@ extern "C" int mfcc_plan_create(const mfcc_params* prm, mfcc_plan** out) {
   cudaError_t e = raise_smem_limit(mfcc_frames_kernel<int16_t>, p->smem);
   if (e == cudaSuccess) e = raise_smem_limit(mfcc_frames_kernel<float>, p->smem);
   if (e != cudaSuccess) { mfcc_free(p); return set_err(FDLP_E_CUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
+  cudaDeviceGetAttribute(&p->sms, cudaDevAttrMultiProcessorCount, dev);
+  if ((rc = mfcc_tc_setup(p, weff, dctb))) { mfcc_free(p); return rc; }
   *out = p;
   return FDLP_OK;
 }
 
 extern "C" int mfcc_plan_destroy(mfcc_plan* p) { mfcc_free(p); return FDLP_OK; }
+
+extern "C" int mfcc_plan_set_tensor_cores(mfcc_plan* p, int32_t enable) {
+  if (!p) return set_err(FDLP_E_ARG, "null plan%s", "");
+  p->tc_on = enable != 0;
+  return (p->tc_ok && p->tc_on) ? 1 : 0;
+}
 
 extern "C" int mfcc_forward(mfcc_plan* p, const mfcc_batch* b, void* stream) {
   if (!p || !b) return set_err(FDLP_E_ARG, "null argument%s", "");
@@ -1638,10 +1734,42 @@ extern "C" int mfcc_forward(mfcc_plan* p, const mfcc_batch* b, void* stream) {
   a.noise = b->noise; a.utt_noise_off = b->utt_noise_off; a.utt_alpha = p->d_alpha;
   const long long tiles = (b->n_frames + kMfccFT - 1) / kMfccFT;
   if (tiles > 2147483647LL) return set_err(FDLP_E_ARG, "too many frames in one batch%s", "");
-  const int threads = std::min(288, (p->nb + 31) / 32 * 32);
-  if (b->wav_dtype == FDLP_WAV_INT16) mfcc_frames_kernel<int16_t><<<(unsigned)tiles, threads, p->smem, st>>>(a);
-  else mfcc_frames_kernel<float><<<(unsigned)tiles, threads, p->smem, st>>>(a);
-  FDLP_CUDA(cudaGetLastError());
+  static const bool env_tc = !(getenv("FDLP_MFCC_TC") && atoi(getenv("FDLP_MFCC_TC")) == 0);  // FDLP_MFCC_TC=0: FFMA kernel
+  if (p->tc_ok && p->tc_on && env_tc) {
+    // tensor-core path: frames -> TF32 planes, then the GEMM kernel (csrc/mfcc_tc.cuh)
+    if (b->n_frames > p->cap_tc) {
+      cudaFree(p->d_ah); cudaFree(p->d_al); cudaFree(p->d_dc);
+      p->d_ah = p->d_al = p->d_dc = nullptr; p->cap_tc = 0;
+      FDLP_CUDA(cudaMalloc((void**)&p->d_ah, (size_t)b->n_frames * tc::kK * sizeof(float)));
+      FDLP_CUDA(cudaMalloc((void**)&p->d_al, (size_t)b->n_frames * tc::kK * sizeof(float)));
+      FDLP_CUDA(cudaMalloc((void**)&p->d_dc, (size_t)b->n_frames * sizeof(float)));
+      p->cap_tc = b->n_frames;
+    }
+    tc::PrepArgs pa;
+    pa.wav = b->wav; pa.utt_wav_off = b->utt_wav_off; pa.utt_frame_off = b->utt_frame_off; pa.frame_utt = p->d_frame_utt;
+    pa.n_frames = b->n_frames; pa.flen = p->flen; pa.shift = p->shift; pa.ham = p->d_ham;
+    pa.ah = p->d_ah; pa.al = p->d_al; pa.dc = p->d_dc;
+    pa.noise = b->noise; pa.utt_noise_off = b->utt_noise_off; pa.utt_alpha = p->d_alpha;
+    const unsigned pblocks = (unsigned)((b->n_frames + 7) / 8);
+    if (b->wav_dtype == FDLP_WAV_INT16) tc::mfcc_tc_prep_kernel<int16_t><<<pblocks, 256, 0, st>>>(pa);
+    else tc::mfcc_tc_prep_kernel<float><<<pblocks, 256, 0, st>>>(pa);
+    FDLP_CUDA(cudaGetLastError());
+    CUtensorMap tm_ah, tm_al;
+    if (!mfcc_tmap(&tm_ah, p->d_ah, (uint64_t)b->n_frames, tc::kM) || !mfcc_tmap(&tm_al, p->d_al, (uint64_t)b->n_frames, tc::kM))
+      return set_err(FDLP_E_CUDA, "cuTensorMapEncodeTiled failed%s", "");
+    tc::Args ta;
+    ta.dc = p->d_dc; ta.wT = p->d_wT; ta.w0 = p->d_w0; ta.dctb = p->d_dctb32; ta.feats = a.feats;
+    ta.n_frames = b->n_frames; ta.J = a.J; ta.ncep = a.ncep;
+    ta.n_tiles = (int)((b->n_frames + tc::kM - 1) / tc::kM);
+    const int grid = std::min(ta.n_tiles, p->sms);
+    tc::mfcc_tc_kernel<<<grid, tc::kThreads, tc::kSmemBytes, st>>>(tm_ah, tm_al, p->tm_bh, p->tm_bl, ta);
+    FDLP_CUDA(cudaGetLastError());
+  } else {
+    const int threads = std::min(288, (p->nb + 31) / 32 * 32);
+    if (b->wav_dtype == FDLP_WAV_INT16) mfcc_frames_kernel<int16_t><<<(unsigned)tiles, threads, p->smem, st>>>(a);
+    else mfcc_frames_kernel<float><<<(unsigned)tiles, threads, p->smem, st>>>(a);
+    FDLP_CUDA(cudaGetLastError());
+  }
   if (b->context > 0) {
     SpliceArgs s;
     s.in = p->d_tmp; s.out = b->feats; s.utt_frame_off = b->utt_frame_off; s.frame_utt = p->d_frame_utt;

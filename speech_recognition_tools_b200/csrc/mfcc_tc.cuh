@@ -1,0 +1,324 @@
+// Kc on the 5th-generation tensor cores: the MFCC path's 513-point DFT as a GEMM (tcgen05.mma + TMA + TMEM).
+//
+// Reference: src/featgen/computeMfccFeatures.py:111-131 -- spec = abs(fft(frames, nfft/2 + 1)) is a P = 513 POINT
+// transform of the 320-sample Hamming frame (no power-of-two FFT exists for it), all P bins meet the filterbank, then
+// log10 and the first 13 coefficients of a DCT-II.  csrc/mfcc.cuh evaluates the 257 distinct bins as a direct DFT on
+// the FP32 pipe (280 GFLOP per bench batch, 10.8 ms).  Here the same contraction runs on the tensor cores:
+//
+//   C[F x 512] = A[F x 320] . B[320 x 512]      A = windowed frames / 2^15, B = cos | -sin of bins 1..256
+//
+// in the 3xTF32 scheme (A = Ah + Al, B = Bh + Bl with Ah, Bh the values cut to 10 mantissa bits -- what kind::tf32
+// reads of a 32-bit word -- and C = Ah Bh + Ah Bl + Al Bh accumulated in FP32: the error of an FP32 dot product; one
+// TF32 pass alone misses the 2e-4 tolerance of the cepstra, profiles/mel_gemm_probe_r02.json).  Bin 0 is the sum of
+// the frame and comes from the preparation kernel.
+//
+//   mfcc_tc_prep_kernel  one warp per frame: reflect-padded samples (+ alpha * noise) times the window -> Ah, Al
+//                        rows (float32) and the frame sum
+//   mfcc_tc_kernel       persistent, one CTA per SM, warp roles:
+//                          warp 0    TMA producer: per k-block of 32 samples the 128-frame tiles of Ah / Al and the
+//                                    256-column tiles of Bh / Bl (128-byte swizzle), 2 stages of 96 KB
+//                          warp 1    MMA issuer: one lane issues 3 x tcgen05.mma (M 128, N 256, K 8) per k-step into
+//                                    one of two 256-column accumulators in tensor memory; tcgen05.commit frees the
+//                                    stage and, after the last k-block, hands the accumulator to the epilogue
+//                          warps 2-5 epilogue: thread = frame (TMEM lane); tcgen05.ld 32 columns of re and of im,
+//                                    magnitudes, the folded filterbank (weights broadcast from shared memory) into 32
+//                                    band sums kept in registers over the two halves of the spectrum (unit 0: bins
+//                                    1..128, unit 1: bins 129..256), then bin 0, log10 and the DCT-II in float64
+//                        The accumulator of unit u + 1 fills while the epilogue drains unit u.
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace fdlp {
+namespace tc {
+
+constexpr int kM = 128;                 // frames per tile
+constexpr int kNUnit = 256;             // accumulator columns per unit: 128 bins x (re | im)
+constexpr int kUnits = 2;
+constexpr int kBinsUnit = 128;
+constexpr int kK = 320;                 // samples per frame
+constexpr int kBK = 32;                 // tf32 elements per k-block = one 128-byte swizzle row
+constexpr int kKB = kK / kBK;
+constexpr int kStages = 2;
+constexpr int kATile = kM * 128;        // bytes of one A plane of a stage
+constexpr int kBTile = kNUnit * 128;
+constexpr int kStageBytes = 2 * kATile + 2 * kBTile;
+constexpr int kJP = 32;                 // bands, padded
+constexpr int kThreads = 192;
+constexpr size_t kSmemBytes = 1024 + (size_t)kStages * kStageBytes + (size_t)kUnits * kBinsUnit * kJP * 4 + kJP * 4 + 128;
+
+struct Args {
+  const float* dc;       // [n_frames] frame sums (bin 0)
+  const float* wT;       // [256][32] folded filterbank of bins 1..256, band fastest, zero beyond J
+  const float* w0;       // [32] weights of bin 0
+  const double* dctb;    // [ncep][32] DCT-II basis, zero beyond J
+  float* feats;          // [n_frames, ncep]
+  int64_t n_frames;
+  int J, ncep, n_tiles;
+};
+
+struct PrepArgs {
+  const void* wav;
+  const int64_t* utt_wav_off;
+  const int64_t* utt_frame_off;
+  const int32_t* frame_utt;
+  int64_t n_frames;
+  int flen, shift;
+  const float* ham;              // [320] hamming(flen) / 2^15
+  float* ah;                     // [n_frames, 320]
+  float* al;
+  float* dc;                     // [n_frames]
+  const int16_t* noise;
+  const int64_t* utt_noise_off;
+  const double* utt_alpha;
+};
+
+template <typename S>
+__global__ void __launch_bounds__(256) mfcc_tc_prep_kernel(const PrepArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int64_t fr = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (fr >= a.n_frames) return;
+  const int u = a.frame_utt[fr];
+  const int k = (int)(fr - a.utt_frame_off[u]);
+  const int64_t base = a.utt_wav_off[u];
+  const int64_t T = a.utt_wav_off[u + 1] - base;
+  const int ext = (a.flen % 2 == 0) ? a.flen / 2 - 1 : (a.flen - 1) / 2;  // features.py:137-146
+  const int64_t q0 = (int64_t)k * a.shift - ext;
+  const S* wav = reinterpret_cast<const S*>(a.wav) + base;
+  const int16_t* nz = a.noise ? a.noise + a.utt_noise_off[u] : nullptr;
+  const float alpha = a.noise ? (float)a.utt_alpha[u] : 0.f;
+  float sum = 0.f;
+#pragma unroll
+  for (int t = 0; t < kK / 32; ++t) {
+    const int i = lane + 32 * t;
+    const int64_t q = (T > 1) ? reflect_index(q0 + i, T) : 0;
+    float x = (float)wav[q];
+    if (nz) x = fmaf(alpha, (float)nz[q], x);
+    const float v = x * __ldg(a.ham + i);
+    const float hi = __uint_as_float(__float_as_uint(v) & 0xffffe000u);
+    a.ah[fr * kK + i] = hi;
+    a.al[fr * kK + i] = v - hi;
+    sum += v;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) a.dc[fr] = sum;
+}
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  const long long t0 = clock64();
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (ok) return;
+    if (clock64() - t0 > 8000000000LL) __trap();  // a lost arrival must not hang the device (seconds, never in a correct run)
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int x, int y) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(x), "r"(y)
+      : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+
+// 32 consecutive columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// shared-memory matrix descriptor of a K-major tile with 128-byte rows and the 128-byte swizzle (what the TMA box
+// {32 floats, rows} writes): 8-row groups 1024 bytes apart, descriptor version 1 (sm_100)
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr) {
+  uint64_t d = (uint64_t)((saddr & 0x3ffffu) >> 4);
+  d |= (uint64_t)1 << 16;            // leading byte offset: not used by swizzled K-major layouts
+  d |= (uint64_t)(1024 >> 4) << 32;  // stride byte offset
+  d |= (uint64_t)1 << 46;            // version
+  d |= (uint64_t)2 << 61;            // SWIZZLE_128B
+  return d;
+}
+
+// instruction descriptor: D = F32, A = B = TF32, both K-major, N = 256, M = 128
+constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kNUnit >> 3) << 17) | ((uint32_t)(kM >> 4) << 24);
+
+__global__ void __launch_bounds__(kThreads, 1)
+mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant__ CUtensorMap tm_al,
+               const __grid_constant__ CUtensorMap tm_bh, const __grid_constant__ CUtensorMap tm_bl, const Args a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  float* wT = reinterpret_cast<float*>(base + (size_t)kStages * kStageBytes);  // [256][32]
+  float* w0 = wT + kUnits * kBinsUnit * kJP;                                    // [32]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(w0 + kJP);  // full[2] empty[2] tmem_full[2] tmem_empty[2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  const uint32_t sbase = smem_u32(base);
+  const uint32_t bar0 = smem_u32(bars);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (2 + s); };
+  auto tfull_bar = [&](int u) { return bar0 + 8u * (4 + u); };
+  auto tempty_bar = [&](int u) { return bar0 + 8u * (6 + u); };
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  for (int i = threadIdx.x; i < kUnits * kBinsUnit * kJP + kJP; i += kThreads)
+    wT[i] = (i < kUnits * kBinsUnit * kJP) ? __ldg(a.wT + i) : __ldg(a.w0 + (i - kUnits * kBinsUnit * kJP));
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int u = 0; u < kUnits; ++u) { mbar_init(tfull_bar(u), 1); mbar_init(tempty_bar(u), 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // tensor memory: all 512 columns (one CTA per SM)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x)
+        for (int u = 0; u < kUnits; ++u)
+          for (int kb = 0; kb < kKB; ++kb, ++it) {
+            const int s = it % kStages;
+            const uint32_t ph = (it / kStages) & 1u;
+            mbar_wait(empty_bar(s), ph ^ 1u);
+            const uint32_t dst = sbase + (uint32_t)s * kStageBytes;
+            mbar_expect_tx(full_bar(s), kStageBytes);
+            tma_load_2d(dst, &tm_ah, full_bar(s), kb * kBK, tile * kM);
+            tma_load_2d(dst + kATile, &tm_al, full_bar(s), kb * kBK, tile * kM);
+            tma_load_2d(dst + 2 * kATile, &tm_bh, full_bar(s), kb * kBK, u * kNUnit);
+            tma_load_2d(dst + 2 * kATile + kBTile, &tm_bl, full_bar(s), kb * kBK, u * kNUnit);
+          }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    uint32_t it = 0, tile_it = 0;
+    for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tile_it)
+      for (int u = 0; u < kUnits; ++u) {
+        mbar_wait(tempty_bar(u), (tile_it & 1u) ^ 1u);  // the epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)u * kNUnit;
+        for (int kb = 0; kb < kKB; ++kb, ++it) {
+          const int s = it % kStages;
+          mbar_wait(full_bar(s), (it / kStages) & 1u);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint32_t st = sbase + (uint32_t)s * kStageBytes;
+            const uint64_t dah = smem_desc(st), dal = smem_desc(st + kATile);
+            const uint64_t dbh = smem_desc(st + 2 * kATile), dbl = smem_desc(st + 2 * kATile + kBTile);
+#pragma unroll
+            for (int ks = 0; ks < kBK / 8; ++ks) {
+              const uint64_t o = (uint64_t)(ks * 32 >> 4);  // 8 tf32 = 32 bytes along the swizzled row
+              umma_tf32(d_tmem, dah + o, dbh + o, kIdesc, (kb | ks) ? 1u : 0u);
+              umma_tf32(d_tmem, dah + o, dbl + o, kIdesc, 1u);
+              umma_tf32(d_tmem, dal + o, dbh + o, kIdesc, 1u);
+            }
+            umma_commit(empty_bar(s));                      // the stage is free once these MMAs have read it
+            if (kb == kKB - 1) umma_commit(tfull_bar(u));   // and the accumulator is complete
+          }
+          __syncwarp();
+        }
+      }
+  } else {
+    // ================= epilogue: thread = frame =================
+    const int quarter = warp & 3;  // the TMEM lanes a warp may read: 32 * (warp id % 4)
+    const int row = quarter * 32 + lane;
+    uint32_t tile_it = 0;
+    for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tile_it) {
+      float band[kJP];
+#pragma unroll
+      for (int j = 0; j < kJP; ++j) band[j] = 0.f;
+      for (int u = 0; u < kUnits; ++u) {
+        mbar_wait(tfull_bar(u), tile_it & 1u);
+        tc_fence_after();
+        const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)u * kNUnit;
+        for (int c = 0; c < kBinsUnit / 32; ++c) {
+          uint32_t re[32], im[32];
+          tmem_ld32(t0 + c * 32, re);
+          tmem_ld32(t0 + kBinsUnit + c * 32, im);
+          tmem_ld_wait();
+          const float4* wrow = reinterpret_cast<const float4*>(wT + (size_t)(u * kBinsUnit + c * 32) * kJP);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const float xr = __uint_as_float(re[i]), xi = __uint_as_float(im[i]);
+            const float mag = sqrtf(fmaf(xr, xr, xi * xi));
+#pragma unroll
+            for (int q = 0; q < kJP / 4; ++q) {
+              const float4 w = wrow[i * (kJP / 4) + q];
+              band[4 * q + 0] = fmaf(w.x, mag, band[4 * q + 0]);
+              band[4 * q + 1] = fmaf(w.y, mag, band[4 * q + 1]);
+              band[4 * q + 2] = fmaf(w.z, mag, band[4 * q + 2]);
+              band[4 * q + 3] = fmaf(w.w, mag, band[4 * q + 3]);
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(u));
+      }
+      const int64_t fr = (int64_t)tile * kM + row;
+      if (fr < a.n_frames) {
+        const float dc = fabsf(__ldg(a.dc + fr));
+        double le[kJP];
+#pragma unroll
+        for (int j = 0; j < kJP; ++j) le[j] = (j < a.J) ? log10((double)fmaf(w0[j], dc, band[j])) : 0.0;
+        for (int c = 0; c < a.ncep; ++c) {
+          const double* brow = a.dctb + (size_t)c * kJP;
+          double s = 0.0;
+#pragma unroll
+          for (int j = 0; j < kJP; ++j) s = fma(__ldg(brow + j), le[j], s);
+          a.feats[fr * a.ncep + c] = (float)s;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+  }
+}
+
+}  // namespace tc
+}  // namespace fdlp

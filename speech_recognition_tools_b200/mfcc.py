@@ -52,6 +52,11 @@ class MfccExtractor:
         self.context = int(self.cfg.context) if self.cfg.context else 0  # `if args.context:` (:129)
         self.dim = NCEP * (2 * self.context + 1)
 
+    def set_tensor_cores(self, enable: bool = True) -> bool:
+        """Choose between the tensor-core kernel (default where the configuration fits: nfft 1024, 20 ms frames, at most
+        32 bands) and the FP32-pipe kernel; returns whether the tensor-core kernel will run."""
+        return bool(L.check_count(self._lib.mfcc_plan_set_tensor_cores(self._plan, 1 if enable else 0)))
+
     def close(self):
         if getattr(self, "_plan", None) and self._plan.value:
             with torch.cuda.device(self.device):

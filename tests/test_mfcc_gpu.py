@@ -101,3 +101,43 @@ def test_noise_then_reverb_against_oracle():
     assert got.shape == ref.shape
     np.testing.assert_allclose(got, ref, rtol=0, atol=ATOL)
     ex.close()
+
+
+def test_mfcc_tensor_core_kernel_agrees_with_fp32_pipe_kernel():
+    """The default configuration runs the 513-point transform as a 3xTF32 GEMM on the tensor cores (csrc/mfcc_tc.cuh);
+    the FP32-pipe kernel stays for other shapes.  Both against the oracle on a ragged batch (int16 and float32 input,
+    noise mixing, an utterance shorter than a frame, a frame count that is not a multiple of the 128-frame tile), and
+    against each other; a configuration the GEMM kernel does not cover reports so."""
+    import torch
+    from oracle import mfcc as omfcc
+    from speech_recognition_tools_b200 import synth
+    from speech_recognition_tools_b200.fdlp import NoiseSpec
+    from speech_recognition_tools_b200.mfcc import MfccConfig, MfccExtractor
+    ex = MfccExtractor(MfccConfig(), device="cuda:0")
+    assert ex.set_tensor_cores(True) is True
+    lens = [200, 16000, 48001, 7777, 130000]
+    wavs = [synth.make_utterance("speechlike" if i % 2 else "white", 91, i, T, 35.0) for i, T in enumerate(lens)]
+    for cast in (lambda w: w, lambda w: w.astype(np.float32)):
+        ws = [cast(w) for w in wavs]
+        tc = [o.cpu().numpy() for o in ex(ws)]
+        assert ex.set_tensor_cores(False) is False
+        ff = [o.cpu().numpy() for o in ex(ws)]
+        assert ex.set_tensor_cores(True) is True
+        for w, a, b in zip(ws, tc, ff):
+            ref = omfcc.mfcc_features(w)
+            assert a.shape == ref.shape == b.shape
+            np.testing.assert_allclose(a, ref, rtol=0, atol=ATOL)
+            np.testing.assert_allclose(b, ref, rtol=0, atol=ATOL)
+            np.testing.assert_allclose(a, b, rtol=0, atol=ATOL)
+    nz = synth.noise_int16("babble", 140000, seed=4)
+    noise = NoiseSpec(nz, 12.0, rand=[0.1 * i for i in range(len(wavs))])
+    tc = [o.cpu().numpy() for o in ex(wavs, noise=noise)]
+    ex.set_tensor_cores(False)
+    ff = [o.cpu().numpy() for o in ex(wavs, noise=noise)]
+    for a, b in zip(tc, ff):
+        np.testing.assert_allclose(a, b, rtol=0, atol=ATOL)
+    ex.close()
+    other = MfccExtractor(MfccConfig(nfft=512, nfilters=23), device="cuda:0")
+    assert other.set_tensor_cores(True) is False
+    other.close()
+    torch.cuda.synchronize()
