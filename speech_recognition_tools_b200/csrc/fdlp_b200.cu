@@ -1536,7 +1536,10 @@ struct mfcc_plan {
   // tensor-core path (csrc/mfcc_tc.cuh): nfft = 1024 (513-point transform), 320-sample frames, <= 32 bands
   bool tc_ok = false;   // the configuration fits the tensor-core kernel and its tables are built
   bool tc_on = true;    // mfcc_plan_set_tensor_cores / FDLP_MFCC_TC=0
-  float *d_bh = nullptr, *d_bl = nullptr, *d_wT = nullptr, *d_w0 = nullptr;
+  float *d_bh = nullptr, *d_bl = nullptr, *d_wblk = nullptr, *d_w0 = nullptr;
+  int32_t* d_blk_off = nullptr;
+  uint8_t* d_blk = nullptr;
+  int tc_nblk = 0;
   double* d_dctb32 = nullptr;
   float *d_ah = nullptr, *d_al = nullptr, *d_dc = nullptr;
   int64_t cap_tc = 0;
@@ -1548,7 +1551,7 @@ static void mfcc_free(mfcc_plan* p) {
   if (!p) return;
   cudaFree(p->d_ham); cudaFree(p->d_tw); cudaFree(p->d_weff); cudaFree(p->d_dctb); cudaFree(p->d_frame_utt);
   cudaFree(p->d_tmp); cudaFree(p->d_alpha);
-  cudaFree(p->d_bh); cudaFree(p->d_bl); cudaFree(p->d_wT); cudaFree(p->d_w0); cudaFree(p->d_dctb32);
+  cudaFree(p->d_bh); cudaFree(p->d_bl); cudaFree(p->d_wblk); cudaFree(p->d_blk); cudaFree(p->d_blk_off); cudaFree(p->d_w0); cudaFree(p->d_dctb32);
   cudaFree(p->d_ah); cudaFree(p->d_al); cudaFree(p->d_dc);
   delete p;
 }
@@ -1603,16 +1606,36 @@ static int mfcc_tc_setup(mfcc_plan* p, const std::vector<float>& weff, const std
       bl[(size_t)col * tc::kK + n] = v - hi;
     }
   }
-  std::vector<float> wT((size_t)tc::kUnits * tc::kBinsUnit * tc::kJP, 0.f), w0(tc::kJP, 0.f);
-  for (int j = 0; j < J; ++j) {
-    w0[j] = weff[(size_t)j * p->nbp];
-    for (int k = 1; k < p->nb; ++k) wT[(size_t)(k - 1) * tc::kJP + j] = weff[(size_t)j * p->nbp + k];
+  // folded filterbank in 32-bin chunks: the (chunk, band) blocks with a non-zero weight, and which bands touch a chunk
+  if (p->prm.ncep > tc::kMaxCep) return 0;
+  std::vector<float> w0(tc::kJP, 0.f), wblk;
+  std::vector<uint8_t> blk_band;
+  std::vector<int32_t> blk_off(tc::kChunks + 1, 0);
+  for (int j = 0; j < J; ++j) w0[j] = weff[(size_t)j * p->nbp];
+  for (int ch = 0; ch < tc::kChunks; ++ch) {
+    blk_off[ch] = (int32_t)blk_band.size();
+    for (int j = 0; j < J; ++j) {
+      float w[32];
+      bool any = false;
+      for (int i = 0; i < 32; ++i) {
+        w[i] = weff[(size_t)j * p->nbp + (1 + ch * 32 + i)];
+        any = any || w[i] != 0.f;
+      }
+      if (!any) continue;
+      if ((int)blk_band.size() >= tc::kMaxBlk) return 0;  // a denser filterbank than the table holds: FP32-pipe kernel
+      blk_band.push_back((uint8_t)j);
+      wblk.insert(wblk.end(), w, w + 32);
+    }
   }
+  blk_off[tc::kChunks] = (int32_t)blk_band.size();
+  p->tc_nblk = (int)blk_band.size();
+  if (wblk.empty()) { wblk.assign(32, 0.f); blk_band.push_back(0); }
   std::vector<double> d32((size_t)p->prm.ncep * tc::kJP, 0.0);
   for (int c = 0; c < p->prm.ncep; ++c)
     for (int j = 0; j < J; ++j) d32[(size_t)c * tc::kJP + j] = dctb[(size_t)c * J + j];
   int rc;
-  if ((rc = upload(&p->d_bh, bh)) || (rc = upload(&p->d_bl, bl)) || (rc = upload(&p->d_wT, wT)) || (rc = upload(&p->d_w0, w0)) ||
+  if ((rc = upload(&p->d_bh, bh)) || (rc = upload(&p->d_bl, bl)) || (rc = upload(&p->d_wblk, wblk)) ||
+      (rc = upload(&p->d_blk, blk_band)) || (rc = upload(&p->d_blk_off, blk_off)) || (rc = upload(&p->d_w0, w0)) ||
       (rc = upload(&p->d_dctb32, d32)))
     return rc;
   if (!mfcc_tmap(&p->tm_bh, p->d_bh, ncol, tc::kNUnit) || !mfcc_tmap(&p->tm_bl, p->d_bl, ncol, tc::kNUnit)) return 0;
@@ -1758,12 +1781,24 @@ extern "C" int mfcc_forward(mfcc_plan* p, const mfcc_batch* b, void* stream) {
     if (!mfcc_tmap(&tm_ah, p->d_ah, (uint64_t)b->n_frames, tc::kM) || !mfcc_tmap(&tm_al, p->d_al, (uint64_t)b->n_frames, tc::kM))
       return set_err(FDLP_E_CUDA, "cuTensorMapEncodeTiled failed%s", "");
     tc::Args ta;
-    ta.dc = p->d_dc; ta.wT = p->d_wT; ta.w0 = p->d_w0; ta.dctb = p->d_dctb32; ta.feats = a.feats;
+    ta.dc = p->d_dc; ta.wblk = p->d_wblk; ta.blk_band = p->d_blk; ta.blk_off = p->d_blk_off; ta.n_blk = p->tc_nblk;
+    ta.w0 = p->d_w0; ta.dctb = p->d_dctb32; ta.feats = a.feats;
     ta.n_frames = b->n_frames; ta.J = a.J; ta.ncep = a.ncep;
     ta.n_tiles = (int)((b->n_frames + tc::kM - 1) / tc::kM);
     const int grid = std::min(ta.n_tiles, p->sms);
     tc::mfcc_tc_kernel<<<grid, tc::kThreads, tc::kSmemBytes, st>>>(tm_ah, tm_al, p->tm_bh, p->tm_bl, ta);
     FDLP_CUDA(cudaGetLastError());
+#ifdef FDLP_X_TC_PROF
+    {
+      long long h[8];
+      cudaStreamSynchronize(st);
+      cudaMemcpyFromSymbol(h, tc::g_tc_prof, sizeof(h));
+      fprintf(stderr, "tc prof (cycles summed over %d CTAs): producer wait empty %lld, mma wait tmem_empty %lld, mma wait full %lld, "
+              "epilogue wait tmem_full %lld, cta total %lld; epilogue: dc + log10 %lld, mags + filterbank %lld, dc + log10 + dct + store %lld\n", grid, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
+      memset(h, 0, sizeof(h));
+      cudaMemcpyToSymbol(tc::g_tc_prof, h, sizeof(h));
+    }
+#endif
   } else {
     const int threads = std::min(288, (p->nb + 31) / 32 * 32);
     if (b->wav_dtype == FDLP_WAV_INT16) mfcc_frames_kernel<int16_t><<<(unsigned)tiles, threads, p->smem, st>>>(a);

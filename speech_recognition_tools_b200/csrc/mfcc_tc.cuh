@@ -21,10 +21,29 @@
 //                                    one of two 256-column accumulators in tensor memory; tcgen05.commit frees the
 //                                    stage and, after the last k-block, hands the accumulator to the epilogue
 //                          warps 2-5 epilogue: thread = frame (TMEM lane); tcgen05.ld 32 columns of re and of im,
-//                                    magnitudes, the folded filterbank (weights broadcast from shared memory) into 32
-//                                    band sums kept in registers over the two halves of the spectrum (unit 0: bins
-//                                    1..128, unit 1: bins 129..256), then bin 0, log10 and the DCT-II in float64
+//                                    magnitudes, then the folded filterbank for the bands that touch the 32-bin chunk
+//                                    (weights broadcast from shared memory, 32 band sums in registers over the two
+//                                    halves of the spectrum: unit 0 = bins 1..128, unit 1 = bins 129..256), then bin 0,
+//                                    log10 and the DCT-II, all in float32
 //                        The accumulator of unit u + 1 fills while the epilogue drains unit u.
+//
+// Measured on the bench batch (852 138 frames, profiles/ncu_full_r02_mfcc_tc_summary.json): preparation 0.60 ms (2.1 GB
+// written, 49 % of HBM) + GEMM kernel 1.14 ms (tensor pipe 75 % busy) = 1.75 ms against 10.8 ms of the FP32-pipe kernel.
+// What the first working version (2.8 ms, tensor pipe 38 %) was missing, found with per-role cycle counters
+// (-DFDLP_X_TC_PROF): the MMA warp waited for the epilogue half of the time.  (1) The epilogue used FP64 (log10 and the
+// DCT in double, as csrc/mfcc.cuh does): DFMA and the tensor cores share a datapath on this part, and behind a stream of
+// tcgen05.mma 416 DFMAs per frame took 16 k cycles per tile, 32 double logarithms 30 k -- as long as the tile's MMAs
+// (32 k).  Now float log10 and a four-chain compensated float DCT (~2e-5 on c0).  (2) All 256 x 32 filterbank weights per
+// frame: 2048 16-byte shared-memory reads; now only the ~100 (32-bin chunk, band) blocks with a non-zero weight, as a
+// branch-free loop (the block's sum is added through a select over the 32 register-resident band sums: a warp-uniform
+// branch per band serialised load and FMA latencies).  Rejected on measurements: per-band 8-column tcgen05.ld segments
+// (latency-bound, 4.9 ms); the tables as a 27 KB kernel parameter in the constant bank (indexed reads slower than shared
+// memory, 2.6 ms); an L2 prefetch of the next tile's frames (no change); and a variant without the preparation kernel --
+// four more warps building the Ah / Al tiles of a stage directly from the waveform, thread = frame, swizzled 16-byte
+// stores, fence.proxy.async -- which was correct and SLOWER (7.5 ms): a frame's 32 samples of a k-block are 64 unaligned
+// bytes, 320 bytes from the next frame's, so the builders issue 2-byte loads that touch 32 sectors per warp instruction;
+// staging a tile's sample span in shared memory first has no room beside the two 96 KB stages.  Left: two stages only
+// (the MMA warp waits for TMA 22 % of the time), and the 2.1 GB round trip of the planes through HBM.
 #pragma once
 #include <cuda.h>
 
@@ -46,11 +65,21 @@ constexpr int kBTile = kNUnit * 128;
 constexpr int kStageBytes = 2 * kATile + 2 * kBTile;
 constexpr int kJP = 32;                 // bands, padded
 constexpr int kThreads = 192;
-constexpr size_t kSmemBytes = 1024 + (size_t)kStages * kStageBytes + (size_t)kUnits * kBinsUnit * kJP * 4 + kJP * 4 + 128;
+constexpr int kChunks = kUnits * kBinsUnit / 32;   // 32-bin chunks of the spectrum
+constexpr int kMaxBlk = 176;                       // (chunk, band) blocks with a non-zero weight (mel, 30 bands: ~100)
+constexpr int kMaxCep = 16;
+constexpr size_t kTabBytes = (size_t)kMaxBlk * 32 * 4 + kJP * 4 + (kChunks + 1) * 4 + kMaxBlk + 4 + (size_t)kMaxCep * kJP * 4;
+constexpr size_t kSmemBytes = 1024 + (size_t)kStages * kStageBytes + kTabBytes + 128;
 
 struct Args {
   const float* dc;       // [n_frames] frame sums (bin 0)
-  const float* wT;       // [256][32] folded filterbank of bins 1..256, band fastest, zero beyond J
+  // folded filterbank of bins 1..256 in 32-bin chunks: the (chunk, band) blocks with a non-zero weight (a mel band
+  // touches 1-3 of the 8 chunks, directly or mirrored), chunk after chunk: blocks blk_off[ch] .. blk_off[ch+1] belong to
+  // chunk ch, block e to band blk_band[e], its 32 weights are wblk[e]
+  const float* wblk;         // [n_blk][32]
+  const uint8_t* blk_band;   // [n_blk]
+  const int32_t* blk_off;    // [9]
+  int n_blk;
   const float* w0;       // [32] weights of bin 0
   const double* dctb;    // [ncep][32] DCT-II basis, zero beyond J
   float* feats;          // [n_frames, ncep]
@@ -89,10 +118,11 @@ __global__ void __launch_bounds__(256) mfcc_tc_prep_kernel(const PrepArgs a) {
   const int16_t* nz = a.noise ? a.noise + a.utt_noise_off[u] : nullptr;
   const float alpha = a.noise ? (float)a.utt_alpha[u] : 0.f;
   float sum = 0.f;
-#pragma unroll
+  const bool inside = q0 >= 0 && q0 + kK <= T;  // all but the first and last frames of an utterance: no reflection (a
+#pragma unroll                                   // 64-bit modulo per sample otherwise)
   for (int t = 0; t < kK / 32; ++t) {
     const int i = lane + 32 * t;
-    const int64_t q = (T > 1) ? reflect_index(q0 + i, T) : 0;
+    const int64_t q = inside ? q0 + i : ((T > 1) ? reflect_index(q0 + i, T) : 0);
     float x = (float)wav[q];
     if (nz) x = fmaf(alpha, (float)nz[q], x);
     const float v = x * __ldg(a.ham + i);
@@ -118,6 +148,12 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+#ifdef FDLP_X_TC_PROF
+__device__ long long g_tc_prof[8];
+#define TC_PROF_ADD(slot, v) atomicAdd((unsigned long long*)&g_tc_prof[slot], (unsigned long long)(v))
+#else
+#define TC_PROF_ADD(slot, v)
+#endif
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   const long long t0 = clock64();
   for (;;) {
@@ -183,9 +219,14 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
                const __grid_constant__ CUtensorMap tm_bh, const __grid_constant__ CUtensorMap tm_bl, const Args a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  float* wT = reinterpret_cast<float*>(base + (size_t)kStages * kStageBytes);  // [256][32]
-  float* w0 = wT + kUnits * kBinsUnit * kJP;                                    // [32]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(w0 + kJP);  // full[2] empty[2] tmem_full[2] tmem_empty[2]
+  // the epilogue's tables: shared memory, broadcast reads (as a 27 KB kernel parameter in the constant bank the indexed
+  // reads were slower: 2.62 against 2.27 ms)
+  float* dct_s = reinterpret_cast<float*>(base + (size_t)kStages * kStageBytes);   // [kMaxCep][32]
+  float* wblk = dct_s + kMaxCep * kJP;                                            // [kMaxBlk][32]
+  float* w0 = wblk + kMaxBlk * 32;                                                // [32]
+  int32_t* blk_off = reinterpret_cast<int32_t*>(w0 + kJP);                        // [9] first block of a chunk
+  uint8_t* blk_band = reinterpret_cast<uint8_t*>(blk_off + kChunks + 1);          // [kMaxBlk] band of a block
+  uint64_t* bars = reinterpret_cast<uint64_t*>(blk_band + kMaxBlk + 4);  // full[2] empty[2] tmem_full[2] tmem_empty[2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
   const uint32_t sbase = smem_u32(base);
   const uint32_t bar0 = smem_u32(bars);
@@ -195,8 +236,11 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
   auto tempty_bar = [&](int u) { return bar0 + 8u * (6 + u); };
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  for (int i = threadIdx.x; i < kUnits * kBinsUnit * kJP + kJP; i += kThreads)
-    wT[i] = (i < kUnits * kBinsUnit * kJP) ? __ldg(a.wT + i) : __ldg(a.w0 + (i - kUnits * kBinsUnit * kJP));
+  for (int i = threadIdx.x; i < a.n_blk * 32; i += kThreads) wblk[i] = __ldg(a.wblk + i);
+  for (int i = threadIdx.x; i < a.n_blk; i += kThreads) blk_band[i] = a.blk_band[i];
+  for (int i = threadIdx.x; i < a.ncep * kJP; i += kThreads) dct_s[i] = (float)__ldg(a.dctb + i);
+  for (int i = threadIdx.x; i < kJP; i += kThreads) w0[i] = __ldg(a.w0 + i);
+  if (threadIdx.x <= kChunks) blk_off[threadIdx.x] = a.blk_off[threadIdx.x];
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int u = 0; u < kUnits; ++u) { mbar_init(tfull_bar(u), 1); mbar_init(tempty_bar(u), 4); }
@@ -211,6 +255,9 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+#ifdef FDLP_X_TC_PROF
+  const long long t_start = clock64();
+#endif
 
   if (warp == 0) {
     // ================= TMA producer =================
@@ -221,7 +268,7 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
           for (int kb = 0; kb < kKB; ++kb, ++it) {
             const int s = it % kStages;
             const uint32_t ph = (it / kStages) & 1u;
-            mbar_wait(empty_bar(s), ph ^ 1u);
+            { const long long tp_ = clock64(); mbar_wait(empty_bar(s), ph ^ 1u); if (true) TC_PROF_ADD(0, clock64() - tp_); }
             const uint32_t dst = sbase + (uint32_t)s * kStageBytes;
             mbar_expect_tx(full_bar(s), kStageBytes);
             tma_load_2d(dst, &tm_ah, full_bar(s), kb * kBK, tile * kM);
@@ -235,12 +282,12 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
     uint32_t it = 0, tile_it = 0;
     for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tile_it)
       for (int u = 0; u < kUnits; ++u) {
-        mbar_wait(tempty_bar(u), (tile_it & 1u) ^ 1u);  // the epilogue has drained this accumulator
+        { const long long tp_ = clock64(); mbar_wait(tempty_bar(u), (tile_it & 1u) ^ 1u); if (lane == 0) TC_PROF_ADD(1, clock64() - tp_); }  // the epilogue has drained this accumulator
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)u * kNUnit;
         for (int kb = 0; kb < kKB; ++kb, ++it) {
           const int s = it % kStages;
-          mbar_wait(full_bar(s), (it / kStages) & 1u);
+          { const long long tp_ = clock64(); mbar_wait(full_bar(s), (it / kStages) & 1u); if (lane == 0) TC_PROF_ADD(2, clock64() - tp_); }
           tc_fence_after();
           if (lane == 0) {
             const uint32_t st = sbase + (uint32_t)s * kStageBytes;
@@ -269,49 +316,95 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
 #pragma unroll
       for (int j = 0; j < kJP; ++j) band[j] = 0.f;
       for (int u = 0; u < kUnits; ++u) {
-        mbar_wait(tfull_bar(u), tile_it & 1u);
+        { const long long tp_ = clock64(); mbar_wait(tfull_bar(u), tile_it & 1u); if (threadIdx.x == 64) TC_PROF_ADD(3, clock64() - tp_); }
         tc_fence_after();
         const uint32_t t0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)u * kNUnit;
         for (int c = 0; c < kBinsUnit / 32; ++c) {
           uint32_t re[32], im[32];
+#ifdef FDLP_X_TC_PROF
+          const long long tl_ = clock64();
+#endif
           tmem_ld32(t0 + c * 32, re);
           tmem_ld32(t0 + kBinsUnit + c * 32, im);
           tmem_ld_wait();
-          const float4* wrow = reinterpret_cast<const float4*>(wT + (size_t)(u * kBinsUnit + c * 32) * kJP);
+#ifdef FDLP_X_TC_PROF
+          const long long tm_ = clock64();
+#endif
+          float mag[32];
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
             const float xr = __uint_as_float(re[i]), xi = __uint_as_float(im[i]);
-            const float mag = sqrtf(fmaf(xr, xr, xi * xi));
-#pragma unroll
-            for (int q = 0; q < kJP / 4; ++q) {
-              const float4 w = wrow[i * (kJP / 4) + q];
-              band[4 * q + 0] = fmaf(w.x, mag, band[4 * q + 0]);
-              band[4 * q + 1] = fmaf(w.y, mag, band[4 * q + 1]);
-              band[4 * q + 2] = fmaf(w.z, mag, band[4 * q + 2]);
-              band[4 * q + 3] = fmaf(w.w, mag, band[4 * q + 3]);
-            }
+            const float p2 = fmaf(xr, xr, xi * xi);
+            mag[i] = p2 > 0.f ? p2 * rsqrtf(p2) : 0.f;  // 2 ulp: the log10 of a sum of ~30 of these is compared to 2e-4
           }
+          // only the (chunk, band) blocks with a non-zero weight, ~100 of the 256 of a mel filterbank, as one runtime loop
+          // (a chunk's blocks are consecutive in wblk; the band a block belongs to is a table entry, and its sum is added
+          // through a select over the 32 register-resident band sums: branch-free, so the loads of the next block overlap
+          // the FMAs of this one -- a warp-uniform branch per band serialised load and FMA latencies, 4.3 k cycles per chunk)
+          const int ch = u * (kBinsUnit / 32) + c;
+          const int e0 = blk_off[ch], e1 = blk_off[ch + 1];
+#pragma unroll 2
+          for (int e = e0; e < e1; ++e) {
+            const float4* wrow = reinterpret_cast<const float4*>(wblk + (size_t)e * 32);
+            const int je = blk_band[e];
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const float4 w = wrow[q];
+              a0 = fmaf(w.x, mag[4 * q + 0], a0);
+              a1 = fmaf(w.y, mag[4 * q + 1], a1);
+              a2 = fmaf(w.z, mag[4 * q + 2], a2);
+              a3 = fmaf(w.w, mag[4 * q + 3], a3);
+            }
+            const float part = (a0 + a1) + (a2 + a3);
+#pragma unroll
+            for (int j = 0; j < kJP; ++j) band[j] += (j == je) ? part : 0.f;
+          }
+#ifdef FDLP_X_TC_PROF
+          if (threadIdx.x == 64) TC_PROF_ADD(6, clock64() - tm_);
+#endif
         }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty_bar(u));
       }
       const int64_t fr = (int64_t)tile * kM + row;
+#ifdef FDLP_X_TC_PROF
+      const long long tf_ = clock64();
+#endif
       if (fr < a.n_frames) {
         const float dc = fabsf(__ldg(a.dc + fr));
-        double le[kJP];
+        // No FP64 here: DFMA and the tensor cores share a datapath on this part, and behind a stream of
+        // tcgen05.mma the 416 DFMAs of the double-precision DCT took 16 k cycles per tile, 32 double logarithms another
+        // 30 k.  float log10 of the float band energy, float products and a compensated (Kahan) sum: ~2e-5 on c0.
+        float le[kJP];
 #pragma unroll
-        for (int j = 0; j < kJP; ++j) le[j] = (j < a.J) ? log10((double)fmaf(w0[j], dc, band[j])) : 0.0;
+        for (int j = 0; j < kJP; ++j) le[j] = (j < a.J) ? log10f(fmaf(w0[j], dc, band[j])) : 0.f;
+#ifdef FDLP_X_TC_PROF
+        if (threadIdx.x == 64) TC_PROF_ADD(5, clock64() - tf_);
+#endif
         for (int c = 0; c < a.ncep; ++c) {
-          const double* brow = a.dctb + (size_t)c * kJP;
-          double s = 0.0;
+          const float* brow = dct_s + (size_t)c * kJP;  // broadcast reads
+          float sq[4] = {0.f, 0.f, 0.f, 0.f}, cq[4] = {0.f, 0.f, 0.f, 0.f};  // four compensated chains
 #pragma unroll
-          for (int j = 0; j < kJP; ++j) s = fma(__ldg(brow + j), le[j], s);
-          a.feats[fr * a.ncep + c] = (float)s;
+          for (int j = 0; j < kJP; ++j) {
+            const float y = brow[j] * le[j] - cq[j & 3];
+            const float t = sq[j & 3] + y;
+            cq[j & 3] = (t - sq[j & 3]) - y;
+            sq[j & 3] = t;
+          }
+          const float s = ((sq[0] + sq[1]) + (sq[2] + sq[3])) - ((cq[0] + cq[1]) + (cq[2] + cq[3]));
+          a.feats[fr * a.ncep + c] = s;
         }
       }
+#ifdef FDLP_X_TC_PROF
+      if (threadIdx.x == 64) TC_PROF_ADD(7, clock64() - tf_);
+#endif
     }
   }
+#ifdef FDLP_X_TC_PROF
+  if (threadIdx.x == 0) TC_PROF_ADD(4, clock64() - t_start);
+#endif
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
