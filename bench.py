@@ -642,6 +642,34 @@ def run_ours(args):
                     "frac_of_hbm": mel_bytes / (mel_ms * 1e-3) / 1e9 / hbm_peak}
         del mfeats
 
+        # ---- MFCC path on the same batch: the tensor-core kernel (csrc/mfcc_tc.cuh) and the FP32-pipe kernel it replaces ----
+        mfcc_info = None
+        try:
+            from speech_recognition_tools_b200.mfcc import MfccConfig, MfccExtractor
+            mf = MfccExtractor(MfccConfig(), device=dev)
+            flay = mf.layout(lens).to(dev)
+            ffeats = torch.empty((flay.n_frames, mf.dim), dtype=torch.float32, device=dev)
+            mfcc_info = {"unit": UNIT, "frames": int(flay.n_frames)}
+            for name, on in (("tensor_core", True), ("fp32_pipe", False)):
+                used = mf.set_tensor_cores(on)
+                for _ in range(3):
+                    mf.forward_packed(wav_dev, flay, feats=ffeats)
+                torch.cuda.synchronize(dev)
+                e0.record()
+                for _ in range(5):
+                    mf.forward_packed(wav_dev, flay, feats=ffeats)
+                e1.record()
+                torch.cuda.synchronize(dev)
+                ms = e0.elapsed_time(e1) / 5
+                mfcc_info[name] = {"ms_per_step": ms, "value": audio_s / (ms * 1e-3), "kernel": "tcgen05 3xTF32 GEMM" if used else "FFMA direct DFT"}
+            # 3 TF32 passes of [frames x 320] . [320 x 512]; dense TF32 peak = half the measured bf16 peak
+            tf32_flops = 3 * 2.0 * flay.n_frames * 320 * 512
+            mfcc_info["tensor_core"]["tf32_tflops_incl_preparation"] = tf32_flops / (mfcc_info["tensor_core"]["ms_per_step"] * 1e-3) / 1e12
+            mf.close()
+            del ffeats
+        except Exception as e:  # noqa: BLE001 -- the main line must not depend on this block
+            mfcc_info = {"error": repr(e)}
+
         # ---- --add_reverb augmentation on the same batch: reverberation alone and followed by the extraction ----
         from speech_recognition_tools_b200.reverb import Reverberator
         R_RIR = 16000
@@ -719,7 +747,7 @@ def run_ours(args):
             "e2e_cli": e2e_cli,
             "gpu_launches": ((7 if ex.geom["nfam"] > 0 else 5) + 1) * args.steps * world,
             "multi_gpu_check": mgc["status"], "multi_gpu_check_detail": mgc,
-            "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "mel_baseline": mel_info,
+            "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "mel_baseline": mel_info, "mfcc": mfcc_info,
             "add_reverb": reverb_info, "other_configs": extra,
         }
     if world > 1:
