@@ -1,13 +1,9 @@
-set -x
 mkdir -p gpurun_out
-N=2
+N=4
 timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29534 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_${N}gpu.json 2> gpurun_out/bench_${N}gpu.err
-tail -3 gpurun_out/bench_${N}gpu.err
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29535 bench.py --impl reference --gpus $N --steps 2 --warmup 1 > gpurun_out/bench_ref_${N}gpu.json 2> gpurun_out/bench_ref_${N}gpu.err
-tail -c 300 gpurun_out/bench_ref_${N}gpu.json
-timeout 300 python -m pytest tests/test_cli_gpu.py -x -q -m gpu 2>&1 | tail -2
+tail -2 gpurun_out/bench_${N}gpu.err
 python - <<'PY'
 import json
-d=json.loads(open('gpurun_out/bench_2gpu.json').read().strip().splitlines()[-1])
-print(d['n_gpus'], round(d['value']), d['ms_per_step'], round(d['e2e']['value']), d['e2e']['ms_per_step'], d['e2e_cli']['wall_s'], d['multi_gpu_check'], d['mfcc']['tensor_core']['ms_per_step'])
+d=json.loads(open('gpurun_out/bench_4gpu.json').read().strip().splitlines()[-1])
+print(d['n_gpus'], round(d['value']), d['ms_per_step'], round(d['e2e']['value']), d['e2e']['ms_per_step'], d['e2e_cli']['wall_s'], d['multi_gpu_check'])
 PY
