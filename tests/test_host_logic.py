@@ -377,3 +377,14 @@ def test_native_wav_probe_and_read_match_scipy_and_the_python_probe(tmp_path):
     assert lib.fdlp_wav_read(p2, src_off.ctypes.data, nbytes.ctypes.data, dst_off.ctypes.data, buf.ctypes.data, 3, 2,
                              status.ctypes.data) == 0
     assert list(status[:3]) == [0, 0, 1]
+
+
+def test_host_threads_shares_the_cores_between_local_ranks(monkeypatch):
+    from speech_recognition_tools_b200.fdlp import host_threads
+    cores = len(os.sched_getaffinity(0))
+    monkeypatch.delenv("LOCAL_WORLD_SIZE", raising=False)
+    assert host_threads(8) == max(2, min(8, cores))
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "8")
+    assert host_threads(16) == max(2, min(16, cores // 8))
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "1000")
+    assert host_threads(16) == 2

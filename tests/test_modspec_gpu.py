@@ -147,3 +147,40 @@ def test_modspec_complex_cli_matches_golden(tmp_path):
     np.testing.assert_allclose(got, c["feats"], rtol=2e-6, atol=2e-6)
     with pytest.raises(ValueError):
         cli.getFeats(cli.get_args(argv + ["--keep_even"]))
+
+
+def test_stage_frames_equals_getframes():
+    """fdlp_stage_frames (the framing kernel's output as float64) == features.py:118-154 getFrames for hanning and
+    square windows, int16 and float32 input, utterances shorter than a frame (multi-bounce reflection)."""
+    import ctypes as C
+    from oracle import fdlp as ofdlp
+    from oracle import modspec as omod
+    from speech_recognition_tools_b200 import _lib as L
+    from speech_recognition_tools_b200 import synth
+    from speech_recognition_tools_b200.fdlp import FdlpExtractor
+    from speech_recognition_tools_b200.modspec import ModSpecConfig, ModSpecExtractor
+    for no_window, fdur, cast in ((False, 0.5, None), (True, 0.1, np.float32)):
+        ex = ModSpecExtractor(ModSpecConfig(no_window=no_window, fduration=fdur, order=20, coeff_n=10, coeff_0=1), device="cuda:0")
+        wavs = [synth.make_utterance("white", 44, i, T) for i, T in enumerate([300, 1601, 9000])]
+        if cast is not None:
+            wavs = [w.astype(cast) for w in wavs]
+        host, lengths = FdlpExtractor.pack(wavs)
+        lay = ex.layout(lengths).to(ex.device)
+        wav_dev = host.to(ex.device)
+        b = L.FdlpBatch()
+        d = lay.dev
+        b.wav = wav_dev.data_ptr()
+        b.wav_dtype = L.FDLP_WAV_INT16 if wav_dev.dtype == torch.int16 else L.FDLP_WAV_FLOAT32
+        b.n_utt, b.n_seg, b.n_frames, b.max_utt_frames = lay.n_utt, lay.n_seg, lay.n_frames, lay.max_utt_frames
+        b.utt_wav_off, b.utt_seg_off = d["utt_wav_off"].data_ptr(), d["utt_seg_off"].data_ptr()
+        b.utt_frame_off, b.seg_utt, b.seg_ptr = d["utt_frame_off"].data_ptr(), d["seg_utt"].data_ptr(), d["seg_ptr"].data_ptr()
+        b.noise_mode = L.FDLP_NOISE_NONE
+        N = ex.geom["N"]
+        frames = torch.zeros((lay.n_seg, N), dtype=torch.float64, device=ex.device)
+        L.check(ex._lib.fdlp_stage_frames(ex._plan, C.byref(b), C.c_void_p(frames.data_ptr()),
+                                          C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        got = frames.cpu().numpy()
+        ref = np.concatenate([ofdlp.get_frames(w, 16000, 100, fdur, omod.sq_wind if no_window else np.hanning) for w in wavs])
+        assert got.shape == ref.shape
+        np.testing.assert_allclose(got, ref, rtol=1e-13, atol=1e-9)
+        ex.close()
