@@ -1809,8 +1809,7 @@ extern "C" int mfcc_forward(mfcc_plan* p, const mfcc_batch* b, void* stream) {
     SpliceArgs s;
     s.in = p->d_tmp; s.out = b->feats; s.utt_frame_off = b->utt_frame_off; s.frame_utt = p->d_frame_utt;
     s.n_frames = b->n_frames; s.D = p->prm.ncep; s.context = b->context;
-    const long long total = (long long)b->n_frames * s.D * (2 * s.context + 1);
-    splice_kernel<<<(unsigned)std::min<long long>((total + 255) / 256, 148LL * 16), 256, 0, st>>>(s);
+    splice_kernel<<<(unsigned)std::min<long long>((b->n_frames + 31) / 32, 148LL * 32), 256, 0, st>>>(s);
     FDLP_CUDA(cudaGetLastError());
   }
   return FDLP_OK;

@@ -177,18 +177,31 @@ struct SpliceArgs {
 };
 
 __global__ void __launch_bounds__(256) splice_kernel(const SpliceArgs a) {
+  // a CTA owns kSpliceFT consecutive frames: 32-bit index arithmetic inside the tile (the first version divided a 64-bit
+  // flat index three times per element and was bound by that: 0.62 ms for 487 MB of output)
+  constexpr int kSpliceFT = 32;
   const int W = 2 * a.context + 1;
-  const int64_t total = a.n_frames * W * a.D;
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
-    const int d = (int)(idx % a.D);
-    const int w = (int)((idx / a.D) % W);
-    const int64_t fr = idx / ((int64_t)a.D * W);
-    const int u = a.frame_utt[fr];
-    const int64_t f0 = a.utt_frame_off[u], F = a.utt_frame_off[u + 1] - f0;
-    const int64_t i = fr - f0, src = i + w - a.context;
-    float v = 0.f;
-    if (i < F - a.context && src >= 0 && src < F) v = a.in[(f0 + src) * a.D + d];
-    a.out[idx] = v;
+  const int row = W * a.D;  // output floats per frame
+  __shared__ int64_t s_f0[kSpliceFT], s_F[kSpliceFT];
+  for (int64_t t0 = (int64_t)blockIdx.x * kSpliceFT; t0 < a.n_frames; t0 += (int64_t)gridDim.x * kSpliceFT) {
+    const int nfr = (int)((a.n_frames - t0 < kSpliceFT) ? a.n_frames - t0 : kSpliceFT);
+    __syncthreads();
+    if ((int)threadIdx.x < nfr) {
+      const int u = a.frame_utt[t0 + threadIdx.x];
+      s_f0[threadIdx.x] = a.utt_frame_off[u];
+      s_F[threadIdx.x] = a.utt_frame_off[u + 1] - a.utt_frame_off[u];
+    }
+    __syncthreads();
+    float* out = a.out + t0 * row;
+    for (int li = threadIdx.x; li < nfr * row; li += blockDim.x) {
+      const int lf = li / row, r = li - lf * row;
+      const int w = r / a.D, d = r - w * a.D;
+      const int64_t f0 = s_f0[lf], F = s_F[lf];
+      const int64_t i = t0 + lf - f0, src = i + w - a.context;
+      float v = 0.f;
+      if (i < F - a.context && src >= 0 && src < F) v = __ldg(a.in + (f0 + src) * a.D + d);
+      out[li] = v;
+    }
   }
 }
 

@@ -1,1 +1,2 @@
-time python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -5
+timeout 300 python -m pytest tests/test_mfcc_gpu.py -x -q -m gpu 2>&1 | tail -2
+timeout 120 python tools/perf_mfcc.py 2>&1 | tail -3
