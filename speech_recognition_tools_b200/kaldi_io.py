@@ -6,7 +6,8 @@ Kaldi is not vendored in the reference (README.md:5-12), so the binary layout be
 one (parity unpinned):
     <utt-id> ' ' '\\0' 'B' 'F' 'M' ' ' '\\4' <int32 rows> '\\4' <int32 cols> <rows*cols float32, row-major>
 and each scp line is `<utt-id> <ark-path>:<byte offset of the '\\0'>`.
-`quantize_3dp=True` reproduces the reference's text round trip (values rounded to 3 decimals)."""
+`quantize_3dp=True` reproduces the reference's text round trip (values rounded to 3 decimals); the CLI shims turn it
+on with FDLP_ARK_3DP=1 (`ark_3dp()`), off by default: the full float32 values are what a new recipe wants."""
 from __future__ import annotations
 
 import struct
@@ -15,15 +16,28 @@ from typing import Dict, Iterable, Tuple
 import numpy as np
 
 
+def ark_3dp() -> bool:
+    """FDLP_ARK_3DP=1: write what the reference's dict2Ark leaves on disk -- every value went through '%.3f' text
+    (features.py:63-69) before Kaldi's copy-feats made it float32 again."""
+    import os
+    return os.environ.get("FDLP_ARK_3DP", "0") not in ("", "0")
+
+
+def round_3dp(m: np.ndarray) -> np.ndarray:
+    return np.round(m.astype(np.float64), 3).astype(np.float32)
+
+
 def write_ark_scp(feats: Iterable[Tuple[str, np.ndarray]], ark_path: str, scp_path: str,
-                  quantize_3dp: bool = False) -> None:
+                  quantize_3dp: bool = None) -> None:
+    if quantize_3dp is None:
+        quantize_3dp = ark_3dp()
     with open(ark_path, "wb") as ark, open(scp_path, "w") as scp:
         for key, mat in feats:
             m = np.asarray(mat, dtype=np.float32)
             if m.ndim != 2:
                 raise ValueError("feature matrix of %s is not 2-D" % key)
             if quantize_3dp:
-                m = np.round(m.astype(np.float64), 3).astype(np.float32)
+                m = round_3dp(m)
             ark.write(key.encode("utf-8") + b" ")
             off = ark.tell()
             ark.write(b"\0BFM ")
@@ -61,8 +75,10 @@ class ArkWriter:
     kernel allocating and clearing pages one fault at a time (272 MB: 45 ms, against 17 ms for one fallocate call plus
     22 ms for the copy, tools/tmpfs_write_probe.py), and the reader thread knows a batch's size before it is computed."""
 
-    def __init__(self, ark_path: str, scp_path: str, pool=None, threads: int = 4, scp_ark_name: str = None):
+    def __init__(self, ark_path: str, scp_path: str, pool=None, threads: int = 4, scp_ark_name: str = None,
+                 quantize_3dp: bool = None):
         import os
+        self._q3 = ark_3dp() if quantize_3dp is None else bool(quantize_3dp)
         self.ark_path, self.scp_name = ark_path, scp_ark_name or ark_path
         self._fd = os.open(ark_path, os.O_RDWR | os.O_CREAT | os.O_TRUNC, 0o644)
         self._scp = open(scp_path, "w")
@@ -96,6 +112,8 @@ class ArkWriter:
         import os
         if mat.dtype != np.float32 or mat.ndim != 2 or not mat.flags.c_contiguous:
             raise ValueError("batch matrix must be C-contiguous float32 [n_frames, dim]")
+        if self._q3:
+            mat = round_3dp(mat)
         dim = mat.shape[1]
         flat = memoryview(mat.reshape(-1)).cast("B")
         bufs, lines, pos = [], [], self._pos

@@ -388,3 +388,28 @@ def test_host_threads_shares_the_cores_between_local_ranks(monkeypatch):
     assert host_threads(16) == max(2, min(16, cores // 8))
     monkeypatch.setenv("LOCAL_WORLD_SIZE", "1000")
     assert host_threads(16) == 2
+
+
+def test_ark_three_decimal_mode_matches_the_text_round_trip(tmp_path, monkeypatch):
+    """FDLP_ARK_3DP=1: the values the reference's dict2Ark leaves on disk ('%.3f' text, features.py:63-69, parsed back
+    to float32 by copy-feats), in both writers; off by default."""
+    import io
+    from speech_recognition_tools_b200.kaldi_io import ArkWriter, read_ark, write_ark_scp
+    rng = np.random.default_rng(3)
+    mat = (rng.standard_normal((50, 6)) * 20).astype(np.float32)
+    mat[0, 0], mat[1, 1] = -np.inf, 0.0005
+    buf = io.StringIO()
+    np.savetxt(buf, mat.astype(np.float64), fmt="%.3f")
+    text = np.loadtxt(io.StringIO(buf.getvalue()), dtype=np.float64).astype(np.float32)
+    off = np.array([0, 20, 50])
+    monkeypatch.setenv("FDLP_ARK_3DP", "1")
+    w = ArkWriter(str(tmp_path / "a.ark"), str(tmp_path / "a.scp"))
+    w.write_batch(["u0", "u1"], mat, off)
+    w.close()
+    write_ark_scp([("u0", mat[:20]), ("u1", mat[20:])], str(tmp_path / "b.ark"), str(tmp_path / "b.scp"))
+    for name in ("a.ark", "b.ark"):
+        got = read_ark(str(tmp_path / name))
+        np.testing.assert_array_equal(np.concatenate([got["u0"], got["u1"]]), text)
+    monkeypatch.delenv("FDLP_ARK_3DP")
+    write_ark_scp([("u0", mat)], str(tmp_path / "c.ark"), str(tmp_path / "c.scp"))
+    np.testing.assert_array_equal(read_ark(str(tmp_path / "c.ark"))["u0"], mat)
