@@ -42,8 +42,9 @@
 // four more warps building the Ah / Al tiles of a stage directly from the waveform, thread = frame, swizzled 16-byte
 // stores, fence.proxy.async -- which was correct and SLOWER (7.5 ms): a frame's 32 samples of a k-block are 64 unaligned
 // bytes, 320 bytes from the next frame's, so the builders issue 2-byte loads that touch 32 sectors per warp instruction;
-// staging a tile's sample span in shared memory first has no room beside the two 96 KB stages.  Left: two stages only
-// (the MMA warp waits for TMA 22 % of the time), and the 2.1 GB round trip of the planes through HBM.
+// staging a tile's sample span in shared memory first has no room beside the two 96 KB stages; and four 48 KB stages of
+// 16-sample k-blocks with the 64-byte swizzle (-DFDLP_TC_BK=16: correct, 1.74 against 1.66 ms -- smaller boxes, twice the
+// barrier traffic).  Left: the MMA warp waits for TMA 22 % of the time, and the 2.1 GB round trip of the planes through HBM.
 #pragma once
 #include <cuda.h>
 
@@ -57,11 +58,15 @@ constexpr int kNUnit = 256;             // accumulator columns per unit: 128 bin
 constexpr int kUnits = 2;
 constexpr int kBinsUnit = 128;
 constexpr int kK = 320;                 // samples per frame
-constexpr int kBK = 32;                 // tf32 elements per k-block = one 128-byte swizzle row
+#ifndef FDLP_TC_BK
+#define FDLP_TC_BK 32
+#endif
+constexpr int kBK = FDLP_TC_BK;         // tf32 elements per k-block = one swizzle row: 32 (128-byte swizzle) or 16 (64-byte)
+constexpr int kRowBytes = kBK * 4;
 constexpr int kKB = kK / kBK;
-constexpr int kStages = 2;
-constexpr int kATile = kM * 128;        // bytes of one A plane of a stage
-constexpr int kBTile = kNUnit * 128;
+constexpr int kStages = (kBK == 32) ? 2 : 4;
+constexpr int kATile = kM * kRowBytes;  // bytes of one A plane of a stage
+constexpr int kBTile = kNUnit * kRowBytes;
 constexpr int kStageBytes = 2 * kATile + 2 * kBTile;
 constexpr int kJP = 32;                 // bands, padded
 constexpr int kThreads = 192;
@@ -205,9 +210,9 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr) {
   uint64_t d = (uint64_t)((saddr & 0x3ffffu) >> 4);
   d |= (uint64_t)1 << 16;            // leading byte offset: not used by swizzled K-major layouts
-  d |= (uint64_t)(1024 >> 4) << 32;  // stride byte offset
-  d |= (uint64_t)1 << 46;            // version
-  d |= (uint64_t)2 << 61;            // SWIZZLE_128B
+  d |= (uint64_t)((8 * kRowBytes) >> 4) << 32;  // stride byte offset: 8 rows
+  d |= (uint64_t)1 << 46;                       // version
+  d |= (uint64_t)(kBK == 32 ? 2 : 4) << 61;     // SWIZZLE_128B / SWIZZLE_64B
   return d;
 }
 
@@ -226,14 +231,14 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
   float* w0 = wblk + kMaxBlk * 32;                                                // [32]
   int32_t* blk_off = reinterpret_cast<int32_t*>(w0 + kJP);                        // [9] first block of a chunk
   uint8_t* blk_band = reinterpret_cast<uint8_t*>(blk_off + kChunks + 1);          // [kMaxBlk] band of a block
-  uint64_t* bars = reinterpret_cast<uint64_t*>(blk_band + kMaxBlk + 4);  // full[2] empty[2] tmem_full[2] tmem_empty[2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(blk_band + kMaxBlk + 4);  // full[S] empty[S] tmem_full[2] tmem_empty[2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
   const uint32_t sbase = smem_u32(base);
   const uint32_t bar0 = smem_u32(bars);
   auto full_bar = [&](int s) { return bar0 + 8u * s; };
-  auto empty_bar = [&](int s) { return bar0 + 8u * (2 + s); };
-  auto tfull_bar = [&](int u) { return bar0 + 8u * (4 + u); };
-  auto tempty_bar = [&](int u) { return bar0 + 8u * (6 + u); };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (kStages + s); };
+  auto tfull_bar = [&](int u) { return bar0 + 8u * (2 * kStages + u); };
+  auto tempty_bar = [&](int u) { return bar0 + 8u * (2 * kStages + 2 + u); };
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   for (int i = threadIdx.x; i < a.n_blk * 32; i += kThreads) wblk[i] = __ldg(a.wblk + i);
