@@ -1639,7 +1639,8 @@ static int mfcc_tc_setup(mfcc_plan* p, const std::vector<float>& weff, const std
       (rc = upload(&p->d_blk, blk_band)) || (rc = upload(&p->d_blk_off, blk_off)) || (rc = upload(&p->d_w0, w0)) ||
       (rc = upload(&p->d_dctb32, d32)))
     return rc;
-  if (!mfcc_tmap(&p->tm_bh, p->d_bh, ncol, tc::kNUnit) || !mfcc_tmap(&p->tm_bl, p->d_bl, ncol, tc::kNUnit)) return 0;
+  if (!mfcc_tmap(&p->tm_bh, p->d_bh, ncol, tc::kNUnit / tc::kCluster) || !mfcc_tmap(&p->tm_bl, p->d_bl, ncol, tc::kNUnit / tc::kCluster))
+    return 0;
   if (cudaFuncSetAttribute(tc::mfcc_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemBytes) != cudaSuccess) {
     cudaGetLastError();
     return 0;
@@ -1786,7 +1787,7 @@ extern "C" int mfcc_forward(mfcc_plan* p, const mfcc_batch* b, void* stream) {
     ta.w0 = p->d_w0; ta.dctb = p->d_dctb32; ta.feats = a.feats;
     ta.n_frames = b->n_frames; ta.J = a.J; ta.ncep = a.ncep;
     ta.n_tiles = (int)((b->n_frames + tc::kM - 1) / tc::kM);
-    const int grid = std::min(ta.n_tiles, p->sms);
+    const int grid = std::min((ta.n_tiles + tc::kCluster - 1) / tc::kCluster * tc::kCluster, p->sms / tc::kCluster * tc::kCluster);
     tc::mfcc_tc_kernel<<<grid, tc::kThreads, tc::kSmemBytes, st>>>(tm_ah, tm_al, p->tm_bh, p->tm_bl, ta);
     FDLP_CUDA(cudaGetLastError());
 #ifdef FDLP_X_TC_PROF

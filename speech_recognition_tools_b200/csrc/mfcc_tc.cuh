@@ -44,7 +44,12 @@
 // bytes, 320 bytes from the next frame's, so the builders issue 2-byte loads that touch 32 sectors per warp instruction;
 // staging a tile's sample span in shared memory first has no room beside the two 96 KB stages; and four 48 KB stages of
 // 16-sample k-blocks with the 64-byte swizzle (-DFDLP_TC_BK=16: correct, 1.74 against 1.66 ms -- smaller boxes, twice the
-// barrier traffic).  Left: the MMA warp waits for TMA 22 % of the time, and the 2.1 GB round trip of the planes through HBM.
+// barrier traffic).  What bounds the 75 %: bytes INTO the SM.  A k-block brings 96 KB for 12 MMAs = 1600 tensor cycles, i.e.
+// 60 bytes per cycle at full rate against an ingest of ~64 per SM; two variants that cut L2 reads but not the bytes
+// entering each SM changed nothing: pairs of CTAs sharing every B tile by TMA multicast (-DFDLP_TC_CLUSTER=2: cluster
+// launch, multicast loads and multicast tcgen05.commit on the stage barriers: correct, 1.66-1.67 against 1.67-1.71 ms)
+// and L2 eviction hints that keep the frames between a tile's two units (-DFDLP_TC_A_HINT: 1.70 ms).  Only a larger
+// tile per byte would move it (cta_group::2: each SM loads half of B), or fewer bytes per product.
 #pragma once
 #include <cuda.h>
 
@@ -61,6 +66,10 @@ constexpr int kK = 320;                 // samples per frame
 #ifndef FDLP_TC_BK
 #define FDLP_TC_BK 32
 #endif
+#ifndef FDLP_TC_CLUSTER
+#define FDLP_TC_CLUSTER 1
+#endif
+constexpr int kCluster = FDLP_TC_CLUSTER;  // 2: pairs of CTAs (consecutive tiles) share every B tile by TMA multicast
 constexpr int kBK = FDLP_TC_BK;         // tf32 elements per k-block = one swizzle row: 32 (128-byte swizzle) or 16 (64-byte)
 constexpr int kRowBytes = kBK * 4;
 constexpr int kKB = kK / kBK;
@@ -178,6 +187,28 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm,
       "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(x), "r"(y)
       : "memory");
 }
+// the same with an L2 eviction-priority hint (policy words as CUTLASS's TMA::CacheHintSm90 encodes them)
+constexpr uint64_t kEvictFirst = 0x12F0000000000000ull, kEvictLast = 0x14F0000000000000ull;
+__device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int x, int y, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(x), "r"(y), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int x, int y, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(x), "r"(y), "h"(mask)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask)
+               : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
   asm volatile(
       "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
@@ -219,7 +250,11 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr) {
 // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 256, M = 128
 constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kNUnit >> 3) << 17) | ((uint32_t)(kM >> 4) << 24);
 
+#if FDLP_TC_CLUSTER == 2
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+#else
 __global__ void __launch_bounds__(kThreads, 1)
+#endif
 mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant__ CUtensorMap tm_al,
                const __grid_constant__ CUtensorMap tm_bh, const __grid_constant__ CUtensorMap tm_bl, const Args a) {
   extern __shared__ uint8_t smem_raw[];
@@ -247,7 +282,7 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
   for (int i = threadIdx.x; i < kJP; i += kThreads) w0[i] = __ldg(a.w0 + i);
   if (threadIdx.x <= kChunks) blk_off[threadIdx.x] = a.blk_off[threadIdx.x];
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < kStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), kCluster); }
     for (int u = 0; u < kUnits; ++u) { mbar_init(tfull_bar(u), 1); mbar_init(tempty_bar(u), 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -258,8 +293,11 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
   }
   tc_fence_before();
   __syncthreads();
+  if (kCluster > 1) cluster_sync_all();  // the peer's barriers exist before anything is multicast to them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const int crank = (kCluster > 1) ? (int)(blockIdx.x & 1u) : 0;  // rank in the CTA pair; the pair walks tiles tb, tb + 1
+  const int tstart = (int)blockIdx.x - crank;
 #ifdef FDLP_X_TC_PROF
   const long long t_start = clock64();
 #endif
@@ -268,7 +306,8 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
     // ================= TMA producer =================
     if (lane == 0) {
       uint32_t it = 0;
-      for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x)
+      for (int tb = tstart; tb < a.n_tiles; tb += gridDim.x) {
+        const int tile = tb + crank;  // beyond the last tile for the odd CTA of the last pair: zero rows, nothing stored
         for (int u = 0; u < kUnits; ++u)
           for (int kb = 0; kb < kKB; ++kb, ++it) {
             const int s = it % kStages;
@@ -276,16 +315,30 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
             { const long long tp_ = clock64(); mbar_wait(empty_bar(s), ph ^ 1u); if (true) TC_PROF_ADD(0, clock64() - tp_); }
             const uint32_t dst = sbase + (uint32_t)s * kStageBytes;
             mbar_expect_tx(full_bar(s), kStageBytes);
+#ifdef FDLP_TC_A_HINT   // keep the frames in L2 between the two units of a tile, drop them after the second
+            const uint64_t pol = (u == 0) ? kEvictLast : kEvictFirst;
+            tma_load_2d_hint(dst, &tm_ah, full_bar(s), kb * kBK, tile * kM, pol);
+            tma_load_2d_hint(dst + kATile, &tm_al, full_bar(s), kb * kBK, tile * kM, pol);
+#else
             tma_load_2d(dst, &tm_ah, full_bar(s), kb * kBK, tile * kM);
             tma_load_2d(dst + kATile, &tm_al, full_bar(s), kb * kBK, tile * kM);
-            tma_load_2d(dst + 2 * kATile, &tm_bh, full_bar(s), kb * kBK, u * kNUnit);
-            tma_load_2d(dst + 2 * kATile + kBTile, &tm_bl, full_bar(s), kb * kBK, u * kNUnit);
+#endif
+            if (kCluster == 1) {
+              tma_load_2d(dst + 2 * kATile, &tm_bh, full_bar(s), kb * kBK, u * kNUnit);
+              tma_load_2d(dst + 2 * kATile + kBTile, &tm_bl, full_bar(s), kb * kBK, u * kNUnit);
+            } else {  // this CTA fetches its half of the rows of Bh and Bl for both CTAs of the pair
+              const int half = kNUnit / 2;
+              tma_load_2d_mc(dst + 2 * kATile + crank * (kBTile / 2), &tm_bh, full_bar(s), kb * kBK, u * kNUnit + crank * half, 3);
+              tma_load_2d_mc(dst + 2 * kATile + kBTile + crank * (kBTile / 2), &tm_bl, full_bar(s), kb * kBK,
+                             u * kNUnit + crank * half, 3);
+            }
           }
+      }
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
     uint32_t it = 0, tile_it = 0;
-    for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tile_it)
+    for (int tb = tstart; tb < a.n_tiles; tb += gridDim.x, ++tile_it)
       for (int u = 0; u < kUnits; ++u) {
         { const long long tp_ = clock64(); mbar_wait(tempty_bar(u), (tile_it & 1u) ^ 1u); if (lane == 0) TC_PROF_ADD(1, clock64() - tp_); }  // the epilogue has drained this accumulator
         tc_fence_after();
@@ -305,7 +358,8 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
               umma_tf32(d_tmem, dah + o, dbl + o, kIdesc, 1u);
               umma_tf32(d_tmem, dal + o, dbh + o, kIdesc, 1u);
             }
-            umma_commit(empty_bar(s));                      // the stage is free once these MMAs have read it
+            if (kCluster == 1) umma_commit(empty_bar(s));   // the stage is free once these MMAs have read it
+            else umma_commit_mc(empty_bar(s), 3);           // ... for both producers of the pair (each writes into both)
             if (kb == kKB - 1) umma_commit(tfull_bar(u));   // and the accumulator is complete
           }
           __syncwarp();
@@ -316,7 +370,8 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
     const int quarter = warp & 3;  // the TMEM lanes a warp may read: 32 * (warp id % 4)
     const int row = quarter * 32 + lane;
     uint32_t tile_it = 0;
-    for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tile_it) {
+    for (int tb = tstart; tb < a.n_tiles; tb += gridDim.x, ++tile_it) {
+      const int tile = tb + crank;
       float band[kJP];
 #pragma unroll
       for (int j = 0; j < kJP; ++j) band[j] = 0.f;
@@ -412,6 +467,7 @@ mfcc_tc_kernel(const __grid_constant__ CUtensorMap tm_ah, const __grid_constant_
 #endif
   tc_fence_before();
   __syncthreads();
+  if (kCluster > 1) cluster_sync_all();  // no multicast or remote arrival is still on its way to this CTA
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
